@@ -1,0 +1,133 @@
+"""Generate golden fixtures by running the REAL reference module (builder container only).
+
+Needs `/root/reference`; never runs on the GPU box.  Usage:  python oracle/gen_golden.py
+Writes `tests/golden/<case>.pt` holding: the case description (shape, dtype, T, seeds), sha256
+checksums of the regenerated inputs, and the reference's outputs (`gate()` indices + weights,
+`experts_output`, `shared_output`, final output) — the same three tensors the reference's own
+debug dump names (moe.py:160-172).
+
+The reference's `forward` reads a debug safetensors file on every call (moe.py:153-157) that
+exists only on its author's machine; `safetensors.torch.load_file` is monkey-patched to hand
+back placeholders.  Nothing else of the reference is altered.
+"""
+from __future__ import annotations
+
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = "/root/reference"
+
+
+def _load_pkg():
+    sys.path.insert(0, ROOT)
+    import glm4_moe_b200  # noqa: F401  (import shim at the repo root)
+    from glm4_moe_b200 import synth
+    return synth
+
+
+def build_reference_module(shape, dtype):
+    """Instantiate the reference Glm4MoeMoE (moe.py:52-69) under the given default dtype."""
+    sys.path.insert(0, REF)
+    import safetensors.torch as st
+    st.load_file = lambda *a, **k: {"experts_output": torch.zeros(1), "shared_output": torch.zeros(1),
+                                    "final_hidden_states": torch.zeros(1)}
+    from transformers.models.glm4_moe import Glm4MoeConfig
+    from nanovllm.models.glm4_moe.moe import Glm4MoeMoE
+    cfg = Glm4MoeConfig(hidden_size=shape.H, n_routed_experts=shape.E, num_experts_per_tok=shape.k,
+                        moe_intermediate_size=shape.I, n_shared_experts=1, n_group=1, topk_group=1,
+                        routed_scaling_factor=shape.routed_scaling_factor, norm_topk_prob=True)
+    prev = torch.get_default_dtype()
+    torch.set_default_dtype(dtype)
+    try:
+        moe = Glm4MoeMoE(cfg)
+    finally:
+        torch.set_default_dtype(prev)
+    return moe
+
+
+def fill_reference_module(moe, weights):
+    E = len(moe.experts)
+    with torch.no_grad():
+        for e in range(E):
+            moe.experts[e].gate_up_proj.weight.data.copy_(weights["w_gate_up"][e])
+            moe.experts[e].down_proj.weight.data.copy_(weights["w_down"][e])
+        moe.shared_experts.gate_up_proj.weight.data.copy_(weights["w_gate_up"][E])
+        moe.shared_experts.down_proj.weight.data.copy_(weights["w_down"][E])
+        moe.gate.weight.data.copy_(weights["gate_weight"])
+        moe.gate.e_score_correction_bias.copy_(weights["bias"])
+
+
+CASES = [
+    # name, shape name, dtype, T, batch_index, zero_bias
+    ("tiny_fp32_T64", "tiny", torch.float32, 64, 0, False),        # BASELINE.json configs[0]
+    ("mini_bf16_T48", "mini", torch.bfloat16, 48, 0, False),
+    ("mini_fp16_T33", "mini", torch.float16, 33, 1, False),
+    ("mini_bf16_T1", "mini", torch.bfloat16, 1, 2, False),
+    ("small_bf16_T256", "small", torch.bfloat16, 256, 0, False),   # SURVEY probe A6 shape
+]
+ROUTER_ONLY = [
+    # Air / GLM-4.5 router shape only (full weights would be GBs): gate() outputs
+    ("air_router_bf16_T256", "glm-4.5-air", torch.bfloat16, 256, 0),
+    ("glm45_router_bf16_T64", "glm-4.5", torch.bfloat16, 64, 0),
+]
+
+
+def main():
+    synth = _load_pkg()
+    out_dir = os.path.join(ROOT, "tests", "golden")
+    os.makedirs(out_dir, exist_ok=True)
+    torch.set_num_threads(8)
+    for name, sname, dtype, T, bi, zero_bias in CASES:
+        shape = synth.SHAPES[sname]
+        weights = synth.make_weights(shape, dtype, zero_bias=zero_bias)
+        x = synth.make_tokens(shape, T, dtype, bi)
+        moe = build_reference_module(shape, dtype)
+        fill_reference_module(moe, weights)
+        with torch.inference_mode():
+            idx, w = moe.gate(x)
+            final = moe(x)                      # moe.py:128-176
+            shared = moe.shared_experts(x)      # the "shared_output" of moe.py:165-166
+        blob = {
+            "case": {"name": name, "shape": sname, "dtype": str(dtype), "T": T, "batch_index": bi,
+                     "zero_bias": zero_bias, "weight_seed": synth.WEIGHT_SEED,
+                     "token_seed": synth.TOKEN_SEED, "torch": torch.__version__},
+            "sha": {n: synth.tensor_sha256(t) for n, t in weights.items()} | {"x": synth.tensor_sha256(x)},
+            "idx": idx.to(torch.int32), "w": w, "shared_out": shared, "out": final,
+        }
+        torch.save(blob, os.path.join(out_dir, name + ".pt"))
+        print(name, "out", tuple(final.shape), final.dtype, "rms", float(final.float().pow(2).mean().sqrt()))
+    for name, sname, dtype, T, bi in ROUTER_ONLY:
+        shape = synth.SHAPES[sname]
+        gate_w, bias = synth.make_router_weights(shape, dtype)
+        x = synth.make_tokens(shape, T, dtype, bi)
+        sys.path.insert(0, REF)
+        from transformers.models.glm4_moe import Glm4MoeConfig
+        from nanovllm.models.glm4_moe.moe import GlmMoeSelectTopk
+        cfg = Glm4MoeConfig(hidden_size=shape.H, n_routed_experts=shape.E, num_experts_per_tok=shape.k,
+                            moe_intermediate_size=shape.I, n_group=1, topk_group=1,
+                            routed_scaling_factor=shape.routed_scaling_factor)
+        prev = torch.get_default_dtype()
+        torch.set_default_dtype(dtype)
+        try:
+            gate = GlmMoeSelectTopk(cfg)
+        finally:
+            torch.set_default_dtype(prev)
+        with torch.no_grad():
+            gate.weight.data.copy_(gate_w)
+            gate.e_score_correction_bias.copy_(bias)
+        with torch.inference_mode():
+            idx, w = gate(x)
+        blob = {"case": {"name": name, "shape": sname, "dtype": str(dtype), "T": T, "batch_index": bi,
+                         "gate_seed": synth.WEIGHT_SEED + 77, "torch": torch.__version__},
+                "sha": {"gate_weight": synth.tensor_sha256(gate_w), "bias": synth.tensor_sha256(bias),
+                        "x": synth.tensor_sha256(x)},
+                "idx": idx.to(torch.int32), "w": w}
+        torch.save(blob, os.path.join(out_dir, name + ".pt"))
+        print(name, tuple(idx.shape))
+
+
+if __name__ == "__main__":
+    main()

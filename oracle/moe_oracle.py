@@ -1,0 +1,128 @@
+"""CPU ORACLE for the GLM4-MoE sparse-expert path.  TEST INFRASTRUCTURE ONLY.
+
+This file is a torch-CPU restatement of the reference algorithm
+(`/root/reference/nanovllm/models/glm4_moe/moe.py`, `mlp.py`, `layers/activation.py`,
+`layers/linear.py`).  Only `tests/`, `__graft_entry__.smoke()` and the `cpu_baseline` /
+`--impl reference` legs of `bench.py` may import it; the product path never does (and fails
+loudly without its CUDA library).
+
+Parity pin: `tests/golden/*.pt` were produced by importing the *real* reference module in the
+builder container (`oracle/gen_golden.py`, which needs `/root/reference`) and this restatement
+is checked bit-for-bit against them in `tests/test_oracle_golden.py`.  The reference ships no
+golden vectors of its own (its fixtures live on the author's machine), so the
+pin is "outputs of the reference itself, run here".
+
+Third-party arithmetic: every op below executes inside torch (2.11.0 here; the reference
+declares torch>=2.4, pyproject.toml:15).  `torch.topk(sorted=False)` order and tie-breaking
+are implementation-defined; `tie_rule="lowest_index"` is the pinned rule of the CUDA router
+(higher score first, then lower expert id) and equals `torch.topk` whenever the k-th and
+(k+1)-th `scores_for_choice` differ, which the non-zero fp32 bias of §8d makes the normal case.
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn.functional as F
+
+
+# --------------------------------------------------------------------------------------
+# router  (moe.py:28-50)
+# --------------------------------------------------------------------------------------
+def router_logits(h: torch.Tensor, gate_weight: torch.Tensor) -> torch.Tensor:
+    """moe.py:32 — logits in the *model dtype* (not fp32)."""
+    return F.linear(h.reshape(-1, h.shape[-1]), gate_weight)
+
+
+def select_from_logits(logits: torch.Tensor, bias: torch.Tensor, k: int, scale: float,
+                       tie_rule: str = "torch"):
+    """moe.py:37-46 applied to given logits.  Returns (idx int64 [T,k], w model-dtype [T,k])."""
+    scores = logits.sigmoid()                                        # moe.py:37 (model dtype)
+    scores_for_choice = scores + bias.unsqueeze(0)                   # moe.py:38 (fp32: bias is fp32)
+    if tie_rule == "torch":
+        idx = torch.topk(scores_for_choice, k=k, dim=-1, sorted=False)[1]   # moe.py:39
+    elif tie_rule == "lowest_index":
+        idx = torch.sort(scores_for_choice, dim=-1, descending=True, stable=True)[1][:, :k]
+    else:
+        raise ValueError(tie_rule)
+    w = scores.gather(1, idx)                                        # moe.py:41 (un-biased)
+    denom = w.sum(dim=-1, keepdim=True) + 1e-20                      # moe.py:43
+    w = w / denom                                                    # moe.py:44 (unconditional)
+    w = w * scale                                                    # moe.py:46
+    return idx, w
+
+
+def router(h, gate_weight, bias, k, scale, tie_rule="torch"):
+    return select_from_logits(router_logits(h, gate_weight), bias, k, scale, tie_rule)
+
+
+def canonical_routing(idx: torch.Tensor, w: torch.Tensor):
+    """Slot order inside a token is unspecified (sorted=False): sort slots by expert id."""
+    order = torch.argsort(idx, dim=-1, stable=True)
+    return idx.gather(1, order), w.gather(1, order)
+
+
+# --------------------------------------------------------------------------------------
+# implied permutation  (moe.py:135-144; SURVEY §8a-R5, probe A4)
+# --------------------------------------------------------------------------------------
+def permutation(idx: torch.Tensor, n_experts: int):
+    """Expert-major, token-ascending order the reference loop visits (token, slot) pairs in.
+
+    Returns (row_token int32 [T*k], row_slot int32 [T*k], expert_offsets int32 [E+1]).
+    `row_token[r]` is the token feeding sorted row r; `expert_offsets[e]:expert_offsets[e+1]`
+    are the rows of expert e.  Equivalent to a stable sort of the token-major flat list.
+    """
+    T, k = idx.shape
+    flat = idx.reshape(-1).to(torch.int64)
+    order = torch.sort(flat, stable=True)[1]
+    counts = torch.bincount(flat, minlength=n_experts)
+    offsets = torch.zeros(n_experts + 1, dtype=torch.int64)
+    offsets[1:] = torch.cumsum(counts, 0)
+    return (order // k).to(torch.int32), (order % k).to(torch.int32), offsets.to(torch.int32)
+
+
+# --------------------------------------------------------------------------------------
+# expert MLP  (mlp.py:49-54, activation.py:12-14, linear.py:74-75,151-152)
+# --------------------------------------------------------------------------------------
+def expert_mlp(x: torch.Tensor, w_gate_up: torch.Tensor, w_down: torch.Tensor) -> torch.Tensor:
+    gate_up = F.linear(x, w_gate_up)            # [n, 2I]
+    g, u = gate_up.chunk(2, -1)                 # first half = gate (activation.py:13)
+    return F.linear(F.silu(g) * u, w_down)      # [n, H]
+
+
+# --------------------------------------------------------------------------------------
+# full block  (moe.py:128-176 minus the debug file read at :153-157)
+# --------------------------------------------------------------------------------------
+def moe_forward(h: torch.Tensor, weights: dict, k: int, scale: float, routing=None,
+                tie_rule: str = "torch") -> dict:
+    """weights: stacked dict from synth.make_weights (index E of the stacks = shared expert).
+
+    `routing=(idx, w)` forces the routing (used for the fp32 truth run).
+    """
+    w_gu, w_d = weights["w_gate_up"], weights["w_down"]
+    E = w_gu.shape[0] - 1
+    h2 = h.reshape(-1, h.shape[-1])                                  # moe.py:130
+    if routing is None:
+        idx, w = router(h2, weights["gate_weight"], weights["bias"], k, scale, tie_rule)
+    else:
+        idx, w = routing
+    acc = torch.zeros_like(h2)                                       # moe.py:133
+    for e in range(E):                                               # moe.py:135
+        mask = idx == e
+        if not mask.any():
+            continue
+        tok, pos = torch.where(mask)                                 # moe.py:142-143
+        y = expert_mlp(h2[tok], w_gu[e], w_d[e])                     # moe.py:147-148
+        acc.index_add_(0, tok, y * w[tok, pos].unsqueeze(-1).to(y.dtype))   # moe.py:149-151
+    shared = expert_mlp(h2, w_gu[E], w_d[E])                         # moe.py:165
+    return {"out": acc + shared, "experts_out": acc, "shared_out": shared,   # moe.py:171
+            "idx": idx, "w": w}
+
+
+def moe_forward_fp32(h: torch.Tensor, weights: dict, k: int, scale: float, routing) -> dict:
+    """fp32 truth: model-dtype values upcast to fp32, routing forced to the native one."""
+    w32 = {n: t.float() for n, t in weights.items()}
+    idx, w = routing
+    return moe_forward(h.float(), w32, k, scale, routing=(idx, w.float()))
+
+
+def count_experts_hit(idx: torch.Tensor) -> int:
+    return int(torch.unique(idx).numel())
