@@ -1,0 +1,318 @@
+#!/usr/bin/env python
+"""bench.py — GLM-4.5-Air MoE-layer tokens/s on B200 (BASELINE.json metric, configs[1]).
+
+A "step" is one forward of the sparse-expert block over one batch of T synthetic tokens
+(default T=32, the top of north_star's decode 1-32 range).  One JSON line on stdout:
+
+  value      tokens/s with the token batches already resident in HBM (CUDA events, K steps)
+  e2e        same metric through the module's host-buffer entry (pinned host in, pinned host
+             out, H2D + D2H inside the timed region)
+  roofline   HBM roofline of the dominant kernel (gate_up grouped GEMM), timed live with CUDA
+             events between stages (glm4moe_layer_forward_timed)
+  cpu_baseline  the oracle port of the reference's torch path on the box's host cores (N=1, rank 0)
+
+`--impl reference` times the reference's CPU torch path (oracle port — the reference itself
+cannot travel to the GPU box) on the same workload.  N>1: expert-parallel (experts sharded over
+ranks, tokens replicated, partial outputs all-reduced over NCCL/NVLink), strong scaling.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+import glm4_moe_b200  # noqa: E402,F401
+from glm4_moe_b200 import synth  # noqa: E402
+
+METRIC = "GLM-4.5-Air MoE-layer tokens/s"
+UNIT = "tokens/s"
+N_BATCHES = 16          # distinct token batches rotated through the timed region
+
+
+def _peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d["hbm_gbs"], "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """Samples SM clocks / throttle reasons during the timed region (nvidia-smi query fields)."""
+
+    def __init__(self, index: int):
+        self.index, self.samples, self.reasons = index, [], set()
+        self.max_mhz, self._stop, self._thr = None, threading.Event(), None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self._nv = pynvml
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self._nv = None
+
+    def _run(self):
+        nv = self._nv
+        names = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "hw_thermal_slowdown": 0x40,
+                 "sw_thermal_slowdown": 0x20, "hw_power_brake": 0x80}
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksEventReasons(self._h)
+                for n, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(n)
+            except Exception:
+                pass
+            time.sleep(0.02)
+
+    def __enter__(self):
+        if self._nv is not None:
+            self._thr = threading.Thread(target=self._run, daemon=True)
+            self._thr.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        if self._thr:
+            self._thr.join()
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+        return {"sm_mhz": statistics.median(self.samples), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons)}
+
+
+def _hf_config(shape):
+    from transformers.models.glm4_moe import Glm4MoeConfig
+    return Glm4MoeConfig(hidden_size=shape.H, n_routed_experts=shape.E, num_experts_per_tok=shape.k,
+                         moe_intermediate_size=shape.I, n_shared_experts=1, n_group=1, topk_group=1,
+                         routed_scaling_factor=shape.routed_scaling_factor, norm_topk_prob=True)
+
+
+def _cpu_reference_run(shape, dt, weights, T, steps, warmup):
+    """The reference's CPU torch path (oracle port) on the host cores. Returns (tok/s, ms/step)."""
+    from oracle import moe_oracle as O
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    xs = [synth.make_tokens(shape, T, dt, b) for b in range(min(N_BATCHES, steps + warmup))]
+    with torch.inference_mode():
+        for i in range(warmup):
+            O.moe_forward(xs[i % len(xs)], weights, shape.k, shape.routed_scaling_factor)
+        t0 = time.perf_counter()
+        for i in range(steps):
+            O.moe_forward(xs[(warmup + i) % len(xs)], weights, shape.k, shape.routed_scaling_factor)
+        dt_s = time.perf_counter() - t0
+    return T * steps / dt_s, dt_s / steps * 1e3, cores
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--tokens", type=int, default=32, help="tokens per step (decode batch)")
+    ap.add_argument("--shape", default="glm-4.5-air")
+    ap.add_argument("--sweep", action="store_true", help="also report T in {1..256, 4096} in `sweep`")
+    ap.add_argument("--cpu-steps", type=int, default=0, help="cpu_baseline steps (0 = about 15 s of CPU work)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    shape = synth.SHAPES[args.shape]
+    dt = torch.bfloat16
+    T = args.tokens
+    workload = (f"{shape.name} MoE layer (H={shape.H}, E={shape.E}, top-{shape.k}, I={shape.I}, 1 shared) "
+                f"bf16 random-init, decode batch T={T}")
+
+    # ------------------------------------------------------------------ reference arm (CPU)
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        weights = synth.make_weights(shape, dt)
+        steps = max(1, min(args.steps, 8))
+        warm = max(1, min(args.warmup, 2))
+        tps, ms, cores = _cpu_reference_run(shape, dt, weights, T, steps, warm)
+        line = {"metric": METRIC, "value": tps, "unit": UNIT, "impl": "reference", "n_gpus": args.gpus,
+                "steps": steps, "warmup": warm, "ms_per_step": ms, "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+                "config": {"workload": workload, "tokens_per_step": T},
+                "cpu_baseline": {"value": tps, "unit": UNIT, "cores": cores, "kind": "port",
+                                 "sample": f"{steps} steps of the full workload after {warm} warm-up "
+                                           "(oracle port of moe.py:128-176; steps capped at 8)"},
+                "e2e": {"value": tps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        return
+
+    # ------------------------------------------------------------------ our arm (GPU)
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the GLM4-MoE path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    from __graft_entry__ import build
+    if rank == 0:
+        build()
+    if world > 1:
+        dist.barrier()
+
+    weights = synth.make_weights(shape, dt)
+    torch.set_default_dtype(dt)
+    moe = glm4_moe_b200.Glm4MoeMoE(_hf_config(shape), max_tokens=max(T, 256), ep_rank=rank, ep_size=world)
+    torch.set_default_dtype(torch.float32)
+    moe.load_stacked(weights)
+    moe = moe.to(dev)
+    batches_host = [synth.make_tokens(shape, T, dt, b).pin_memory() for b in range(N_BATCHES)]
+    batches = [b.to(dev) for b in batches_host]
+
+    def step(x):
+        y = moe(x)
+        if world > 1:
+            dist.all_reduce(y)
+        return y
+
+    with torch.inference_mode():
+        for i in range(max(args.warmup, 3)):
+            step(batches[i % N_BATCHES])
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with ClockSampler(local_rank) as clk:
+            torch.cuda.synchronize()
+            start.record()
+            for i in range(args.steps):
+                step(batches[i % N_BATCHES])
+            end.record()
+            torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        ms_total = start.elapsed_time(end)
+        if world > 1:
+            t = torch.tensor([ms_total], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms_total = float(t.item())
+        ms_step = ms_total / args.steps
+        launches = moe.last_launches * args.steps
+
+        # per-stage timing (separate loop; an event between stages)
+        stage_acc = {}
+        n_timed = min(args.steps, 50)
+        for i in range(n_timed):
+            _, ms = moe.forward_timed(batches[i % N_BATCHES])
+            for k_, v in ms.items():
+                stage_acc[k_] = stage_acc.get(k_, 0.0) + v / n_timed
+        # experts hit per batch (for the algorithmic bytes)
+        hits = []
+        for b in batches:
+            moe(b)
+            idx = moe.workspace_view("idx", T)
+            local = idx[(idx >= moe.expert_begin) & (idx < moe.expert_end)]
+            hits.append(int(torch.unique(local).numel()))
+        U = sum(hits) / len(hits)
+
+        # end-to-end through the host-buffer entry
+        out_host = torch.empty((T, shape.H), dtype=dt).pin_memory()
+        e2e = None
+        if world == 1:
+            for i in range(3):
+                moe.forward_host(batches_host[i], out_host)
+            t0 = time.perf_counter()
+            for i in range(args.steps):
+                moe.forward_host(batches_host[i % N_BATCHES], out_host)
+            e2e_s = time.perf_counter() - t0
+            e2e = {"value": T * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": T * shape.H * 2,
+                   "d2h_bytes_per_step": T * shape.H * 2, "ms_per_step": e2e_s / args.steps * 1e3}
+
+        sweep = None
+        if args.sweep and world == 1:
+            sweep = []
+            for Ts in (1, 2, 4, 8, 16, 32, 64, 128, 256, 4096):
+                xs = [synth.make_tokens(shape, Ts, dt, 100 + b).to(dev) for b in range(8)]
+                for i in range(5):
+                    moe(xs[i % 8])
+                torch.cuda.synchronize()
+                s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                n = 100 if Ts <= 256 else 20
+                s0.record()
+                for i in range(n):
+                    moe(xs[i % 8])
+                s1.record()
+                torch.cuda.synchronize()
+                ms = s0.elapsed_time(s1) / n
+                us = []
+                for x in xs:
+                    moe(x)
+                    us.append(int(torch.unique(moe.workspace_view("idx", Ts)).numel()))
+                Us = sum(us) / len(us)
+                by = shape.algorithmic_bytes(Ts, Us)
+                fl = shape.flops_per_token() * Ts
+                sweep.append({"T": Ts, "ms": ms, "tokens_per_s": Ts / ms * 1e3, "experts_hit": Us,
+                              "GBps": by / ms / 1e6, "TFLOPs": fl / ms / 1e9,
+                              "tile_rows": moe.last_impl})
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    hbm_peak, peak_src = _peaks()
+    H, I, k = shape.H, shape.I, shape.k
+    # dominant kernel: gate_up grouped GEMM. Algorithmic bytes of one launch = gate_up weights of
+    # the (U local + shared) experts it touches + the activation rows it reads + act rows it writes.
+    n_sh = 1 if moe.with_shared else 0
+    rows = T * k / world + n_sh * T
+    gu_bytes = (U + n_sh) * 2 * I * H * 2 + rows * H * 2 + rows * I * 2
+    gu_ms = stage_acc["gate_up"]
+    achieved = gu_bytes / gu_ms / 1e6
+    layer_bytes = shape.algorithmic_bytes(T, U) if world == 1 else None
+    roofline = {"bound": "hbm", "kernel": "umma_grouped_kernel<gate_up+silu_mul>", "achieved": achieved,
+                "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
+                "peak_source": peak_src, "kernel_ms": gu_ms, "algorithmic_bytes_per_launch": gu_bytes,
+                "stage_ms": stage_acc}
+    if layer_bytes:
+        roofline["layer"] = {"algorithmic_bytes": layer_bytes, "achieved": layer_bytes / ms_step / 1e6,
+                             "frac": layer_bytes / ms_step / 1e6 / hbm_peak}
+    cpu_baseline = None
+    if world == 1 and not args.no_cpu_baseline:
+        n = args.cpu_steps or 40
+        tps, ms, cores = _cpu_reference_run(shape, dt, weights, T, n, 2)
+        cpu_baseline = {"value": tps, "unit": UNIT, "cores": cores, "kind": "port", "ms_per_step": ms,
+                        "sample": f"{n} steps of the same workload (T={T}) after 2 warm-up, oracle port of the "
+                                  "reference torch path (moe.py:128-176), torch threads = all host cores"}
+    line = {"metric": METRIC, "value": T * 1e3 / ms_step, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": workload, "tokens_per_step": T, "experts_hit_mean": U,
+                       "parallelism": f"ep{world}" if world > 1 else "single",
+                       "l2": f"{N_BATCHES} distinct token batches rotated; weights touched per step "
+                             f"({(U + 1) * 3 * H * I * 2 / 1e9:.2f} GB) exceed the 126 MB L2",
+                       "expert_gemm_impl": moe.last_impl},
+            "e2e": e2e, "gpu_launches": launches, "clocks": clk.summary(), "roofline": roofline,
+            "cpu_baseline": cpu_baseline}
+    if sweep:
+        line["sweep"] = sweep
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,113 @@
+"""ctypes binding of `csrc/libglm4moe_b200.so` (header: include/glm4_moe_b200.h).
+
+There is no CPU fallback: if the library is missing or fails to load, every entry point raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import torch
+
+from .build import LIB_PATH
+
+F32, F16, BF16 = 0, 1, 2
+IMPL_AUTO, IMPL_SIMT, IMPL_UMMA = 0, 1, 2
+W_NATIVE, W_FP8_BLOCK128 = 0, 1
+
+DTYPE_CODE = {torch.float32: F32, torch.float16: F16, torch.bfloat16: BF16}
+
+# every symbol include/glm4_moe_b200.h declares (tests check the export list against the header)
+SYMBOLS = [
+    "glm4moe_abi_version", "glm4moe_error_string", "glm4moe_router_logits", "glm4moe_router_select",
+    "glm4moe_permute", "glm4moe_permute_scratch_elems", "glm4moe_tile_capacity", "glm4moe_gather_rows",
+    "glm4moe_expert_gate_up_simt", "glm4moe_expert_down_simt", "glm4moe_combine",
+    "glm4moe_workspace_bytes", "glm4moe_layer_create", "glm4moe_layer_destroy",
+    "glm4moe_layer_forward", "glm4moe_layer_forward_timed", "glm4moe_layer_forward_host", "glm4moe_layer_view",
+    "glm4moe_layer_last_launches", "glm4moe_layer_last_impl", "glm4moe_layer_tile_rows",
+]
+
+
+class Config(C.Structure):
+    """Mirror of `glm4moe_config_t`."""
+    _fields_ = [
+        ("hidden_size", C.c_int32), ("n_routed_experts", C.c_int32),
+        ("num_experts_per_tok", C.c_int32), ("moe_intermediate_size", C.c_int32),
+        ("routed_scaling_factor", C.c_float), ("dtype", C.c_int32), ("weight_format", C.c_int32),
+        ("max_tokens", C.c_int32), ("expert_begin", C.c_int32), ("expert_end", C.c_int32),
+        ("with_shared", C.c_int32), ("impl", C.c_int32),
+    ]
+
+
+class Glm4MoeLibraryError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    """Load the CUDA library; raise loudly when it is not built (no fallback path exists)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise Glm4MoeLibraryError(
+            f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc, sm_100a). The GLM4-MoE path has no CPU or PyTorch fallback.")
+    lib = C.CDLL(LIB_PATH)
+    vp, i32, f32, sz = C.c_void_p, C.c_int, C.c_float, C.c_size_t
+    lib.glm4moe_abi_version.restype = i32
+    lib.glm4moe_error_string.restype = C.c_char_p
+    lib.glm4moe_error_string.argtypes = [i32]
+    lib.glm4moe_router_logits.argtypes = [vp, vp, vp, i32, i32, i32, i32, vp]
+    lib.glm4moe_router_select.argtypes = [vp, vp, i32, i32, i32, f32, i32, vp, vp, vp]
+    lib.glm4moe_permute.argtypes = [vp, vp, i32, i32, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, i32, vp, vp, vp]
+    lib.glm4moe_permute_scratch_elems.restype = sz
+    lib.glm4moe_permute_scratch_elems.argtypes = [i32, i32]
+    lib.glm4moe_tile_capacity.restype = C.c_int32
+    lib.glm4moe_tile_capacity.argtypes = [i32, i32, i32, i32]
+    lib.glm4moe_gather_rows.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp]
+    lib.glm4moe_expert_gate_up_simt.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, vp]
+    lib.glm4moe_expert_down_simt.argtypes = [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp]
+    lib.glm4moe_combine.argtypes = [vp, vp, vp, i32, i32, i32, i32, i32, vp]
+    lib.glm4moe_workspace_bytes.restype = sz
+    lib.glm4moe_workspace_bytes.argtypes = [C.POINTER(Config)]
+    lib.glm4moe_layer_create.argtypes = [C.POINTER(Config), vp, vp, vp, vp, vp, vp, vp, sz, C.POINTER(vp)]
+    lib.glm4moe_layer_destroy.argtypes = [vp]
+    lib.glm4moe_layer_forward.argtypes = [vp, vp, vp, i32, vp]
+    lib.glm4moe_layer_forward_timed.argtypes = [vp, vp, vp, i32, vp, C.POINTER(C.c_float)]
+    lib.glm4moe_layer_forward_host.argtypes = [vp, vp, vp, i32, vp, vp, vp]
+    lib.glm4moe_layer_view.argtypes = [vp, i32, C.POINTER(vp), C.POINTER(sz)]
+    lib.glm4moe_layer_last_launches.argtypes = [vp]
+    lib.glm4moe_layer_last_impl.argtypes = [vp]
+    lib.glm4moe_layer_tile_rows.argtypes = [vp, i32]
+    for name in SYMBOLS:
+        if lib.glm4moe_abi_version is None or not hasattr(lib, name):
+            raise Glm4MoeLibraryError(f"{LIB_PATH} does not export {name}")
+    if lib.glm4moe_abi_version() != 1:
+        raise Glm4MoeLibraryError("ABI version mismatch between _lib.py and the built library")
+    _lib = lib
+    return lib
+
+
+def check(code: int, what: str = "") -> None:
+    if code != 0:
+        msg = load().glm4moe_error_string(code).decode()
+        raise Glm4MoeLibraryError(f"{what or 'glm4moe call'} failed: {msg} (code {code})")
+
+
+def ptr(t: torch.Tensor | None) -> int | None:
+    return None if t is None else t.data_ptr()
+
+
+def stream_ptr(device=None) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def require_cuda(t: torch.Tensor, name: str) -> None:
+    if not t.is_cuda:
+        raise Glm4MoeLibraryError(f"{name} must live on a CUDA device (got {t.device}); "
+                                  "the GLM4-MoE path has no CPU implementation")
+    if not t.is_contiguous():
+        raise Glm4MoeLibraryError(f"{name} must be contiguous")

@@ -1,0 +1,345 @@
+// C-ABI layer object: replaces Glm4MoeMoE.forward (reference moe.py:128-176) with the kernel
+// sequence  router logits -> select -> permute (rank, scan, scatter) -> gather -> gate_up ->
+// down -> combine, all on the caller's stream, no host sync, no allocation (CUDA-graph safe;
+// the reference's decode path replays graphs, model_runner.py:197-213,239-247).
+#include <cuda.h>
+
+#include <cstring>
+#include <new>
+
+#include "common.cuh"
+#include "umma_gemm.cuh"
+
+using namespace glm4moe;
+
+namespace {
+
+constexpr int kSimtRows = 8;
+constexpr int kBnChoices[4] = {16, 32, 64, 128};
+
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+struct WsLayout {
+  size_t logits, idx, w, offsets, row_token, row_weight, slot_row, num_tiles, tiles, scratch, x_rows,
+      act, y, total;
+  int tile_capacity;
+};
+
+WsLayout make_layout(const glm4moe_config_t& c) {
+  WsLayout L{};
+  const size_t T = c.max_tokens, k = c.num_experts_per_tok, E = c.n_routed_experts;
+  const size_t H = c.hidden_size, I = c.moe_intermediate_size, es = dtype_size(c.dtype);
+  const size_t R = T * (k + 1);
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    size_t o = off;
+    off = align_up(off + bytes, 1024);
+    return o;
+  };
+  L.logits = take(T * E * es);
+  L.idx = take(T * k * 4);
+  L.w = take(T * k * 4);
+  L.offsets = take((E + 1) * 4);
+  L.row_token = take(T * k * 4);
+  L.row_weight = take(T * k * 4);
+  L.slot_row = take(T * k * 4);
+  L.num_tiles = take(16);
+  L.tile_capacity = glm4moe_tile_capacity(static_cast<int>(T), static_cast<int>(k), static_cast<int>(E),
+                                          kSimtRows);
+  L.tiles = take(static_cast<size_t>(L.tile_capacity) * 16);
+  L.scratch = take(glm4moe_permute_scratch_elems(static_cast<int>(T), static_cast<int>(E)) * 4);
+  L.x_rows = take(R * H * es);
+  L.act = take(R * I * es);
+  L.y = take(R * H * es);
+  L.total = off;
+  return L;
+}
+
+}  // namespace
+
+struct glm4moe_layer {
+  glm4moe_config_t cfg;
+  WsLayout L;
+  unsigned char* ws;
+  const void* gate_w;
+  const float* bias;
+  const void* w_gate_up;
+  const void* w_down;
+  int sm_count;
+  bool umma_ok;
+  int last_launches;
+  int last_impl;
+  bool events_ready;
+  cudaEvent_t ev[8];
+  alignas(64) CUtensorMap tm_w_gu;
+  alignas(64) CUtensorMap tm_w_d;
+  alignas(64) CUtensorMap tm_x[4];
+  alignas(64) CUtensorMap tm_act[4];
+};
+
+extern "C" int glm4moe_abi_version(void) { return GLM4MOE_ABI_VERSION; }
+
+extern "C" const char* glm4moe_error_string(int code) {
+  switch (code) {
+    case GLM4MOE_OK: return "ok";
+    case GLM4MOE_ERR_ARG: return "invalid argument";
+    case GLM4MOE_ERR_UNSUPPORTED: return "unsupported shape or dtype";
+    case GLM4MOE_ERR_WORKSPACE: return "workspace too small";
+    case GLM4MOE_ERR_DEVICE: return "device/driver does not provide the required sm_100 features";
+    default: return code > 0 ? cudaGetErrorString(static_cast<cudaError_t>(code)) : "unknown error";
+  }
+}
+
+static int check_cfg(const glm4moe_config_t* c) {
+  if (!c) return GLM4MOE_ERR_ARG;
+  if (c->hidden_size <= 0 || c->n_routed_experts <= 0 || c->num_experts_per_tok <= 0 ||
+      c->moe_intermediate_size <= 0 || c->max_tokens <= 0)
+    return GLM4MOE_ERR_ARG;
+  if (c->num_experts_per_tok > c->n_routed_experts || c->n_routed_experts > 256) return GLM4MOE_ERR_UNSUPPORTED;
+  if (c->dtype != GLM4MOE_F32 && c->dtype != GLM4MOE_F16 && c->dtype != GLM4MOE_BF16) return GLM4MOE_ERR_ARG;
+  if (c->expert_begin < 0 || c->expert_end > c->n_routed_experts || c->expert_begin > c->expert_end)
+    return GLM4MOE_ERR_ARG;
+  if (c->weight_format != GLM4MOE_W_NATIVE) return GLM4MOE_ERR_UNSUPPORTED;
+  return GLM4MOE_OK;
+}
+
+extern "C" size_t glm4moe_workspace_bytes(const glm4moe_config_t* cfg) {
+  if (check_cfg(cfg) != GLM4MOE_OK) return 0;
+  return make_layout(*cfg).total;
+}
+
+extern "C" int glm4moe_layer_create(const glm4moe_config_t* cfg, const void* gate_w, const float* bias,
+                                    const void* w_gate_up, const void* w_down, const float* s_gate_up,
+                                    const float* s_down, void* workspace, size_t workspace_bytes,
+                                    glm4moe_layer_t** out) {
+  (void)s_gate_up;
+  (void)s_down;
+  int rc = check_cfg(cfg);
+  if (rc != GLM4MOE_OK) return rc;
+  if (!gate_w || !bias || !w_gate_up || !w_down || !workspace || !out) return GLM4MOE_ERR_ARG;
+  if (reinterpret_cast<uintptr_t>(workspace) % 1024 != 0) return GLM4MOE_ERR_ARG;
+  WsLayout L = make_layout(*cfg);
+  if (workspace_bytes < L.total) return GLM4MOE_ERR_WORKSPACE;
+  glm4moe_layer* l = new (std::nothrow) glm4moe_layer();
+  if (!l) return GLM4MOE_ERR_ARG;
+  l->cfg = *cfg;
+  l->L = L;
+  l->ws = static_cast<unsigned char*>(workspace);
+  l->gate_w = gate_w;
+  l->bias = bias;
+  l->w_gate_up = w_gate_up;
+  l->w_down = w_down;
+  l->last_launches = 0;
+  l->last_impl = GLM4MOE_IMPL_AUTO;
+  l->events_ready = false;
+  int dev = 0;
+  l->sm_count = 148;
+  if (cudaGetDevice(&dev) == cudaSuccess)
+    cudaDeviceGetAttribute(&l->sm_count, cudaDevAttrMultiProcessorCount, dev);
+  const int H = cfg->hidden_size, I = cfg->moe_intermediate_size;
+  l->umma_ok = false;
+  if (cfg->impl != GLM4MOE_IMPL_SIMT && umma_shape_ok(H, I, cfg->dtype)) {
+    const uint64_t n_stack = static_cast<uint64_t>(cfg->expert_end - cfg->expert_begin) + 1;
+    const uint64_t R = static_cast<uint64_t>(cfg->max_tokens) * (cfg->num_experts_per_tok + 1);
+    rc = umma_make_tensor_map(&l->tm_w_gu, w_gate_up, cfg->dtype, n_stack * 2 * I, H, 128);
+    if (rc == GLM4MOE_OK) rc = umma_make_tensor_map(&l->tm_w_d, w_down, cfg->dtype, n_stack * H, I, 128);
+    for (int i = 0; i < 4 && rc == GLM4MOE_OK; ++i) {
+      rc = umma_make_tensor_map(&l->tm_x[i], l->ws + L.x_rows, cfg->dtype, R, H, kBnChoices[i]);
+      if (rc == GLM4MOE_OK)
+        rc = umma_make_tensor_map(&l->tm_act[i], l->ws + L.act, cfg->dtype, R, I, kBnChoices[i]);
+    }
+    if (rc == GLM4MOE_OK) l->umma_ok = true;
+  }
+  if (cfg->impl == GLM4MOE_IMPL_UMMA && !l->umma_ok) {
+    delete l;
+    return rc != GLM4MOE_OK ? rc : GLM4MOE_ERR_UNSUPPORTED;
+  }
+  *out = l;
+  return GLM4MOE_OK;
+}
+
+extern "C" int glm4moe_layer_destroy(glm4moe_layer_t* layer) {
+  if (layer && layer->events_ready)
+    for (int i = 0; i < 8; ++i) cudaEventDestroy(layer->ev[i]);
+  delete layer;
+  return GLM4MOE_OK;
+}
+
+// rows of one token tile on the tensor-core path: sized to the mean rows per local expert so a
+// typical expert is one tile (weights cross HBM once; a second tile re-reads them from L2).
+static int pick_bn_index(const glm4moe_config_t& c, int T) {
+  const int e_local = c.expert_end - c.expert_begin;
+  const double mean = e_local > 0 ? static_cast<double>(T) * c.num_experts_per_tok / c.n_routed_experts : T;
+  if (mean <= 6.0) return 0;
+  if (mean <= 20.0) return 1;
+  if (mean <= 48.0) return 2;
+  return 3;
+}
+
+extern "C" int glm4moe_layer_tile_rows(const glm4moe_layer_t* l, int T) {
+  if (!l) return GLM4MOE_ERR_ARG;
+  return l->umma_ok ? kBnChoices[pick_bn_index(l->cfg, T)] : kSimtRows;
+}
+
+static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, void* stream, cudaEvent_t* ev) {
+  if (!l || !x || !out) return GLM4MOE_ERR_ARG;
+  cudaStream_t cst = static_cast<cudaStream_t>(stream);
+#define STAGE_MARK(i)                                        \
+  do {                                                       \
+    if (ev) GLM4MOE_CUDA_CHECK(cudaEventRecord(ev[i], cst)); \
+  } while (0)
+  const glm4moe_config_t& c = l->cfg;
+  if (T < 0 || T > c.max_tokens) return GLM4MOE_ERR_ARG;
+  if (T == 0) return GLM4MOE_OK;
+  const int H = c.hidden_size, E = c.n_routed_experts, k = c.num_experts_per_tok,
+            I = c.moe_intermediate_size;
+  unsigned char* ws = l->ws;
+  const WsLayout& L = l->L;
+  void* logits = ws + L.logits;
+  int32_t* idx = reinterpret_cast<int32_t*>(ws + L.idx);
+  float* w = reinterpret_cast<float*>(ws + L.w);
+  int32_t* offsets = reinterpret_cast<int32_t*>(ws + L.offsets);
+  int32_t* row_token = reinterpret_cast<int32_t*>(ws + L.row_token);
+  float* row_weight = reinterpret_cast<float*>(ws + L.row_weight);
+  int32_t* slot_row = reinterpret_cast<int32_t*>(ws + L.slot_row);
+  int32_t* num_tiles = reinterpret_cast<int32_t*>(ws + L.num_tiles);
+  int32_t* tiles = reinterpret_cast<int32_t*>(ws + L.tiles);
+  int32_t* scratch = reinterpret_cast<int32_t*>(ws + L.scratch);
+  void* x_rows = ws + L.x_rows;
+  void* act = ws + L.act;
+  void* y = ws + L.y;
+  const bool use_umma = l->umma_ok;
+  const int bi = pick_bn_index(c, T);
+  const int tile_rows = use_umma ? kBnChoices[bi] : kSimtRows;
+  int launches = 0;
+  int rc;
+  STAGE_MARK(0);
+  if ((rc = glm4moe_router_logits(x, l->gate_w, logits, T, H, E, c.dtype, stream))) return rc;
+  STAGE_MARK(1);
+  if ((rc = glm4moe_router_select(logits, l->bias, T, E, k, c.routed_scaling_factor, c.dtype, idx, w, stream)))
+    return rc;
+  STAGE_MARK(2);
+  if ((rc = glm4moe_permute(idx, w, T, k, E, c.expert_begin, c.expert_end, tile_rows, c.with_shared, offsets,
+                            row_token, row_weight, slot_row, tiles, L.tile_capacity, num_tiles, scratch, stream)))
+    return rc;
+  STAGE_MARK(3);
+  if ((rc = glm4moe_gather_rows(x, row_token, offsets, x_rows, T, k, E, H, c.with_shared, c.dtype, stream)))
+    return rc;
+  launches += 6;
+  STAGE_MARK(4);
+  if (use_umma) {
+    UmmaLaunch a{};
+    a.tiles = tiles;
+    a.num_tiles = num_tiles;
+    a.tile_rows = tile_rows;
+    a.dtype = c.dtype;
+    a.grid = l->sm_count;
+    a.row_weight = row_weight;
+    a.n_routed_rows = T * k;
+    // gate_up + SiLU*mul
+    a.tm_w = &l->tm_w_gu;
+    a.tm_x = &l->tm_x[bi];
+    a.out = act;
+    a.ld_out = I;
+    a.n_feat_tiles = I / 128;
+    a.n_kblocks = H / 64;
+    a.w_rows_per_expert = 2 * I;
+    a.up_row_offset = I;
+    a.gated = 1;
+    if ((rc = umma_launch(a, stream))) return rc;
+    STAGE_MARK(5);
+    // down * routing weight
+    a.tm_w = &l->tm_w_d;
+    a.tm_x = &l->tm_act[bi];
+    a.out = y;
+    a.ld_out = H;
+    a.n_feat_tiles = H / 128;
+    a.n_kblocks = I / 64;
+    a.w_rows_per_expert = H;
+    a.up_row_offset = 0;
+    a.gated = 0;
+    if ((rc = umma_launch(a, stream))) return rc;
+  } else {
+    if ((rc = glm4moe_expert_gate_up_simt(x_rows, l->w_gate_up, tiles, num_tiles, act, H, I, tile_rows, c.dtype,
+                                          stream)))
+      return rc;
+    STAGE_MARK(5);
+    if ((rc = glm4moe_expert_down_simt(act, l->w_down, tiles, num_tiles, row_weight, y, H, I, T, k, tile_rows,
+                                       c.dtype, stream)))
+      return rc;
+  }
+  launches += 2;
+  STAGE_MARK(6);
+  if ((rc = glm4moe_combine(y, slot_row, out, T, k, H, c.with_shared, c.dtype, stream))) return rc;
+  STAGE_MARK(7);
+#undef STAGE_MARK
+  launches += 1;
+  l->last_launches = launches;
+  l->last_impl = use_umma ? GLM4MOE_IMPL_UMMA : GLM4MOE_IMPL_SIMT;
+  return GLM4MOE_OK;
+}
+
+extern "C" int glm4moe_layer_forward(glm4moe_layer_t* l, const void* x, void* out, int T, void* stream) {
+  return forward_impl(l, x, out, T, stream, nullptr);
+}
+
+extern "C" int glm4moe_layer_forward_timed(glm4moe_layer_t* l, const void* x, void* out, int T, void* stream,
+                                           float* stage_ms) {
+  if (!l || !stage_ms) return GLM4MOE_ERR_ARG;
+  if (T <= 0) return GLM4MOE_ERR_ARG;
+  if (!l->events_ready) {
+    for (int i = 0; i < 8; ++i) GLM4MOE_CUDA_CHECK(cudaEventCreate(&l->ev[i]));
+    l->events_ready = true;
+  }
+  int rc = forward_impl(l, x, out, T, stream, l->ev);
+  if (rc) return rc;
+  GLM4MOE_CUDA_CHECK(cudaEventSynchronize(l->ev[7]));
+  for (int i = 0; i < 7; ++i) GLM4MOE_CUDA_CHECK(cudaEventElapsedTime(&stage_ms[i], l->ev[i], l->ev[i + 1]));
+  GLM4MOE_CUDA_CHECK(cudaEventElapsedTime(&stage_ms[7], l->ev[0], l->ev[7]));
+  return GLM4MOE_OK;
+}
+
+extern "C" int glm4moe_layer_forward_host(glm4moe_layer_t* l, const void* x_host, void* out_host, int T,
+                                          void* x_dev_staging, void* out_dev_staging, void* stream) {
+  if (!l || !x_host || !out_host || !x_dev_staging || !out_dev_staging) return GLM4MOE_ERR_ARG;
+  if (T < 0 || T > l->cfg.max_tokens) return GLM4MOE_ERR_ARG;
+  if (T == 0) return GLM4MOE_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const size_t bytes = static_cast<size_t>(T) * l->cfg.hidden_size * dtype_size(l->cfg.dtype);
+  GLM4MOE_CUDA_CHECK(cudaMemcpyAsync(x_dev_staging, x_host, bytes, cudaMemcpyHostToDevice, st));
+  int rc = glm4moe_layer_forward(l, x_dev_staging, out_dev_staging, T, stream);
+  if (rc) return rc;
+  GLM4MOE_CUDA_CHECK(cudaMemcpyAsync(out_host, out_dev_staging, bytes, cudaMemcpyDeviceToHost, st));
+  GLM4MOE_CUDA_CHECK(cudaStreamSynchronize(st));
+  return GLM4MOE_OK;
+}
+
+extern "C" int glm4moe_layer_view(glm4moe_layer_t* l, int which, void** ptr, size_t* bytes) {
+  if (!l || !ptr || !bytes) return GLM4MOE_ERR_ARG;
+  const glm4moe_config_t& c = l->cfg;
+  const WsLayout& L = l->L;
+  const size_t T = c.max_tokens, k = c.num_experts_per_tok, E = c.n_routed_experts, H = c.hidden_size,
+               I = c.moe_intermediate_size, es = dtype_size(c.dtype), R = T * (k + 1);
+  size_t off, n;
+  switch (which) {
+    case 0: off = L.idx; n = T * k * 4; break;
+    case 1: off = L.w; n = T * k * 4; break;
+    case 2: off = L.offsets; n = (E + 1) * 4; break;
+    case 3: off = L.row_token; n = T * k * 4; break;
+    case 4: off = L.slot_row; n = T * k * 4; break;
+    case 5: off = L.logits; n = T * E * es; break;
+    case 6: off = L.act; n = R * I * es; break;
+    case 7: off = L.y; n = R * H * es; break;
+    case 8: off = L.num_tiles; n = 4; break;
+    case 9: off = L.tiles; n = static_cast<size_t>(L.tile_capacity) * 16; break;
+    case 10: off = L.x_rows; n = R * H * es; break;
+    case 11: off = L.row_weight; n = T * k * 4; break;
+    default: return GLM4MOE_ERR_ARG;
+  }
+  *ptr = l->ws + off;
+  *bytes = n;
+  return GLM4MOE_OK;
+}
+
+extern "C" int glm4moe_layer_last_launches(const glm4moe_layer_t* l) { return l ? l->last_launches : 0; }
+extern "C" int glm4moe_layer_last_impl(const glm4moe_layer_t* l) { return l ? l->last_impl : 0; }

@@ -1,0 +1,220 @@
+// Permutation kernels: replace the per-expert mask / where / gather loop of the reference
+// (nanovllm/models/glm4_moe/moe.py:135-147) with one histogram + prefix-sum + stable scatter.
+//
+// The order produced is exactly the order the reference loop visits (token, slot) pairs in:
+// expert-major, token-ascending inside an expert.  A token selects an expert
+// at most once, so the rank of token t inside expert e is the number of smaller tokens that
+// selected e — computed from a per-expert bitmap with popcounts, no atomics on the order.
+//
+//   rank_kernel   (grid = ceil(T/256)): per-block bitmap -> local rank of every (t,slot) and the
+//                 per-block per-expert counts
+//   scan_kernel   (1 block): block-exclusive prefix per expert, expert offsets, tile work list
+//   scatter_kernel(grid = ceil(T/256)): row = offsets[e] + block_base[b][e] + local rank
+#include "common.cuh"
+
+namespace glm4moe {
+
+constexpr int kTokPerBlock = 256;
+constexpr int kWordsPerExpert = kTokPerBlock / 32;
+constexpr int kMaxExperts = 256;
+
+__global__ void __launch_bounds__(kTokPerBlock) permute_rank_kernel(
+    const int32_t* __restrict__ idx, int T, int k, int E, int e_lo, int e_hi,
+    int32_t* __restrict__ local_rank /*[T*k]*/, int32_t* __restrict__ block_counts /*[nblk][E]*/) {
+  __shared__ uint32_t bitmap[kMaxExperts * kWordsPerExpert];
+  const int tid = threadIdx.x;
+  const int t = blockIdx.x * kTokPerBlock + tid;
+  for (int i = tid; i < E * kWordsPerExpert; i += kTokPerBlock) bitmap[i] = 0u;
+  __syncthreads();
+  const int word = tid >> 5;
+  const uint32_t bit = 1u << (tid & 31);
+  if (t < T) {
+    for (int s = 0; s < k; ++s) {
+      const int e = idx[static_cast<size_t>(t) * k + s];
+      if (e >= e_lo && e < e_hi) atomicOr(&bitmap[e * kWordsPerExpert + word], bit);
+    }
+  }
+  __syncthreads();
+  if (t < T) {
+    for (int s = 0; s < k; ++s) {
+      const int e = idx[static_cast<size_t>(t) * k + s];
+      int r = -1;
+      if (e >= e_lo && e < e_hi) {
+        const uint32_t* bm = &bitmap[e * kWordsPerExpert];
+        r = __popc(bm[word] & (bit - 1u));
+        for (int wd = 0; wd < word; ++wd) r += __popc(bm[wd]);
+      }
+      local_rank[static_cast<size_t>(t) * k + s] = r;
+    }
+  }
+  for (int e = tid; e < E; e += kTokPerBlock) {
+    int c = 0;
+#pragma unroll
+    for (int wd = 0; wd < kWordsPerExpert; ++wd) c += __popc(bitmap[e * kWordsPerExpert + wd]);
+    block_counts[static_cast<size_t>(blockIdx.x) * E + e] = c;
+  }
+}
+
+// One block of 256 threads; thread e owns expert e.
+__global__ void __launch_bounds__(256) permute_scan_kernel(
+    int32_t* __restrict__ block_counts /*[nblk][E] in: counts, out: exclusive prefix over blocks*/,
+    int nblk, int E, int T, int k, int e_lo, int e_hi, int tile_rows, int with_shared,
+    int32_t* __restrict__ expert_offsets /*[E+1]*/, int4* __restrict__ tiles, int tile_capacity,
+    int32_t* __restrict__ num_tiles) {
+  __shared__ int s_cnt[kMaxExperts];
+  __shared__ int s_off[kMaxExperts + 1];
+  __shared__ int s_tile_off[kMaxExperts + 1];
+  const int e = threadIdx.x;
+  int total = 0;
+  if (e < E) {
+    for (int b = 0; b < nblk; ++b) {
+      const int c = block_counts[static_cast<size_t>(b) * E + e];
+      block_counts[static_cast<size_t>(b) * E + e] = total;
+      total += c;
+    }
+    s_cnt[e] = total;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int off = 0, toff = 0;
+    for (int i = 0; i < E; ++i) {
+      s_off[i] = off;
+      s_tile_off[i] = toff;
+      off += s_cnt[i];
+      toff += (s_cnt[i] + tile_rows - 1) / tile_rows;
+    }
+    s_off[E] = off;
+    s_tile_off[E] = toff;
+    const int shared_tiles = with_shared ? (T + tile_rows - 1) / tile_rows : 0;
+    const int n = toff + shared_tiles;
+    *num_tiles = n <= tile_capacity ? n : 0;   // capacity is sized for the worst case; 0 = refuse
+  }
+  __syncthreads();
+  if (e < E) expert_offsets[e] = s_off[e];
+  if (e == 0) expert_offsets[E] = s_off[E];
+  if (s_tile_off[E] + (with_shared ? (T + tile_rows - 1) / tile_rows : 0) > tile_capacity) return;
+  if (e < E) {
+    const int n = s_cnt[e];
+    int ti = s_tile_off[e];
+    for (int r = 0; r < n; r += tile_rows, ++ti)
+      tiles[ti] = make_int4(e - e_lo, s_off[e] + r, min(tile_rows, n - r), 0);
+  }
+  if (with_shared) {
+    const int base = s_tile_off[E];
+    const int nt = (T + tile_rows - 1) / tile_rows;
+    for (int i = threadIdx.x; i < nt; i += blockDim.x)
+      tiles[base + i] = make_int4(e_hi - e_lo, T * k + i * tile_rows, min(tile_rows, T - i * tile_rows), 0);
+  }
+}
+
+__global__ void __launch_bounds__(kTokPerBlock) permute_scatter_kernel(
+    const int32_t* __restrict__ idx, const float* __restrict__ w, int T, int k, int E,
+    const int32_t* __restrict__ local_rank, const int32_t* __restrict__ block_base,
+    const int32_t* __restrict__ expert_offsets, int32_t* __restrict__ row_token,
+    float* __restrict__ row_weight, int32_t* __restrict__ slot_row) {
+  const int t = blockIdx.x * kTokPerBlock + threadIdx.x;
+  if (t >= T) return;
+  for (int s = 0; s < k; ++s) {
+    const size_t i = static_cast<size_t>(t) * k + s;
+    const int r = local_rank[i];
+    int row = -1;
+    if (r >= 0) {
+      const int e = idx[i];
+      row = expert_offsets[e] + block_base[static_cast<size_t>(blockIdx.x) * E + e] + r;
+      row_token[row] = t;
+      row_weight[row] = w[i];
+    }
+    slot_row[i] = row;
+  }
+}
+
+// x_rows[r] = x[row_token[r]] (routed), x_rows[T*k + t] = x[t] (shared). One warp per row,
+// 128-bit copies.
+template <int kBytesPerElem>
+__global__ void __launch_bounds__(256) gather_rows_kernel(const uint4* __restrict__ x,
+                                                          const int32_t* __restrict__ row_token,
+                                                          const int32_t* __restrict__ expert_offsets,
+                                                          uint4* __restrict__ x_rows, int T, int k,
+                                                          int E, int vec_per_row, int with_shared) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * 8 + warp;
+  const int n_routed = expert_offsets[E];
+  const int Tk = T * k;
+  int src;
+  if (row < Tk) {
+    if (row >= n_routed) return;
+    src = row_token[row];
+  } else {
+    if (!with_shared || row >= Tk + T) return;
+    src = row - Tk;
+  }
+  const uint4* s = x + static_cast<size_t>(src) * vec_per_row;
+  uint4* d = x_rows + static_cast<size_t>(row) * vec_per_row;
+  for (int c = lane; c < vec_per_row; c += 32) d[c] = __ldg(s + c);
+}
+
+}  // namespace glm4moe
+
+using namespace glm4moe;
+
+extern "C" size_t glm4moe_permute_scratch_elems(int T, int E) {
+  const size_t nblk = (static_cast<size_t>(T) + kTokPerBlock - 1) / kTokPerBlock;
+  return (nblk + 1) * static_cast<size_t>(E) + 8;
+}
+
+extern "C" int32_t glm4moe_tile_capacity(int T, int k, int E, int tile_rows) {
+  if (tile_rows <= 0) return 0;
+  // every expert may leave one ragged tile; the shared expert adds ceil(T/tile_rows)
+  return E + (T * k) / tile_rows + (T + tile_rows - 1) / tile_rows + 1;
+}
+
+extern "C" int glm4moe_permute(const int32_t* idx, const float* w, int T, int k, int E, int e_lo,
+                               int e_hi, int tile_rows, int with_shared, int32_t* expert_offsets,
+                               int32_t* row_token, float* row_weight, int32_t* slot_row,
+                               int32_t* tiles, int32_t tile_capacity, int32_t* num_tiles,
+                               int32_t* scratch, void* stream) {
+  if (!idx || !w || !expert_offsets || !row_token || !row_weight || !slot_row || !tiles ||
+      !num_tiles || !scratch)
+    return GLM4MOE_ERR_ARG;
+  if (T < 0 || k <= 0 || E <= 0 || E > kMaxExperts || tile_rows <= 0 || e_lo < 0 || e_hi > E ||
+      e_lo > e_hi)
+    return GLM4MOE_ERR_ARG;
+  if (tile_capacity < glm4moe_tile_capacity(T, k, E, tile_rows)) return GLM4MOE_ERR_WORKSPACE;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int nblk = (T + kTokPerBlock - 1) / kTokPerBlock;
+  int32_t* block_counts = scratch;                       // [nblk][E]
+  // local ranks live in slot_row until the scatter overwrites them in place
+  int32_t* local_rank = slot_row;
+  if (nblk > 0) {
+    permute_rank_kernel<<<nblk, kTokPerBlock, 0, st>>>(idx, T, k, E, e_lo, e_hi, local_rank,
+                                                       block_counts);
+    GLM4MOE_LAUNCH_CHECK();
+  }
+  permute_scan_kernel<<<1, 256, 0, st>>>(block_counts, nblk, E, T, k, e_lo, e_hi, tile_rows, with_shared,
+                                         expert_offsets, reinterpret_cast<int4*>(tiles),
+                                         tile_capacity, num_tiles);
+  GLM4MOE_LAUNCH_CHECK();
+  if (nblk > 0) {
+    permute_scatter_kernel<<<nblk, kTokPerBlock, 0, st>>>(idx, w, T, k, E, local_rank, block_counts,
+                                                          expert_offsets, row_token, row_weight,
+                                                          slot_row);
+    GLM4MOE_LAUNCH_CHECK();
+  }
+  return GLM4MOE_OK;
+}
+
+extern "C" int glm4moe_gather_rows(const void* x, const int32_t* row_token,
+                                   const int32_t* expert_offsets, void* x_rows, int T, int k, int E,
+                                   int H, int with_shared, int dtype, void* stream) {
+  if (!x || !row_token || !expert_offsets || !x_rows) return GLM4MOE_ERR_ARG;
+  const int es = dtype_size(dtype);
+  if ((static_cast<size_t>(H) * es) % 16 != 0) return GLM4MOE_ERR_UNSUPPORTED;
+  if (T == 0) return GLM4MOE_OK;
+  const int rows = T * k + (with_shared ? T : 0);
+  const int vec_per_row = H * es / 16;
+  gather_rows_kernel<2><<<(rows + 7) / 8, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const uint4*>(x), row_token, expert_offsets, static_cast<uint4*>(x_rows), T, k, E,
+      vec_per_row, with_shared);
+  GLM4MOE_LAUNCH_CHECK();
+  return GLM4MOE_OK;
+}

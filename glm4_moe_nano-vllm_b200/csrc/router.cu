@@ -1,0 +1,175 @@
+// Router kernels: replaces GlmMoeSelectTopk.forward (reference nanovllm/models/glm4_moe/moe.py:28-50).
+//
+//   router_logits_kernel  logits[T,E] = h @ Wg^T, fp32 accumulate in a fixed order, one rounding to
+//                         the model dtype (the reference's F.linear output dtype, moe.py:32)
+//   router_select_kernel  warp per token: sigmoid (rounded to model dtype, moe.py:37), + fp32 bias
+//                         (moe.py:38), k rounds of warp-shuffle arg-max with the pinned tie rule
+//                         "higher score, then lower expert id" (moe.py:39), un-biased gather,
+//                         renormalise and scale with the reference's roundings (moe.py:41-46).
+#include "common.cuh"
+
+namespace glm4moe {
+
+// ---------------------------------------------------------------------------------------------
+// logits: block = 8 warps, warp w owns expert (blockIdx.x*8 + w); TT tokens per block.
+// Each lane walks its 16-byte chunks of the expert row once and re-uses it for TT tokens.
+// ---------------------------------------------------------------------------------------------
+template <typename T, int TT>
+__global__ void __launch_bounds__(256) router_logits_kernel(const T* __restrict__ h,
+                                                            const T* __restrict__ gate_w,
+                                                            T* __restrict__ logits, int Tn, int H,
+                                                            int E) {
+  constexpr int V = Dt<T>::kVec;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int e = blockIdx.x * 8 + warp;
+  const int t0 = blockIdx.y * TT;
+  if (e >= E) return;
+  const int nvec = H / V;
+  float acc[TT];
+#pragma unroll
+  for (int i = 0; i < TT; ++i) acc[i] = 0.f;
+  const uint4* wrow = reinterpret_cast<const uint4*>(gate_w + static_cast<size_t>(e) * H);
+  for (int c = lane; c < nvec; c += 32) {
+    float wv[V];
+    unpack16<T>(ld_cached16(wrow + c), wv);
+#pragma unroll
+    for (int i = 0; i < TT; ++i) {
+      const int t = t0 + i;
+      if (t < Tn) {
+        float xv[V];
+        unpack16<T>(ld_cached16(reinterpret_cast<const uint4*>(h + static_cast<size_t>(t) * H) + c), xv);
+#pragma unroll
+        for (int j = 0; j < V; ++j) acc[i] = fmaf(xv[j], wv[j], acc[i]);
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < TT; ++i) {
+    const float s = warp_sum(acc[i]);
+    const int t = t0 + i;
+    if (lane == 0 && t < Tn) logits[static_cast<size_t>(t) * E + e] = Dt<T>::from_f(s);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// select: one warp per token, expert e = j*32 + lane held in register slot j (E <= 256).
+// ---------------------------------------------------------------------------------------------
+constexpr int kMaxSlots = 8;   // E <= 256
+constexpr int kMaxTopK = 32;
+
+template <typename T>
+__global__ void __launch_bounds__(128) router_select_kernel(const T* __restrict__ logits,
+                                                            const float* __restrict__ bias, int Tn,
+                                                            int E, int k, float scale,
+                                                            int32_t* __restrict__ idx_out,
+                                                            float* __restrict__ w_out) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int t = blockIdx.x * 4 + warp;
+  if (t >= Tn) return;
+  float choice[kMaxSlots], score[kMaxSlots];
+#pragma unroll
+  for (int j = 0; j < kMaxSlots; ++j) {
+    const int e = j * 32 + lane;
+    if (e < E) {
+      const float lg = Dt<T>::to_f(logits[static_cast<size_t>(t) * E + e]);
+      const float s = Dt<T>::round(sigmoid_f(lg));       // moe.py:37, model dtype
+      score[j] = s;
+      choice[j] = s + bias[e];                           // moe.py:38, fp32
+    } else {
+      score[j] = 0.f;
+      choice[j] = -INFINITY;
+    }
+  }
+  // k rounds of arg-max; ties -> lower expert id (lane-local scan is ascending in e for fixed
+  // lane, the cross-lane reduction compares (value, id) lexicographically).
+  int my_e = -1;          // lane r keeps the r-th pick
+  float my_s = 0.f;
+  unsigned taken = 0;     // bit j set: my slot j already picked
+  for (int r = 0; r < k; ++r) {
+    float bv = -INFINITY;
+    int be = 0x7fffffff;
+#pragma unroll
+    for (int j = 0; j < kMaxSlots; ++j) {
+      const int e = j * 32 + lane;
+      if (e < E && !((taken >> j) & 1u) && (choice[j] > bv || be == 0x7fffffff)) {
+        bv = choice[j];
+        be = e;
+      }
+    }
+    float bs = 0.f;
+#pragma unroll
+    for (int j = 0; j < kMaxSlots; ++j)
+      if (be == j * 32 + lane) bs = score[j];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+      const int oe = __shfl_xor_sync(0xffffffffu, be, o);
+      const float os = __shfl_xor_sync(0xffffffffu, bs, o);
+      if (oe != 0x7fffffff && (be == 0x7fffffff || ov > bv || (ov == bv && oe < be))) {
+        bv = ov; be = oe; bs = os;
+      }
+    }
+    if ((be & 31) == lane) taken |= 1u << (be >> 5);
+    if (lane == r) { my_e = be; my_s = bs; }
+  }
+  // renormalise: sum in fp32 over the k picks, every intermediate rounded to the model dtype
+  float sum = 0.f;
+  for (int r = 0; r < k; ++r) sum += __shfl_sync(0xffffffffu, my_s, r);
+  const float denom = Dt<T>::round(Dt<T>::round(sum) + 1e-20f);   // moe.py:43
+  float wgt = Dt<T>::round(my_s / denom);                          // moe.py:44
+  wgt = Dt<T>::round(wgt * scale);                                 // moe.py:46
+  // canonical slot order: ascending expert id (the order the reference accumulates in)
+  int rank = 0;
+  for (int r = 0; r < k; ++r) {
+    const int oe = __shfl_sync(0xffffffffu, my_e, r);
+    rank += (lane < k && oe < my_e) ? 1 : 0;
+  }
+  if (lane < k) {
+    idx_out[static_cast<size_t>(t) * k + rank] = my_e;
+    w_out[static_cast<size_t>(t) * k + rank] = wgt;
+  }
+}
+
+template <typename T>
+static int launch_logits(const void* h, const void* gw, void* logits, int T_, int H, int E,
+                         cudaStream_t st) {
+  constexpr int V = Dt<T>::kVec;
+  if (H % V != 0) return GLM4MOE_ERR_UNSUPPORTED;
+  if (T_ <= 2) {
+    dim3 grid((E + 7) / 8, (T_ + 1) / 2);
+    router_logits_kernel<T, 2><<<grid, 256, 0, st>>>(static_cast<const T*>(h), static_cast<const T*>(gw),
+                                                     static_cast<T*>(logits), T_, H, E);
+  } else {
+    dim3 grid((E + 7) / 8, (T_ + 7) / 8);
+    router_logits_kernel<T, 8><<<grid, 256, 0, st>>>(static_cast<const T*>(h), static_cast<const T*>(gw),
+                                                     static_cast<T*>(logits), T_, H, E);
+  }
+  GLM4MOE_LAUNCH_CHECK();
+  return GLM4MOE_OK;
+}
+
+}  // namespace glm4moe
+
+using namespace glm4moe;
+
+extern "C" int glm4moe_router_logits(const void* h, const void* gate_w, void* logits, int T, int H,
+                                     int E, int dtype, void* stream) {
+  if (!h || !gate_w || !logits || T < 0 || H <= 0 || E <= 0) return GLM4MOE_ERR_ARG;
+  if (T == 0) return GLM4MOE_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  GLM4MOE_DISPATCH_DTYPE(dtype, T_, return launch_logits<T_>(h, gate_w, logits, T, H, E, st));
+  return GLM4MOE_OK;
+}
+
+extern "C" int glm4moe_router_select(const void* logits, const float* bias, int T, int E, int k,
+                                     float scale, int dtype, int32_t* idx, float* w, void* stream) {
+  if (!logits || !bias || !idx || !w || T < 0) return GLM4MOE_ERR_ARG;
+  if (E <= 0 || E > 32 * kMaxSlots || k <= 0 || k > kMaxTopK || k > E) return GLM4MOE_ERR_UNSUPPORTED;
+  if (T == 0) return GLM4MOE_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  GLM4MOE_DISPATCH_DTYPE(dtype, T_,
+                         (router_select_kernel<T_><<<(T + 3) / 4, 128, 0, st>>>(
+                             static_cast<const T_*>(logits), bias, T, E, k, scale, idx, w)));
+  GLM4MOE_LAUNCH_CHECK();
+  return GLM4MOE_OK;
+}

@@ -1,0 +1,425 @@
+// Grouped expert GEMMs on the 5th-generation tensor cores (tcgen05 + TMEM + TMA), sm_100a only.
+//
+// Replaces the per-expert F.linear calls of the reference (mlp.py:50,52 -> linear.py:75,152),
+// with SiLU-and-mul (activation.py:13-14) fused into the gate_up epilogue and the routing-weight
+// scale (moe.py:149) fused into the down epilogue.
+//
+// Orientation ("swap-AB"): the *weights* are the M=128 operand and the *token rows* are the N
+// operand, D[feature, token] = sum_k W[e][feature, k] * X[row(token), k].  An expert with n_e
+// rows costs ceil(n_e / BN) MMAs of N = BN (16..128) per weight tile, so the decode regime
+// (n_e = 1..8) streams every weight byte through shared memory exactly once while the tensor
+// pipe stays far from its limit, and the prefill regime uses the same kernel with BN = 128.
+//
+// CTA = 8 warps, warp-specialised, persistent over a device-side work list (tile x feature-tile):
+//   warp 0  TMA producer: weights [128 x 64] (+ the matching up_proj tile when GATED) and the
+//           activation tile [BN x 64] per k-block into a kStages-deep 128B-swizzled smem ring
+//   warp 1  MMA issuer (one elected lane): 4 x tcgen05.mma (K=16) per k-block per accumulator
+//   warp 2  TMEM allocator / deallocator
+//   warps 4-7 epilogue: tcgen05.ld 32 lanes x 16 columns, fused math, coalesced 2-byte stores
+//           (lane = output feature, so a warp writes 64 contiguous bytes per token)
+// Pipelines: smem full/empty mbarriers (TMA <-> MMA) and 2 TMEM accumulator stages
+// (MMA <-> epilogue) so the epilogue of tile i overlaps the MMAs of tile i+1.
+#include <cuda.h>
+
+#include <type_traits>
+
+#include "common.cuh"
+#include "umma_gemm.cuh"
+
+namespace glm4moe {
+
+// ------------------------------------------------------------------------------------------
+// PTX wrappers
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.b32 %0, 1, 0, p;\n\t"
+      "}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  while (!mbar_try_wait(bar, parity)) {
+  }
+}
+__device__ __forceinline__ void fence_barrier_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void tma_load_2d(const CUtensorMap* map, uint64_t* bar, void* dst, int c0,
+                                            int c1, uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.L2::cache_hint"
+      " [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(smem_u32(dst)),
+      "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "l"(policy)
+      : "memory");
+}
+__device__ __forceinline__ void prefetch_tmap(const CUtensorMap* map) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() {
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_after() {
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+template <int kCols>
+__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                   smem_u32(dst_smem)),
+               "n"(kCols));
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+}
+template <int kCols>
+__device__ __forceinline__ void tmem_dealloc(uint32_t addr) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "n"(kCols));
+}
+// D[tmem] (+)= A[smem desc] * B[smem desc], kind::f16 (bf16 or fp16 inputs, fp32 accumulate)
+__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc,
+                                         uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}\n" ::"r"(d_tmem),
+      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrive on an mbarrier once every previously issued tcgen05.mma of this thread has completed
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+                   smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* r) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]),
+        "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]),
+        "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld_wait() {
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred = 0;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred P;\n\t"
+      "elect.sync _|P, 0xffffffff;\n\t"
+      "selp.b32 %0, 1, 0, P;\n\t"
+      "}\n"
+      : "=r"(pred));
+  return pred != 0;
+}
+
+// K-major operand tile, rows of 64 two-byte elements = one 128-byte swizzle atom per row:
+// start address >> 4 | LBO (unused for a single K atom) | SBO = 8 rows * 128 B | version 1 |
+// layout SWIZZLE_128B.  Advancing K by 16 elements inside the atom = +32 bytes on the address.
+__device__ __forceinline__ uint64_t make_kmajor_desc(uint32_t saddr) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((saddr >> 4) & 0x3fffu);
+  d |= static_cast<uint64_t>(1024u >> 4) << 32;   // stride byte offset between 8-row groups
+  d |= static_cast<uint64_t>(1) << 46;            // descriptor version (sm_100)
+  d |= static_cast<uint64_t>(2) << 61;            // SWIZZLE_128B
+  return d;
+}
+
+// instruction descriptor, kind::f16: D fp32, A/B both K-major, M = 128, N = n
+__host__ __device__ constexpr uint32_t make_idesc(bool bf16, int n) {
+  return (1u << 4)                         // c_format = F32
+         | ((bf16 ? 1u : 0u) << 7)         // a_format
+         | ((bf16 ? 1u : 0u) << 10)        // b_format
+         | (static_cast<uint32_t>(n >> 3) << 17) | (static_cast<uint32_t>(128 >> 4) << 24);
+}
+
+constexpr uint64_t kEvictFirst = 0x12F0000000000000ull;   // weights: touched once
+constexpr uint64_t kEvictLast = 0x14F0000000000000ull;    // activation rows: re-read per feature tile
+
+constexpr int kBM = 128;   // weight rows (output features) per tile
+constexpr int kBK = 64;    // 64 two-byte elements = 128 B swizzle atom
+
+template <int BN, bool GATED>
+struct UmmaCfg {
+  static constexpr int kABytes = kBM * kBK * 2;                 // 16 KB per weight tile
+  static constexpr int kBBytes = BN * kBK * 2;
+  static constexpr int kStageBytes = (GATED ? 2 : 1) * kABytes + kBBytes;
+  static constexpr int kStages = (212 * 1024) / kStageBytes > 12 ? 12 : (212 * 1024) / kStageBytes;
+  static constexpr int kAccCols = (GATED ? 2 : 1) * BN;         // TMEM columns per accumulator stage
+  static constexpr int kTmemColsRaw = 2 * kAccCols;
+  static constexpr int kTmemCols = kTmemColsRaw <= 32 ? 32 : kTmemColsRaw <= 64 ? 64
+                                   : kTmemColsRaw <= 128 ? 128 : kTmemColsRaw <= 256 ? 256 : 512;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+  static_assert(kTmemColsRaw <= 512, "accumulators do not fit TMEM");
+  static_assert(kBBytes % 1024 == 0, "operand tiles must stay 1024-byte aligned");
+};
+
+// ------------------------------------------------------------------------------------------
+// the kernel
+// ------------------------------------------------------------------------------------------
+template <typename T, int BN, bool GATED>
+__global__ void __launch_bounds__(256, 1) umma_grouped_kernel(
+    const __grid_constant__ CUtensorMap tm_w,   // weights  [rows_w_total, K], box {64, 128}
+    const __grid_constant__ CUtensorMap tm_x,   // activation rows [rows_x_total, K], box {64, BN}
+    const int4* __restrict__ tiles, const int32_t* __restrict__ num_tiles_ptr,
+    T* __restrict__ out, int ld_out,            // out[row, feature]
+    const float* __restrict__ row_weight,       // !GATED: per-row scale for rows < n_routed_rows
+    int n_routed_rows, int n_feat_tiles, int n_kblocks,
+    int w_rows_per_expert,                      // GATED: 2I, else H
+    int up_row_offset) {                        // GATED: I
+  using Cfg = UmmaCfg<BN, GATED>;
+  extern __shared__ unsigned char smem_dyn[];
+  unsigned char* smem = reinterpret_cast<unsigned char*>(
+      (reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~static_cast<uintptr_t>(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
+  uint64_t* full_bar = bars;
+  uint64_t* empty_bar = bars + Cfg::kStages;
+  uint64_t* tmem_full = bars + 2 * Cfg::kStages;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tm_w);
+    prefetch_tmap(&tm_x);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < Cfg::kStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tmem_full[s], 1);
+      mbar_init(&tmem_empty[s], 4);   // one arrive per epilogue warp
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc<Cfg::kTmemCols>(tmem_ptr_smem);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  const int total_work = *num_tiles_ptr * n_feat_tiles;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+        const int ti = w / n_feat_tiles, f = w - ti * n_feat_tiles;
+        const int4 tile = tiles[ti];
+        const int w_row = tile.x * w_rows_per_expert + f * kBM;
+        for (int kb = 0; kb < n_kblocks; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1u);
+          unsigned char* sa = smem + stage * Cfg::kStageBytes;
+          mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+          tma_load_2d(&tm_w, &full_bar[stage], sa, kb * kBK, w_row, kEvictFirst);
+          if (GATED)
+            tma_load_2d(&tm_w, &full_bar[stage], sa + Cfg::kABytes, kb * kBK, w_row + up_row_offset,
+                        kEvictFirst);
+          tma_load_2d(&tm_x, &full_bar[stage], sa + (GATED ? 2 : 1) * Cfg::kABytes, kb * kBK, tile.y,
+                      kEvictLast);
+          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    constexpr uint32_t idesc = make_idesc(sizeof(T) == 2 && !std::is_same<T, __half>::value, BN);
+    int stage = 0;
+    uint32_t phase = 0;
+    int it = 0;
+    for (int w = blockIdx.x; w < total_work; w += gridDim.x, ++it) {
+      const int as = it & 1;
+      const uint32_t aphase = (it >> 1) & 1u;
+      mbar_wait(&tmem_empty[as], aphase ^ 1u);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + as * Cfg::kAccCols;
+      for (int kb = 0; kb < n_kblocks; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
+          const uint64_t a_desc = make_kmajor_desc(sa);
+          const uint64_t b_desc = make_kmajor_desc(sa + (GATED ? 2 : 1) * Cfg::kABytes);
+#pragma unroll
+          for (int ks = 0; ks < kBK / 16; ++ks) {
+            const uint32_t acc = (kb > 0 || ks > 0) ? 1u : 0u;
+            umma_f16(d_tmem, a_desc + 2 * ks, b_desc + 2 * ks, idesc, acc);
+            if (GATED) {
+              const uint64_t u_desc = make_kmajor_desc(sa + Cfg::kABytes);
+              umma_f16(d_tmem + BN, u_desc + 2 * ks, b_desc + 2 * ks, idesc, acc);
+            }
+          }
+          umma_commit(&empty_bar[stage]);                       // smem slot free when MMAs finish
+          if (kb == n_kblocks - 1) umma_commit(&tmem_full[as]); // accumulator ready
+        }
+        __syncwarp();
+        if (++stage == Cfg::kStages) { stage = 0; phase ^= 1u; }
+      }
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue =====================
+    const int ew = warp - 4;                      // TMEM lanes [32*ew, 32*ew+32)
+    const uint32_t lane_base = static_cast<uint32_t>(ew * 32) << 16;
+    int it = 0;
+    for (int w = blockIdx.x; w < total_work; w += gridDim.x, ++it) {
+      const int ti = w / n_feat_tiles, f = w - ti * n_feat_tiles;
+      const int4 tile = tiles[ti];
+      const int as = it & 1;
+      const uint32_t aphase = (it >> 1) & 1u;
+      mbar_wait(&tmem_full[as], aphase);
+      tc_fence_after();
+      const uint32_t t_acc = tmem_base + lane_base + as * Cfg::kAccCols;
+      const int feat = f * kBM + ew * 32 + lane;
+      T* out_col = out + static_cast<size_t>(tile.y) * ld_out + feat;
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 16) {
+        if (c0 >= tile.z) break;                  // warp-uniform: remaining token columns unused
+        uint32_t g[16];
+        tmem_ld16(t_acc + c0, g);
+        if (GATED) {
+          uint32_t u[16];
+          tmem_ld16(t_acc + BN + c0, u);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            if (c0 + j < tile.z) {
+              const float v = silu_f(__uint_as_float(g[j])) * __uint_as_float(u[j]);
+              out_col[static_cast<size_t>(c0 + j) * ld_out] = Dt<T>::from_f(v);
+            }
+          }
+        } else {
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            if (c0 + j < tile.z) {
+              const int row = tile.y + c0 + j;
+              const float rw = row < n_routed_rows ? __ldg(row_weight + row) : 1.0f;
+              out_col[static_cast<size_t>(c0 + j) * ld_out] = Dt<T>::from_f(__uint_as_float(g[j]) * rw);
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty[as]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+}
+
+// ------------------------------------------------------------------------------------------
+// host side: tensor maps + launch
+// ------------------------------------------------------------------------------------------
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                    const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                    const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled get_encode_fn() {
+  static PFN_encodeTiled fn = nullptr;
+  if (fn) return fn;
+  void* p = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+      q != cudaDriverEntryPointSuccess)
+    return nullptr;
+  fn = reinterpret_cast<PFN_encodeTiled>(p);
+  return fn;
+}
+
+int umma_make_tensor_map(void* map_out, const void* base, int dtype, uint64_t rows, uint64_t cols,
+                         uint32_t box_rows) {
+  PFN_encodeTiled enc = get_encode_fn();
+  if (!enc) return GLM4MOE_ERR_DEVICE;
+  if (dtype != GLM4MOE_BF16 && dtype != GLM4MOE_F16) return GLM4MOE_ERR_UNSUPPORTED;
+  if (cols % 8 != 0 || box_rows == 0 || box_rows > 256 || rows == 0) return GLM4MOE_ERR_ARG;
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {cols * 2};
+  cuuint32_t box[2] = {static_cast<cuuint32_t>(kBK), box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(static_cast<CUtensorMap*>(map_out),
+                   dtype == GLM4MOE_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16,
+                   2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? GLM4MOE_OK : GLM4MOE_ERR_ARG;
+}
+
+template <typename T, int BN, bool GATED>
+static int launch_one(const UmmaLaunch& a, cudaStream_t st) {
+  using Cfg = UmmaCfg<BN, GATED>;
+  auto kern = umma_grouped_kernel<T, BN, GATED>;
+  static bool attr_set = false;   // per instantiation
+  if (!attr_set) {
+    GLM4MOE_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            Cfg::kSmemBytes));
+    attr_set = true;
+  }
+  kern<<<a.grid, 256, Cfg::kSmemBytes, st>>>(
+      *static_cast<const CUtensorMap*>(a.tm_w), *static_cast<const CUtensorMap*>(a.tm_x),
+      reinterpret_cast<const int4*>(a.tiles), a.num_tiles, static_cast<T*>(a.out), a.ld_out,
+      a.row_weight, a.n_routed_rows, a.n_feat_tiles, a.n_kblocks, a.w_rows_per_expert,
+      a.up_row_offset);
+  GLM4MOE_LAUNCH_CHECK();
+  return GLM4MOE_OK;
+}
+
+template <typename T, bool GATED>
+static int launch_bn(const UmmaLaunch& a, cudaStream_t st) {
+  switch (a.tile_rows) {
+    case 16: return launch_one<T, 16, GATED>(a, st);
+    case 32: return launch_one<T, 32, GATED>(a, st);
+    case 64: return launch_one<T, 64, GATED>(a, st);
+    case 128: return launch_one<T, 128, GATED>(a, st);
+    default: return GLM4MOE_ERR_ARG;
+  }
+}
+
+int umma_launch(const UmmaLaunch& a, void* stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (a.dtype == GLM4MOE_BF16)
+    return a.gated ? launch_bn<__nv_bfloat16, true>(a, st) : launch_bn<__nv_bfloat16, false>(a, st);
+  if (a.dtype == GLM4MOE_F16)
+    return a.gated ? launch_bn<__half, true>(a, st) : launch_bn<__half, false>(a, st);
+  return GLM4MOE_ERR_UNSUPPORTED;
+}
+
+bool umma_shape_ok(int H, int I, int dtype) {
+  return (dtype == GLM4MOE_BF16 || dtype == GLM4MOE_F16) && H % kBM == 0 && I % kBM == 0;
+}
+
+}  // namespace glm4moe

@@ -1,0 +1,379 @@
+"""Drop-in replacement for the reference's GLM4-MoE sparse block.
+
+Mirrors `nanovllm/models/glm4_moe/moe.py` (`GlmMoeSelectTopk` :13-50, `Glm4MoeMoE` :52-176) and
+`nanovllm/models/glm4_moe/mlp.py` (`Glm4MoeMLP` :12-54): same constructor argument, same
+`forward(hidden_states)`, same `load_weights(path, prefix)`, same parameter / buffer names
+(`experts.{i}.gate_up_proj.weight`, `experts.{i}.down_proj.weight`, `gate.weight`,
+`gate.e_score_correction_bias`, `shared_experts.*`).  The decoder layer swaps it in by importing
+this `Glm4MoeMoE` instead of the reference's at `decode_layer.py:6`.
+
+Differences that are deliberate: the debug safetensors read of
+moe.py:153-157 is gone; expert weights live in two stacked tensors (`[E+1, 2I, H]`, `[E+1, H, I]`,
+last index = shared expert) of which the per-expert parameters are views; the combine
+accumulates in fp32; the loader matches keys exactly (the reference's `startswith` at
+mlp.py:96 lets `experts.1` also match `experts.10`..).  All compute runs in the CUDA library
+(`csrc/`, C ABI in `include/glm4_moe_b200.h`); there is no CPU path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import torch
+from torch import nn
+
+from . import _lib
+
+_VIEW = {"idx": 0, "w": 1, "expert_offsets": 2, "row_token": 3, "slot_row": 4, "logits": 5,
+         "act": 6, "y": 7, "num_tiles": 8, "tiles": 9, "x_rows": 10, "row_weight": 11}
+_IMPL = {"auto": _lib.IMPL_AUTO, "simt": _lib.IMPL_SIMT, "umma": _lib.IMPL_UMMA}
+
+
+class _Weight(nn.Module):
+    """Stand-in for the reference's linear layers (linear.py:56-155): only `.weight` [out, in]."""
+
+    def __init__(self, view: torch.Tensor):
+        super().__init__()
+        self.weight = nn.Parameter(view, requires_grad=False)
+
+
+class Glm4MoeMLP(nn.Module):
+    """One expert: `gate_up_proj.weight [2I, H]` (rows [0,I) gate, [I,2I) up — mlp.py:118) and
+    `down_proj.weight [H, I]`, both views into the owning block's stacks (mlp.py:27-38)."""
+
+    def __init__(self, gate_up_view: torch.Tensor, down_view: torch.Tensor, hidden_act: str = "silu"):
+        super().__init__()
+        if hidden_act.lower() != "silu":      # mlp.py:41-44
+            raise ValueError(f"Unsupported activation: {hidden_act}. Only silu is supported for now.")
+        self.gate_up_proj = _Weight(gate_up_view)
+        self.down_proj = _Weight(down_view)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        """mlp.py:49-54 for one expert, through the CUDA-core expert kernels (exact path)."""
+        lib = _lib.load()
+        wgu, wd = self.gate_up_proj.weight, self.down_proj.weight
+        x2 = x.reshape(-1, x.shape[-1]).contiguous()
+        _lib.require_cuda(x2, "x")
+        n, H = x2.shape
+        I = wd.shape[1]
+        dt = _lib.DTYPE_CODE[x2.dtype]
+        dev = x2.device
+        ntile = (n + 7) // 8
+        tiles = torch.tensor([[0, 8 * i, min(8, n - 8 * i), 0] for i in range(ntile)], dtype=torch.int32,
+                             device=dev).reshape(-1, 4)
+        num = torch.tensor([ntile], dtype=torch.int32, device=dev)
+        act = torch.empty((n, I), dtype=x2.dtype, device=dev)
+        y = torch.empty((n, H), dtype=x2.dtype, device=dev)
+        ones = torch.ones(max(n, 1), dtype=torch.float32, device=dev)
+        st = _lib.stream_ptr(dev)
+        if n:
+            _lib.check(lib.glm4moe_expert_gate_up_simt(x2.data_ptr(), wgu.data_ptr(), tiles.data_ptr(),
+                                                       num.data_ptr(), act.data_ptr(), H, I, 8, dt, st), "gate_up")
+            # T*k = n with k = 1 so every row takes its weight (1.0) from `ones`
+            _lib.check(lib.glm4moe_expert_down_simt(act.data_ptr(), wd.data_ptr(), tiles.data_ptr(),
+                                                    num.data_ptr(), ones.data_ptr(), y.data_ptr(), H, I, n, 1,
+                                                    8, dt, st), "down")
+        return y
+
+
+class GlmMoeSelectTopk(nn.Module):
+    """Router (moe.py:13-50): returns `(topk_indices int64 [T,k], topk_weights model-dtype [T,k])`.
+    Slots come back sorted by ascending expert id (the reference's order is unspecified,
+    `torch.topk(sorted=False)`); ties are broken towards the lower expert id."""
+
+    def __init__(self, config):
+        super().__init__()
+        self.config = config
+        self.top_k = config.num_experts_per_tok
+        self.n_routed_experts = config.n_routed_experts
+        assert config.n_group == 1          # moe.py:21
+        assert config.topk_group == 1       # moe.py:22
+        self.routed_scaling_factor = config.routed_scaling_factor
+        self.weight = nn.Parameter(torch.empty((self.n_routed_experts, config.hidden_size)),
+                                   requires_grad=False)
+        self.register_buffer("e_score_correction_bias",
+                             torch.zeros((self.n_routed_experts,), dtype=torch.float32))
+
+    def forward(self, hidden_states: torch.Tensor, return_logits: bool = False):
+        lib = _lib.load()
+        H = self.config.hidden_size
+        h = hidden_states.reshape(-1, H).contiguous()
+        _lib.require_cuda(h, "hidden_states")
+        if h.dtype != self.weight.dtype:
+            raise _lib.Glm4MoeLibraryError(f"hidden_states dtype {h.dtype} != router dtype {self.weight.dtype}")
+        T, E, k = h.shape[0], self.n_routed_experts, self.top_k
+        dt = _lib.DTYPE_CODE[h.dtype]
+        logits = torch.empty((T, E), dtype=h.dtype, device=h.device)
+        idx = torch.empty((T, k), dtype=torch.int32, device=h.device)
+        w = torch.empty((T, k), dtype=torch.float32, device=h.device)
+        st = _lib.stream_ptr(h.device)
+        _lib.check(lib.glm4moe_router_logits(h.data_ptr(), self.weight.data_ptr(), logits.data_ptr(), T, H, E, dt, st),
+                   "router_logits")
+        _lib.check(lib.glm4moe_router_select(logits.data_ptr(), self.e_score_correction_bias.data_ptr(), T, E, k,
+                                             float(self.routed_scaling_factor), dt, idx.data_ptr(), w.data_ptr(), st),
+                   "router_select")
+        out = (idx.to(torch.int64), w.to(h.dtype))
+        return out + (logits,) if return_logits else out
+
+
+class Glm4MoeMoE(nn.Module):
+    """GLM4-MoE sparse block (moe.py:52-176).
+
+    Extra keyword arguments (all default to the reference's single-GPU behaviour):
+      max_tokens   initial workspace capacity in tokens (grows on demand outside graph capture)
+      ep_rank/ep_size  expert-parallel shard: this module then owns experts
+                   [rank*E/size, (rank+1)*E/size) and `forward` returns the *partial* sum over the
+                   local experts (+ the shared expert on rank 0 only); see distributed.py
+      impl         "auto" | "simt" | "umma": expert-GEMM implementation
+    """
+
+    def __init__(self, config, *, max_tokens: int = 256, ep_rank: int = 0, ep_size: int = 1,
+                 impl: str = "auto"):
+        super().__init__()
+        self.config = config
+        E, H, I = config.n_routed_experts, config.hidden_size, config.moe_intermediate_size
+        if E % ep_size != 0:
+            raise ValueError(f"n_routed_experts={E} not divisible by ep_size={ep_size}")
+        self.ep_rank, self.ep_size = ep_rank, ep_size
+        self.expert_begin = ep_rank * (E // ep_size)
+        self.expert_end = self.expert_begin + E // ep_size
+        self.with_shared = ep_rank == 0
+        self.impl = impl
+        n_local = self.expert_end - self.expert_begin
+        # stacked storage, created under the process-wide default dtype/device like the
+        # reference's parameters (model_runner.py:29-31)
+        self._w_gate_up = torch.empty((n_local + 1, 2 * I, H))
+        self._w_down = torch.empty((n_local + 1, H, I))
+        self.experts = nn.ModuleList(
+            [Glm4MoeMLP(self._w_gate_up[i], self._w_down[i], config.hidden_act) for i in range(n_local)])
+        self.gate = GlmMoeSelectTopk(config)
+        self.shared_experts = Glm4MoeMLP(self._w_gate_up[n_local], self._w_down[n_local], config.hidden_act)
+        self._max_tokens = int(max_tokens)
+        self._handle = None
+        self._workspace = None
+        self._host = None
+
+    # ---- storage management -------------------------------------------------------------
+    def _mlps(self):
+        return list(self.experts) + [self.shared_experts]
+
+    def _apply(self, fn, recurse=True):
+        """Keep per-expert parameters aliased to the stacks across .to()/.cuda()/.half()."""
+        self._destroy_handle()
+        self._w_gate_up = fn(self._w_gate_up)
+        self._w_down = fn(self._w_down)
+        out = super()._apply(fn, recurse)
+        for i, mlp in enumerate(self._mlps()):
+            mlp.gate_up_proj.weight.data = self._w_gate_up[i]
+            mlp.down_proj.weight.data = self._w_down[i]
+        return out
+
+    def _destroy_handle(self):
+        if getattr(self, "_handle", None) is not None:
+            _lib.load().glm4moe_layer_destroy(self._handle)
+        self._handle = None
+        self._workspace = None
+        self._host = None
+
+    def __del__(self):
+        try:
+            self._destroy_handle()
+        except Exception:
+            pass
+
+    def _lib_config(self, max_tokens: int) -> _lib.Config:
+        c = self.config
+        return _lib.Config(c.hidden_size, c.n_routed_experts, c.num_experts_per_tok, c.moe_intermediate_size,
+                           float(c.routed_scaling_factor), _lib.DTYPE_CODE[self._w_gate_up.dtype], _lib.W_NATIVE,
+                           max_tokens, self.expert_begin, self.expert_end, int(self.with_shared),
+                           _IMPL[self.impl])
+
+    def _ensure_layer(self, T: int):
+        if self._handle is not None and T <= self._max_tokens:
+            return
+        lib = _lib.load()
+        _lib.require_cuda(self._w_gate_up, "expert weights")
+        if torch.cuda.is_current_stream_capturing():
+            raise _lib.Glm4MoeLibraryError(
+                f"workspace for {T} tokens must exist before CUDA-graph capture (run a warm-up forward first)")
+        self._destroy_handle()
+        cap = max(self._max_tokens, 1)
+        while cap < T:
+            cap *= 2
+        self._max_tokens = cap
+        cfg = self._lib_config(cap)
+        nbytes = lib.glm4moe_workspace_bytes(C.byref(cfg))
+        if nbytes == 0:
+            raise _lib.Glm4MoeLibraryError("unsupported GLM4-MoE configuration for the CUDA library")
+        dev = self._w_gate_up.device
+        self._workspace = torch.empty(nbytes + 1024, dtype=torch.uint8, device=dev)
+        base = (self._workspace.data_ptr() + 1023) // 1024 * 1024
+        handle = C.c_void_p()
+        with torch.cuda.device(dev):
+            _lib.check(lib.glm4moe_layer_create(C.byref(cfg), self.gate.weight.data_ptr(),
+                                                self.gate.e_score_correction_bias.data_ptr(),
+                                                self._w_gate_up.data_ptr(), self._w_down.data_ptr(), None, None,
+                                                base, nbytes, C.byref(handle)), "layer_create")
+        self._handle = handle
+        self._cfg = cfg
+
+    # ---- reference API ----------------------------------------------------------------------
+    def forward(self, hidden_states: torch.Tensor) -> torch.Tensor:
+        """moe.py:128-176: returns a fresh 2-D `[T, H]` tensor; the input is not modified."""
+        h = hidden_states.reshape(-1, hidden_states.shape[-1])
+        if not h.is_contiguous():
+            h = h.contiguous()
+        _lib.require_cuda(h, "hidden_states")
+        if h.dtype != self._w_gate_up.dtype:
+            raise _lib.Glm4MoeLibraryError(f"hidden_states dtype {h.dtype} != weight dtype {self._w_gate_up.dtype}")
+        T = h.shape[0]
+        out = torch.empty_like(h)
+        if T == 0:
+            return out
+        self._ensure_layer(T)
+        with torch.cuda.device(h.device):
+            _lib.check(_lib.load().glm4moe_layer_forward(self._handle, h.data_ptr(), out.data_ptr(), T,
+                                                        _lib.stream_ptr(h.device)), "layer_forward")
+        return out
+
+    STAGES = ("router_logits", "router_select", "permute", "gather", "gate_up", "down", "combine", "total")
+
+    def forward_timed(self, hidden_states: torch.Tensor):
+        """`forward` with a CUDA event between stages; returns (out, {stage: ms})."""
+        h = hidden_states.reshape(-1, hidden_states.shape[-1]).contiguous()
+        _lib.require_cuda(h, "hidden_states")
+        T = h.shape[0]
+        out = torch.empty_like(h)
+        self._ensure_layer(T)
+        ms = (C.c_float * 8)()
+        with torch.cuda.device(h.device):
+            _lib.check(_lib.load().glm4moe_layer_forward_timed(self._handle, h.data_ptr(), out.data_ptr(), T,
+                                                              _lib.stream_ptr(h.device), ms), "layer_forward_timed")
+        return out, dict(zip(self.STAGES, list(ms)))
+
+    def forward_host(self, hidden_states_host: torch.Tensor, out_host: torch.Tensor | None = None) -> torch.Tensor:
+        """Host-buffer entry (`glm4moe_layer_forward_host`): H2D copy, forward, D2H copy, sync."""
+        h = hidden_states_host.reshape(-1, hidden_states_host.shape[-1])
+        if h.is_cuda or not h.is_contiguous():
+            raise _lib.Glm4MoeLibraryError("forward_host expects a contiguous host tensor")
+        T, H = h.shape
+        self._ensure_layer(T)
+        dev = self._w_gate_up.device
+        if self._host is None or self._host[0].shape[0] < T:
+            self._host = (torch.empty((self._max_tokens, H), dtype=h.dtype, device=dev),
+                          torch.empty((self._max_tokens, H), dtype=h.dtype, device=dev))
+        if out_host is None:
+            out_host = torch.empty((T, H), dtype=h.dtype, pin_memory=True)
+        with torch.cuda.device(dev):
+            _lib.check(_lib.load().glm4moe_layer_forward_host(self._handle, h.data_ptr(), out_host.data_ptr(), T,
+                                                             self._host[0].data_ptr(), self._host[1].data_ptr(),
+                                                             _lib.stream_ptr(dev)), "layer_forward_host")
+        return out_host
+
+    def load_weights(self, path: str, prefix: str):
+        """moe.py:71-126 + mlp.py:83-131: HF keys -> parameters, one pass, exact key match.
+
+        Keys: `{p}.gate.weight`, `{p}.gate.e_score_correction_bias`,
+        `{p}.experts.{i}.{gate_proj,up_proj,down_proj}.weight`, `{p}.shared_experts.*`;
+        gate_proj and up_proj are concatenated along dim 0 (mlp.py:118), nothing is transposed.
+        """
+        from safetensors import safe_open
+        if os.path.isdir(path):
+            files = sorted(os.path.join(path, f) for f in os.listdir(path) if f.endswith(".safetensors"))
+        else:
+            files = [path]
+        I = self.config.moe_intermediate_size
+        n_local = self.expert_end - self.expert_begin
+        found = 0
+        seen = set()
+        with torch.no_grad():
+            for fn in files:
+                with safe_open(fn, framework="pt", device="cpu") as f:
+                    for key in f.keys():
+                        if not key.startswith(prefix + "."):
+                            continue
+                        found += 1
+                        rest = key[len(prefix) + 1:]
+                        if rest == "gate.weight":
+                            self.gate.weight.data.copy_(f.get_tensor(key))
+                        elif rest == "gate.e_score_correction_bias":
+                            self.gate.e_score_correction_bias.copy_(f.get_tensor(key))
+                        else:
+                            parts = rest.split(".")
+                            if parts[0] == "experts" and len(parts) == 4 and parts[3] == "weight":
+                                e = int(parts[1])
+                                if not (self.expert_begin <= e < self.expert_end):
+                                    continue
+                                slot, proj = e - self.expert_begin, parts[2]
+                            elif parts[0] == "shared_experts" and len(parts) == 3 and parts[2] == "weight":
+                                slot, proj = n_local, parts[1]
+                            else:
+                                continue
+                            t = f.get_tensor(key)
+                            if proj == "gate_proj":
+                                assert t.shape == self._w_gate_up[slot, :I].shape, f"{key}: {tuple(t.shape)}"
+                                self._w_gate_up[slot, :I].copy_(t)
+                            elif proj == "up_proj":
+                                assert t.shape == self._w_gate_up[slot, I:].shape, f"{key}: {tuple(t.shape)}"
+                                self._w_gate_up[slot, I:].copy_(t)
+                            elif proj == "down_proj":
+                                assert t.shape == self._w_down[slot].shape, f"{key}: {tuple(t.shape)}"
+                                self._w_down[slot].copy_(t)
+                            else:
+                                continue
+                            seen.add((slot, proj))
+        if not found:
+            raise ValueError(f"No tensors with prefix '{prefix}' found in '{path}'")   # moe.py:94-95
+        for slot in range(n_local + 1):
+            for proj in ("gate_proj", "up_proj", "down_proj"):
+                assert (slot, proj) in seen, f"{proj}.weight missing for expert slot {slot}"   # mlp.py:113-115
+
+    # ---- helpers used by tests / bench -------------------------------------------------------
+    def load_stacked(self, weights: dict):
+        """Fill from the stacked synthetic dict of `synth.make_weights` (full E+1 stacks)."""
+        with torch.no_grad():
+            sl = list(range(self.expert_begin, self.expert_end)) + [self.config.n_routed_experts]
+            self._w_gate_up.copy_(weights["w_gate_up"][sl])
+            self._w_down.copy_(weights["w_down"][sl])
+            self.gate.weight.data.copy_(weights["gate_weight"])
+            self.gate.e_score_correction_bias.copy_(weights["bias"])
+
+    def workspace_view(self, name: str, T: int | None = None) -> torch.Tensor:
+        """Typed copy of a workspace region after a forward (parity triage)."""
+        lib = _lib.load()
+        p, n = C.c_void_p(), C.c_size_t()
+        _lib.check(lib.glm4moe_layer_view(self._handle, _VIEW[name], C.byref(p), C.byref(n)), "layer_view")
+        base = (self._workspace.data_ptr() + 1023) // 1024 * 1024
+        off = p.value - base
+        raw = self._workspace[(base - self._workspace.data_ptr()) + off:][:n.value]
+        c = self.config
+        k, E, H, I = c.num_experts_per_tok, c.n_routed_experts, c.hidden_size, c.moe_intermediate_size
+        md = self._w_gate_up.dtype
+        if name in ("idx", "row_token", "slot_row", "expert_offsets", "num_tiles", "tiles"):
+            t = raw.view(torch.int32)
+            if name in ("idx", "slot_row"):
+                t = t.view(-1, k)
+            if name == "tiles":
+                t = t.view(-1, 4)
+        elif name in ("w", "row_weight"):
+            t = raw.view(torch.float32)
+            if name == "w":
+                t = t.view(-1, k)
+        elif name == "logits":
+            t = raw.view(md).view(-1, E)
+        elif name == "act":
+            t = raw.view(md).view(-1, I)
+        else:
+            t = raw.view(md).view(-1, H)
+        if T is not None and name in ("idx", "w", "slot_row", "logits"):
+            t = t[:T]
+        return t.clone()
+
+    @property
+    def last_launches(self) -> int:
+        return _lib.load().glm4moe_layer_last_launches(self._handle) if self._handle else 0
+
+    @property
+    def last_impl(self) -> str:
+        code = _lib.load().glm4moe_layer_last_impl(self._handle) if self._handle else 0
+        return {0: "none", 1: "simt", 2: "umma"}[code]

@@ -1,0 +1,137 @@
+/*
+ * glm4_moe_b200.h — C ABI of the B200-native GLM4-MoE sparse-expert block.
+ *
+ * Drop-in boundary for the reference's MoE layer (a Python nn.Module; the reference has no FFI
+ * of its own).  Each entry point names the reference code it replaces.
+ * All pointers are raw device pointers unless the name says `_host`; sizes are element counts;
+ * `stream` is a `cudaStream_t` passed as `void*`.  No entry point allocates device memory,
+ * none synchronises except `glm4moe_layer_forward_host`.  Return value: 0 = ok, <0 = argument /
+ * support error (GLM4MOE_ERR_*), >0 = `cudaError_t`.
+ *
+ * Row space used by permute / expert GEMMs / combine:
+ *   rows [0, T*k)        routed rows, expert-major, token-ascending inside an expert
+ *                        (the order the reference loop visits them, moe.py:135-143)
+ *   rows [T*k, T*k + T)  the always-on shared expert, token order (moe.py:165)
+ */
+#ifndef GLM4_MOE_B200_H
+#define GLM4_MOE_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GLM4MOE_ABI_VERSION 1
+
+enum { GLM4MOE_F32 = 0, GLM4MOE_F16 = 1, GLM4MOE_BF16 = 2 };          /* model dtype */
+enum { GLM4MOE_W_NATIVE = 0, GLM4MOE_W_FP8_BLOCK128 = 1 };            /* expert weight format */
+enum { GLM4MOE_IMPL_AUTO = 0, GLM4MOE_IMPL_SIMT = 1, GLM4MOE_IMPL_UMMA = 2 };
+
+#define GLM4MOE_OK 0
+#define GLM4MOE_ERR_ARG (-1)          /* bad pointer / size / alignment */
+#define GLM4MOE_ERR_UNSUPPORTED (-2)  /* shape or dtype outside what the kernels cover */
+#define GLM4MOE_ERR_WORKSPACE (-3)    /* workspace too small */
+#define GLM4MOE_ERR_DEVICE (-4)       /* not an sm_100 device / driver entry point missing */
+
+typedef struct glm4moe_config {
+  int32_t hidden_size;            /* H   (Glm4MoeConfig.hidden_size) */
+  int32_t n_routed_experts;       /* E   */
+  int32_t num_experts_per_tok;    /* k   */
+  int32_t moe_intermediate_size;  /* I   (also the shared expert's width, moe.py:65-69) */
+  float routed_scaling_factor;    /* moe.py:24,46 */
+  int32_t dtype;                  /* GLM4MOE_F32 / F16 / BF16: activations, router, outputs */
+  int32_t weight_format;          /* GLM4MOE_W_* for the expert stacks */
+  int32_t max_tokens;             /* largest T any forward will see (workspace sizing) */
+  int32_t expert_begin;           /* expert-parallel: this rank owns experts [begin, end) */
+  int32_t expert_end;             /*   (0, E) on a single GPU                              */
+  int32_t with_shared;            /* 1: add the shared expert (moe.py:165,171); 0: routed partial only */
+  int32_t impl;                   /* GLM4MOE_IMPL_* (AUTO picks tcgen05 when the shape allows) */
+} glm4moe_config_t;
+
+typedef struct glm4moe_layer glm4moe_layer_t;   /* opaque */
+
+int glm4moe_abi_version(void);
+const char* glm4moe_error_string(int code);
+
+/* ---- router: replaces GlmMoeSelectTopk.forward (moe.py:28-50) ------------------------------ */
+/* logits[T,E] = h[T,H] @ gate_w[E,H]^T, fp32 accumulate, rounded to the model dtype (moe.py:32) */
+int glm4moe_router_logits(const void* h, const void* gate_w, void* logits, int T, int H, int E,
+                          int dtype, void* stream);
+/* sigmoid -> +bias(fp32) -> top-k (higher score, then lower expert id) -> gather un-biased
+ * scores -> renormalise (+1e-20) -> * scale, with the model-dtype roundings of moe.py:37-46.
+ * idx[T,k] int32, slots sorted by ascending expert id; w[T,k] fp32 holding model-dtype values. */
+int glm4moe_router_select(const void* logits, const float* bias, int T, int E, int k, float scale,
+                          int dtype, int32_t* idx, float* w, void* stream);
+
+/* ---- permutation: replaces the mask / where / gather loop (moe.py:135-147) ------------------ */
+/* Stable expert-major order of the (token, slot) pairs whose expert is in [e_lo, e_hi).
+ *   expert_offsets[E+1]  rows of expert e are [offsets[e], offsets[e+1])
+ *   row_token[T*k]       token feeding row r          row_weight[T*k]  its routing weight
+ *   slot_row[T*k]        row of (t, slot), -1 if that expert is not local
+ *   tiles[cap] int4      {expert - e_lo, row_start, nrows, 0} work list in `tile_rows` chunks
+ *                        (index into the local weight stack), the shared expert's tiles last
+ *                        (stack index e_hi - e_lo); *num_tiles = its length
+ * scratch: int32[(ceil(T/256)+1) * E + 8].                                                     */
+int glm4moe_permute(const int32_t* idx, const float* w, int T, int k, int E, int e_lo, int e_hi,
+                    int tile_rows, int with_shared, int32_t* expert_offsets, int32_t* row_token,
+                    float* row_weight, int32_t* slot_row, int32_t* tiles, int32_t tile_capacity,
+                    int32_t* num_tiles, int32_t* scratch, void* stream);
+size_t glm4moe_permute_scratch_elems(int T, int E);
+int32_t glm4moe_tile_capacity(int T, int k, int E, int tile_rows);
+
+/* x_rows[r,:] = x[row_token[r],:] for routed rows, x_rows[T*k + t,:] = x[t,:]  (moe.py:147) */
+int glm4moe_gather_rows(const void* x, const int32_t* row_token, const int32_t* expert_offsets,
+                        void* x_rows, int T, int k, int E, int H, int with_shared, int dtype,
+                        void* stream);
+
+/* ---- expert MLP: replaces Glm4MoeMLP.forward over every hit expert + the shared expert ------ */
+/* act[r, :I] = silu(x_rows[r] @ Wg^T) * (x_rows[r] @ Wu^T)   (mlp.py:50-51, activation.py:13-14)
+ * w_gate_up: stacked [E+1, 2I, H], rows [0,I) gate, [I,2I) up (mlp.py:118); index E = shared.  */
+int glm4moe_expert_gate_up_simt(const void* x_rows, const void* w_gate_up, const int32_t* tiles,
+                                const int32_t* num_tiles, void* act, int H, int I, int tile_rows,
+                                int dtype, void* stream);
+/* y[r, :H] = (act[r] @ Wd^T) * row_weight[r]   (mlp.py:52, moe.py:149); shared rows weight 1 */
+int glm4moe_expert_down_simt(const void* act, const void* w_down, const int32_t* tiles,
+                             const int32_t* num_tiles, const float* row_weight, void* y, int H,
+                             int I, int T, int k, int tile_rows, int dtype, void* stream);
+
+/* ---- combine: replaces index_add_ + shared add (moe.py:151,171) ----------------------------- */
+/* out[t] = sum_{slot, ascending expert} y[slot_row[t,slot]] (+ y[T*k+t]); fp32 accumulate.     */
+int glm4moe_combine(const void* y, const int32_t* slot_row, void* out, int T, int k, int H,
+                    int with_shared, int dtype, void* stream);
+
+/* ---- whole layer: replaces Glm4MoeMoE.forward (moe.py:128-176) ------------------------------ */
+size_t glm4moe_workspace_bytes(const glm4moe_config_t* cfg);
+/* w_gate_up [E_local+1, 2I, H], w_down [E_local+1, H, I] hold experts [begin,end) then the
+ * shared expert.  s_* are the fp32 128x128 block scales of the FP8 format (NULL otherwise).     */
+int glm4moe_layer_create(const glm4moe_config_t* cfg, const void* gate_w, const float* bias,
+                         const void* w_gate_up, const void* w_down, const float* s_gate_up,
+                         const float* s_down, void* workspace, size_t workspace_bytes,
+                         glm4moe_layer_t** out);
+int glm4moe_layer_destroy(glm4moe_layer_t* layer);
+int glm4moe_layer_forward(glm4moe_layer_t* layer, const void* x, void* out, int T, void* stream);
+/* Same launches, with a CUDA event recorded on `stream` before every stage; after the last event
+ * completes, stage_ms[0..6] = {router_logits, router_select, permute, gather, gate_up, down,
+ * combine} durations and stage_ms[7] = the whole sequence (bench.py's per-kernel roofline).     */
+int glm4moe_layer_forward_timed(glm4moe_layer_t* layer, const void* x, void* out, int T, void* stream,
+                                float* stage_ms);
+/* Host-buffer entry: H2D of x_host (pinned or pageable), forward, D2H into out_host, stream sync. */
+int glm4moe_layer_forward_host(glm4moe_layer_t* layer, const void* x_host, void* out_host, int T,
+                               void* x_dev_staging, void* out_dev_staging, void* stream);
+/* Debug views into the workspace after a forward (parity triage; mirrors the reference's
+ * experts_output / shared_output dump idea, moe.py:160-172).
+ * which: 0 idx[T,k] i32, 1 w[T,k] f32, 2 expert_offsets[E+1] i32, 3 row_token[T*k] i32,
+ *        4 slot_row[T*k] i32, 5 logits[T,E] model dtype, 6 act rows, 7 y rows, 8 num_tiles i32,
+ *        9 tiles int4, 10 x_rows, 11 row_weight f32.                                           */
+int glm4moe_layer_view(glm4moe_layer_t* layer, int which, void** ptr, size_t* bytes);
+/* number of kernels the last forward launched, and which expert-GEMM implementation it used */
+int glm4moe_layer_last_launches(const glm4moe_layer_t* layer);
+int glm4moe_layer_last_impl(const glm4moe_layer_t* layer);
+int glm4moe_layer_tile_rows(const glm4moe_layer_t* layer, int T);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GLM4_MOE_B200_H */

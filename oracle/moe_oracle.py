@@ -92,10 +92,12 @@ def expert_mlp(x: torch.Tensor, w_gate_up: torch.Tensor, w_down: torch.Tensor) -
 # full block  (moe.py:128-176 minus the debug file read at :153-157)
 # --------------------------------------------------------------------------------------
 def moe_forward(h: torch.Tensor, weights: dict, k: int, scale: float, routing=None,
-                tie_rule: str = "torch") -> dict:
+                tie_rule: str = "torch", compute_dtype=None) -> dict:
     """weights: stacked dict from synth.make_weights (index E of the stacks = shared expert).
 
     `routing=(idx, w)` forces the routing (used for the fp32 truth run).
+    `compute_dtype` upcasts tokens and each expert's weights on the fly (fp32 truth without
+    materialising an fp32 copy of a multi-GB stack).
     """
     w_gu, w_d = weights["w_gate_up"], weights["w_down"]
     E = w_gu.shape[0] - 1
@@ -104,24 +106,25 @@ def moe_forward(h: torch.Tensor, weights: dict, k: int, scale: float, routing=No
         idx, w = router(h2, weights["gate_weight"], weights["bias"], k, scale, tie_rule)
     else:
         idx, w = routing
+    cast = (lambda t: t) if compute_dtype is None else (lambda t: t.to(compute_dtype))
+    h2 = cast(h2)
+    w = cast(w)
     acc = torch.zeros_like(h2)                                       # moe.py:133
     for e in range(E):                                               # moe.py:135
         mask = idx == e
         if not mask.any():
             continue
         tok, pos = torch.where(mask)                                 # moe.py:142-143
-        y = expert_mlp(h2[tok], w_gu[e], w_d[e])                     # moe.py:147-148
-        acc.index_add_(0, tok, y * w[tok, pos].unsqueeze(-1).to(y.dtype))   # moe.py:149-151
-    shared = expert_mlp(h2, w_gu[E], w_d[E])                         # moe.py:165
+        y = expert_mlp(h2[tok], cast(w_gu[e]), cast(w_d[e]))         # moe.py:147-148
+        acc.index_add_(0, tok, y * w[tok, pos].unsqueeze(-1))        # moe.py:149-151
+    shared = expert_mlp(h2, cast(w_gu[E]), cast(w_d[E]))             # moe.py:165
     return {"out": acc + shared, "experts_out": acc, "shared_out": shared,   # moe.py:171
             "idx": idx, "w": w}
 
 
 def moe_forward_fp32(h: torch.Tensor, weights: dict, k: int, scale: float, routing) -> dict:
     """fp32 truth: model-dtype values upcast to fp32, routing forced to the native one."""
-    w32 = {n: t.float() for n, t in weights.items()}
-    idx, w = routing
-    return moe_forward(h.float(), w32, k, scale, routing=(idx, w.float()))
+    return moe_forward(h, weights, k, scale, routing=routing, compute_dtype=torch.float32)
 
 
 def count_experts_hit(idx: torch.Tensor) -> int:

@@ -1,0 +1,116 @@
+"""CPU: the C-ABI library builds, loads and exports every symbol include/glm4_moe_b200.h declares;
+host-side module logic (parameter names, stack aliasing, loader, loud failure without CUDA)."""
+import os
+import re
+
+import pytest
+import torch
+
+import glm4_moe_b200
+from glm4_moe_b200 import synth
+from glm4_moe_b200 import _lib
+from glm4_moe_b200.build import build_library, LIB_PATH
+from conftest import ROOT
+
+
+@pytest.fixture(scope="session", autouse=True)
+def built_library():
+    build_library()
+    assert os.path.exists(LIB_PATH)
+
+
+def _cfg(shape):
+    from transformers.models.glm4_moe import Glm4MoeConfig
+    return Glm4MoeConfig(hidden_size=shape.H, n_routed_experts=shape.E, num_experts_per_tok=shape.k,
+                         moe_intermediate_size=shape.I, n_shared_experts=1, n_group=1, topk_group=1,
+                         routed_scaling_factor=shape.routed_scaling_factor, norm_topk_prob=True)
+
+
+def test_header_symbols_are_exported():
+    hdr = open(os.path.join(ROOT, "include", "glm4_moe_b200.h")).read()
+    declared = set(re.findall(r"\b(glm4moe_[a-z0-9_]+)\s*\(", hdr))
+    assert declared == set(_lib.SYMBOLS), declared ^ set(_lib.SYMBOLS)
+    lib = _lib.load()
+    for name in declared:
+        assert hasattr(lib, name), name
+    assert lib.glm4moe_abi_version() == 1
+    assert lib.glm4moe_error_string(-2).decode().startswith("unsupported")
+
+
+def test_no_torch_types_in_abi():
+    hdr = open(os.path.join(ROOT, "include", "glm4_moe_b200.h")).read()
+    assert "torch" not in hdr and "at::" not in hdr and "Tensor" not in hdr
+
+
+def test_workspace_and_arg_errors_without_gpu():
+    lib = _lib.load()
+    import ctypes as C
+    s = synth.AIR
+    cfg = _lib.Config(s.H, s.E, s.k, s.I, 1.0, _lib.BF16, _lib.W_NATIVE, 256, 0, s.E, 1, 0)
+    n = lib.glm4moe_workspace_bytes(C.byref(cfg))
+    rows = 256 * (s.k + 1)
+    assert n > rows * (2 * s.H + s.I) * 2          # x_rows + y + act at least
+    bad = _lib.Config(s.H, 300, s.k, s.I, 1.0, _lib.BF16, 0, 256, 0, 300, 1, 0)   # E > 256
+    assert lib.glm4moe_workspace_bytes(C.byref(bad)) == 0
+    assert lib.glm4moe_router_logits(None, None, None, 1, 8, 8, _lib.BF16, None) == -1
+    assert lib.glm4moe_tile_capacity(32, 8, 128, 16) == 128 + 16 + 2 + 1
+
+
+def test_module_names_match_reference_and_alias_stacks():
+    shape = synth.TINY
+    moe = glm4_moe_b200.Glm4MoeMoE(_cfg(shape))
+    names = [n for n, _ in moe.named_parameters()]
+    assert len(names) == 2 * shape.E + 3          # 35 parameters at E=16
+    assert "experts.0.gate_up_proj.weight" in names and "experts.15.down_proj.weight" in names
+    assert "gate.weight" in names and "shared_experts.gate_up_proj.weight" in names
+    assert [n for n, _ in moe.named_buffers()] == ["gate.e_score_correction_bias"]
+    assert moe.gate.e_score_correction_bias.dtype == torch.float32
+    assert moe.experts[3].gate_up_proj.weight.shape == (2 * shape.I, shape.H)
+    assert moe.experts[3].down_proj.weight.shape == (shape.H, shape.I)
+    # reference-style initialisation through the per-expert parameters lands in the stacks
+    moe.experts[3].gate_up_proj.weight.data.fill_(0.5)
+    moe.shared_experts.down_proj.weight.data.fill_(-2.0)
+    assert float(moe._w_gate_up[3].min()) == 0.5 and float(moe._w_down[shape.E].max()) == -2.0
+    # dtype conversion keeps the aliasing
+    moe = moe.to(torch.bfloat16)
+    moe.experts[1].down_proj.weight.data.fill_(1.25)
+    assert moe._w_down.dtype == torch.bfloat16 and float(moe._w_down[1].min()) == 1.25
+
+
+def test_forward_fails_loudly_on_cpu():
+    moe = glm4_moe_b200.Glm4MoeMoE(_cfg(synth.MINI))
+    with pytest.raises(_lib.Glm4MoeLibraryError):
+        moe(torch.zeros(4, synth.MINI.H))
+    with pytest.raises(_lib.Glm4MoeLibraryError):
+        moe.gate(torch.zeros(4, synth.MINI.H))
+
+
+def test_load_weights_hf_layout(tmp_path):
+    """moe.py:71-126 / mlp.py:83-131 key layout, incl. the experts.1 vs experts.1x prefix trap."""
+    from safetensors.torch import save_file
+    shape = synth.MoeShape(64, 12, 2, 32, 1.0, "loader")
+    w = synth.make_weights(shape, torch.float32)
+    p = "model.layers.1.mlp"
+    sd = {f"{p}.gate.weight": w["gate_weight"], f"{p}.gate.e_score_correction_bias": w["bias"]}
+    for e in range(shape.E + 1):
+        q = f"{p}.experts.{e}" if e < shape.E else f"{p}.shared_experts"
+        sd[f"{q}.gate_proj.weight"] = w["w_gate_up"][e, :shape.I].contiguous()
+        sd[f"{q}.up_proj.weight"] = w["w_gate_up"][e, shape.I:].contiguous()
+        sd[f"{q}.down_proj.weight"] = w["w_down"][e].contiguous()
+    sd["model.layers.1.self_attn.o_proj.weight"] = torch.zeros(4, 4)
+    keys = sorted(sd)
+    save_file({k: sd[k] for k in keys[::2]}, str(tmp_path / "a.safetensors"))
+    save_file({k: sd[k] for k in keys[1::2]}, str(tmp_path / "b.safetensors"))
+    moe = glm4_moe_b200.Glm4MoeMoE(_cfg(shape))
+    moe.load_weights(str(tmp_path), p)
+    assert torch.equal(moe._w_gate_up, w["w_gate_up"]) and torch.equal(moe._w_down, w["w_down"])
+    assert torch.equal(moe.gate.weight.data, w["gate_weight"])
+    assert torch.equal(moe.gate.e_score_correction_bias, w["bias"])
+    assert torch.equal(moe.experts[1].down_proj.weight.data, w["w_down"][1])     # not experts.10/11
+    with pytest.raises(ValueError):
+        moe.load_weights(str(tmp_path), "model.layers.7.mlp")
+    # expert-parallel shard reads only its experts
+    half = glm4_moe_b200.Glm4MoeMoE(_cfg(shape), ep_rank=1, ep_size=2)
+    half.load_weights(str(tmp_path), p)
+    assert torch.equal(half._w_gate_up[:6], w["w_gate_up"][6:12])
+    assert torch.equal(half._w_down[6], w["w_down"][12])

@@ -1,0 +1,368 @@
+"""GPU parity tests proper: every call goes through the C ABI (ctypes) into the sm_100a kernels and
+is compared with the CPU oracle (oracle/moe_oracle.py) and the golden outputs of the real reference
+(tests/golden).  Bars (BASELINE.json north_star): expert indices and the permutation bit-exact;
+layer outputs within rtol 2e-2 of the fp32 truth (|d| <= rtol*|ref| + rtol*rms(ref))
+and within the reference's own rtol=atol=1e-2 of its native output (nanovllm/tests/moe.py:40)."""
+import pytest
+import torch
+
+import glm4_moe_b200
+from glm4_moe_b200 import synth, _lib
+from oracle import moe_oracle as O
+from conftest import load_golden, dtype_of
+
+pytestmark = pytest.mark.gpu
+
+RTOL_BF16 = 2e-2     # north_star: bf16 outputs vs the fp32 reference
+FULL = ["tiny_fp32_T64", "mini_bf16_T48", "mini_fp16_T33", "mini_bf16_T1", "small_bf16_T256"]
+
+
+def _cfg(shape):
+    from transformers.models.glm4_moe import Glm4MoeConfig
+    return Glm4MoeConfig(hidden_size=shape.H, n_routed_experts=shape.E, num_experts_per_tok=shape.k,
+                         moe_intermediate_size=shape.I, n_shared_experts=1, n_group=1, topk_group=1,
+                         routed_scaling_factor=shape.routed_scaling_factor, norm_topk_prob=True)
+
+
+def _module(shape, dt, weights, **kw):
+    prev = torch.get_default_dtype()
+    torch.set_default_dtype(dt)
+    try:
+        moe = glm4_moe_b200.Glm4MoeMoE(_cfg(shape), **kw)
+    finally:
+        torch.set_default_dtype(prev)
+    moe.load_stacked(weights)
+    return moe.cuda()
+
+
+def _close(got, truth, rtol):
+    got, truth = got.float().cpu(), truth.float().cpu()
+    rms = truth.pow(2).mean().sqrt()
+    bad = (got - truth).abs() > rtol * truth.abs() + rtol * rms
+    rel = ((got - truth).norm() / truth.norm()).item()
+    return int(bad.sum()), rel
+
+
+def _ulp(dt):
+    return {torch.bfloat16: 2.0 ** -8, torch.float16: 2.0 ** -11, torch.float32: 2.0 ** -24}[dt]
+
+
+def _impls(shape, dt):
+    ok = dt in (torch.bfloat16, torch.float16) and shape.H % 128 == 0 and shape.I % 128 == 0
+    return ["simt", "umma"] if ok else ["simt"]
+
+
+# ------------------------------------------------------------------------------------------
+# router
+# ------------------------------------------------------------------------------------------
+def _check_router(x, gate_w, bias, shape, dt, ref_idx, ref_w):
+    """Three-stage router parity: logits within one model-dtype ulp of the
+    oracle's; selection bit-exact given the kernel's own logits; and end-to-end index sets equal
+    to the reference's except where a logit rounding flip sits on the k-th/k+1-th boundary."""
+    cfg = _cfg(shape)
+    prev = torch.get_default_dtype()
+    torch.set_default_dtype(dt)
+    try:
+        gate = glm4_moe_b200.GlmMoeSelectTopk(cfg)
+    finally:
+        torch.set_default_dtype(prev)
+    gate.weight.data.copy_(gate_w)
+    gate.e_score_correction_bias.copy_(bias)
+    gate = gate.cuda()
+    idx, w, logits = gate(x.cuda(), return_logits=True)
+    idx, w, logits = idx.cpu(), w.cpu(), logits.cpu()
+    assert idx.dtype == torch.int64 and w.dtype == dt
+    # (1) logits: fp32 accumulate, one rounding; differences only from accumulation order
+    ref_logits = O.router_logits(x, gate_w)
+    d = (logits.float() - ref_logits.float()).abs()
+    tol = 2 * _ulp(dt) * ref_logits.float().abs().clamp_min(1.0) if dt != torch.float32 else 1e-5
+    assert bool((d <= tol).all()), f"router logits differ by more than one ulp: {d.max()}"
+    flips = float((d > 0).float().mean())
+    assert flips < 5e-3 or dt == torch.float32
+    # (2) selection given identical logits: bit-exact indices (as sets, canonical order) + weights
+    oi, ow = O.select_from_logits(logits, bias, shape.k, shape.routed_scaling_factor)
+    oi, ow = O.canonical_routing(oi, ow)
+    assert torch.equal(idx, oi), "top-k indices differ from the oracle on identical logits"
+    if dt == torch.float32:
+        assert torch.allclose(w, ow, rtol=1e-6, atol=0)
+    else:
+        assert torch.equal(w, ow), "routing weights differ from the oracle on identical logits"
+    # (3) end to end vs the reference's own outputs
+    ri, rw = O.canonical_routing(ref_idx.long(), ref_w)
+    mism = (idx != ri).any(-1)
+    if bool(mism.any()):
+        # every disputed token must be explained by a logit flip on a boundary expert
+        sc = logits.float().sigmoid().to(dt).float() + bias
+        for t in torch.nonzero(mism).flatten().tolist():
+            a, b = set(idx[t].tolist()), set(ri[t].tolist())
+            only = list(a ^ b)
+            assert len(only) == 2, f"token {t}: sets differ in more than one expert"
+            gap = abs(float(sc[t, only[0]] - sc[t, only[1]]))
+            assert gap <= 2 * _ulp(dt), f"token {t}: real routing mismatch (gap {gap})"
+            assert float(d[t, only].max()) > 0, f"token {t}: mismatch without a logit flip"
+    assert float(mism.float().mean()) <= 2e-3
+    return int(mism.sum())
+
+
+@pytest.mark.parametrize("name", ["air_router_bf16_T256", "glm45_router_bf16_T64"])
+def test_router_big_shapes_vs_reference(name):
+    g = load_golden(name)
+    c = g["case"]
+    shape, dt = synth.SHAPES[c["shape"]], dtype_of(c["dtype"])
+    gate_w, bias = synth.make_router_weights(shape, dt)
+    x = synth.make_tokens(shape, c["T"], dt, c["batch_index"])
+    _check_router(x, gate_w, bias, shape, dt, g["idx"], g["w"])
+
+
+@pytest.mark.parametrize("name", FULL)
+def test_router_vs_reference(name):
+    g = load_golden(name)
+    c = g["case"]
+    shape, dt = synth.SHAPES[c["shape"]], dtype_of(c["dtype"])
+    wts = synth.make_weights(shape, dt)
+    x = synth.make_tokens(shape, c["T"], dt, c["batch_index"])
+    _check_router(x, wts["gate_weight"], wts["bias"], shape, dt, g["idx"], g["w"])
+
+
+def test_router_tie_rule_is_pinned():
+    """Tie stress: zero bias + constant tokens => all scores equal; duplicated router
+    rows => pairwise ties.  The pinned rule is 'higher score, then lower expert id'."""
+    shape, dt = synth.AIR, torch.bfloat16
+    gate_w, _ = synth.make_router_weights(shape, dt)
+    gate_w[1::2] = gate_w[0::2]                      # expert 2j+1 duplicates expert 2j
+    bias = torch.zeros(shape.E)
+    x = synth.make_tokens(shape, 64, dt, 5)
+    x[:8] = 0                                        # all logits 0 -> all scores 0.5
+    prev = torch.get_default_dtype()
+    torch.set_default_dtype(dt)
+    gate = glm4_moe_b200.GlmMoeSelectTopk(_cfg(shape))
+    torch.set_default_dtype(prev)
+    gate.weight.data.copy_(gate_w)
+    gate = gate.cuda()
+    idx, w, logits = gate(x.cuda(), return_logits=True)
+    idx, w, logits = idx.cpu(), w.cpu(), logits.cpu()
+    assert torch.equal(idx[:8], torch.arange(shape.k).expand(8, -1))       # lowest ids win
+    assert torch.equal(w[:8].float(), torch.full((8, shape.k), 0.125))
+    oi, ow = O.select_from_logits(logits, bias, shape.k, shape.routed_scaling_factor, tie_rule="lowest_index")
+    oi, ow = O.canonical_routing(oi, ow)
+    assert torch.equal(idx, oi) and torch.equal(w, ow)
+    # and it is a valid top-k for torch.topk too: same multiset of selected scores
+    ti, _ = O.select_from_logits(logits, bias, shape.k, shape.routed_scaling_factor, tie_rule="torch")
+    sc = logits.sigmoid().float()
+    assert torch.equal(sc.gather(1, idx).sort(-1)[0], sc.gather(1, ti).sort(-1)[0])
+
+
+# ------------------------------------------------------------------------------------------
+# permutation
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("T,E,k", [(1, 16, 4), (33, 32, 8), (256, 128, 8), (300, 160, 8), (4096, 128, 8)])
+def test_permutation_bit_exact(T, E, k):
+    lib = _lib.load()
+    g = torch.Generator().manual_seed(T * 131 + E)
+    idx = torch.stack([torch.randperm(E, generator=g)[:k].sort()[0] for _ in range(T)]).to(torch.int32)
+    w = torch.rand((T, k), generator=g)
+    row_token, row_slot, offs = O.permutation(idx.long(), E)
+    dev = "cuda"
+    tr = 16
+    cap = lib.glm4moe_tile_capacity(T, k, E, tr)
+    d_idx, d_w = idx.to(dev), w.to(dev)
+    d_off = torch.empty(E + 1, dtype=torch.int32, device=dev)
+    d_rt = torch.full((T * k,), -7, dtype=torch.int32, device=dev)
+    d_rw = torch.empty(T * k, dtype=torch.float32, device=dev)
+    d_sr = torch.empty(T * k, dtype=torch.int32, device=dev)
+    d_tiles = torch.zeros((cap, 4), dtype=torch.int32, device=dev)
+    d_nt = torch.zeros(4, dtype=torch.int32, device=dev)
+    d_scr = torch.empty(lib.glm4moe_permute_scratch_elems(T, E), dtype=torch.int32, device=dev)
+    _lib.check(lib.glm4moe_permute(d_idx.data_ptr(), d_w.data_ptr(), T, k, E, 0, E, tr, 1, d_off.data_ptr(),
+                                   d_rt.data_ptr(), d_rw.data_ptr(), d_sr.data_ptr(), d_tiles.data_ptr(), cap,
+                                   d_nt.data_ptr(), d_scr.data_ptr(), _lib.stream_ptr()))
+    torch.cuda.synchronize()
+    assert torch.equal(d_off.cpu(), offs)
+    assert torch.equal(d_rt.cpu(), row_token)
+    assert torch.equal(d_rw.cpu(), w[row_token.long(), row_slot.long()])
+    sr = d_sr.cpu().view(T, k)
+    inv = torch.empty(T * k, dtype=torch.int64)
+    inv[row_token.long() * k + row_slot.long()] = torch.arange(T * k)
+    assert torch.equal(sr.long().view(-1), inv)
+    # tile list covers every routed row exactly once, then the shared rows
+    nt = int(d_nt[0])
+    tiles = d_tiles.cpu()[:nt]
+    covered = torch.zeros(T * k + T, dtype=torch.int32)
+    for e, r0, n, _ in tiles.tolist():
+        assert 0 < n <= tr
+        covered[r0:r0 + n] += 1
+        if e < E:
+            assert offs[e] <= r0 and r0 + n <= offs[e + 1]
+        else:
+            assert r0 >= T * k
+    assert bool((covered == 1).all())
+    # expert-parallel filter: only experts [E/2, E) keep rows, order still stable
+    _lib.check(lib.glm4moe_permute(d_idx.data_ptr(), d_w.data_ptr(), T, k, E, E // 2, E, tr, 0, d_off.data_ptr(),
+                                   d_rt.data_ptr(), d_rw.data_ptr(), d_sr.data_ptr(), d_tiles.data_ptr(), cap,
+                                   d_nt.data_ptr(), d_scr.data_ptr(), _lib.stream_ptr()))
+    torch.cuda.synchronize()
+    keep = idx.long().view(-1)[row_token.long() * k + row_slot.long()] >= E // 2
+    n_keep = int(keep.sum())
+    assert int(d_off[E]) == n_keep
+    assert torch.equal(d_rt.cpu()[:n_keep], row_token[keep])
+    assert bool((d_sr.cpu().view(T, k)[idx < E // 2] == -1).all())
+
+
+# ------------------------------------------------------------------------------------------
+# whole block vs the reference's outputs (golden) and the fp32 truth
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", FULL)
+def test_layer_vs_reference_golden(name):
+    g = load_golden(name)
+    c = g["case"]
+    shape, dt = synth.SHAPES[c["shape"]], dtype_of(c["dtype"])
+    wts = synth.make_weights(shape, dt)
+    x = synth.make_tokens(shape, c["T"], dt, c["batch_index"])
+    ri, rw = O.canonical_routing(g["idx"].long(), g["w"])
+    with torch.inference_mode():
+        truth = O.moe_forward_fp32(x, wts, shape.k, shape.routed_scaling_factor, routing=(ri, rw))["out"]
+    for impl in _impls(shape, dt):
+        moe = _module(shape, dt, wts, impl=impl)
+        with torch.inference_mode():
+            out = moe(x.cuda())
+        torch.cuda.synchronize()
+        assert out.shape == (c["T"], shape.H) and out.dtype == dt
+        assert moe.last_impl == impl
+        idx = moe.workspace_view("idx", c["T"]).cpu().long()
+        assert torch.equal(idx, ri), f"{impl}: routing differs from the reference"
+        rt, _, offs = O.permutation(ri, shape.E)
+        assert torch.equal(moe.workspace_view("expert_offsets").cpu(), offs)
+        assert torch.equal(moe.workspace_view("row_token").cpu()[:c["T"] * shape.k], rt)
+        rtol = 1e-5 if dt == torch.float32 else RTOL_BF16
+        nbad, rel = _close(out, truth, rtol)
+        assert nbad == 0, f"{impl}: {nbad} elements outside rtol {rtol} of the fp32 truth (rel-F {rel})"
+        assert rel < (1e-5 if dt == torch.float32 else 6e-3)
+        # the reference's own tolerance against its native-dtype output (tests/moe.py:40)
+        torch.testing.assert_close(out.cpu().float(), g["out"].float(), rtol=1e-2, atol=1e-2)
+
+
+def test_simt_and_umma_agree():
+    shape, dt = synth.MINI, torch.bfloat16
+    wts = synth.make_weights(shape, dt)
+    x = synth.make_tokens(shape, 200, dt, 9).cuda()
+    outs = {}
+    for impl in ("simt", "umma"):
+        moe = _module(shape, dt, wts, impl=impl)
+        outs[impl] = moe(x).float().cpu()
+    nbad, rel = _close(outs["umma"], outs["simt"], 1e-2)
+    assert nbad == 0 and rel < 4e-3
+
+
+def test_edge_cases_and_properties():
+    shape, dt = synth.MINI, torch.bfloat16
+    wts = synth.make_weights(shape, dt)
+    for impl in ("simt", "umma"):
+        moe = _module(shape, dt, wts, impl=impl)
+        # empty input
+        assert moe(torch.empty((0, shape.H), dtype=dt, device="cuda")).shape == (0, shape.H)
+        # 3-D input comes back 2-D (moe.py:130,176); input is not modified
+        x = synth.make_tokens(shape, 48, dt, 3).cuda()
+        x0 = x.clone()
+        y = moe(x.view(4, 12, shape.H))
+        assert y.shape == (48, shape.H) and torch.equal(x, x0)
+        # permutation equivariance and batch-split consistency, bit-exact
+        perm = torch.randperm(48, generator=torch.Generator().manual_seed(1)).cuda()
+        assert torch.equal(moe(x[perm]), y[perm])
+        assert torch.equal(moe(x[:17]), y[:17])
+        # run-to-run determinism (no atomics in the combine)
+        assert torch.equal(moe(x), y)
+        # every token identical -> 8 experts take all rows (several row tiles per expert)
+        xs = x[:1].expand(300, -1).contiguous()
+        ys = moe(xs)
+        assert torch.equal(ys, ys[:1].expand(300, -1))
+        assert torch.equal(ys[0], moe(x[:1])[0])
+        offs = moe.workspace_view("expert_offsets").cpu()
+        assert int(offs[-1]) == 300 * shape.k and int((offs[1:] - offs[:-1]).max()) == 300
+
+
+def test_cuda_graph_capture_and_host_entry():
+    shape, dt = synth.MINI, torch.bfloat16
+    wts = synth.make_weights(shape, dt)
+    moe = _module(shape, dt, wts)
+    x = synth.make_tokens(shape, 16, dt, 4)
+    xs = x.cuda()
+    eager = moe(xs)                                   # also sizes the workspace before capture
+    torch.cuda.synchronize()
+    static_in = xs.clone()
+    graph = torch.cuda.CUDAGraph()
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        moe(static_in)
+    torch.cuda.current_stream().wait_stream(s)
+    with torch.cuda.graph(graph):
+        static_out = moe(static_in)
+    static_in.copy_(synth.make_tokens(shape, 16, dt, 5).cuda())
+    graph.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(static_out, moe(static_in))
+    static_in.copy_(xs)
+    graph.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(static_out, eager)
+    # host-buffer entry point == device entry point
+    out_host = moe.forward_host(x.pin_memory())
+    assert torch.equal(out_host, eager.cpu())
+    assert moe.last_launches == 9
+
+
+# ------------------------------------------------------------------------------------------
+# BASELINE configs[1]: GLM-4.5-Air shape, bf16
+# ------------------------------------------------------------------------------------------
+@pytest.fixture(scope="module")
+def air():
+    shape, dt = synth.AIR, torch.bfloat16
+    wts = synth.make_weights(shape, dt)
+    moe = _module(shape, dt, wts, max_tokens=4096)
+    return shape, dt, wts, moe
+
+
+@pytest.mark.parametrize("T", [1, 32, 256])
+def test_air_decode_vs_oracle(air, T):
+    shape, dt, wts, moe = air
+    x = synth.make_tokens(shape, T, dt, T)
+    torch.set_num_threads(max(1, torch.get_num_threads()))
+    with torch.inference_mode():
+        out = moe(x.cuda())
+        torch.cuda.synchronize()
+        assert moe.last_impl == "umma"
+        idx = moe.workspace_view("idx", T).cpu().long()
+        w = moe.workspace_view("w", T).cpu().to(dt)
+        # routing vs the oracle router on the box's CPU (rounding-boundary flips excused + counted)
+        oi, ow = O.canonical_routing(*O.router(x, wts["gate_weight"], wts["bias"], shape.k, 1.0))
+        assert float((idx != oi).any(-1).float().mean()) <= 0.01
+        rt, _, offs = O.permutation(idx, shape.E)
+        assert torch.equal(moe.workspace_view("expert_offsets").cpu(), offs)
+        assert torch.equal(moe.workspace_view("row_token").cpu()[:T * shape.k], rt)
+        truth = O.moe_forward_fp32(x, wts, shape.k, 1.0, routing=(idx, w))["out"]
+    nbad, rel = _close(out, truth, RTOL_BF16)
+    assert nbad == 0 and rel < 6e-3, (nbad, rel)
+
+
+def test_air_prefill_properties(air):
+    """Full BASELINE size (T=4096): size-independent properties, no CPU oracle needed."""
+    shape, dt, wts, moe = air
+    T = 4096
+    x = synth.make_tokens(shape, T, dt, 77).cuda()
+    with torch.inference_mode():
+        y = moe(x)
+        offs = moe.workspace_view("expert_offsets").cpu().long()
+        idx = moe.workspace_view("idx", T).cpu().long()
+        rt = moe.workspace_view("row_token").cpu().long()
+        sr = moe.workspace_view("slot_row", T).cpu().long()
+        assert int(offs[-1]) == T * shape.k
+        assert torch.equal(offs[1:] - offs[:-1], torch.bincount(idx.view(-1), minlength=shape.E))
+        assert bool((idx[:, 1:] > idx[:, :-1]).all())                 # k distinct experts, ascending
+        assert torch.equal(rt[sr.view(-1)], torch.arange(T).repeat_interleave(shape.k))
+        for e in (0, 17, 127):                                        # token-ascending inside an expert
+            seg = rt[offs[e]:offs[e + 1]]
+            assert bool((seg[1:] > seg[:-1]).all())
+        # a decode-size slice of the same tokens gives bit-identical rows (other tile size, same math)
+        sub = torch.arange(0, T, 128, device="cuda")
+        assert torch.equal(moe(x[sub]), y[sub])
+        assert bool(torch.isfinite(y.float()).all())
