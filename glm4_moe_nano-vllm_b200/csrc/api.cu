@@ -4,6 +4,7 @@
 // the reference's decode path replays graphs, model_runner.py:197-213,239-247).
 #include <cuda.h>
 
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -15,12 +16,14 @@ using namespace glm4moe;
 namespace {
 
 constexpr int kSimtRows = 8;
-constexpr int kBnChoices[4] = {16, 32, 64, 128};
+constexpr int kNumBn = 5;
+constexpr int kBnChoices[kNumBn] = {16, 32, 64, 128, 256};
+constexpr int kRouterUmmaMinTokens = 64;   // below this the K-split CUDA-core router wins (latency)
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct WsLayout {
-  size_t logits, idx, w, offsets, row_token, row_weight, slot_row, num_tiles, tiles, scratch, x_rows,
+  size_t logits, idx, w, offsets, row_token, row_weight, slot_row, num_tiles, sched, tiles, scratch, x_rows,
       act, y, total;
   int tile_capacity;
 };
@@ -44,6 +47,7 @@ WsLayout make_layout(const glm4moe_config_t& c) {
   L.row_weight = take(T * k * 4);
   L.slot_row = take(T * k * 4);
   L.num_tiles = take(16);
+  L.sched = take(64);
   L.tile_capacity = glm4moe_tile_capacity(static_cast<int>(T), static_cast<int>(k), static_cast<int>(E),
                                           kSimtRows);
   L.tiles = take(static_cast<size_t>(L.tile_capacity) * 16);
@@ -73,9 +77,21 @@ struct glm4moe_layer {
   cudaEvent_t ev[8];
   alignas(64) CUtensorMap tm_w_gu;
   alignas(64) CUtensorMap tm_w_d;
-  alignas(64) CUtensorMap tm_x[4];
-  alignas(64) CUtensorMap tm_act[4];
+  alignas(64) CUtensorMap tm_gate;
+  alignas(64) CUtensorMap tm_x[kNumBn];
+  alignas(64) CUtensorMap tm_act[kNumBn];
 };
+
+namespace glm4moe {
+bool pdl_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("GLM4MOE_NO_PDL");
+    v = (e && e[0] == '1') ? 0 : 1;
+  }
+  return v == 1;
+}
+}  // namespace glm4moe
 
 extern "C" int glm4moe_abi_version(void) { return GLM4MOE_ABI_VERSION; }
 
@@ -132,6 +148,10 @@ extern "C" int glm4moe_layer_create(const glm4moe_config_t* cfg, const void* gat
   l->last_launches = 0;
   l->last_impl = GLM4MOE_IMPL_AUTO;
   l->events_ready = false;
+  if (cudaMemset(l->ws + L.sched, 0, 64) != cudaSuccess) {
+    delete l;
+    return GLM4MOE_ERR_DEVICE;
+  }
   int dev = 0;
   l->sm_count = 148;
   if (cudaGetDevice(&dev) == cudaSuccess)
@@ -143,7 +163,9 @@ extern "C" int glm4moe_layer_create(const glm4moe_config_t* cfg, const void* gat
     const uint64_t R = static_cast<uint64_t>(cfg->max_tokens) * (cfg->num_experts_per_tok + 1);
     rc = umma_make_tensor_map(&l->tm_w_gu, w_gate_up, cfg->dtype, n_stack * 2 * I, H, 128);
     if (rc == GLM4MOE_OK) rc = umma_make_tensor_map(&l->tm_w_d, w_down, cfg->dtype, n_stack * H, I, 128);
-    for (int i = 0; i < 4 && rc == GLM4MOE_OK; ++i) {
+    if (rc == GLM4MOE_OK)
+      rc = umma_make_tensor_map(&l->tm_gate, gate_w, cfg->dtype, cfg->n_routed_experts, H, 128);
+    for (int i = 0; i < kNumBn && rc == GLM4MOE_OK; ++i) {
       rc = umma_make_tensor_map(&l->tm_x[i], l->ws + L.x_rows, cfg->dtype, R, H, kBnChoices[i]);
       if (rc == GLM4MOE_OK)
         rc = umma_make_tensor_map(&l->tm_act[i], l->ws + L.act, cfg->dtype, R, I, kBnChoices[i]);
@@ -168,12 +190,20 @@ extern "C" int glm4moe_layer_destroy(glm4moe_layer_t* layer) {
 // rows of one token tile on the tensor-core path: sized to the mean rows per local expert so a
 // typical expert is one tile (weights cross HBM once; a second tile re-reads them from L2).
 static int pick_bn_index(const glm4moe_config_t& c, int T) {
+  static int forced = -2;
+  if (forced == -2) {
+    const char* e = getenv("GLM4MOE_FORCE_BN");   // tuning aid: 16/32/64/128/256
+    forced = -1;
+    if (e) for (int i = 0; i < kNumBn; ++i) if (atoi(e) == kBnChoices[i]) forced = i;
+  }
+  if (forced >= 0) return forced;
   const int e_local = c.expert_end - c.expert_begin;
   const double mean = e_local > 0 ? static_cast<double>(T) * c.num_experts_per_tok / c.n_routed_experts : T;
   if (mean <= 6.0) return 0;
   if (mean <= 20.0) return 1;
   if (mean <= 48.0) return 2;
-  return 3;
+  if (mean <= 96.0) return 3;
+  return 4;
 }
 
 extern "C" int glm4moe_layer_tile_rows(const glm4moe_layer_t* l, int T) {
@@ -214,7 +244,32 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
   int launches = 0;
   int rc;
   STAGE_MARK(0);
-  if ((rc = glm4moe_router_logits(x, l->gate_w, logits, T, H, E, c.dtype, stream))) return rc;
+  if (use_umma && T >= kRouterUmmaMinTokens && H % 64 == 0) {
+    // router logits on the tensor cores: D[expert, token] = Wg . x^T, dense token tiles of x itself
+    alignas(64) CUtensorMap tm_xin;
+    const int rbn = T >= 128 ? 128 : 64;
+    if ((rc = umma_make_tensor_map(&tm_xin, x, c.dtype, static_cast<uint64_t>(T), H, rbn))) return rc;
+    UmmaLaunch r{};
+    r.tm_w = &l->tm_gate;
+    r.tm_x = &tm_xin;
+    r.tiles = nullptr;
+    r.num_tiles = nullptr;
+    r.dense_rows = T;
+    r.out = logits;
+    r.ld_out = E;
+    r.n_feat_tiles = (E + 127) / 128;
+    r.n_feat_valid = E;
+    r.n_kblocks = H / 64;
+    r.w_rows_per_expert = 0;
+    r.tile_rows = rbn;
+    r.mode = 2;
+    r.dtype = c.dtype;
+    r.grid = l->sm_count;
+    r.sched = reinterpret_cast<int32_t*>(ws + L.sched) + 4;
+    if ((rc = umma_launch(r, stream))) return rc;
+  } else if ((rc = glm4moe_router_logits(x, l->gate_w, logits, T, H, E, c.dtype, stream))) {
+    return rc;
+  }
   STAGE_MARK(1);
   if ((rc = glm4moe_router_select(logits, l->bias, T, E, k, c.routed_scaling_factor, c.dtype, idx, w, stream)))
     return rc;
@@ -225,7 +280,7 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
   STAGE_MARK(3);
   if ((rc = glm4moe_gather_rows(x, row_token, offsets, x_rows, T, k, E, H, c.with_shared, c.dtype, stream)))
     return rc;
-  launches += 6;
+  launches += T <= 256 ? 4 : 6;
   STAGE_MARK(4);
   if (use_umma) {
     UmmaLaunch a{};
@@ -242,10 +297,12 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
     a.out = act;
     a.ld_out = I;
     a.n_feat_tiles = I / 128;
+    a.n_feat_valid = I;
     a.n_kblocks = H / 64;
     a.w_rows_per_expert = 2 * I;
     a.up_row_offset = I;
-    a.gated = 1;
+    a.mode = 1;
+    a.sched = reinterpret_cast<int32_t*>(ws + L.sched);
     if ((rc = umma_launch(a, stream))) return rc;
     STAGE_MARK(5);
     // down * routing weight
@@ -254,10 +311,12 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
     a.out = y;
     a.ld_out = H;
     a.n_feat_tiles = H / 128;
+    a.n_feat_valid = H;
     a.n_kblocks = I / 64;
     a.w_rows_per_expert = H;
     a.up_row_offset = 0;
-    a.gated = 0;
+    a.mode = 0;
+    a.sched = reinterpret_cast<int32_t*>(ws + L.sched) + 2;
     if ((rc = umma_launch(a, stream))) return rc;
   } else {
     if ((rc = glm4moe_expert_gate_up_simt(x_rows, l->w_gate_up, tiles, num_tiles, act, H, I, tile_rows, c.dtype,

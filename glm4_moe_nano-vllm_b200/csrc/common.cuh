@@ -96,6 +96,33 @@ __device__ __forceinline__ float warp_sum(float v) {
 
 __device__ __forceinline__ float sigmoid_f(float x) { return 1.0f / (1.0f + expf(-x)); }
 __device__ __forceinline__ float silu_f(float x) { return x / (1.0f + expf(-x)); }
+// tensor-core epilogues: fast exp + fast divide (rel. error ~1e-6, far below the 2-byte output ulp)
+__device__ __forceinline__ float silu_fast(float x) { return __fdividef(x, 1.0f + __expf(-x)); }
+
+// Programmatic dependent launch.  Every kernel on the forward path runs
+//   [prologue that touches nothing a predecessor writes] -> pdl_wait() -> pdl_launch() -> body
+// so a kernel only starts once its predecessor passed its own wait: everything two or more
+// launches back is complete and visible, and only the direct predecessor's outputs need the wait.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+bool pdl_enabled();   // api.cu: false when GLM4MOE_NO_PDL=1
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
 
 inline int dtype_size(int dtype) { return dtype == GLM4MOE_F32 ? 4 : 2; }
 

@@ -22,6 +22,8 @@ __global__ void __launch_bounds__(kTokPerBlock) permute_rank_kernel(
     const int32_t* __restrict__ idx, int T, int k, int E, int e_lo, int e_hi,
     int32_t* __restrict__ local_rank /*[T*k]*/, int32_t* __restrict__ block_counts /*[nblk][E]*/) {
   __shared__ uint32_t bitmap[kMaxExperts * kWordsPerExpert];
+  pdl_wait();
+  pdl_launch();
   const int tid = threadIdx.x;
   const int t = blockIdx.x * kTokPerBlock + tid;
   for (int i = tid; i < E * kWordsPerExpert; i += kTokPerBlock) bitmap[i] = 0u;
@@ -64,6 +66,8 @@ __global__ void __launch_bounds__(256) permute_scan_kernel(
   __shared__ int s_cnt[kMaxExperts];
   __shared__ int s_off[kMaxExperts + 1];
   __shared__ int s_tile_off[kMaxExperts + 1];
+  pdl_wait();
+  pdl_launch();
   const int e = threadIdx.x;
   int total = 0;
   if (e < E) {
@@ -112,6 +116,8 @@ __global__ void __launch_bounds__(kTokPerBlock) permute_scatter_kernel(
     const int32_t* __restrict__ local_rank, const int32_t* __restrict__ block_base,
     const int32_t* __restrict__ expert_offsets, int32_t* __restrict__ row_token,
     float* __restrict__ row_weight, int32_t* __restrict__ slot_row) {
+  pdl_wait();
+  pdl_launch();
   const int t = blockIdx.x * kTokPerBlock + threadIdx.x;
   if (t >= T) return;
   for (int s = 0; s < k; ++s) {
@@ -128,6 +134,96 @@ __global__ void __launch_bounds__(kTokPerBlock) permute_scatter_kernel(
   }
 }
 
+// Decode-size batches (T <= 256): the three phases above in ONE block, thread t owns token t.
+__global__ void __launch_bounds__(kTokPerBlock) permute_small_kernel(
+    const int32_t* __restrict__ idx, const float* __restrict__ w, int T, int k, int E, int e_lo,
+    int e_hi, int tile_rows, int with_shared, int32_t* __restrict__ expert_offsets,
+    int32_t* __restrict__ row_token, float* __restrict__ row_weight, int32_t* __restrict__ slot_row,
+    int4* __restrict__ tiles, int tile_capacity, int32_t* __restrict__ num_tiles) {
+  __shared__ uint32_t bitmap[kMaxExperts * kWordsPerExpert];
+  __shared__ int s_cnt[kMaxExperts];
+  __shared__ int s_off[kMaxExperts + 1];
+  __shared__ int s_tile_off[kMaxExperts + 1];
+  const int tid = threadIdx.x;
+  for (int i = tid; i < E * kWordsPerExpert; i += kTokPerBlock) bitmap[i] = 0u;
+  pdl_wait();
+  pdl_launch();
+  __syncthreads();
+  const int word = tid >> 5;
+  const uint32_t bit = 1u << (tid & 31);
+  if (tid < T) {
+    for (int s = 0; s < k; ++s) {
+      const int e = idx[static_cast<size_t>(tid) * k + s];
+      if (e >= e_lo && e < e_hi) atomicOr(&bitmap[e * kWordsPerExpert + word], bit);
+    }
+  }
+  __syncthreads();
+  for (int e = tid; e < E; e += kTokPerBlock) {
+    int c = 0;
+#pragma unroll
+    for (int wd = 0; wd < kWordsPerExpert; ++wd) c += __popc(bitmap[e * kWordsPerExpert + wd]);
+    s_cnt[e] = c;
+  }
+  __syncthreads();
+  if (tid < 32) {
+    // warp scan over experts: lane handles ceil(E/32) consecutive experts
+    const int per = (E + 31) / 32;
+    int rows = 0, tl = 0;
+    for (int i = 0; i < per; ++i) {
+      const int e = tid * per + i;
+      if (e < E) { rows += s_cnt[e]; tl += (s_cnt[e] + tile_rows - 1) / tile_rows; }
+    }
+    int rows_incl = rows, tl_incl = tl;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int a = __shfl_up_sync(0xffffffffu, rows_incl, o);
+      const int b = __shfl_up_sync(0xffffffffu, tl_incl, o);
+      if (tid >= o) { rows_incl += a; tl_incl += b; }
+    }
+    int roff = rows_incl - rows, toff = tl_incl - tl;
+    for (int i = 0; i < per; ++i) {
+      const int e = tid * per + i;
+      if (e < E) {
+        s_off[e] = roff; s_tile_off[e] = toff;
+        roff += s_cnt[e]; toff += (s_cnt[e] + tile_rows - 1) / tile_rows;
+      }
+    }
+    if (tid == 31) { s_off[E] = rows_incl; s_tile_off[E] = tl_incl; }
+  }
+  __syncthreads();
+  const int shared_tiles = with_shared ? (T + tile_rows - 1) / tile_rows : 0;
+  const bool fits = s_tile_off[E] + shared_tiles <= tile_capacity;
+  if (tid == 0) *num_tiles = fits ? s_tile_off[E] + shared_tiles : 0;
+  for (int e = tid; e <= E; e += kTokPerBlock) expert_offsets[e] = s_off[e];
+  if (fits) {
+    for (int e = tid; e < E; e += kTokPerBlock) {
+      const int n = s_cnt[e];
+      int ti = s_tile_off[e];
+      for (int r = 0; r < n; r += tile_rows, ++ti)
+        tiles[ti] = make_int4(e - e_lo, s_off[e] + r, min(tile_rows, n - r), 0);
+    }
+    for (int i = tid; i < shared_tiles; i += kTokPerBlock)
+      tiles[s_tile_off[E] + i] =
+          make_int4(e_hi - e_lo, T * k + i * tile_rows, min(tile_rows, T - i * tile_rows), 0);
+  }
+  if (tid < T) {
+    for (int s = 0; s < k; ++s) {
+      const size_t i = static_cast<size_t>(tid) * k + s;
+      const int e = idx[i];
+      int row = -1;
+      if (e >= e_lo && e < e_hi) {
+        const uint32_t* bm = &bitmap[e * kWordsPerExpert];
+        int r = __popc(bm[word] & (bit - 1u));
+        for (int wd = 0; wd < word; ++wd) r += __popc(bm[wd]);
+        row = s_off[e] + r;
+        row_token[row] = tid;
+        row_weight[row] = w[i];
+      }
+      slot_row[i] = row;
+    }
+  }
+}
+
 // x_rows[r] = x[row_token[r]] (routed), x_rows[T*k + t] = x[t] (shared). One warp per row,
 // 128-bit copies.
 template <int kBytesPerElem>
@@ -136,6 +232,8 @@ __global__ void __launch_bounds__(256) gather_rows_kernel(const uint4* __restric
                                                           const int32_t* __restrict__ expert_offsets,
                                                           uint4* __restrict__ x_rows, int T, int k,
                                                           int E, int vec_per_row, int with_shared) {
+  pdl_wait();
+  pdl_launch();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * 8 + warp;
   const int n_routed = expert_offsets[E];
@@ -182,23 +280,26 @@ extern "C" int glm4moe_permute(const int32_t* idx, const float* w, int T, int k,
   if (tile_capacity < glm4moe_tile_capacity(T, k, E, tile_rows)) return GLM4MOE_ERR_WORKSPACE;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int nblk = (T + kTokPerBlock - 1) / kTokPerBlock;
+  if (T > 0 && T <= kTokPerBlock) {
+    GLM4MOE_CUDA_CHECK(launch_pdl(permute_small_kernel, dim3(1), dim3(kTokPerBlock), 0, st, idx, w, T, k, E, e_lo,
+                                  e_hi, tile_rows, with_shared, expert_offsets, row_token, row_weight, slot_row,
+                                  reinterpret_cast<int4*>(tiles), tile_capacity, num_tiles));
+    return GLM4MOE_OK;
+  }
   int32_t* block_counts = scratch;                       // [nblk][E]
   // local ranks live in slot_row until the scatter overwrites them in place
   int32_t* local_rank = slot_row;
   if (nblk > 0) {
-    permute_rank_kernel<<<nblk, kTokPerBlock, 0, st>>>(idx, T, k, E, e_lo, e_hi, local_rank,
-                                                       block_counts);
-    GLM4MOE_LAUNCH_CHECK();
+    GLM4MOE_CUDA_CHECK(launch_pdl(permute_rank_kernel, dim3(nblk), dim3(kTokPerBlock), 0, st, idx, T, k, E, e_lo,
+                                  e_hi, local_rank, block_counts));
   }
-  permute_scan_kernel<<<1, 256, 0, st>>>(block_counts, nblk, E, T, k, e_lo, e_hi, tile_rows, with_shared,
-                                         expert_offsets, reinterpret_cast<int4*>(tiles),
-                                         tile_capacity, num_tiles);
-  GLM4MOE_LAUNCH_CHECK();
+  GLM4MOE_CUDA_CHECK(launch_pdl(permute_scan_kernel, dim3(1), dim3(256), 0, st, block_counts, nblk, E, T, k, e_lo,
+                                e_hi, tile_rows, with_shared, expert_offsets, reinterpret_cast<int4*>(tiles),
+                                tile_capacity, num_tiles));
   if (nblk > 0) {
-    permute_scatter_kernel<<<nblk, kTokPerBlock, 0, st>>>(idx, w, T, k, E, local_rank, block_counts,
-                                                          expert_offsets, row_token, row_weight,
-                                                          slot_row);
-    GLM4MOE_LAUNCH_CHECK();
+    GLM4MOE_CUDA_CHECK(launch_pdl(permute_scatter_kernel, dim3(nblk), dim3(kTokPerBlock), 0, st, idx, w, T, k, E,
+                                  static_cast<const int32_t*>(local_rank), static_cast<const int32_t*>(block_counts),
+                                  static_cast<const int32_t*>(expert_offsets), row_token, row_weight, slot_row));
   }
   return GLM4MOE_OK;
 }
@@ -212,9 +313,8 @@ extern "C" int glm4moe_gather_rows(const void* x, const int32_t* row_token,
   if (T == 0) return GLM4MOE_OK;
   const int rows = T * k + (with_shared ? T : 0);
   const int vec_per_row = H * es / 16;
-  gather_rows_kernel<2><<<(rows + 7) / 8, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const uint4*>(x), row_token, expert_offsets, static_cast<uint4*>(x_rows), T, k, E,
-      vec_per_row, with_shared);
-  GLM4MOE_LAUNCH_CHECK();
+  GLM4MOE_CUDA_CHECK(launch_pdl(gather_rows_kernel<2>, dim3((rows + 7) / 8), dim3(256), 0,
+                                static_cast<cudaStream_t>(stream), static_cast<const uint4*>(x), row_token,
+                                expert_offsets, static_cast<uint4*>(x_rows), T, k, E, vec_per_row, with_shared));
   return GLM4MOE_OK;
 }

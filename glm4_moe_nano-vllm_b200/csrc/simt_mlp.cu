@@ -37,6 +37,8 @@ __global__ void __launch_bounds__(256) simt_gate_up_kernel(
   extern __shared__ __align__(16) unsigned char smem_raw[];
   T* xs = reinterpret_cast<T*>(smem_raw);
   constexpr int V = Dt<T>::kVec;
+  pdl_wait();
+  pdl_launch();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int units_per_tile = (I + kColsPerUnit - 1) / kColsPerUnit;
   const int total = *num_tiles * units_per_tile;
@@ -89,6 +91,8 @@ __global__ void __launch_bounds__(256) simt_down_kernel(
   extern __shared__ __align__(16) unsigned char smem_raw[];
   T* as = reinterpret_cast<T*>(smem_raw);
   constexpr int V = Dt<T>::kVec;
+  pdl_wait();
+  pdl_launch();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int units_per_tile = (H + kColsPerUnit - 1) / kColsPerUnit;
   const int total = *num_tiles * units_per_tile;
@@ -138,6 +142,8 @@ __global__ void __launch_bounds__(256) combine_kernel(const T* __restrict__ y,
   const int t = blockIdx.x;
   const int nvec = H / V;
   __shared__ int rows[64];
+  pdl_wait();
+  pdl_launch();
   if (threadIdx.x < k) rows[threadIdx.x] = slot_row[static_cast<size_t>(t) * k + threadIdx.x];
   __syncthreads();
   for (int c = threadIdx.x; c < nvec; c += blockDim.x) {
@@ -179,10 +185,9 @@ static int launch_gate_up(const void* x_rows, const void* w, const int32_t* tile
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   const int per_sm = smem > 100 * 1024 ? 1 : (smem > 64 * 1024 ? 2 : 3);
-  simt_gate_up_kernel<T><<<sms * per_sm, 256, smem, st>>>(
-      static_cast<const T*>(x_rows), static_cast<const T*>(w), reinterpret_cast<const int4*>(tiles),
-      num_tiles, static_cast<T*>(act), H, I);
-  GLM4MOE_LAUNCH_CHECK();
+  GLM4MOE_CUDA_CHECK(launch_pdl(simt_gate_up_kernel<T>, dim3(sms * per_sm), dim3(256), smem, st,
+                                static_cast<const T*>(x_rows), static_cast<const T*>(w),
+                                reinterpret_cast<const int4*>(tiles), num_tiles, static_cast<T*>(act), H, I));
   return GLM4MOE_OK;
 }
 
@@ -200,10 +205,10 @@ static int launch_down(const void* act, const void* w, const int32_t* tiles,
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   const int per_sm = smem > 100 * 1024 ? 1 : (smem > 64 * 1024 ? 2 : 3);
-  simt_down_kernel<T><<<sms * per_sm, 256, smem, st>>>(
-      static_cast<const T*>(act), static_cast<const T*>(w), reinterpret_cast<const int4*>(tiles),
-      num_tiles, row_weight, static_cast<T*>(y), H, I, n_routed_rows);
-  GLM4MOE_LAUNCH_CHECK();
+  GLM4MOE_CUDA_CHECK(launch_pdl(simt_down_kernel<T>, dim3(sms * per_sm), dim3(256), smem, st,
+                                static_cast<const T*>(act), static_cast<const T*>(w),
+                                reinterpret_cast<const int4*>(tiles), num_tiles, row_weight, static_cast<T*>(y), H, I,
+                                n_routed_rows));
   return GLM4MOE_OK;
 }
 
@@ -241,9 +246,8 @@ extern "C" int glm4moe_combine(const void* y, const int32_t* slot_row, void* out
   if (T == 0) return GLM4MOE_OK;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   GLM4MOE_DISPATCH_DTYPE(dtype, T_,
-                         (combine_kernel<T_><<<T, 256, 0, st>>>(static_cast<const T_*>(y), slot_row,
-                                                               static_cast<T_*>(out), T, k, H,
-                                                               with_shared)));
-  GLM4MOE_LAUNCH_CHECK();
+                         GLM4MOE_CUDA_CHECK(launch_pdl(combine_kernel<T_>, dim3(T), dim3(256), 0, st,
+                                                       static_cast<const T_*>(y), slot_row, static_cast<T_*>(out), T,
+                                                       k, H, with_shared)));
   return GLM4MOE_OK;
 }

@@ -164,35 +164,64 @@ constexpr uint64_t kEvictLast = 0x14F0000000000000ull;    // activation rows: re
 constexpr int kBM = 128;   // weight rows (output features) per tile
 constexpr int kBK = 64;    // 64 two-byte elements = 128 B swizzle atom
 
-template <int BN, bool GATED>
+// Epilogue modes
+constexpr int kModeDown = 0;    // y = acc * routing weight              (mlp.py:52, moe.py:149)
+constexpr int kModeGated = 1;   // act = silu(acc_gate) * acc_up         (mlp.py:50-51)
+constexpr int kModePlain = 2;   // out = acc (router logits, moe.py:32), features bounded by n_feat_valid
+
+template <int BN, int MODE>
 struct UmmaCfg {
+  static constexpr bool kGated = MODE == kModeGated;
   static constexpr int kABytes = kBM * kBK * 2;                 // 16 KB per weight tile
   static constexpr int kBBytes = BN * kBK * 2;
-  static constexpr int kStageBytes = (GATED ? 2 : 1) * kABytes + kBBytes;
+  static constexpr int kStageBytes = (kGated ? 2 : 1) * kABytes + kBBytes;
   static constexpr int kStages = (212 * 1024) / kStageBytes > 12 ? 12 : (212 * 1024) / kStageBytes;
-  static constexpr int kAccCols = (GATED ? 2 : 1) * BN;         // TMEM columns per accumulator stage
-  static constexpr int kTmemColsRaw = 2 * kAccCols;
+  static constexpr int kAccCols = (kGated ? 2 : 1) * BN;        // TMEM columns per accumulator stage
+  static constexpr int kAccStages = 2 * kAccCols <= 512 ? 2 : 1;   // BN=256 gated fills TMEM: 1 stage
+  static constexpr int kTmemColsRaw = kAccStages * kAccCols;
   static constexpr int kTmemCols = kTmemColsRaw <= 32 ? 32 : kTmemColsRaw <= 64 ? 64
                                    : kTmemColsRaw <= 128 ? 128 : kTmemColsRaw <= 256 ? 256 : 512;
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int kEpiWarps = BN >= 64 ? 8 : 4;            // wide tiles: two warps per TMEM lane quadrant
+  static constexpr int kThreads = 128 + 32 * kEpiWarps;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 512 /*barriers*/;
   static_assert(kTmemColsRaw <= 512, "accumulators do not fit TMEM");
   static_assert(kBBytes % 1024 == 0, "operand tiles must stay 1024-byte aligned");
+  static_assert(kStages >= 3, "pipeline too shallow");
 };
+
+struct TileRef { int expert, row_start, nrows; };
+
+// work item -> tile.  `tiles == nullptr` means dense rows [0, dense_rows) cut into BN-row tiles.
+template <int BN>
+__device__ __forceinline__ TileRef get_tile(const int4* __restrict__ tiles, int ti, int dense_rows) {
+  if (tiles) {
+    const int4 t = tiles[ti];
+    return {t.x, t.y, t.z};
+  }
+  const int r0 = ti * BN;
+  return {0, r0, min(BN, dense_rows - r0)};
+}
 
 // ------------------------------------------------------------------------------------------
 // the kernel
 // ------------------------------------------------------------------------------------------
-template <typename T, int BN, bool GATED>
-__global__ void __launch_bounds__(256, 1) umma_grouped_kernel(
+constexpr int kSchedDepth = 4;   // work-index queue between the producer and the consumer warps
+
+template <typename T, int BN, int MODE>
+__global__ void __launch_bounds__(UmmaCfg<BN, MODE>::kThreads, 1) umma_grouped_kernel(
     const __grid_constant__ CUtensorMap tm_w,   // weights  [rows_w_total, K], box {64, 128}
     const __grid_constant__ CUtensorMap tm_x,   // activation rows [rows_x_total, K], box {64, BN}
-    const int4* __restrict__ tiles, const int32_t* __restrict__ num_tiles_ptr,
+    const int4* __restrict__ tiles, const int32_t* __restrict__ num_tiles_ptr, int dense_rows,
     T* __restrict__ out, int ld_out,            // out[row, feature]
-    const float* __restrict__ row_weight,       // !GATED: per-row scale for rows < n_routed_rows
-    int n_routed_rows, int n_feat_tiles, int n_kblocks,
-    int w_rows_per_expert,                      // GATED: 2I, else H
-    int up_row_offset) {                        // GATED: I
-  using Cfg = UmmaCfg<BN, GATED>;
+    const float* __restrict__ row_weight,       // kModeDown: per-row scale for rows < n_routed_rows
+    int n_routed_rows, int n_feat_tiles, int n_feat_valid, int n_kblocks,
+    int w_rows_per_expert,                      // gated: 2I, down: H, plain: 0
+    int up_row_offset,                          // gated: I
+    int32_t* __restrict__ sched) {              // [0] next work index - gridDim, [1] CTAs finished
+  using Cfg = UmmaCfg<BN, MODE>;
+  constexpr bool GATED = Cfg::kGated;
+  constexpr int AS = Cfg::kAccStages;
+  constexpr int EW = Cfg::kEpiWarps;
   extern __shared__ unsigned char smem_dyn[];
   unsigned char* smem = reinterpret_cast<unsigned char*>(
       (reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~static_cast<uintptr_t>(1023));
@@ -201,7 +230,10 @@ __global__ void __launch_bounds__(256, 1) umma_grouped_kernel(
   uint64_t* empty_bar = bars + Cfg::kStages;
   uint64_t* tmem_full = bars + 2 * Cfg::kStages;
   uint64_t* tmem_empty = tmem_full + 2;
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  uint64_t* sched_full = tmem_empty + 2;
+  uint64_t* sched_empty = sched_full + kSchedDepth;
+  int32_t* sched_w = reinterpret_cast<int32_t*>(sched_empty + kSchedDepth);
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(sched_w + kSchedDepth);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -217,7 +249,11 @@ __global__ void __launch_bounds__(256, 1) umma_grouped_kernel(
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tmem_full[s], 1);
-      mbar_init(&tmem_empty[s], 4);   // one arrive per epilogue warp
+      mbar_init(&tmem_empty[s], EW);   // one arrive per epilogue warp
+    }
+    for (int s = 0; s < kSchedDepth; ++s) {
+      mbar_init(&sched_full[s], 1);
+      mbar_init(&sched_empty[s], 1 + EW);   // MMA warp + epilogue warps
     }
     fence_barrier_init();
   }
@@ -227,40 +263,105 @@ __global__ void __launch_bounds__(256, 1) umma_grouped_kernel(
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
 
-  const int total_work = *num_tiles_ptr * n_feat_tiles;
+  const int n_tiles = tiles ? *num_tiles_ptr : (dense_rows + BN - 1) / BN;
+  const int total_work = n_tiles * n_feat_tiles;
+
+  // consumer side of the work queue: n-th work index of this CTA (-1 = done)
+  auto next_work = [&](int n) -> int {
+    const int q = n % kSchedDepth;
+    mbar_wait(&sched_full[q], (n / kSchedDepth) & 1u);
+    const int w = sched_w[q];
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&sched_empty[q]);
+    return w;
+  };
 
   if (warp == 0) {
-    // ===================== TMA producer =====================
+    // ===================== TMA producer + dynamic tile scheduler =====================
     if (elect_one()) {
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+      int n_pushed = 0;
+      auto push_work = [&](int w) {
+        const int q = n_pushed % kSchedDepth;
+        mbar_wait(&sched_empty[q], ((n_pushed / kSchedDepth) & 1u) ^ 1u);
+        sched_w[q] = w;
+        mbar_arrive(&sched_full[q]);
+        ++n_pushed;
+      };
+      // the first item is static (blockIdx.x); later ones come from a global counter so CTAs
+      // always take the lowest unprocessed index: balanced, and neighbours in time share
+      // activation / weight tiles in L2
+      auto fetch_work = [&]() -> int {
+        const int w = atomicAdd(&sched[0], 1) + static_cast<int>(gridDim.x);
+        return w < total_work ? w : -1;
+      };
+      auto issue = [&](int w, int kb, int stage, bool do_w, bool do_x) {
         const int ti = w / n_feat_tiles, f = w - ti * n_feat_tiles;
-        const int4 tile = tiles[ti];
-        const int w_row = tile.x * w_rows_per_expert + f * kBM;
-        for (int kb = 0; kb < n_kblocks; ++kb) {
-          mbar_wait(&empty_bar[stage], phase ^ 1u);
-          unsigned char* sa = smem + stage * Cfg::kStageBytes;
+        const TileRef tile = get_tile<BN>(tiles, ti, dense_rows);
+        const int w_row = tile.expert * w_rows_per_expert + f * kBM;
+        unsigned char* sa = smem + stage * Cfg::kStageBytes;
+        if (do_w) {
           mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
           tma_load_2d(&tm_w, &full_bar[stage], sa, kb * kBK, w_row, kEvictFirst);
           if (GATED)
             tma_load_2d(&tm_w, &full_bar[stage], sa + Cfg::kABytes, kb * kBK, w_row + up_row_offset,
                         kEvictFirst);
-          tma_load_2d(&tm_x, &full_bar[stage], sa + (GATED ? 2 : 1) * Cfg::kABytes, kb * kBK, tile.y,
-                      kEvictLast);
-          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1u; }
         }
+        if (do_x)
+          tma_load_2d(&tm_x, &full_bar[stage], sa + (GATED ? 2 : 1) * Cfg::kABytes, kb * kBK,
+                      tile.row_start, kEvictLast);
+      };
+      int w = static_cast<int>(blockIdx.x) < total_work ? static_cast<int>(blockIdx.x) : -1;
+      push_work(w);
+      // (1) Before the dependency wait: weight tiles of the first item for the first pass over
+      //     the ring.  Weights and the work list are at least two launches old (see common.cuh),
+      //     so this overlaps the predecessor's tail with our pipeline fill.
+      int kb = 0, n_pre = 0;
+      if (w >= 0)
+        for (; n_pre < Cfg::kStages && n_pre < n_kblocks; ++n_pre) issue(w, n_pre, n_pre, true, false);
+      pdl_wait();
+      pdl_launch();
+      // (2) the activation tiles of those stages (written by the direct predecessor)
+      for (int i = 0; i < n_pre; ++i) issue(w, i, i, false, true);
+      kb = n_pre;
+      int stage = n_pre == Cfg::kStages ? 0 : n_pre;
+      uint32_t phase = n_pre == Cfg::kStages ? 1u : 0u;
+      // (3) steady state
+      while (w >= 0) {
+        if (kb == n_kblocks) {
+          kb = 0;
+          w = fetch_work();
+          push_work(w);
+          continue;
+        }
+        mbar_wait(&empty_bar[stage], phase ^ 1u);
+        issue(w, kb, stage, true, true);
+        ++kb;
+        if (++stage == Cfg::kStages) { stage = 0; phase ^= 1u; }
+      }
+      // last CTA out re-arms the counters for the next launch
+      __threadfence();
+      if (atomicAdd(&sched[1], 1) == static_cast<int>(gridDim.x) - 1) {
+        sched[0] = 0;
+        sched[1] = 0;
+        __threadfence();
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    constexpr uint32_t idesc = make_idesc(sizeof(T) == 2 && !std::is_same<T, __half>::value, BN);
+    constexpr uint32_t idesc_base = make_idesc(sizeof(T) == 2 && !std::is_same<T, __half>::value, 0);
     int stage = 0;
     uint32_t phase = 0;
-    int it = 0;
-    for (int w = blockIdx.x; w < total_work; w += gridDim.x, ++it) {
-      const int as = it & 1;
-      const uint32_t aphase = (it >> 1) & 1u;
+    for (int it = 0;; ++it) {
+      const int w = next_work(it);
+      if (w < 0) break;
+      const int ti = w / n_feat_tiles;
+      const TileRef tile = get_tile<BN>(tiles, ti, dense_rows);
+      // MMA N follows the rows this tile really holds (multiple of 16): a ragged tail tile of an
+      // expert costs tensor time in proportion to its rows, not to BN.
+      const int n_eff = min(BN, (tile.nrows + 15) & ~15);
+      const uint32_t idesc = idesc_base | (static_cast<uint32_t>(n_eff >> 3) << 17);
+      const int as = AS == 2 ? (it & 1) : 0;
+      const uint32_t aphase = AS == 2 ? ((it >> 1) & 1u) : (it & 1u);
       mbar_wait(&tmem_empty[as], aphase ^ 1u);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + as * Cfg::kAccCols;
@@ -270,15 +371,13 @@ __global__ void __launch_bounds__(256, 1) umma_grouped_kernel(
         if (elect_one()) {
           const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
           const uint64_t a_desc = make_kmajor_desc(sa);
+          const uint64_t u_desc = make_kmajor_desc(sa + Cfg::kABytes);
           const uint64_t b_desc = make_kmajor_desc(sa + (GATED ? 2 : 1) * Cfg::kABytes);
 #pragma unroll
           for (int ks = 0; ks < kBK / 16; ++ks) {
             const uint32_t acc = (kb > 0 || ks > 0) ? 1u : 0u;
             umma_f16(d_tmem, a_desc + 2 * ks, b_desc + 2 * ks, idesc, acc);
-            if (GATED) {
-              const uint64_t u_desc = make_kmajor_desc(sa + Cfg::kABytes);
-              umma_f16(d_tmem + BN, u_desc + 2 * ks, b_desc + 2 * ks, idesc, acc);
-            }
+            if (GATED) umma_f16(d_tmem + BN, u_desc + 2 * ks, b_desc + 2 * ks, idesc, acc);
           }
           umma_commit(&empty_bar[stage]);                       // smem slot free when MMAs finish
           if (kb == n_kblocks - 1) umma_commit(&tmem_full[as]); // accumulator ready
@@ -289,44 +388,61 @@ __global__ void __launch_bounds__(256, 1) umma_grouped_kernel(
     }
   } else if (warp >= 4) {
     // ===================== epilogue =====================
-    const int ew = warp - 4;                      // TMEM lanes [32*ew, 32*ew+32)
+    // EW = 4: warp q owns TMEM lanes [32q, 32q+32) and all token columns.
+    // EW = 8: two warps share a lane quadrant and take alternate 16-column chunks.
+    const int ew = (warp - 4) & 3;
+    const int chunk0 = (warp - 4) >> 2;           // 0, or 1 for the second warp of a quadrant
+    constexpr int kChunkStep = 16 * (EW / 4);
     const uint32_t lane_base = static_cast<uint32_t>(ew * 32) << 16;
-    int it = 0;
-    for (int w = blockIdx.x; w < total_work; w += gridDim.x, ++it) {
+    for (int it = 0;; ++it) {
+      const int w = next_work(it);
+      if (w < 0) break;
       const int ti = w / n_feat_tiles, f = w - ti * n_feat_tiles;
-      const int4 tile = tiles[ti];
-      const int as = it & 1;
-      const uint32_t aphase = (it >> 1) & 1u;
+      const TileRef tile = get_tile<BN>(tiles, ti, dense_rows);
+      const int as = AS == 2 ? (it & 1) : 0;
+      const uint32_t aphase = AS == 2 ? ((it >> 1) & 1u) : (it & 1u);
       mbar_wait(&tmem_full[as], aphase);
       tc_fence_after();
       const uint32_t t_acc = tmem_base + lane_base + as * Cfg::kAccCols;
       const int feat = f * kBM + ew * 32 + lane;
-      T* out_col = out + static_cast<size_t>(tile.y) * ld_out + feat;
+      const bool feat_ok = MODE != kModePlain || feat < n_feat_valid;
+      T* out_col = out + static_cast<size_t>(tile.row_start) * ld_out + feat;
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 16) {
-        if (c0 >= tile.z) break;                  // warp-uniform: remaining token columns unused
+      for (int c0 = 16 * chunk0; c0 < BN; c0 += kChunkStep) {
+        if (c0 >= tile.nrows) break;              // warp-uniform: remaining token columns unused
         uint32_t g[16];
         tmem_ld16(t_acc + c0, g);
-        if (GATED) {
+        if (MODE == kModeGated) {
           uint32_t u[16];
           tmem_ld16(t_acc + BN + c0, u);
           tmem_ld_wait();
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
-            if (c0 + j < tile.z) {
-              const float v = silu_f(__uint_as_float(g[j])) * __uint_as_float(u[j]);
+            if (c0 + j < tile.nrows) {
+              const float v = silu_fast(__uint_as_float(g[j])) * __uint_as_float(u[j]);
               out_col[static_cast<size_t>(c0 + j) * ld_out] = Dt<T>::from_f(v);
             }
+          }
+        } else if (MODE == kModeDown) {
+          // lane j (< 16) fetches the routing weight of token column c0 + j once; broadcast by shuffle
+          float rw_lane = 1.0f;
+          {
+            const int row = tile.row_start + c0 + (lane & 15);
+            if (c0 + (lane & 15) < tile.nrows && row < n_routed_rows) rw_lane = __ldg(row_weight + row);
+          }
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const float rw = __shfl_sync(0xffffffffu, rw_lane, j);
+            if (c0 + j < tile.nrows)
+              out_col[static_cast<size_t>(c0 + j) * ld_out] = Dt<T>::from_f(__uint_as_float(g[j]) * rw);
           }
         } else {
           tmem_ld_wait();
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
-            if (c0 + j < tile.z) {
-              const int row = tile.y + c0 + j;
-              const float rw = row < n_routed_rows ? __ldg(row_weight + row) : 1.0f;
-              out_col[static_cast<size_t>(c0 + j) * ld_out] = Dt<T>::from_f(__uint_as_float(g[j]) * rw);
-            }
+            if (c0 + j < tile.nrows && feat_ok)
+              out_col[static_cast<size_t>(c0 + j) * ld_out] = Dt<T>::from_f(__uint_as_float(g[j]));
           }
         }
       }
@@ -379,42 +495,50 @@ int umma_make_tensor_map(void* map_out, const void* base, int dtype, uint64_t ro
   return r == CUDA_SUCCESS ? GLM4MOE_OK : GLM4MOE_ERR_ARG;
 }
 
-template <typename T, int BN, bool GATED>
+template <typename T, int BN, int MODE>
 static int launch_one(const UmmaLaunch& a, cudaStream_t st) {
-  using Cfg = UmmaCfg<BN, GATED>;
-  auto kern = umma_grouped_kernel<T, BN, GATED>;
+  using Cfg = UmmaCfg<BN, MODE>;
+  auto kern = umma_grouped_kernel<T, BN, MODE>;
   static bool attr_set = false;   // per instantiation
   if (!attr_set) {
     GLM4MOE_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                             Cfg::kSmemBytes));
     attr_set = true;
   }
-  kern<<<a.grid, 256, Cfg::kSmemBytes, st>>>(
-      *static_cast<const CUtensorMap*>(a.tm_w), *static_cast<const CUtensorMap*>(a.tm_x),
-      reinterpret_cast<const int4*>(a.tiles), a.num_tiles, static_cast<T*>(a.out), a.ld_out,
-      a.row_weight, a.n_routed_rows, a.n_feat_tiles, a.n_kblocks, a.w_rows_per_expert,
-      a.up_row_offset);
-  GLM4MOE_LAUNCH_CHECK();
+  GLM4MOE_CUDA_CHECK(launch_pdl(
+      kern, dim3(a.grid), dim3(Cfg::kThreads), Cfg::kSmemBytes, st, *static_cast<const CUtensorMap*>(a.tm_w),
+      *static_cast<const CUtensorMap*>(a.tm_x), reinterpret_cast<const int4*>(a.tiles), a.num_tiles, a.dense_rows,
+      static_cast<T*>(a.out), a.ld_out, a.row_weight, a.n_routed_rows, a.n_feat_tiles, a.n_feat_valid, a.n_kblocks,
+      a.w_rows_per_expert, a.up_row_offset, a.sched));
   return GLM4MOE_OK;
 }
 
-template <typename T, bool GATED>
+template <typename T, int MODE>
 static int launch_bn(const UmmaLaunch& a, cudaStream_t st) {
   switch (a.tile_rows) {
-    case 16: return launch_one<T, 16, GATED>(a, st);
-    case 32: return launch_one<T, 32, GATED>(a, st);
-    case 64: return launch_one<T, 64, GATED>(a, st);
-    case 128: return launch_one<T, 128, GATED>(a, st);
+    case 16: return launch_one<T, 16, MODE>(a, st);
+    case 32: return launch_one<T, 32, MODE>(a, st);
+    case 64: return launch_one<T, 64, MODE>(a, st);
+    case 128: return launch_one<T, 128, MODE>(a, st);
+    case 256: return launch_one<T, 256, MODE>(a, st);
+    default: return GLM4MOE_ERR_ARG;
+  }
+}
+
+template <typename T>
+static int launch_mode(const UmmaLaunch& a, cudaStream_t st) {
+  switch (a.mode) {
+    case kModeDown: return launch_bn<T, kModeDown>(a, st);
+    case kModeGated: return launch_bn<T, kModeGated>(a, st);
+    case kModePlain: return launch_bn<T, kModePlain>(a, st);
     default: return GLM4MOE_ERR_ARG;
   }
 }
 
 int umma_launch(const UmmaLaunch& a, void* stream) {
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (a.dtype == GLM4MOE_BF16)
-    return a.gated ? launch_bn<__nv_bfloat16, true>(a, st) : launch_bn<__nv_bfloat16, false>(a, st);
-  if (a.dtype == GLM4MOE_F16)
-    return a.gated ? launch_bn<__half, true>(a, st) : launch_bn<__half, false>(a, st);
+  if (a.dtype == GLM4MOE_BF16) return launch_mode<__nv_bfloat16>(a, st);
+  if (a.dtype == GLM4MOE_F16) return launch_mode<__half>(a, st);
   return GLM4MOE_ERR_UNSUPPORTED;
 }
 
