@@ -129,6 +129,8 @@ def main():
     ap.add_argument("--sweep", action="store_true", help="also report T in {1..256, 4096} in `sweep`")
     ap.add_argument("--cpu-steps", type=int, default=0, help="cpu_baseline steps (0 = about 15 s of CPU work)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--ep-layout", default="allreduce", choices=["allreduce", "alltoall"],
+                    help="expert-parallel layout for --gpus > 1 (distributed.py)")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -173,20 +175,23 @@ def main():
     if world > 1:
         dist.barrier()
 
-    weights = synth.make_weights(shape, dt)
     torch.set_default_dtype(dt)
+    torch.set_default_device(dev)
     moe = glm4_moe_b200.Glm4MoeMoE(_hf_config(shape), max_tokens=max(T, 256), ep_rank=rank, ep_size=world)
+    torch.set_default_device("cpu")
     torch.set_default_dtype(torch.float32)
-    moe.load_stacked(weights)
-    moe = moe.to(dev)
+    weights = synth.make_weights_device(shape, dt, dev, experts=range(moe.expert_begin, moe.expert_end))
+    moe.load_local_stacks(weights)
+    if world > 1:
+        from glm4_moe_b200.distributed import ExpertParallelMoE
+        layer = ExpertParallelMoE(moe, shape.E, layout=args.ep_layout)
+    else:
+        layer = moe
     batches_host = [synth.make_tokens(shape, T, dt, b).pin_memory() for b in range(N_BATCHES)]
     batches = [b.to(dev) for b in batches_host]
 
     def step(x):
-        y = moe(x)
-        if world > 1:
-            dist.all_reduce(y)
-        return y
+        return layer(x)
 
     with torch.inference_mode():
         for i in range(max(args.warmup, 3)):
@@ -228,18 +233,32 @@ def main():
             hits.append(int(torch.unique(local).numel()))
         U = sum(hits) / len(hits)
 
-        # end-to-end through the host-buffer entry
+        # end-to-end through the public API with host buffers: pinned host tokens in, result on the host
         out_host = torch.empty((T, shape.H), dtype=dt).pin_memory()
-        e2e = None
-        if world == 1:
-            for i in range(3):
-                moe.forward_host(batches_host[i], out_host)
-            t0 = time.perf_counter()
-            for i in range(args.steps):
-                moe.forward_host(batches_host[i % N_BATCHES], out_host)
-            e2e_s = time.perf_counter() - t0
-            e2e = {"value": T * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": T * shape.H * 2,
-                   "d2h_bytes_per_step": T * shape.H * 2, "ms_per_step": e2e_s / args.steps * 1e3}
+
+        def e2e_step(i):
+            if world == 1:
+                moe.forward_host(batches_host[i % N_BATCHES], out_host)     # glm4moe_layer_forward_host
+            else:
+                y = layer(batches_host[i % N_BATCHES].to(dev, non_blocking=True))
+                if rank == 0:
+                    out_host.copy_(y, non_blocking=True)
+                torch.cuda.synchronize()
+
+        for i in range(3):
+            e2e_step(i)
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        for i in range(args.steps):
+            e2e_step(i)
+        e2e_s = time.perf_counter() - t0
+        if world > 1:
+            t = torch.tensor([e2e_s], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            e2e_s = float(t.item())
+        e2e = {"value": T * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": T * shape.H * 2 * world,
+               "d2h_bytes_per_step": T * shape.H * 2, "ms_per_step": e2e_s / args.steps * 1e3}
 
         sweep = None
         if args.sweep and world == 1:
@@ -277,8 +296,8 @@ def main():
     H, I, k = shape.H, shape.I, shape.k
     # dominant kernel: gate_up grouped GEMM. Algorithmic bytes of one launch = gate_up weights of
     # the (U local + shared) experts it touches + the activation rows it reads + act rows it writes.
-    n_sh = 1 if moe.with_shared else 0
-    rows = T * k / world + n_sh * T
+    n_sh = 1
+    rows = T * k / world + T / world
     gu_bytes = (U + n_sh) * 2 * I * H * 2 + rows * H * 2 + rows * I * 2
     gu_ms = stage_acc["gate_up"]
     achieved = gu_bytes / gu_ms / 1e6
@@ -293,7 +312,8 @@ def main():
     cpu_baseline = None
     if world == 1 and not args.no_cpu_baseline:
         n = args.cpu_steps or 40
-        tps, ms, cores = _cpu_reference_run(shape, dt, weights, T, n, 2)
+        host_w = {k_: v.cpu() for k_, v in weights.items()}
+        tps, ms, cores = _cpu_reference_run(shape, dt, host_w, T, n, 2)
         cpu_baseline = {"value": tps, "unit": UNIT, "cores": cores, "kind": "port", "ms_per_step": ms,
                         "sample": f"{n} steps of the same workload (T={T}) after 2 warm-up, oracle port of the "
                                   "reference torch path (moe.py:128-176), torch threads = all host cores"}
@@ -301,7 +321,7 @@ def main():
             "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": workload, "tokens_per_step": T, "experts_hit_mean": U,
-                       "parallelism": f"ep{world}" if world > 1 else "single",
+                       "parallelism": f"ep{world}-{args.ep_layout}" if world > 1 else "single",
                        "l2": f"{N_BATCHES} distinct token batches rotated; weights touched per step "
                              f"({(U + 1) * 3 * H * I * 2 / 1e9:.2f} GB) exceed the 126 MB L2",
                        "expert_gemm_impl": moe.last_impl},

@@ -23,7 +23,7 @@ SYMBOLS = [
     "glm4moe_permute", "glm4moe_permute_scratch_elems", "glm4moe_tile_capacity", "glm4moe_gather_rows",
     "glm4moe_expert_gate_up_simt", "glm4moe_expert_down_simt", "glm4moe_combine",
     "glm4moe_workspace_bytes", "glm4moe_layer_create", "glm4moe_layer_destroy",
-    "glm4moe_layer_forward", "glm4moe_layer_forward_timed", "glm4moe_layer_forward_host", "glm4moe_layer_view",
+    "glm4moe_layer_forward", "glm4moe_layer_forward_ex", "glm4moe_layer_forward_timed", "glm4moe_layer_forward_host", "glm4moe_layer_view",
     "glm4moe_layer_last_launches", "glm4moe_layer_last_impl", "glm4moe_layer_tile_rows",
 ]
 
@@ -62,20 +62,21 @@ def load() -> C.CDLL:
     lib.glm4moe_error_string.argtypes = [i32]
     lib.glm4moe_router_logits.argtypes = [vp, vp, vp, i32, i32, i32, i32, vp]
     lib.glm4moe_router_select.argtypes = [vp, vp, i32, i32, i32, f32, i32, vp, vp, vp]
-    lib.glm4moe_permute.argtypes = [vp, vp, i32, i32, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, i32, vp, vp, vp]
+    lib.glm4moe_permute.argtypes = [vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, i32, vp, vp, vp]
     lib.glm4moe_permute_scratch_elems.restype = sz
     lib.glm4moe_permute_scratch_elems.argtypes = [i32, i32]
     lib.glm4moe_tile_capacity.restype = C.c_int32
     lib.glm4moe_tile_capacity.argtypes = [i32, i32, i32, i32]
-    lib.glm4moe_gather_rows.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp]
+    lib.glm4moe_gather_rows.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp]
     lib.glm4moe_expert_gate_up_simt.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, vp]
     lib.glm4moe_expert_down_simt.argtypes = [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp]
-    lib.glm4moe_combine.argtypes = [vp, vp, vp, i32, i32, i32, i32, i32, vp]
+    lib.glm4moe_combine.argtypes = [vp, vp, vp, i32, i32, i32, i32, i32, i32, vp]
     lib.glm4moe_workspace_bytes.restype = sz
     lib.glm4moe_workspace_bytes.argtypes = [C.POINTER(Config)]
     lib.glm4moe_layer_create.argtypes = [C.POINTER(Config), vp, vp, vp, vp, vp, vp, vp, sz, C.POINTER(vp)]
     lib.glm4moe_layer_destroy.argtypes = [vp]
     lib.glm4moe_layer_forward.argtypes = [vp, vp, vp, i32, vp]
+    lib.glm4moe_layer_forward_ex.argtypes = [vp, vp, vp, i32, i32, i32, vp]
     lib.glm4moe_layer_forward_timed.argtypes = [vp, vp, vp, i32, vp, C.POINTER(C.c_float)]
     lib.glm4moe_layer_forward_host.argtypes = [vp, vp, vp, i32, vp, vp, vp]
     lib.glm4moe_layer_view.argtypes = [vp, i32, C.POINTER(vp), C.POINTER(sz)]

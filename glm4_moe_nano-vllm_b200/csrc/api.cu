@@ -211,7 +211,8 @@ extern "C" int glm4moe_layer_tile_rows(const glm4moe_layer_t* l, int T) {
   return l->umma_ok ? kBnChoices[pick_bn_index(l->cfg, T)] : kSimtRows;
 }
 
-static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, void* stream, cudaEvent_t* ev) {
+static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, void* stream, cudaEvent_t* ev,
+                        int sh_lo_arg = -1, int sh_hi_arg = -1) {
   if (!l || !x || !out) return GLM4MOE_ERR_ARG;
   cudaStream_t cst = static_cast<cudaStream_t>(stream);
 #define STAGE_MARK(i)                                        \
@@ -238,6 +239,23 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
   void* x_rows = ws + L.x_rows;
   void* act = ws + L.act;
   void* y = ws + L.y;
+  // shared-expert rows this rank computes: all tokens, none, or (with_shared == 2) its 1/R slice
+  // of the tokens so expert-parallel ranks stay balanced (the partial outputs are summed later)
+  int sh_lo = 0, sh_hi = 0;
+  if (c.with_shared == 1) {
+    sh_hi = T;
+  } else if (c.with_shared == 2) {
+    const int n_local = c.expert_end - c.expert_begin;
+    const int R = n_local > 0 ? E / n_local : 1, r = n_local > 0 ? c.expert_begin / n_local : 0;
+    const int per = (T + R - 1) / R;
+    sh_lo = r * per < T ? r * per : T;
+    sh_hi = sh_lo + per < T ? sh_lo + per : T;
+  }
+  if (sh_lo_arg >= 0) {   // explicit range (glm4moe_layer_forward_ex)
+    if (sh_hi_arg > T || sh_lo_arg > sh_hi_arg) return GLM4MOE_ERR_ARG;
+    sh_lo = sh_lo_arg;
+    sh_hi = sh_hi_arg;
+  }
   const bool use_umma = l->umma_ok;
   const int bi = pick_bn_index(c, T);
   const int tile_rows = use_umma ? kBnChoices[bi] : kSimtRows;
@@ -274,11 +292,11 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
   if ((rc = glm4moe_router_select(logits, l->bias, T, E, k, c.routed_scaling_factor, c.dtype, idx, w, stream)))
     return rc;
   STAGE_MARK(2);
-  if ((rc = glm4moe_permute(idx, w, T, k, E, c.expert_begin, c.expert_end, tile_rows, c.with_shared, offsets,
+  if ((rc = glm4moe_permute(idx, w, T, k, E, c.expert_begin, c.expert_end, tile_rows, sh_lo, sh_hi, offsets,
                             row_token, row_weight, slot_row, tiles, L.tile_capacity, num_tiles, scratch, stream)))
     return rc;
   STAGE_MARK(3);
-  if ((rc = glm4moe_gather_rows(x, row_token, offsets, x_rows, T, k, E, H, c.with_shared, c.dtype, stream)))
+  if ((rc = glm4moe_gather_rows(x, row_token, offsets, x_rows, T, k, E, H, sh_lo, sh_hi, c.dtype, stream)))
     return rc;
   launches += T <= 256 ? 4 : 6;
   STAGE_MARK(4);
@@ -329,7 +347,7 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
   }
   launches += 2;
   STAGE_MARK(6);
-  if ((rc = glm4moe_combine(y, slot_row, out, T, k, H, c.with_shared, c.dtype, stream))) return rc;
+  if ((rc = glm4moe_combine(y, slot_row, out, T, k, H, sh_lo, sh_hi, c.dtype, stream))) return rc;
   STAGE_MARK(7);
 #undef STAGE_MARK
   launches += 1;
@@ -340,6 +358,12 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
 
 extern "C" int glm4moe_layer_forward(glm4moe_layer_t* l, const void* x, void* out, int T, void* stream) {
   return forward_impl(l, x, out, T, stream, nullptr);
+}
+
+extern "C" int glm4moe_layer_forward_ex(glm4moe_layer_t* l, const void* x, void* out, int T, int shared_lo,
+                                        int shared_hi, void* stream) {
+  if (shared_lo < 0 || shared_hi < shared_lo) return GLM4MOE_ERR_ARG;
+  return forward_impl(l, x, out, T, stream, nullptr, shared_lo, shared_hi);
 }
 
 extern "C" int glm4moe_layer_forward_timed(glm4moe_layer_t* l, const void* x, void* out, int T, void* stream,

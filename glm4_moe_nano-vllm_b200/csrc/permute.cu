@@ -60,7 +60,7 @@ __global__ void __launch_bounds__(kTokPerBlock) permute_rank_kernel(
 // One block of 256 threads; thread e owns expert e.
 __global__ void __launch_bounds__(256) permute_scan_kernel(
     int32_t* __restrict__ block_counts /*[nblk][E] in: counts, out: exclusive prefix over blocks*/,
-    int nblk, int E, int T, int k, int e_lo, int e_hi, int tile_rows, int with_shared,
+    int nblk, int E, int T, int k, int e_lo, int e_hi, int tile_rows, int sh_lo, int sh_hi,
     int32_t* __restrict__ expert_offsets /*[E+1]*/, int4* __restrict__ tiles, int tile_capacity,
     int32_t* __restrict__ num_tiles) {
   __shared__ int s_cnt[kMaxExperts];
@@ -89,25 +89,26 @@ __global__ void __launch_bounds__(256) permute_scan_kernel(
     }
     s_off[E] = off;
     s_tile_off[E] = toff;
-    const int shared_tiles = with_shared ? (T + tile_rows - 1) / tile_rows : 0;
+    const int shared_tiles = (sh_hi - sh_lo + tile_rows - 1) / tile_rows;
     const int n = toff + shared_tiles;
     *num_tiles = n <= tile_capacity ? n : 0;   // capacity is sized for the worst case; 0 = refuse
   }
   __syncthreads();
   if (e < E) expert_offsets[e] = s_off[e];
   if (e == 0) expert_offsets[E] = s_off[E];
-  if (s_tile_off[E] + (with_shared ? (T + tile_rows - 1) / tile_rows : 0) > tile_capacity) return;
+  if (s_tile_off[E] + (sh_hi - sh_lo + tile_rows - 1) / tile_rows > tile_capacity) return;
   if (e < E) {
     const int n = s_cnt[e];
     int ti = s_tile_off[e];
     for (int r = 0; r < n; r += tile_rows, ++ti)
       tiles[ti] = make_int4(e - e_lo, s_off[e] + r, min(tile_rows, n - r), 0);
   }
-  if (with_shared) {
+  {
     const int base = s_tile_off[E];
-    const int nt = (T + tile_rows - 1) / tile_rows;
+    const int nt = (sh_hi - sh_lo + tile_rows - 1) / tile_rows;
     for (int i = threadIdx.x; i < nt; i += blockDim.x)
-      tiles[base + i] = make_int4(e_hi - e_lo, T * k + i * tile_rows, min(tile_rows, T - i * tile_rows), 0);
+      tiles[base + i] = make_int4(e_hi - e_lo, T * k + sh_lo + i * tile_rows,
+                                  min(tile_rows, sh_hi - sh_lo - i * tile_rows), 0);
   }
 }
 
@@ -137,7 +138,7 @@ __global__ void __launch_bounds__(kTokPerBlock) permute_scatter_kernel(
 // Decode-size batches (T <= 256): the three phases above in ONE block, thread t owns token t.
 __global__ void __launch_bounds__(kTokPerBlock) permute_small_kernel(
     const int32_t* __restrict__ idx, const float* __restrict__ w, int T, int k, int E, int e_lo,
-    int e_hi, int tile_rows, int with_shared, int32_t* __restrict__ expert_offsets,
+    int e_hi, int tile_rows, int sh_lo, int sh_hi, int32_t* __restrict__ expert_offsets,
     int32_t* __restrict__ row_token, float* __restrict__ row_weight, int32_t* __restrict__ slot_row,
     int4* __restrict__ tiles, int tile_capacity, int32_t* __restrict__ num_tiles) {
   __shared__ uint32_t bitmap[kMaxExperts * kWordsPerExpert];
@@ -191,7 +192,7 @@ __global__ void __launch_bounds__(kTokPerBlock) permute_small_kernel(
     if (tid == 31) { s_off[E] = rows_incl; s_tile_off[E] = tl_incl; }
   }
   __syncthreads();
-  const int shared_tiles = with_shared ? (T + tile_rows - 1) / tile_rows : 0;
+  const int shared_tiles = (sh_hi - sh_lo + tile_rows - 1) / tile_rows;
   const bool fits = s_tile_off[E] + shared_tiles <= tile_capacity;
   if (tid == 0) *num_tiles = fits ? s_tile_off[E] + shared_tiles : 0;
   for (int e = tid; e <= E; e += kTokPerBlock) expert_offsets[e] = s_off[e];
@@ -203,8 +204,8 @@ __global__ void __launch_bounds__(kTokPerBlock) permute_small_kernel(
         tiles[ti] = make_int4(e - e_lo, s_off[e] + r, min(tile_rows, n - r), 0);
     }
     for (int i = tid; i < shared_tiles; i += kTokPerBlock)
-      tiles[s_tile_off[E] + i] =
-          make_int4(e_hi - e_lo, T * k + i * tile_rows, min(tile_rows, T - i * tile_rows), 0);
+      tiles[s_tile_off[E] + i] = make_int4(e_hi - e_lo, T * k + sh_lo + i * tile_rows,
+                                           min(tile_rows, sh_hi - sh_lo - i * tile_rows), 0);
   }
   if (tid < T) {
     for (int s = 0; s < k; ++s) {
@@ -231,7 +232,7 @@ __global__ void __launch_bounds__(256) gather_rows_kernel(const uint4* __restric
                                                           const int32_t* __restrict__ row_token,
                                                           const int32_t* __restrict__ expert_offsets,
                                                           uint4* __restrict__ x_rows, int T, int k,
-                                                          int E, int vec_per_row, int with_shared) {
+                                                          int E, int vec_per_row, int sh_lo, int sh_hi) {
   pdl_wait();
   pdl_launch();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -243,8 +244,8 @@ __global__ void __launch_bounds__(256) gather_rows_kernel(const uint4* __restric
     if (row >= n_routed) return;
     src = row_token[row];
   } else {
-    if (!with_shared || row >= Tk + T) return;
     src = row - Tk;
+    if (src < sh_lo || src >= sh_hi) return;
   }
   const uint4* s = x + static_cast<size_t>(src) * vec_per_row;
   uint4* d = x_rows + static_cast<size_t>(row) * vec_per_row;
@@ -267,7 +268,7 @@ extern "C" int32_t glm4moe_tile_capacity(int T, int k, int E, int tile_rows) {
 }
 
 extern "C" int glm4moe_permute(const int32_t* idx, const float* w, int T, int k, int E, int e_lo,
-                               int e_hi, int tile_rows, int with_shared, int32_t* expert_offsets,
+                               int e_hi, int tile_rows, int shared_lo, int shared_hi, int32_t* expert_offsets,
                                int32_t* row_token, float* row_weight, int32_t* slot_row,
                                int32_t* tiles, int32_t tile_capacity, int32_t* num_tiles,
                                int32_t* scratch, void* stream) {
@@ -275,14 +276,14 @@ extern "C" int glm4moe_permute(const int32_t* idx, const float* w, int T, int k,
       !num_tiles || !scratch)
     return GLM4MOE_ERR_ARG;
   if (T < 0 || k <= 0 || E <= 0 || E > kMaxExperts || tile_rows <= 0 || e_lo < 0 || e_hi > E ||
-      e_lo > e_hi)
+      e_lo > e_hi || shared_lo < 0 || shared_hi > T || shared_lo > shared_hi)
     return GLM4MOE_ERR_ARG;
   if (tile_capacity < glm4moe_tile_capacity(T, k, E, tile_rows)) return GLM4MOE_ERR_WORKSPACE;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int nblk = (T + kTokPerBlock - 1) / kTokPerBlock;
   if (T > 0 && T <= kTokPerBlock) {
     GLM4MOE_CUDA_CHECK(launch_pdl(permute_small_kernel, dim3(1), dim3(kTokPerBlock), 0, st, idx, w, T, k, E, e_lo,
-                                  e_hi, tile_rows, with_shared, expert_offsets, row_token, row_weight, slot_row,
+                                  e_hi, tile_rows, shared_lo, shared_hi, expert_offsets, row_token, row_weight, slot_row,
                                   reinterpret_cast<int4*>(tiles), tile_capacity, num_tiles));
     return GLM4MOE_OK;
   }
@@ -294,7 +295,7 @@ extern "C" int glm4moe_permute(const int32_t* idx, const float* w, int T, int k,
                                   e_hi, local_rank, block_counts));
   }
   GLM4MOE_CUDA_CHECK(launch_pdl(permute_scan_kernel, dim3(1), dim3(256), 0, st, block_counts, nblk, E, T, k, e_lo,
-                                e_hi, tile_rows, with_shared, expert_offsets, reinterpret_cast<int4*>(tiles),
+                                e_hi, tile_rows, shared_lo, shared_hi, expert_offsets, reinterpret_cast<int4*>(tiles),
                                 tile_capacity, num_tiles));
   if (nblk > 0) {
     GLM4MOE_CUDA_CHECK(launch_pdl(permute_scatter_kernel, dim3(nblk), dim3(kTokPerBlock), 0, st, idx, w, T, k, E,
@@ -306,15 +307,15 @@ extern "C" int glm4moe_permute(const int32_t* idx, const float* w, int T, int k,
 
 extern "C" int glm4moe_gather_rows(const void* x, const int32_t* row_token,
                                    const int32_t* expert_offsets, void* x_rows, int T, int k, int E,
-                                   int H, int with_shared, int dtype, void* stream) {
+                                   int H, int shared_lo, int shared_hi, int dtype, void* stream) {
   if (!x || !row_token || !expert_offsets || !x_rows) return GLM4MOE_ERR_ARG;
   const int es = dtype_size(dtype);
   if ((static_cast<size_t>(H) * es) % 16 != 0) return GLM4MOE_ERR_UNSUPPORTED;
   if (T == 0) return GLM4MOE_OK;
-  const int rows = T * k + (with_shared ? T : 0);
+  const int rows = T * k + shared_hi;
   const int vec_per_row = H * es / 16;
   GLM4MOE_CUDA_CHECK(launch_pdl(gather_rows_kernel<2>, dim3((rows + 7) / 8), dim3(256), 0,
                                 static_cast<cudaStream_t>(stream), static_cast<const uint4*>(x), row_token,
-                                expert_offsets, static_cast<uint4*>(x_rows), T, k, E, vec_per_row, with_shared));
+                                expert_offsets, static_cast<uint4*>(x_rows), T, k, E, vec_per_row, shared_lo, shared_hi));
   return GLM4MOE_OK;
 }

@@ -137,7 +137,7 @@ template <typename T>
 __global__ void __launch_bounds__(256) combine_kernel(const T* __restrict__ y,
                                                       const int32_t* __restrict__ slot_row,
                                                       T* __restrict__ out, int Tn, int k, int H,
-                                                      int with_shared) {
+                                                      int sh_lo, int sh_hi) {
   constexpr int V = Dt<T>::kVec;
   const int t = blockIdx.x;
   const int nvec = H / V;
@@ -158,7 +158,7 @@ __global__ void __launch_bounds__(256) combine_kernel(const T* __restrict__ y,
 #pragma unroll
       for (int q = 0; q < V; ++q) acc[q] += v[q];
     }
-    if (with_shared) {
+    if (t >= sh_lo && t < sh_hi) {
       float v[V];
       const size_t r = static_cast<size_t>(Tn) * k + t;
       unpack16<T>(ld_stream16(reinterpret_cast<const uint4*>(y + r * H) + c), v);
@@ -240,7 +240,7 @@ extern "C" int glm4moe_expert_down_simt(const void* act, const void* w_down, con
 }
 
 extern "C" int glm4moe_combine(const void* y, const int32_t* slot_row, void* out, int T, int k,
-                               int H, int with_shared, int dtype, void* stream) {
+                               int H, int shared_lo, int shared_hi, int dtype, void* stream) {
   if (!y || !slot_row || !out || T < 0 || k <= 0 || k > 64) return GLM4MOE_ERR_ARG;
   if ((static_cast<size_t>(H) * dtype_size(dtype)) % 16 != 0) return GLM4MOE_ERR_UNSUPPORTED;
   if (T == 0) return GLM4MOE_OK;
@@ -248,6 +248,6 @@ extern "C" int glm4moe_combine(const void* y, const int32_t* slot_row, void* out
   GLM4MOE_DISPATCH_DTYPE(dtype, T_,
                          GLM4MOE_CUDA_CHECK(launch_pdl(combine_kernel<T_>, dim3(T), dim3(256), 0, st,
                                                        static_cast<const T_*>(y), slot_row, static_cast<T_*>(out), T,
-                                                       k, H, with_shared)));
+                                                       k, H, shared_lo, shared_hi)));
   return GLM4MOE_OK;
 }

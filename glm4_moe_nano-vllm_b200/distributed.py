@@ -1,0 +1,131 @@
+"""Expert-parallel GLM4-MoE block over the GPUs of one box (one process per GPU, NCCL/NVLink).
+
+The reference has no expert parallelism: its only distributed hook on this path is the dead
+`dist.all_reduce` in `RowParallelLinear.forward` (`nanovllm/layers/linear.py:153-154`, `tp_size`
+is pinned to 1 by `nanovllm/distributed/parallel_state.py:1-9`).  This module is the layer
+north_star puts in `nanovllm/distributed`: experts are sharded contiguously, rank r owns
+`[r*E/R, (r+1)*E/R)`; the router weights are replicated and routing is recomputed identically
+on every rank (deterministic kernels), so no routing metadata is exchanged.
+
+Two layouts:
+
+* ``allreduce`` (layout A) — activations entering the block are replicated (TP attention ends
+  in an all-reduce).  Each rank runs its local experts over all T tokens plus the shared expert
+  on its 1/R token slice, producing a partial `[T, H]`; one all-reduce sums the partials.  No
+  dispatch, no host sync, CUDA-graph capturable.
+* ``alltoall`` (layout B) — rank r owns tokens `[r*T/R, (r+1)*T/R)`, sends each owned token once
+  to every rank hosting one of its experts (all-to-all-v), the hosts return the weighted partial
+  sums over their local experts (reverse all-to-all-v), the owner adds them (and its shared
+  expert) and an all-gather rebuilds the replicated `[T, H]`.  Split sizes are read on the host
+  (one D2H sync per call), so this layout is eager-only.
+
+The per-rank compute is `Glm4MoeMoE(ep_rank, ep_size)`; tests replace it with an oracle-backed
+callable to exercise this file's bookkeeping on CPU with the gloo backend.
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+from torch import nn
+
+
+def expert_range(n_experts: int, rank: int, world: int) -> tuple[int, int]:
+    per = n_experts // world
+    if per * world != n_experts:
+        raise ValueError(f"{n_experts} experts do not divide over {world} ranks")
+    return rank * per, (rank + 1) * per
+
+
+def token_slice(T: int, rank: int, world: int) -> tuple[int, int]:
+    """Tokens owned by `rank`: contiguous ceil(T/R) chunks (same rule as the C library's
+    `with_shared == 2` shared-expert slice)."""
+    per = -(-T // world)
+    lo = min(rank * per, T)
+    return lo, min(lo + per, T)
+
+
+def dispatch_plan(idx: torch.Tensor, n_experts: int, world: int):
+    """For owned tokens with routing `idx [n, k]`: which ranks host at least one selected expert.
+    Returns (send_mask [n, R] bool, send_counts [R])."""
+    per = n_experts // world
+    dest = torch.div(idx, per, rounding_mode="floor")          # [n, k] rank hosting each expert
+    mask = torch.zeros((idx.shape[0], world), dtype=torch.bool, device=idx.device)
+    mask.scatter_(1, dest, True)
+    return mask, mask.sum(0)
+
+
+class ExpertParallelMoE(nn.Module):
+    def __init__(self, local_moe: nn.Module, n_experts: int, group=None, layout: str = "allreduce"):
+        super().__init__()
+        if layout not in ("allreduce", "alltoall"):
+            raise ValueError(layout)
+        self.local = local_moe
+        self.n_experts = n_experts
+        self.group = group
+        self.layout = layout
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+
+    @classmethod
+    def build(cls, config, group=None, layout: str = "allreduce", **kw) -> "ExpertParallelMoE":
+        from .moe import Glm4MoeMoE
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+        local = Glm4MoeMoE(config, ep_rank=rank, ep_size=world, **kw)
+        return cls(local, config.n_routed_experts, group, layout)
+
+    # ---- layout A --------------------------------------------------------------------------
+    def _forward_allreduce(self, h: torch.Tensor) -> torch.Tensor:
+        y = self.local(h)                       # local experts + shared expert on this rank's slice
+        dist.all_reduce(y, group=self.group)
+        return y
+
+    # ---- layout B --------------------------------------------------------------------------
+    def _forward_alltoall(self, h: torch.Tensor) -> torch.Tensor:
+        T, H = h.shape
+        R, r = self.world, self.rank
+        lo, hi = token_slice(T, r, R)
+        own = h[lo:hi]
+        n_own = hi - lo
+        # routing of the owned tokens decides the destinations (self is always a destination: the
+        # shared expert of an owned token runs on its owner)
+        if n_own:
+            idx, _ = self.local.gate(own)
+            mask, _ = dispatch_plan(idx, self.n_experts, R)
+            mask[:, r] = True
+        else:
+            mask = torch.zeros((0, R), dtype=torch.bool, device=h.device)
+        send_counts = mask.sum(0)
+        recv_counts = torch.empty_like(send_counts)
+        dist.all_to_all_single(recv_counts, send_counts, group=self.group)
+        sc, rc = send_counts.tolist(), recv_counts.tolist()          # host sync
+        # rows ordered by destination rank, token-ascending inside a destination
+        tok_of_row = torch.cat([torch.nonzero(mask[:, d]).flatten() for d in range(R)]) if n_own else \
+            torch.zeros(0, dtype=torch.long, device=h.device)
+        send = own[tok_of_row]
+        recv = torch.empty((sum(rc), H), dtype=h.dtype, device=h.device)
+        dist.all_to_all_single(recv, send, rc, sc, group=self.group)
+        # put this rank's own tokens first so the shared expert covers exactly rows [0, n_own)
+        starts = [sum(rc[:d]) for d in range(R)]
+        order = list(range(starts[r], starts[r] + rc[r])) + \
+            [i for d in range(R) if d != r for i in range(starts[d], starts[d] + rc[d])]
+        order_t = torch.tensor(order, dtype=torch.long, device=h.device)
+        part = self.local(recv[order_t], shared_range=(0, rc[r]))    # local experts (+ shared on own rows)
+        back = torch.empty_like(part)
+        back[order_t] = part
+        ret = torch.empty_like(send)
+        dist.all_to_all_single(ret, back, sc, rc, group=self.group)
+        acc = torch.zeros((n_own, H), dtype=torch.float32, device=h.device)
+        acc.index_add_(0, tok_of_row, ret.float())
+        mine = acc.to(h.dtype)
+        per = -(-T // R)
+        padded = torch.zeros((per, H), dtype=h.dtype, device=h.device)
+        padded[:n_own] = mine
+        gathered = torch.empty((R * per, H), dtype=h.dtype, device=h.device)
+        dist.all_gather_into_tensor(gathered, padded, group=self.group)
+        return gathered[:T].contiguous()
+
+    def forward(self, hidden_states: torch.Tensor) -> torch.Tensor:
+        h = hidden_states.reshape(-1, hidden_states.shape[-1])
+        if self.layout == "allreduce":
+            return self._forward_allreduce(h)
+        return self._forward_alltoall(h)

@@ -137,7 +137,8 @@ class Glm4MoeMoE(nn.Module):
         self.ep_rank, self.ep_size = ep_rank, ep_size
         self.expert_begin = ep_rank * (E // ep_size)
         self.expert_end = self.expert_begin + E // ep_size
-        self.with_shared = ep_rank == 0
+        # single GPU: shared expert on every token; expert-parallel: on this rank's 1/R token slice
+        self.with_shared = 1 if ep_size == 1 else 2
         self.impl = impl
         n_local = self.expert_end - self.expert_begin
         # stacked storage, created under the process-wide default dtype/device like the
@@ -218,8 +219,9 @@ class Glm4MoeMoE(nn.Module):
         self._cfg = cfg
 
     # ---- reference API ----------------------------------------------------------------------
-    def forward(self, hidden_states: torch.Tensor) -> torch.Tensor:
-        """moe.py:128-176: returns a fresh 2-D `[T, H]` tensor; the input is not modified."""
+    def forward(self, hidden_states: torch.Tensor, shared_range: tuple[int, int] | None = None) -> torch.Tensor:
+        """moe.py:128-176: returns a fresh 2-D `[T, H]` tensor; the input is not modified.
+        `shared_range=(lo, hi)` restricts the shared expert to those tokens (expert-parallel dispatch)."""
         h = hidden_states.reshape(-1, hidden_states.shape[-1])
         if not h.is_contiguous():
             h = h.contiguous()
@@ -232,8 +234,13 @@ class Glm4MoeMoE(nn.Module):
             return out
         self._ensure_layer(T)
         with torch.cuda.device(h.device):
-            _lib.check(_lib.load().glm4moe_layer_forward(self._handle, h.data_ptr(), out.data_ptr(), T,
-                                                        _lib.stream_ptr(h.device)), "layer_forward")
+            if shared_range is None:
+                _lib.check(_lib.load().glm4moe_layer_forward(self._handle, h.data_ptr(), out.data_ptr(), T,
+                                                            _lib.stream_ptr(h.device)), "layer_forward")
+            else:
+                _lib.check(_lib.load().glm4moe_layer_forward_ex(self._handle, h.data_ptr(), out.data_ptr(), T,
+                                                               int(shared_range[0]), int(shared_range[1]),
+                                                               _lib.stream_ptr(h.device)), "layer_forward_ex")
         return out
 
     STAGES = ("router_logits", "router_select", "permute", "gather", "gate_up", "down", "combine", "total")
@@ -335,6 +342,14 @@ class Glm4MoeMoE(nn.Module):
             sl = list(range(self.expert_begin, self.expert_end)) + [self.config.n_routed_experts]
             self._w_gate_up.copy_(weights["w_gate_up"][sl])
             self._w_down.copy_(weights["w_down"][sl])
+            self.gate.weight.data.copy_(weights["gate_weight"])
+            self.gate.e_score_correction_bias.copy_(weights["bias"])
+
+    def load_local_stacks(self, weights: dict):
+        """Fill from stacks that already hold only this rank's experts + the shared expert."""
+        with torch.no_grad():
+            self._w_gate_up.copy_(weights["w_gate_up"])
+            self._w_down.copy_(weights["w_down"])
             self.gate.weight.data.copy_(weights["gate_weight"])
             self.gate.e_score_correction_bias.copy_(weights["bias"])
 

@@ -106,6 +106,26 @@ def make_weights(shape: MoeShape, dtype: torch.dtype, seed: int = WEIGHT_SEED,
     return {"w_gate_up": w_gu, "w_down": w_d, "gate_weight": gate_w, "bias": bias}
 
 
+def make_weights_device(shape: MoeShape, dtype: torch.dtype, device, experts=None, seed: int = WEIGHT_SEED):
+    """Same distributions as `make_weights`, drawn on the GPU with one generator seed per expert so
+    an expert-parallel rank can create just its shard (bench.py; values differ from `make_weights`).
+    Returns stacks over `experts` (default all) followed by the shared expert."""
+    H, E, I = shape.H, shape.E, shape.I
+    experts = list(range(E)) if experts is None else list(experts)
+    n = len(experts)
+    w_gu = torch.empty((n + 1, 2 * I, H), dtype=dtype, device=device)
+    w_d = torch.empty((n + 1, H, I), dtype=dtype, device=device)
+    gen = torch.Generator(device=device)
+    for slot, e in enumerate(experts + [E]):
+        gen.manual_seed(seed * 1000 + e)
+        w_gu[slot] = (torch.randn((2 * I, H), generator=gen, device=device, dtype=torch.float32) * WEIGHT_STD).to(dtype)
+        w_d[slot] = (torch.randn((H, I), generator=gen, device=device, dtype=torch.float32) * WEIGHT_STD).to(dtype)
+    gen.manual_seed(seed * 1000 + E + 1)
+    gate_w = (torch.randn((E, H), generator=gen, device=device, dtype=torch.float32) * WEIGHT_STD).to(dtype)
+    bias = torch.rand(E, generator=gen, device=device, dtype=torch.float32) * BIAS_HIGH
+    return {"w_gate_up": w_gu, "w_down": w_d, "gate_weight": gate_w, "bias": bias}
+
+
 def make_router_weights(shape: MoeShape, dtype: torch.dtype, seed: int = WEIGHT_SEED + 77):
     """Router-only shard (gate weight [E,H] + fp32 bias) for the big router shapes."""
     gen = torch.Generator(device="cpu").manual_seed(seed)

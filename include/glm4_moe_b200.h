@@ -46,7 +46,8 @@ typedef struct glm4moe_config {
   int32_t max_tokens;             /* largest T any forward will see (workspace sizing) */
   int32_t expert_begin;           /* expert-parallel: this rank owns experts [begin, end) */
   int32_t expert_end;             /*   (0, E) on a single GPU                              */
-  int32_t with_shared;            /* 1: add the shared expert (moe.py:165,171); 0: routed partial only */
+  int32_t with_shared;            /* 1: shared expert on all tokens (moe.py:165,171); 0: routed partial only;
+                                     2: shared expert on this rank's 1/R slice of the tokens (expert-parallel) */
   int32_t impl;                   /* GLM4MOE_IMPL_* (AUTO picks tcgen05 when the shape allows) */
 } glm4moe_config_t;
 
@@ -72,18 +73,19 @@ int glm4moe_router_select(const void* logits, const float* bias, int T, int E, i
  *   slot_row[T*k]        row of (t, slot), -1 if that expert is not local
  *   tiles[cap] int4      {expert - e_lo, row_start, nrows, 0} work list in `tile_rows` chunks
  *                        (index into the local weight stack), the shared expert's tiles last
- *                        (stack index e_hi - e_lo); *num_tiles = its length
+ *                        (stack index e_hi - e_lo, tokens [shared_lo, shared_hi)); *num_tiles = its length
  * scratch: int32[(ceil(T/256)+1) * E + 8].                                                     */
 int glm4moe_permute(const int32_t* idx, const float* w, int T, int k, int E, int e_lo, int e_hi,
-                    int tile_rows, int with_shared, int32_t* expert_offsets, int32_t* row_token,
+                    int tile_rows, int shared_lo, int shared_hi, int32_t* expert_offsets, int32_t* row_token,
                     float* row_weight, int32_t* slot_row, int32_t* tiles, int32_t tile_capacity,
                     int32_t* num_tiles, int32_t* scratch, void* stream);
 size_t glm4moe_permute_scratch_elems(int T, int E);
 int32_t glm4moe_tile_capacity(int T, int k, int E, int tile_rows);
 
-/* x_rows[r,:] = x[row_token[r],:] for routed rows, x_rows[T*k + t,:] = x[t,:]  (moe.py:147) */
+/* x_rows[r,:] = x[row_token[r],:] for routed rows, x_rows[T*k + t,:] = x[t,:] for t in
+ * [shared_lo, shared_hi)  (moe.py:147) */
 int glm4moe_gather_rows(const void* x, const int32_t* row_token, const int32_t* expert_offsets,
-                        void* x_rows, int T, int k, int E, int H, int with_shared, int dtype,
+                        void* x_rows, int T, int k, int E, int H, int shared_lo, int shared_hi, int dtype,
                         void* stream);
 
 /* ---- expert MLP: replaces Glm4MoeMLP.forward over every hit expert + the shared expert ------ */
@@ -98,9 +100,10 @@ int glm4moe_expert_down_simt(const void* act, const void* w_down, const int32_t*
                              int I, int T, int k, int tile_rows, int dtype, void* stream);
 
 /* ---- combine: replaces index_add_ + shared add (moe.py:151,171) ----------------------------- */
-/* out[t] = sum_{slot, ascending expert} y[slot_row[t,slot]] (+ y[T*k+t]); fp32 accumulate.     */
+/* out[t] = sum_{slot, ascending expert} y[slot_row[t,slot]] (+ y[T*k+t] for t in
+ * [shared_lo, shared_hi)); fp32 accumulate.                                                     */
 int glm4moe_combine(const void* y, const int32_t* slot_row, void* out, int T, int k, int H,
-                    int with_shared, int dtype, void* stream);
+                    int shared_lo, int shared_hi, int dtype, void* stream);
 
 /* ---- whole layer: replaces Glm4MoeMoE.forward (moe.py:128-176) ------------------------------ */
 size_t glm4moe_workspace_bytes(const glm4moe_config_t* cfg);
@@ -112,6 +115,10 @@ int glm4moe_layer_create(const glm4moe_config_t* cfg, const void* gate_w, const 
                          glm4moe_layer_t** out);
 int glm4moe_layer_destroy(glm4moe_layer_t* layer);
 int glm4moe_layer_forward(glm4moe_layer_t* layer, const void* x, void* out, int T, void* stream);
+/* As glm4moe_layer_forward, with the shared expert applied to tokens [shared_lo, shared_hi) only
+ * (expert-parallel dispatch: the owner's own tokens come first in the batch).                  */
+int glm4moe_layer_forward_ex(glm4moe_layer_t* layer, const void* x, void* out, int T, int shared_lo,
+                             int shared_hi, void* stream);
 /* Same launches, with a CUDA event recorded on `stream` before every stage; after the last event
  * completes, stage_ms[0..6] = {router_logits, router_select, permute, gather, gate_up, down,
  * combine} durations and stage_ms[7] = the whole sequence (bench.py's per-kernel roofline).     */

@@ -1,0 +1,98 @@
+"""CPU, gloo, world_size 2: the expert-parallel bookkeeping of distributed.py (partition, dispatch
+plan, all-to-all-v row order, shared-expert placement, all-reduce / all-gather) with the per-rank
+compute replaced by an oracle-backed stand-in (the CUDA library needs a GPU)."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from glm4_moe_b200 import synth
+from glm4_moe_b200.distributed import ExpertParallelMoE, dispatch_plan, expert_range, token_slice
+from oracle import moe_oracle as O
+
+SHAPE = synth.MoeShape(64, 8, 2, 32, 2.5, "ep-test")
+
+
+class OracleLocal(torch.nn.Module):
+    """What `Glm4MoeMoE(ep_rank, ep_size)` computes on one rank, restated with the oracle."""
+
+    def __init__(self, weights, shape, rank, world):
+        super().__init__()
+        self.w, self.shape, self.rank, self.world = weights, shape, rank, world
+        self.lo, self.hi = expert_range(shape.E, rank, world)
+
+    def gate(self, h):
+        idx, w = O.router(h, self.w["gate_weight"], self.w["bias"], self.shape.k,
+                          self.shape.routed_scaling_factor, tie_rule="lowest_index")
+        return O.canonical_routing(idx, w)
+
+    def forward(self, h, shared_range=None):
+        T = h.shape[0]
+        idx, w = self.gate(h)
+        out = torch.zeros_like(h)
+        for e in range(self.lo, self.hi):
+            tok, pos = torch.where(idx == e)
+            if tok.numel():
+                out.index_add_(0, tok, O.expert_mlp(h[tok], self.w["w_gate_up"][e], self.w["w_down"][e])
+                               * w[tok, pos].unsqueeze(-1))
+        s_lo, s_hi = shared_range if shared_range is not None else token_slice(T, self.rank, self.world)
+        E = self.shape.E
+        out[s_lo:s_hi] += O.expert_mlp(h[s_lo:s_hi], self.w["w_gate_up"][E], self.w["w_down"][E])
+        return out
+
+
+def _worker(rank, world, port, layout, T, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        torch.set_num_threads(2)
+        wts = synth.make_weights(SHAPE, torch.float32)
+        x = synth.make_tokens(SHAPE, T, torch.float32, 3)
+        ep = ExpertParallelMoE(OracleLocal(wts, SHAPE, rank, world), SHAPE.E, layout=layout)
+        y = ep(x)
+        ref = O.moe_forward(x, wts, SHAPE.k, SHAPE.routed_scaling_factor, tie_rule="lowest_index")["out"]
+        err = float((y - ref).abs().max())
+        q.put((rank, err, tuple(y.shape)))
+    finally:
+        dist.destroy_process_group()
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+@pytest.mark.parametrize("layout,T", [("allreduce", 37), ("alltoall", 37), ("alltoall", 1), ("allreduce", 2)])
+def test_expert_parallel_layouts_match_single_rank(layout, T):
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, layout, T, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, err, shape in res:
+        assert shape == (T, SHAPE.H)
+        assert err < 1e-5, (layout, rank, err)
+
+
+def test_partition_helpers():
+    assert expert_range(128, 3, 8) == (48, 64)
+    with pytest.raises(ValueError):
+        expert_range(10, 0, 4)
+    assert [token_slice(10, r, 4) for r in range(4)] == [(0, 3), (3, 6), (6, 9), (9, 10)]
+    assert token_slice(1, 1, 2) == (1, 1)
+    idx = torch.tensor([[0, 5], [6, 7], [2, 3]])
+    mask, counts = dispatch_plan(idx, 8, 2)
+    assert mask.tolist() == [[True, True], [False, True], [True, False]] and counts.tolist() == [2, 2]

@@ -1,0 +1,73 @@
+"""GPU (>= 2 devices): expert-parallel layouts over NCCL against the single-GPU block and the fp32
+truth.  Skipped on a 1-GPU box; run with `gpurun --gpus 2 -- python -m pytest tests/test_gpu_ep.py -m gpu`."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+pytestmark = pytest.mark.gpu
+
+
+def _worker(rank, world, port, q):
+    import glm4_moe_b200
+    from glm4_moe_b200 import synth
+    from glm4_moe_b200.distributed import ExpertParallelMoE
+    from oracle import moe_oracle as O
+    from test_gpu_parity import _cfg, _module
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        shape, dt = synth.MINI, torch.bfloat16
+        wts = synth.make_weights(shape, dt)
+        res = {}
+        for T in (1, 40, 300):
+            x = synth.make_tokens(shape, T, dt, T)
+            single = _module(shape, dt, wts)
+            with torch.inference_mode():
+                y1 = single(x.cuda())
+                idx = single.workspace_view("idx", T).cpu().long()
+                w = single.workspace_view("w", T).cpu().to(dt)
+                truth = O.moe_forward_fp32(x, wts, shape.k, shape.routed_scaling_factor, routing=(idx, w))["out"]
+            for layout in ("allreduce", "alltoall"):
+                local = _module(shape, dt, wts, ep_rank=rank, ep_size=world)
+                ep = ExpertParallelMoE(local, shape.E, layout=layout)
+                with torch.inference_mode():
+                    y = ep(x.cuda())
+                torch.cuda.synchronize()
+                got = y.float().cpu()
+                rms = truth.pow(2).mean().sqrt()
+                bad = int(((got - truth).abs() > 2e-2 * truth.abs() + 2e-2 * rms).sum())
+                rel = float((got - truth).norm() / truth.norm())
+                d1 = float((got - y1.float().cpu()).abs().max() / y1.float().abs().max())
+                res[(T, layout)] = (bad, rel, d1)
+        q.put((rank, res))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_expert_parallel_two_gpus():
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    world = 2
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    out = [q.get(timeout=600) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    for rank, res in out:
+        for key, (bad, rel, d1) in res.items():
+            assert bad == 0 and rel < 8e-3, (rank, key, bad, rel)
+            assert d1 < 3e-2, (rank, key, d1)

@@ -173,7 +173,7 @@ def test_permutation_bit_exact(T, E, k):
     d_tiles = torch.zeros((cap, 4), dtype=torch.int32, device=dev)
     d_nt = torch.zeros(4, dtype=torch.int32, device=dev)
     d_scr = torch.empty(lib.glm4moe_permute_scratch_elems(T, E), dtype=torch.int32, device=dev)
-    _lib.check(lib.glm4moe_permute(d_idx.data_ptr(), d_w.data_ptr(), T, k, E, 0, E, tr, 1, d_off.data_ptr(),
+    _lib.check(lib.glm4moe_permute(d_idx.data_ptr(), d_w.data_ptr(), T, k, E, 0, E, tr, 0, T, d_off.data_ptr(),
                                    d_rt.data_ptr(), d_rw.data_ptr(), d_sr.data_ptr(), d_tiles.data_ptr(), cap,
                                    d_nt.data_ptr(), d_scr.data_ptr(), _lib.stream_ptr()))
     torch.cuda.synchronize()
@@ -197,7 +197,7 @@ def test_permutation_bit_exact(T, E, k):
             assert r0 >= T * k
     assert bool((covered == 1).all())
     # expert-parallel filter: only experts [E/2, E) keep rows, order still stable
-    _lib.check(lib.glm4moe_permute(d_idx.data_ptr(), d_w.data_ptr(), T, k, E, E // 2, E, tr, 0, d_off.data_ptr(),
+    _lib.check(lib.glm4moe_permute(d_idx.data_ptr(), d_w.data_ptr(), T, k, E, E // 2, E, tr, 0, 0, d_off.data_ptr(),
                                    d_rt.data_ptr(), d_rw.data_ptr(), d_sr.data_ptr(), d_tiles.data_ptr(), cap,
                                    d_nt.data_ptr(), d_scr.data_ptr(), _lib.stream_ptr()))
     torch.cuda.synchronize()
