@@ -24,7 +24,7 @@ inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct WsLayout {
   size_t logits, idx, w, offsets, row_token, row_weight, slot_row, num_tiles, sched, tiles, scratch, x_rows,
-      act, y, total;
+      act, y, xq, sx, actq, sact, total;
   int tile_capacity;
 };
 
@@ -55,6 +55,13 @@ WsLayout make_layout(const glm4moe_config_t& c) {
   L.x_rows = take(R * H * es);
   L.act = take(R * I * es);
   L.y = take(R * H * es);
+  L.xq = L.sx = L.actq = L.sact = 0;
+  if (c.weight_format == GLM4MOE_W_FP8_BLOCK128) {
+    L.xq = take(R * H);                 // e4m3 activation rows
+    L.sx = take((H / 128) * R * 4);     // their per-128 scales, k-block major [H/128, R]
+    L.actq = take(R * I);
+    L.sact = take(((I + 127) / 128) * R * 4);
+  }
   L.total = off;
   return L;
 }
@@ -69,6 +76,8 @@ struct glm4moe_layer {
   const float* bias;
   const void* w_gate_up;
   const void* w_down;
+  const float* s_gate_up;
+  const float* s_down;
   int sm_count;
   bool umma_ok;
   int last_launches;
@@ -115,7 +124,13 @@ static int check_cfg(const glm4moe_config_t* c) {
   if (c->dtype != GLM4MOE_F32 && c->dtype != GLM4MOE_F16 && c->dtype != GLM4MOE_BF16) return GLM4MOE_ERR_ARG;
   if (c->expert_begin < 0 || c->expert_end > c->n_routed_experts || c->expert_begin > c->expert_end)
     return GLM4MOE_ERR_ARG;
-  if (c->weight_format != GLM4MOE_W_NATIVE) return GLM4MOE_ERR_UNSUPPORTED;
+  if (c->weight_format == GLM4MOE_W_FP8_BLOCK128) {
+    // e4m3 weights with 128x128 fp32 block scales run only on the tensor-core path
+    if (c->dtype == GLM4MOE_F32 || c->hidden_size % 128 != 0 || c->moe_intermediate_size % 128 != 0)
+      return GLM4MOE_ERR_UNSUPPORTED;
+  } else if (c->weight_format != GLM4MOE_W_NATIVE) {
+    return GLM4MOE_ERR_UNSUPPORTED;
+  }
   return GLM4MOE_OK;
 }
 
@@ -128,8 +143,6 @@ extern "C" int glm4moe_layer_create(const glm4moe_config_t* cfg, const void* gat
                                     const void* w_gate_up, const void* w_down, const float* s_gate_up,
                                     const float* s_down, void* workspace, size_t workspace_bytes,
                                     glm4moe_layer_t** out) {
-  (void)s_gate_up;
-  (void)s_down;
   int rc = check_cfg(cfg);
   if (rc != GLM4MOE_OK) return rc;
   if (!gate_w || !bias || !w_gate_up || !w_down || !workspace || !out) return GLM4MOE_ERR_ARG;
@@ -145,6 +158,8 @@ extern "C" int glm4moe_layer_create(const glm4moe_config_t* cfg, const void* gat
   l->bias = bias;
   l->w_gate_up = w_gate_up;
   l->w_down = w_down;
+  l->s_gate_up = s_gate_up;
+  l->s_down = s_down;
   l->last_launches = 0;
   l->last_impl = GLM4MOE_IMPL_AUTO;
   l->events_ready = false;
@@ -158,7 +173,29 @@ extern "C" int glm4moe_layer_create(const glm4moe_config_t* cfg, const void* gat
     cudaDeviceGetAttribute(&l->sm_count, cudaDevAttrMultiProcessorCount, dev);
   const int H = cfg->hidden_size, I = cfg->moe_intermediate_size;
   l->umma_ok = false;
-  if (cfg->impl != GLM4MOE_IMPL_SIMT && umma_shape_ok(H, I, cfg->dtype)) {
+  const bool fp8 = cfg->weight_format == GLM4MOE_W_FP8_BLOCK128;
+  if (fp8) {
+    if (!s_gate_up || !s_down || cfg->impl == GLM4MOE_IMPL_SIMT) {
+      delete l;
+      return GLM4MOE_ERR_ARG;
+    }
+    const uint64_t n_stack = static_cast<uint64_t>(cfg->expert_end - cfg->expert_begin) + 1;
+    const uint64_t R = static_cast<uint64_t>(cfg->max_tokens) * (cfg->num_experts_per_tok + 1);
+    rc = umma_make_tensor_map_u8(&l->tm_w_gu, w_gate_up, n_stack * 2 * I, H, 128);
+    if (rc == GLM4MOE_OK) rc = umma_make_tensor_map_u8(&l->tm_w_d, w_down, n_stack * H, I, 128);
+    for (int i = 0; i < 3 && rc == GLM4MOE_OK; ++i) {
+      rc = umma_make_tensor_map_u8(&l->tm_x[i], l->ws + L.xq, R, H, kBnChoices[i]);
+      if (rc == GLM4MOE_OK) rc = umma_make_tensor_map_u8(&l->tm_act[i], l->ws + L.actq, R, I, kBnChoices[i]);
+    }
+    // the router stays in the model dtype
+    if (rc == GLM4MOE_OK && H % 64 == 0)
+      rc = umma_make_tensor_map(&l->tm_gate, gate_w, cfg->dtype, cfg->n_routed_experts, H, 128);
+    if (rc != GLM4MOE_OK) {
+      delete l;
+      return rc;
+    }
+    l->umma_ok = true;
+  } else if (cfg->impl != GLM4MOE_IMPL_SIMT && umma_shape_ok(H, I, cfg->dtype)) {
     const uint64_t n_stack = static_cast<uint64_t>(cfg->expert_end - cfg->expert_begin) + 1;
     const uint64_t R = static_cast<uint64_t>(cfg->max_tokens) * (cfg->num_experts_per_tok + 1);
     rc = umma_make_tensor_map(&l->tm_w_gu, w_gate_up, cfg->dtype, n_stack * 2 * I, H, 128);
@@ -257,7 +294,8 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
     sh_hi = sh_hi_arg;
   }
   const bool use_umma = l->umma_ok;
-  const int bi = pick_bn_index(c, T);
+  const bool fp8 = c.weight_format == GLM4MOE_W_FP8_BLOCK128;
+  const int bi = fp8 ? (pick_bn_index(c, T) < 2 ? pick_bn_index(c, T) : 2) : pick_bn_index(c, T);
   const int tile_rows = use_umma ? kBnChoices[bi] : kSimtRows;
   int launches = 0;
   int rc;
@@ -296,11 +334,60 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
                             row_token, row_weight, slot_row, tiles, L.tile_capacity, num_tiles, scratch, stream)))
     return rc;
   STAGE_MARK(3);
-  if ((rc = glm4moe_gather_rows(x, row_token, offsets, x_rows, T, k, E, H, sh_lo, sh_hi, c.dtype, stream)))
+  const int R_cap = c.max_tokens * (k + 1);
+  if (fp8) {
+    // gather fused with the per-token 1x128 activation quantiser
+    if ((rc = quant_rows_fp8(x, H, row_token, offsets, E, T, k, H, sh_lo, sh_hi, ws + L.xq,
+                             reinterpret_cast<float*>(ws + L.sx), R_cap, c.dtype, stream)))
+      return rc;
+  } else if ((rc = glm4moe_gather_rows(x, row_token, offsets, x_rows, T, k, E, H, sh_lo, sh_hi, c.dtype, stream))) {
     return rc;
-  launches += T <= 256 ? 4 : 6;
+  }
   STAGE_MARK(4);
-  if (use_umma) {
+  if (fp8) {
+    UmmaFp8Launch a{};
+    a.tiles = tiles;
+    a.num_tiles = num_tiles;
+    a.tile_rows = tile_rows;
+    a.dtype = c.dtype;
+    a.grid = l->sm_count;
+    a.row_weight = row_weight;
+    a.n_routed_rows = T * k;
+    a.x_scale_ld = R_cap;
+    // gate_up + SiLU*mul
+    a.tm_w = &l->tm_w_gu;
+    a.tm_x = &l->tm_x[bi];
+    a.w_scale = l->s_gate_up;
+    a.x_scale_t = reinterpret_cast<const float*>(ws + L.sx);
+    a.out = act;
+    a.ld_out = I;
+    a.n_feat_tiles = I / 128;
+    a.n_kblocks = H / 128;
+    a.w_rows_per_expert = 2 * I;
+    a.up_row_offset = I;
+    a.gated = 1;
+    a.sched = reinterpret_cast<int32_t*>(ws + L.sched);
+    if ((rc = umma_fp8_launch(a, stream))) return rc;
+    STAGE_MARK(5);
+    // re-quantise the activation rows for the down projection
+    if ((rc = quant_rows_fp8(act, I, nullptr, offsets, E, T, k, I, sh_lo, sh_hi, ws + L.actq,
+                             reinterpret_cast<float*>(ws + L.sact), R_cap, c.dtype, stream)))
+      return rc;
+    a.tm_w = &l->tm_w_d;
+    a.tm_x = &l->tm_act[bi];
+    a.w_scale = l->s_down;
+    a.x_scale_t = reinterpret_cast<const float*>(ws + L.sact);
+    a.out = y;
+    a.ld_out = H;
+    a.n_feat_tiles = H / 128;
+    a.n_kblocks = I / 128;
+    a.w_rows_per_expert = H;
+    a.up_row_offset = 0;
+    a.gated = 0;
+    a.sched = reinterpret_cast<int32_t*>(ws + L.sched) + 2;
+    if ((rc = umma_fp8_launch(a, stream))) return rc;
+    launches += 1;
+  } else if (use_umma) {
     UmmaLaunch a{};
     a.tiles = tiles;
     a.num_tiles = num_tiles;
@@ -353,6 +440,7 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
   launches += 1;
   l->last_launches = launches;
   l->last_impl = use_umma ? GLM4MOE_IMPL_UMMA : GLM4MOE_IMPL_SIMT;
+  (void)fp8;
   return GLM4MOE_OK;
 }
 

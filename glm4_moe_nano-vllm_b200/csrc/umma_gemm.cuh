@@ -32,4 +32,34 @@ int umma_make_tensor_map(void* map_out, const void* base, int dtype, uint64_t ro
 int umma_launch(const UmmaLaunch& args, void* stream);
 bool umma_shape_ok(int H, int I, int dtype);
 
+// ---- FP8 block-scaled tier (umma_fp8.cu) ----
+struct UmmaFp8Launch {
+  const void* tm_w;          // CUtensorMap over the e4m3 weight stack (uint8), box {128 bytes, 128 rows}
+  const void* tm_x;          // CUtensorMap over the e4m3 activation rows, box {128 bytes, tile_rows}
+  const float* w_scale;      // [n_stack, w_rows_per_expert/128, K/128]
+  const float* x_scale_t;    // [K/128, x_scale_ld]
+  int x_scale_ld;
+  const int32_t* tiles;
+  const int32_t* num_tiles;
+  void* out;
+  int ld_out;
+  const float* row_weight;
+  int n_routed_rows;
+  int n_feat_tiles;
+  int n_kblocks;             // K / 128
+  int w_rows_per_expert;
+  int up_row_offset;
+  int tile_rows;             // 16 / 32 / 64
+  int gated;
+  int dtype;                 // output / activation model dtype
+  int grid;
+  int32_t* sched;
+};
+int umma_make_tensor_map_u8(void* map_out, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows);
+int umma_fp8_launch(const UmmaFp8Launch& args, void* stream);
+// rows -> e4m3 + per-128 fp32 scales (scale_t is k-block major); row_token != nullptr gathers tokens
+int quant_rows_fp8(const void* src, int src_ld, const int32_t* row_token, const int32_t* expert_offsets, int E,
+                   int T, int k, int K, int sh_lo, int sh_hi, void* dst, float* scale_t, int scale_ld, int dtype,
+                   void* stream);
+
 }  // namespace glm4moe

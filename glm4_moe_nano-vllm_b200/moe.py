@@ -149,6 +149,8 @@ class Glm4MoeMoE(nn.Module):
             [Glm4MoeMLP(self._w_gate_up[i], self._w_down[i], config.hidden_act) for i in range(n_local)])
         self.gate = GlmMoeSelectTopk(config)
         self.shared_experts = Glm4MoeMLP(self._w_gate_up[n_local], self._w_down[n_local], config.hidden_act)
+        self.weight_format = "native"
+        self._wq_gate_up = self._wq_down = self._s_gate_up = self._s_down = None
         self._max_tokens = int(max_tokens)
         self._handle = None
         self._workspace = None
@@ -163,6 +165,10 @@ class Glm4MoeMoE(nn.Module):
         self._destroy_handle()
         self._w_gate_up = fn(self._w_gate_up)
         self._w_down = fn(self._w_down)
+        if self._wq_gate_up is not None:      # fp8 stacks follow device moves only (never re-cast)
+            dev = self._w_gate_up.device
+            self._wq_gate_up, self._wq_down = self._wq_gate_up.to(dev), self._wq_down.to(dev)
+            self._s_gate_up, self._s_down = self._s_gate_up.to(dev), self._s_down.to(dev)
         out = super()._apply(fn, recurse)
         for i, mlp in enumerate(self._mlps()):
             mlp.gate_up_proj.weight.data = self._w_gate_up[i]
@@ -184,8 +190,9 @@ class Glm4MoeMoE(nn.Module):
 
     def _lib_config(self, max_tokens: int) -> _lib.Config:
         c = self.config
+        fmt = _lib.W_FP8_BLOCK128 if self.weight_format == "fp8" else _lib.W_NATIVE
         return _lib.Config(c.hidden_size, c.n_routed_experts, c.num_experts_per_tok, c.moe_intermediate_size,
-                           float(c.routed_scaling_factor), _lib.DTYPE_CODE[self._w_gate_up.dtype], _lib.W_NATIVE,
+                           float(c.routed_scaling_factor), _lib.DTYPE_CODE[self.gate.weight.dtype], fmt,
                            max_tokens, self.expert_begin, self.expert_end, int(self.with_shared),
                            _IMPL[self.impl])
 
@@ -193,7 +200,7 @@ class Glm4MoeMoE(nn.Module):
         if self._handle is not None and T <= self._max_tokens:
             return
         lib = _lib.load()
-        _lib.require_cuda(self._w_gate_up, "expert weights")
+        _lib.require_cuda(self.gate.weight, "weights")
         if torch.cuda.is_current_stream_capturing():
             raise _lib.Glm4MoeLibraryError(
                 f"workspace for {T} tokens must exist before CUDA-graph capture (run a warm-up forward first)")
@@ -206,17 +213,44 @@ class Glm4MoeMoE(nn.Module):
         nbytes = lib.glm4moe_workspace_bytes(C.byref(cfg))
         if nbytes == 0:
             raise _lib.Glm4MoeLibraryError("unsupported GLM4-MoE configuration for the CUDA library")
-        dev = self._w_gate_up.device
+        dev = self.gate.weight.device
         self._workspace = torch.empty(nbytes + 1024, dtype=torch.uint8, device=dev)
         base = (self._workspace.data_ptr() + 1023) // 1024 * 1024
         handle = C.c_void_p()
+        if self.weight_format == "fp8":
+            wgu, wd = self._wq_gate_up.data_ptr(), self._wq_down.data_ptr()
+            sgu, sd = self._s_gate_up.data_ptr(), self._s_down.data_ptr()
+        else:
+            wgu, wd, sgu, sd = self._w_gate_up.data_ptr(), self._w_down.data_ptr(), None, None
         with torch.cuda.device(dev):
             _lib.check(lib.glm4moe_layer_create(C.byref(cfg), self.gate.weight.data_ptr(),
-                                                self.gate.e_score_correction_bias.data_ptr(),
-                                                self._w_gate_up.data_ptr(), self._w_down.data_ptr(), None, None,
+                                                self.gate.e_score_correction_bias.data_ptr(), wgu, wd, sgu, sd,
                                                 base, nbytes, C.byref(handle)), "layer_create")
         self._handle = handle
         self._cfg = cfg
+
+    def quantize_fp8(self, drop_native: bool = False):
+        """Convert the expert stacks to e4m3 + 128x128 fp32 block scales (fp8.py) and switch the
+        block to the FP8 tensor-core path.  Router weights and activations keep the model dtype."""
+        from . import fp8
+        self._destroy_handle()
+        self._wq_gate_up, self._s_gate_up = fp8.quantize_block128(self._w_gate_up)
+        self._wq_down, self._s_down = fp8.quantize_block128(self._w_down)
+        self.weight_format = "fp8"
+        if drop_native:
+            dev, dt = self._w_gate_up.device, self._w_gate_up.dtype
+            self._w_gate_up = torch.empty((0,), device=dev, dtype=dt)
+            self._w_down = torch.empty((0,), device=dev, dtype=dt)
+            for mlp in self._mlps():
+                mlp.gate_up_proj.weight.data = self._w_gate_up
+                mlp.down_proj.weight.data = self._w_down
+        return self
+
+    def dequantized_weights(self) -> dict:
+        """fp32 stacks the FP8 path is equivalent to (oracle input for the quant-tier parity test)."""
+        from . import fp8
+        return {"w_gate_up": fp8.dequantize_block128(self._wq_gate_up, self._s_gate_up),
+                "w_down": fp8.dequantize_block128(self._wq_down, self._s_down)}
 
     # ---- reference API ----------------------------------------------------------------------
     def forward(self, hidden_states: torch.Tensor, shared_range: tuple[int, int] | None = None) -> torch.Tensor:
@@ -226,8 +260,8 @@ class Glm4MoeMoE(nn.Module):
         if not h.is_contiguous():
             h = h.contiguous()
         _lib.require_cuda(h, "hidden_states")
-        if h.dtype != self._w_gate_up.dtype:
-            raise _lib.Glm4MoeLibraryError(f"hidden_states dtype {h.dtype} != weight dtype {self._w_gate_up.dtype}")
+        if h.dtype != self.gate.weight.dtype:
+            raise _lib.Glm4MoeLibraryError(f"hidden_states dtype {h.dtype} != model dtype {self.gate.weight.dtype}")
         T = h.shape[0]
         out = torch.empty_like(h)
         if T == 0:
@@ -265,7 +299,7 @@ class Glm4MoeMoE(nn.Module):
             raise _lib.Glm4MoeLibraryError("forward_host expects a contiguous host tensor")
         T, H = h.shape
         self._ensure_layer(T)
-        dev = self._w_gate_up.device
+        dev = self.gate.weight.device
         if self._host is None or self._host[0].shape[0] < T:
             self._host = (torch.empty((self._max_tokens, H), dtype=h.dtype, device=dev),
                           torch.empty((self._max_tokens, H), dtype=h.dtype, device=dev))
@@ -363,7 +397,7 @@ class Glm4MoeMoE(nn.Module):
         raw = self._workspace[(base - self._workspace.data_ptr()) + off:][:n.value]
         c = self.config
         k, E, H, I = c.num_experts_per_tok, c.n_routed_experts, c.hidden_size, c.moe_intermediate_size
-        md = self._w_gate_up.dtype
+        md = self.gate.weight.dtype
         if name in ("idx", "row_token", "slot_row", "expert_offsets", "num_tiles", "tiles"):
             t = raw.view(torch.int32)
             if name in ("idx", "slot_row"):

@@ -5,7 +5,8 @@ import torch
 import glm4_moe_b200
 from glm4_moe_b200 import synth
 from bench import _hf_config
-Ts = [int(a) for a in sys.argv[1:]] or [1, 4, 32, 256, 4096]
+FP8 = "--fp8" in sys.argv
+Ts = [int(a) for a in sys.argv[1:] if not a.startswith("--")] or [1, 4, 32, 256, 4096]
 shape, dt = synth.AIR, torch.bfloat16
 torch.manual_seed(0)
 torch.set_default_dtype(dt)
@@ -15,6 +16,8 @@ moe = moe.cuda()
 with torch.no_grad():
     moe._w_gate_up.normal_(0, 0.02); moe._w_down.normal_(0, 0.02); moe.gate.weight.normal_(0, 0.02)
     moe.gate.e_score_correction_bias.uniform_(0, 0.1)
+if FP8:
+    moe.quantize_fp8(drop_native=True)
 for T in Ts:
     xs = [torch.randn(T, shape.H, device="cuda", dtype=dt) for _ in range(8)]
     for i in range(5):
@@ -42,5 +45,5 @@ for T in Ts:
     for i in range(4):
         g.replay()
     g1.record(); torch.cuda.synchronize()
-    print(json.dumps({"T": T, "eager_ms": s0.elapsed_time(s1) / n, "graph_ms": g0.elapsed_time(g1) / 32,
+    print(json.dumps({"fp8": FP8, "T": T, "eager_ms": s0.elapsed_time(s1) / n, "graph_ms": g0.elapsed_time(g1) / 32,
                       "stages_us": {k: round(v * 1e3, 1) for k, v in acc.items()}}))

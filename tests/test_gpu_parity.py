@@ -372,3 +372,67 @@ def test_air_prefill_properties(air):
         a, b = ys.float().cpu()[same], y[sub].float().cpu()[same]
         assert float((a - b).abs().max()) <= 2e-2 * float(b.abs().max())
         assert float(((a - b).norm() / b.norm())) < 2e-3
+
+
+# ------------------------------------------------------------------------------------------
+# BASELINE configs[2]: FP8 e4m3 weights with 128x128 block scales, per-token 1x128 activations
+# ------------------------------------------------------------------------------------------
+RTOL_FP8 = 5e-2      # north_star: FP8 outputs vs the fp32 reference (on the dequantised weights)
+
+
+def _fp8_case(shape, dt, T, batch, max_tokens=256):
+    wts = synth.make_weights(shape, dt)
+    moe = _module(shape, dt, wts, max_tokens=max_tokens)
+    moe.quantize_fp8()
+    x = synth.make_tokens(shape, T, dt, batch)
+    with torch.inference_mode():
+        out = moe(x.cuda())
+        torch.cuda.synchronize()
+        idx = moe.workspace_view("idx", T).cpu().long()
+        w = moe.workspace_view("w", T).cpu().to(dt)
+        deq = moe.dequantized_weights()
+        ref_w = {"w_gate_up": deq["w_gate_up"].cpu(), "w_down": deq["w_down"].cpu(),
+                 "gate_weight": wts["gate_weight"], "bias": wts["bias"]}
+        truth = O.moe_forward(x.float(), ref_w, shape.k, shape.routed_scaling_factor,
+                              routing=(idx, w.float()))["out"]
+        # routing is untouched by the quant tier (router stays in the model dtype)
+        oi, _ = O.canonical_routing(*O.router(x, wts["gate_weight"], wts["bias"], shape.k,
+                                              shape.routed_scaling_factor))
+    return out, truth, idx, oi
+
+
+@pytest.mark.parametrize("T", [1, 40, 200])
+def test_fp8_block_scaled_mini(T):
+    out, truth, idx, oi = _fp8_case(synth.MINI, torch.bfloat16, T, T)
+    assert torch.equal(idx, oi)
+    nbad, rel = _close(out, truth, RTOL_FP8)
+    assert nbad == 0 and rel < 3e-2, (nbad, rel)
+
+
+def test_fp8_quantiser_matches_reference_formula():
+    """Weight blocks and the dequantised stacks follow q*scale with scale = amax/448."""
+    from glm4_moe_b200 import fp8
+    w = torch.randn(3, 256, 384) * 0.02
+    q, s = fp8.quantize_block128(w)
+    assert q.dtype == torch.float8_e4m3fn and s.shape == (3, 2, 3)
+    d = fp8.dequantize_block128(q, s)
+    assert float((d - w).abs().max()) <= float(w.abs().max()) * 2 ** -4
+    assert torch.allclose(s[1, 0, 2], w[1, :128, 256:].abs().max() / 448)
+
+
+def test_fp8_air_decode(air):
+    shape, dt, wts, _ = air
+    moe = _module(shape, dt, wts, max_tokens=64)
+    moe.quantize_fp8(drop_native=True)
+    for T in (1, 32):
+        x = synth.make_tokens(shape, T, dt, 300 + T)
+        with torch.inference_mode():
+            out = moe(x.cuda())
+            torch.cuda.synchronize()
+            idx = moe.workspace_view("idx", T).cpu().long()
+            w = moe.workspace_view("w", T).cpu().float()
+            deq = moe.dequantized_weights()
+            ref_w = {"w_gate_up": deq["w_gate_up"].cpu(), "w_down": deq["w_down"].cpu()}
+            truth = O.moe_forward(x.float(), ref_w, shape.k, 1.0, routing=(idx, w))["out"]
+        nbad, rel = _close(out, truth, RTOL_FP8)
+        assert nbad == 0 and rel < 3e-2, (T, nbad, rel)
