@@ -175,5 +175,23 @@ __device__ __forceinline__ TileRef get_tile(const int4* __restrict__ tiles, int 
   return {0, r0, min(BN, dense_rows - r0)};
 }
 
+// ---- stream-K bookkeeping (umma_gemm.cu, umma_fp8.cu) ----
+struct Seg { int w, k0, k1; };   // k-blocks [k0, k1) of work item w
+
+// first unit of CTA c when `units` k-blocks are cut into `grid` ranges (grid <= units)
+__device__ __forceinline__ long long sk_range_start(int c, long long units, int grid) {
+  return static_cast<long long>(c) * units / grid;
+}
+// the CTA whose range holds unit u: the largest c with sk_range_start(c) <= u
+__device__ __forceinline__ int sk_owner(long long u, long long units, int grid) {
+  int c = static_cast<int>(((u + 1) * grid - 1) / units);
+  if (c > grid - 1) c = grid - 1;
+  while (c + 1 < grid && sk_range_start(c + 1, units, grid) <= u) ++c;
+  while (c > 0 && sk_range_start(c, units, grid) > u) --c;
+  return c;
+}
+__device__ __forceinline__ void epi_bar_sync(int nthreads) {
+  asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory");
+}
 
 }  // namespace glm4moe

@@ -201,6 +201,9 @@ __global__ void __launch_bounds__(Fp8Cfg<BN, GATED>::kThreads, 1) umma_fp8_kerne
     const uint32_t lane_base = static_cast<uint32_t>(ew * 32) << 16;
     const int kb_total = n_kblocks;
     uint32_t pcount = 0;
+    // the activation scales are written by the direct predecessor (the quantiser): unlike the
+    // bf16 epilogue, these warps read predecessor data themselves and must pass the dependency wait
+    pdl_wait();
     for (int it = 0;; ++it) {
       const int w = next_work(it);
       if (w < 0) break;

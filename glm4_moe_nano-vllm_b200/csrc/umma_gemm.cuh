@@ -24,6 +24,8 @@ struct UmmaLaunch {
   int dtype;
   int grid;
   int32_t* sched;          // 2 zero-initialised ints owned by this launch site (self re-arming)
+  float* sk_part;          // stream-K (tile_rows <= 32 only): fp32 partial tiles, grid*2*accs*tile_rows*128 floats
+  int32_t* sk_cnt;         // stream-K: zero-initialised counter per work item (self re-arming); nullptr = off
 };
 
 // 2-D row-major [rows, cols] two-byte tensor, box {64 cols, box_rows}, 128B swizzle.

@@ -127,5 +127,47 @@ def moe_forward_fp32(h: torch.Tensor, weights: dict, k: int, scale: float, routi
     return moe_forward(h, weights, k, scale, routing=routing, compute_dtype=torch.float32)
 
 
+# --------------------------------------------------------------------------------------
+# quant tier (BASELINE.json configs[2]).  The reference has no FP8 path; this restates the
+# published DeepSeek-V3-style block format the tier implements on top of the reference's
+# structure (mlp.py:49-54): weights e4m3 with one fp32 scale per 128x128 block (dequantised by
+# the caller), activations e4m3 with one fp32 scale per token per 128 columns, scale = amax/448,
+# products exact, fp32 accumulation; the SiLU*mul intermediate is rounded to the model dtype
+# (it is stored in it) before it is re-quantised for the down projection.
+# --------------------------------------------------------------------------------------
+def fp8_act_roundtrip(a: torch.Tensor) -> torch.Tensor:
+    """a [n, K] -> fp32 values of its per-token 1x128 e4m3 quantisation."""
+    n, K = a.shape
+    g = a.float().reshape(n, K // 128, 128)
+    scale = g.abs().amax(-1, keepdim=True).clamp_min(1e-10) / 448.0
+    q = (g / scale).clamp(-448.0, 448.0).to(torch.float8_e4m3fn).float()
+    return (q * scale).reshape(n, K)
+
+
+def expert_mlp_fp8(x: torch.Tensor, w_gate_up_deq: torch.Tensor, w_down_deq: torch.Tensor,
+                   model_dtype: torch.dtype) -> torch.Tensor:
+    gate_up = F.linear(fp8_act_roundtrip(x), w_gate_up_deq.float())
+    g, u = gate_up.chunk(2, -1)
+    act = (F.silu(g) * u).to(model_dtype)
+    return F.linear(fp8_act_roundtrip(act), w_down_deq.float())
+
+
+def moe_forward_fp8(h: torch.Tensor, deq_weights: dict, routing, model_dtype: torch.dtype) -> torch.Tensor:
+    """fp32 evaluation of the quant-tier algorithm with forced routing (idx, w)."""
+    w_gu, w_d = deq_weights["w_gate_up"], deq_weights["w_down"]
+    E = w_gu.shape[0] - 1
+    h2 = h.reshape(-1, h.shape[-1])
+    idx, w = routing
+    acc = torch.zeros(h2.shape, dtype=torch.float32)
+    for e in range(E):
+        mask = idx == e
+        if not mask.any():
+            continue
+        tok, pos = torch.where(mask)
+        y = expert_mlp_fp8(h2[tok], w_gu[e], w_d[e], model_dtype)
+        acc.index_add_(0, tok, y * w[tok, pos].float().unsqueeze(-1))
+    return acc + expert_mlp_fp8(h2, w_gu[E], w_d[E], model_dtype)
+
+
 def count_experts_hit(idx: torch.Tensor) -> int:
     return int(torch.unique(idx).numel())
