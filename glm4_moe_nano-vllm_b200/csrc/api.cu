@@ -19,16 +19,12 @@ constexpr int kSimtRows = 8;
 constexpr int kNumBn = 5;
 constexpr int kBnChoices[kNumBn] = {16, 32, 64, 128, 256};
 constexpr int kRouterUmmaMinTokens = 64;   // below this the K-split CUDA-core router wins (latency)
-// stream-K schedule of the expert GEMMs (decode): 16-row tiles only
-constexpr int kSkTileRows = 16;
-constexpr int kSkMaxItems = 16384;
-constexpr int kSkMaxGrid = 256;
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct WsLayout {
   size_t logits, idx, w, offsets, row_token, row_weight, slot_row, num_tiles, sched, tiles, scratch, x_rows,
-      act, y, xq, sx, actq, sact, sk_part, sk_cnt, total;
+      act, y, xq, sx, actq, sact, total;
   int tile_capacity;
 };
 
@@ -52,8 +48,6 @@ WsLayout make_layout(const glm4moe_config_t& c) {
   L.slot_row = take(T * k * 4);
   L.num_tiles = take(16);
   L.sched = take(64);
-  L.sk_cnt = take(2 * kSkMaxItems * 4);                                 // gate_up and down launches
-  L.sk_part = take(static_cast<size_t>(kSkMaxGrid) * 2 * 2 * kSkTileRows * 128 * 4);
   L.tile_capacity = glm4moe_tile_capacity(static_cast<int>(T), static_cast<int>(k), static_cast<int>(E),
                                           kSimtRows);
   L.tiles = take(static_cast<size_t>(L.tile_capacity) * 16);
@@ -171,8 +165,7 @@ extern "C" int glm4moe_layer_create(const glm4moe_config_t* cfg, const void* gat
   l->last_launches = 0;
   l->last_impl = GLM4MOE_IMPL_AUTO;
   l->events_ready = false;
-  if (cudaMemset(l->ws + L.sched, 0, 64) != cudaSuccess ||
-      cudaMemset(l->ws + L.sk_cnt, 0, 2 * kSkMaxItems * 4) != cudaSuccess) {
+  if (cudaMemset(l->ws + L.sched, 0, 64) != cudaSuccess) {
     delete l;
     return GLM4MOE_ERR_DEVICE;
   }
@@ -250,15 +243,6 @@ static int pick_bn_index(const glm4moe_config_t& c, int T) {
   if (mean <= 48.0) return 2;
   if (mean <= 96.0) return 3;
   return 4;
-}
-
-static int sk_max_waves() {
-  static int v = -1;
-  if (v < 0) {
-    const char* e = getenv("GLM4MOE_SK_WAVES");   // tuning aid: > 0 enables stream-K (off: no measured gain, and it gives up batch invariance)
-    v = e ? atoi(e) : 0;
-  }
-  return v;
 }
 
 extern "C" int glm4moe_layer_tile_rows(const glm4moe_layer_t* l, int T) {
@@ -406,14 +390,6 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
     if ((rc = umma_fp8_launch(a, stream))) return rc;
   } else if (use_umma) {
     UmmaLaunch a{};
-    // stream-K when the work-item count is a small, uneven multiple of the SM count
-    const int e_local = c.expert_end - c.expert_begin;
-    const int max_tiles = (T * k < e_local ? T * k : e_local) + (sh_hi - sh_lo + tile_rows - 1) / tile_rows;
-    const bool sk = tile_rows == kSkTileRows && l->sm_count <= kSkMaxGrid &&
-                    max_tiles * (H / 128 > I / 128 ? H / 128 : I / 128) <= kSkMaxItems &&
-                    max_tiles * (I / 128) <= sk_max_waves() * l->sm_count;
-    a.sk_part = sk ? reinterpret_cast<float*>(ws + L.sk_part) : nullptr;
-    a.sk_cnt = sk ? reinterpret_cast<int32_t*>(ws + L.sk_cnt) : nullptr;
     a.tiles = tiles;
     a.num_tiles = num_tiles;
     a.tile_rows = tile_rows;
@@ -447,7 +423,6 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
     a.up_row_offset = 0;
     a.mode = 0;
     a.sched = reinterpret_cast<int32_t*>(ws + L.sched) + 2;
-    if (sk) a.sk_cnt += kSkMaxItems;
     if ((rc = umma_launch(a, stream))) return rc;
   } else {
     if ((rc = glm4moe_expert_gate_up_simt(x_rows, l->w_gate_up, tiles, num_tiles, act, H, I, tile_rows, c.dtype,

@@ -18,6 +18,20 @@ constexpr int kTokPerBlock = 256;
 constexpr int kWordsPerExpert = kTokPerBlock / 32;
 constexpr int kMaxExperts = 256;
 
+// Rows [r0, r0 + n) of stack entry `e` as ceil(n / tile_rows) tiles of near-equal size (multiples of
+// 16 rows where the tile size allows: the tensor-core N granularity), written from tiles[ti].
+// .w = index inside the expert | tiles of the expert << 16 (work ordering, umma_common.cuh).
+__device__ __forceinline__ void emit_tiles(int4* __restrict__ tiles, int ti, int e, int r0, int n, int tile_rows) {
+  const int nt = (n + tile_rows - 1) / tile_rows;
+  if (nt == 0) return;
+  const int gran = tile_rows < 16 ? tile_rows : 16;
+  int per = ((n + nt - 1) / nt + gran - 1) / gran * gran;
+  if (per > tile_rows) per = tile_rows;
+  const int packed_nt = nt < 32768 ? nt : 0;     // does not fit the packing: plain per-tile order
+  for (int j = 0, r = 0; j < nt; ++j, r += per)
+    tiles[ti + j] = make_int4(e, r0 + r, min(per, n - r), packed_nt ? (j | (packed_nt << 16)) : 0);
+}
+
 __global__ void __launch_bounds__(kTokPerBlock) permute_rank_kernel(
     const int32_t* __restrict__ idx, int T, int k, int E, int e_lo, int e_hi,
     int32_t* __restrict__ local_rank /*[T*k]*/, int32_t* __restrict__ block_counts /*[nblk][E]*/) {
@@ -98,18 +112,10 @@ __global__ void __launch_bounds__(256) permute_scan_kernel(
   if (e == 0) expert_offsets[E] = s_off[E];
   if (s_tile_off[E] + (sh_hi - sh_lo + tile_rows - 1) / tile_rows > tile_capacity) return;
   if (e < E) {
-    const int n = s_cnt[e];
-    int ti = s_tile_off[e];
-    for (int r = 0; r < n; r += tile_rows, ++ti)
-      tiles[ti] = make_int4(e - e_lo, s_off[e] + r, min(tile_rows, n - r), 0);
+    emit_tiles(tiles, s_tile_off[e], e - e_lo, s_off[e], s_cnt[e], tile_rows);
   }
-  {
-    const int base = s_tile_off[E];
-    const int nt = (sh_hi - sh_lo + tile_rows - 1) / tile_rows;
-    for (int i = threadIdx.x; i < nt; i += blockDim.x)
-      tiles[base + i] = make_int4(e_hi - e_lo, T * k + sh_lo + i * tile_rows,
-                                  min(tile_rows, sh_hi - sh_lo - i * tile_rows), 0);
-  }
+  if (threadIdx.x == blockDim.x - 1)
+    emit_tiles(tiles, s_tile_off[E], e_hi - e_lo, T * k + sh_lo, sh_hi - sh_lo, tile_rows);
 }
 
 __global__ void __launch_bounds__(kTokPerBlock) permute_scatter_kernel(
@@ -197,15 +203,10 @@ __global__ void __launch_bounds__(kTokPerBlock) permute_small_kernel(
   if (tid == 0) *num_tiles = fits ? s_tile_off[E] + shared_tiles : 0;
   for (int e = tid; e <= E; e += kTokPerBlock) expert_offsets[e] = s_off[e];
   if (fits) {
-    for (int e = tid; e < E; e += kTokPerBlock) {
-      const int n = s_cnt[e];
-      int ti = s_tile_off[e];
-      for (int r = 0; r < n; r += tile_rows, ++ti)
-        tiles[ti] = make_int4(e - e_lo, s_off[e] + r, min(tile_rows, n - r), 0);
-    }
-    for (int i = tid; i < shared_tiles; i += kTokPerBlock)
-      tiles[s_tile_off[E] + i] = make_int4(e_hi - e_lo, T * k + sh_lo + i * tile_rows,
-                                           min(tile_rows, sh_hi - sh_lo - i * tile_rows), 0);
+    for (int e = tid; e < E; e += kTokPerBlock)
+      emit_tiles(tiles, s_tile_off[e], e - e_lo, s_off[e], s_cnt[e], tile_rows);
+    if (tid == kTokPerBlock - 1)
+      emit_tiles(tiles, s_tile_off[E], e_hi - e_lo, T * k + sh_lo, sh_hi - sh_lo, tile_rows);
   }
   if (tid < T) {
     for (int s = 0; s < k; ++s) {

@@ -162,36 +162,31 @@ __host__ __device__ constexpr uint32_t make_idesc_f8(int n) {
 
 constexpr int kBM = 128;   // weight rows (output features) per tile
 
-struct TileRef { int expert, row_start, nrows; };
+struct WorkRef { int expert, row_start, nrows, f; };
 
-// work item -> tile.  `tiles == nullptr` means dense rows [0, dense_rows) cut into BN-row tiles.
+// work index -> (token tile, feature tile).  Tiles of one expert are contiguous in the list and
+// carry {index inside the expert | tiles of the expert << 16} in .w; the work items of an expert
+// are ordered feature-tile major, token-tile minor, so the CTAs that share a weight slab
+// [128 x K] run at the same time and it crosses HBM once (the second reader hits L2).
+// `tiles == nullptr`: dense rows [0, dense_rows) of a single weight, BN-row tiles, same order.
 template <int BN>
-__device__ __forceinline__ TileRef get_tile(const int4* __restrict__ tiles, int ti, int dense_rows) {
-  if (tiles) {
-    const int4 t = tiles[ti];
-    return {t.x, t.y, t.z};
+__device__ __forceinline__ WorkRef get_work(const int4* __restrict__ tiles, int w, int n_feat_tiles,
+                                            int n_tiles, int dense_rows) {
+  if (!tiles) {
+    const int f = w / n_tiles, ti = w - f * n_tiles;
+    return {0, ti * BN, min(BN, dense_rows - ti * BN), f};
   }
-  const int r0 = ti * BN;
-  return {0, r0, min(BN, dense_rows - r0)};
-}
-
-// ---- stream-K bookkeeping (umma_gemm.cu, umma_fp8.cu) ----
-struct Seg { int w, k0, k1; };   // k-blocks [k0, k1) of work item w
-
-// first unit of CTA c when `units` k-blocks are cut into `grid` ranges (grid <= units)
-__device__ __forceinline__ long long sk_range_start(int c, long long units, int grid) {
-  return static_cast<long long>(c) * units / grid;
-}
-// the CTA whose range holds unit u: the largest c with sk_range_start(c) <= u
-__device__ __forceinline__ int sk_owner(long long u, long long units, int grid) {
-  int c = static_cast<int>(((u + 1) * grid - 1) / units);
-  if (c > grid - 1) c = grid - 1;
-  while (c + 1 < grid && sk_range_start(c + 1, units, grid) <= u) ++c;
-  while (c > 0 && sk_range_start(c, units, grid) > u) --c;
-  return c;
-}
-__device__ __forceinline__ void epi_bar_sync(int nthreads) {
-  asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory");
+  const int t0 = w / n_feat_tiles;
+  int4 t = tiles[t0];
+  int f = w - t0 * n_feat_tiles;
+  const int nt = t.w >> 16;
+  if (nt > 1) {
+    const int first = t0 - (t.w & 0xffff);
+    const int local = w - first * n_feat_tiles;
+    f = local / nt;
+    t = tiles[first + local - f * nt];
+  }
+  return {t.x, t.y, t.z, f};
 }
 
 }  // namespace glm4moe

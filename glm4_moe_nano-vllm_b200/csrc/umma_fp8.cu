@@ -91,7 +91,8 @@ __global__ void __launch_bounds__(Fp8Cfg<BN, GATED>::kThreads, 1) umma_fp8_kerne
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
-  const int total_work = *num_tiles_ptr * n_feat_tiles;
+  const int n_tiles = *num_tiles_ptr;
+  const int total_work = n_tiles * n_feat_tiles;
 
   auto next_work = [&](int n) -> int {
     const int q = n & 3;
@@ -114,9 +115,8 @@ __global__ void __launch_bounds__(Fp8Cfg<BN, GATED>::kThreads, 1) umma_fp8_kerne
         ++n_pushed;
       };
       auto issue = [&](int w, int kb, int stage, bool do_w, bool do_x) {
-        const int ti = w / n_feat_tiles, f = w - ti * n_feat_tiles;
-        const int4 tile = tiles[ti];
-        const int w_row = tile.x * w_rows_per_expert + f * kBM;
+        const WorkRef tile = get_work<BN>(tiles, w, n_feat_tiles, n_tiles, 0);
+        const int w_row = tile.expert * w_rows_per_expert + tile.f * kBM;
         unsigned char* sa = smem + stage * Cfg::kStageBytes;
         if (do_w) {
           mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
@@ -126,7 +126,7 @@ __global__ void __launch_bounds__(Fp8Cfg<BN, GATED>::kThreads, 1) umma_fp8_kerne
                         kEvictFirst);
         }
         if (do_x)
-          tma_load_2d(&tm_x, &full_bar[stage], sa + (GATED ? 2 : 1) * Cfg::kABytes, kb * kBKF8, tile.y,
+          tma_load_2d(&tm_x, &full_bar[stage], sa + (GATED ? 2 : 1) * Cfg::kABytes, kb * kBKF8, tile.row_start,
                       kEvictLast);
       };
       int w = static_cast<int>(blockIdx.x) < total_work ? static_cast<int>(blockIdx.x) : -1;
@@ -168,8 +168,8 @@ __global__ void __launch_bounds__(Fp8Cfg<BN, GATED>::kThreads, 1) umma_fp8_kerne
     for (int it = 0;; ++it) {
       const int w = next_work(it);
       if (w < 0) break;
-      const int4 tile = tiles[w / n_feat_tiles];
-      const int n_eff = min(BN, (tile.z + 15) & ~15);
+      const WorkRef tile = get_work<BN>(tiles, w, n_feat_tiles, n_tiles, 0);
+      const int n_eff = min(BN, (tile.nrows + 15) & ~15);
       const uint32_t idesc = make_idesc_f8(0) | (static_cast<uint32_t>(n_eff >> 3) << 17);
       for (int kb = 0; kb < n_kblocks; ++kb, ++pcount) {
         const int ps = pcount & 1u;
@@ -207,21 +207,21 @@ __global__ void __launch_bounds__(Fp8Cfg<BN, GATED>::kThreads, 1) umma_fp8_kerne
     for (int it = 0;; ++it) {
       const int w = next_work(it);
       if (w < 0) break;
-      const int ti = w / n_feat_tiles, f = w - ti * n_feat_tiles;
-      const int4 tile = tiles[ti];
-      const int nrows = tile.z;
+      const WorkRef tile = get_work<BN>(tiles, w, n_feat_tiles, n_tiles, 0);
+      const int f = tile.f;
+      const int nrows = tile.nrows;
       float acc_g[NC], acc_u[GATED ? NC : 1];
 #pragma unroll
       for (int j = 0; j < NC; ++j) acc_g[j] = 0.f;
 #pragma unroll
       for (int j = 0; j < (GATED ? NC : 1); ++j) acc_u[j] = 0.f;
       // weight scale rows of this tile: gate/down block row f, up block row (up_row_offset/128 + f)
-      const float* sw_g = w_scale + (static_cast<size_t>(tile.x) * (w_rows_per_expert / 128) + f) * kb_total;
+      const float* sw_g = w_scale + (static_cast<size_t>(tile.expert) * (w_rows_per_expert / 128) + f) * kb_total;
       const float* sw_u = sw_g + static_cast<size_t>(up_row_offset / 128) * kb_total;
       // lane j (< NC) owns the activation scale of token column col_base + j
       const int my_col = col_base + (lane % NC);
       const bool my_col_ok = my_col < nrows;
-      const float* sx = x_scale_t + tile.y + my_col;
+      const float* sx = x_scale_t + tile.row_start + my_col;
       for (int kb = 0; kb < kb_total; ++kb, ++pcount) {
         const int ps = pcount & 1u;
         // scales first: they do not depend on the MMA
@@ -252,10 +252,10 @@ __global__ void __launch_bounds__(Fp8Cfg<BN, GATED>::kThreads, 1) umma_fp8_kerne
       }
       // fused output math + store (lane = feature, coalesced 2-byte stores per token)
       const int feat = f * kBM + ew * 32 + lane;
-      T* out_col = out + static_cast<size_t>(tile.y) * ld_out + feat;
+      T* out_col = out + static_cast<size_t>(tile.row_start) * ld_out + feat;
       float rw_lane = 1.0f;
       if (!GATED) {
-        const int row = tile.y + my_col;
+        const int row = tile.row_start + my_col;
         if (my_col_ok && row < n_routed_rows) rw_lane = __ldg(row_weight + row);
       }
 #pragma unroll
@@ -312,13 +312,15 @@ __global__ void __launch_bounds__(256) quant_rows_fp8_kernel(
     for (int q = 0; q < 8; ++q) amax = fmaxf(amax, fabsf(v[q]));
 #pragma unroll
     for (int o = 8; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
-    const float scale = fmaxf(amax, 1e-10f) * (1.0f / 448.0f);
-    const float inv = 1.0f / scale;
+    // IEEE divisions, exactly the published formula (scale = amax / 448, q = rn_e4m3(v / scale)):
+    // with 8-bit-mantissa inputs v / scale lands on e4m3 rounding ties often enough that a
+    // reciprocal-multiply variant re-rounds ~0.3 % of the elements differently
+    const float scale = __fdiv_rn(fmaxf(amax, 1e-10f), 448.0f);
     uint32_t lo = 0, hi = 0;
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
-      lo |= static_cast<uint32_t>(__nv_cvt_float_to_fp8(v[q] * inv, __NV_SATFINITE, __NV_E4M3)) << (8 * q);
-      hi |= static_cast<uint32_t>(__nv_cvt_float_to_fp8(v[4 + q] * inv, __NV_SATFINITE, __NV_E4M3)) << (8 * q);
+      lo |= static_cast<uint32_t>(__nv_cvt_float_to_fp8(__fdiv_rn(v[q], scale), __NV_SATFINITE, __NV_E4M3)) << (8 * q);
+      hi |= static_cast<uint32_t>(__nv_cvt_float_to_fp8(__fdiv_rn(v[4 + q], scale), __NV_SATFINITE, __NV_E4M3)) << (8 * q);
     }
     if (ok) {
       *reinterpret_cast<uint2*>(d + c) = make_uint2(lo, hi);

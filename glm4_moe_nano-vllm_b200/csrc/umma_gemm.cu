@@ -13,6 +13,8 @@
 // CTA = 8 warps, warp-specialised, persistent over a device-side work list (tile x feature-tile):
 //   warp 0  TMA producer: weights [128 x 64] (+ the matching up_proj tile when GATED) and the
 //           activation tile [BN x 64] per k-block into a kStages-deep 128B-swizzled smem ring
+//           (a `tile::gather4` variant that read the un-permuted tokens directly was measured
+//           2.4-4x slower at 256-row tiles and only tied at decode: profiles/r1_gather4.md)
 //   warp 1  MMA issuer (one elected lane): 4 x tcgen05.mma (K=16) per k-block per accumulator
 //   warp 2  TMEM allocator / deallocator
 //   warps 4-7 epilogue: tcgen05.ld 32 lanes x 16 columns, fused math, coalesced 2-byte stores
@@ -67,9 +69,7 @@ __global__ void __launch_bounds__(UmmaCfg<BN, MODE>::kThreads, 1) umma_grouped_k
     int n_routed_rows, int n_feat_tiles, int n_feat_valid, int n_kblocks,
     int w_rows_per_expert,                      // gated: 2I, down: H, plain: 0
     int up_row_offset,                          // gated: I
-    int32_t* __restrict__ sched,                // [0] next work index - gridDim, [1] CTAs finished
-    float* __restrict__ sk_part,                // stream-K: fp32 partial tiles [grid][2][accs][BN][128] (nullptr = off)
-    int32_t* __restrict__ sk_cnt) {             // stream-K: per work item arrival counter (self re-arming)
+    int32_t* __restrict__ sched) {              // [0] next work index - gridDim, [1] CTAs finished
   using Cfg = UmmaCfg<BN, MODE>;
   constexpr bool GATED = Cfg::kGated;
   constexpr int AS = Cfg::kAccStages;
@@ -84,9 +84,8 @@ __global__ void __launch_bounds__(UmmaCfg<BN, MODE>::kThreads, 1) umma_grouped_k
   uint64_t* tmem_empty = tmem_full + 2;
   uint64_t* sched_full = tmem_empty + 2;
   uint64_t* sched_empty = sched_full + kSchedDepth;
-  int32_t* sched_w = reinterpret_cast<int32_t*>(sched_empty + kSchedDepth);   // [depth][3]: item, kb0, kb1
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(sched_w + 3 * kSchedDepth);
-  int32_t* sk_flag = reinterpret_cast<int32_t*>(tmem_ptr_smem + 1);
+  int32_t* sched_w = reinterpret_cast<int32_t*>(sched_empty + kSchedDepth);   // [depth][2]: work item, n_tiles
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(sched_w + 2 * kSchedDepth);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -116,115 +115,84 @@ __global__ void __launch_bounds__(UmmaCfg<BN, MODE>::kThreads, 1) umma_grouped_k
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
 
-  const int n_tiles = tiles ? *num_tiles_ptr : (dense_rows + BN - 1) / BN;
-  const int total_work = n_tiles * n_feat_tiles;
-  // Stream-K (decode, few work items): the K loops of all items form one unit line of
-  // total_work * n_kblocks k-blocks that is cut into gridDim equal ranges, so every SM streams the
-  // same number of weight bytes whatever the item count; items cut by a range boundary are
-  // finished by whichever CTA delivers the last partial (fixed summation order).
-  const bool SK = sk_part != nullptr;
-  const long long sk_units = static_cast<long long>(total_work) * n_kblocks;
-  const int sk_grid = sk_units < static_cast<long long>(gridDim.x) ? static_cast<int>(sk_units)
-                                                                     : static_cast<int>(gridDim.x);
-
-  // consumer side of the work queue: n-th work segment of this CTA (item -1 = done)
-  auto next_work = [&](int n) -> Seg {
+  // consumer side of the work queue: n-th work item of this CTA (-1 = done) and the tile count
+  auto next_work = [&](int n, int& n_tiles) -> int {
     const int q = n % kSchedDepth;
     mbar_wait(&sched_full[q], (n / kSchedDepth) & 1u);
-    const Seg sg{sched_w[3 * q], sched_w[3 * q + 1], sched_w[3 * q + 2]};
+    const int w = sched_w[2 * q];
+    n_tiles = sched_w[2 * q + 1];
     __syncwarp();
     if (lane == 0) mbar_arrive(&sched_empty[q]);
-    return sg;
+    return w;
   };
 
   if (warp == 0) {
     // ===================== TMA producer + dynamic tile scheduler =====================
     if (elect_one()) {
+      const int n_tiles = tiles ? *num_tiles_ptr : (dense_rows + BN - 1) / BN;
+      const int total_work = n_tiles * n_feat_tiles;
       int n_pushed = 0;
-      auto push_work = [&](const Seg& sg) {
+      bool first = true;
+      // dynamic schedule: the first item is static (blockIdx.x); later ones come from a global counter so
+      // CTAs always take the lowest unprocessed index: balanced, and neighbours in time share
+      // activation / weight tiles in L2.
+      auto fetch_push = [&]() -> int {
+        int w = first ? static_cast<int>(blockIdx.x) : atomicAdd(&sched[0], 1) + static_cast<int>(gridDim.x);
+        first = false;
+        if (w >= total_work) w = -1;
         const int q = n_pushed % kSchedDepth;
         mbar_wait(&sched_empty[q], ((n_pushed / kSchedDepth) & 1u) ^ 1u);
-        sched_w[3 * q] = sg.w;
-        sched_w[3 * q + 1] = sg.k0;
-        sched_w[3 * q + 2] = sg.k1;
+        sched_w[2 * q] = w;
+        sched_w[2 * q + 1] = n_tiles;
         mbar_arrive(&sched_full[q]);
         ++n_pushed;
+        return w;
       };
-      // dynamic mode: the first item is static (blockIdx.x); later ones come from a global counter so
-      // CTAs always take the lowest unprocessed index: balanced, and neighbours in time share
-      // activation / weight tiles in L2.  Stream-K mode: this CTA's unit range, item by item.
-      long long sk_u = 0, sk_end = 0;
-      if (SK && static_cast<int>(blockIdx.x) < sk_grid) {
-        sk_u = sk_range_start(blockIdx.x, sk_units, sk_grid);
-        sk_end = sk_range_start(blockIdx.x + 1, sk_units, sk_grid);
-      }
-      bool first = true;
-      auto fetch_work = [&]() -> Seg {
-        if (SK) {
-          if (sk_u >= sk_end) return Seg{-1, 0, 0};
-          const int w = static_cast<int>(sk_u / n_kblocks);
-          const int k0 = static_cast<int>(sk_u - static_cast<long long>(w) * n_kblocks);
-          const long long left = sk_end - sk_u;
-          const int k1 = left < n_kblocks - k0 ? k0 + static_cast<int>(left) : n_kblocks;
-          sk_u += k1 - k0;
-          return Seg{w, k0, k1};
-        }
-        int w;
-        if (first) {
-          first = false;
-          w = static_cast<int>(blockIdx.x);
-        } else {
-          w = atomicAdd(&sched[0], 1) + static_cast<int>(gridDim.x);
-        }
-        return Seg{w < total_work ? w : -1, 0, n_kblocks};
-      };
-      auto issue = [&](int w, int kb, int stage, bool do_w, bool do_x) {
-        const int ti = w / n_feat_tiles, f = w - ti * n_feat_tiles;
-        const TileRef tile = get_tile<BN>(tiles, ti, dense_rows);
-        const int w_row = tile.expert * w_rows_per_expert + f * kBM;
+      WorkRef wr{0, 0, 0, 0};
+      auto issue = [&](int kb, int stage, bool do_w, bool do_x) {
         unsigned char* sa = smem + stage * Cfg::kStageBytes;
         if (do_w) {
+          const int w_row = wr.expert * w_rows_per_expert + wr.f * kBM;
           mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
           tma_load_2d(&tm_w, &full_bar[stage], sa, kb * kBK, w_row, kEvictFirst);
           if (GATED)
-            tma_load_2d(&tm_w, &full_bar[stage], sa + Cfg::kABytes, kb * kBK, w_row + up_row_offset,
-                        kEvictFirst);
+            tma_load_2d(&tm_w, &full_bar[stage], sa + Cfg::kABytes, kb * kBK, w_row + up_row_offset, kEvictFirst);
         }
         if (do_x)
-          tma_load_2d(&tm_x, &full_bar[stage], sa + (GATED ? 2 : 1) * Cfg::kABytes, kb * kBK,
-                      tile.row_start, kEvictLast);
+          tma_load_2d(&tm_x, &full_bar[stage], sa + (GATED ? 2 : 1) * Cfg::kABytes, kb * kBK, wr.row_start,
+                      kEvictLast);
       };
-      Seg sg = fetch_work();
-      push_work(sg);
-      // (1) Before the dependency wait: weight tiles of the first segment for the first pass over
+      int w = fetch_push();
+      if (w >= 0) wr = get_work<BN>(tiles, w, n_feat_tiles, n_tiles, dense_rows);
+      // (1) Before the dependency wait: weight tiles of the first item for the first pass over
       //     the ring.  Weights and the work list are at least two launches old (see common.cuh),
       //     so this overlaps the predecessor's tail with our pipeline fill.
       int n_pre = 0;
-      if (sg.w >= 0)
-        for (; n_pre < Cfg::kStages && sg.k0 + n_pre < sg.k1; ++n_pre) issue(sg.w, sg.k0 + n_pre, n_pre, true, false);
+      if (w >= 0)
+        for (; n_pre < Cfg::kStages && n_pre < n_kblocks; ++n_pre) issue(n_pre, n_pre, true, false);
       pdl_wait();
       pdl_launch();
       // (2) the activation tiles of those stages (written by the direct predecessor)
-      for (int i = 0; i < n_pre; ++i) issue(sg.w, sg.k0 + i, i, false, true);
-      int kb = sg.k0 + n_pre;
+      for (int i = 0; i < n_pre; ++i) issue(i, i, false, true);
+      int kb = n_pre;
       int stage = n_pre == Cfg::kStages ? 0 : n_pre;
       uint32_t phase = n_pre == Cfg::kStages ? 1u : 0u;
       // (3) steady state
-      while (sg.w >= 0) {
-        if (kb == sg.k1) {
-          sg = fetch_work();
-          push_work(sg);
-          kb = sg.k0;
+      while (w >= 0) {
+        if (kb == n_kblocks) {
+          w = fetch_push();
+          if (w >= 0) wr = get_work<BN>(tiles, w, n_feat_tiles, n_tiles, dense_rows);
+          kb = 0;
           continue;
         }
         mbar_wait(&empty_bar[stage], phase ^ 1u);
-        issue(sg.w, kb, stage, true, true);
+        issue(kb, stage, true, true);
         ++kb;
         if (++stage == Cfg::kStages) { stage = 0; phase ^= 1u; }
       }
       // last CTA out re-arms the counters for the next launch
       __threadfence();
-      if (!SK && atomicAdd(&sched[1], 1) == static_cast<int>(gridDim.x) - 1) {
+      if (atomicAdd(&sched[1], 1) == static_cast<int>(gridDim.x) - 1) {
         sched[0] = 0;
         sched[1] = 0;
         __threadfence();
@@ -236,20 +204,20 @@ __global__ void __launch_bounds__(UmmaCfg<BN, MODE>::kThreads, 1) umma_grouped_k
     int stage = 0;
     uint32_t phase = 0;
     for (int it = 0;; ++it) {
-      const Seg sg = next_work(it);
-      if (sg.w < 0) break;
-      const int ti = sg.w / n_feat_tiles;
-      const TileRef tile = get_tile<BN>(tiles, ti, dense_rows);
+      int n_tiles;
+      const int w = next_work(it, n_tiles);
+      if (w < 0) break;
+      const WorkRef wr = get_work<BN>(tiles, w, n_feat_tiles, n_tiles, dense_rows);
       // MMA N follows the rows this tile really holds (multiple of 16): a ragged tail tile of an
       // expert costs tensor time in proportion to its rows, not to BN.
-      const int n_eff = min(BN, (tile.nrows + 15) & ~15);
+      const int n_eff = min(BN, (wr.nrows + 15) & ~15);
       const uint32_t idesc = idesc_base | (static_cast<uint32_t>(n_eff >> 3) << 17);
       const int as = AS == 2 ? (it & 1) : 0;
       const uint32_t aphase = AS == 2 ? ((it >> 1) & 1u) : (it & 1u);
       mbar_wait(&tmem_empty[as], aphase ^ 1u);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + as * Cfg::kAccCols;
-      for (int kb = sg.k0; kb < sg.k1; ++kb) {
+      for (int kb = 0; kb < n_kblocks; ++kb) {
         mbar_wait(&full_bar[stage], phase);
         tc_fence_after();
         if (elect_one()) {
@@ -259,12 +227,12 @@ __global__ void __launch_bounds__(UmmaCfg<BN, MODE>::kThreads, 1) umma_grouped_k
           const uint64_t b_desc = make_kmajor_desc(sa + (GATED ? 2 : 1) * Cfg::kABytes);
 #pragma unroll
           for (int ks = 0; ks < kBK / 16; ++ks) {
-            const uint32_t acc = (kb > sg.k0 || ks > 0) ? 1u : 0u;
+            const uint32_t acc = (kb > 0 || ks > 0) ? 1u : 0u;
             umma_f16(d_tmem, a_desc + 2 * ks, b_desc + 2 * ks, idesc, acc);
             if (GATED) umma_f16(d_tmem + BN, u_desc + 2 * ks, b_desc + 2 * ks, idesc, acc);
           }
-          umma_commit(&empty_bar[stage]);                       // smem slot free when MMAs finish
-          if (kb == sg.k1 - 1) umma_commit(&tmem_full[as]);     // accumulator ready
+          umma_commit(&empty_bar[stage]);                          // smem slot free when MMAs finish
+          if (kb == n_kblocks - 1) umma_commit(&tmem_full[as]);    // accumulator ready
         }
         __syncwarp();
         if (++stage == Cfg::kStages) { stage = 0; phase ^= 1u; }
@@ -279,124 +247,60 @@ __global__ void __launch_bounds__(UmmaCfg<BN, MODE>::kThreads, 1) umma_grouped_k
     constexpr int kChunkStep = 16 * (EW / 4);
     const uint32_t lane_base = static_cast<uint32_t>(ew * 32) << 16;
     for (int it = 0;; ++it) {
-      const Seg sg = next_work(it);
-      const int w = sg.w;
+      int n_tiles;
+      const int w = next_work(it, n_tiles);
       if (w < 0) break;
-      const int ti = w / n_feat_tiles, f = w - ti * n_feat_tiles;
-      const TileRef tile = get_tile<BN>(tiles, ti, dense_rows);
+      const WorkRef wr = get_work<BN>(tiles, w, n_feat_tiles, n_tiles, dense_rows);
       const int as = AS == 2 ? (it & 1) : 0;
       const uint32_t aphase = AS == 2 ? ((it >> 1) & 1u) : (it & 1u);
       mbar_wait(&tmem_full[as], aphase);
       tc_fence_after();
       const uint32_t t_acc = tmem_base + lane_base + as * Cfg::kAccCols;
-      const int feat = f * kBM + ew * 32 + lane;
+      const int feat = wr.f * kBM + ew * 32 + lane;
       const bool feat_ok = MODE != kModePlain || feat < n_feat_valid;
-      T* out_col = out + static_cast<size_t>(tile.row_start) * ld_out + feat;
-      const bool partial = sg.k0 > 0 || sg.k1 < n_kblocks;     // stream-K only
-      if (!partial) {
+      T* out_col = out + static_cast<size_t>(wr.row_start) * ld_out + feat;
 #pragma unroll 1
-        for (int c0 = 16 * chunk0; c0 < BN; c0 += kChunkStep) {
-          if (c0 >= tile.nrows) break;              // warp-uniform: remaining token columns unused
-          uint32_t g[16];
-          tmem_ld16(t_acc + c0, g);
-          if (MODE == kModeGated) {
-            uint32_t u[16];
-            tmem_ld16(t_acc + BN + c0, u);
-            tmem_ld_wait();
-#pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              if (c0 + j < tile.nrows) {
-                const float v = silu_fast(__uint_as_float(g[j])) * __uint_as_float(u[j]);
-                out_col[static_cast<size_t>(c0 + j) * ld_out] = Dt<T>::from_f(v);
-              }
-            }
-          } else if (MODE == kModeDown) {
-            // lane j (< 16) fetches the routing weight of token column c0 + j once; broadcast by shuffle
-            float rw_lane = 1.0f;
-            {
-              const int row = tile.row_start + c0 + (lane & 15);
-              if (c0 + (lane & 15) < tile.nrows && row < n_routed_rows) rw_lane = __ldg(row_weight + row);
-            }
-            tmem_ld_wait();
-#pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              const float rw = __shfl_sync(0xffffffffu, rw_lane, j);
-              if (c0 + j < tile.nrows)
-                out_col[static_cast<size_t>(c0 + j) * ld_out] = Dt<T>::from_f(__uint_as_float(g[j]) * rw);
-            }
-          } else {
-            tmem_ld_wait();
-#pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              if (c0 + j < tile.nrows && feat_ok)
-                out_col[static_cast<size_t>(c0 + j) * ld_out] = Dt<T>::from_f(__uint_as_float(g[j]));
-            }
-          }
-        }
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&tmem_empty[as]);
-        continue;
-      }
-      // ---- stream-K partial segment (EW == 4: warp = lane quadrant, all token columns) ----
-      constexpr int kAccs = GATED ? 2 : 1;
-      constexpr size_t kPartElems = static_cast<size_t>(kAccs) * BN * kBM;
-      const int my_feat = ew * 32 + lane;
-      {
-        // slot 0: segment continuing an item (k0 > 0); slot 1: segment opening one (k0 == 0)
-        float* part = sk_part + (static_cast<size_t>(blockIdx.x) * 2 + (sg.k0 > 0 ? 0 : 1)) * kPartElems;
-#pragma unroll 1
-        for (int c0 = 0; c0 < BN; c0 += 16) {
-          if (c0 >= tile.nrows) break;
-          uint32_t g[16], u[16];
-          tmem_ld16(t_acc + c0, g);
-          if (GATED) tmem_ld16(t_acc + BN + c0, u);
+      for (int c0 = 16 * chunk0; c0 < BN; c0 += kChunkStep) {
+        if (c0 >= wr.nrows) break;              // warp-uniform: remaining token columns unused
+        uint32_t g[16];
+        tmem_ld16(t_acc + c0, g);
+        if (MODE == kModeGated) {
+          uint32_t u[16];
+          tmem_ld16(t_acc + BN + c0, u);
           tmem_ld_wait();
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
-            if (c0 + j < tile.nrows) {
-              __stcg(part + static_cast<size_t>(c0 + j) * kBM + my_feat, __uint_as_float(g[j]));
-              if (GATED) __stcg(part + static_cast<size_t>(BN + c0 + j) * kBM + my_feat, __uint_as_float(u[j]));
+            if (c0 + j < wr.nrows) {
+              const float v = silu_fast(__uint_as_float(g[j])) * __uint_as_float(u[j]);
+              out_col[static_cast<size_t>(c0 + j) * ld_out] = Dt<T>::from_f(v);
             }
+          }
+        } else if (MODE == kModeDown) {
+          // lane j (< 16) fetches the routing weight of token column c0 + j once; broadcast by shuffle
+          float rw_lane = 1.0f;
+          {
+            const int row = wr.row_start + c0 + (lane & 15);
+            if (c0 + (lane & 15) < wr.nrows && row < n_routed_rows) rw_lane = __ldg(row_weight + row);
+          }
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const float rw = __shfl_sync(0xffffffffu, rw_lane, j);
+            if (c0 + j < wr.nrows)
+              out_col[static_cast<size_t>(c0 + j) * ld_out] = Dt<T>::from_f(__uint_as_float(g[j]) * rw);
+          }
+        } else {
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            if (c0 + j < wr.nrows && feat_ok)
+              out_col[static_cast<size_t>(c0 + j) * ld_out] = Dt<T>::from_f(__uint_as_float(g[j]));
           }
         }
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty[as]);
-      // publish, then find out whether this was the item's last missing segment
-      const long long u_first = static_cast<long long>(w) * n_kblocks;
-      const int c_first = sk_owner(u_first, sk_units, sk_grid);
-      const int c_last = sk_owner(u_first + n_kblocks - 1, sk_units, sk_grid);
-      __threadfence();
-      epi_bar_sync(EW * 32);
-      if (warp == 4 && lane == 0) *sk_flag = atomicAdd(&sk_cnt[w], 1) == c_last - c_first;
-      epi_bar_sync(EW * 32);
-      if (*sk_flag) {
-        __threadfence();
-        float rw_lane = 1.0f;
-        if (MODE == kModeDown) {
-          const int row = tile.row_start + lane;
-          if (lane < tile.nrows && row < n_routed_rows) rw_lane = __ldg(row_weight + row);
-        }
-        for (int c = 0; c < tile.nrows; ++c) {
-          float gs = 0.f, us = 0.f;
-          for (int cc = c_first; cc <= c_last; ++cc) {
-            // CTA cc's segment of this item opens it iff its range starts at or before the item's first unit
-            const int slot = sk_range_start(cc, sk_units, sk_grid) > u_first ? 0 : 1;
-            const float* part = sk_part + (static_cast<size_t>(cc) * 2 + slot) * kPartElems;
-            gs += __ldcg(part + static_cast<size_t>(c) * kBM + my_feat);
-            if (GATED) us += __ldcg(part + static_cast<size_t>(BN + c) * kBM + my_feat);
-          }
-          float v;
-          if (MODE == kModeGated) v = silu_fast(gs) * us;
-          else if (MODE == kModeDown) v = gs * __shfl_sync(0xffffffffu, rw_lane, c & 31);
-          else v = gs;
-          if (feat_ok) out_col[static_cast<size_t>(c) * ld_out] = Dt<T>::from_f(v);
-        }
-        if (warp == 4 && lane == 0) sk_cnt[w] = 0;     // re-arm for the next launch
-      }
-      epi_bar_sync(EW * 32);   // sk_flag is reused by the next segment
     }
   }
 
@@ -457,7 +361,7 @@ static int launch_one(const UmmaLaunch& a, cudaStream_t st) {
       kern, dim3(a.grid), dim3(Cfg::kThreads), Cfg::kSmemBytes, st, *static_cast<const CUtensorMap*>(a.tm_w),
       *static_cast<const CUtensorMap*>(a.tm_x), reinterpret_cast<const int4*>(a.tiles), a.num_tiles, a.dense_rows,
       static_cast<T*>(a.out), a.ld_out, a.row_weight, a.n_routed_rows, a.n_feat_tiles, a.n_feat_valid, a.n_kblocks,
-      a.w_rows_per_expert, a.up_row_offset, a.sched, a.sk_part, a.sk_cnt));
+      a.w_rows_per_expert, a.up_row_offset, a.sched));
   return GLM4MOE_OK;
 }
 

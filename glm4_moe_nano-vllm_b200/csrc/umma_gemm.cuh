@@ -7,7 +7,7 @@ namespace glm4moe {
 struct UmmaLaunch {
   const void* tm_w;        // CUtensorMap (128 bytes) over the stacked weights
   const void* tm_x;        // CUtensorMap over the activation rows, box rows == tile_rows
-  const int32_t* tiles;    // int4 {expert, row_start, nrows, 0}
+  const int32_t* tiles;    // int4 {expert, row_start, nrows, index in expert | tiles of expert << 16}
   const int32_t* num_tiles;
   int dense_rows;          // tiles == nullptr: rows [0, dense_rows) in tile_rows chunks, expert 0
   void* out;
@@ -24,8 +24,6 @@ struct UmmaLaunch {
   int dtype;
   int grid;
   int32_t* sched;          // 2 zero-initialised ints owned by this launch site (self re-arming)
-  float* sk_part;          // stream-K (tile_rows <= 32 only): fp32 partial tiles, grid*2*accs*tile_rows*128 floats
-  int32_t* sk_cnt;         // stream-K: zero-initialised counter per work item (self re-arming); nullptr = off
 };
 
 // 2-D row-major [rows, cols] two-byte tensor, box {64 cols, box_rows}, 128B swizzle.

@@ -22,6 +22,18 @@ moe.quantize_fp8()
 deq = moe.dequantized_weights()
 wgu, wd = deq["w_gate_up"].cpu().float(), deq["w_down"].cpu().float()
 E, k, I, H = shape.E, shape.k, shape.I, shape.H
+
+
+def rt_kernel(a):
+    """the device quantiser's arithmetic: scale = amax * (1/448), q = v * (1/scale)"""
+    n, K = a.shape
+    g = a.float().reshape(n, K // 128, 128)
+    scale = g.abs().amax(-1, keepdim=True).clamp_min(1e-10) * torch.tensor(1.0 / 448.0, dtype=torch.float32)
+    inv = 1.0 / scale
+    q = (g * inv).clamp(-448.0, 448.0).to(torch.float8_e4m3fn).float()
+    return (q * scale).reshape(n, K)
+
+
 for T in Ts:
     x = synth.make_tokens(shape, T, dt, T)
     out = moe(x.cuda())
@@ -35,6 +47,7 @@ for T in Ts:
     nt = int(moe.workspace_view("num_tiles")[0])
     print(f"== T={T} tiles={nt} tile_rows={tiles[:nt].tolist()[:12]}")
     worst = []
+    tot = {"a": [0, 0], "a2": [0, 0], "y": [0, 0], "y2": [0, 0], "x12": [0, 0]}
     for e in list(range(E)) + [E]:
         if e < E:
             r0, r1 = int(offs[e]), int(offs[e + 1])
@@ -57,6 +70,14 @@ for T in Ts:
         y_ref = F.linear(O.fp8_act_roundtrip(a_got.to(dt)), wd[e]) * wts_r[:, None]
         y_got = y[rows]
         ey = (y_got - y_ref).abs().max().item() / (y_ref.abs().max().item() + 1e-9)
+        gu2 = F.linear(rt_kernel(xe), wgu[e])
+        g2, u2 = gu2.chunk(2, -1)
+        a_ref2 = (F.silu(g2) * u2).to(dt).float()
+        y_ref2 = F.linear(rt_kernel(a_got.to(dt)), wd[e]) * wts_r[:, None]
+        for key, got_, ref_ in (("a", a_got, a_ref), ("a2", a_got, a_ref2), ("y", y_got, y_ref), ("y2", y_got, y_ref2),
+                                ("x12", O.fp8_act_roundtrip(xe), rt_kernel(xe))):
+            tot[key][0] += (got_ - ref_).pow(2).sum().item()
+            tot[key][1] += ref_.pow(2).sum().item()
         worst.append((max(ea, ey), e, len(rows), rows[0], ea, ey))
         if ea > 2e-2 or ey > 2e-2:
             # which rows / which feature ranges are off
@@ -69,6 +90,7 @@ for T in Ts:
             print("   y   err per row :", [round(v, 3) for v in dy.tolist()])
             print("   act err per ftile:", [round(v, 3) for v in fa.tolist()])
             print("   y   err per ftile:", [round(v, 3) for v in fy.tolist()])
+    print("rel-F per stage:", {k_: round((v[0] / max(v[1], 1e-30)) ** 0.5, 5) for k_, v in tot.items()})
     worst.sort(reverse=True)
     print("worst:", [(round(a, 4), e, n, r0, round(b, 4), round(c, 4)) for a, e, n, r0, b, c in worst[:5]])
     idx = moe.workspace_view("idx", T).cpu().long()

