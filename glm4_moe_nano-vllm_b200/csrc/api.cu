@@ -19,6 +19,16 @@ constexpr int kSimtRows = 8;
 constexpr int kNumBn = 5;
 constexpr int kBnChoices[kNumBn] = {16, 32, 64, 128, 256};
 constexpr int kRouterUmmaMinTokens = 64;   // below this the K-split CUDA-core router wins (latency)
+constexpr int kDirectMaxTokens = 32;       // decode "direct" mode (fused front-end, no gather): T <= this
+
+int g_direct = -1;   // -1: read GLM4MOE_NO_DIRECT on first use; glm4moe_debug_set(0, v) overrides
+bool direct_enabled() {
+  if (g_direct < 0) {
+    const char* e = getenv("GLM4MOE_NO_DIRECT");   // tuning aid: 1 = always use the general path
+    g_direct = (e && e[0] == '1') ? 0 : 1;
+  }
+  return g_direct == 1;
+}
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
@@ -103,6 +113,13 @@ bool pdl_enabled() {
   return v == 1;
 }
 }  // namespace glm4moe
+
+extern "C" int glm4moe_debug_set(int knob, int value) {
+  switch (knob) {
+    case GLM4MOE_KNOB_DIRECT: g_direct = value ? 1 : 0; return GLM4MOE_OK;
+    default: return GLM4MOE_ERR_ARG;
+  }
+}
 
 extern "C" int glm4moe_abi_version(void) { return GLM4MOE_ABI_VERSION; }
 
@@ -297,11 +314,26 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
   }
   const bool use_umma = l->umma_ok;
   const bool fp8 = c.weight_format == GLM4MOE_W_FP8_BLOCK128;
-  const int bi = fp8 ? (pick_bn_index(c, T) < 2 ? pick_bn_index(c, T) : 2) : pick_bn_index(c, T);
+  // decode "direct" mode: fused front-end + gate_up reading the input tokens in place
+  const bool direct = use_umma && !fp8 && T <= kDirectMaxTokens && H % 64 == 0 && direct_enabled();
+  const int bi = direct ? (T <= 16 ? 0 : 1)
+                        : fp8 ? (pick_bn_index(c, T) < 2 ? pick_bn_index(c, T) : 2) : pick_bn_index(c, T);
   const int tile_rows = use_umma ? kBnChoices[bi] : kSimtRows;
   const int launches0 = g_launches;
   int rc;
+  alignas(64) CUtensorMap tm_xdirect;
   STAGE_MARK(0);
+  if (direct) {
+    if ((rc = umma_make_tensor_map(&tm_xdirect, x, c.dtype, static_cast<uint64_t>(T), H, tile_rows))) return rc;
+    if ((rc = glm4moe_route_small(x, l->gate_w, l->bias, logits, T, H, E, k, c.routed_scaling_factor, c.dtype,
+                                  c.expert_begin, c.expert_end, tile_rows, sh_lo, sh_hi, idx, w, offsets, row_token,
+                                  row_weight, slot_row, tiles, L.tile_capacity, num_tiles,
+                                  reinterpret_cast<int32_t*>(ws + L.sched) + 8, stream)))
+      return rc;
+    STAGE_MARK(1);
+    STAGE_MARK(2);
+    STAGE_MARK(3);
+  } else {
   if (use_umma && T >= kRouterUmmaMinTokens && H % 64 == 0) {
     // router logits on the tensor cores: D[expert, token] = Wg . x^T, dense token tiles of x itself
     alignas(64) CUtensorMap tm_xin;
@@ -336,8 +368,11 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
                             row_token, row_weight, slot_row, tiles, L.tile_capacity, num_tiles, scratch, stream)))
     return rc;
   STAGE_MARK(3);
+  }
   const int R_cap = c.max_tokens * (k + 1);
-  if (fp8) {
+  if (direct) {
+    // no gathered copy of the token rows
+  } else if (fp8) {
     // gather fused with the per-token 1x128 activation quantiser
     if ((rc = quant_rows_fp8(x, H, row_token, offsets, E, T, k, H, sh_lo, sh_hi, ws + L.xq,
                              reinterpret_cast<float*>(ws + L.sx), R_cap, c.dtype, stream)))
@@ -409,7 +444,17 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
     a.up_row_offset = I;
     a.mode = 1;
     a.sched = reinterpret_cast<int32_t*>(ws + L.sched);
+    if (direct) {
+      a.tm_x = &tm_xdirect;
+      a.direct.tokens = T;
+      a.direct.shared_expert = c.expert_end - c.expert_begin;
+      a.direct.shared_row0 = T * k;
+      a.direct.sh_lo = sh_lo;
+      a.direct.sh_hi = sh_hi;
+      a.direct.row_token = row_token;
+    }
     if ((rc = umma_launch(a, stream))) return rc;
+    a.direct = DirectArgs{};
     STAGE_MARK(5);
     // down * routing weight
     a.tm_w = &l->tm_w_d;

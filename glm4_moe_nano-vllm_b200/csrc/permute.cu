@@ -11,26 +11,9 @@
 //   scan_kernel   (1 block): block-exclusive prefix per expert, expert offsets, tile work list
 //   scatter_kernel(grid = ceil(T/256)): row = offsets[e] + block_base[b][e] + local rank
 #include "common.cuh"
+#include "route_device.cuh"
 
 namespace glm4moe {
-
-constexpr int kTokPerBlock = 256;
-constexpr int kWordsPerExpert = kTokPerBlock / 32;
-constexpr int kMaxExperts = 256;
-
-// Rows [r0, r0 + n) of stack entry `e` as ceil(n / tile_rows) tiles of near-equal size (multiples of
-// 16 rows where the tile size allows: the tensor-core N granularity), written from tiles[ti].
-// .w = index inside the expert | tiles of the expert << 16 (work ordering, umma_common.cuh).
-__device__ __forceinline__ void emit_tiles(int4* __restrict__ tiles, int ti, int e, int r0, int n, int tile_rows) {
-  const int nt = (n + tile_rows - 1) / tile_rows;
-  if (nt == 0) return;
-  const int gran = tile_rows < 16 ? tile_rows : 16;
-  int per = ((n + nt - 1) / nt + gran - 1) / gran * gran;
-  if (per > tile_rows) per = tile_rows;
-  const int packed_nt = nt < 32768 ? nt : 0;     // does not fit the packing: plain per-tile order
-  for (int j = 0, r = 0; j < nt; ++j, r += per)
-    tiles[ti + j] = make_int4(e, r0 + r, min(per, n - r), packed_nt ? (j | (packed_nt << 16)) : 0);
-}
 
 __global__ void __launch_bounds__(kTokPerBlock) permute_rank_kernel(
     const int32_t* __restrict__ idx, int T, int k, int E, int e_lo, int e_hi,
@@ -147,83 +130,13 @@ __global__ void __launch_bounds__(kTokPerBlock) permute_small_kernel(
     int e_hi, int tile_rows, int sh_lo, int sh_hi, int32_t* __restrict__ expert_offsets,
     int32_t* __restrict__ row_token, float* __restrict__ row_weight, int32_t* __restrict__ slot_row,
     int4* __restrict__ tiles, int tile_capacity, int32_t* __restrict__ num_tiles) {
-  __shared__ uint32_t bitmap[kMaxExperts * kWordsPerExpert];
-  __shared__ int s_cnt[kMaxExperts];
-  __shared__ int s_off[kMaxExperts + 1];
-  __shared__ int s_tile_off[kMaxExperts + 1];
-  const int tid = threadIdx.x;
-  for (int i = tid; i < E * kWordsPerExpert; i += kTokPerBlock) bitmap[i] = 0u;
+  __shared__ PermuteSmallSmem sm;
+  for (int i = threadIdx.x; i < E * kWordsPerExpert; i += kTokPerBlock) sm.bitmap[i] = 0u;
   pdl_wait();
   pdl_launch();
   __syncthreads();
-  const int word = tid >> 5;
-  const uint32_t bit = 1u << (tid & 31);
-  if (tid < T) {
-    for (int s = 0; s < k; ++s) {
-      const int e = idx[static_cast<size_t>(tid) * k + s];
-      if (e >= e_lo && e < e_hi) atomicOr(&bitmap[e * kWordsPerExpert + word], bit);
-    }
-  }
-  __syncthreads();
-  for (int e = tid; e < E; e += kTokPerBlock) {
-    int c = 0;
-#pragma unroll
-    for (int wd = 0; wd < kWordsPerExpert; ++wd) c += __popc(bitmap[e * kWordsPerExpert + wd]);
-    s_cnt[e] = c;
-  }
-  __syncthreads();
-  if (tid < 32) {
-    // warp scan over experts: lane handles ceil(E/32) consecutive experts
-    const int per = (E + 31) / 32;
-    int rows = 0, tl = 0;
-    for (int i = 0; i < per; ++i) {
-      const int e = tid * per + i;
-      if (e < E) { rows += s_cnt[e]; tl += (s_cnt[e] + tile_rows - 1) / tile_rows; }
-    }
-    int rows_incl = rows, tl_incl = tl;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int a = __shfl_up_sync(0xffffffffu, rows_incl, o);
-      const int b = __shfl_up_sync(0xffffffffu, tl_incl, o);
-      if (tid >= o) { rows_incl += a; tl_incl += b; }
-    }
-    int roff = rows_incl - rows, toff = tl_incl - tl;
-    for (int i = 0; i < per; ++i) {
-      const int e = tid * per + i;
-      if (e < E) {
-        s_off[e] = roff; s_tile_off[e] = toff;
-        roff += s_cnt[e]; toff += (s_cnt[e] + tile_rows - 1) / tile_rows;
-      }
-    }
-    if (tid == 31) { s_off[E] = rows_incl; s_tile_off[E] = tl_incl; }
-  }
-  __syncthreads();
-  const int shared_tiles = (sh_hi - sh_lo + tile_rows - 1) / tile_rows;
-  const bool fits = s_tile_off[E] + shared_tiles <= tile_capacity;
-  if (tid == 0) *num_tiles = fits ? s_tile_off[E] + shared_tiles : 0;
-  for (int e = tid; e <= E; e += kTokPerBlock) expert_offsets[e] = s_off[e];
-  if (fits) {
-    for (int e = tid; e < E; e += kTokPerBlock)
-      emit_tiles(tiles, s_tile_off[e], e - e_lo, s_off[e], s_cnt[e], tile_rows);
-    if (tid == kTokPerBlock - 1)
-      emit_tiles(tiles, s_tile_off[E], e_hi - e_lo, T * k + sh_lo, sh_hi - sh_lo, tile_rows);
-  }
-  if (tid < T) {
-    for (int s = 0; s < k; ++s) {
-      const size_t i = static_cast<size_t>(tid) * k + s;
-      const int e = idx[i];
-      int row = -1;
-      if (e >= e_lo && e < e_hi) {
-        const uint32_t* bm = &bitmap[e * kWordsPerExpert];
-        int r = __popc(bm[word] & (bit - 1u));
-        for (int wd = 0; wd < word; ++wd) r += __popc(bm[wd]);
-        row = s_off[e] + r;
-        row_token[row] = tid;
-        row_weight[row] = w[i];
-      }
-      slot_row[i] = row;
-    }
-  }
+  permute_small_body(sm, idx, w, T, k, E, e_lo, e_hi, tile_rows, sh_lo, sh_hi, expert_offsets, row_token,
+                     row_weight, slot_row, tiles, tile_capacity, num_tiles);
 }
 
 // x_rows[r] = x[row_token[r]] (routed), x_rows[T*k + t] = x[t] (shared). One warp per row,

@@ -1,0 +1,185 @@
+// Device-side pieces shared by the stand-alone router / permute kernels (router.cu, permute.cu) and the
+// fused decode front-end (route_small.cu): the per-token expert selection (moe.py:37-46) and the
+// single-block permutation (moe.py:135-147).
+#pragma once
+#include "common.cuh"
+
+namespace glm4moe {
+
+constexpr int kMaxSlots = 8;   // E <= 256
+constexpr int kMaxTopK = 32;
+
+// One warp selects the experts of one token.  `logit_row` may have been written earlier in the same
+// kernel by other blocks (route_small.cu), hence the L2-coherent loads.
+template <typename T>
+__device__ __forceinline__ void select_token(const T* logit_row, const float* __restrict__ bias, int E, int k,
+                                             float scale, int lane, int32_t* __restrict__ idx_row,
+                                             float* __restrict__ w_row) {
+  float choice[kMaxSlots], score[kMaxSlots];
+#pragma unroll
+  for (int j = 0; j < kMaxSlots; ++j) {
+    const int e = j * 32 + lane;
+    if (e < E) {
+      const float lg = Dt<T>::to_f(__ldcg(logit_row + e));
+      const float s = Dt<T>::round(sigmoid_f(lg));       // moe.py:37, model dtype
+      score[j] = s;
+      choice[j] = s + bias[e];                           // moe.py:38, fp32
+    } else {
+      score[j] = 0.f;
+      choice[j] = -INFINITY;
+    }
+  }
+  // k rounds of arg-max; ties -> lower expert id (lane-local scan is ascending in e for fixed
+  // lane, the cross-lane reduction compares (value, id) lexicographically).
+  int my_e = -1;          // lane r keeps the r-th pick
+  float my_s = 0.f;
+  unsigned taken = 0;     // bit j set: my slot j already picked
+  for (int r = 0; r < k; ++r) {
+    float bv = -INFINITY;
+    int be = 0x7fffffff;
+#pragma unroll
+    for (int j = 0; j < kMaxSlots; ++j) {
+      const int e = j * 32 + lane;
+      if (e < E && !((taken >> j) & 1u) && (choice[j] > bv || be == 0x7fffffff)) {
+        bv = choice[j];
+        be = e;
+      }
+    }
+    float bs = 0.f;
+#pragma unroll
+    for (int j = 0; j < kMaxSlots; ++j)
+      if (be == j * 32 + lane) bs = score[j];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+      const int oe = __shfl_xor_sync(0xffffffffu, be, o);
+      const float os = __shfl_xor_sync(0xffffffffu, bs, o);
+      if (oe != 0x7fffffff && (be == 0x7fffffff || ov > bv || (ov == bv && oe < be))) {
+        bv = ov; be = oe; bs = os;
+      }
+    }
+    if ((be & 31) == lane) taken |= 1u << (be >> 5);
+    if (lane == r) { my_e = be; my_s = bs; }
+  }
+  // renormalise: sum in fp32 over the k picks, every intermediate rounded to the model dtype
+  float sum = 0.f;
+  for (int r = 0; r < k; ++r) sum += __shfl_sync(0xffffffffu, my_s, r);
+  const float denom = Dt<T>::round(Dt<T>::round(sum) + 1e-20f);   // moe.py:43
+  float wgt = Dt<T>::round(my_s / denom);                          // moe.py:44
+  wgt = Dt<T>::round(wgt * scale);                                 // moe.py:46
+  // canonical slot order: ascending expert id (the order the reference accumulates in)
+  int rank = 0;
+  for (int r = 0; r < k; ++r) {
+    const int oe = __shfl_sync(0xffffffffu, my_e, r);
+    rank += (lane < k && oe < my_e) ? 1 : 0;
+  }
+  if (lane < k) {
+    idx_row[rank] = my_e;
+    w_row[rank] = wgt;
+  }
+}
+
+constexpr int kTokPerBlock = 256;
+constexpr int kWordsPerExpert = kTokPerBlock / 32;
+constexpr int kMaxExperts = 256;
+
+// Rows [r0, r0 + n) of stack entry `e` as ceil(n / tile_rows) tiles of near-equal size (multiples of
+// 16 rows where the tile size allows: the tensor-core N granularity), written from tiles[ti].
+// .w = index inside the expert | tiles of the expert << 16 (work ordering, umma_common.cuh).
+__device__ __forceinline__ void emit_tiles(int4* __restrict__ tiles, int ti, int e, int r0, int n, int tile_rows) {
+  const int nt = (n + tile_rows - 1) / tile_rows;
+  if (nt == 0) return;
+  const int gran = tile_rows < 16 ? tile_rows : 16;
+  int per = ((n + nt - 1) / nt + gran - 1) / gran * gran;
+  if (per > tile_rows) per = tile_rows;
+  const int packed_nt = nt < 32768 ? nt : 0;     // does not fit the packing: plain per-tile order
+  for (int j = 0, r = 0; j < nt; ++j, r += per)
+    tiles[ti + j] = make_int4(e, r0 + r, min(per, n - r), packed_nt ? (j | (packed_nt << 16)) : 0);
+}
+
+// Decode-size batches (T <= 256): rank + scan + scatter in ONE block of 256 threads, thread t owns
+// token t.  `idx` / `w` may have been written earlier in the same kernel by this block.
+struct PermuteSmallSmem {
+  uint32_t bitmap[kMaxExperts * kWordsPerExpert];
+  int cnt[kMaxExperts];
+  int off[kMaxExperts + 1];
+  int tile_off[kMaxExperts + 1];
+};
+
+__device__ __forceinline__ void permute_small_body(
+    PermuteSmallSmem& sm, const int32_t* idx, const float* w, int T, int k, int E, int e_lo, int e_hi,
+    int tile_rows, int sh_lo, int sh_hi, int32_t* __restrict__ expert_offsets, int32_t* __restrict__ row_token,
+    float* __restrict__ row_weight, int32_t* __restrict__ slot_row, int4* __restrict__ tiles, int tile_capacity,
+    int32_t* __restrict__ num_tiles) {
+  const int tid = threadIdx.x;
+  const int word = tid >> 5;
+  const uint32_t bit = 1u << (tid & 31);
+  if (tid < T) {
+    for (int s = 0; s < k; ++s) {
+      const int e = idx[static_cast<size_t>(tid) * k + s];
+      if (e >= e_lo && e < e_hi) atomicOr(&sm.bitmap[e * kWordsPerExpert + word], bit);
+    }
+  }
+  __syncthreads();
+  for (int e = tid; e < E; e += kTokPerBlock) {
+    int c = 0;
+#pragma unroll
+    for (int wd = 0; wd < kWordsPerExpert; ++wd) c += __popc(sm.bitmap[e * kWordsPerExpert + wd]);
+    sm.cnt[e] = c;
+  }
+  __syncthreads();
+  if (tid < 32) {
+    // warp scan over experts: lane handles ceil(E/32) consecutive experts
+    const int per = (E + 31) / 32;
+    int rows = 0, tl = 0;
+    for (int i = 0; i < per; ++i) {
+      const int e = tid * per + i;
+      if (e < E) { rows += sm.cnt[e]; tl += (sm.cnt[e] + tile_rows - 1) / tile_rows; }
+    }
+    int rows_incl = rows, tl_incl = tl;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int a = __shfl_up_sync(0xffffffffu, rows_incl, o);
+      const int b = __shfl_up_sync(0xffffffffu, tl_incl, o);
+      if (tid >= o) { rows_incl += a; tl_incl += b; }
+    }
+    int roff = rows_incl - rows, toff = tl_incl - tl;
+    for (int i = 0; i < per; ++i) {
+      const int e = tid * per + i;
+      if (e < E) {
+        sm.off[e] = roff; sm.tile_off[e] = toff;
+        roff += sm.cnt[e]; toff += (sm.cnt[e] + tile_rows - 1) / tile_rows;
+      }
+    }
+    if (tid == 31) { sm.off[E] = rows_incl; sm.tile_off[E] = tl_incl; }
+  }
+  __syncthreads();
+  const int shared_tiles = (sh_hi - sh_lo + tile_rows - 1) / tile_rows;
+  const bool fits = sm.tile_off[E] + shared_tiles <= tile_capacity;
+  if (tid == 0) *num_tiles = fits ? sm.tile_off[E] + shared_tiles : 0;
+  for (int e = tid; e <= E; e += kTokPerBlock) expert_offsets[e] = sm.off[e];
+  if (fits) {
+    for (int e = tid; e < E; e += kTokPerBlock)
+      emit_tiles(tiles, sm.tile_off[e], e - e_lo, sm.off[e], sm.cnt[e], tile_rows);
+    if (tid == kTokPerBlock - 1)
+      emit_tiles(tiles, sm.tile_off[E], e_hi - e_lo, T * k + sh_lo, sh_hi - sh_lo, tile_rows);
+  }
+  if (tid < T) {
+    for (int s = 0; s < k; ++s) {
+      const size_t i = static_cast<size_t>(tid) * k + s;
+      const int e = idx[i];
+      int row = -1;
+      if (e >= e_lo && e < e_hi) {
+        const uint32_t* bm = &sm.bitmap[e * kWordsPerExpert];
+        int r = __popc(bm[word] & (bit - 1u));
+        for (int wd = 0; wd < word; ++wd) r += __popc(bm[wd]);
+        row = sm.off[e] + r;
+        row_token[row] = tid;
+        row_weight[row] = w[i];
+      }
+      slot_row[i] = row;
+    }
+  }
+}
+
+}  // namespace glm4moe

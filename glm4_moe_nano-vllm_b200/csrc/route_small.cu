@@ -1,0 +1,143 @@
+// Fused decode front-end (T <= 32): router logits + expert selection + permutation in ONE launch.
+//
+// Replaces GlmMoeSelectTopk.forward (reference moe.py:28-50) and the mask / where loop bookkeeping
+// (moe.py:135-144) for decode-size batches, where three separate launches cost more than their
+// work.  Grid = (E/EB) x (T/TT) blocks compute the logits exactly as router_logits_small_kernel
+// (8 warps split K, fixed-order fp32 accumulate, one rounding to the model dtype); every block then
+// takes a ticket, and the LAST block to finish selects the experts of all T tokens (one warp per
+// token) and builds the permutation / work list in place (single-block path of permute.cu).
+// Arithmetic and tie rule are the stand-alone kernels' (same device functions): bit-identical.
+#include "common.cuh"
+#include "route_device.cuh"
+
+namespace glm4moe {
+
+template <typename T, int TT, int EB>
+__global__ void __launch_bounds__(256) route_small_kernel(
+    const T* __restrict__ h, const T* __restrict__ gate_w, const float* __restrict__ bias, T* logits, int Tn,
+    int H, int E, int k, float scale, int e_lo, int e_hi, int tile_rows, int sh_lo, int sh_hi, int32_t* idx,
+    float* w, int32_t* __restrict__ expert_offsets, int32_t* __restrict__ row_token,
+    float* __restrict__ row_weight, int32_t* __restrict__ slot_row, int4* __restrict__ tiles, int tile_capacity,
+    int32_t* __restrict__ num_tiles, int32_t* __restrict__ ticket) {
+  constexpr int V = Dt<T>::kVec;
+  __shared__ float part[8][TT * EB];
+  __shared__ PermuteSmallSmem psm;
+  __shared__ int s_last;
+  // first kernel of the layer: the input must be complete before anything reads it; the dependants
+  // (expert GEMMs) may start their own prologue right away
+  pdl_wait();
+  pdl_launch();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int e0 = blockIdx.x * EB, t0 = blockIdx.y * TT;
+  const int nvec = H / V;
+  float acc[TT][EB];
+#pragma unroll
+  for (int i = 0; i < TT; ++i)
+#pragma unroll
+    for (int j = 0; j < EB; ++j) acc[i][j] = 0.f;
+  for (int c = threadIdx.x; c < nvec; c += 256) {
+    float wv[EB][V], xv[TT][V];
+#pragma unroll
+    for (int j = 0; j < EB; ++j) {
+      const int e = min(e0 + j, E - 1);
+      unpack16<T>(ld_cached16(reinterpret_cast<const uint4*>(gate_w + static_cast<size_t>(e) * H) + c), wv[j]);
+    }
+#pragma unroll
+    for (int i = 0; i < TT; ++i) {
+      const int t = min(t0 + i, Tn - 1);
+      unpack16<T>(ld_cached16(reinterpret_cast<const uint4*>(h + static_cast<size_t>(t) * H) + c), xv[i]);
+    }
+#pragma unroll
+    for (int i = 0; i < TT; ++i)
+#pragma unroll
+      for (int j = 0; j < EB; ++j)
+#pragma unroll
+        for (int q = 0; q < V; ++q) acc[i][j] = fmaf(xv[i][q], wv[j][q], acc[i][j]);
+  }
+#pragma unroll
+  for (int i = 0; i < TT; ++i)
+#pragma unroll
+    for (int j = 0; j < EB; ++j) {
+      const float s = warp_sum(acc[i][j]);
+      if (lane == 0) part[warp][i * EB + j] = s;
+    }
+  __syncthreads();
+  if (threadIdx.x < TT * EB) {
+    float s = 0.f;
+#pragma unroll
+    for (int wdx = 0; wdx < 8; ++wdx) s += part[wdx][threadIdx.x];
+    const int t = t0 + threadIdx.x / EB, e = e0 + threadIdx.x % EB;
+    if (t < Tn && e < E) logits[static_cast<size_t>(t) * E + e] = Dt<T>::from_f(s);
+    __threadfence();
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const int total = static_cast<int>(gridDim.x * gridDim.y);
+    const int prev = atomicAdd(ticket, 1);
+    s_last = prev == total - 1;
+    if (s_last) *ticket = 0;   // re-armed for the next launch (graph replay safe)
+  }
+  for (int i = threadIdx.x; i < E * kWordsPerExpert; i += 256) psm.bitmap[i] = 0u;
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  // ---- last block: select (warp per token), then the single-block permutation ----
+  for (int t = warp; t < Tn; t += 8)
+    select_token<T>(logits + static_cast<size_t>(t) * E, bias, E, k, scale, lane, idx + static_cast<size_t>(t) * k,
+                    w + static_cast<size_t>(t) * k);
+  __syncthreads();   // idx / w of this block's own global writes are visible to the block
+  permute_small_body(psm, idx, w, Tn, k, E, e_lo, e_hi, tile_rows, sh_lo, sh_hi, expert_offsets, row_token,
+                     row_weight, slot_row, tiles, tile_capacity, num_tiles);
+}
+
+template <typename T>
+static int launch_route_small(const void* h, const void* gw, const float* bias, void* logits, int T_, int H, int E,
+                              int k, float scale, int e_lo, int e_hi, int tile_rows, int sh_lo, int sh_hi,
+                              int32_t* idx, float* w, int32_t* offsets, int32_t* row_token, float* row_weight,
+                              int32_t* slot_row, int32_t* tiles, int tile_capacity, int32_t* num_tiles,
+                              int32_t* ticket, cudaStream_t st) {
+  constexpr int V = Dt<T>::kVec;
+  if (H % V != 0) return GLM4MOE_ERR_UNSUPPORTED;
+  if (T_ <= 2) {
+    dim3 grid((E + 3) / 4, (T_ + 1) / 2);
+    GLM4MOE_CUDA_CHECK(launch_pdl(route_small_kernel<T, 2, 4>, grid, dim3(256), 0, st, static_cast<const T*>(h),
+                                  static_cast<const T*>(gw), bias, static_cast<T*>(logits), T_, H, E, k, scale, e_lo,
+                                  e_hi, tile_rows, sh_lo, sh_hi, idx, w, offsets, row_token, row_weight, slot_row,
+                                  reinterpret_cast<int4*>(tiles), tile_capacity, num_tiles, ticket));
+  } else {
+    dim3 grid((E + 3) / 4, (T_ + 3) / 4);
+    GLM4MOE_CUDA_CHECK(launch_pdl(route_small_kernel<T, 4, 4>, grid, dim3(256), 0, st, static_cast<const T*>(h),
+                                  static_cast<const T*>(gw), bias, static_cast<T*>(logits), T_, H, E, k, scale, e_lo,
+                                  e_hi, tile_rows, sh_lo, sh_hi, idx, w, offsets, row_token, row_weight, slot_row,
+                                  reinterpret_cast<int4*>(tiles), tile_capacity, num_tiles, ticket));
+  }
+  return GLM4MOE_OK;
+}
+
+}  // namespace glm4moe
+
+using namespace glm4moe;
+
+extern "C" int glm4moe_route_small(const void* h, const void* gate_w, const float* bias, void* logits, int T, int H,
+                                   int E, int k, float scale, int dtype, int e_lo, int e_hi, int tile_rows,
+                                   int shared_lo, int shared_hi, int32_t* idx, float* w, int32_t* expert_offsets,
+                                   int32_t* row_token, float* row_weight, int32_t* slot_row, int32_t* tiles,
+                                   int32_t tile_capacity, int32_t* num_tiles, int32_t* ticket, void* stream) {
+  if (!h || !gate_w || !bias || !logits || !idx || !w || !expert_offsets || !row_token || !row_weight ||
+      !slot_row || !tiles || !num_tiles || !ticket)
+    return GLM4MOE_ERR_ARG;
+  if (T <= 0 || T > GLM4MOE_ROUTE_SMALL_MAX_TOKENS || H <= 0) return GLM4MOE_ERR_ARG;
+  if (E <= 0 || E > kMaxExperts || E > 32 * kMaxSlots || k <= 0 || k > kMaxTopK || k > E)
+    return GLM4MOE_ERR_UNSUPPORTED;
+  if (tile_rows <= 0 || e_lo < 0 || e_hi > E || e_lo > e_hi || shared_lo < 0 || shared_hi > T ||
+      shared_lo > shared_hi)
+    return GLM4MOE_ERR_ARG;
+  if (tile_capacity < glm4moe_tile_capacity(T, k, E, tile_rows)) return GLM4MOE_ERR_WORKSPACE;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  GLM4MOE_DISPATCH_DTYPE(dtype, T_,
+                         return launch_route_small<T_>(h, gate_w, bias, logits, T, H, E, k, scale, e_lo, e_hi,
+                                                       tile_rows, shared_lo, shared_hi, idx, w, expert_offsets,
+                                                       row_token, row_weight, slot_row, tiles, tile_capacity,
+                                                       num_tiles, ticket, st));
+  return GLM4MOE_OK;
+}

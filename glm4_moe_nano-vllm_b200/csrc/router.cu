@@ -7,6 +7,7 @@
 //                         "higher score, then lower expert id" (moe.py:39), un-biased gather,
 //                         renormalise and scale with the reference's roundings (moe.py:41-46).
 #include "common.cuh"
+#include "route_device.cuh"
 
 namespace glm4moe {
 
@@ -114,9 +115,6 @@ __global__ void __launch_bounds__(256) router_logits_small_kernel(const T* __res
 // ---------------------------------------------------------------------------------------------
 // select: one warp per token, expert e = j*32 + lane held in register slot j (E <= 256).
 // ---------------------------------------------------------------------------------------------
-constexpr int kMaxSlots = 8;   // E <= 256
-constexpr int kMaxTopK = 32;
-
 template <typename T>
 __global__ void __launch_bounds__(128) router_select_kernel(const T* __restrict__ logits,
                                                             const float* __restrict__ bias, int Tn,
@@ -128,68 +126,8 @@ __global__ void __launch_bounds__(128) router_select_kernel(const T* __restrict_
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int t = blockIdx.x * 4 + warp;
   if (t >= Tn) return;
-  float choice[kMaxSlots], score[kMaxSlots];
-#pragma unroll
-  for (int j = 0; j < kMaxSlots; ++j) {
-    const int e = j * 32 + lane;
-    if (e < E) {
-      const float lg = Dt<T>::to_f(logits[static_cast<size_t>(t) * E + e]);
-      const float s = Dt<T>::round(sigmoid_f(lg));       // moe.py:37, model dtype
-      score[j] = s;
-      choice[j] = s + bias[e];                           // moe.py:38, fp32
-    } else {
-      score[j] = 0.f;
-      choice[j] = -INFINITY;
-    }
-  }
-  // k rounds of arg-max; ties -> lower expert id (lane-local scan is ascending in e for fixed
-  // lane, the cross-lane reduction compares (value, id) lexicographically).
-  int my_e = -1;          // lane r keeps the r-th pick
-  float my_s = 0.f;
-  unsigned taken = 0;     // bit j set: my slot j already picked
-  for (int r = 0; r < k; ++r) {
-    float bv = -INFINITY;
-    int be = 0x7fffffff;
-#pragma unroll
-    for (int j = 0; j < kMaxSlots; ++j) {
-      const int e = j * 32 + lane;
-      if (e < E && !((taken >> j) & 1u) && (choice[j] > bv || be == 0x7fffffff)) {
-        bv = choice[j];
-        be = e;
-      }
-    }
-    float bs = 0.f;
-#pragma unroll
-    for (int j = 0; j < kMaxSlots; ++j)
-      if (be == j * 32 + lane) bs = score[j];
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
-      const int oe = __shfl_xor_sync(0xffffffffu, be, o);
-      const float os = __shfl_xor_sync(0xffffffffu, bs, o);
-      if (oe != 0x7fffffff && (be == 0x7fffffff || ov > bv || (ov == bv && oe < be))) {
-        bv = ov; be = oe; bs = os;
-      }
-    }
-    if ((be & 31) == lane) taken |= 1u << (be >> 5);
-    if (lane == r) { my_e = be; my_s = bs; }
-  }
-  // renormalise: sum in fp32 over the k picks, every intermediate rounded to the model dtype
-  float sum = 0.f;
-  for (int r = 0; r < k; ++r) sum += __shfl_sync(0xffffffffu, my_s, r);
-  const float denom = Dt<T>::round(Dt<T>::round(sum) + 1e-20f);   // moe.py:43
-  float wgt = Dt<T>::round(my_s / denom);                          // moe.py:44
-  wgt = Dt<T>::round(wgt * scale);                                 // moe.py:46
-  // canonical slot order: ascending expert id (the order the reference accumulates in)
-  int rank = 0;
-  for (int r = 0; r < k; ++r) {
-    const int oe = __shfl_sync(0xffffffffu, my_e, r);
-    rank += (lane < k && oe < my_e) ? 1 : 0;
-  }
-  if (lane < k) {
-    idx_out[static_cast<size_t>(t) * k + rank] = my_e;
-    w_out[static_cast<size_t>(t) * k + rank] = wgt;
-  }
+  select_token<T>(logits + static_cast<size_t>(t) * E, bias, E, k, scale, lane,
+                  idx_out + static_cast<size_t>(t) * k, w_out + static_cast<size_t>(t) * k);
 }
 
 template <typename T>

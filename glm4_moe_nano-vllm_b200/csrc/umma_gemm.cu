@@ -57,6 +57,7 @@ struct UmmaCfg {
 // ------------------------------------------------------------------------------------------
 // the kernel
 // ------------------------------------------------------------------------------------------
+constexpr int kSharedWorkBase = 1 << 30;   // direct mode: work id of the shared expert's feature tile f
 constexpr int kSchedDepth = 4;   // work-index queue between the producer and the consumer warps
 
 template <typename T, int BN, int MODE>
@@ -69,7 +70,8 @@ __global__ void __launch_bounds__(UmmaCfg<BN, MODE>::kThreads, 1) umma_grouped_k
     int n_routed_rows, int n_feat_tiles, int n_feat_valid, int n_kblocks,
     int w_rows_per_expert,                      // gated: 2I, down: H, plain: 0
     int up_row_offset,                          // gated: I
-    int32_t* __restrict__ sched) {              // [0] next work index - gridDim, [1] CTAs finished
+    int32_t* __restrict__ sched,                // [0] next work index - gridDim, [1] CTAs finished
+    const DirectArgs direct) {                  // decode "direct" mode (tokens > 0), see umma_gemm.cuh
   using Cfg = UmmaCfg<BN, MODE>;
   constexpr bool GATED = Cfg::kGated;
   constexpr int AS = Cfg::kAccStages;
@@ -129,7 +131,7 @@ __global__ void __launch_bounds__(UmmaCfg<BN, MODE>::kThreads, 1) umma_grouped_k
   if (warp == 0) {
     // ===================== TMA producer + dynamic tile scheduler =====================
     if (elect_one()) {
-      const int n_tiles = tiles ? *num_tiles_ptr : (dense_rows + BN - 1) / BN;
+      const int n_tiles = direct.tokens > 0 ? 0 : tiles ? *num_tiles_ptr : (dense_rows + BN - 1) / BN;
       const int total_work = n_tiles * n_feat_tiles;
       int n_pushed = 0;
       bool first = true;
@@ -149,6 +151,7 @@ __global__ void __launch_bounds__(UmmaCfg<BN, MODE>::kThreads, 1) umma_grouped_k
         return w;
       };
       WorkRef wr{0, 0, 0, 0};
+      const bool is_direct = direct.tokens > 0;
       auto issue = [&](int kb, int stage, bool do_w, bool do_x) {
         unsigned char* sa = smem + stage * Cfg::kStageBytes;
         if (do_w) {
@@ -159,9 +162,52 @@ __global__ void __launch_bounds__(UmmaCfg<BN, MODE>::kThreads, 1) umma_grouped_k
             tma_load_2d(&tm_w, &full_bar[stage], sa + Cfg::kABytes, kb * kBK, w_row + up_row_offset, kEvictFirst);
         }
         if (do_x)
-          tma_load_2d(&tm_x, &full_bar[stage], sa + (GATED ? 2 : 1) * Cfg::kABytes, kb * kBK, wr.row_start,
-                      kEvictLast);
+          tma_load_2d(&tm_x, &full_bar[stage], sa + (GATED ? 2 : 1) * Cfg::kABytes, kb * kBK,
+                      is_direct ? 0 : wr.row_start, kEvictLast);
       };
+      if (is_direct) {
+        // Decode "direct" mode: the token tile is the layer input itself (all T <= BN tokens are the
+        // MMA columns of every expert), so nothing here depends on the routing except WHICH experts
+        // run.  The shared expert's feature tiles therefore stream before the dependency wait,
+        // overlapping the router; the routed items come from the global counter afterwards.
+        int stage = 0;
+        uint32_t phase = 0;
+        auto stream_item = [&]() {
+          for (int kb = 0; kb < n_kblocks; ++kb) {
+            mbar_wait(&empty_bar[stage], phase ^ 1u);
+            issue(kb, stage, true, true);
+            if (++stage == Cfg::kStages) { stage = 0; phase ^= 1u; }
+          }
+        };
+        auto push = [&](int w, int nt) {
+          const int q = n_pushed % kSchedDepth;
+          mbar_wait(&sched_empty[q], ((n_pushed / kSchedDepth) & 1u) ^ 1u);
+          sched_w[2 * q] = w;
+          sched_w[2 * q + 1] = nt;
+          mbar_arrive(&sched_full[q]);
+          ++n_pushed;
+        };
+        const int n_sh_items = direct.sh_hi > direct.sh_lo ? n_feat_tiles : 0;
+        for (int f = blockIdx.x; f < n_sh_items; f += gridDim.x) {
+          wr = WorkRef{direct.shared_expert, 0, 0, f};
+          push(kSharedWorkBase + f, 0);
+          stream_item();
+        }
+        pdl_wait();
+        pdl_launch();
+        const int n_routed_tiles = *num_tiles_ptr - (n_sh_items ? 1 : 0);
+        const int total_routed = n_routed_tiles * n_feat_tiles;
+        for (;;) {
+          const int w = atomicAdd(&sched[0], 1);
+          if (w >= total_routed) {
+            push(-1, 0);
+            break;
+          }
+          push(w, n_routed_tiles);
+          wr = get_work<BN>(tiles, w, n_feat_tiles, n_routed_tiles, 0);
+          stream_item();
+        }
+      } else {
       int w = fetch_push();
       if (w >= 0) wr = get_work<BN>(tiles, w, n_feat_tiles, n_tiles, dense_rows);
       // (1) Before the dependency wait: weight tiles of the first item for the first pass over
@@ -190,6 +236,7 @@ __global__ void __launch_bounds__(UmmaCfg<BN, MODE>::kThreads, 1) umma_grouped_k
         ++kb;
         if (++stage == Cfg::kStages) { stage = 0; phase ^= 1u; }
       }
+      }
       // last CTA out re-arms the counters for the next launch
       __threadfence();
       if (atomicAdd(&sched[1], 1) == static_cast<int>(gridDim.x) - 1) {
@@ -207,10 +254,15 @@ __global__ void __launch_bounds__(UmmaCfg<BN, MODE>::kThreads, 1) umma_grouped_k
       int n_tiles;
       const int w = next_work(it, n_tiles);
       if (w < 0) break;
-      const WorkRef wr = get_work<BN>(tiles, w, n_feat_tiles, n_tiles, dense_rows);
       // MMA N follows the rows this tile really holds (multiple of 16): a ragged tail tile of an
-      // expert costs tensor time in proportion to its rows, not to BN.
-      const int n_eff = min(BN, (wr.nrows + 15) & ~15);
+      // expert costs tensor time in proportion to its rows, not to BN.  Direct mode: all T tokens.
+      int n_eff;
+      if (direct.tokens > 0) {
+        n_eff = min(BN, (direct.tokens + 15) & ~15);
+      } else {
+        const WorkRef wr = get_work<BN>(tiles, w, n_feat_tiles, n_tiles, dense_rows);
+        n_eff = min(BN, (wr.nrows + 15) & ~15);
+      }
       const uint32_t idesc = idesc_base | (static_cast<uint32_t>(n_eff >> 3) << 17);
       const int as = AS == 2 ? (it & 1) : 0;
       const uint32_t aphase = AS == 2 ? ((it >> 1) & 1u) : (it & 1u);
@@ -246,11 +298,29 @@ __global__ void __launch_bounds__(UmmaCfg<BN, MODE>::kThreads, 1) umma_grouped_k
     const int chunk0 = (warp - 4) >> 2;           // 0, or 1 for the second warp of a quadrant
     constexpr int kChunkStep = 16 * (EW / 4);
     const uint32_t lane_base = static_cast<uint32_t>(ew * 32) << 16;
+    bool dep_waited = false;
     for (int it = 0;; ++it) {
       int n_tiles;
       const int w = next_work(it, n_tiles);
       if (w < 0) break;
-      const WorkRef wr = get_work<BN>(tiles, w, n_feat_tiles, n_tiles, dense_rows);
+      WorkRef wr;
+      int tok_lane = -1;     // direct mode: token (= MMA column) held by row (row_start + lane) of this item
+      if (MODE == kModeGated && direct.tokens > 0) {
+        if (w >= kSharedWorkBase) {
+          wr = WorkRef{direct.shared_expert, direct.shared_row0 + direct.sh_lo, direct.sh_hi - direct.sh_lo,
+                       w - kSharedWorkBase};
+          if (lane < wr.nrows) tok_lane = direct.sh_lo + lane;
+        } else {
+          if (!dep_waited) {   // the work list and row_token are the direct predecessor's output
+            pdl_wait();
+            dep_waited = true;
+          }
+          wr = get_work<BN>(tiles, w, n_feat_tiles, n_tiles, 0);
+          if (lane < wr.nrows) tok_lane = __ldcg(direct.row_token + wr.row_start + lane);
+        }
+      } else {
+        wr = get_work<BN>(tiles, w, n_feat_tiles, n_tiles, dense_rows);
+      }
       const int as = AS == 2 ? (it & 1) : 0;
       const uint32_t aphase = AS == 2 ? ((it >> 1) & 1u) : (it & 1u);
       mbar_wait(&tmem_full[as], aphase);
@@ -260,19 +330,32 @@ __global__ void __launch_bounds__(UmmaCfg<BN, MODE>::kThreads, 1) umma_grouped_k
       const bool feat_ok = MODE != kModePlain || feat < n_feat_valid;
       T* out_col = out + static_cast<size_t>(wr.row_start) * ld_out + feat;
 #pragma unroll 1
+      const int n_cols = (MODE == kModeGated && direct.tokens > 0) ? direct.tokens : wr.nrows;
       for (int c0 = 16 * chunk0; c0 < BN; c0 += kChunkStep) {
-        if (c0 >= wr.nrows) break;              // warp-uniform: remaining token columns unused
+        if (c0 >= n_cols) break;                // warp-uniform: remaining token columns unused
         uint32_t g[16];
         tmem_ld16(t_acc + c0, g);
         if (MODE == kModeGated) {
           uint32_t u[16];
           tmem_ld16(t_acc + BN + c0, u);
           tmem_ld_wait();
+          if (direct.tokens > 0) {
+            // column = token; its output row inside this expert is the lane that holds the token
 #pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            if (c0 + j < wr.nrows) {
-              const float v = silu_fast(__uint_as_float(g[j])) * __uint_as_float(u[j]);
-              out_col[static_cast<size_t>(c0 + j) * ld_out] = Dt<T>::from_f(v);
+            for (int j = 0; j < 16; ++j) {
+              const uint32_t m = __ballot_sync(0xffffffffu, tok_lane == c0 + j);
+              if (m) {
+                const float v = silu_fast(__uint_as_float(g[j])) * __uint_as_float(u[j]);
+                out_col[static_cast<size_t>(__ffs(m) - 1) * ld_out] = Dt<T>::from_f(v);
+              }
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              if (c0 + j < wr.nrows) {
+                const float v = silu_fast(__uint_as_float(g[j])) * __uint_as_float(u[j]);
+                out_col[static_cast<size_t>(c0 + j) * ld_out] = Dt<T>::from_f(v);
+              }
             }
           }
         } else if (MODE == kModeDown) {
@@ -361,7 +444,7 @@ static int launch_one(const UmmaLaunch& a, cudaStream_t st) {
       kern, dim3(a.grid), dim3(Cfg::kThreads), Cfg::kSmemBytes, st, *static_cast<const CUtensorMap*>(a.tm_w),
       *static_cast<const CUtensorMap*>(a.tm_x), reinterpret_cast<const int4*>(a.tiles), a.num_tiles, a.dense_rows,
       static_cast<T*>(a.out), a.ld_out, a.row_weight, a.n_routed_rows, a.n_feat_tiles, a.n_feat_valid, a.n_kblocks,
-      a.w_rows_per_expert, a.up_row_offset, a.sched));
+      a.w_rows_per_expert, a.up_row_offset, a.sched, a.direct));
   return GLM4MOE_OK;
 }
 

@@ -4,6 +4,19 @@
 
 namespace glm4moe {
 
+// Decode "direct" mode of the gate_up GEMM (T <= tile_rows <= 32): the MMA token tile is the layer
+// input x itself (tm_x maps x, every token is a column of every expert's MMA), so no gathered copy of
+// the token rows exists; the epilogue writes column t of expert e to the expert-major row that
+// row_token assigns it.  The shared expert's items do not depend on the routing and run before the
+// programmatic dependency wait.  tokens == 0: off.
+struct DirectArgs {
+  int tokens;                // T
+  int shared_expert;         // stack index of the shared expert's weights
+  int shared_row0;           // T*k: first shared-expert row of the row space
+  int sh_lo, sh_hi;          // tokens the shared expert is applied to
+  const int32_t* row_token;  // [T*k] token of every routed row
+};
+
 struct UmmaLaunch {
   const void* tm_w;        // CUtensorMap (128 bytes) over the stacked weights
   const void* tm_x;        // CUtensorMap over the activation rows, box rows == tile_rows
@@ -24,6 +37,7 @@ struct UmmaLaunch {
   int dtype;
   int grid;
   int32_t* sched;          // 2 zero-initialised ints owned by this launch site (self re-arming)
+  DirectArgs direct;       // gate_up only
 };
 
 // 2-D row-major [rows, cols] two-byte tensor, box {64 cols, box_rows}, 128B swizzle.

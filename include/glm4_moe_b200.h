@@ -54,6 +54,11 @@ typedef struct glm4moe_config {
 typedef struct glm4moe_layer glm4moe_layer_t;   /* opaque */
 
 int glm4moe_abi_version(void);
+/* Process-wide tuning / test knobs (parity tests compare the paths against each other).
+ * GLM4MOE_KNOB_DIRECT: 1 (default) = decode batches T <= 32 use the fused front-end and read the
+ * input tokens in place; 0 = always the general router / permute / gather sequence.            */
+enum { GLM4MOE_KNOB_DIRECT = 0 };
+int glm4moe_debug_set(int knob, int value);
 const char* glm4moe_error_string(int code);
 
 /* ---- router: replaces GlmMoeSelectTopk.forward (moe.py:28-50) ------------------------------ */
@@ -65,6 +70,17 @@ int glm4moe_router_logits(const void* h, const void* gate_w, void* logits, int T
  * idx[T,k] int32, slots sorted by ascending expert id; w[T,k] fp32 holding model-dtype values. */
 int glm4moe_router_select(const void* logits, const float* bias, int T, int E, int k, float scale,
                           int dtype, int32_t* idx, float* w, void* stream);
+
+/* Decode front-end, T <= GLM4MOE_ROUTE_SMALL_MAX_TOKENS: glm4moe_router_logits + glm4moe_router_select +
+ * glm4moe_permute in ONE launch with bit-identical results (the last block to finish its logits runs
+ * the selection and the permutation).  `ticket`: one zero-initialised int32 owned by the call site
+ * (left at zero).  Replaces moe.py:28-50 and the bookkeeping of moe.py:135-144 at decode sizes.     */
+#define GLM4MOE_ROUTE_SMALL_MAX_TOKENS 64
+int glm4moe_route_small(const void* h, const void* gate_w, const float* bias, void* logits, int T, int H,
+                        int E, int k, float scale, int dtype, int e_lo, int e_hi, int tile_rows,
+                        int shared_lo, int shared_hi, int32_t* idx, float* w, int32_t* expert_offsets,
+                        int32_t* row_token, float* row_weight, int32_t* slot_row, int32_t* tiles,
+                        int32_t tile_capacity, int32_t* num_tiles, int32_t* ticket, void* stream);
 
 /* ---- permutation: replaces the mask / where / gather loop (moe.py:135-147) ------------------ */
 /* Stable expert-major order of the (token, slot) pairs whose expert is in [e_lo, e_hi).

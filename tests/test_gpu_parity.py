@@ -308,8 +308,84 @@ def test_cuda_graph_capture_and_host_entry():
     # host-buffer entry point == device entry point
     out_host = moe.forward_host(x.pin_memory())
     assert torch.equal(out_host, eager.cpu())
-    assert moe.last_launches == 7      # logits, select, permute, gather, gate_up, down, combine
+    assert moe.last_launches == 4      # fused route (logits+select+permute), gate_up, down, combine
 
+
+
+# ------------------------------------------------------------------------------------------
+# decode front-end: one fused launch == the three stand-alone kernels; direct mode == general path
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("T,shape_name,dt", [(1, "glm-4.5-air", torch.bfloat16), (7, "glm-4.5-air", torch.bfloat16),
+                                             (32, "glm-4.5-air", torch.bfloat16), (33, "mini", torch.float16),
+                                             (64, "glm-4.5", torch.bfloat16), (5, "tiny", torch.float32)])
+def test_route_small_bit_identical_to_separate_kernels(T, shape_name, dt):
+    lib = _lib.load()
+    shape = synth.SHAPES[shape_name]
+    gate_w, bias = synth.make_router_weights(shape, dt)
+    x = synth.make_tokens(shape, T, dt, 40 + T).cuda()
+    gate_w, bias = gate_w.cuda(), bias.cuda()
+    E, k, H, tr = shape.E, shape.k, shape.H, 16 if T <= 16 else 32
+    cap = lib.glm4moe_tile_capacity(T, k, E, tr)
+    code = _lib.DTYPE_CODE[dt]
+    e_lo, e_hi, sh_lo, sh_hi = E // 4, E, 0, T   # also exercises the expert-parallel filter
+
+    def bufs():
+        return dict(logits=torch.zeros((T, E), dtype=dt, device="cuda"),
+                    idx=torch.zeros((T, k), dtype=torch.int32, device="cuda"),
+                    w=torch.zeros((T, k), dtype=torch.float32, device="cuda"),
+                    off=torch.zeros(E + 1, dtype=torch.int32, device="cuda"),
+                    rt=torch.full((T * k,), -7, dtype=torch.int32, device="cuda"),
+                    rw=torch.zeros(T * k, dtype=torch.float32, device="cuda"),
+                    sr=torch.zeros(T * k, dtype=torch.int32, device="cuda"),
+                    tiles=torch.zeros((cap, 4), dtype=torch.int32, device="cuda"),
+                    nt=torch.zeros(4, dtype=torch.int32, device="cuda"))
+    a, b = bufs(), bufs()
+    st = _lib.stream_ptr()
+    _lib.check(lib.glm4moe_router_logits(x.data_ptr(), gate_w.data_ptr(), a["logits"].data_ptr(), T, H, E, code, st))
+    _lib.check(lib.glm4moe_router_select(a["logits"].data_ptr(), bias.data_ptr(), T, E, k, shape.routed_scaling_factor,
+                                         code, a["idx"].data_ptr(), a["w"].data_ptr(), st))
+    scr = torch.empty(lib.glm4moe_permute_scratch_elems(T, E), dtype=torch.int32, device="cuda")
+    _lib.check(lib.glm4moe_permute(a["idx"].data_ptr(), a["w"].data_ptr(), T, k, E, e_lo, e_hi, tr, sh_lo, sh_hi,
+                                   a["off"].data_ptr(), a["rt"].data_ptr(), a["rw"].data_ptr(), a["sr"].data_ptr(),
+                                   a["tiles"].data_ptr(), cap, a["nt"].data_ptr(), scr.data_ptr(), st))
+    ticket = torch.zeros(4, dtype=torch.int32, device="cuda")
+    for _ in range(2):   # twice: the ticket re-arms itself
+        _lib.check(lib.glm4moe_route_small(x.data_ptr(), gate_w.data_ptr(), bias.data_ptr(), b["logits"].data_ptr(), T, H,
+                                           E, k, shape.routed_scaling_factor, code, e_lo, e_hi, tr, sh_lo, sh_hi,
+                                           b["idx"].data_ptr(), b["w"].data_ptr(), b["off"].data_ptr(),
+                                           b["rt"].data_ptr(), b["rw"].data_ptr(), b["sr"].data_ptr(),
+                                           b["tiles"].data_ptr(), cap, b["nt"].data_ptr(), ticket.data_ptr(), st))
+    torch.cuda.synchronize()
+    assert int(ticket[0]) == 0
+    n_rows = int(a["off"][E])
+    for name in ("logits", "idx", "w", "off", "sr", "nt"):
+        assert torch.equal(a[name], b[name]), name
+    assert torch.equal(a["rt"][:n_rows], b["rt"][:n_rows]) and torch.equal(a["rw"][:n_rows], b["rw"][:n_rows])
+    nt = int(a["nt"][0])
+    assert nt > 0 and torch.equal(a["tiles"][:nt], b["tiles"][:nt])
+
+
+@pytest.mark.parametrize("shape_name,Ts", [("mini", (1, 5, 16, 17, 32)), ("glm-4.5-air", (1, 2, 13, 32))])
+def test_direct_mode_bit_identical_to_general_path(shape_name, Ts):
+    """T <= 32 runs the fused front-end and feeds the input tokens to the gate_up MMA in place
+    (no gathered copy); the general path must give the same bits (same K order per output)."""
+    lib = _lib.load()
+    shape, dt = synth.SHAPES[shape_name], torch.bfloat16
+    moe = _module(shape, dt, synth.make_weights(shape, dt), max_tokens=64)
+    try:
+        for T in Ts:
+            x = synth.make_tokens(shape, T, dt, 900 + T).cuda()
+            _lib.check(lib.glm4moe_debug_set(0, 1))
+            a = moe(x).clone()
+            assert moe.last_launches == 4
+            ia = moe.workspace_view("idx", T).clone()
+            _lib.check(lib.glm4moe_debug_set(0, 0))
+            b = moe(x).clone()
+            assert moe.last_launches == 7
+            assert torch.equal(ia, moe.workspace_view("idx", T))
+            assert torch.equal(a, b), f"T={T}: direct and general paths differ"
+    finally:
+        lib.glm4moe_debug_set(0, 1)
 
 # ------------------------------------------------------------------------------------------
 # BASELINE configs[1]: GLM-4.5-Air shape, bf16
