@@ -21,6 +21,14 @@ constexpr int kBnChoices[kNumBn] = {16, 32, 64, 128, 256};
 constexpr int kRouterUmmaMinTokens = 64;   // below this the K-split CUDA-core router wins (latency)
 constexpr int kDirectMaxTokens = 32;       // decode "direct" mode (fused front-end, no gather): T <= this
 
+int g_fused = -1;    // decode_fused kernel inside direct mode; GLM4MOE_NO_FUSED=1 / glm4moe_debug_set(1, v)
+bool fused_enabled() {
+  if (g_fused < 0) {
+    const char* e = getenv("GLM4MOE_NO_FUSED");
+    g_fused = (e && e[0] == '1') ? 0 : 1;
+  }
+  return g_fused == 1;
+}
 int g_direct = -1;   // -1: read GLM4MOE_NO_DIRECT on first use; glm4moe_debug_set(0, v) overrides
 bool direct_enabled() {
   if (g_direct < 0) {
@@ -33,7 +41,7 @@ bool direct_enabled() {
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct WsLayout {
-  size_t logits, idx, w, offsets, row_token, row_weight, slot_row, num_tiles, sched, tiles, scratch, x_rows,
+  size_t logits, idx, w, offsets, row_token, row_weight, slot_row, num_tiles, sched, ready, fdone, tiles, scratch, x_rows,
       act, y, xq, sx, actq, sact, total;
   int tile_capacity;
 };
@@ -57,7 +65,9 @@ WsLayout make_layout(const glm4moe_config_t& c) {
   L.row_weight = take(T * k * 4);
   L.slot_row = take(T * k * 4);
   L.num_tiles = take(16);
-  L.sched = take(64);
+  L.sched = take(256);
+  L.fdone = take((H / 128 + 8) * 4);
+  L.ready = take((E + 8) * 4);   // decode_fused: gate_up completion counter per tile (<= E + 1 tiles)
   L.tile_capacity = glm4moe_tile_capacity(static_cast<int>(T), static_cast<int>(k), static_cast<int>(E),
                                           kSimtRows);
   L.tiles = take(static_cast<size_t>(L.tile_capacity) * 16);
@@ -117,6 +127,7 @@ bool pdl_enabled() {
 extern "C" int glm4moe_debug_set(int knob, int value) {
   switch (knob) {
     case GLM4MOE_KNOB_DIRECT: g_direct = value ? 1 : 0; return GLM4MOE_OK;
+    case GLM4MOE_KNOB_FUSED: g_fused = value ? 1 : 0; return GLM4MOE_OK;
     default: return GLM4MOE_ERR_ARG;
   }
 }
@@ -182,7 +193,9 @@ extern "C" int glm4moe_layer_create(const glm4moe_config_t* cfg, const void* gat
   l->last_launches = 0;
   l->last_impl = GLM4MOE_IMPL_AUTO;
   l->events_ready = false;
-  if (cudaMemset(l->ws + L.sched, 0, 64) != cudaSuccess) {
+  if (cudaMemset(l->ws + L.sched, 0, 256) != cudaSuccess ||
+      cudaMemset(l->ws + L.ready, 0, (cfg->n_routed_experts + 8) * 4) != cudaSuccess ||
+      cudaMemset(l->ws + L.fdone, 0, (cfg->hidden_size / 128 + 8) * 4) != cudaSuccess) {
     delete l;
     return GLM4MOE_ERR_DEVICE;
   }
@@ -322,13 +335,14 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
   const int launches0 = g_launches;
   int rc;
   alignas(64) CUtensorMap tm_xdirect;
+  bool combine_done = false;
   STAGE_MARK(0);
   if (direct) {
     if ((rc = umma_make_tensor_map(&tm_xdirect, x, c.dtype, static_cast<uint64_t>(T), H, tile_rows))) return rc;
     if ((rc = glm4moe_route_small(x, l->gate_w, l->bias, logits, T, H, E, k, c.routed_scaling_factor, c.dtype,
                                   c.expert_begin, c.expert_end, tile_rows, sh_lo, sh_hi, idx, w, offsets, row_token,
                                   row_weight, slot_row, tiles, L.tile_capacity, num_tiles,
-                                  reinterpret_cast<int32_t*>(ws + L.sched) + 8, stream)))
+                                  reinterpret_cast<int32_t*>(ws + L.sched) + 24, stream)))
       return rc;
     STAGE_MARK(1);
     STAGE_MARK(2);
@@ -423,6 +437,44 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
     a.gated = 0;
     a.sched = reinterpret_cast<int32_t*>(ws + L.sched) + 2;
     if ((rc = umma_fp8_launch(a, stream))) return rc;
+  } else if (direct && fused_enabled()) {
+    DecodeFusedLaunch f{};
+    f.tm_wgu = &l->tm_w_gu;
+    f.tm_wd = &l->tm_w_d;
+    f.tm_x = &tm_xdirect;
+    f.tm_act = &l->tm_act[bi];
+    f.tiles = tiles;
+    f.num_tiles = num_tiles;
+    f.row_token = row_token;
+    f.row_weight = row_weight;
+    f.act = act;
+    f.y = y;
+    f.H = H;
+    f.I = I;
+    f.tokens = T;
+    f.n_routed_rows = T * k;
+    f.shared_expert = c.expert_end - c.expert_begin;
+    f.sh_lo = sh_lo;
+    f.sh_hi = sh_hi;
+    f.tile_rows = tile_rows;
+    f.dtype = c.dtype;
+    f.grid = l->sm_count;
+    f.sched = reinterpret_cast<int32_t*>(ws + L.sched) + 16;
+    f.ready = reinterpret_cast<int32_t*>(ws + L.ready);
+    f.slot_row = slot_row;
+    f.out = out;
+    f.k = k;
+    f.fdone = reinterpret_cast<int32_t*>(ws + L.fdone);
+    {
+      const size_t es = dtype_size(c.dtype), n_local = static_cast<size_t>(c.expert_end - c.expert_begin);
+      f.pf0 = static_cast<const unsigned char*>(l->w_gate_up) + n_local * 2 * I * H * es;
+      f.pf0_bytes = static_cast<size_t>(2) * I * H * es;
+      f.pf1 = static_cast<const unsigned char*>(l->w_down) + n_local * H * I * es;
+      f.pf1_bytes = static_cast<size_t>(H) * I * es;
+    }
+    if ((rc = decode_fused_launch(f, stream))) return rc;
+    STAGE_MARK(5);
+    combine_done = true;
   } else if (use_umma) {
     UmmaLaunch a{};
     a.tiles = tiles;
@@ -479,7 +531,7 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
       return rc;
   }
   STAGE_MARK(6);
-  if ((rc = glm4moe_combine(y, slot_row, out, T, k, H, sh_lo, sh_hi, c.dtype, stream))) return rc;
+  if (!combine_done && (rc = glm4moe_combine(y, slot_row, out, T, k, H, sh_lo, sh_hi, c.dtype, stream))) return rc;
   STAGE_MARK(7);
 #undef STAGE_MARK
   l->last_launches = g_launches - launches0;

@@ -67,7 +67,11 @@ __global__ void __launch_bounds__(FusedCfg<BN>::kThreads, 1) decode_fused_kernel
     const int32_t* row_token, const float* row_weight, T* __restrict__ act, T* __restrict__ y, int H, int I,
     int tokens, int n_routed_rows, int shared_expert, int sh_lo, int sh_hi,
     int32_t* __restrict__ sched,                  // [0] queue head, [1] CTAs finished
-    int32_t* __restrict__ ready) {                // [1 + tile capacity] gate_up completion counters
+    int32_t* __restrict__ ready,                  // [1 + tile capacity] gate_up completion counters
+    const int32_t* slot_row, T* __restrict__ out, int k,
+    int32_t* __restrict__ fdone,                  // [H/128] down items finished per feature tile
+    const unsigned char* __restrict__ pf0, size_t pf0_bytes,    // shared expert's gate_up / down weights:
+    const unsigned char* __restrict__ pf1, size_t pf1_bytes) {  // pulled into L2 while the router runs
   using Cfg = FusedCfg<BN>;
   extern __shared__ unsigned char smem_dyn[];
   unsigned char* smem = reinterpret_cast<unsigned char*>(
@@ -81,13 +85,14 @@ __global__ void __launch_bounds__(FusedCfg<BN>::kThreads, 1) decode_fused_kernel
   uint64_t* q_empty = q_full + kFusedQueue;
   int32_t* q_w = reinterpret_cast<int32_t*>(q_empty + kFusedQueue);   // [depth][2]: work id, routed tiles
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(q_w + 2 * kFusedQueue);
+  int32_t* s_last = reinterpret_cast<int32_t*>(tmem_ptr_smem + 1);   // epilogue-warp broadcast slot
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int FG = I / kBM, FD = H / kBM;           // feature tiles of the two projections
   const int n_sh = sh_hi - sh_lo;
   const int has_shared = n_sh > 0 ? 1 : 0;
-  const int shared_row0 = tokens * (n_routed_rows / max(tokens, 1)) + sh_lo;   // T*k + sh_lo
+  const int shared_row0 = n_routed_rows + sh_lo;   // T*k + sh_lo
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tm_wgu);
@@ -118,6 +123,7 @@ __global__ void __launch_bounds__(FusedCfg<BN>::kThreads, 1) decode_fused_kernel
 
   // work id -> item.  ids: kSharedBase + f = phase S; [0, G) phase G; [G, G + D) phase D.
   constexpr int kSharedBase = 1 << 30;
+  constexpr int kZeroBase = 1 << 29;     // no local work at all: feature tile (w - kZeroBase) of `out` is zeroed
   auto decode = [&](int w, int n_routed) -> FusedItem {
     FusedItem it;
     if (w >= kSharedBase) {
@@ -152,8 +158,8 @@ __global__ void __launch_bounds__(FusedCfg<BN>::kThreads, 1) decode_fused_kernel
     if (lane == 0) mbar_arrive(&q_empty[q]);
     return w;
   };
-  const int atoms_gu = H / 64 * static_cast<int>(sizeof(T)) / 2;    // K atoms of gate_up (two-byte: H/64)
-  const int atoms_d = I / 64 * static_cast<int>(sizeof(T)) / 2;     // K atoms of down
+  const int atoms_gu = H / 64;    // K atoms (128 B = 64 two-byte elements) of gate_up
+  const int atoms_d = I / 64;     // K atoms of down
 
   if (warp == 0) {
     // ===================== TMA producer + scheduler =====================
@@ -229,7 +235,22 @@ __global__ void __launch_bounds__(FusedCfg<BN>::kThreads, 1) decode_fused_kernel
           advance();
         }
       };
-      // ---- phase S: before the dependency wait ----
+      // ---- before the dependency wait: the shared expert is always on.  Every CTA pulls its slice of
+      // the shared expert's 3*H*I weights into L2 (HBM would otherwise idle while the router runs;
+      // they fit the 126 MB L2 many times over), then phase S streams gate_up from there. ----
+      if (has_shared) {
+        constexpr size_t kChunk = 32768;
+        auto prefetch_slice = [&](const unsigned char* base, size_t bytes) {
+          const size_t n_chunks = (bytes + kChunk - 1) / kChunk;
+          for (size_t c = blockIdx.x; c < n_chunks; c += gridDim.x) {
+            const size_t off = c * kChunk;
+            const uint32_t sz = static_cast<uint32_t>(min(kChunk, bytes - off));
+            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(base + off), "r"(sz) : "memory");
+          }
+        };
+        prefetch_slice(pf0, pf0_bytes);
+        prefetch_slice(pf1, pf1_bytes);
+      }
       if (has_shared)
         for (int f = blockIdx.x; f < FG; f += gridDim.x) {
           push(kSharedBase + f, 0);
@@ -239,6 +260,8 @@ __global__ void __launch_bounds__(FusedCfg<BN>::kThreads, 1) decode_fused_kernel
       pdl_launch();
       const int n_routed = *num_tiles_ptr - has_shared;
       const int total = n_routed * FG + (n_routed + has_shared) * FD;
+      if (n_routed + has_shared == 0)   // expert-parallel rank without a hit expert: the partial output is zero
+        for (int f = blockIdx.x; f < FD; f += gridDim.x) push(kZeroBase + f, 0);
       for (;;) {
         const int w = atomicAdd(&sched[0], 1);
         if (w >= total) {
@@ -265,10 +288,11 @@ __global__ void __launch_bounds__(FusedCfg<BN>::kThreads, 1) decode_fused_kernel
     int stage = 0;
     uint32_t phase = 0;
     bool dep_waited = false;
-    for (int n = 0;; ++n) {
+    for (int qn = 0, n = 0;; ++qn) {
       int n_routed;
-      const int w = next_work(n, n_routed);
+      const int w = next_work(qn, n_routed);
       if (w < 0) break;
+      if (w >= kZeroBase && w < kSharedBase) continue;
       if (w < kSharedBase && !dep_waited) {   // decode() reads the work list: the direct predecessor's output
         pdl_wait();
         dep_waited = true;
@@ -312,16 +336,22 @@ __global__ void __launch_bounds__(FusedCfg<BN>::kThreads, 1) decode_fused_kernel
         __syncwarp();
         if (++stage == Cfg::kStages) { stage = 0; phase ^= 1u; }
       }
+      ++n;
     }
   } else if (warp >= 4) {
     // ===================== epilogue =====================
     const int ew = warp - 4;
     const uint32_t lane_base = static_cast<uint32_t>(ew * 32) << 16;
     bool dep_waited = false;
-    for (int n = 0;; ++n) {
+    for (int qn = 0, n = 0;; ++qn) {
       int n_routed;
-      const int w = next_work(n, n_routed);
+      const int w = next_work(qn, n_routed);
       if (w < 0) break;
+      if (w >= kZeroBase && w < kSharedBase) {
+        const int col = (w - kZeroBase) * kBM + 4 * lane;
+        for (int t = ew; t < tokens; t += 4) *reinterpret_cast<uint2*>(out + static_cast<size_t>(t) * H + col) = make_uint2(0u, 0u);
+        continue;
+      }
       if (w < kSharedBase && !dep_waited) {
         pdl_wait();
         dep_waited = true;
@@ -387,7 +417,44 @@ __global__ void __launch_bounds__(FusedCfg<BN>::kThreads, 1) decode_fused_kernel
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&tmem_empty[as]);
+        // ---- combine (moe.py:151,171), fused: the LAST down item of feature tile f sums, for every
+        // token, its k routed rows in ascending expert order + the shared row over these 128
+        // features.  Same order and single rounding as combine_kernel: bit-identical, no atomics on data.
+        __threadfence();
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (ew == 0 && lane == 0) {
+          const int done = atomicAdd(fdone + it.f, 1) + 1;
+          const int last = done == n_routed + has_shared;
+          if (last) fdone[it.f] = 0;          // re-armed for the next launch
+          *s_last = last;
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        const int last = *reinterpret_cast<volatile int32_t*>(s_last);
+        asm volatile("bar.sync 1, 128;" ::: "memory");   // slot may be rewritten by the next item
+        if (last) {
+          __threadfence();
+          const size_t col = static_cast<size_t>(it.f) * kBM + 4 * lane;
+          for (int t = ew; t < tokens; t += 4) {
+            float acc[4] = {0.f, 0.f, 0.f, 0.f};
+            auto add_row = [&](int r) {
+              const uint2 raw = __ldcg(reinterpret_cast<const uint2*>(y + static_cast<size_t>(r) * H + col));
+              const T* h4 = reinterpret_cast<const T*>(&raw);
+#pragma unroll
+              for (int q = 0; q < 4; ++q) acc[q] += Dt<T>::to_f(h4[q]);
+            };
+            for (int sl = 0; sl < k; ++sl) {
+              const int r = __ldcg(slot_row + static_cast<size_t>(t) * k + sl);
+              if (r >= 0) add_row(r);
+            }
+            if (t >= sh_lo && t < sh_hi) add_row(n_routed_rows + t);
+            __align__(8) T o[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) o[q] = Dt<T>::from_f(acc[q]);
+            *reinterpret_cast<uint2*>(out + static_cast<size_t>(t) * H + col) = *reinterpret_cast<uint2*>(o);
+          }
+        }
       }
+      ++n;
     }
   }
 
@@ -410,7 +477,8 @@ static int launch_fused_one(const DecodeFusedLaunch& a, cudaStream_t st) {
       *static_cast<const CUtensorMap*>(a.tm_wd), *static_cast<const CUtensorMap*>(a.tm_x),
       *static_cast<const CUtensorMap*>(a.tm_act), reinterpret_cast<const int4*>(a.tiles), a.num_tiles, a.row_token,
       a.row_weight, static_cast<T*>(a.act), static_cast<T*>(a.y), a.H, a.I, a.tokens, a.n_routed_rows,
-      a.shared_expert, a.sh_lo, a.sh_hi, a.sched, a.ready));
+      a.shared_expert, a.sh_lo, a.sh_hi, a.sched, a.ready, a.slot_row, static_cast<T*>(a.out), a.k, a.fdone,
+      static_cast<const unsigned char*>(a.pf0), a.pf0_bytes, static_cast<const unsigned char*>(a.pf1), a.pf1_bytes));
   return GLM4MOE_OK;
 }
 

@@ -15,7 +15,10 @@ template <typename T>
 __device__ __forceinline__ void select_token(const T* logit_row, const float* __restrict__ bias, int E, int k,
                                              float scale, int lane, int32_t* __restrict__ idx_row,
                                              float* __restrict__ w_row) {
-  float choice[kMaxSlots], score[kMaxSlots];
+  // choice (moe.py:38, fp32) is held as an order-preserving 32-bit key so a round's arg-max is two
+  // warp reductions (redux.sync) instead of fifteen shuffles; slots past E get key 0 (< key(-inf)).
+  uint32_t key[kMaxSlots];
+  float score[kMaxSlots];
 #pragma unroll
   for (int j = 0; j < kMaxSlots; ++j) {
     const int e = j * 32 + lane;
@@ -23,43 +26,36 @@ __device__ __forceinline__ void select_token(const T* logit_row, const float* __
       const float lg = Dt<T>::to_f(__ldcg(logit_row + e));
       const float s = Dt<T>::round(sigmoid_f(lg));       // moe.py:37, model dtype
       score[j] = s;
-      choice[j] = s + bias[e];                           // moe.py:38, fp32
+      const uint32_t u = __float_as_uint(s + bias[e]);   // moe.py:38, fp32
+      key[j] = (u & 0x80000000u) ? ~u : (u | 0x80000000u);
     } else {
       score[j] = 0.f;
-      choice[j] = -INFINITY;
+      key[j] = 0u;
     }
   }
-  // k rounds of arg-max; ties -> lower expert id (lane-local scan is ascending in e for fixed
-  // lane, the cross-lane reduction compares (value, id) lexicographically).
+  // k rounds of arg-max; ties -> lower expert id (the lane-local scan is ascending in e for a fixed
+  // lane; across lanes the smallest expert id among the holders of the maximum wins).
   int my_e = -1;          // lane r keeps the r-th pick
   float my_s = 0.f;
   unsigned taken = 0;     // bit j set: my slot j already picked
   for (int r = 0; r < k; ++r) {
-    float bv = -INFINITY;
+    uint32_t bk = 0u;
     int be = 0x7fffffff;
+    float bs = 0.f;
 #pragma unroll
     for (int j = 0; j < kMaxSlots; ++j) {
       const int e = j * 32 + lane;
-      if (e < E && !((taken >> j) & 1u) && (choice[j] > bv || be == 0x7fffffff)) {
-        bv = choice[j];
+      if (e < E && !((taken >> j) & 1u) && (key[j] > bk || be == 0x7fffffff)) {
+        bk = key[j];
         be = e;
+        bs = score[j];
       }
     }
-    float bs = 0.f;
-#pragma unroll
-    for (int j = 0; j < kMaxSlots; ++j)
-      if (be == j * 32 + lane) bs = score[j];
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
-      const int oe = __shfl_xor_sync(0xffffffffu, be, o);
-      const float os = __shfl_xor_sync(0xffffffffu, bs, o);
-      if (oe != 0x7fffffff && (be == 0x7fffffff || ov > bv || (ov == bv && oe < be))) {
-        bv = ov; be = oe; bs = os;
-      }
-    }
-    if ((be & 31) == lane) taken |= 1u << (be >> 5);
-    if (lane == r) { my_e = be; my_s = bs; }
+    const uint32_t mk = __reduce_max_sync(0xffffffffu, bk);
+    const int we = __reduce_min_sync(0xffffffffu, (bk == mk && be != 0x7fffffff) ? be : 0x7fffffff);
+    const float ws = __shfl_sync(0xffffffffu, bs, we & 31);
+    if ((we & 31) == lane) taken |= 1u << (we >> 5);
+    if (lane == r) { my_e = we; my_s = ws; }
   }
   // renormalise: sum in fp32 over the k picks, every intermediate rounded to the model dtype
   float sum = 0.f;
@@ -98,7 +94,7 @@ __device__ __forceinline__ void emit_tiles(int4* __restrict__ tiles, int ti, int
 }
 
 // Decode-size batches (T <= 256): rank + scan + scatter in ONE block of 256 threads, thread t owns
-// token t.  `idx` / `w` may have been written earlier in the same kernel by this block.
+// token t.  `idx` / `w` may have been written earlier in the same kernel (L2-coherent loads).
 struct PermuteSmallSmem {
   uint32_t bitmap[kMaxExperts * kWordsPerExpert];
   int cnt[kMaxExperts];
@@ -116,7 +112,7 @@ __device__ __forceinline__ void permute_small_body(
   const uint32_t bit = 1u << (tid & 31);
   if (tid < T) {
     for (int s = 0; s < k; ++s) {
-      const int e = idx[static_cast<size_t>(tid) * k + s];
+      const int e = __ldcg(idx + static_cast<size_t>(tid) * k + s);
       if (e >= e_lo && e < e_hi) atomicOr(&sm.bitmap[e * kWordsPerExpert + word], bit);
     }
   }
@@ -167,7 +163,7 @@ __device__ __forceinline__ void permute_small_body(
   if (tid < T) {
     for (int s = 0; s < k; ++s) {
       const size_t i = static_cast<size_t>(tid) * k + s;
-      const int e = idx[i];
+      const int e = __ldcg(idx + i);
       int row = -1;
       if (e >= e_lo && e < e_hi) {
         const uint32_t* bm = &sm.bitmap[e * kWordsPerExpert];
@@ -175,7 +171,7 @@ __device__ __forceinline__ void permute_small_body(
         for (int wd = 0; wd < word; ++wd) r += __popc(bm[wd]);
         row = sm.off[e] + r;
         row_token[row] = tid;
-        row_weight[row] = w[i];
+        row_weight[row] = __ldcg(w + i);
       }
       slot_row[i] = row;
     }

@@ -4,8 +4,9 @@
 // (moe.py:135-144) for decode-size batches, where three separate launches cost more than their
 // work.  Grid = (E/EB) x (T/TT) blocks compute the logits exactly as router_logits_small_kernel
 // (8 warps split K, fixed-order fp32 accumulate, one rounding to the model dtype); every block then
-// takes a ticket, and the LAST block to finish selects the experts of all T tokens (one warp per
-// token) and builds the permutation / work list in place (single-block path of permute.cu).
+// takes a ticket: the last block of a token group selects the experts of its TT tokens (one warp per
+// token), and the last group to finish builds the permutation / work list of the whole batch
+// (single-block path of permute.cu).
 // Arithmetic and tie rule are the stand-alone kernels' (same device functions): bit-identical.
 #include "common.cuh"
 #include "route_device.cuh"
@@ -71,20 +72,32 @@ __global__ void __launch_bounds__(256) route_small_kernel(
     __threadfence();
   }
   __syncthreads();
+  // ticket 1: the last of the gridDim.x blocks that share these TT tokens selects their experts
   if (threadIdx.x == 0) {
-    const int total = static_cast<int>(gridDim.x * gridDim.y);
-    const int prev = atomicAdd(ticket, 1);
-    s_last = prev == total - 1;
-    if (s_last) *ticket = 0;   // re-armed for the next launch (graph replay safe)
+    const int prev = atomicAdd(ticket + 1 + blockIdx.y, 1);
+    s_last = prev == static_cast<int>(gridDim.x) - 1;
+    if (s_last) ticket[1 + blockIdx.y] = 0;   // re-armed for the next launch (graph replay safe)
   }
   for (int i = threadIdx.x; i < E * kWordsPerExpert; i += 256) psm.bitmap[i] = 0u;
   __syncthreads();
   if (!s_last) return;
   __threadfence();
-  // ---- last block: select (warp per token), then the single-block permutation ----
-  for (int t = warp; t < Tn; t += 8)
+  if (warp < TT && t0 + warp < Tn) {
+    const int t = t0 + warp;
     select_token<T>(logits + static_cast<size_t>(t) * E, bias, E, k, scale, lane, idx + static_cast<size_t>(t) * k,
                     w + static_cast<size_t>(t) * k);
+    __threadfence();
+  }
+  __syncthreads();
+  // ticket 2: the last token group builds the permutation of the whole batch
+  if (threadIdx.x == 0) {
+    const int prev = atomicAdd(ticket, 1);
+    s_last = prev == static_cast<int>(gridDim.y) - 1;
+    if (s_last) *ticket = 0;
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
   __syncthreads();   // idx / w of this block's own global writes are visible to the block
   permute_small_body(psm, idx, w, Tn, k, E, e_lo, e_hi, tile_rows, sh_lo, sh_hi, expert_offsets, row_token,
                      row_weight, slot_row, tiles, tile_capacity, num_tiles);

@@ -46,6 +46,39 @@ int umma_make_tensor_map(void* map_out, const void* base, int dtype, uint64_t ro
 int umma_launch(const UmmaLaunch& args, void* stream);
 bool umma_shape_ok(int H, int I, int dtype);
 
+// ---- decode regime: gate_up + down in one persistent kernel (decode_fused.cu) ----
+struct DecodeFusedLaunch {
+  const void* tm_wgu;        // gate_up weight stack, box {64, 128}
+  const void* tm_wd;         // down weight stack, box {64, 128}
+  const void* tm_x;          // the layer input [T, H], box {64, tile_rows}
+  const void* tm_act;        // activation rows [R, I], box {64, tile_rows}
+  const int32_t* tiles;      // one tile per hit expert (rows <= tile_rows), the shared tile last
+  const int32_t* num_tiles;
+  const int32_t* row_token;
+  const float* row_weight;
+  void* act;                 // [R, I]
+  void* y;                   // [R, H]
+  int H, I;
+  int tokens;                // T <= tile_rows
+  int n_routed_rows;         // T * k
+  int shared_expert;         // stack index of the shared expert
+  int sh_lo, sh_hi;
+  int tile_rows;             // 16 / 32
+  int dtype;
+  int grid;                  // <= SM count (co-residency is required by the in-kernel dependency)
+  int32_t* sched;            // 2 zero-initialised ints (self re-arming)
+  int32_t* ready;            // 1 + tile capacity zero-initialised ints (self re-arming)
+  const int32_t* slot_row;   // [T, k] row of every (token, slot), -1 = expert not local
+  void* out;                 // [T, H] layer output (combine fused into the last down item per feature tile)
+  int k;
+  int32_t* fdone;            // H/128 zero-initialised ints (self re-arming)
+  const void* pf0;           // shared expert's gate_up weights (L2 prefetch while the router runs)
+  size_t pf0_bytes;
+  const void* pf1;           // shared expert's down weights
+  size_t pf1_bytes;
+};
+int decode_fused_launch(const DecodeFusedLaunch& args, void* stream);
+
 // ---- FP8 block-scaled tier (umma_fp8.cu) ----
 struct UmmaFp8Launch {
   const void* tm_w;          // CUtensorMap over the e4m3 weight stack (uint8), box {128 bytes, 128 rows}

@@ -56,8 +56,10 @@ typedef struct glm4moe_layer glm4moe_layer_t;   /* opaque */
 int glm4moe_abi_version(void);
 /* Process-wide tuning / test knobs (parity tests compare the paths against each other).
  * GLM4MOE_KNOB_DIRECT: 1 (default) = decode batches T <= 32 use the fused front-end and read the
- * input tokens in place; 0 = always the general router / permute / gather sequence.            */
-enum { GLM4MOE_KNOB_DIRECT = 0 };
+ * input tokens in place; 0 = always the general router / permute / gather sequence.
+ * GLM4MOE_KNOB_FUSED: 1 (default) = inside direct mode, gate_up and down run as one persistent kernel
+ * (decode_fused.cu); 0 = two grouped-GEMM launches.                                              */
+enum { GLM4MOE_KNOB_DIRECT = 0, GLM4MOE_KNOB_FUSED = 1 };
 int glm4moe_debug_set(int knob, int value);
 const char* glm4moe_error_string(int code);
 
@@ -73,7 +75,7 @@ int glm4moe_router_select(const void* logits, const float* bias, int T, int E, i
 
 /* Decode front-end, T <= GLM4MOE_ROUTE_SMALL_MAX_TOKENS: glm4moe_router_logits + glm4moe_router_select +
  * glm4moe_permute in ONE launch with bit-identical results (the last block to finish its logits runs
- * the selection and the permutation).  `ticket`: one zero-initialised int32 owned by the call site
+ * the selection and the permutation).  `ticket`: 40 zero-initialised int32 owned by the call site
  * (left at zero).  Replaces moe.py:28-50 and the bookkeeping of moe.py:135-144 at decode sizes.     */
 #define GLM4MOE_ROUTE_SMALL_MAX_TOKENS 64
 int glm4moe_route_small(const void* h, const void* gate_w, const float* bias, void* logits, int T, int H,
