@@ -64,7 +64,7 @@ def load() -> C.CDLL:
     lib.glm4moe_router_logits.argtypes = [vp, vp, vp, i32, i32, i32, i32, vp]
     lib.glm4moe_router_select.argtypes = [vp, vp, i32, i32, i32, f32, i32, vp, vp, vp]
     lib.glm4moe_route_small.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, f32, i32, i32, i32, i32, i32, i32,
-                                        vp, vp, vp, vp, vp, vp, vp, i32, vp, vp, vp]
+                                        vp, vp, vp, vp, vp, vp, vp, i32, vp, vp, vp, vp, i32, vp]
     lib.glm4moe_permute.argtypes = [vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, i32, vp, vp, vp]
     lib.glm4moe_permute_scratch_elems.restype = sz
     lib.glm4moe_permute_scratch_elems.argtypes = [i32, i32]

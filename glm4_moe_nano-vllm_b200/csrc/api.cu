@@ -328,7 +328,9 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
   const bool use_umma = l->umma_ok;
   const bool fp8 = c.weight_format == GLM4MOE_W_FP8_BLOCK128;
   // decode "direct" mode: fused front-end + gate_up reading the input tokens in place
-  const bool direct = use_umma && !fp8 && T <= kDirectMaxTokens && H % 64 == 0 && direct_enabled();
+  // (the e4m3 tier has no un-fused direct variant)
+  const bool direct = use_umma && T <= kDirectMaxTokens && H % 64 == 0 && direct_enabled() &&
+                      (!fp8 || fused_enabled());
   const int bi = direct ? (T <= 16 ? 0 : 1)
                         : fp8 ? (pick_bn_index(c, T) < 2 ? pick_bn_index(c, T) : 2) : pick_bn_index(c, T);
   const int tile_rows = use_umma ? kBnChoices[bi] : kSimtRows;
@@ -338,11 +340,14 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
   bool combine_done = false;
   STAGE_MARK(0);
   if (direct) {
-    if ((rc = umma_make_tensor_map(&tm_xdirect, x, c.dtype, static_cast<uint64_t>(T), H, tile_rows))) return rc;
+    if (!fp8 && (rc = umma_make_tensor_map(&tm_xdirect, x, c.dtype, static_cast<uint64_t>(T), H, tile_rows)))
+      return rc;
     if ((rc = glm4moe_route_small(x, l->gate_w, l->bias, logits, T, H, E, k, c.routed_scaling_factor, c.dtype,
                                   c.expert_begin, c.expert_end, tile_rows, sh_lo, sh_hi, idx, w, offsets, row_token,
                                   row_weight, slot_row, tiles, L.tile_capacity, num_tiles,
-                                  reinterpret_cast<int32_t*>(ws + L.sched) + 24, stream)))
+                                  reinterpret_cast<int32_t*>(ws + L.sched) + 24, fp8 ? ws + L.xq : nullptr,
+                                  fp8 ? reinterpret_cast<float*>(ws + L.sx) : nullptr,
+                                  c.max_tokens * (k + 1), stream)))
       return rc;
     STAGE_MARK(1);
     STAGE_MARK(2);
@@ -395,7 +400,54 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
     return rc;
   }
   STAGE_MARK(4);
-  if (fp8) {
+  if (direct && fused_enabled()) {
+    DecodeFusedLaunch f{};
+    f.tm_wgu = &l->tm_w_gu;
+    f.tm_wd = &l->tm_w_d;
+    f.tm_x = fp8 ? &l->tm_x[bi] : &tm_xdirect;
+    f.tm_act = &l->tm_act[bi];
+    f.tiles = tiles;
+    f.num_tiles = num_tiles;
+    f.row_token = row_token;
+    f.row_weight = row_weight;
+    f.act = act;
+    f.y = y;
+    f.H = H;
+    f.I = I;
+    f.tokens = T;
+    f.n_routed_rows = T * k;
+    f.shared_expert = c.expert_end - c.expert_begin;
+    f.sh_lo = sh_lo;
+    f.sh_hi = sh_hi;
+    f.tile_rows = tile_rows;
+    f.dtype = c.dtype;
+    f.grid = l->sm_count;
+    f.sched = reinterpret_cast<int32_t*>(ws + L.sched) + 16;
+    f.ready = reinterpret_cast<int32_t*>(ws + L.ready);
+    f.slot_row = slot_row;
+    f.out = out;
+    f.k = k;
+    f.fdone = reinterpret_cast<int32_t*>(ws + L.fdone);
+    {
+      const size_t es = fp8 ? 1 : dtype_size(c.dtype), n_local = static_cast<size_t>(c.expert_end - c.expert_begin);
+      f.pf0 = static_cast<const unsigned char*>(l->w_gate_up) + n_local * 2 * I * H * es;
+      f.pf0_bytes = static_cast<size_t>(2) * I * H * es;
+      f.pf1 = static_cast<const unsigned char*>(l->w_down) + n_local * H * I * es;
+      f.pf1_bytes = static_cast<size_t>(H) * I * es;
+    }
+    if (fp8) {
+      f.fp8 = 1;
+      f.q.s_gate_up = l->s_gate_up;
+      f.q.s_down = l->s_down;
+      f.q.sx_t = reinterpret_cast<const float*>(ws + L.sx);
+      f.q.sact_t = reinterpret_cast<float*>(ws + L.sact);
+      f.q.actq = ws + L.actq;
+      f.q.scale_ld = R_cap;
+    }
+    if ((rc = decode_fused_launch(f, stream))) return rc;
+    STAGE_MARK(5);
+    combine_done = true;
+  } else if (fp8) {
     UmmaFp8Launch a{};
     a.tiles = tiles;
     a.num_tiles = num_tiles;
@@ -437,44 +489,6 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
     a.gated = 0;
     a.sched = reinterpret_cast<int32_t*>(ws + L.sched) + 2;
     if ((rc = umma_fp8_launch(a, stream))) return rc;
-  } else if (direct && fused_enabled()) {
-    DecodeFusedLaunch f{};
-    f.tm_wgu = &l->tm_w_gu;
-    f.tm_wd = &l->tm_w_d;
-    f.tm_x = &tm_xdirect;
-    f.tm_act = &l->tm_act[bi];
-    f.tiles = tiles;
-    f.num_tiles = num_tiles;
-    f.row_token = row_token;
-    f.row_weight = row_weight;
-    f.act = act;
-    f.y = y;
-    f.H = H;
-    f.I = I;
-    f.tokens = T;
-    f.n_routed_rows = T * k;
-    f.shared_expert = c.expert_end - c.expert_begin;
-    f.sh_lo = sh_lo;
-    f.sh_hi = sh_hi;
-    f.tile_rows = tile_rows;
-    f.dtype = c.dtype;
-    f.grid = l->sm_count;
-    f.sched = reinterpret_cast<int32_t*>(ws + L.sched) + 16;
-    f.ready = reinterpret_cast<int32_t*>(ws + L.ready);
-    f.slot_row = slot_row;
-    f.out = out;
-    f.k = k;
-    f.fdone = reinterpret_cast<int32_t*>(ws + L.fdone);
-    {
-      const size_t es = dtype_size(c.dtype), n_local = static_cast<size_t>(c.expert_end - c.expert_begin);
-      f.pf0 = static_cast<const unsigned char*>(l->w_gate_up) + n_local * 2 * I * H * es;
-      f.pf0_bytes = static_cast<size_t>(2) * I * H * es;
-      f.pf1 = static_cast<const unsigned char*>(l->w_down) + n_local * H * I * es;
-      f.pf1_bytes = static_cast<size_t>(H) * I * es;
-    }
-    if ((rc = decode_fused_launch(f, stream))) return rc;
-    STAGE_MARK(5);
-    combine_done = true;
   } else if (use_umma) {
     UmmaLaunch a{};
     a.tiles = tiles;

@@ -8,6 +8,8 @@
 // token), and the last group to finish builds the permutation / work list of the whole batch
 // (single-block path of permute.cu).
 // Arithmetic and tie rule are the stand-alone kernels' (same device functions): bit-identical.
+#include <cuda_fp8.h>
+
 #include "common.cuh"
 #include "route_device.cuh"
 
@@ -19,7 +21,8 @@ __global__ void __launch_bounds__(256) route_small_kernel(
     int H, int E, int k, float scale, int e_lo, int e_hi, int tile_rows, int sh_lo, int sh_hi, int32_t* idx,
     float* w, int32_t* __restrict__ expert_offsets, int32_t* __restrict__ row_token,
     float* __restrict__ row_weight, int32_t* __restrict__ slot_row, int4* __restrict__ tiles, int tile_capacity,
-    int32_t* __restrict__ num_tiles, int32_t* __restrict__ ticket) {
+    int32_t* __restrict__ num_tiles, int32_t* __restrict__ ticket, unsigned char* __restrict__ xq,
+    float* __restrict__ sx_t, int sx_ld) {
   constexpr int V = Dt<T>::kVec;
   __shared__ float part[8][TT * EB];
   __shared__ PermuteSmallSmem psm;
@@ -31,6 +34,43 @@ __global__ void __launch_bounds__(256) route_small_kernel(
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int e0 = blockIdx.x * EB, t0 = blockIdx.y * TT;
   const int nvec = H / V;
+  if constexpr (sizeof(T) == 2) {
+    // e4m3 tier: the input tokens are also the MMA token tile of the fused expert kernel; quantise
+    // them here (per token, per 128 elements: scale = amax / 448, q = rn_e4m3(v / scale), the formula
+    // of quant_rows_fp8_kernel).  This block's share: its TT tokens x the 128-groups {bx, bx + gridDim.x, ..}.
+    if (xq != nullptr) {
+      const int n_groups = H / 128;
+      const int per_block = (n_groups - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) /
+                            static_cast<int>(gridDim.x);
+      const int n_items = TT * per_block;
+      for (int base = warp * 2; base < n_items; base += 16) {
+        const int item = base + (lane >> 4);
+        const int t = t0 + item % TT, g = static_cast<int>(blockIdx.x) + (item / TT) * static_cast<int>(gridDim.x);
+        const bool ok = item < n_items && t < Tn;
+        float v[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[i] = 0.f;
+        const int c = g * 128 + (lane & 15) * 8;
+        if (ok) unpack16<T>(ld_cached16(h + static_cast<size_t>(t) * H + c), v);
+        float amax = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) amax = fmaxf(amax, fabsf(v[i]));
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+        const float sc = __fdiv_rn(fmaxf(amax, 1e-10f), 448.0f);
+        uint32_t lo = 0, hi = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          lo |= static_cast<uint32_t>(__nv_cvt_float_to_fp8(__fdiv_rn(v[i], sc), __NV_SATFINITE, __NV_E4M3)) << (8 * i);
+          hi |= static_cast<uint32_t>(__nv_cvt_float_to_fp8(__fdiv_rn(v[4 + i], sc), __NV_SATFINITE, __NV_E4M3)) << (8 * i);
+        }
+        if (ok) {
+          *reinterpret_cast<uint2*>(xq + static_cast<size_t>(t) * H + c) = make_uint2(lo, hi);
+          if ((lane & 15) == 0) sx_t[static_cast<size_t>(g) * sx_ld + t] = sc;
+        }
+      }
+    }
+  }
   float acc[TT][EB];
 #pragma unroll
   for (int i = 0; i < TT; ++i)
@@ -108,7 +148,7 @@ static int launch_route_small(const void* h, const void* gw, const float* bias, 
                               int k, float scale, int e_lo, int e_hi, int tile_rows, int sh_lo, int sh_hi,
                               int32_t* idx, float* w, int32_t* offsets, int32_t* row_token, float* row_weight,
                               int32_t* slot_row, int32_t* tiles, int tile_capacity, int32_t* num_tiles,
-                              int32_t* ticket, cudaStream_t st) {
+                              int32_t* ticket, void* xq, float* sx_t, int sx_ld, cudaStream_t st) {
   constexpr int V = Dt<T>::kVec;
   if (H % V != 0) return GLM4MOE_ERR_UNSUPPORTED;
   if (T_ <= 2) {
@@ -116,13 +156,15 @@ static int launch_route_small(const void* h, const void* gw, const float* bias, 
     GLM4MOE_CUDA_CHECK(launch_pdl(route_small_kernel<T, 2, 4>, grid, dim3(256), 0, st, static_cast<const T*>(h),
                                   static_cast<const T*>(gw), bias, static_cast<T*>(logits), T_, H, E, k, scale, e_lo,
                                   e_hi, tile_rows, sh_lo, sh_hi, idx, w, offsets, row_token, row_weight, slot_row,
-                                  reinterpret_cast<int4*>(tiles), tile_capacity, num_tiles, ticket));
+                                  reinterpret_cast<int4*>(tiles), tile_capacity, num_tiles, ticket,
+                                  static_cast<unsigned char*>(xq), sx_t, sx_ld));
   } else {
     dim3 grid((E + 3) / 4, (T_ + 3) / 4);
     GLM4MOE_CUDA_CHECK(launch_pdl(route_small_kernel<T, 4, 4>, grid, dim3(256), 0, st, static_cast<const T*>(h),
                                   static_cast<const T*>(gw), bias, static_cast<T*>(logits), T_, H, E, k, scale, e_lo,
                                   e_hi, tile_rows, sh_lo, sh_hi, idx, w, offsets, row_token, row_weight, slot_row,
-                                  reinterpret_cast<int4*>(tiles), tile_capacity, num_tiles, ticket));
+                                  reinterpret_cast<int4*>(tiles), tile_capacity, num_tiles, ticket,
+                                  static_cast<unsigned char*>(xq), sx_t, sx_ld));
   }
   return GLM4MOE_OK;
 }
@@ -135,7 +177,8 @@ extern "C" int glm4moe_route_small(const void* h, const void* gate_w, const floa
                                    int E, int k, float scale, int dtype, int e_lo, int e_hi, int tile_rows,
                                    int shared_lo, int shared_hi, int32_t* idx, float* w, int32_t* expert_offsets,
                                    int32_t* row_token, float* row_weight, int32_t* slot_row, int32_t* tiles,
-                                   int32_t tile_capacity, int32_t* num_tiles, int32_t* ticket, void* stream) {
+                                   int32_t tile_capacity, int32_t* num_tiles, int32_t* ticket, void* xq,
+                                   float* x_scale_t, int x_scale_ld, void* stream) {
   if (!h || !gate_w || !bias || !logits || !idx || !w || !expert_offsets || !row_token || !row_weight ||
       !slot_row || !tiles || !num_tiles || !ticket)
     return GLM4MOE_ERR_ARG;
@@ -146,11 +189,12 @@ extern "C" int glm4moe_route_small(const void* h, const void* gate_w, const floa
       shared_lo > shared_hi)
     return GLM4MOE_ERR_ARG;
   if (tile_capacity < glm4moe_tile_capacity(T, k, E, tile_rows)) return GLM4MOE_ERR_WORKSPACE;
+  if (xq && (!x_scale_t || x_scale_ld < T || H % 128 != 0 || dtype == GLM4MOE_F32)) return GLM4MOE_ERR_ARG;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   GLM4MOE_DISPATCH_DTYPE(dtype, T_,
                          return launch_route_small<T_>(h, gate_w, bias, logits, T, H, E, k, scale, e_lo, e_hi,
                                                        tile_rows, shared_lo, shared_hi, idx, w, expert_offsets,
                                                        row_token, row_weight, slot_row, tiles, tile_capacity,
-                                                       num_tiles, ticket, st));
+                                                       num_tiles, ticket, xq, x_scale_t, x_scale_ld, st));
   return GLM4MOE_OK;
 }

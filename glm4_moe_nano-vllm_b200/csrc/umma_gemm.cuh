@@ -47,6 +47,17 @@ int umma_launch(const UmmaLaunch& args, void* stream);
 bool umma_shape_ok(int H, int I, int dtype);
 
 // ---- decode regime: gate_up + down in one persistent kernel (decode_fused.cu) ----
+// e4m3 tier of the fused kernel: 128x128 fp32 weight block scales, per-token 1x128 activation scales
+// (k-block major, [K/128, scale_ld]); the gate_up epilogue quantises its activation tile itself.
+struct Fp8Args {
+  const float* s_gate_up;    // [n_stack, 2I/128, H/128]
+  const float* s_down;       // [n_stack, H/128, I/128]
+  const float* sx_t;         // [H/128, scale_ld]: scales of the quantised input tokens (row = token)
+  float* sact_t;             // [I/128, scale_ld]: scales of the quantised activation rows
+  unsigned char* actq;       // [R, I] e4m3 activation rows
+  int scale_ld;
+};
+
 struct DecodeFusedLaunch {
   const void* tm_wgu;        // gate_up weight stack, box {64, 128}
   const void* tm_wd;         // down weight stack, box {64, 128}
@@ -76,6 +87,8 @@ struct DecodeFusedLaunch {
   size_t pf0_bytes;
   const void* pf1;           // shared expert's down weights
   size_t pf1_bytes;
+  int fp8;                   // 1: e4m3 weights / activations (tm_* are byte maps), q is set
+  Fp8Args q;
 };
 int decode_fused_launch(const DecodeFusedLaunch& args, void* stream);
 

@@ -76,13 +76,16 @@ int glm4moe_router_select(const void* logits, const float* bias, int T, int E, i
 /* Decode front-end, T <= GLM4MOE_ROUTE_SMALL_MAX_TOKENS: glm4moe_router_logits + glm4moe_router_select +
  * glm4moe_permute in ONE launch with bit-identical results (the last block to finish its logits runs
  * the selection and the permutation).  `ticket`: 40 zero-initialised int32 owned by the call site
- * (left at zero).  Replaces moe.py:28-50 and the bookkeeping of moe.py:135-144 at decode sizes.     */
+ * (left at zero).  Replaces moe.py:28-50 and the bookkeeping of moe.py:135-144 at decode sizes.
+ * FP8 tier: xq != NULL additionally writes the e4m3 copy of the tokens, xq[T,H], with per-token 1x128
+ * scales x_scale_t[H/128, x_scale_ld] (scale = amax/448), the token tile of the fused expert kernel.  */
 #define GLM4MOE_ROUTE_SMALL_MAX_TOKENS 64
 int glm4moe_route_small(const void* h, const void* gate_w, const float* bias, void* logits, int T, int H,
                         int E, int k, float scale, int dtype, int e_lo, int e_hi, int tile_rows,
                         int shared_lo, int shared_hi, int32_t* idx, float* w, int32_t* expert_offsets,
                         int32_t* row_token, float* row_weight, int32_t* slot_row, int32_t* tiles,
-                        int32_t tile_capacity, int32_t* num_tiles, int32_t* ticket, void* stream);
+                        int32_t tile_capacity, int32_t* num_tiles, int32_t* ticket, void* xq,
+                        float* x_scale_t, int x_scale_ld, void* stream);
 
 /* ---- permutation: replaces the mask / where / gather loop (moe.py:135-147) ------------------ */
 /* Stable expert-major order of the (token, slot) pairs whose expert is in [e_lo, e_hi).

@@ -354,7 +354,7 @@ def test_route_small_bit_identical_to_separate_kernels(T, shape_name, dt):
                                            E, k, shape.routed_scaling_factor, code, e_lo, e_hi, tr, sh_lo, sh_hi,
                                            b["idx"].data_ptr(), b["w"].data_ptr(), b["off"].data_ptr(),
                                            b["rt"].data_ptr(), b["rw"].data_ptr(), b["sr"].data_ptr(),
-                                           b["tiles"].data_ptr(), cap, b["nt"].data_ptr(), ticket.data_ptr(), st))
+                                           b["tiles"].data_ptr(), cap, b["nt"].data_ptr(), ticket.data_ptr(), None, None, 0, st))
     torch.cuda.synchronize()
     assert int(ticket.abs().sum()) == 0
     n_rows = int(a["off"][E])
@@ -365,18 +365,23 @@ def test_route_small_bit_identical_to_separate_kernels(T, shape_name, dt):
     assert nt > 0 and torch.equal(a["tiles"][:nt], b["tiles"][:nt])
 
 
-@pytest.mark.parametrize("shape_name,Ts", [("mini", (1, 5, 16, 17, 32)), ("glm-4.5-air", (1, 2, 13, 32))])
-def test_direct_mode_bit_identical_to_general_path(shape_name, Ts):
+@pytest.mark.parametrize("shape_name,Ts,fp8", [("mini", (1, 5, 16, 17, 32), False), ("glm-4.5-air", (1, 2, 13, 32), False),
+                                               ("mini", (1, 5, 16, 17, 32), True), ("glm-4.5-air", (1, 3, 32), True)])
+def test_direct_mode_bit_identical_to_general_path(shape_name, Ts, fp8):
     """T <= 32 runs the fused front-end and feeds the input tokens to the gate_up MMA in place
     (no gathered copy); the general path must give the same bits (same K order per output)."""
     lib = _lib.load()
     shape, dt = synth.SHAPES[shape_name], torch.bfloat16
     moe = _module(shape, dt, synth.make_weights(shape, dt), max_tokens=64)
+    modes = {"fused": (1, 1, 2), "direct": (1, 0, 4), "general": (0, 0, 7)}
+    if fp8:
+        moe.quantize_fp8(drop_native=True)
+        modes = {"fused": (1, 1, 2), "direct": (1, 0, 8), "general": (0, 0, 8)}   # no un-fused direct variant
     try:
         for T in Ts:
             x = synth.make_tokens(shape, T, dt, 900 + T).cuda()
             outs = {}
-            for name, (direct, fused, launches) in {"fused": (1, 1, 2), "direct": (1, 0, 4), "general": (0, 0, 7)}.items():
+            for name, (direct, fused, launches) in modes.items():
                 _lib.check(lib.glm4moe_debug_set(0, direct))
                 _lib.check(lib.glm4moe_debug_set(1, fused))
                 for rep in range(3):       # repeated: the in-kernel counters re-arm themselves
