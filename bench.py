@@ -298,11 +298,18 @@ def main():
     # the (U local + shared) experts it touches + the activation rows it reads + act rows it writes.
     n_sh = 1
     rows = T * k / world + T / world
-    gu_bytes = (U + n_sh) * 2 * I * H * 2 + rows * H * 2 + rows * I * 2
     gu_ms = stage_acc["gate_up"]
+    if moe.last_fused:
+        # decode regime: gate_up + SiLU*mul + down + combine are ONE persistent launch
+        # (decode_fused.cu); the "gate_up" stage interval brackets exactly that launch.
+        kern = "decode_fused_kernel<gate_up+silu_mul+down+combine>"
+        gu_bytes = (U + n_sh) * 3 * I * H * 2 + (T / world) * H * 2 + T * H * 2
+    else:
+        kern = "umma_grouped_kernel<gate_up+silu_mul>"
+        gu_bytes = (U + n_sh) * 2 * I * H * 2 + rows * H * 2 + rows * I * 2
     achieved = gu_bytes / gu_ms / 1e6
     layer_bytes = shape.algorithmic_bytes(T, U) if world == 1 else None
-    roofline = {"bound": "hbm", "kernel": "umma_grouped_kernel<gate_up+silu_mul>", "achieved": achieved,
+    roofline = {"bound": "hbm", "kernel": kern, "achieved": achieved,
                 "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
                 "peak_source": peak_src, "kernel_ms": gu_ms, "algorithmic_bytes_per_launch": gu_bytes,
                 "stage_ms": stage_acc}

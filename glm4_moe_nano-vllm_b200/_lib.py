@@ -24,7 +24,7 @@ SYMBOLS = [
     "glm4moe_expert_gate_up_simt", "glm4moe_expert_down_simt", "glm4moe_combine",
     "glm4moe_workspace_bytes", "glm4moe_layer_create", "glm4moe_layer_destroy",
     "glm4moe_layer_forward", "glm4moe_layer_forward_ex", "glm4moe_layer_forward_timed", "glm4moe_layer_forward_host", "glm4moe_layer_view",
-    "glm4moe_layer_last_launches", "glm4moe_layer_last_impl", "glm4moe_layer_tile_rows",
+    "glm4moe_layer_last_launches", "glm4moe_layer_last_impl", "glm4moe_layer_last_fused", "glm4moe_layer_tile_rows",
 ]
 
 
@@ -85,6 +85,7 @@ def load() -> C.CDLL:
     lib.glm4moe_layer_view.argtypes = [vp, i32, C.POINTER(vp), C.POINTER(sz)]
     lib.glm4moe_layer_last_launches.argtypes = [vp]
     lib.glm4moe_layer_last_impl.argtypes = [vp]
+    lib.glm4moe_layer_last_fused.argtypes = [vp]
     lib.glm4moe_layer_tile_rows.argtypes = [vp, i32]
     for name in SYMBOLS:
         if lib.glm4moe_abi_version is None or not hasattr(lib, name):

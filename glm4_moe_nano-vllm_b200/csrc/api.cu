@@ -102,6 +102,7 @@ struct glm4moe_layer {
   bool umma_ok;
   int last_launches;
   int last_impl;
+  int last_fused;
   bool events_ready;
   cudaEvent_t ev[8];
   alignas(64) CUtensorMap tm_w_gu;
@@ -192,6 +193,7 @@ extern "C" int glm4moe_layer_create(const glm4moe_config_t* cfg, const void* gat
   l->s_down = s_down;
   l->last_launches = 0;
   l->last_impl = GLM4MOE_IMPL_AUTO;
+  l->last_fused = 0;
   l->events_ready = false;
   if (cudaMemset(l->ws + L.sched, 0, 256) != cudaSuccess ||
       cudaMemset(l->ws + L.ready, 0, (cfg->n_routed_experts + 8) * 4) != cudaSuccess ||
@@ -550,6 +552,7 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
 #undef STAGE_MARK
   l->last_launches = g_launches - launches0;
   l->last_impl = use_umma ? GLM4MOE_IMPL_UMMA : GLM4MOE_IMPL_SIMT;
+  l->last_fused = combine_done ? 1 : 0;
   return GLM4MOE_OK;
 }
 
@@ -623,3 +626,4 @@ extern "C" int glm4moe_layer_view(glm4moe_layer_t* l, int which, void** ptr, siz
 
 extern "C" int glm4moe_layer_last_launches(const glm4moe_layer_t* l) { return l ? l->last_launches : 0; }
 extern "C" int glm4moe_layer_last_impl(const glm4moe_layer_t* l) { return l ? l->last_impl : 0; }
+extern "C" int glm4moe_layer_last_fused(const glm4moe_layer_t* l) { return l ? l->last_fused : 0; }

@@ -426,3 +426,8 @@ class Glm4MoeMoE(nn.Module):
     def last_impl(self) -> str:
         code = _lib.load().glm4moe_layer_last_impl(self._handle) if self._handle else 0
         return {0: "none", 1: "simt", 2: "umma"}[code]
+
+    @property
+    def last_fused(self) -> bool:
+        """True when the last forward ran the experts as the single persistent decode kernel."""
+        return bool(_lib.load().glm4moe_layer_last_fused(self._handle)) if self._handle else False

@@ -157,6 +157,8 @@ int glm4moe_layer_view(glm4moe_layer_t* layer, int which, void** ptr, size_t* by
 /* number of kernels the last forward launched, and which expert-GEMM implementation it used */
 int glm4moe_layer_last_launches(const glm4moe_layer_t* layer);
 int glm4moe_layer_last_impl(const glm4moe_layer_t* layer);
+/* 1 when the last forward ran gate_up + down + combine as the single persistent decode kernel */
+int glm4moe_layer_last_fused(const glm4moe_layer_t* layer);
 int glm4moe_layer_tile_rows(const glm4moe_layer_t* layer, int T);
 
 #ifdef __cplusplus

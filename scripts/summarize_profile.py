@@ -6,7 +6,9 @@ import io
 import subprocess
 import sys
 
+# usage: summarize_profile.py <tag> [full-capture .ncu-rep ...]   (default capture: gpurun_out/prof_<tag>.ncu-rep)
 tag = sys.argv[1]
+reps = sys.argv[2:] or [f"gpurun_out/prof_{tag}.ncu-rep"]
 out = [f"# ncu summary `{tag}`", ""]
 try:
     lines = [l for l in open(f"gpurun_out/launches_{tag}.csv") if not l.startswith("==")]
@@ -29,30 +31,30 @@ try:
     out.append("")
 except FileNotFoundError:
     pass
-try:
-    raw = subprocess.run(["ncu", "-i", f"gpurun_out/prof_{tag}.ncu-rep", "--page", "raw", "--csv"],
-                         capture_output=True, text=True).stdout
-    r = list(csv.reader(io.StringIO(raw)))
-    hdr = r[0]
-    want = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
-            "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
-            "dram__throughput.avg.pct_of_peak_sustained_elapsed",
-            "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
-            "sm__inst_executed_pipe_tensor.sum", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
-            "lts__t_bytes.sum", "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum",
-            "sm__warps_active.avg.pct_of_peak_sustained_active", "launch__registers_per_thread",
-            "launch__grid_size", "launch__block_size", "smsp__cycles_active.avg"]
-    ki = hdr.index("Kernel Name")
-    out += ["## full capture (`ncu --set full --clock-control none --import-source on`)", ""]
-    names = [row[ki][:80] for row in r[2:]]
-    out.append("| metric | unit | " + " | ".join(f"`{n}`" for n in names) + " |")
-    out.append("|---|---|" + "---|" * len(names))
-    for w in want:
-        if w in hdr:
-            i = hdr.index(w)
-            out.append(f"| {w} | {r[1][i]} | " + " | ".join(row[i] for row in r[2:]) + " |")
-    out.append("")
-except Exception as e:  # noqa: BLE001
-    out.append(f"(no full capture: {e})")
+WANT = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
+        "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
+        "dram__throughput.avg.pct_of_peak_sustained_elapsed",
+        "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_tensor.sum", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
+        "lts__t_bytes.sum", "lts__t_sector_hit_rate.pct", "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum",
+        "sm__warps_active.avg.pct_of_peak_sustained_active", "launch__registers_per_thread",
+        "launch__grid_size", "launch__block_size", "smsp__cycles_active.avg"]
+for rep in reps:
+    try:
+        raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+        r = list(csv.reader(io.StringIO(raw)))
+        hdr = r[0]
+        ki = hdr.index("Kernel Name")
+        out += [f"## full capture `{rep}` (`ncu --set full --clock-control none --import-source on`)", ""]
+        names = [row[ki][:80] for row in r[2:]]
+        out.append("| metric | unit | " + " | ".join(f"`{n}`" for n in names) + " |")
+        out.append("|---|---|" + "---|" * len(names))
+        for w in WANT:
+            if w in hdr:
+                i = hdr.index(w)
+                out.append(f"| {w} | {r[1][i]} | " + " | ".join(row[i] for row in r[2:]) + " |")
+        out.append("")
+    except Exception as e:  # noqa: BLE001
+        out.append(f"(no full capture {rep}: {e})")
 open(f"profiles/{tag}.md", "w").write("\n".join(out) + "\n")
 print("\n".join(out))
