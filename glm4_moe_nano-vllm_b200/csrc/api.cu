@@ -29,6 +29,14 @@ bool fused_enabled() {
   }
   return g_fused == 1;
 }
+int g_fp8_prefill = -1;   // token-major FP8 kernel at prefill; GLM4MOE_NO_FP8_PREFILL=1 / glm4moe_debug_set(2, v)
+bool fp8_prefill_enabled() {
+  if (g_fp8_prefill < 0) {
+    const char* e = getenv("GLM4MOE_NO_FP8_PREFILL");
+    g_fp8_prefill = (e && e[0] == '1') ? 0 : 1;
+  }
+  return g_fp8_prefill == 1;
+}
 int g_direct = -1;   // -1: read GLM4MOE_NO_DIRECT on first use; glm4moe_debug_set(0, v) overrides
 bool direct_enabled() {
   if (g_direct < 0) {
@@ -129,6 +137,7 @@ extern "C" int glm4moe_debug_set(int knob, int value) {
   switch (knob) {
     case GLM4MOE_KNOB_DIRECT: g_direct = value ? 1 : 0; return GLM4MOE_OK;
     case GLM4MOE_KNOB_FUSED: g_fused = value ? 1 : 0; return GLM4MOE_OK;
+    case GLM4MOE_KNOB_FP8_PREFILL: g_fp8_prefill = value ? 1 : 0; return GLM4MOE_OK;
     default: return GLM4MOE_ERR_ARG;
   }
 }
@@ -217,7 +226,7 @@ extern "C" int glm4moe_layer_create(const glm4moe_config_t* cfg, const void* gat
     const uint64_t R = static_cast<uint64_t>(cfg->max_tokens) * (cfg->num_experts_per_tok + 1);
     rc = umma_make_tensor_map_u8(&l->tm_w_gu, w_gate_up, n_stack * 2 * I, H, 128);
     if (rc == GLM4MOE_OK) rc = umma_make_tensor_map_u8(&l->tm_w_d, w_down, n_stack * H, I, 128);
-    for (int i = 0; i < 3 && rc == GLM4MOE_OK; ++i) {
+    for (int i = 0; i < 4 && rc == GLM4MOE_OK; ++i) {
       rc = umma_make_tensor_map_u8(&l->tm_x[i], l->ws + L.xq, R, H, kBnChoices[i]);
       if (rc == GLM4MOE_OK) rc = umma_make_tensor_map_u8(&l->tm_act[i], l->ws + L.actq, R, I, kBnChoices[i]);
     }
@@ -333,8 +342,12 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
   // (the e4m3 tier has no un-fused direct variant)
   const bool direct = use_umma && T <= kDirectMaxTokens && H % 64 == 0 && direct_enabled() &&
                       (!fp8 || fused_enabled());
+  // e4m3 tier at prefill (>= ~48 rows per expert): token-major 128 x 256 tiles (umma_fp8_prefill.cu)
+  const bool fp8_prefill = fp8 && !direct && pick_bn_index(c, T) >= 3 && fp8_prefill_enabled() &&
+                           umma_fp8_prefill_shape_ok(H, I);
   const int bi = direct ? (T <= 16 ? 0 : 1)
-                        : fp8 ? (pick_bn_index(c, T) < 2 ? pick_bn_index(c, T) : 2) : pick_bn_index(c, T);
+                 : fp8_prefill ? 3
+                 : fp8 ? (pick_bn_index(c, T) < 2 ? pick_bn_index(c, T) : 2) : pick_bn_index(c, T);
   const int tile_rows = use_umma ? kBnChoices[bi] : kSimtRows;
   const int launches0 = g_launches;
   int rc;
@@ -358,7 +371,9 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
   if (use_umma && T >= kRouterUmmaMinTokens && H % 64 == 0) {
     // router logits on the tensor cores: D[expert, token] = Wg . x^T, dense token tiles of x itself
     alignas(64) CUtensorMap tm_xin;
-    const int rbn = T >= 128 ? 128 : 64;
+    // token-tile rows: the gate has a single 128-expert feature tile, so the tile count is the only
+    // source of parallelism; small tiles until the tiles alone cover the SMs
+    const int rbn = T >= 128 * l->sm_count ? 128 : T >= 64 * l->sm_count ? 64 : T >= 3200 ? 32 : 16;
     if ((rc = umma_make_tensor_map(&tm_xin, x, c.dtype, static_cast<uint64_t>(T), H, rbn))) return rc;
     UmmaLaunch r{};
     r.tm_w = &l->tm_gate;
@@ -395,8 +410,8 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
     // no gathered copy of the token rows
   } else if (fp8) {
     // gather fused with the per-token 1x128 activation quantiser
-    if ((rc = quant_rows_fp8(x, H, row_token, offsets, E, T, k, H, sh_lo, sh_hi, ws + L.xq,
-                             reinterpret_cast<float*>(ws + L.sx), R_cap, c.dtype, stream)))
+    if ((rc = quant_scatter_fp8(x, H, slot_row, T, k, sh_lo, sh_hi, ws + L.xq,
+                                reinterpret_cast<float*>(ws + L.sx), R_cap, c.dtype, stream)))
       return rc;
   } else if ((rc = glm4moe_gather_rows(x, row_token, offsets, x_rows, T, k, E, H, sh_lo, sh_hi, c.dtype, stream))) {
     return rc;
@@ -449,6 +464,48 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
     if ((rc = decode_fused_launch(f, stream))) return rc;
     STAGE_MARK(5);
     combine_done = true;
+  } else if (fp8_prefill) {
+    UmmaFp8PrefillLaunch a{};
+    a.tiles = tiles;
+    a.num_tiles = num_tiles;
+    a.dtype = c.dtype;
+    a.grid = l->sm_count;
+    a.row_weight = row_weight;
+    a.n_routed_rows = T * k;
+    a.scale_ld = R_cap;
+    // gate_up + SiLU*mul + e4m3 re-quantisation (the activation rows exist only in e4m3)
+    a.tm_w = &l->tm_w_gu;
+    a.tm_x = &l->tm_x[bi];
+    a.w_scale = l->s_gate_up;
+    a.x_scale_t = reinterpret_cast<const float*>(ws + L.sx);
+    a.out = nullptr;
+    a.ld_out = I;
+    a.out_q = ws + L.actq;
+    a.out_scale_t = reinterpret_cast<float*>(ws + L.sact);
+    a.n_feat_tiles = I / 128;
+    a.n_kblocks = H / 128;
+    a.w_rows_per_expert = 2 * I;
+    a.up_row_offset = I;
+    a.gated = 1;
+    a.sched = reinterpret_cast<int32_t*>(ws + L.sched);
+    if ((rc = umma_fp8_prefill_launch(a, stream))) return rc;
+    STAGE_MARK(5);
+    // down * routing weight
+    a.tm_w = &l->tm_w_d;
+    a.tm_x = &l->tm_act[bi];
+    a.w_scale = l->s_down;
+    a.x_scale_t = reinterpret_cast<const float*>(ws + L.sact);
+    a.out = y;
+    a.ld_out = H;
+    a.out_q = nullptr;
+    a.out_scale_t = nullptr;
+    a.n_feat_tiles = H / 256;
+    a.n_kblocks = I / 128;
+    a.w_rows_per_expert = H;
+    a.up_row_offset = 0;
+    a.gated = 0;
+    a.sched = reinterpret_cast<int32_t*>(ws + L.sched) + 2;
+    if ((rc = umma_fp8_prefill_launch(a, stream))) return rc;
   } else if (fp8) {
     UmmaFp8Launch a{};
     a.tiles = tiles;

@@ -329,6 +329,53 @@ __global__ void __launch_bounds__(256) quant_rows_fp8_kernel(
   }
 }
 
+// Token-major variant for the first GEMM's input: every token is quantised ONCE (same formula) and its
+// e4m3 row + scales are written to each of its k expert-major rows and its shared-expert row
+// (slot_row[t, j] = row of (token t, slot j), -1 = expert not on this rank).  The row-major kernel above
+// re-quantises a token k+1 times; at prefill that made the quantiser cost as much as a GEMM stage.
+template <typename T>
+__global__ void __launch_bounds__(256) quant_scatter_fp8_kernel(
+    const T* __restrict__ x, int K, const int32_t* __restrict__ slot_row, int T_tokens, int k, int sh_lo,
+    int sh_hi, uint8_t* __restrict__ dst, float* __restrict__ scale_t, int scale_ld) {
+  pdl_wait();
+  pdl_launch();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int t = blockIdx.x * 8 + warp;
+  if (t >= T_tokens) return;
+  // lane j < k: row of slot j; lane k: the shared-expert row
+  int my_row = -1;
+  if (lane < k) my_row = slot_row[static_cast<size_t>(t) * k + lane];
+  else if (lane == k && t >= sh_lo && t < sh_hi) my_row = T_tokens * k + t;
+  const T* s = x + static_cast<size_t>(t) * K;
+  for (int c0 = 0; c0 < K; c0 += 256) {
+    const int c = c0 + lane * 8;
+    const bool ok = c < K;
+    float v[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) v[q] = 0.f;
+    if (ok) unpack16<T>(ld_cached16(s + c), v);
+    float amax = 0.f;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) amax = fmaxf(amax, fabsf(v[q]));
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+    const float scale = __fdiv_rn(fmaxf(amax, 1e-10f), 448.0f);
+    uint32_t lo = 0, hi = 0;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      lo |= static_cast<uint32_t>(__nv_cvt_float_to_fp8(__fdiv_rn(v[q], scale), __NV_SATFINITE, __NV_E4M3)) << (8 * q);
+      hi |= static_cast<uint32_t>(__nv_cvt_float_to_fp8(__fdiv_rn(v[4 + q], scale), __NV_SATFINITE, __NV_E4M3)) << (8 * q);
+    }
+    for (int j = 0; j <= k; ++j) {
+      const int row = __shfl_sync(0xffffffffu, my_row, j);
+      if (row >= 0 && ok) {
+        *reinterpret_cast<uint2*>(dst + static_cast<size_t>(row) * K + c) = make_uint2(lo, hi);
+        if ((lane & 15) == 0) scale_t[static_cast<size_t>(c / 128) * scale_ld + row] = scale;
+      }
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------
@@ -410,6 +457,25 @@ int quant_rows_fp8(const void* src, int src_ld, const int32_t* row_token, const 
     GLM4MOE_CUDA_CHECK(launch_pdl(quant_rows_fp8_kernel<__half>, dim3((rows + 7) / 8), dim3(256), 0, st,
                                   static_cast<const __half*>(src), src_ld, row_token, expert_offsets, E, T, k, K,
                                   sh_lo, sh_hi, static_cast<uint8_t*>(dst), scale_t, scale_ld));
+  } else {
+    return GLM4MOE_ERR_UNSUPPORTED;
+  }
+  return GLM4MOE_OK;
+}
+
+int quant_scatter_fp8(const void* x, int K, const int32_t* slot_row, int T, int k, int sh_lo, int sh_hi, void* dst,
+                      float* scale_t, int scale_ld, int dtype, void* stream) {
+  if (K % 128 != 0 || k >= 32) return GLM4MOE_ERR_UNSUPPORTED;
+  if (T <= 0) return GLM4MOE_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (dtype == GLM4MOE_BF16) {
+    GLM4MOE_CUDA_CHECK(launch_pdl(quant_scatter_fp8_kernel<__nv_bfloat16>, dim3((T + 7) / 8), dim3(256), 0, st,
+                                  static_cast<const __nv_bfloat16*>(x), K, slot_row, T, k, sh_lo, sh_hi,
+                                  static_cast<uint8_t*>(dst), scale_t, scale_ld));
+  } else if (dtype == GLM4MOE_F16) {
+    GLM4MOE_CUDA_CHECK(launch_pdl(quant_scatter_fp8_kernel<__half>, dim3((T + 7) / 8), dim3(256), 0, st,
+                                  static_cast<const __half*>(x), K, slot_row, T, k, sh_lo, sh_hi,
+                                  static_cast<uint8_t*>(dst), scale_t, scale_ld));
   } else {
     return GLM4MOE_ERR_UNSUPPORTED;
   }

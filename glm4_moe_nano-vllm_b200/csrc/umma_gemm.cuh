@@ -121,5 +121,35 @@ int umma_fp8_launch(const UmmaFp8Launch& args, void* stream);
 int quant_rows_fp8(const void* src, int src_ld, const int32_t* row_token, const int32_t* expert_offsets, int E,
                    int T, int k, int K, int sh_lo, int sh_hi, void* dst, float* scale_t, int scale_ld, int dtype,
                    void* stream);
+// layer input -> e4m3 rows, each token quantised once and written to its k expert rows + shared row
+int quant_scatter_fp8(const void* x, int K, const int32_t* slot_row, int T, int k, int sh_lo, int sh_hi, void* dst,
+                      float* scale_t, int scale_ld, int dtype, void* stream);
+
+// ---- FP8 tier, prefill geometry (umma_fp8_prefill.cu): token rows = MMA M (128), weight rows = N (256) ----
+struct UmmaFp8PrefillLaunch {
+  const void* tm_w;          // e4m3 weight stack (uint8), box {128 bytes, 128 rows}
+  const void* tm_x;          // e4m3 activation rows, box {128 bytes, 128 rows}
+  const float* w_scale;      // [n_stack, w_rows_per_expert/128, K/128]
+  const float* x_scale_t;    // [K/128, scale_ld]
+  int scale_ld;
+  const int32_t* tiles;      // 128-row tiles (permute with tile_rows = 128)
+  const int32_t* num_tiles;
+  void* out;                 // down: y rows [R, H] model dtype
+  int ld_out;                // down: H; gate_up: I (row pitch of out_q in bytes)
+  void* out_q;               // gate_up: e4m3 activation rows [R, I]
+  float* out_scale_t;        // gate_up: [I/128, scale_ld]
+  const float* row_weight;
+  int n_routed_rows;
+  int n_feat_tiles;          // gate_up: I/128; down: H/256
+  int n_kblocks;             // K / 128
+  int w_rows_per_expert;     // gate_up: 2I; down: H
+  int up_row_offset;         // gate_up: I
+  int gated;
+  int dtype;
+  int grid;
+  int32_t* sched;
+};
+bool umma_fp8_prefill_shape_ok(int H, int I);
+int umma_fp8_prefill_launch(const UmmaFp8PrefillLaunch& args, void* stream);
 
 }  // namespace glm4moe

@@ -58,8 +58,10 @@ int glm4moe_abi_version(void);
  * GLM4MOE_KNOB_DIRECT: 1 (default) = decode batches T <= 32 use the fused front-end and read the
  * input tokens in place; 0 = always the general router / permute / gather sequence.
  * GLM4MOE_KNOB_FUSED: 1 (default) = inside direct mode, gate_up and down run as one persistent kernel
- * (decode_fused.cu); 0 = two grouped-GEMM launches.                                              */
-enum { GLM4MOE_KNOB_DIRECT = 0, GLM4MOE_KNOB_FUSED = 1 };
+ * (decode_fused.cu); 0 = two grouped-GEMM launches.
+ * GLM4MOE_KNOB_FP8_PREFILL: 1 (default) = the e4m3 tier uses token-major 128 x 256 tiles once an expert
+ * averages >= 48 rows (umma_fp8_prefill.cu); 0 = always the 16..64-token swap-AB tiles (umma_fp8.cu). */
+enum { GLM4MOE_KNOB_DIRECT = 0, GLM4MOE_KNOB_FUSED = 1, GLM4MOE_KNOB_FP8_PREFILL = 2 };
 int glm4moe_debug_set(int knob, int value);
 const char* glm4moe_error_string(int code);
 
