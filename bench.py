@@ -13,7 +13,8 @@ A "step" is one forward of the sparse-expert block over one batch of T synthetic
 
 `--impl reference` times the reference's CPU torch path (oracle port — the reference itself
 cannot travel to the GPU box) on the same workload.  N>1: expert-parallel (experts sharded over
-ranks, tokens replicated, partial outputs all-reduced over NCCL/NVLink), strong scaling.
+ranks, tokens replicated; the weighted expert rows are combined and reduced across ranks by one kernel
+reading NVLink peer memory, `--ep-layout allreduce` = NCCL instead), strong scaling.
 """
 from __future__ import annotations
 
@@ -129,8 +130,9 @@ def main():
     ap.add_argument("--sweep", action="store_true", help="also report T in {1..256, 4096} in `sweep`")
     ap.add_argument("--cpu-steps", type=int, default=0, help="cpu_baseline steps (0 = about 15 s of CPU work)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--ep-layout", default="allreduce", choices=["allreduce", "alltoall"],
-                    help="expert-parallel layout for --gpus > 1 (distributed.py)")
+    ap.add_argument("--ep-layout", default="p2p", choices=["p2p", "allreduce", "alltoall"],
+                    help="expert-parallel layout for --gpus > 1 (distributed.py): p2p = combine + reduction in "
+                         "one kernel over NVLink peer memory, allreduce / alltoall = NCCL")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -177,7 +179,8 @@ def main():
 
     torch.set_default_dtype(dt)
     torch.set_default_device(dev)
-    moe = glm4_moe_b200.Glm4MoeMoE(_hf_config(shape), max_tokens=max(T, 256), ep_rank=rank, ep_size=world)
+    moe = glm4_moe_b200.Glm4MoeMoE(_hf_config(shape), max_tokens=max(T, 256), ep_rank=rank, ep_size=world,
+                                   peer_workspace=(world > 1 and args.ep_layout == "p2p"))
     torch.set_default_device("cpu")
     torch.set_default_dtype(torch.float32)
     weights = synth.make_weights_device(shape, dt, dev, experts=range(moe.expert_begin, moe.expert_end))
@@ -185,6 +188,8 @@ def main():
     if world > 1:
         from glm4_moe_b200.distributed import ExpertParallelMoE
         layer = ExpertParallelMoE(moe, shape.E, layout=args.ep_layout)
+        if args.ep_layout == "p2p":
+            layer.setup_p2p()
     else:
         layer = moe
     batches_host = [synth.make_tokens(shape, T, dt, b).pin_memory() for b in range(N_BATCHES)]
@@ -287,6 +292,8 @@ def main():
                               "GBps": by / ms / 1e6, "TFLOPs": fl / ms / 1e9,
                               "tile_rows": moe.last_impl})
 
+    if world > 1 and args.ep_layout == "p2p":
+        layer.close_p2p()
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()

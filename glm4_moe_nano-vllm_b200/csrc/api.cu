@@ -10,6 +10,7 @@
 
 #include "common.cuh"
 #include "umma_gemm.cuh"
+#include "ep_combine.cuh"
 
 using namespace glm4moe;
 
@@ -50,7 +51,7 @@ inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct WsLayout {
   size_t logits, idx, w, offsets, row_token, row_weight, slot_row, num_tiles, sched, ready, fdone, tiles, scratch, x_rows,
-      act, y, xq, sx, actq, sact, total;
+      act, y, xq, sx, actq, sact, ctl, total;
   int tile_capacity;
 };
 
@@ -90,6 +91,7 @@ WsLayout make_layout(const glm4moe_config_t& c) {
     L.actq = take(R * I);
     L.sact = take(((I + 127) / 128) * R * 4);
   }
+  L.ctl = take(kEpCtlBytes);   // peer-memory combine: epoch, ticket, ready / done flags (ep_combine.cu)
   L.total = off;
   return L;
 }
@@ -206,7 +208,8 @@ extern "C" int glm4moe_layer_create(const glm4moe_config_t* cfg, const void* gat
   l->events_ready = false;
   if (cudaMemset(l->ws + L.sched, 0, 256) != cudaSuccess ||
       cudaMemset(l->ws + L.ready, 0, (cfg->n_routed_experts + 8) * 4) != cudaSuccess ||
-      cudaMemset(l->ws + L.fdone, 0, (cfg->hidden_size / 128 + 8) * 4) != cudaSuccess) {
+      cudaMemset(l->ws + L.fdone, 0, (cfg->hidden_size / 128 + 8) * 4) != cudaSuccess ||
+      cudaMemset(l->ws + L.ctl, 0, kEpCtlBytes) != cudaSuccess) {
     delete l;
     return GLM4MOE_ERR_DEVICE;
   }
@@ -292,8 +295,10 @@ extern "C" int glm4moe_layer_tile_rows(const glm4moe_layer_t* l, int T) {
 }
 
 static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, void* stream, cudaEvent_t* ev,
-                        int sh_lo_arg = -1, int sh_hi_arg = -1) {
-  if (!l || !x || !out) return GLM4MOE_ERR_ARG;
+                        int sh_lo_arg = -1, int sh_hi_arg = -1, bool rows_only = false) {
+  // rows_only: stop after the weighted expert rows y (no combine, `out` unused): the peer-memory
+  // expert-parallel combine (ep_combine.cu) reads the rows of every rank
+  if (!l || !x || (!out && !rows_only)) return GLM4MOE_ERR_ARG;
   cudaStream_t cst = static_cast<cudaStream_t>(stream);
 #define STAGE_MARK(i)                                        \
   do {                                                       \
@@ -442,7 +447,7 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
     f.sched = reinterpret_cast<int32_t*>(ws + L.sched) + 16;
     f.ready = reinterpret_cast<int32_t*>(ws + L.ready);
     f.slot_row = slot_row;
-    f.out = out;
+    f.out = rows_only ? nullptr : out;
     f.k = k;
     f.fdone = reinterpret_cast<int32_t*>(ws + L.fdone);
     {
@@ -604,7 +609,7 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
       return rc;
   }
   STAGE_MARK(6);
-  if (!combine_done && (rc = glm4moe_combine(y, slot_row, out, T, k, H, sh_lo, sh_hi, c.dtype, stream))) return rc;
+  if (!combine_done && !rows_only && (rc = glm4moe_combine(y, slot_row, out, T, k, H, sh_lo, sh_hi, c.dtype, stream))) return rc;
   STAGE_MARK(7);
 #undef STAGE_MARK
   l->last_launches = g_launches - launches0;
@@ -684,3 +689,80 @@ extern "C" int glm4moe_layer_view(glm4moe_layer_t* l, int which, void** ptr, siz
 extern "C" int glm4moe_layer_last_launches(const glm4moe_layer_t* l) { return l ? l->last_launches : 0; }
 extern "C" int glm4moe_layer_last_impl(const glm4moe_layer_t* l) { return l ? l->last_impl : 0; }
 extern "C" int glm4moe_layer_last_fused(const glm4moe_layer_t* l) { return l ? l->last_fused : 0; }
+
+// ---- expert parallelism over peer memory (distributed.py layout "p2p") -------------------------
+extern "C" int glm4moe_p2p_alloc(size_t bytes, void** ptr, unsigned char* handle64) {
+  if (!ptr || !handle64 || bytes == 0) return GLM4MOE_ERR_ARG;
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  void* p = nullptr;
+  GLM4MOE_CUDA_CHECK(cudaMalloc(&p, bytes));
+  cudaError_t e = cudaMemset(p, 0, bytes);
+  cudaIpcMemHandle_t h;
+  if (e == cudaSuccess) e = cudaIpcGetMemHandle(&h, p);
+  if (e != cudaSuccess) {
+    cudaFree(p);
+    return static_cast<int>(e);
+  }
+  memcpy(handle64, &h, 64);
+  *ptr = p;
+  return GLM4MOE_OK;
+}
+
+extern "C" int glm4moe_p2p_open(const unsigned char* handle64, void** peer_ptr) {
+  if (!handle64 || !peer_ptr) return GLM4MOE_ERR_ARG;
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, 64);
+  GLM4MOE_CUDA_CHECK(cudaIpcOpenMemHandle(peer_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return GLM4MOE_OK;
+}
+
+extern "C" int glm4moe_p2p_close(void* peer_ptr) {
+  if (!peer_ptr) return GLM4MOE_ERR_ARG;
+  GLM4MOE_CUDA_CHECK(cudaIpcCloseMemHandle(peer_ptr));
+  return GLM4MOE_OK;
+}
+
+extern "C" int glm4moe_p2p_free(void* ptr) {
+  if (!ptr) return GLM4MOE_ERR_ARG;
+  GLM4MOE_CUDA_CHECK(cudaFree(ptr));
+  return GLM4MOE_OK;
+}
+
+extern "C" int glm4moe_layer_forward_ep_p2p(glm4moe_layer_t* l, const void* x, void* out, int T,
+                                            void* const* peer_workspaces, int rank, int world, void* stream) {
+  if (!l || !x || !out || !peer_workspaces) return GLM4MOE_ERR_ARG;
+  const glm4moe_config_t& c = l->cfg;
+  const int n_local = c.expert_end - c.expert_begin;
+  if (world < 1 || world > kEpMaxRanks || rank < 0 || rank >= world || n_local <= 0 ||
+      n_local * world != c.n_routed_experts || c.expert_begin != rank * n_local)
+    return GLM4MOE_ERR_ARG;
+  if (c.num_experts_per_tok > kEpMaxTopK || c.dtype == GLM4MOE_F32 || c.with_shared == 1 && world > 1)
+    return GLM4MOE_ERR_UNSUPPORTED;
+  if (peer_workspaces[rank] != l->ws) return GLM4MOE_ERR_ARG;
+  if (T < 0 || T > c.max_tokens) return GLM4MOE_ERR_ARG;
+  if (T == 0) return GLM4MOE_OK;
+  const int launches0 = g_launches;
+  int rc = forward_impl(l, x, nullptr, T, stream, nullptr, -1, -1, /*rows_only=*/true);
+  if (rc) return rc;
+  EpCombineArgs a{};
+  for (int r = 0; r < world; ++r) {
+    if (!peer_workspaces[r]) return GLM4MOE_ERR_ARG;
+    a.ws[r] = static_cast<unsigned char*>(peer_workspaces[r]);
+  }
+  a.off_y = l->L.y;
+  a.off_slot_row = l->L.slot_row;
+  a.off_idx = l->L.idx;
+  a.off_ctl = l->L.ctl;
+  a.rank = rank;
+  a.world = world;
+  a.tokens = T;
+  a.k = c.num_experts_per_tok;
+  a.H = c.hidden_size;
+  a.experts_per_rank = n_local;
+  a.with_shared = c.with_shared != 0;
+  a.shared_per_rank = (T + world - 1) / world;
+  if (c.with_shared == 1) a.shared_per_rank = T;   // world == 1: every shared row is local
+  rc = ep_combine_p2p_launch(a, out, c.dtype, stream);
+  l->last_launches = g_launches - launches0;
+  return rc;
+}

@@ -460,7 +460,7 @@ __global__ void __launch_bounds__(FusedCfg<BN, FP8>::kThreads, 1) decode_fused_k
     auto resolve = [&]() {
       if (pend_f < 0) return;                           // uniform over the epilogue warps
       const int last = reinterpret_cast<volatile int32_t*>(s_last)[pend_slot];
-      if (last) combine_f(pend_f);
+      if (last && out != nullptr) combine_f(pend_f);   // out == nullptr: rows only (peer-memory combine follows)
       pend_f = -1;
       pend_slot ^= 1;
     };
@@ -470,7 +470,8 @@ __global__ void __launch_bounds__(FusedCfg<BN, FP8>::kThreads, 1) decode_fused_k
       if (w < 0) break;
       if (w >= kZeroBase && w < kSharedBase) {
         const int col = (w - kZeroBase) * kBM + 4 * lane;
-        for (int t = ewi; t < tokens; t += EW) *reinterpret_cast<uint2*>(out + static_cast<size_t>(t) * H + col) = make_uint2(0u, 0u);
+        if (out != nullptr)
+          for (int t = ewi; t < tokens; t += EW) *reinterpret_cast<uint2*>(out + static_cast<size_t>(t) * H + col) = make_uint2(0u, 0u);
         continue;
       }
       if ((FP8 || w < kSharedBase) && !dep_waited) {   // e4m3: the token scales are the router kernel's output

@@ -1,0 +1,161 @@
+// Expert-parallel combine over NVLink peer memory: the weighted un-permute / accumulate of the
+// reference (moe.py:149-151,171) and the cross-GPU reduction in ONE kernel, no NCCL call.
+//
+// Layout "p2p" (distributed.py): tokens are replicated, rank r owns experts [r*E/R, (r+1)*E/R) and
+// has just written the weighted expert outputs of ITS experts as rows of its own workspace
+// (y[row, H], row = slot_row[t, j]; shared-expert rows T*k + t on the rank that owns token t's
+// slice).  Every rank's workspace is one cudaMalloc'd region mapped into all peers (cudaIpc), with
+// identical layout.  For each token this kernel walks the k slots in ascending expert order (=
+// ascending owner rank), reads each row from its owner's memory (local or over NVLink), adds the
+// shared row, accumulates in fp32 and rounds once: the same order and rounding as the single-GPU
+// combine_kernel, so an expert-parallel forward is BIT-IDENTICAL to the single-GPU forward and
+// every rank ends with the full replicated [T, H] (the all-reduce is implicit in the reads).
+//
+// Cross-GPU ordering (epoch e = calls so far + 1, kept in the workspace, CUDA-graph-replay safe):
+//   ready: block 0 thread p stores e into peer p's ready[me] (st.release.sys); every block spins on
+//          its own ready[0..R) >= e before the first peer read  -> the peer's rows are complete
+//          (they were written by the peer's previous kernel in stream order).
+//   done:  the last block of the grid (ticket) stores e into every peer's done[me] and spins on its
+//          own done[0..R) >= e before the grid retires -> nobody overwrites y / slot_row (next
+//          forward) while a peer still reads them.
+#include "common.cuh"
+#include "ep_combine.cuh"
+
+namespace glm4moe {
+
+namespace {
+
+__device__ __forceinline__ void st_release_sys(int32_t* p, int32_t v) {
+  asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ int32_t ld_acquire_sys(const int32_t* p) {
+  int32_t v;
+  asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint4 ld_peer16(const void* p) {   // L1-bypassing 128-bit load (peer or local)
+  uint4 r;
+  asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ int32_t ld_peer_s32(const int32_t* p) {
+  int32_t v;
+  asm volatile("ld.global.cg.s32 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
+}
+
+}  // namespace
+
+template <typename T>
+__global__ void __launch_bounds__(kEpThreads) ep_combine_p2p_kernel(const EpCombineArgs a, T* __restrict__ out) {
+  constexpr int V = Dt<T>::kVec;   // 8 two-byte elements per 16-byte vector
+  __shared__ int32_t s_row[kEpMaxTopK + 1];
+  __shared__ int32_t s_owner[kEpMaxTopK + 1];
+  __shared__ int s_last;
+  pdl_wait();      // the local rows are the direct predecessor's output
+  pdl_launch();
+  unsigned char* my_ws = a.ws[a.rank];
+  int32_t* ctl = reinterpret_cast<int32_t*>(my_ws + a.off_ctl);   // [0] epoch, [1] blocks done, [16..] ready, [32..] done
+  const int e = *reinterpret_cast<volatile int32_t*>(ctl) + 1;
+  // ---- ready: tell every peer our rows exist, wait until theirs do ----
+  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x < a.world) {
+    __threadfence_system();
+    int32_t* peer_ctl = reinterpret_cast<int32_t*>(a.ws[threadIdx.x] + a.off_ctl);
+    st_release_sys(peer_ctl + 16 + a.rank, e);
+  }
+  if (threadIdx.x < a.world) {
+    while (ld_acquire_sys(ctl + 16 + threadIdx.x) < e) {
+    }
+  }
+  __syncthreads();
+
+  // ---- reduce: block (x = column chunk, y strides over tokens) ----
+  const int col = (blockIdx.x * kEpThreads + threadIdx.x) * V;
+  const int32_t* my_idx = reinterpret_cast<const int32_t*>(my_ws + a.off_idx);
+  for (int t = blockIdx.y; t < a.tokens; t += gridDim.y) {
+    // slot j -> (owner rank, row on the owner); the shared expert's row lives on the rank owning t's slice
+    if (threadIdx.x <= a.k) {
+      int owner, row;
+      if (threadIdx.x < a.k) {
+        const int ex = my_idx[static_cast<size_t>(t) * a.k + threadIdx.x];
+        owner = ex / a.experts_per_rank;
+        row = ld_peer_s32(reinterpret_cast<const int32_t*>(a.ws[owner] + a.off_slot_row) +
+                          static_cast<size_t>(t) * a.k + threadIdx.x);
+      } else {
+        owner = a.with_shared ? min(t / a.shared_per_rank, a.world - 1) : 0;
+        row = a.with_shared ? a.tokens * a.k + t : -1;
+      }
+      s_owner[threadIdx.x] = owner;
+      s_row[threadIdx.x] = row;
+    }
+    __syncthreads();
+    if (col < a.H) {
+      float acc[V];
+#pragma unroll
+      for (int i = 0; i < V; ++i) acc[i] = 0.f;
+      uint4 raw[kEpMaxTopK + 1];
+      // all loads first (independent NVLink round trips in flight), then the ordered fp32 sum
+#pragma unroll
+      for (int j = 0; j <= kEpMaxTopK; ++j) {
+        if (j <= a.k && s_row[j] >= 0)
+          raw[j] = ld_peer16(a.ws[s_owner[j]] + a.off_y +
+                             (static_cast<size_t>(s_row[j]) * a.H + col) * sizeof(T));
+      }
+#pragma unroll
+      for (int j = 0; j <= kEpMaxTopK; ++j) {
+        if (j <= a.k && s_row[j] >= 0) {
+          float v[V];
+          unpack16<T>(raw[j], v);
+#pragma unroll
+          for (int i = 0; i < V; ++i) acc[i] += v[i];
+        }
+      }
+      __align__(16) T o[V];
+#pragma unroll
+      for (int i = 0; i < V; ++i) o[i] = Dt<T>::from_f(acc[i]);
+      *reinterpret_cast<uint4*>(out + static_cast<size_t>(t) * a.H + col) = *reinterpret_cast<uint4*>(o);
+    }
+    __syncthreads();
+  }
+
+  // ---- done: the last block tells every peer we no longer read, and waits for theirs ----
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const int total = static_cast<int>(gridDim.x * gridDim.y);
+    s_last = atomicAdd(ctl + 1, 1) == total - 1;
+  }
+  __syncthreads();
+  if (!s_last) return;
+  if (threadIdx.x < a.world) {
+    int32_t* peer_ctl = reinterpret_cast<int32_t*>(a.ws[threadIdx.x] + a.off_ctl);
+    st_release_sys(peer_ctl + 32 + a.rank, e);
+    while (ld_acquire_sys(ctl + 32 + threadIdx.x) < e) {
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    ctl[1] = 0;
+    *reinterpret_cast<volatile int32_t*>(ctl) = e;
+    __threadfence();
+  }
+}
+
+int ep_combine_p2p_launch(const EpCombineArgs& a, void* out, int dtype, void* stream) {
+  if (a.world < 1 || a.world > kEpMaxRanks || a.k > kEpMaxTopK || a.rank < 0 || a.rank >= a.world)
+    return GLM4MOE_ERR_ARG;
+  if (dtype != GLM4MOE_BF16 && dtype != GLM4MOE_F16) return GLM4MOE_ERR_UNSUPPORTED;
+  if (a.H % 8 != 0 || a.tokens <= 0) return GLM4MOE_ERR_ARG;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int gx = (a.H / 8 + kEpThreads - 1) / kEpThreads;
+  int gy = a.tokens < 128 ? a.tokens : 128;
+  dim3 grid(gx, gy);
+  if (dtype == GLM4MOE_BF16)
+    GLM4MOE_CUDA_CHECK(launch_pdl(ep_combine_p2p_kernel<__nv_bfloat16>, grid, dim3(kEpThreads), 0, st, a,
+                                  static_cast<__nv_bfloat16*>(out)));
+  else
+    GLM4MOE_CUDA_CHECK(launch_pdl(ep_combine_p2p_kernel<__half>, grid, dim3(kEpThreads), 0, st, a,
+                                  static_cast<__half*>(out)));
+  return GLM4MOE_OK;
+}
+
+}  // namespace glm4moe

@@ -7,7 +7,15 @@ north_star puts in `nanovllm/distributed`: experts are sharded contiguously, ran
 `[r*E/R, (r+1)*E/R)`; the router weights are replicated and routing is recomputed identically
 on every rank (deterministic kernels), so no routing metadata is exchanged.
 
-Two layouts:
+Three layouts:
+
+* ``p2p`` (layout A over peer memory, the default on GPUs of one box) — tokens replicated like
+  ``allreduce``; every rank's layer workspace is a cudaIpc-shared region, and after the local experts
+  ONE kernel per rank reads, for every token, its k weighted expert rows (+ the shared-expert row)
+  from the ranks that own them over NVLink and sums them in ascending expert order in fp32
+  (`csrc/ep_combine.cu`).  No NCCL call on the data path, CUDA-graph capturable, and the result is
+  bit-identical to the single-GPU block.  The handles are exchanged once, on the host, with
+  `all_gather_object`.
 
 * ``allreduce`` (layout A) — activations entering the block are replicated (TP attention ends
   in an all-reduce).  Each rank runs its local experts over all T tokens plus the shared expert
@@ -57,7 +65,7 @@ def dispatch_plan(idx: torch.Tensor, n_experts: int, world: int):
 class ExpertParallelMoE(nn.Module):
     def __init__(self, local_moe: nn.Module, n_experts: int, group=None, layout: str = "allreduce"):
         super().__init__()
-        if layout not in ("allreduce", "alltoall"):
+        if layout not in ("allreduce", "alltoall", "p2p"):
             raise ValueError(layout)
         self.local = local_moe
         self.n_experts = n_experts
@@ -65,12 +73,51 @@ class ExpertParallelMoE(nn.Module):
         self.layout = layout
         self.rank = dist.get_rank(group)
         self.world = dist.get_world_size(group)
+        self._peer_bases = None      # ctypes array of every rank's workspace base (layout "p2p")
+        self._peer_opened = []
+
+    # ---- layout "p2p": one-time handle exchange ---------------------------------------------------
+    def setup_p2p(self, max_tokens: int | None = None) -> None:
+        """Collective: allocate / export the local workspace, exchange the cudaIpc handles on the host
+        and map every peer's workspace.  Called by the first forward if not done explicitly."""
+        import ctypes as C
+        from . import _lib
+        handle, off = self.local.ipc_handle(max_tokens)
+        gathered = [None] * self.world
+        dist.all_gather_object(gathered, (handle, off), group=self.group)
+        lib = _lib.load()
+        bases = (C.c_void_p * self.world)()
+        for r, (h, o) in enumerate(gathered):
+            if r == self.rank:
+                bases[r] = self.local.workspace_base()
+                continue
+            ptr = C.c_void_p()
+            with torch.cuda.device(self.local.gate.weight.device):
+                _lib.check(lib.glm4moe_p2p_open(h, C.byref(ptr)), "p2p_open")
+            self._peer_opened.append(ptr.value)
+            bases[r] = ptr.value + o
+        self._peer_bases = bases
+        dist.barrier(group=self.group)     # nobody launches before every mapping exists
+
+    def close_p2p(self) -> None:
+        from . import _lib
+        if self._peer_opened:
+            torch.cuda.synchronize()
+            dist.barrier(group=self.group)
+            for p in self._peer_opened:
+                _lib.load().glm4moe_p2p_close(p)
+        self._peer_opened, self._peer_bases = [], None
+
+    def _forward_p2p(self, h: torch.Tensor) -> torch.Tensor:
+        if self._peer_bases is None:
+            self.setup_p2p()
+        return self.local.forward_ep_p2p(h, self._peer_bases)
 
     @classmethod
     def build(cls, config, group=None, layout: str = "allreduce", **kw) -> "ExpertParallelMoE":
         from .moe import Glm4MoeMoE
         rank, world = dist.get_rank(group), dist.get_world_size(group)
-        local = Glm4MoeMoE(config, ep_rank=rank, ep_size=world, **kw)
+        local = Glm4MoeMoE(config, ep_rank=rank, ep_size=world, peer_workspace=(layout == "p2p"), **kw)
         return cls(local, config.n_routed_experts, group, layout)
 
     # ---- layout A --------------------------------------------------------------------------
@@ -126,6 +173,8 @@ class ExpertParallelMoE(nn.Module):
 
     def forward(self, hidden_states: torch.Tensor) -> torch.Tensor:
         h = hidden_states.reshape(-1, hidden_states.shape[-1])
+        if self.layout == "p2p":
+            return self._forward_p2p(h)
         if self.layout == "allreduce":
             return self._forward_allreduce(h)
         return self._forward_alltoall(h)

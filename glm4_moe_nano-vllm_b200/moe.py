@@ -116,6 +116,14 @@ class GlmMoeSelectTopk(nn.Module):
         return out + (logits,) if return_logits else out
 
 
+class _ForeignCudaBuffer:
+    """uint8 view of device memory the CUDA library allocated (zero-copy via __cuda_array_interface__)."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 3,
+                                         "strides": None}
+
+
 class Glm4MoeMoE(nn.Module):
     """GLM4-MoE sparse block (moe.py:52-176).
 
@@ -128,7 +136,7 @@ class Glm4MoeMoE(nn.Module):
     """
 
     def __init__(self, config, *, max_tokens: int = 256, ep_rank: int = 0, ep_size: int = 1,
-                 impl: str = "auto"):
+                 impl: str = "auto", peer_workspace: bool = False):
         super().__init__()
         self.config = config
         E, H, I = config.n_routed_experts, config.hidden_size, config.moe_intermediate_size
@@ -140,6 +148,11 @@ class Glm4MoeMoE(nn.Module):
         # single GPU: shared expert on every token; expert-parallel: on this rank's 1/R token slice
         self.with_shared = 1 if ep_size == 1 else 2
         self.impl = impl
+        # peer_workspace: the layer workspace is a cudaMalloc'd, IPC-exportable region (fixed capacity)
+        # that the other expert-parallel ranks map and read (distributed.py layout "p2p")
+        self.peer_workspace = bool(peer_workspace)
+        self._ipc_ptr = None
+        self._ipc_handle = None
         n_local = self.expert_end - self.expert_begin
         # stacked storage, created under the process-wide default dtype/device like the
         # reference's parameters (model_runner.py:29-31)
@@ -181,6 +194,10 @@ class Glm4MoeMoE(nn.Module):
         self._handle = None
         self._workspace = None
         self._host = None
+        if getattr(self, "_ipc_ptr", None):
+            _lib.load().glm4moe_p2p_free(self._ipc_ptr)
+        self._ipc_ptr = None
+        self._ipc_handle = None
 
     def __del__(self):
         try:
@@ -204,6 +221,10 @@ class Glm4MoeMoE(nn.Module):
         if torch.cuda.is_current_stream_capturing():
             raise _lib.Glm4MoeLibraryError(
                 f"workspace for {T} tokens must exist before CUDA-graph capture (run a warm-up forward first)")
+        if self.peer_workspace and self._handle is not None:
+            raise _lib.Glm4MoeLibraryError(
+                f"peer-mapped workspace holds {self._max_tokens} tokens, got {T}: it is mapped by the other "
+                "ranks and cannot grow; construct the block with a larger max_tokens")
         self._destroy_handle()
         cap = max(self._max_tokens, 1)
         while cap < T:
@@ -214,7 +235,14 @@ class Glm4MoeMoE(nn.Module):
         if nbytes == 0:
             raise _lib.Glm4MoeLibraryError("unsupported GLM4-MoE configuration for the CUDA library")
         dev = self.gate.weight.device
-        self._workspace = torch.empty(nbytes + 1024, dtype=torch.uint8, device=dev)
+        if self.peer_workspace:
+            ptr, hbuf = C.c_void_p(), C.create_string_buffer(64)
+            with torch.cuda.device(dev):
+                _lib.check(lib.glm4moe_p2p_alloc(nbytes + 1024, C.byref(ptr), hbuf), "p2p_alloc")
+            self._ipc_ptr, self._ipc_handle = ptr.value, hbuf.raw
+            self._workspace = torch.as_tensor(_ForeignCudaBuffer(ptr.value, nbytes + 1024), device=dev)
+        else:
+            self._workspace = torch.empty(nbytes + 1024, dtype=torch.uint8, device=dev)
         base = (self._workspace.data_ptr() + 1023) // 1024 * 1024
         handle = C.c_void_p()
         if self.weight_format == "fp8":
@@ -431,3 +459,36 @@ class Glm4MoeMoE(nn.Module):
     def last_fused(self) -> bool:
         """True when the last forward ran the experts as the single persistent decode kernel."""
         return bool(_lib.load().glm4moe_layer_last_fused(self._handle)) if self._handle else False
+
+    # ---- expert parallelism over peer memory (distributed.py layout "p2p") -------------------------
+    def ipc_handle(self, max_tokens: int | None = None) -> tuple[bytes, int]:
+        """(64-byte cudaIpc handle of the workspace allocation, offset of the 1 KB-aligned workspace base)."""
+        if not self.peer_workspace:
+            raise _lib.Glm4MoeLibraryError("construct the block with peer_workspace=True")
+        self._ensure_layer(max_tokens or self._max_tokens)
+        base = (self._ipc_ptr + 1023) // 1024 * 1024
+        return self._ipc_handle, base - self._ipc_ptr
+
+    def workspace_base(self) -> int:
+        return (self._workspace.data_ptr() + 1023) // 1024 * 1024
+
+    def forward_ep_p2p(self, hidden_states: torch.Tensor, peer_bases) -> torch.Tensor:
+        """Local experts + the peer-memory combine (`glm4moe_layer_forward_ep_p2p`): returns the full
+        replicated `[T, H]`, bit-identical to the single-GPU block.  `peer_bases`: ctypes array of the
+        workspace base of every rank as mapped in this process."""
+        h = hidden_states.reshape(-1, hidden_states.shape[-1])
+        if not h.is_contiguous():
+            h = h.contiguous()
+        _lib.require_cuda(h, "hidden_states")
+        if h.dtype != self.gate.weight.dtype:
+            raise _lib.Glm4MoeLibraryError(f"hidden_states dtype {h.dtype} != model dtype {self.gate.weight.dtype}")
+        T = h.shape[0]
+        out = torch.empty_like(h)
+        if T == 0:
+            return out
+        self._ensure_layer(T)
+        with torch.cuda.device(h.device):
+            _lib.check(_lib.load().glm4moe_layer_forward_ep_p2p(self._handle, h.data_ptr(), out.data_ptr(), T,
+                                                               peer_bases, self.ep_rank, self.ep_size,
+                                                               _lib.stream_ptr(h.device)), "layer_forward_ep_p2p")
+        return out

@@ -163,6 +163,23 @@ int glm4moe_layer_last_impl(const glm4moe_layer_t* layer);
 int glm4moe_layer_last_fused(const glm4moe_layer_t* layer);
 int glm4moe_layer_tile_rows(const glm4moe_layer_t* layer, int T);
 
+/* ---- expert parallelism over NVLink peer memory (replaces the dead all_reduce of linear.py:153-154
+ * for the sparse block; the reference itself has no expert parallelism) -----------------
+ * Every rank allocates its layer workspace with glm4moe_p2p_alloc (cudaMalloc + cudaIpc handle, zeroed),
+ * ships the 64-byte handle to its peers over any host channel, and maps theirs with glm4moe_p2p_open.
+ * glm4moe_layer_forward_ep_p2p then runs the local experts of a replicated token batch and ONE kernel
+ * that, per token, reads the k weighted expert rows (+ shared-expert row) from the ranks that own them
+ * and sums them in ascending expert order in fp32: bit-identical to the single-GPU forward, result
+ * replicated on every rank, no NCCL call.  peer_workspaces[r] = rank r's workspace as mapped in this
+ * process (peer_workspaces[rank] = the layer's own workspace).  The layer must have been created with
+ * with_shared = 2 (world > 1) and contiguous expert blocks; all ranks call it the same number of times. */
+int glm4moe_p2p_alloc(size_t bytes, void** ptr, unsigned char* handle64);
+int glm4moe_p2p_open(const unsigned char* handle64, void** peer_ptr);
+int glm4moe_p2p_close(void* peer_ptr);
+int glm4moe_p2p_free(void* ptr);
+int glm4moe_layer_forward_ep_p2p(glm4moe_layer_t* layer, const void* x, void* out, int T,
+                                 void* const* peer_workspaces, int rank, int world, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

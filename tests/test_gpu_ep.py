@@ -33,12 +33,20 @@ def _worker(rank, world, port, q):
                 idx = single.workspace_view("idx", T).cpu().long()
                 w = single.workspace_view("w", T).cpu().to(dt)
                 truth = O.moe_forward_fp32(x, wts, shape.k, shape.routed_scaling_factor, routing=(idx, w))["out"]
-            for layout in ("allreduce", "alltoall"):
-                local = _module(shape, dt, wts, ep_rank=rank, ep_size=world)
+            for layout in ("allreduce", "alltoall", "p2p"):
+                local = _module(shape, dt, wts, ep_rank=rank, ep_size=world, max_tokens=512,
+                                peer_workspace=(layout == "p2p"))
                 ep = ExpertParallelMoE(local, shape.E, layout=layout)
                 with torch.inference_mode():
                     y = ep(x.cuda())
+                    if layout == "p2p":
+                        # peer-memory combine: same summation order and single rounding as one GPU
+                        for rep in range(3):
+                            assert torch.equal(ep(x.cuda()), y)
+                        assert torch.equal(y, y1), f"T={T}: p2p layout differs from the single-GPU block"
                 torch.cuda.synchronize()
+                if layout == "p2p":
+                    ep.close_p2p()
                 got = y.float().cpu()
                 rms = truth.pow(2).mean().sqrt()
                 bad = int(((got - truth).abs() > 2e-2 * truth.abs() + 2e-2 * rms).sum())

@@ -600,3 +600,27 @@ def test_fp8_air_prefill_properties(air):
     assert torch.isfinite(out.float()).all()
     d = float((out[:1024].float() - half.float()).norm() / half.float().norm())
     assert d < 1e-3, d
+
+
+@pytest.mark.parametrize("shape_name,Ts", [("mini", (1, 7, 32, 200)), ("glm-4.5-air", (3, 32))])
+def test_peer_memory_combine_world1_bit_identical(shape_name, Ts):
+    """`glm4moe_layer_forward_ep_p2p` with a world of one rank (the workspace is the cudaIpc-exportable
+    allocation, every row is local): the expert rows + peer-memory combine kernel must reproduce the
+    ordinary forward bit for bit (same order, one rounding), also through the fused decode kernel
+    running in rows-only mode (T <= 32), repeatedly (epoch counters re-arm)."""
+    import ctypes as C
+    shape, dt = synth.SHAPES[shape_name], torch.bfloat16
+    wts = synth.make_weights(shape, dt)
+    ref = _module(shape, dt, wts, max_tokens=256)
+    ep = _module(shape, dt, wts, max_tokens=256, peer_workspace=True)
+    handle, off = ep.ipc_handle()
+    assert len(handle) == 64
+    bases = (C.c_void_p * 1)(ep.workspace_base())
+    for T in Ts:
+        x = synth.make_tokens(shape, T, dt, 50 + T).cuda()
+        with torch.inference_mode():
+            want = ref(x)
+            for rep in range(3):
+                got = ep.forward_ep_p2p(x, bases)
+                assert torch.equal(got, want), f"T={T} rep={rep}"
+            assert torch.equal(ep(x), want)       # the ordinary entry still works on the same workspace
