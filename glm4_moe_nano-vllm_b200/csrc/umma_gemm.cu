@@ -45,7 +45,9 @@ struct UmmaCfg {
   static constexpr int kTmemColsRaw = kAccStages * kAccCols;
   static constexpr int kTmemCols = kTmemColsRaw <= 32 ? 32 : kTmemColsRaw <= 64 ? 64
                                    : kTmemColsRaw <= 128 ? 128 : kTmemColsRaw <= 256 ? 256 : 512;
-  static constexpr int kEpiWarps = BN >= 64 ? 8 : 4;            // wide tiles: two warps per TMEM lane quadrant
+  // wide tiles: two warps per TMEM lane quadrant; the gated 256-row tile has a single accumulator
+  // stage (TMEM is full), so its epilogue is on the MMA's critical path: four warps per quadrant
+  static constexpr int kEpiWarps = (kGated && BN == 256) ? 16 : BN >= 64 ? 8 : 4;
   static constexpr int kThreads = 128 + 32 * kEpiWarps;
   static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 512 /*barriers*/;
   static_assert(kTmemColsRaw <= 512, "accumulators do not fit TMEM");

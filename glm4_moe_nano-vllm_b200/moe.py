@@ -345,16 +345,38 @@ class Glm4MoeMoE(nn.Module):
         Keys: `{p}.gate.weight`, `{p}.gate.e_score_correction_bias`,
         `{p}.experts.{i}.{gate_proj,up_proj,down_proj}.weight`, `{p}.shared_experts.*`;
         gate_proj and up_proj are concatenated along dim 0 (mlp.py:118), nothing is transposed.
+        An expert-parallel shard reads only its own experts.  FP8 checkpoints (e4m3 `weight` +
+        fp32 `weight_scale_inv [rows/128, cols/128]`, the block format of fp8.py) fill the
+        quantised stacks directly and switch the block to the e4m3 kernels.
         """
         from safetensors import safe_open
         if os.path.isdir(path):
             files = sorted(os.path.join(path, f) for f in os.listdir(path) if f.endswith(".safetensors"))
         else:
             files = [path]
-        I = self.config.moe_intermediate_size
+        I, H = self.config.moe_intermediate_size, self.config.hidden_size
         n_local = self.expert_end - self.expert_begin
         found = 0
-        seen = set()
+        seen, seen_scale = set(), set()
+        f8 = torch.float8_e4m3fn
+
+        def fp8_stacks():
+            if self._wq_gate_up is None:
+                if I % 128 or H % 128:
+                    raise ValueError(f"block-128 FP8 needs dimensions divisible by 128, got I={I}, H={H}")
+                dev = self._w_gate_up.device
+                self._wq_gate_up = torch.empty((n_local + 1, 2 * I, H), dtype=f8, device=dev)
+                self._wq_down = torch.empty((n_local + 1, H, I), dtype=f8, device=dev)
+                self._s_gate_up = torch.empty((n_local + 1, 2 * I // 128, H // 128), dtype=torch.float32, device=dev)
+                self._s_down = torch.empty((n_local + 1, H // 128, I // 128), dtype=torch.float32, device=dev)
+
+        def put(dst, t, key):
+            assert t.shape == dst.shape, f"{key}: {tuple(t.shape)} != {tuple(dst.shape)}"
+            if t.dtype == f8:
+                dst.view(torch.uint8).copy_(t.view(torch.uint8))     # bytes, no conversion
+            else:
+                dst.copy_(t)
+
         with torch.no_grad():
             for fn in files:
                 with safe_open(fn, framework="pt", device="cpu") as f:
@@ -365,37 +387,49 @@ class Glm4MoeMoE(nn.Module):
                         rest = key[len(prefix) + 1:]
                         if rest == "gate.weight":
                             self.gate.weight.data.copy_(f.get_tensor(key))
-                        elif rest == "gate.e_score_correction_bias":
+                            continue
+                        if rest == "gate.e_score_correction_bias":
                             self.gate.e_score_correction_bias.copy_(f.get_tensor(key))
+                            continue
+                        parts = rest.split(".")
+                        if parts[0] == "experts" and len(parts) == 4:
+                            e = int(parts[1])
+                            if not (self.expert_begin <= e < self.expert_end):
+                                continue
+                            slot, proj, leaf = e - self.expert_begin, parts[2], parts[3]
+                        elif parts[0] == "shared_experts" and len(parts) == 3:
+                            slot, proj, leaf = n_local, parts[1], parts[2]
                         else:
-                            parts = rest.split(".")
-                            if parts[0] == "experts" and len(parts) == 4 and parts[3] == "weight":
-                                e = int(parts[1])
-                                if not (self.expert_begin <= e < self.expert_end):
-                                    continue
-                                slot, proj = e - self.expert_begin, parts[2]
-                            elif parts[0] == "shared_experts" and len(parts) == 3 and parts[2] == "weight":
-                                slot, proj = n_local, parts[1]
-                            else:
-                                continue
-                            t = f.get_tensor(key)
-                            if proj == "gate_proj":
-                                assert t.shape == self._w_gate_up[slot, :I].shape, f"{key}: {tuple(t.shape)}"
-                                self._w_gate_up[slot, :I].copy_(t)
-                            elif proj == "up_proj":
-                                assert t.shape == self._w_gate_up[slot, I:].shape, f"{key}: {tuple(t.shape)}"
-                                self._w_gate_up[slot, I:].copy_(t)
-                            elif proj == "down_proj":
-                                assert t.shape == self._w_down[slot].shape, f"{key}: {tuple(t.shape)}"
-                                self._w_down[slot].copy_(t)
-                            else:
-                                continue
-                            seen.add((slot, proj))
+                            continue
+                        if proj not in ("gate_proj", "up_proj", "down_proj") or leaf not in ("weight", "weight_scale_inv"):
+                            continue
+                        t = f.get_tensor(key)
+                        if leaf == "weight_scale_inv":
+                            fp8_stacks()
+                            sI = I // 128
+                            dst = {"gate_proj": self._s_gate_up[slot, :sI], "up_proj": self._s_gate_up[slot, sI:],
+                                   "down_proj": self._s_down[slot]}[proj]
+                            put(dst, t.float(), key)
+                            seen_scale.add((slot, proj))
+                            continue
+                        if t.dtype == f8:
+                            fp8_stacks()
+                            gu, dn = self._wq_gate_up, self._wq_down
+                        else:
+                            gu, dn = self._w_gate_up, self._w_down
+                        dst = {"gate_proj": gu[slot, :I], "up_proj": gu[slot, I:], "down_proj": dn[slot]}[proj]
+                        put(dst, t, key)
+                        seen.add((slot, proj, t.dtype == f8))
         if not found:
             raise ValueError(f"No tensors with prefix '{prefix}' found in '{path}'")   # moe.py:94-95
+        is_fp8 = any(q for _, _, q in seen)
         for slot in range(n_local + 1):
             for proj in ("gate_proj", "up_proj", "down_proj"):
-                assert (slot, proj) in seen, f"{proj}.weight missing for expert slot {slot}"   # mlp.py:113-115
+                assert (slot, proj, is_fp8) in seen, f"{proj}.weight missing for expert slot {slot}"   # mlp.py:113-115
+                assert not is_fp8 or (slot, proj) in seen_scale, f"{proj}.weight_scale_inv missing for expert slot {slot}"
+        if is_fp8:
+            self._destroy_handle()
+            self.weight_format = "fp8"
 
     # ---- helpers used by tests / bench -------------------------------------------------------
     def load_stacked(self, weights: dict):

@@ -24,6 +24,9 @@ echo "launch-list rc=$?"
 bash scripts/ncu_full.sh ${TAG}_T32 decode_fused 3 32
 bash scripts/ncu_full.sh ${TAG}_T1 decode_fused 3 1
 bash scripts/ncu_full.sh ${TAG}_T4096_gu umma_grouped 4 4096
+bash scripts/ncu_full.sh ${TAG}_T4096_fp8_gu umma_fp8_prefill 2 4096 4 --fp8
 NCU_SKIP=0 NCU_COUNT=40 bash scripts/ncu_kernels.sh ${TAG}_T4096 4096 3
+NCU_SKIP=0 NCU_COUNT=40 bash scripts/ncu_kernels.sh ${TAG}_T4096_fp8 4096 3 --fp8
+NCU_SKIP=0 NCU_COUNT=12 bash scripts/ncu_kernels.sh ${TAG}_T1 1 6
 fi
 ls -la gpurun_out | tail -30

@@ -114,3 +114,36 @@ def test_load_weights_hf_layout(tmp_path):
     half.load_weights(str(tmp_path), p)
     assert torch.equal(half._w_gate_up[:6], w["w_gate_up"][6:12])
     assert torch.equal(half._w_down[6], w["w_down"][12])
+
+
+def test_load_weights_fp8_block_checkpoint(tmp_path):
+    """An FP8 checkpoint (e4m3 `weight` + fp32 `weight_scale_inv [rows/128, cols/128]`) fills the quantised
+    stacks byte for byte, concatenates gate/up scales along dim 0 like the weights (mlp.py:118), switches
+    the block to the e4m3 kernels and dequantises back to the source within e4m3 rounding."""
+    from safetensors.torch import save_file
+    from glm4_moe_b200 import fp8
+    shape = synth.MoeShape(256, 4, 2, 128, 1.0, "loader-fp8")
+    w = synth.make_weights(shape, torch.float32)
+    p = "model.layers.3.mlp"
+    sd = {f"{p}.gate.weight": w["gate_weight"], f"{p}.gate.e_score_correction_bias": w["bias"]}
+    qs = {}
+    for e in range(shape.E + 1):
+        q = f"{p}.experts.{e}" if e < shape.E else f"{p}.shared_experts"
+        for proj, t in (("gate_proj", w["w_gate_up"][e, :shape.I]), ("up_proj", w["w_gate_up"][e, shape.I:]),
+                        ("down_proj", w["w_down"][e])):
+            tq, ts = fp8.quantize_block128(t.contiguous())
+            sd[f"{q}.{proj}.weight"], sd[f"{q}.{proj}.weight_scale_inv"] = tq, ts
+            qs[(e, proj)] = (tq, ts)
+    save_file(sd, str(tmp_path / "m.safetensors"))
+    moe = glm4_moe_b200.Glm4MoeMoE(_cfg(shape), ep_rank=1, ep_size=2)      # experts 2, 3 + shared
+    moe.load_weights(str(tmp_path / "m.safetensors"), p)
+    assert moe.weight_format == "fp8"
+    for slot, e in enumerate((2, 3, shape.E)):
+        g, u, d = qs[(e, "gate_proj")], qs[(e, "up_proj")], qs[(e, "down_proj")]
+        assert torch.equal(moe._wq_gate_up[slot].view(torch.uint8), torch.cat([g[0], u[0]]).view(torch.uint8))
+        assert torch.equal(moe._s_gate_up[slot], torch.cat([g[1], u[1]]))
+        assert torch.equal(moe._wq_down[slot].view(torch.uint8), d[0].view(torch.uint8))
+        assert torch.equal(moe._s_down[slot], d[1])
+    deq = moe.dequantized_weights()
+    src = w["w_gate_up"][[2, 3, shape.E]]
+    assert float((deq["w_gate_up"] - src).abs().max()) <= float(src.abs().max()) * 2 ** -4
