@@ -315,9 +315,16 @@ def main():
         kern = "umma_grouped_kernel<gate_up+silu_mul>"
         gu_bytes = (U + n_sh) * 2 * I * H * 2 + rows * H * 2 + rows * I * 2
     achieved = gu_bytes / gu_ms / 1e6
+    # DRAM traffic of the same launch from the committed `ncu --set full` capture (profiles/ncu_traffic.json)
+    traffic = None
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        traffic = tj.get(f"{kern.split('<')[0]}:T={T}:bf16") if world == 1 else None
+    except (OSError, ValueError):
+        pass
     layer_bytes = shape.algorithmic_bytes(T, U) if world == 1 else None
     roofline = {"bound": "hbm", "kernel": kern, "achieved": achieved,
-                "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
+                "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": traffic,
                 "peak_source": peak_src, "kernel_ms": gu_ms, "algorithmic_bytes_per_launch": gu_bytes,
                 "stage_ms": stage_acc}
     if layer_bytes:

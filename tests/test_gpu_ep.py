@@ -59,9 +59,10 @@ def _worker(rank, world, port, q):
 
 
 def test_expert_parallel_two_gpus():
-    if torch.cuda.device_count() < 2:
-        pytest.skip("needs 2 GPUs")
-    world = 2
+    """world = 2 by default; GLM4MOE_TEST_WORLD=4/8 runs the same checks over more ranks of one box."""
+    world = int(os.environ.get("GLM4MOE_TEST_WORLD", "2"))
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
     port = s.getsockname()[1]
