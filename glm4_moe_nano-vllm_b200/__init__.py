@@ -3,13 +3,16 @@
 library for sm_100a (`csrc/`, header `include/glm4_moe_b200.h`).  No CPU fallback."""
 from . import synth  # noqa: F401
 
-__all__ = ["synth", "Glm4MoeMoE", "GlmMoeSelectTopk", "Glm4MoeMLP", "lib"]
+__all__ = ["synth", "Glm4MoeMoE", "GlmMoeSelectTopk", "Glm4MoeMLP", "RMSNorm", "lib"]
 
 
 def __getattr__(name):
     if name in ("Glm4MoeMoE", "GlmMoeSelectTopk", "Glm4MoeMLP"):
         from . import moe
         return getattr(moe, name)
+    if name == "RMSNorm":
+        from . import layernorm
+        return layernorm.RMSNorm
     if name == "lib":
         from . import _lib
         return _lib

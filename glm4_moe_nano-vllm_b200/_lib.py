@@ -25,7 +25,7 @@ SYMBOLS = [
     "glm4moe_workspace_bytes", "glm4moe_layer_create", "glm4moe_layer_destroy",
     "glm4moe_layer_forward", "glm4moe_layer_forward_ex", "glm4moe_layer_forward_timed", "glm4moe_layer_forward_host", "glm4moe_layer_view",
     "glm4moe_layer_last_launches", "glm4moe_layer_last_impl", "glm4moe_layer_last_fused", "glm4moe_layer_tile_rows",
-    "glm4moe_p2p_alloc", "glm4moe_p2p_open", "glm4moe_p2p_close", "glm4moe_p2p_free", "glm4moe_layer_forward_ep_p2p",
+    "glm4moe_p2p_alloc", "glm4moe_p2p_open", "glm4moe_p2p_close", "glm4moe_p2p_free", "glm4moe_layer_forward_ep_p2p", "glm4moe_add_rmsnorm",
 ]
 
 
@@ -91,6 +91,7 @@ def load() -> C.CDLL:
     lib.glm4moe_p2p_alloc.argtypes = [sz, C.POINTER(vp), C.c_char_p]
     lib.glm4moe_p2p_open.argtypes = [C.c_char_p, C.POINTER(vp)]
     lib.glm4moe_p2p_close.argtypes = [vp]
+    lib.glm4moe_add_rmsnorm.argtypes = [vp, vp, vp, f32, i32, i32, i32, vp, vp, vp]
     lib.glm4moe_p2p_free.argtypes = [vp]
     lib.glm4moe_layer_forward_ep_p2p.argtypes = [vp, vp, vp, i32, C.POINTER(vp), i32, i32, vp]
     for name in SYMBOLS:

@@ -163,6 +163,14 @@ int glm4moe_layer_last_impl(const glm4moe_layer_t* layer);
 int glm4moe_layer_last_fused(const glm4moe_layer_t* layer);
 int glm4moe_layer_tile_rows(const glm4moe_layer_t* layer, int T);
 
+/* ---- the step in front of the block: residual add + RMSNorm (layers/layernorm.py:29-40, called as
+ * post_attention_layernorm at models/glm4_moe/decode_layer.py:98) --------------------------------
+ * x32 = x + residual (fp32); residual_out = round(x32); out = round(round(x32 * rsqrt(mean(x32^2) + eps))
+ * * weight).  residual == NULL: plain RMSNorm of x (layernorm.py:17-26), residual_out unused.
+ * out may alias x; residual_out may alias residual.                                               */
+int glm4moe_add_rmsnorm(const void* x, const void* residual, const void* weight, float eps, int T, int H,
+                        int dtype, void* out, void* residual_out, void* stream);
+
 /* ---- expert parallelism over NVLink peer memory (replaces the dead all_reduce of linear.py:153-154
  * for the sparse block; the reference itself has no expert parallelism) -----------------
  * Every rank allocates its layer workspace with glm4moe_p2p_alloc (cudaMalloc + cudaIpc handle, zeroed),

@@ -127,6 +127,29 @@ def main():
                 "idx": idx.to(torch.int32), "w": w}
         torch.save(blob, os.path.join(out_dir, name + ".pt"))
         print(name, tuple(idx.shape))
+    # RMSNorm in front of the block (layers/layernorm.py), with and without the residual
+    sys.path.insert(0, REF)
+    from nanovllm.layers.layernorm import RMSNorm
+    for name, H, T, dtype in (("rmsnorm_bf16_H4096_T5", 4096, 5, torch.bfloat16), ("rmsnorm_fp32_H1024_T3", 1024, 3, torch.float32),
+                              ("rmsnorm_fp16_H512_T9", 512, 9, torch.float16)):
+        g = torch.Generator().manual_seed(99)
+        x = (torch.randn(T, H, generator=g) * 1.5).to(dtype)
+        res = torch.randn(T, H, generator=g).to(dtype)
+        wgt = (1.0 + 0.1 * torch.randn(H, generator=g)).to(dtype)
+        prev = torch.get_default_dtype()
+        torch.set_default_dtype(dtype)
+        try:
+            norm = RMSNorm(H, eps=1e-5)
+        finally:
+            torch.set_default_dtype(prev)
+        with torch.no_grad():
+            norm.weight.copy_(wgt)
+            y0 = norm(x.clone())
+            y1, r1 = norm(x.clone(), res.clone())
+        torch.save({"case": {"name": name, "H": H, "T": T, "dtype": str(dtype), "eps": 1e-5, "seed": 99},
+                    "x": x, "residual": res, "weight": wgt, "y_plain": y0, "y_add": y1, "residual_out": r1},
+                   os.path.join(out_dir, name + ".pt"))
+        print(name, float(y1.float().abs().mean()))
 
 
 if __name__ == "__main__":

@@ -171,3 +171,19 @@ def moe_forward_fp8(h: torch.Tensor, deq_weights: dict, routing, model_dtype: to
 
 def count_experts_hit(idx: torch.Tensor) -> int:
     return int(torch.unique(idx).numel())
+
+
+# --------------------------------------------------------------------------------------
+# the step in front of the block: residual add + RMSNorm
+# --------------------------------------------------------------------------------------
+def rmsnorm(x: torch.Tensor, weight: torch.Tensor, eps: float, residual: torch.Tensor | None = None):
+    """layers/layernorm.py:17-26 (`rms_forward`) and :29-40 (`add_rms_forward`), out of place."""
+    orig = x.dtype
+    x32 = x.float()
+    res_out = None
+    if residual is not None:
+        x32 = x32 + residual.float()                        # layernorm.py:35
+        res_out = x32.to(orig)                              # :36
+    var = x32.pow(2).mean(dim=-1, keepdim=True)             # :22 / :37
+    y = (x32 * torch.rsqrt(var + eps)).to(orig) * weight    # :23-24 / :38-39
+    return y if residual is None else (y, res_out)

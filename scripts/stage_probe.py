@@ -7,7 +7,7 @@ from glm4_moe_b200 import synth
 from bench import _hf_config
 FP8 = "--fp8" in sys.argv
 Ts = [int(a) for a in sys.argv[1:] if not a.startswith("--")] or [1, 4, 32, 256, 4096]
-shape, dt = synth.AIR, torch.bfloat16
+shape, dt = synth.SHAPES[os.environ.get("GLM4MOE_SHAPE", "glm-4.5-air")], torch.bfloat16
 torch.manual_seed(0)
 torch.set_default_dtype(dt)
 moe = glm4_moe_b200.Glm4MoeMoE(_hf_config(shape), max_tokens=max(Ts))

@@ -3,6 +3,8 @@ is compared with the CPU oracle (oracle/moe_oracle.py) and the golden outputs of
 (tests/golden).  Bars (BASELINE.json north_star): expert indices and the permutation bit-exact;
 layer outputs within rtol 2e-2 of the fp32 truth (|d| <= rtol*|ref| + rtol*rms(ref))
 and within the reference's own rtol=atol=1e-2 of its native output (nanovllm/tests/moe.py:40)."""
+import os
+
 import pytest
 import torch
 
@@ -624,3 +626,84 @@ def test_peer_memory_combine_world1_bit_identical(shape_name, Ts):
                 got = ep.forward_ep_p2p(x, bases)
                 assert torch.equal(got, want), f"T={T} rep={rep}"
             assert torch.equal(ep(x), want)       # the ordinary entry still works on the same workspace
+
+
+# ------------------------------------------------------------------------------------------
+# BASELINE configs[4]: GLM-4.5 shape (H=5120, E=160, top-8, I=1536, routed_scaling_factor 2.5)
+# ------------------------------------------------------------------------------------------
+def test_glm45_shape_decode_and_prefill():
+    """One GPU holds the whole bf16 layer (7.6 GB).  Decode T=8 (fused kernel, 40 down feature tiles,
+    12 gate_up tiles) against the CPU oracle with forced routing; prefill T=2048 (256-row tcgen05
+    tiles) via the size-independent properties, plus agreement of a decode-size slice with the
+    prefill rows; FP8 tier of the same module at both sizes against the bf16 run."""
+    shape, dt = synth.GLM45, torch.bfloat16
+    wts = synth.make_weights(shape, dt)
+    moe = _module(shape, dt, wts, max_tokens=2048)
+    T = 8
+    x = synth.make_tokens(shape, T, dt, 8)
+    with torch.inference_mode():
+        out = moe(x.cuda())
+        assert moe.last_fused and moe.last_impl == "umma"
+        idx = moe.workspace_view("idx", T).cpu().long()
+        w = moe.workspace_view("w", T).cpu().to(dt)
+        oi, _ = O.canonical_routing(*O.router(x, wts["gate_weight"], wts["bias"], shape.k,
+                                              shape.routed_scaling_factor))
+        assert float((idx != oi).any(-1).float().mean()) <= 0.13      # at most one boundary flip in 8 tokens
+        truth = O.moe_forward_fp32(x, wts, shape.k, shape.routed_scaling_factor, routing=(idx, w))["out"]
+        nbad, rel = _close(out, truth, RTOL_BF16)
+        assert nbad == 0 and rel < 6e-3, (nbad, rel)
+        Tp = 2048
+        xp = synth.make_tokens(shape, Tp, dt, 9).cuda()
+        y = moe(xp)
+        offs = moe.workspace_view("expert_offsets").cpu().long()
+        pidx = moe.workspace_view("idx", Tp).cpu().long()
+        assert int(offs[-1]) == Tp * shape.k
+        assert torch.equal(offs[1:] - offs[:-1], torch.bincount(pidx.view(-1), minlength=shape.E))
+        assert bool(torch.isfinite(y.float()).all())
+        sub = torch.arange(0, Tp, 64, device="cuda")
+        ys = moe(xp[sub])
+        same = (moe.workspace_view("idx", sub.numel()).cpu().long() == pidx[sub.cpu()]).all(-1)
+        a, b = ys.float().cpu()[same], y[sub].float().cpu()[same]
+        assert int(same.sum()) >= sub.numel() - 1 and float(((a - b).norm() / b.norm())) < 2e-3
+        # quant tier on the same module
+        moe.quantize_fp8(drop_native=True)
+        for xin, ref in ((x.cuda(), out), (xp, y)):
+            q = moe(xin)
+            rel = float((q.float() - ref.float()).norm() / ref.float().norm())
+            assert rel < 2 * RTOL_FP8, rel
+
+
+# ------------------------------------------------------------------------------------------
+# the step in front of the block: residual add + RMSNorm (layers/layernorm.py)
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", ["rmsnorm_bf16_H4096_T5", "rmsnorm_fp32_H1024_T3", "rmsnorm_fp16_H512_T9"])
+def test_rmsnorm_vs_reference_golden(name):
+    """`glm4moe_add_rmsnorm` through the RMSNorm mirror against the real reference's outputs.  The residual
+    stream (one rounding of an exact fp32 sum) is bit-exact; the normalised output may differ by one
+    model-dtype ulp where rsqrtf / the reduction order moves the fp32 scale by an ulp."""
+    blob = torch.load(os.path.join(os.path.dirname(__file__), "golden", name + ".pt"))
+    dt = blob["x"].dtype
+    H = blob["x"].shape[-1]
+    prev = torch.get_default_dtype()
+    torch.set_default_dtype(dt)
+    try:
+        norm = glm4_moe_b200.RMSNorm(H, eps=blob["case"]["eps"])
+    finally:
+        torch.set_default_dtype(prev)
+    with torch.no_grad():
+        norm.weight.copy_(blob["weight"])
+    norm = norm.cuda()
+    x, res = blob["x"].cuda(), blob["residual"].cuda()
+    with torch.inference_mode():
+        y0 = norm(x)
+        y1, r1 = norm(x.view(1, *x.shape), res.view(1, *res.shape))      # 3-D input like the runner's
+    want_res = blob["x"] + blob["residual"] if dt == torch.float32 else blob["residual_out"]   # fp32: see the oracle test
+    assert torch.equal(r1[0].cpu(), want_res)
+    for got, want in ((y0, blob["y_plain"]), (y1[0], blob["y_add"])):
+        d = (got.float().cpu() - want.float()).abs()
+        assert float((d > 0).float().mean()) < 5e-3
+        assert bool((d <= _ulp(dt) * 2 * want.float().abs() + 1e-30).all())
+    # rows are independent and the kernel is deterministic
+    with torch.inference_mode():
+        again, _ = norm(x, res)
+    assert torch.equal(again, y1[0])
