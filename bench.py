@@ -44,8 +44,8 @@ def _peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
         d = json.load(open(p))
-        return d["hbm_gbs"], "measured (MEASURED_PEAKS.json)"
-    return 6650.0, "fallback (B200_PROFILING.md)"
+        return d["hbm_gbs"], "measured (MEASURED_PEAKS.json)", d.get("bf16_tflops", 1650.0)
+    return 6650.0, "fallback (B200_PROFILING.md)", 1650.0
 
 
 class ClockSampler:
@@ -133,6 +133,9 @@ def main():
     ap.add_argument("--ep-layout", default="p2p", choices=["p2p", "allreduce", "alltoall"],
                     help="expert-parallel layout for --gpus > 1 (distributed.py): p2p = combine + reduction in "
                          "one kernel over NVLink peer memory, allreduce / alltoall = NCCL")
+    ap.add_argument("--ep-sliced", type=int, default=-1, choices=[-1, 0, 1],
+                    help="p2p layout: -1 pick by size, 0 every rank pulls every row, 1 reduce the own token slice "
+                         "and store it to the peers (glm4moe_set_ep_sliced)")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -141,8 +144,10 @@ def main():
     shape = synth.SHAPES[args.shape]
     dt = torch.bfloat16
     T = args.tokens
+    regime = "decode batch" if T <= 256 else "prefill"
     workload = (f"{shape.name} MoE layer (H={shape.H}, E={shape.E}, top-{shape.k}, I={shape.I}, 1 shared) "
-                f"bf16 random-init, decode batch T={T}")
+                f"bf16 random-init, {regime} T={T}")
+    n_batches = N_BATCHES if T <= 1024 else 4
 
     # ------------------------------------------------------------------ reference arm (CPU)
     if args.impl == "reference":
@@ -189,10 +194,12 @@ def main():
         from glm4_moe_b200.distributed import ExpertParallelMoE
         layer = ExpertParallelMoE(moe, shape.E, layout=args.ep_layout)
         if args.ep_layout == "p2p":
+            from glm4_moe_b200 import _lib
+            _lib.check(_lib.load().glm4moe_set_ep_sliced(args.ep_sliced))
             layer.setup_p2p()
     else:
         layer = moe
-    batches_host = [synth.make_tokens(shape, T, dt, b).pin_memory() for b in range(N_BATCHES)]
+    batches_host = [synth.make_tokens(shape, T, dt, b).pin_memory() for b in range(n_batches)]
     batches = [b.to(dev) for b in batches_host]
 
     def step(x):
@@ -200,7 +207,7 @@ def main():
 
     with torch.inference_mode():
         for i in range(max(args.warmup, 3)):
-            step(batches[i % N_BATCHES])
+            step(batches[i % n_batches])
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
@@ -209,7 +216,7 @@ def main():
             torch.cuda.synchronize()
             start.record()
             for i in range(args.steps):
-                step(batches[i % N_BATCHES])
+                step(batches[i % n_batches])
             end.record()
             torch.cuda.synchronize()
         if world > 1:
@@ -226,7 +233,7 @@ def main():
         stage_acc = {}
         n_timed = min(args.steps, 50)
         for i in range(n_timed):
-            _, ms = moe.forward_timed(batches[i % N_BATCHES])
+            _, ms = moe.forward_timed(batches[i % n_batches])
             for k_, v in ms.items():
                 stage_acc[k_] = stage_acc.get(k_, 0.0) + v / n_timed
         # experts hit per batch (for the algorithmic bytes)
@@ -243,9 +250,9 @@ def main():
 
         def e2e_step(i):
             if world == 1:
-                moe.forward_host(batches_host[i % N_BATCHES], out_host)     # glm4moe_layer_forward_host
+                moe.forward_host(batches_host[i % n_batches], out_host)     # glm4moe_layer_forward_host
             else:
-                y = layer(batches_host[i % N_BATCHES].to(dev, non_blocking=True))
+                y = layer(batches_host[i % n_batches].to(dev, non_blocking=True))
                 if rank == 0:
                     out_host.copy_(y, non_blocking=True)
                 torch.cuda.synchronize()
@@ -299,7 +306,7 @@ def main():
             dist.destroy_process_group()
         return
 
-    hbm_peak, peak_src = _peaks()
+    hbm_peak, peak_src, tc_peak = _peaks()
     H, I, k = shape.H, shape.I, shape.k
     # dominant kernel: gate_up grouped GEMM. Algorithmic bytes of one launch = gate_up weights of
     # the (U local + shared) experts it touches + the activation rows it reads + act rows it writes.
@@ -315,6 +322,7 @@ def main():
         kern = "umma_grouped_kernel<gate_up+silu_mul>"
         gu_bytes = (U + n_sh) * 2 * I * H * 2 + rows * H * 2 + rows * I * 2
     achieved = gu_bytes / gu_ms / 1e6
+    gu_flops = rows * 2 * H * 2 * I
     # DRAM traffic of the same launch from the committed `ncu --set full` capture (profiles/ncu_traffic.json)
     traffic = None
     try:
@@ -327,12 +335,20 @@ def main():
                 "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": traffic,
                 "peak_source": peak_src, "kernel_ms": gu_ms, "algorithmic_bytes_per_launch": gu_bytes,
                 "stage_ms": stage_acc}
+    if T * k / shape.E >= 96 * world and not moe.last_fused:
+        # prefill: the grouped GEMMs are a dense contraction bound by the tensor pipe
+        roofline.update({"bound": "tensor", "achieved": gu_flops / gu_ms / 1e9, "peak": tc_peak, "unit": "TFLOP/s",
+                         "frac": gu_flops / gu_ms / 1e9 / tc_peak, "algorithmic_flops_per_launch": gu_flops,
+                         "hbm": {"achieved": achieved, "peak": hbm_peak, "frac": achieved / hbm_peak}})
+        fl = shape.flops_per_token() * T / world
+        roofline["layer_tensor"] = {"algorithmic_flops": fl, "achieved": fl / ms_step / 1e9,
+                                    "frac": fl / ms_step / 1e9 / tc_peak}
     if layer_bytes:
         roofline["layer"] = {"algorithmic_bytes": layer_bytes, "achieved": layer_bytes / ms_step / 1e6,
                              "frac": layer_bytes / ms_step / 1e6 / hbm_peak}
     cpu_baseline = None
     if world == 1 and not args.no_cpu_baseline:
-        n = args.cpu_steps or 40
+        n = args.cpu_steps or (40 if T <= 64 else 8 if T <= 512 else 2)
         host_w = {k_: v.cpu() for k_, v in weights.items()}
         tps, ms, cores = _cpu_reference_run(shape, dt, host_w, T, n, 2)
         cpu_baseline = {"value": tps, "unit": UNIT, "cores": cores, "kind": "port", "ms_per_step": ms,
@@ -342,8 +358,9 @@ def main():
             "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": workload, "tokens_per_step": T, "experts_hit_mean": U,
-                       "parallelism": f"ep{world}-{args.ep_layout}" if world > 1 else "single",
-                       "l2": f"{N_BATCHES} distinct token batches rotated; weights touched per step "
+                       "parallelism": (f"ep{world}-{args.ep_layout}" + (f"-sliced{args.ep_sliced}" if args.ep_sliced >= 0 else ""))
+                       if world > 1 else "single",
+                       "l2": f"{n_batches} distinct token batches rotated; weights touched per step "
                              f"({(U + 1) * 3 * H * I * 2 / 1e9:.2f} GB) exceed the 126 MB L2",
                        "expert_gemm_impl": moe.last_impl},
             "e2e": e2e, "gpu_launches": launches, "clocks": clk.summary(), "roofline": roofline,

@@ -25,7 +25,7 @@ SYMBOLS = [
     "glm4moe_workspace_bytes", "glm4moe_layer_create", "glm4moe_layer_destroy",
     "glm4moe_layer_forward", "glm4moe_layer_forward_ex", "glm4moe_layer_forward_timed", "glm4moe_layer_forward_host", "glm4moe_layer_view",
     "glm4moe_layer_last_launches", "glm4moe_layer_last_impl", "glm4moe_layer_last_fused", "glm4moe_layer_tile_rows",
-    "glm4moe_p2p_alloc", "glm4moe_p2p_open", "glm4moe_p2p_close", "glm4moe_p2p_free", "glm4moe_layer_forward_ep_p2p", "glm4moe_add_rmsnorm",
+    "glm4moe_p2p_alloc", "glm4moe_p2p_open", "glm4moe_p2p_close", "glm4moe_p2p_free", "glm4moe_layer_forward_ep_p2p", "glm4moe_set_ep_sliced", "glm4moe_add_rmsnorm",
 ]
 
 
@@ -94,6 +94,7 @@ def load() -> C.CDLL:
     lib.glm4moe_add_rmsnorm.argtypes = [vp, vp, vp, f32, i32, i32, i32, vp, vp, vp]
     lib.glm4moe_p2p_free.argtypes = [vp]
     lib.glm4moe_layer_forward_ep_p2p.argtypes = [vp, vp, vp, i32, C.POINTER(vp), i32, i32, vp]
+    lib.glm4moe_set_ep_sliced.argtypes = [i32]
     for name in SYMBOLS:
         if lib.glm4moe_abi_version is None or not hasattr(lib, name):
             raise Glm4MoeLibraryError(f"{LIB_PATH} does not export {name}")

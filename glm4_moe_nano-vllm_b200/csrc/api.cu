@@ -51,7 +51,7 @@ inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct WsLayout {
   size_t logits, idx, w, offsets, row_token, row_weight, slot_row, num_tiles, sched, ready, fdone, tiles, scratch, x_rows,
-      act, y, xq, sx, actq, sact, ctl, total;
+      act, y, xq, sx, actq, sact, ctl, stage, total;
   int tile_capacity;
 };
 
@@ -92,6 +92,10 @@ WsLayout make_layout(const glm4moe_config_t& c) {
     L.sact = take(((I + 127) / 128) * R * 4);
   }
   L.ctl = take(kEpCtlBytes);   // peer-memory combine: epoch, ticket, ready / done flags (ep_combine.cu)
+  // sliced peer-memory combine: the rows peers store their reduced token slices into.  Only layers
+  // that can run expert-parallel (with_shared == 2 or a strict subset of the experts) pay for it.
+  const bool ep_capable = c.with_shared == 2 || c.expert_end - c.expert_begin < c.n_routed_experts;
+  L.stage = take(ep_capable && c.dtype != GLM4MOE_F32 ? T * H * es : 0);
   L.total = off;
   return L;
 }
@@ -728,6 +732,14 @@ extern "C" int glm4moe_p2p_free(void* ptr) {
   return GLM4MOE_OK;
 }
 
+// sliced peer-memory combine: -1 = by size (default), 0 = never, 1 = whenever the layer has a staging region
+static int g_ep_sliced_mode = -1;
+extern "C" int glm4moe_set_ep_sliced(int mode) {
+  if (mode < -1 || mode > 1) return GLM4MOE_ERR_ARG;
+  g_ep_sliced_mode = mode;
+  return GLM4MOE_OK;
+}
+
 extern "C" int glm4moe_layer_forward_ep_p2p(glm4moe_layer_t* l, const void* x, void* out, int T,
                                             void* const* peer_workspaces, int rank, int world, void* stream) {
   if (!l || !x || !out || !peer_workspaces) return GLM4MOE_ERR_ARG;
@@ -762,6 +774,13 @@ extern "C" int glm4moe_layer_forward_ep_p2p(glm4moe_layer_t* l, const void* x, v
   a.with_shared = c.with_shared != 0;
   a.shared_per_rank = (T + world - 1) / world;
   if (c.with_shared == 1) a.shared_per_rank = T;   // world == 1: every shared row is local
+  // Large batches: reduce the own token slice and store it to the peers (T/R as many NVLink reads)
+  // instead of every rank pulling every row.  Same decision on every rank (depends on T only).
+  a.off_stage = l->L.stage;
+  const bool has_stage = world > 1 && c.with_shared == 2;
+  const size_t row_bytes = static_cast<size_t>(T) * (a.k + 1) * a.H * dtype_size(c.dtype);
+  a.sliced = g_ep_sliced_mode == 1 ? (has_stage || world == 1)      // world == 1: no peer, no staging needed
+                                   : g_ep_sliced_mode == -1 && has_stage && row_bytes >= (16u << 20);
   rc = ep_combine_p2p_launch(a, out, c.dtype, stream);
   l->last_launches = g_launches - launches0;
   return rc;

@@ -12,6 +12,8 @@ constexpr int kEpThreads = 128;
 struct EpCombineArgs {
   unsigned char* ws[kEpMaxRanks];   // workspace base of every rank as mapped in THIS process (own = local)
   size_t off_y, off_slot_row, off_idx, off_ctl;   // identical workspace layout on every rank
+  size_t off_stage;                 // [T_max, H] staging rows peers store their token slices into (sliced mode)
+  int sliced;                       // 1: reduce own token slice, store it to every peer (ep_combine.cu)
   int rank, world;
   int tokens, k, H;
   int experts_per_rank;             // E / world (contiguous expert blocks)

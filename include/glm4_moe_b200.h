@@ -180,13 +180,19 @@ int glm4moe_add_rmsnorm(const void* x, const void* residual, const void* weight,
  * and sums them in ascending expert order in fp32: bit-identical to the single-GPU forward, result
  * replicated on every rank, no NCCL call.  peer_workspaces[r] = rank r's workspace as mapped in this
  * process (peer_workspaces[rank] = the layer's own workspace).  The layer must have been created with
- * with_shared = 2 (world > 1) and contiguous expert blocks; all ranks call it the same number of times. */
+ * with_shared = 2 (world > 1) and contiguous expert blocks; all ranks call it the same number of times.
+ * Large batches (T*(k+1)*H*elt >= 16 MiB) use the sliced form of the same kernel: every rank reduces
+ * only its ceil(T/world) token slice and stores the finished rows into `out` and into a staging region
+ * of every peer's workspace (reduce-scatter + all-gather in one launch; same sums, same bits).
+ * glm4moe_set_ep_sliced: -1 choose by size (default), 0 never, 1 always; process-wide, must be set
+ * identically on every rank. */
 int glm4moe_p2p_alloc(size_t bytes, void** ptr, unsigned char* handle64);
 int glm4moe_p2p_open(const unsigned char* handle64, void** peer_ptr);
 int glm4moe_p2p_close(void* peer_ptr);
 int glm4moe_p2p_free(void* ptr);
 int glm4moe_layer_forward_ep_p2p(glm4moe_layer_t* layer, const void* x, void* out, int T,
                                  void* const* peer_workspaces, int rank, int world, void* stream);
+int glm4moe_set_ep_sliced(int mode);
 
 #ifdef __cplusplus
 }

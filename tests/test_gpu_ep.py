@@ -44,6 +44,14 @@ def _worker(rank, world, port, q):
                         for rep in range(3):
                             assert torch.equal(ep(x.cuda()), y)
                         assert torch.equal(y, y1), f"T={T}: p2p layout differs from the single-GPU block"
+                        # sliced form (each rank reduces its token slice and stores it to the peers),
+                        # interleaved with the pull form on the same epoch counters
+                        from glm4_moe_b200 import _lib
+                        for mode in (1, 0, 1, -1):
+                            _lib.check(_lib.load().glm4moe_set_ep_sliced(mode))
+                            dist.barrier()
+                            ys = ep(x.cuda())
+                            assert torch.equal(ys, y1), f"T={T}: sliced mode {mode} differs"
                 torch.cuda.synchronize()
                 if layout == "p2p":
                     ep.close_p2p()

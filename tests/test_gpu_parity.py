@@ -626,6 +626,13 @@ def test_peer_memory_combine_world1_bit_identical(shape_name, Ts):
                 got = ep.forward_ep_p2p(x, bases)
                 assert torch.equal(got, want), f"T={T} rep={rep}"
             assert torch.equal(ep(x), want)       # the ordinary entry still works on the same workspace
+            # sliced form of the combine (own token slice = all tokens in a world of one)
+            _lib.check(_lib.load().glm4moe_set_ep_sliced(1))
+            try:
+                for rep in range(2):
+                    assert torch.equal(ep.forward_ep_p2p(x, bases), want), f"sliced T={T} rep={rep}"
+            finally:
+                _lib.check(_lib.load().glm4moe_set_ep_sliced(-1))
 
 
 # ------------------------------------------------------------------------------------------
