@@ -37,3 +37,53 @@ def quantize_rows_1x128(x: torch.Tensor):
     scale = g.abs().amax(-1, keepdim=True).clamp_min(1e-10) / E4M3_MAX
     q = (g / scale).clamp(-E4M3_MAX, E4M3_MAX).to(torch.float8_e4m3fn)
     return q.reshape(*lead, K), scale.squeeze(-1)
+
+
+def convert_checkpoint(src: str, dst: str, prefixes=None) -> dict:
+    """Offline conversion of the sparse-block expert weights of an HF-layout checkpoint to the block
+    FP8 format `Glm4MoeMoE.load_weights` reads.
+
+    `src`: a `.safetensors` file or a directory of them; `dst`: output file / directory (same file
+    names).  Every `...experts.{i}.{gate,up,down}_proj.weight` and `...shared_experts.*_proj.weight`
+    (optionally restricted to keys starting with one of `prefixes`) is replaced by an e4m3 `weight`
+    and an fp32 `weight_scale_inv [rows/128, cols/128]`; router weights, the fp32
+    `e_score_correction_bias` and everything outside the sparse block are copied through untouched.
+    One pass, one tensor in memory at a time.  Returns {"converted": n, "copied": m}."""
+    import os
+    import re
+    from safetensors import safe_open
+    from safetensors.torch import save_file
+    pat = re.compile(r"\.(experts\.\d+|shared_experts)\.(gate_proj|up_proj|down_proj)\.weight$")
+    if os.path.isdir(src):
+        os.makedirs(dst, exist_ok=True)
+        pairs = [(os.path.join(src, f), os.path.join(dst, f)) for f in sorted(os.listdir(src))
+                 if f.endswith(".safetensors")]
+    else:
+        pairs = [(src, dst)]
+    stats = {"converted": 0, "copied": 0}
+    for fin, fout in pairs:
+        out = {}
+        with safe_open(fin, framework="pt", device="cpu") as f:
+            for key in f.keys():
+                t = f.get_tensor(key)
+                wanted = prefixes is None or any(key.startswith(p + ".") for p in prefixes)
+                if wanted and pat.search(key) and t.dtype != torch.float8_e4m3fn:
+                    q, s = quantize_block128(t.contiguous())
+                    out[key] = q
+                    out[key[:-len("weight")] + "weight_scale_inv"] = s
+                    stats["converted"] += 1
+                else:
+                    out[key] = t.contiguous()
+                    stats["copied"] += 1
+        save_file(out, fout)
+    return stats
+
+
+if __name__ == "__main__":
+    import argparse
+    ap = argparse.ArgumentParser(description="bf16/fp16 GLM4-MoE checkpoint -> block-128 FP8 expert weights")
+    ap.add_argument("src")
+    ap.add_argument("dst")
+    ap.add_argument("--prefix", action="append", help="only convert keys under this prefix (repeatable)")
+    a = ap.parse_args()
+    print(convert_checkpoint(a.src, a.dst, a.prefix))

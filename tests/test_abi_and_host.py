@@ -147,3 +147,38 @@ def test_load_weights_fp8_block_checkpoint(tmp_path):
     deq = moe.dequantized_weights()
     src = w["w_gate_up"][[2, 3, shape.E]]
     assert float((deq["w_gate_up"] - src).abs().max()) <= float(src.abs().max()) * 2 ** -4
+
+
+def test_offline_fp8_conversion_round_trip(tmp_path):
+    """`fp8.convert_checkpoint`: a bf16 HF-layout checkpoint becomes an FP8 block checkpoint
+    that `load_weights` accepts; the loaded stacks equal quantising the source stacks directly, and
+    non-expert tensors pass through untouched."""
+    from safetensors.torch import save_file, load_file
+    from glm4_moe_b200 import fp8
+    shape = synth.MoeShape(256, 4, 2, 128, 1.0, "convert-fp8")
+    w = synth.make_weights(shape, torch.bfloat16)
+    p = "model.layers.1.mlp"
+    sd = {f"{p}.gate.weight": w["gate_weight"], f"{p}.gate.e_score_correction_bias": w["bias"],
+          "model.layers.1.input_layernorm.weight": torch.ones(shape.H, dtype=torch.bfloat16)}
+    for e in range(shape.E + 1):
+        q = f"{p}.experts.{e}" if e < shape.E else f"{p}.shared_experts"
+        sd[f"{q}.gate_proj.weight"] = w["w_gate_up"][e, :shape.I].contiguous()
+        sd[f"{q}.up_proj.weight"] = w["w_gate_up"][e, shape.I:].contiguous()
+        sd[f"{q}.down_proj.weight"] = w["w_down"][e].contiguous()
+    os.makedirs(tmp_path / "src")
+    save_file(sd, str(tmp_path / "src" / "model-00001.safetensors"))
+    stats = fp8.convert_checkpoint(str(tmp_path / "src"), str(tmp_path / "dst"))
+    assert stats == {"converted": 3 * (shape.E + 1), "copied": 3}
+    out = load_file(str(tmp_path / "dst" / "model-00001.safetensors"))
+    assert torch.equal(out["model.layers.1.input_layernorm.weight"], sd["model.layers.1.input_layernorm.weight"])
+    assert out[f"{p}.gate.weight"].dtype == torch.bfloat16
+    moe = glm4_moe_b200.Glm4MoeMoE(_cfg(shape))
+    moe.load_weights(str(tmp_path / "dst"), p)
+    assert moe.weight_format == "fp8"
+    # gate/up are quantised per projection (their 128-row blocks never straddle the two)
+    q_gu, s_gu = fp8.quantize_block128(w["w_gate_up"])
+    q_d, s_d = fp8.quantize_block128(w["w_down"])
+    assert torch.equal(moe._wq_gate_up.view(torch.uint8), q_gu.view(torch.uint8))
+    assert torch.equal(moe._s_gate_up, s_gu)
+    assert torch.equal(moe._wq_down.view(torch.uint8), q_d.view(torch.uint8))
+    assert torch.equal(moe._s_down, s_d)
