@@ -228,6 +228,7 @@ def main():
             ms_total = float(t.item())
         ms_step = ms_total / args.steps
         launches = moe.last_launches * args.steps
+        fused, impl_name = moe.last_fused, moe.last_impl     # of the timed workload (the sweep below runs other T)
 
         # per-stage timing (separate loop; an event between stages)
         stage_acc = {}
@@ -313,7 +314,7 @@ def main():
     n_sh = 1
     rows = T * k / world + T / world
     gu_ms = stage_acc["gate_up"]
-    if moe.last_fused:
+    if fused:
         # decode regime: gate_up + SiLU*mul + down + combine are ONE persistent launch
         # (decode_fused.cu); the "gate_up" stage interval brackets exactly that launch.
         kern = "decode_fused_kernel<gate_up+silu_mul+down+combine>"
@@ -335,7 +336,7 @@ def main():
                 "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": traffic,
                 "peak_source": peak_src, "kernel_ms": gu_ms, "algorithmic_bytes_per_launch": gu_bytes,
                 "stage_ms": stage_acc}
-    if T * k / shape.E >= 96 * world and not moe.last_fused:
+    if T * k / shape.E >= 96 * world and not fused:
         # prefill: the grouped GEMMs are a dense contraction bound by the tensor pipe
         roofline.update({"bound": "tensor", "achieved": gu_flops / gu_ms / 1e9, "peak": tc_peak, "unit": "TFLOP/s",
                          "frac": gu_flops / gu_ms / 1e9 / tc_peak, "algorithmic_flops_per_launch": gu_flops,
@@ -362,7 +363,7 @@ def main():
                        if world > 1 else "single",
                        "l2": f"{n_batches} distinct token batches rotated; weights touched per step "
                              f"({(U + 1) * 3 * H * I * 2 / 1e9:.2f} GB) exceed the 126 MB L2",
-                       "expert_gemm_impl": moe.last_impl},
+                       "expert_gemm_impl": impl_name},
             "e2e": e2e, "gpu_launches": launches, "clocks": clk.summary(), "roofline": roofline,
             "cpu_baseline": cpu_baseline}
     if sweep:

@@ -124,6 +124,12 @@ struct glm4moe_layer {
   alignas(64) CUtensorMap tm_gate;
   alignas(64) CUtensorMap tm_x[kNumBn];
   alignas(64) CUtensorMap tm_act[kNumBn];
+  // prefill (256-token tiles), half-size pipeline stages: box {32 cols, rows}, 64-byte swizzle
+  bool bk32_ok;
+  alignas(64) CUtensorMap tm_w_gu32;
+  alignas(64) CUtensorMap tm_w_d32;
+  alignas(64) CUtensorMap tm_x32;
+  alignas(64) CUtensorMap tm_act32;
 };
 
 namespace glm4moe {
@@ -258,6 +264,13 @@ extern "C" int glm4moe_layer_create(const glm4moe_config_t* cfg, const void* gat
         rc = umma_make_tensor_map(&l->tm_act[i], l->ws + L.act, cfg->dtype, R, I, kBnChoices[i]);
     }
     if (rc == GLM4MOE_OK) l->umma_ok = true;
+    if (rc == GLM4MOE_OK && H % 32 == 0 && I % 32 == 0) {
+      int r2 = umma_make_tensor_map_bk(&l->tm_w_gu32, w_gate_up, cfg->dtype, n_stack * 2 * I, H, 128, 32);
+      if (!r2) r2 = umma_make_tensor_map_bk(&l->tm_w_d32, w_down, cfg->dtype, n_stack * H, I, 128, 32);
+      if (!r2) r2 = umma_make_tensor_map_bk(&l->tm_x32, l->ws + L.x_rows, cfg->dtype, R, H, 256, 32);
+      if (!r2) r2 = umma_make_tensor_map_bk(&l->tm_act32, l->ws + L.act, cfg->dtype, R, I, 256, 32);
+      l->bk32_ok = r2 == GLM4MOE_OK;
+    }
   }
   if (cfg->impl == GLM4MOE_IMPL_UMMA && !l->umma_ok) {
     delete l;
@@ -276,6 +289,27 @@ extern "C" int glm4moe_layer_destroy(glm4moe_layer_t* layer) {
 
 // rows of one token tile on the tensor-core path: sized to the mean rows per local expert so a
 // typical expert is one tile (weights cross HBM once; a second tile re-reads them from L2).
+static bool bk32_enabled() {
+  // Off by default: measured SLOWER than the 3 x 64 KB ring (Air T=4096 gate_up 852 -> 881 us, T=8192
+  // 1490 -> 1625 us; profiles/r1d.md) although it keeps 1.5x the bytes in flight: 64-byte boxes cost
+  // more per byte than they gain in look-ahead.  GLM4MOE_BK32=1 turns it on for experiments.
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("GLM4MOE_BK32");
+    v = (e && atoi(e) != 0) ? 1 : 0;
+  }
+  return v == 1;
+}
+
+static bool down2_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("GLM4MOE_NO_DOWN2");   // tuning aid: 1 = plain 128-feature down tiles at prefill
+    v = (e && atoi(e) != 0) ? 0 : 1;
+  }
+  return v == 1;
+}
+
 static int pick_bn_index(const glm4moe_config_t& c, int T) {
   static int forced = -2;
   if (forced == -2) {
@@ -578,6 +612,14 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
     a.up_row_offset = I;
     a.mode = 1;
     a.sched = reinterpret_cast<int32_t*>(ws + L.sched);
+    // prefill tiles: half-size stages (K blocks of 32, 7-deep ring) keep 1.5x the bytes in flight
+    const bool bk32 = tile_rows == 256 && l->bk32_ok && !direct && bk32_enabled();
+    if (bk32) {
+      a.bk = 32;
+      a.tm_w = &l->tm_w_gu32;
+      a.tm_x = &l->tm_x32;
+      a.n_kblocks = H / 32;
+    }
     if (direct) {
       a.tm_x = &tm_xdirect;
       a.direct.tokens = T;
@@ -601,6 +643,19 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
     a.w_rows_per_expert = H;
     a.up_row_offset = 0;
     a.mode = 0;
+    a.bk = 0;
+    if (tile_rows == 256 && H % 256 == 0 && down2_enabled()) {
+      // prefill: 256 features x 256 tokens per CTA tile (two weight tiles share one token tile)
+      a.mode = 3;
+      a.n_feat_tiles = H / 256;
+      a.up_row_offset = 128;
+      if (bk32) {
+        a.bk = 32;
+        a.tm_w = &l->tm_w_d32;
+        a.tm_x = &l->tm_act32;
+        a.n_kblocks = I / 32;
+      }
+    }
     a.sched = reinterpret_cast<int32_t*>(ws + L.sched) + 2;
     if ((rc = umma_launch(a, stream))) return rc;
   } else {

@@ -141,6 +141,18 @@ __device__ __forceinline__ uint64_t make_kmajor_desc(uint32_t saddr) {
   return d;
 }
 
+// K-major operand tile whose rows are 32 two-byte elements = one 64-byte swizzle atom per row
+// (SWIZZLE_64B: 8-row groups of 512 B).  Half-size pipeline stages: finer-grained ring, more bytes
+// in flight for the same shared memory (umma_gemm.cu, BK = 32).
+__device__ __forceinline__ uint64_t make_kmajor_desc_sw64(uint32_t saddr) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((saddr >> 4) & 0x3fffu);
+  d |= static_cast<uint64_t>(512u >> 4) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  d |= static_cast<uint64_t>(4) << 61;            // SWIZZLE_64B
+  return d;
+}
+
 // instruction descriptor, kind::f16: D fp32, A/B both K-major, M = 128, N = n
 __host__ __device__ constexpr uint32_t make_idesc(bool bf16, int n) {
   return (1u << 4)                         // c_format = F32

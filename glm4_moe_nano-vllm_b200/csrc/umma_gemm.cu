@@ -32,14 +32,25 @@ constexpr int kBK = 64;    // 64 two-byte elements = 128 B swizzle atom
 constexpr int kModeDown = 0;    // y = acc * routing weight              (mlp.py:52, moe.py:149)
 constexpr int kModeGated = 1;   // act = silu(acc_gate) * acc_up         (mlp.py:50-51)
 constexpr int kModePlain = 2;   // out = acc (router logits, moe.py:32), features bounded by n_feat_valid
+// Down with TWO 128-feature weight tiles per CTA tile (256 features x BN tokens): the token tile is
+// fetched once for both, so the shared-memory fill per MMA cycle drops from 96 to 64 B/clk at BN = 256
+// (the plain down tile is bound by that fill rate at prefill: profiles/r1d.md).  The two accumulators
+// fill TMEM like the gated tile's (one accumulator stage).
+constexpr int kModeDown2 = 3;
 
-template <int BN, int MODE>
+template <int BN, int MODE, int BK = kBK>
 struct UmmaCfg {
-  static constexpr bool kGated = MODE == kModeGated;
-  static constexpr int kABytes = kBM * kBK * 2;                 // 16 KB per weight tile
-  static constexpr int kBBytes = BN * kBK * 2;
+  static constexpr bool kGated = MODE == kModeGated || MODE == kModeDown2;   // two weight tiles per stage
+  static constexpr int kFeatPerTile = MODE == kModeDown2 ? 2 * kBM : kBM;
+  static constexpr int kABytes = kBM * BK * 2;                  // 16 KB per weight tile (8 KB at BK = 32)
+  static constexpr int kBBytes = BN * BK * 2;
   static constexpr int kStageBytes = (kGated ? 2 : 1) * kABytes + kBBytes;
-  static constexpr int kStages = (212 * 1024) / kStageBytes > 12 ? 12 : (212 * 1024) / kStageBytes;
+  // BK = 32 (64-byte swizzle atoms): half-size stages, ring sized to the whole 227 KB.  The 256-token
+  // two-weight-tile stage is 64 KB at BK = 64, i.e. 3 stages = 2 in flight while one is consumed
+  // (1.4 us of look-ahead; ncu: the MMA warp waits for data 27 % of the time); 7 x 32 KB keeps 6 in
+  // flight (2.1 us).
+  static constexpr int kSmemBudget = BK == 32 ? 232448 - 1536 : 212 * 1024;
+  static constexpr int kStages = kSmemBudget / kStageBytes > 12 ? 12 : kSmemBudget / kStageBytes;
   static constexpr int kAccCols = (kGated ? 2 : 1) * BN;        // TMEM columns per accumulator stage
   static constexpr int kAccStages = 2 * kAccCols <= 512 ? 2 : 1;   // BN=256 gated fills TMEM: 1 stage
   static constexpr int kTmemColsRaw = kAccStages * kAccCols;
@@ -62,8 +73,8 @@ struct UmmaCfg {
 constexpr int kSharedWorkBase = 1 << 30;   // direct mode: work id of the shared expert's feature tile f
 constexpr int kSchedDepth = 4;   // work-index queue between the producer and the consumer warps
 
-template <typename T, int BN, int MODE>
-__global__ void __launch_bounds__(UmmaCfg<BN, MODE>::kThreads, 1) umma_grouped_kernel(
+template <typename T, int BN, int MODE, int BK = kBK>
+__global__ void __launch_bounds__(UmmaCfg<BN, MODE, BK>::kThreads, 1) umma_grouped_kernel(
     const __grid_constant__ CUtensorMap tm_w,   // weights  [rows_w_total, K], box {64, 128}
     const __grid_constant__ CUtensorMap tm_x,   // activation rows [rows_x_total, K], box {64, BN}
     const int4* __restrict__ tiles, const int32_t* __restrict__ num_tiles_ptr, int dense_rows,
@@ -74,9 +85,10 @@ __global__ void __launch_bounds__(UmmaCfg<BN, MODE>::kThreads, 1) umma_grouped_k
     int up_row_offset,                          // gated: I
     int32_t* __restrict__ sched,                // [0] next work index - gridDim, [1] CTAs finished
     const DirectArgs direct) {                  // decode "direct" mode (tokens > 0), see umma_gemm.cuh
-  using Cfg = UmmaCfg<BN, MODE>;
+  using Cfg = UmmaCfg<BN, MODE, BK>;
   constexpr bool GATED = Cfg::kGated;
   constexpr int AS = Cfg::kAccStages;
+  auto kdesc = [](uint32_t saddr) { return BK == 32 ? make_kmajor_desc_sw64(saddr) : make_kmajor_desc(saddr); };
   constexpr int EW = Cfg::kEpiWarps;
   extern __shared__ unsigned char smem_dyn[];
   unsigned char* smem = reinterpret_cast<unsigned char*>(
@@ -157,14 +169,14 @@ __global__ void __launch_bounds__(UmmaCfg<BN, MODE>::kThreads, 1) umma_grouped_k
       auto issue = [&](int kb, int stage, bool do_w, bool do_x) {
         unsigned char* sa = smem + stage * Cfg::kStageBytes;
         if (do_w) {
-          const int w_row = wr.expert * w_rows_per_expert + wr.f * kBM;
+          const int w_row = wr.expert * w_rows_per_expert + wr.f * Cfg::kFeatPerTile;
           mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
-          tma_load_2d(&tm_w, &full_bar[stage], sa, kb * kBK, w_row, kEvictFirst);
+          tma_load_2d(&tm_w, &full_bar[stage], sa, kb * BK, w_row, kEvictFirst);
           if (GATED)
-            tma_load_2d(&tm_w, &full_bar[stage], sa + Cfg::kABytes, kb * kBK, w_row + up_row_offset, kEvictFirst);
+            tma_load_2d(&tm_w, &full_bar[stage], sa + Cfg::kABytes, kb * BK, w_row + up_row_offset, kEvictFirst);
         }
         if (do_x)
-          tma_load_2d(&tm_x, &full_bar[stage], sa + (GATED ? 2 : 1) * Cfg::kABytes, kb * kBK,
+          tma_load_2d(&tm_x, &full_bar[stage], sa + (GATED ? 2 : 1) * Cfg::kABytes, kb * BK,
                       is_direct ? 0 : wr.row_start, kEvictLast);
       };
       if (is_direct) {
@@ -276,11 +288,11 @@ __global__ void __launch_bounds__(UmmaCfg<BN, MODE>::kThreads, 1) umma_grouped_k
         tc_fence_after();
         if (elect_one()) {
           const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
-          const uint64_t a_desc = make_kmajor_desc(sa);
-          const uint64_t u_desc = make_kmajor_desc(sa + Cfg::kABytes);
-          const uint64_t b_desc = make_kmajor_desc(sa + (GATED ? 2 : 1) * Cfg::kABytes);
+          const uint64_t a_desc = kdesc(sa);
+          const uint64_t u_desc = kdesc(sa + Cfg::kABytes);
+          const uint64_t b_desc = kdesc(sa + (GATED ? 2 : 1) * Cfg::kABytes);
 #pragma unroll
-          for (int ks = 0; ks < kBK / 16; ++ks) {
+          for (int ks = 0; ks < BK / 16; ++ks) {
             const uint32_t acc = (kb > 0 || ks > 0) ? 1u : 0u;
             umma_f16(d_tmem, a_desc + 2 * ks, b_desc + 2 * ks, idesc, acc);
             if (GATED) umma_f16(d_tmem + BN, u_desc + 2 * ks, b_desc + 2 * ks, idesc, acc);
@@ -328,7 +340,7 @@ __global__ void __launch_bounds__(UmmaCfg<BN, MODE>::kThreads, 1) umma_grouped_k
       mbar_wait(&tmem_full[as], aphase);
       tc_fence_after();
       const uint32_t t_acc = tmem_base + lane_base + as * Cfg::kAccCols;
-      const int feat = wr.f * kBM + ew * 32 + lane;
+      const int feat = wr.f * Cfg::kFeatPerTile + ew * 32 + lane;
       const bool feat_ok = MODE != kModePlain || feat < n_feat_valid;
       T* out_col = out + static_cast<size_t>(wr.row_start) * ld_out + feat;
 #pragma unroll 1
@@ -360,19 +372,24 @@ __global__ void __launch_bounds__(UmmaCfg<BN, MODE>::kThreads, 1) umma_grouped_k
               }
             }
           }
-        } else if (MODE == kModeDown) {
+        } else if (MODE == kModeDown || MODE == kModeDown2) {
           // lane j (< 16) fetches the routing weight of token column c0 + j once; broadcast by shuffle
           float rw_lane = 1.0f;
           {
             const int row = wr.row_start + c0 + (lane & 15);
             if (c0 + (lane & 15) < wr.nrows && row < n_routed_rows) rw_lane = __ldg(row_weight + row);
           }
+          uint32_t g2[16];
+          if (MODE == kModeDown2) tmem_ld16(t_acc + BN + c0, g2);   // features [128, 256) of the tile
           tmem_ld_wait();
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
             const float rw = __shfl_sync(0xffffffffu, rw_lane, j);
-            if (c0 + j < wr.nrows)
+            if (c0 + j < wr.nrows) {
               out_col[static_cast<size_t>(c0 + j) * ld_out] = Dt<T>::from_f(__uint_as_float(g[j]) * rw);
+              if (MODE == kModeDown2)
+                out_col[static_cast<size_t>(c0 + j) * ld_out + kBM] = Dt<T>::from_f(__uint_as_float(g2[j]) * rw);
+            }
           }
         } else {
           tmem_ld_wait();
@@ -416,26 +433,31 @@ static PFN_encodeTiled get_encode_fn() {
 
 int umma_make_tensor_map(void* map_out, const void* base, int dtype, uint64_t rows, uint64_t cols,
                          uint32_t box_rows) {
+  return umma_make_tensor_map_bk(map_out, base, dtype, rows, cols, box_rows, kBK);
+}
+
+int umma_make_tensor_map_bk(void* map_out, const void* base, int dtype, uint64_t rows, uint64_t cols,
+                            uint32_t box_rows, int bk) {
   PFN_encodeTiled enc = get_encode_fn();
   if (!enc) return GLM4MOE_ERR_DEVICE;
   if (dtype != GLM4MOE_BF16 && dtype != GLM4MOE_F16) return GLM4MOE_ERR_UNSUPPORTED;
-  if (cols % 8 != 0 || box_rows == 0 || box_rows > 256 || rows == 0) return GLM4MOE_ERR_ARG;
+  if (cols % 8 != 0 || box_rows == 0 || box_rows > 256 || rows == 0 || (bk != 64 && bk != 32)) return GLM4MOE_ERR_ARG;
   cuuint64_t dims[2] = {cols, rows};
   cuuint64_t strides[1] = {cols * 2};
-  cuuint32_t box[2] = {static_cast<cuuint32_t>(kBK), box_rows};
+  cuuint32_t box[2] = {static_cast<cuuint32_t>(bk), box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = enc(static_cast<CUtensorMap*>(map_out),
                    dtype == GLM4MOE_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16,
                    2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                   bk == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS ? GLM4MOE_OK : GLM4MOE_ERR_ARG;
 }
 
-template <typename T, int BN, int MODE>
+template <typename T, int BN, int MODE, int BK = kBK>
 static int launch_one(const UmmaLaunch& a, cudaStream_t st) {
-  using Cfg = UmmaCfg<BN, MODE>;
-  auto kern = umma_grouped_kernel<T, BN, MODE>;
+  using Cfg = UmmaCfg<BN, MODE, BK>;
+  auto kern = umma_grouped_kernel<T, BN, MODE, BK>;
   static bool attr_set = false;   // per instantiation
   if (!attr_set) {
     GLM4MOE_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -464,6 +486,13 @@ static int launch_bn(const UmmaLaunch& a, cudaStream_t st) {
 
 template <typename T>
 static int launch_mode(const UmmaLaunch& a, cudaStream_t st) {
+  if (a.bk == 32) {   // half-size stages: the 256-token two-weight-tile configurations only
+    if (a.tile_rows != 256) return GLM4MOE_ERR_ARG;
+    if (a.mode == kModeDown2) return launch_one<T, 256, kModeDown2, 32>(a, st);
+    if (a.mode == kModeGated) return launch_one<T, 256, kModeGated, 32>(a, st);
+    return GLM4MOE_ERR_ARG;
+  }
+  if (a.mode == kModeDown2) return a.tile_rows == 256 ? launch_one<T, 256, kModeDown2>(a, st) : GLM4MOE_ERR_ARG;
   switch (a.mode) {
     case kModeDown: return launch_bn<T, kModeDown>(a, st);
     case kModeGated: return launch_bn<T, kModeGated>(a, st);

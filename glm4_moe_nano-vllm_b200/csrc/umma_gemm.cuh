@@ -29,7 +29,8 @@ struct UmmaLaunch {
   int n_routed_rows;
   int n_feat_tiles;        // ceil(output features / 128)
   int n_feat_valid;        // plain mode: features >= this are not stored
-  int n_kblocks;           // K / 64
+  int n_kblocks;           // K / bk
+  int bk;                  // 0 / 64: 128-byte swizzle atoms; 32: 64-byte atoms, half-size stages (tile_rows 256 only)
   int w_rows_per_expert;
   int up_row_offset;
   int tile_rows;           // BN: 16 / 32 / 64 / 128 / 256
@@ -43,6 +44,9 @@ struct UmmaLaunch {
 // 2-D row-major [rows, cols] two-byte tensor, box {64 cols, box_rows}, 128B swizzle.
 int umma_make_tensor_map(void* map_out, const void* base, int dtype, uint64_t rows, uint64_t cols,
                          uint32_t box_rows);
+// same with box {bk cols, box_rows}: bk = 64 (128B swizzle) or 32 (64B swizzle)
+int umma_make_tensor_map_bk(void* map_out, const void* base, int dtype, uint64_t rows, uint64_t cols,
+                            uint32_t box_rows, int bk);
 int umma_launch(const UmmaLaunch& args, void* stream);
 bool umma_shape_ok(int H, int I, int dtype);
 
