@@ -47,6 +47,8 @@ bool direct_enabled() {
   return g_direct == 1;
 }
 
+int g_router_rows = 0;   // 0: pick by T; 16/32/64/128: token rows per router tile (glm4moe_debug_set(3, v))
+
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct WsLayout {
@@ -150,6 +152,10 @@ extern "C" int glm4moe_debug_set(int knob, int value) {
     case GLM4MOE_KNOB_DIRECT: g_direct = value ? 1 : 0; return GLM4MOE_OK;
     case GLM4MOE_KNOB_FUSED: g_fused = value ? 1 : 0; return GLM4MOE_OK;
     case GLM4MOE_KNOB_FP8_PREFILL: g_fp8_prefill = value ? 1 : 0; return GLM4MOE_OK;
+    case GLM4MOE_KNOB_ROUTER_ROWS:
+      if (value != 0 && value != 16 && value != 32 && value != 64 && value != 128) return GLM4MOE_ERR_ARG;
+      g_router_rows = value;
+      return GLM4MOE_OK;
     default: return GLM4MOE_ERR_ARG;
   }
 }
@@ -416,7 +422,11 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
     alignas(64) CUtensorMap tm_xin;
     // token-tile rows: the gate has a single 128-expert feature tile, so the tile count is the only
     // source of parallelism; small tiles until the tiles alone cover the SMs
-    const int rbn = T >= 128 * l->sm_count ? 128 : T >= 64 * l->sm_count ? 64 : T >= 3200 ? 32 : 16;
+    // The gate's weight tile (E x H, ~1 MB) is re-read from L2 by every token tile, so at prefill the
+    // kernel is bound by L2 bandwidth in proportion to the tile count: 128-token tiles from T = 4096
+    // (32 tiles: each SM then streams its own 2 MB instead of 148 SMs fighting for 160 MB).
+    int rbn = T >= 4096 ? 128 : T >= 3200 ? 32 : 16;
+    if (g_router_rows) rbn = g_router_rows;
     if ((rc = umma_make_tensor_map(&tm_xin, x, c.dtype, static_cast<uint64_t>(T), H, rbn))) return rc;
     UmmaLaunch r{};
     r.tm_w = &l->tm_gate;

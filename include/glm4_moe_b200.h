@@ -61,7 +61,8 @@ int glm4moe_abi_version(void);
  * (decode_fused.cu); 0 = two grouped-GEMM launches.
  * GLM4MOE_KNOB_FP8_PREFILL: 1 (default) = the e4m3 tier uses token-major 128 x 256 tiles once an expert
  * averages >= 48 rows (umma_fp8_prefill.cu); 0 = always the 16..64-token swap-AB tiles (umma_fp8.cu). */
-enum { GLM4MOE_KNOB_DIRECT = 0, GLM4MOE_KNOB_FUSED = 1, GLM4MOE_KNOB_FP8_PREFILL = 2 };
+enum { GLM4MOE_KNOB_DIRECT = 0, GLM4MOE_KNOB_FUSED = 1, GLM4MOE_KNOB_FP8_PREFILL = 2,
+       GLM4MOE_KNOB_ROUTER_ROWS = 3 /* token rows per tensor-core router tile: 0 = by T, 16/32/64/128 */ };
 int glm4moe_debug_set(int knob, int value);
 const char* glm4moe_error_string(int code);
 
