@@ -133,6 +133,9 @@ def main():
     ap.add_argument("--ep-layout", default="p2p", choices=["p2p", "allreduce", "alltoall"],
                     help="expert-parallel layout for --gpus > 1 (distributed.py): p2p = combine + reduction in "
                          "one kernel over NVLink peer memory, allreduce / alltoall = NCCL")
+    ap.add_argument("--weights", default="bf16", choices=["bf16", "fp8"],
+                    help="fp8 = e4m3 expert weights with 128x128 fp32 block scales, per-token 1x128 activations "
+                         "(BASELINE configs[2]); single GPU")
     ap.add_argument("--ep-sliced", type=int, default=-1, choices=[-1, 0, 1],
                     help="p2p layout: -1 pick by size, 0 every rank pulls every row, 1 reduce the own token slice "
                          "and store it to the peers (glm4moe_set_ep_sliced)")
@@ -146,7 +149,11 @@ def main():
     T = args.tokens
     regime = "decode batch" if T <= 256 else "prefill"
     workload = (f"{shape.name} MoE layer (H={shape.H}, E={shape.E}, top-{shape.k}, I={shape.I}, 1 shared) "
-                f"bf16 random-init, {regime} T={T}")
+                f"{'bf16' if args.weights == 'bf16' else 'FP8 e4m3 block-128 expert weights, bf16 activations in/out,'} "
+                f"random-init, {regime} T={T}")
+    fp8 = args.weights == "fp8"
+    if fp8 and world > 1:
+        raise SystemExit("--weights fp8 is a single-GPU bench")
     n_batches = N_BATCHES if T <= 1024 else 4
 
     # ------------------------------------------------------------------ reference arm (CPU)
@@ -190,6 +197,8 @@ def main():
     torch.set_default_dtype(torch.float32)
     weights = synth.make_weights_device(shape, dt, dev, experts=range(moe.expert_begin, moe.expert_end))
     moe.load_local_stacks(weights)
+    if fp8:
+        moe.quantize_fp8(drop_native=True)      # offline conversion (fp8.quantize_block128), outside the timed region
     if world > 1:
         from glm4_moe_b200.distributed import ExpertParallelMoE
         layer = ExpertParallelMoE(moe, shape.E, layout=args.ep_layout)
@@ -308,30 +317,36 @@ def main():
         return
 
     hbm_peak, peak_src, tc_peak = _peaks()
+    if fp8:
+        tc_peak *= 2.0      # no measured FP8 figure in MEASURED_PEAKS.json: dense e4m3 = 2 x the bf16 rate
     H, I, k = shape.H, shape.I, shape.k
     # dominant kernel: gate_up grouped GEMM. Algorithmic bytes of one launch = gate_up weights of
     # the (U local + shared) experts it touches + the activation rows it reads + act rows it writes.
     n_sh = 1
+    wb = 1 if fp8 else 2          # bytes per expert-weight element (and per gathered / activation row element)
     rows = T * k / world + T / world
     gu_ms = stage_acc["gate_up"]
     if fused:
         # decode regime: gate_up + SiLU*mul + down + combine are ONE persistent launch
         # (decode_fused.cu); the "gate_up" stage interval brackets exactly that launch.
         kern = "decode_fused_kernel<gate_up+silu_mul+down+combine>"
-        gu_bytes = (U + n_sh) * 3 * I * H * 2 + (T / world) * H * 2 + T * H * 2
+        gu_bytes = (U + n_sh) * 3 * I * H * wb + (T / world) * H * 2 + T * H * 2
     else:
-        kern = "umma_grouped_kernel<gate_up+silu_mul>"
-        gu_bytes = (U + n_sh) * 2 * I * H * 2 + rows * H * 2 + rows * I * 2
+        kern = ("umma_fp8_prefill_kernel<gate_up+silu_mul+requant>" if fp8 and T * k / shape.E >= 48 else
+                "umma_fp8_kernel<gate_up+silu_mul>" if fp8 else "umma_grouped_kernel<gate_up+silu_mul>")
+        gu_bytes = (U + n_sh) * 2 * I * H * wb + rows * H * wb + rows * I * wb
     achieved = gu_bytes / gu_ms / 1e6
     gu_flops = rows * 2 * H * 2 * I
     # DRAM traffic of the same launch from the committed `ncu --set full` capture (profiles/ncu_traffic.json)
     traffic = None
     try:
         tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
-        traffic = tj.get(f"{kern.split('<')[0]}:T={T}:bf16") if world == 1 else None
+        base = kern.split('<')[0]
+        traffic = (tj.get(f"{base}:T={T}:{args.weights}") or tj.get(f"{base}<gate_up>:T={T}:{args.weights}")) \
+            if world == 1 else None
     except (OSError, ValueError):
         pass
-    layer_bytes = shape.algorithmic_bytes(T, U) if world == 1 else None
+    layer_bytes = shape.algorithmic_bytes(T, U, weight_bytes=wb, fp8_scales=fp8) if world == 1 else None
     roofline = {"bound": "hbm", "kernel": kern, "achieved": achieved,
                 "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": traffic,
                 "peak_source": peak_src, "kernel_ms": gu_ms, "algorithmic_bytes_per_launch": gu_bytes,
@@ -340,6 +355,7 @@ def main():
         # prefill: the grouped GEMMs are a dense contraction bound by the tensor pipe
         roofline.update({"bound": "tensor", "achieved": gu_flops / gu_ms / 1e9, "peak": tc_peak, "unit": "TFLOP/s",
                          "frac": gu_flops / gu_ms / 1e9 / tc_peak, "algorithmic_flops_per_launch": gu_flops,
+                         "peak_source": peak_src + (" x 2 for e4m3 (no measured FP8 peak)" if fp8 else ""),
                          "hbm": {"achieved": achieved, "peak": hbm_peak, "frac": achieved / hbm_peak}})
         fl = shape.flops_per_token() * T / world
         roofline["layer_tensor"] = {"algorithmic_flops": fl, "achieved": fl / ms_step / 1e9,
@@ -357,7 +373,8 @@ def main():
                                   "reference torch path (moe.py:128-176), torch threads = all host cores"}
     line = {"metric": METRIC, "value": T * 1e3 / ms_step, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "scaling": "strong", "vs_baseline": None, "dtype": "bf16" if not fp8 else "fp8_e4m3 (fp32 block scales, fp32 accumulate)",
+            "data": "synthetic",
             "config": {"workload": workload, "tokens_per_step": T, "experts_hit_mean": U,
                        "parallelism": (f"ep{world}-{args.ep_layout}" + (f"-sliced{args.ep_sliced}" if args.ep_sliced >= 0 else ""))
                        if world > 1 else "single",
