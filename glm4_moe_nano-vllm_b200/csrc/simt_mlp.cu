@@ -146,6 +146,38 @@ __global__ void __launch_bounds__(256) combine_kernel(const T* __restrict__ y,
   pdl_launch();
   if (threadIdx.x < k) rows[threadIdx.x] = slot_row[static_cast<size_t>(t) * k + threadIdx.x];
   __syncthreads();
+  constexpr int KMAX = 8;
+  if (k <= KMAX) {
+    // All row loads of a column chunk are issued before the first add (k + 1 independent 16-byte loads in
+    // flight per thread instead of one: the kernel is a pure HBM gather), then summed in slot order.
+    const int sh_row = (t >= sh_lo && t < sh_hi) ? Tn * k + t : -1;
+    for (int c = threadIdx.x; c < nvec; c += blockDim.x) {
+      uint4 raw[KMAX + 1];
+#pragma unroll
+      for (int s = 0; s < KMAX; ++s)
+        if (s < k && rows[s] >= 0)
+          raw[s] = ld_stream16(reinterpret_cast<const uint4*>(y + static_cast<size_t>(rows[s]) * H) + c);
+      if (sh_row >= 0) raw[KMAX] = ld_stream16(reinterpret_cast<const uint4*>(y + static_cast<size_t>(sh_row) * H) + c);
+      float acc[V];
+#pragma unroll
+      for (int q = 0; q < V; ++q) acc[q] = 0.f;
+#pragma unroll
+      for (int s = 0; s <= KMAX; ++s) {
+        const bool on = s < KMAX ? (s < k && rows[s] >= 0) : sh_row >= 0;
+        if (on) {
+          float v[V];
+          unpack16<T>(raw[s], v);
+#pragma unroll
+          for (int q = 0; q < V; ++q) acc[q] += v[q];
+        }
+      }
+      __align__(16) T o[V];
+#pragma unroll
+      for (int q = 0; q < V; ++q) o[q] = Dt<T>::from_f(acc[q]);
+      reinterpret_cast<uint4*>(out + static_cast<size_t>(t) * H)[c] = *reinterpret_cast<uint4*>(o);
+    }
+    return;
+  }
   for (int c = threadIdx.x; c < nvec; c += blockDim.x) {
     float acc[V];
 #pragma unroll
