@@ -350,6 +350,8 @@ def main():
     roofline = {"bound": "hbm", "kernel": kern, "achieved": achieved,
                 "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": traffic,
                 "peak_source": peak_src, "kernel_ms": gu_ms, "algorithmic_bytes_per_launch": gu_bytes,
+                "peak_note": "hbm_gbs of MEASURED_PEAKS.json is a read+write copy; read-only bulk-copy streaming on the "
+                             "same box type reaches 7.2 TB/s (profiles/r1d_ubench.jsonl), so frac can exceed 1",
                 "stage_ms": stage_acc}
     if T * k / shape.E >= 96 and not fused:    # rows per local expert do not depend on the world size
         # prefill: the grouped GEMMs are a dense contraction bound by the tensor pipe
