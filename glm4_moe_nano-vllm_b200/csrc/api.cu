@@ -222,10 +222,15 @@ extern "C" int glm4moe_layer_create(const glm4moe_config_t* cfg, const void* gat
   l->last_impl = GLM4MOE_IMPL_AUTO;
   l->last_fused = 0;
   l->events_ready = false;
-  if (cudaMemset(l->ws + L.sched, 0, 256) != cudaSuccess ||
+  // The self-re-arming counters start at zero.  The workspace usually comes from a stream-ordered
+  // caching allocator and forwards run on the caller's (non-blocking) stream, which is not ordered
+  // against the legacy stream these memsets run on: fence the device on both sides.  Creation is
+  // rare (once per layer / capacity change) and never happens inside a graph capture.
+  if (cudaDeviceSynchronize() != cudaSuccess ||
+      cudaMemset(l->ws + L.sched, 0, 256) != cudaSuccess ||
       cudaMemset(l->ws + L.ready, 0, (cfg->n_routed_experts + 8) * 4) != cudaSuccess ||
       cudaMemset(l->ws + L.fdone, 0, (cfg->hidden_size / 128 + 8) * 4) != cudaSuccess ||
-      cudaMemset(l->ws + L.ctl, 0, kEpCtlBytes) != cudaSuccess) {
+      cudaMemset(l->ws + L.ctl, 0, kEpCtlBytes) != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess) {
     delete l;
     return GLM4MOE_ERR_DEVICE;
   }

@@ -126,6 +126,20 @@ inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, siz
   return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
 }
 
+// cudaFuncAttributeMaxDynamicSharedMemorySize is per device (per context): set it once per
+// (kernel instantiation, device).  `done` is the instantiation's own bit mask of devices served.
+template <typename K>
+inline cudaError_t ensure_dynamic_smem(K kern, int bytes, unsigned long long* done) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  const unsigned long long bit = 1ull << (dev & 63);
+  if (*done & bit) return cudaSuccess;
+  e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e == cudaSuccess) *done |= bit;
+  return e;
+}
+
 inline int dtype_size(int dtype) { return dtype == GLM4MOE_F32 ? 4 : 2; }
 
 // dispatch a templated launcher on the model dtype

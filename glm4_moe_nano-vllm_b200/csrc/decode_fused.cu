@@ -726,11 +726,8 @@ template <typename T, int BN, bool FP8>
 static int launch_fused_one(const DecodeFusedLaunch& a, cudaStream_t st) {
   using Cfg = FusedCfg<BN, FP8>;
   auto kern = decode_fused_kernel<T, BN, FP8>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    GLM4MOE_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
-    attr_set = true;
-  }
+  static unsigned long long attr_done = 0;   // per instantiation, one bit per device
+  GLM4MOE_CUDA_CHECK(ensure_dynamic_smem(kern, 232448, &attr_done));
   if (FP8 && (a.H / 128 > 64 || a.I / 128 > 64 || Cfg::kSmemBytes + a.H / 128 * BN * 4 > 232448))
     return GLM4MOE_ERR_UNSUPPORTED;
   const size_t smem_bytes = Cfg::kSmemBytes + (FP8 ? a.H / 128 * BN * 4 : 0);

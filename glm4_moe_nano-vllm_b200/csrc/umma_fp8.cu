@@ -409,11 +409,8 @@ template <typename T, int BN, bool GATED>
 static int launch_fp8_one(const UmmaFp8Launch& a, cudaStream_t st) {
   using Cfg = Fp8Cfg<BN, GATED>;
   auto kern = umma_fp8_kernel<T, BN, GATED>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    GLM4MOE_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
-    attr_set = true;
-  }
+  static unsigned long long attr_done = 0;   // per instantiation, one bit per device
+  GLM4MOE_CUDA_CHECK(ensure_dynamic_smem(kern, Cfg::kSmemBytes, &attr_done));
   GLM4MOE_CUDA_CHECK(launch_pdl(kern, dim3(a.grid), dim3(Cfg::kThreads), Cfg::kSmemBytes, st,
                                 *static_cast<const CUtensorMap*>(a.tm_w), *static_cast<const CUtensorMap*>(a.tm_x),
                                 a.w_scale, a.x_scale_t, a.x_scale_ld, reinterpret_cast<const int4*>(a.tiles),

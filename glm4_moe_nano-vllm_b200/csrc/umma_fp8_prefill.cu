@@ -345,11 +345,8 @@ __global__ void __launch_bounds__(kPThreads, 1) umma_fp8_prefill_kernel(
 template <typename T, bool GATED>
 static int launch_prefill_one(const UmmaFp8PrefillLaunch& a, cudaStream_t st) {
   auto kern = umma_fp8_prefill_kernel<T, GATED>;
-  static bool attr_set = false;   // per instantiation
-  if (!attr_set) {
-    GLM4MOE_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kPSmemBytes));
-    attr_set = true;
-  }
+  static unsigned long long attr_done = 0;   // per instantiation, one bit per device
+  GLM4MOE_CUDA_CHECK(ensure_dynamic_smem(kern, kPSmemBytes, &attr_done));
   GLM4MOE_CUDA_CHECK(launch_pdl(kern, dim3(a.grid), dim3(kPThreads), kPSmemBytes, st,
                                 *static_cast<const CUtensorMap*>(a.tm_w), *static_cast<const CUtensorMap*>(a.tm_x),
                                 a.w_scale, a.x_scale_t, a.scale_ld, reinterpret_cast<const int4*>(a.tiles),

@@ -458,12 +458,8 @@ template <typename T, int BN, int MODE, int BK = kBK>
 static int launch_one(const UmmaLaunch& a, cudaStream_t st) {
   using Cfg = UmmaCfg<BN, MODE, BK>;
   auto kern = umma_grouped_kernel<T, BN, MODE, BK>;
-  static bool attr_set = false;   // per instantiation
-  if (!attr_set) {
-    GLM4MOE_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                            Cfg::kSmemBytes));
-    attr_set = true;
-  }
+  static unsigned long long attr_done = 0;   // per instantiation, one bit per device
+  GLM4MOE_CUDA_CHECK(ensure_dynamic_smem(kern, Cfg::kSmemBytes, &attr_done));
   GLM4MOE_CUDA_CHECK(launch_pdl(
       kern, dim3(a.grid), dim3(Cfg::kThreads), Cfg::kSmemBytes, st, *static_cast<const CUtensorMap*>(a.tm_w),
       *static_cast<const CUtensorMap*>(a.tm_x), reinterpret_cast<const int4*>(a.tiles), a.num_tiles, a.dense_rows,

@@ -94,6 +94,27 @@ class GlmMoeSelectTopk(nn.Module):
         self.register_buffer("e_score_correction_bias",
                              torch.zeros((self.n_routed_experts,), dtype=torch.float32))
 
+    def _apply(self, fn, recurse=True):
+        """`.half()` / `.bfloat16()` / `.to(dtype)` cast floating-point buffers too (nn.Module._apply);
+        the kernels read `e_score_correction_bias` as fp32 (moe.py:26,38), so the buffer follows device
+        moves only and keeps its exact fp32 values."""
+        bias = self.e_score_correction_bias
+        out = super()._apply(fn, recurse)
+        moved = self.e_score_correction_bias
+        if moved.dtype != torch.float32:
+            self.e_score_correction_bias = bias.to(device=moved.device, dtype=torch.float32)
+        return out
+
+    def bias_ptr(self) -> int:
+        """Device pointer of the fp32 bias, validated (the library reads E * 4 bytes from it)."""
+        b = self.e_score_correction_bias
+        if b.dtype != torch.float32 or not b.is_contiguous() or b.numel() != self.n_routed_experts:
+            raise _lib.Glm4MoeLibraryError(
+                f"gate.e_score_correction_bias must be a contiguous fp32 [{self.n_routed_experts}] buffer, "
+                f"got {b.dtype} {tuple(b.shape)}")
+        _lib.require_cuda(b, "gate.e_score_correction_bias")
+        return b.data_ptr()
+
     def forward(self, hidden_states: torch.Tensor, return_logits: bool = False):
         lib = _lib.load()
         H = self.config.hidden_size
@@ -109,7 +130,7 @@ class GlmMoeSelectTopk(nn.Module):
         st = _lib.stream_ptr(h.device)
         _lib.check(lib.glm4moe_router_logits(h.data_ptr(), self.weight.data_ptr(), logits.data_ptr(), T, H, E, dt, st),
                    "router_logits")
-        _lib.check(lib.glm4moe_router_select(logits.data_ptr(), self.e_score_correction_bias.data_ptr(), T, E, k,
+        _lib.check(lib.glm4moe_router_select(logits.data_ptr(), self.bias_ptr(), T, E, k,
                                              float(self.routed_scaling_factor), dt, idx.data_ptr(), w.data_ptr(), st),
                    "router_select")
         out = (idx.to(torch.int64), w.to(h.dtype))
@@ -131,7 +152,8 @@ class Glm4MoeMoE(nn.Module):
       max_tokens   initial workspace capacity in tokens (grows on demand outside graph capture)
       ep_rank/ep_size  expert-parallel shard: this module then owns experts
                    [rank*E/size, (rank+1)*E/size) and `forward` returns the *partial* sum over the
-                   local experts (+ the shared expert on rank 0 only); see distributed.py
+                   local experts (+ the shared expert on this rank's 1/size slice of the tokens,
+                   `with_shared = 2`); see distributed.py
       impl         "auto" | "simt" | "umma": expert-GEMM implementation
     """
 
@@ -174,7 +196,10 @@ class Glm4MoeMoE(nn.Module):
         return list(self.experts) + [self.shared_experts]
 
     def _apply(self, fn, recurse=True):
-        """Keep per-expert parameters aliased to the stacks across .to()/.cuda()/.half()."""
+        """Keep per-expert parameters aliased to the stacks across .to()/.cuda()/.half().  Only the two
+        stacks are moved / cast: the per-expert views are parked on an empty tensor while
+        `nn.Module._apply` walks the parameters (it would otherwise copy every view on its own, a second
+        full copy of the stack on the target device) and re-aliased afterwards."""
         self._destroy_handle()
         self._w_gate_up = fn(self._w_gate_up)
         self._w_down = fn(self._w_down)
@@ -182,11 +207,21 @@ class Glm4MoeMoE(nn.Module):
             dev = self._w_gate_up.device
             self._wq_gate_up, self._wq_down = self._wq_gate_up.to(dev), self._wq_down.to(dev)
             self._s_gate_up, self._s_down = self._s_gate_up.to(dev), self._s_down.to(dev)
+        park = torch.empty((0,), dtype=self._w_gate_up.dtype, device=self._w_gate_up.device)
+        for mlp in self._mlps():
+            mlp.gate_up_proj.weight.data = park
+            mlp.down_proj.weight.data = park
         out = super()._apply(fn, recurse)
-        for i, mlp in enumerate(self._mlps()):
-            mlp.gate_up_proj.weight.data = self._w_gate_up[i]
-            mlp.down_proj.weight.data = self._w_down[i]
+        self._alias_experts()
         return out
+
+    def _alias_experts(self):
+        """Point `experts.{i}.*.weight` / `shared_experts.*.weight` at their slices of the stacks (or at
+        the empty stack after `quantize_fp8(drop_native=True)`)."""
+        dropped = self._w_gate_up.dim() != 3
+        for i, mlp in enumerate(self._mlps()):
+            mlp.gate_up_proj.weight.data = self._w_gate_up if dropped else self._w_gate_up[i]
+            mlp.down_proj.weight.data = self._w_down if dropped else self._w_down[i]
 
     def _destroy_handle(self):
         if getattr(self, "_handle", None) is not None:
@@ -252,7 +287,7 @@ class Glm4MoeMoE(nn.Module):
             wgu, wd, sgu, sd = self._w_gate_up.data_ptr(), self._w_down.data_ptr(), None, None
         with torch.cuda.device(dev):
             _lib.check(lib.glm4moe_layer_create(C.byref(cfg), self.gate.weight.data_ptr(),
-                                                self.gate.e_score_correction_bias.data_ptr(), wgu, wd, sgu, sd,
+                                                self.gate.bias_ptr(), wgu, wd, sgu, sd,
                                                 base, nbytes, C.byref(handle)), "layer_create")
         self._handle = handle
         self._cfg = cfg
@@ -269,9 +304,7 @@ class Glm4MoeMoE(nn.Module):
             dev, dt = self._w_gate_up.device, self._w_gate_up.dtype
             self._w_gate_up = torch.empty((0,), device=dev, dtype=dt)
             self._w_down = torch.empty((0,), device=dev, dtype=dt)
-            for mlp in self._mlps():
-                mlp.gate_up_proj.weight.data = self._w_gate_up
-                mlp.down_proj.weight.data = self._w_down
+            self._alias_experts()
         return self
 
     def dequantized_weights(self) -> dict:

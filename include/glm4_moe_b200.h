@@ -5,7 +5,8 @@
  * of its own).  Each entry point names the reference code it replaces.
  * All pointers are raw device pointers unless the name says `_host`; sizes are element counts;
  * `stream` is a `cudaStream_t` passed as `void*`.  No entry point allocates device memory,
- * none synchronises except `glm4moe_layer_forward_host`.  Return value: 0 = ok, <0 = argument /
+ * none synchronises except `glm4moe_layer_forward_host` (its stream) and `glm4moe_layer_create`
+ * (the device, once: it zeroes the workspace counters).  Return value: 0 = ok, <0 = argument /
  * support error (GLM4MOE_ERR_*), >0 = `cudaError_t`.
  *
  * Row space used by permute / expert GEMMs / combine:

@@ -182,3 +182,44 @@ def test_offline_fp8_conversion_round_trip(tmp_path):
     assert torch.equal(moe._s_gate_up, s_gu)
     assert torch.equal(moe._wq_down.view(torch.uint8), q_d.view(torch.uint8))
     assert torch.equal(moe._s_down, s_d)
+
+
+def test_casts_keep_bias_fp32_and_move_only_the_stacks():
+    """`.bfloat16()` / `.to(dtype)` cast floating-point buffers (nn.Module._apply); the library
+    reads `e_score_correction_bias` as E fp32 values, so it must stay fp32 with its exact values, and
+    per-expert parameters must stay views of the two stacks (no second copy)."""
+    shape = synth.MINI
+    moe = glm4_moe_b200.Glm4MoeMoE(_cfg(shape))
+    w = synth.make_weights(shape, torch.float32)
+    moe.load_stacked(w)
+    for cast in (lambda m: m.bfloat16(), lambda m: m.to(torch.float16), lambda m: m.to(torch.bfloat16)):
+        m = cast(moe)
+        assert m.gate.e_score_correction_bias.dtype == torch.float32
+        assert torch.equal(m.gate.e_score_correction_bias, w["bias"])
+        assert m.gate.weight.dtype in (torch.bfloat16, torch.float16)
+        base = m._w_gate_up.untyped_storage().data_ptr()
+        for i, mlp in enumerate(m._mlps()):
+            assert mlp.gate_up_proj.weight.untyped_storage().data_ptr() == base
+            assert mlp.gate_up_proj.weight.shape == (2 * shape.I, shape.H)
+            assert mlp.down_proj.weight.data_ptr() == m._w_down[i].data_ptr()
+    # a bias of the wrong dtype is rejected before its pointer reaches the library
+    moe.gate.e_score_correction_bias = moe.gate.e_score_correction_bias.to(torch.bfloat16)
+    with pytest.raises(_lib.Glm4MoeLibraryError):
+        moe.gate.bias_ptr()
+
+
+def test_apply_after_dropping_the_native_stacks():
+    """`.to()` after `quantize_fp8(drop_native=True)` (empty native stacks) must not index them."""
+    shape = synth.MoeShape(256, 4, 2, 128, 1.0, "drop-native")
+    prev = torch.get_default_dtype()
+    torch.set_default_dtype(torch.bfloat16)
+    try:
+        moe = glm4_moe_b200.Glm4MoeMoE(_cfg(shape))
+    finally:
+        torch.set_default_dtype(prev)
+    moe.load_stacked(synth.make_weights(shape, torch.bfloat16))
+    moe.quantize_fp8(drop_native=True)
+    moe = moe.to(torch.bfloat16).to("cpu")
+    assert moe._w_gate_up.numel() == 0 and moe.experts[0].gate_up_proj.weight.numel() == 0
+    assert moe._wq_gate_up.shape == (shape.E + 1, 2 * shape.I, shape.H)
+    assert moe.gate.e_score_correction_bias.dtype == torch.float32
