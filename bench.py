@@ -4,17 +4,20 @@
 A "step" is one forward of the sparse-expert block over one batch of T synthetic tokens
 (default T=32, the top of north_star's decode 1-32 range).  One JSON line on stdout:
 
-  value      tokens/s with the token batches already resident in HBM (CUDA events, K steps)
+  value      tokens/s with the token batches already resident in HBM (CUDA events over exactly K steps,
+             max over ranks); `ms_per_step_median` = median of per-step event pairs taken in a second loop
   e2e        same metric through the module's host-buffer entry (pinned host in, pinned host
              out, H2D + D2H inside the timed region)
-  roofline   HBM roofline of the dominant kernel (gate_up grouped GEMM), timed live with CUDA
+  roofline   HBM (decode) or tensor (prefill) roofline of the dominant kernel, timed live with CUDA
              events between stages (glm4moe_layer_forward_timed)
-  cpu_baseline  the oracle port of the reference's torch path on the box's host cores (N=1, rank 0)
+  cpu_baseline  the reference's own torch path on the box's host cores (N=1, rank 0)
 
-`--impl reference` times the reference's CPU torch path (oracle port — the reference itself
-cannot travel to the GPU box) on the same workload.  N>1: expert-parallel (experts sharded over
+`--impl reference` times the reference's CPU torch path on the same workload: the REAL reference
+module from `oracle/_ref/` (installed by `oracle/make_ref.py`; `kind: "reference"`), or the oracle
+port of it when that copy is absent (`kind: "port"`).  N>1: expert-parallel (experts sharded over
 ranks, tokens replicated; the weighted expert rows are combined and reduced across ranks by one kernel
-reading NVLink peer memory, `--ep-layout allreduce` = NCCL instead), strong scaling.
+reading NVLink peer memory, `--ep-layout allreduce` = NCCL instead), strong scaling; one batch is
+checked bit for bit against a single-GPU forward outside the timed region (`ep_bit_identical`).
 """
 from __future__ import annotations
 
@@ -38,6 +41,7 @@ from glm4_moe_b200 import synth  # noqa: E402
 METRIC = "GLM-4.5-Air MoE-layer tokens/s"
 UNIT = "tokens/s"
 N_BATCHES = 16          # distinct token batches rotated through the timed region
+READ_STREAM_GBS = 7200.0    # read-only bulk-copy streaming measured on this box type (profiles/r1d_ubench.jsonl)
 
 
 def _peaks():
@@ -45,11 +49,23 @@ def _peaks():
     if os.path.exists(p):
         d = json.load(open(p))
         return d["hbm_gbs"], "measured (MEASURED_PEAKS.json)", d.get("bf16_tflops", 1650.0)
-    return 6650.0, "fallback (B200_PROFILING.md)", 1650.0
+    return 6650.0, "fallback (B200_PROFILING.md)", 1590.0
+
+
+def _fp8_peak(bf16_peak):
+    """Dense e4m3 peak: measured by scripts/fp8_peak.py on the box (profiles/fp8_peak_r2.json) when
+    committed, else 2 x the measured bf16 rate (stated as an assumption)."""
+    p = os.path.join(ROOT, "profiles", "fp8_peak_r2.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["fp8_tflops"]), "measured (profiles/fp8_peak_r2.json)"
+        except (OSError, ValueError, KeyError):
+            pass
+    return 2.0 * bf16_peak, "2 x the measured bf16 peak (no measured FP8 figure)"
 
 
 class ClockSampler:
-    """Samples SM clocks / throttle reasons during the timed region (nvidia-smi query fields)."""
+    """Samples SM clocks / throttle reasons during the timed region (NVML, ~1 ms period)."""
 
     def __init__(self, index: int):
         self.index, self.samples, self.reasons = index, [], set()
@@ -76,24 +92,30 @@ class ClockSampler:
                         self.reasons.add(n)
             except Exception:
                 pass
-            time.sleep(0.02)
+            time.sleep(0.001)
 
-    def __enter__(self):
-        if self._nv is not None:
+    def start(self):
+        if self._nv is not None and self._thr is None:
             self._thr = threading.Thread(target=self._run, daemon=True)
             self._thr.start()
+            time.sleep(0.005)      # the thread is up and sampling before the caller goes on
         return self
 
-    def __exit__(self, *a):
+    def mark(self):
+        """Samples taken so far are outside the timed region: forget them."""
+        self.samples.clear()
+        self.reasons.clear()
+
+    def stop(self):
         self._stop.set()
         if self._thr:
             self._thr.join()
 
     def summary(self):
         if not self.samples:
-            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": 0}
         return {"sm_mhz": statistics.median(self.samples), "sm_max_mhz": self.max_mhz,
-                "reasons": sorted(self.reasons)}
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
 
 
 def _hf_config(shape):
@@ -103,20 +125,60 @@ def _hf_config(shape):
                          routed_scaling_factor=shape.routed_scaling_factor, norm_topk_prob=True)
 
 
-def _cpu_reference_run(shape, dt, weights, T, steps, warmup):
-    """The reference's CPU torch path (oracle port) on the host cores. Returns (tok/s, ms/step)."""
-    from oracle import moe_oracle as O
+def _workload(shape, T, fp8):
+    regime = "decode batch" if T <= 256 else "prefill"
+    return (f"{shape.name} MoE layer (H={shape.H}, E={shape.E}, top-{shape.k}, I={shape.I}, 1 shared) "
+            f"{'FP8 e4m3 block-128 expert weights, bf16 activations in/out,' if fp8 else 'bf16'} "
+            f"random-init, {regime} T={T}")
+
+
+def _config(shape, T, fp8, n_batches):
+    """The `config` object: identical in both arms (the driver compares them)."""
+    return {"workload": _workload(shape, T, fp8), "tokens_per_step": T,
+            "l2": f"{n_batches} distinct token batches rotated; expert weights touched per step exceed the 126 MB L2 "
+                  "from T >= 2 (no L2 flush between steps)"}
+
+
+class _CpuReference:
+    """The reference's CPU torch path on the host cores: the real module when oracle/_ref exists."""
+
+    def __init__(self, shape, dt, weights):
+        from oracle import reference_live as R
+        self.shape, self.weights = shape, weights
+        self.kind = "reference" if R.available() else "port"
+        self.what = ("the reference's own Glm4MoeMoE.forward (moe.py:128-176) imported from oracle/_ref "
+                     "(debug file read patched out)") if self.kind == "reference" else \
+            "oracle port of the reference torch path (moe.py:128-176); oracle/_ref not installed"
+        self.module = None
+        if self.kind == "reference":
+            self.module = R.build_reference_module(shape, dt)
+            R.fill_reference_module(self.module, weights)
+
+    def __call__(self, x):
+        if self.module is not None:
+            return self.module(x)
+        from oracle import moe_oracle as O
+        return O.moe_forward(x, self.weights, self.shape.k, self.shape.routed_scaling_factor)["out"]
+
+
+def _cpu_reference_run(shape, dt, weights, T, steps, warmup, budget_s=150.0):
+    """Returns (tok/s, ms/step, cores, steps actually timed, kind, what)."""
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
+    ref = _CpuReference(shape, dt, weights)
     xs = [synth.make_tokens(shape, T, dt, b) for b in range(min(N_BATCHES, steps + warmup))]
     with torch.inference_mode():
         for i in range(warmup):
-            O.moe_forward(xs[i % len(xs)], weights, shape.k, shape.routed_scaling_factor)
+            ref(xs[i % len(xs)])
         t0 = time.perf_counter()
+        done = 0
         for i in range(steps):
-            O.moe_forward(xs[(warmup + i) % len(xs)], weights, shape.k, shape.routed_scaling_factor)
+            ref(xs[(warmup + i) % len(xs)])
+            done += 1
+            if time.perf_counter() - t0 > budget_s:      # bounded sample: a prefill step takes seconds on a CPU
+                break
         dt_s = time.perf_counter() - t0
-    return T * steps / dt_s, dt_s / steps * 1e3, cores
+    return T * done / dt_s, dt_s / done * 1e3, cores, done, ref.kind, ref.what
 
 
 def main():
@@ -139,6 +201,9 @@ def main():
     ap.add_argument("--ep-sliced", type=int, default=-1, choices=[-1, 0, 1],
                     help="p2p layout: -1 pick by size, 0 every rank pulls every row, 1 reduce the own token slice "
                          "and store it to the peers (glm4moe_set_ep_sliced)")
+    ap.add_argument("--no-ep-check", action="store_true", help="skip the single-GPU bit-identity check at N > 1")
+    ap.add_argument("--one-forward", action="store_true",
+                    help="after warm-up run ONE forward of batch 0 and exit (the launch an ncu capture profiles)")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -147,30 +212,26 @@ def main():
     shape = synth.SHAPES[args.shape]
     dt = torch.bfloat16
     T = args.tokens
-    regime = "decode batch" if T <= 256 else "prefill"
-    workload = (f"{shape.name} MoE layer (H={shape.H}, E={shape.E}, top-{shape.k}, I={shape.I}, 1 shared) "
-                f"{'bf16' if args.weights == 'bf16' else 'FP8 e4m3 block-128 expert weights, bf16 activations in/out,'} "
-                f"random-init, {regime} T={T}")
     fp8 = args.weights == "fp8"
     if fp8 and world > 1:
         raise SystemExit("--weights fp8 is a single-GPU bench")
     n_batches = N_BATCHES if T <= 1024 else 4
+    config = _config(shape, T, fp8, n_batches)
 
     # ------------------------------------------------------------------ reference arm (CPU)
     if args.impl == "reference":
         if rank != 0:
             return
         weights = synth.make_weights(shape, dt)
-        steps = max(1, min(args.steps, 8))
-        warm = max(1, min(args.warmup, 2))
-        tps, ms, cores = _cpu_reference_run(shape, dt, weights, T, steps, warm)
+        steps, warm = max(1, args.steps), max(1, args.warmup)
+        tps, ms, cores, done, kind, what = _cpu_reference_run(shape, dt, weights, T, steps, warm)
         line = {"metric": METRIC, "value": tps, "unit": UNIT, "impl": "reference", "n_gpus": args.gpus,
-                "steps": steps, "warmup": warm, "ms_per_step": ms, "higher_is_better": True,
+                "steps": done, "warmup": warm, "ms_per_step": ms, "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-                "config": {"workload": workload, "tokens_per_step": T},
-                "cpu_baseline": {"value": tps, "unit": UNIT, "cores": cores, "kind": "port",
-                                 "sample": f"{steps} steps of the full workload after {warm} warm-up "
-                                           "(oracle port of moe.py:128-176; steps capped at 8)"},
+                "config": config,
+                "cpu_baseline": {"value": tps, "unit": UNIT, "cores": cores, "kind": kind,
+                                 "sample": f"{done} steps of the full workload after {warm} warm-up: {what}; "
+                                           f"torch threads = all {cores} host cores"},
                 "e2e": {"value": tps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
         print(json.dumps(line))
         return
@@ -214,20 +275,33 @@ def main():
     def step(x):
         return layer(x)
 
+    clk = ClockSampler(local_rank)
     with torch.inference_mode():
         for i in range(max(args.warmup, 3)):
             step(batches[i % n_batches])
         torch.cuda.synchronize()
+        if args.one_forward:
+            step(batches[0])
+            torch.cuda.synchronize()
+            return
+        # ---- timed region: exactly K steps, CUDA events, max over ranks.  Everything host-side that
+        # differs per rank (NVML init, thread start) happens BEFORE the barrier; a tiny NCCL all-reduce
+        # enqueued right in front of the start event is the cross-rank *device* barrier, so no rank's clock
+        # starts while a peer is still behind (a p2p step spins on its peers' flags). ----
+        clk.start()
+        start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        sync_t = torch.zeros(1, device=dev)
+        torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
-        start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        with ClockSampler(local_rank) as clk:
-            torch.cuda.synchronize()
-            start.record()
-            for i in range(args.steps):
-                step(batches[i % n_batches])
-            end.record()
-            torch.cuda.synchronize()
+            dist.all_reduce(sync_t)
+        clk.mark()
+        start.record()
+        for i in range(args.steps):
+            step(batches[i % n_batches])
+        end.record()
+        torch.cuda.synchronize()
+        clocks = clk.summary()
         if world > 1:
             dist.barrier()
         ms_total = start.elapsed_time(end)
@@ -238,6 +312,25 @@ def main():
         ms_step = ms_total / args.steps
         launches = moe.last_launches * args.steps
         fused, impl_name = moe.last_fused, moe.last_impl     # of the timed workload (the sweep below runs other T)
+
+        # per-step event pairs (second loop: an event between steps costs ~2-3 us and breaks the
+        # programmatic overlap of consecutive forwards, so it stays out of the headline region)
+        n_med = min(args.steps, 100)
+        evs = [torch.cuda.Event(enable_timing=True) for _ in range(n_med + 1)]
+        if world > 1:
+            dist.barrier()
+            dist.all_reduce(sync_t)
+        evs[0].record()
+        for i in range(n_med):
+            step(batches[i % n_batches])
+            evs[i + 1].record()
+        torch.cuda.synchronize()
+        per_step = [evs[i].elapsed_time(evs[i + 1]) for i in range(n_med)]
+        ms_median = statistics.median(per_step)
+        if world > 1:
+            t = torch.tensor([ms_median], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms_median = float(t.item())
 
         # per-stage timing (separate loop; an event between stages)
         stage_acc = {}
@@ -254,6 +347,29 @@ def main():
             local = idx[(idx >= moe.expert_begin) & (idx < moe.expert_end)]
             hits.append(int(torch.unique(local).numel()))
         U = sum(hits) / len(hits)
+
+        # N > 1: one batch of the expert-parallel layer against a single-GPU forward, bit for bit
+        ep_bit_identical = None
+        if world > 1 and not args.no_ep_check:
+            y_ep = layer(batches[0]).clone()
+            ok = torch.ones(1, device=dev)
+            if rank == 0:
+                torch.set_default_dtype(dt)
+                torch.set_default_device(dev)
+                single = glm4_moe_b200.Glm4MoeMoE(_hf_config(shape), max_tokens=max(T, 256))
+                torch.set_default_device("cpu")
+                torch.set_default_dtype(torch.float32)
+                single.load_local_stacks(synth.make_weights_device(shape, dt, dev))
+                y_1 = single(batches[0])
+                ok[0] = 1.0 if torch.equal(y_1, y_ep) else 0.0
+                ok_close = bool(((y_1.float() - y_ep.float()).abs().max() <=
+                                 2e-2 * y_1.float().abs().max()).item())
+                del single
+            dist.broadcast(ok, 0)
+            ep_bit_identical = bool(ok.item() == 1.0)
+            if rank == 0 and not ep_bit_identical and args.ep_layout == "p2p":
+                print(f"WARNING: expert-parallel output differs from the single-GPU forward (close: {ok_close})",
+                      file=sys.stderr)
 
         # end-to-end through the public API with host buffers: pinned host tokens in, result on the host
         out_host = torch.empty((T, shape.H), dtype=dt).pin_memory()
@@ -303,11 +419,13 @@ def main():
                     moe(x)
                     us.append(int(torch.unique(moe.workspace_view("idx", Ts)).numel()))
                 Us = sum(us) / len(us)
-                by = shape.algorithmic_bytes(Ts, Us)
+                by = shape.algorithmic_bytes(Ts, Us, weight_bytes=1 if fp8 else 2, fp8_scales=fp8)
                 fl = shape.flops_per_token() * Ts
                 sweep.append({"T": Ts, "ms": ms, "tokens_per_s": Ts / ms * 1e3, "experts_hit": Us,
                               "GBps": by / ms / 1e6, "TFLOPs": fl / ms / 1e9,
-                              "tile_rows": moe.last_impl})
+                              "impl": moe.last_impl, "fused_decode_kernel": moe.last_fused,
+                              "tile_rows": _lib_tile_rows(moe, Ts)})
+    clk.stop()
 
     if world > 1 and args.ep_layout == "p2p":
         layer.close_p2p()
@@ -317,8 +435,9 @@ def main():
         return
 
     hbm_peak, peak_src, tc_peak = _peaks()
+    tc_src = peak_src
     if fp8:
-        tc_peak *= 2.0      # no measured FP8 figure in MEASURED_PEAKS.json: dense e4m3 = 2 x the bf16 rate
+        tc_peak, tc_src = _fp8_peak(tc_peak)
     H, I, k = shape.H, shape.I, shape.k
     # dominant kernel: gate_up grouped GEMM. Algorithmic bytes of one launch = gate_up weights of
     # the (U local + shared) experts it touches + the activation rows it reads + act rows it writes.
@@ -337,59 +456,74 @@ def main():
         gu_bytes = (U + n_sh) * 2 * I * H * wb + rows * H * wb + rows * I * wb
     achieved = gu_bytes / gu_ms / 1e6
     gu_flops = rows * 2 * H * 2 * I
-    # DRAM traffic of the same launch from the committed `ncu --set full` capture (profiles/ncu_traffic.json)
-    traffic = None
+    # DRAM traffic of this launch as ncu saw it on THIS bench's batch 0 (`bench.py --one-forward` under
+    # `ncu --set full`, summarised by scripts/ncu_traffic.py into profiles/ncu_traffic_r2.json together
+    # with the experts that launch hit); null when no capture of this exact workload is committed.
+    traffic, traffic_info = None, None
     try:
-        tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
-        base = kern.split('<')[0]
-        traffic = (tj.get(f"{base}:T={T}:{args.weights}") or tj.get(f"{base}<gate_up>:T={T}:{args.weights}")) \
-            if world == 1 else None
+        tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic_r2.json")))
+        ent = tj.get(f"{shape.name}:T={T}:{args.weights}:n={world}")
+        if ent and ent.get("kernel", "").split("<")[0] == kern.split("<")[0]:
+            traffic = ent["dram_bytes"]
+            traffic_info = {k_: ent[k_] for k_ in ("experts_hit", "algorithmic_bytes", "duration_us", "capture")
+                            if k_ in ent}
     except (OSError, ValueError):
         pass
     layer_bytes = shape.algorithmic_bytes(T, U, weight_bytes=wb, fp8_scales=fp8) if world == 1 else None
     roofline = {"bound": "hbm", "kernel": kern, "achieved": achieved,
                 "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": traffic,
+                "traffic_capture": traffic_info,
                 "peak_source": peak_src, "kernel_ms": gu_ms, "algorithmic_bytes_per_launch": gu_bytes,
-                "peak_note": "hbm_gbs of MEASURED_PEAKS.json is a read+write copy; read-only bulk-copy streaming on the "
-                             "same box type reaches 7.2 TB/s (profiles/r1d_ubench.jsonl), so frac can exceed 1",
+                "frac_of_read_stream": achieved / READ_STREAM_GBS, "read_stream_peak": READ_STREAM_GBS,
+                "peak_note": "`peak` (hbm_gbs of MEASURED_PEAKS.json) is a read+write copy; this kernel only reads, and "
+                             "read-only bulk-copy streaming on the same box type reaches 7.2 TB/s "
+                             "(profiles/r1d_ubench.jsonl): `frac_of_read_stream` is the fraction of that ceiling",
                 "stage_ms": stage_acc}
     if T * k / shape.E >= 96 and not fused:    # rows per local expert do not depend on the world size
         # prefill: the grouped GEMMs are a dense contraction bound by the tensor pipe
         roofline.update({"bound": "tensor", "achieved": gu_flops / gu_ms / 1e9, "peak": tc_peak, "unit": "TFLOP/s",
                          "frac": gu_flops / gu_ms / 1e9 / tc_peak, "algorithmic_flops_per_launch": gu_flops,
-                         "peak_source": peak_src + (" x 2 for e4m3 (no measured FP8 peak)" if fp8 else ""),
+                         "peak_source": tc_src,
                          "hbm": {"achieved": achieved, "peak": hbm_peak, "frac": achieved / hbm_peak}})
         fl = shape.flops_per_token() * T / world
         roofline["layer_tensor"] = {"algorithmic_flops": fl, "achieved": fl / ms_step / 1e9,
                                     "frac": fl / ms_step / 1e9 / tc_peak}
     if layer_bytes:
         roofline["layer"] = {"algorithmic_bytes": layer_bytes, "achieved": layer_bytes / ms_step / 1e6,
-                             "frac": layer_bytes / ms_step / 1e6 / hbm_peak}
+                             "frac": layer_bytes / ms_step / 1e6 / hbm_peak,
+                             "frac_of_read_stream": layer_bytes / ms_step / 1e6 / READ_STREAM_GBS}
     cpu_baseline = None
     if world == 1 and not args.no_cpu_baseline:
         n = args.cpu_steps or (40 if T <= 64 else 8 if T <= 512 else 2)
         host_w = {k_: v.cpu() for k_, v in weights.items()}
-        tps, ms, cores = _cpu_reference_run(shape, dt, host_w, T, n, 2)
-        cpu_baseline = {"value": tps, "unit": UNIT, "cores": cores, "kind": "port", "ms_per_step": ms,
-                        "sample": f"{n} steps of the same workload (T={T}) after 2 warm-up, oracle port of the "
-                                  "reference torch path (moe.py:128-176), torch threads = all host cores"}
+        tps, ms, cores, done, kind, what = _cpu_reference_run(shape, dt, host_w, T, n, 2, budget_s=60.0)
+        cpu_baseline = {"value": tps, "unit": UNIT, "cores": cores, "kind": kind, "ms_per_step": ms,
+                        "sample": f"{done} steps of the same workload (T={T}) after 2 warm-up: {what}; "
+                                  f"torch threads = all {cores} host cores"}
     line = {"metric": METRIC, "value": T * 1e3 / ms_step, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "ms_per_step_median": ms_median,
+            "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "bf16" if not fp8 else "fp8_e4m3 (fp32 block scales, fp32 accumulate)",
-            "data": "synthetic",
-            "config": {"workload": workload, "tokens_per_step": T, "experts_hit_mean": U,
-                       "parallelism": (f"ep{world}-{args.ep_layout}" + (f"-sliced{args.ep_sliced}" if args.ep_sliced >= 0 else ""))
-                       if world > 1 else "single",
-                       "l2": f"{n_batches} distinct token batches rotated; weights touched per step "
-                             f"({(U + 1) * 3 * H * I * 2 / 1e9:.2f} GB) exceed the 126 MB L2",
-                       "expert_gemm_impl": impl_name},
-            "e2e": e2e, "gpu_launches": launches, "clocks": clk.summary(), "roofline": roofline,
+            "data": "synthetic", "config": config,
+            "details": {"experts_hit_mean": U, "expert_gemm_impl": impl_name, "fused_decode_kernel": bool(fused),
+                        "parallelism": (f"ep{world}-{args.ep_layout}" + (f"-sliced{args.ep_sliced}" if args.ep_sliced >= 0 else ""))
+                        if world > 1 else "single",
+                        "weights_touched_per_step_gb": (U + 1) * 3 * H * I * wb / 1e9,
+                        "ep_bit_identical": ep_bit_identical},
+            "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roofline,
             "cpu_baseline": cpu_baseline}
+    if ep_bit_identical is not None:
+        line["ep_bit_identical"] = ep_bit_identical
     if sweep:
         line["sweep"] = sweep
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+def _lib_tile_rows(moe, T):
+    from glm4_moe_b200 import _lib
+    return int(_lib.load().glm4moe_layer_tile_rows(moe._handle, T)) if moe._handle else None
 
 
 if __name__ == "__main__":

@@ -1,14 +1,15 @@
 """Generate golden fixtures by running the REAL reference module (builder container only).
 
-Needs `/root/reference`; never runs on the GPU box.  Usage:  python oracle/gen_golden.py
+Needs the reference (`/root/reference`, or its installed copy `oracle/_ref/`, see
+`oracle/make_ref.py` and `oracle/reference_live.py`).  Usage:  python oracle/gen_golden.py
 Writes `tests/golden/<case>.pt` holding: the case description (shape, dtype, T, seeds), sha256
 checksums of the regenerated inputs, and the reference's outputs (`gate()` indices + weights,
 `experts_output`, `shared_output`, final output) — the same three tensors the reference's own
 debug dump names (moe.py:160-172).
 
 The reference's `forward` reads a debug safetensors file on every call (moe.py:153-157) that
-exists only on its author's machine; `safetensors.torch.load_file` is monkey-patched to hand
-back placeholders.  Nothing else of the reference is altered.
+exists only on its author's machine; `safetensors.torch.load_file` is wrapped to hand back
+placeholders for those paths.  Nothing else of the reference is altered.
 """
 from __future__ import annotations
 
@@ -28,36 +29,9 @@ def _load_pkg():
     return synth
 
 
-def build_reference_module(shape, dtype):
-    """Instantiate the reference Glm4MoeMoE (moe.py:52-69) under the given default dtype."""
-    sys.path.insert(0, REF)
-    import safetensors.torch as st
-    st.load_file = lambda *a, **k: {"experts_output": torch.zeros(1), "shared_output": torch.zeros(1),
-                                    "final_hidden_states": torch.zeros(1)}
-    from transformers.models.glm4_moe import Glm4MoeConfig
-    from nanovllm.models.glm4_moe.moe import Glm4MoeMoE
-    cfg = Glm4MoeConfig(hidden_size=shape.H, n_routed_experts=shape.E, num_experts_per_tok=shape.k,
-                        moe_intermediate_size=shape.I, n_shared_experts=1, n_group=1, topk_group=1,
-                        routed_scaling_factor=shape.routed_scaling_factor, norm_topk_prob=True)
-    prev = torch.get_default_dtype()
-    torch.set_default_dtype(dtype)
-    try:
-        moe = Glm4MoeMoE(cfg)
-    finally:
-        torch.set_default_dtype(prev)
-    return moe
-
-
-def fill_reference_module(moe, weights):
-    E = len(moe.experts)
-    with torch.no_grad():
-        for e in range(E):
-            moe.experts[e].gate_up_proj.weight.data.copy_(weights["w_gate_up"][e])
-            moe.experts[e].down_proj.weight.data.copy_(weights["w_down"][e])
-        moe.shared_experts.gate_up_proj.weight.data.copy_(weights["w_gate_up"][E])
-        moe.shared_experts.down_proj.weight.data.copy_(weights["w_down"][E])
-        moe.gate.weight.data.copy_(weights["gate_weight"])
-        moe.gate.e_score_correction_bias.copy_(weights["bias"])
+sys.path.insert(0, ROOT)
+from oracle.reference_live import (build_reference_gate, build_reference_module,   # noqa: E402,F401
+                                   fill_reference_module, import_reference)
 
 
 CASES = [
@@ -103,18 +77,7 @@ def main():
         shape = synth.SHAPES[sname]
         gate_w, bias = synth.make_router_weights(shape, dtype)
         x = synth.make_tokens(shape, T, dtype, bi)
-        sys.path.insert(0, REF)
-        from transformers.models.glm4_moe import Glm4MoeConfig
-        from nanovllm.models.glm4_moe.moe import GlmMoeSelectTopk
-        cfg = Glm4MoeConfig(hidden_size=shape.H, n_routed_experts=shape.E, num_experts_per_tok=shape.k,
-                            moe_intermediate_size=shape.I, n_group=1, topk_group=1,
-                            routed_scaling_factor=shape.routed_scaling_factor)
-        prev = torch.get_default_dtype()
-        torch.set_default_dtype(dtype)
-        try:
-            gate = GlmMoeSelectTopk(cfg)
-        finally:
-            torch.set_default_dtype(prev)
+        gate = build_reference_gate(shape, dtype)
         with torch.no_grad():
             gate.weight.data.copy_(gate_w)
             gate.e_score_correction_bias.copy_(bias)
@@ -128,7 +91,7 @@ def main():
         torch.save(blob, os.path.join(out_dir, name + ".pt"))
         print(name, tuple(idx.shape))
     # RMSNorm in front of the block (layers/layernorm.py), with and without the residual
-    sys.path.insert(0, REF)
+    import_reference()
     from nanovllm.layers.layernorm import RMSNorm
     for name, H, T, dtype in (("rmsnorm_bf16_H4096_T5", 4096, 5, torch.bfloat16), ("rmsnorm_fp32_H1024_T3", 1024, 3, torch.float32),
                               ("rmsnorm_fp16_H512_T9", 512, 9, torch.float16)):

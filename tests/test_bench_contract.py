@@ -26,10 +26,17 @@ def test_reference_arm_prints_one_contract_line():
     assert KEYS <= set(d), KEYS - set(d)
     assert d["impl"] == "reference" and d["unit"] == "tokens/s" and d["higher_is_better"] is True
     assert d["value"] > 0 and d["ms_per_step"] > 0 and d["vs_baseline"] is None
-    assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1
+    from oracle import reference_live as R
+    # the real reference module when oracle/_ref is installed (oracle/make_ref.py), else the oracle port
+    assert d["cpu_baseline"]["kind"] == ("reference" if R.available() else "port") and d["cpu_baseline"]["cores"] >= 1
+    assert d["steps"] == 2 and d["warmup"] == 1          # no step cap: the driver compares steps across arms
     assert d["cpu_baseline"]["value"] == d["value"] == d["e2e"]["value"]
     assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0
     assert "workload" in d["config"] and "model" not in d["config"]
+    # both arms print the same `config` object (the driver compares them)
+    import bench
+    from glm4_moe_b200 import synth
+    assert d["config"] == bench._config(synth.SHAPES["mini"], 8, False, bench.N_BATCHES)
 
 
 def test_reference_arm_under_torchrun_rank0_only():

@@ -1,4 +1,4 @@
-"""CPU, builder container only (needs /root/reference): the drop-in boundary of SURVEY 8b exercised
+"""CPU (needs the reference: /root/reference or its installed copy oracle/_ref/): the drop-in boundary of SURVEY 8b exercised
 against the REAL reference classes.  The reference decoder layer (decode_layer.py:10-38) is built once
 with its own `Glm4MoeMoE` and once with ours bound to the same name (`from .moe import Glm4MoeMoE`,
 decode_layer.py:6), and the two sparse blocks must be indistinguishable to their caller: same
@@ -14,9 +14,9 @@ import torch
 import glm4_moe_b200
 from glm4_moe_b200 import synth
 
-REF = "/root/reference"
-pytestmark = pytest.mark.skipif(not os.path.isdir(os.path.join(REF, "nanovllm")),
-                                reason="reference tree not on this machine")
+from oracle import reference_live as R
+
+pytestmark = pytest.mark.skipif(not R.available(), reason="reference package neither mounted nor installed")
 
 
 def _config(shape):
@@ -32,8 +32,7 @@ def _config(shape):
 
 
 def _layers(shape, dtype):
-    if REF not in sys.path:
-        sys.path.insert(0, REF)
+    R.import_reference()
     from nanovllm.models.glm4_moe import decode_layer as DL
     from nanovllm.models.glm4_moe.moe import Glm4MoeMoE as RefMoE
     cfg = _config(shape)
