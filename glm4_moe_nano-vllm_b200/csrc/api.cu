@@ -48,6 +48,9 @@ bool direct_enabled() {
 }
 
 int g_router_rows = 0;   // 0: pick by T; 16/32/64/128: token rows per router tile (glm4moe_debug_set(3, v))
+int g_bk32 = -1;         // see bk32_enabled()
+int g_down2 = -1;        // see down2_enabled()
+int g_force_bn = -2;     // see forced_bn_index()
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
@@ -156,6 +159,13 @@ extern "C" int glm4moe_debug_set(int knob, int value) {
       if (value != 0 && value != 16 && value != 32 && value != 64 && value != 128) return GLM4MOE_ERR_ARG;
       g_router_rows = value;
       return GLM4MOE_OK;
+    case GLM4MOE_KNOB_BK32: g_bk32 = value ? 1 : 0; return GLM4MOE_OK;
+    case GLM4MOE_KNOB_DOWN2: g_down2 = value ? 1 : 0; return GLM4MOE_OK;
+    case GLM4MOE_KNOB_FORCE_TILE_ROWS:
+      g_force_bn = -1;
+      if (value == 0) return GLM4MOE_OK;
+      for (int i = 0; i < kNumBn; ++i) if (value == kBnChoices[i]) g_force_bn = i;
+      return g_force_bn >= 0 ? GLM4MOE_OK : GLM4MOE_ERR_ARG;
     default: return GLM4MOE_ERR_ARG;
   }
 }
@@ -298,36 +308,40 @@ extern "C" int glm4moe_layer_destroy(glm4moe_layer_t* layer) {
   return GLM4MOE_OK;
 }
 
+// ---- tuning / test knobs of the tensor-core path (glm4moe_debug_set; the environment variable only
+// gives the initial value) ----
+// GLM4MOE_BK32: K blocks of 32 with a 7-deep ring for the 256-token prefill tiles.  Off by default:
+// measured SLOWER than the 3 x 64 KB ring (Air T=4096 gate_up 852 -> 881 us, T=8192 1490 -> 1625 us;
+// profiles/r1d.md) although it keeps 1.5x the bytes in flight.
+static bool bk32_enabled() {
+  if (g_bk32 < 0) {
+    const char* e = getenv("GLM4MOE_BK32");
+    g_bk32 = (e && atoi(e) != 0) ? 1 : 0;
+  }
+  return g_bk32 == 1;
+}
+// GLM4MOE_NO_DOWN2=1: plain 128-feature down tiles at prefill instead of 256 features x 256 tokens
+static bool down2_enabled() {
+  if (g_down2 < 0) {
+    const char* e = getenv("GLM4MOE_NO_DOWN2");
+    g_down2 = (e && atoi(e) != 0) ? 0 : 1;
+  }
+  return g_down2 == 1;
+}
+// GLM4MOE_FORCE_BN=16/32/64/128/256: token rows per tile regardless of the batch (-1 = by mean rows per expert)
+static int forced_bn_index() {
+  if (g_force_bn == -2) {
+    const char* e = getenv("GLM4MOE_FORCE_BN");
+    g_force_bn = -1;
+    if (e) for (int i = 0; i < kNumBn; ++i) if (atoi(e) == kBnChoices[i]) g_force_bn = i;
+  }
+  return g_force_bn;
+}
+
 // rows of one token tile on the tensor-core path: sized to the mean rows per local expert so a
 // typical expert is one tile (weights cross HBM once; a second tile re-reads them from L2).
-static bool bk32_enabled() {
-  // Off by default: measured SLOWER than the 3 x 64 KB ring (Air T=4096 gate_up 852 -> 881 us, T=8192
-  // 1490 -> 1625 us; profiles/r1d.md) although it keeps 1.5x the bytes in flight: 64-byte boxes cost
-  // more per byte than they gain in look-ahead.  GLM4MOE_BK32=1 turns it on for experiments.
-  static int v = -1;
-  if (v < 0) {
-    const char* e = getenv("GLM4MOE_BK32");
-    v = (e && atoi(e) != 0) ? 1 : 0;
-  }
-  return v == 1;
-}
-
-static bool down2_enabled() {
-  static int v = -1;
-  if (v < 0) {
-    const char* e = getenv("GLM4MOE_NO_DOWN2");   // tuning aid: 1 = plain 128-feature down tiles at prefill
-    v = (e && atoi(e) != 0) ? 0 : 1;
-  }
-  return v == 1;
-}
-
 static int pick_bn_index(const glm4moe_config_t& c, int T) {
-  static int forced = -2;
-  if (forced == -2) {
-    const char* e = getenv("GLM4MOE_FORCE_BN");   // tuning aid: 16/32/64/128/256
-    forced = -1;
-    if (e) for (int i = 0; i < kNumBn; ++i) if (atoi(e) == kBnChoices[i]) forced = i;
-  }
+  const int forced = forced_bn_index();
   if (forced >= 0) return forced;
   const int e_local = c.expert_end - c.expert_begin;
   const double mean = e_local > 0 ? static_cast<double>(T) * c.num_experts_per_tok / c.n_routed_experts : T;

@@ -61,9 +61,14 @@ int glm4moe_abi_version(void);
  * GLM4MOE_KNOB_FUSED: 1 (default) = inside direct mode, gate_up and down run as one persistent kernel
  * (decode_fused.cu); 0 = two grouped-GEMM launches.
  * GLM4MOE_KNOB_FP8_PREFILL: 1 (default) = the e4m3 tier uses token-major 128 x 256 tiles once an expert
- * averages >= 48 rows (umma_fp8_prefill.cu); 0 = always the 16..64-token swap-AB tiles (umma_fp8.cu). */
+ * averages >= 48 rows (umma_fp8_prefill.cu); 0 = always the 16..64-token swap-AB tiles (umma_fp8.cu).
+ * GLM4MOE_KNOB_BK32: 1 = K blocks of 32 elements (64-byte swizzle, 7-deep ring) for the 256-token bf16 prefill tiles
+ * (default 0: measured slower).  GLM4MOE_KNOB_DOWN2: 1 (default) = the prefill down projection runs 256 features x
+ * 256 tokens per CTA tile.  GLM4MOE_KNOB_FORCE_TILE_ROWS: 0 (default) = token rows per tile follow the mean rows per
+ * expert; 16/32/64/128/256 force one tile size (parity tests walk every tile geometry with it). */
 enum { GLM4MOE_KNOB_DIRECT = 0, GLM4MOE_KNOB_FUSED = 1, GLM4MOE_KNOB_FP8_PREFILL = 2,
-       GLM4MOE_KNOB_ROUTER_ROWS = 3 /* token rows per tensor-core router tile: 0 = by T, 16/32/64/128 */ };
+       GLM4MOE_KNOB_ROUTER_ROWS = 3 /* token rows per tensor-core router tile: 0 = by T, 16/32/64/128 */,
+       GLM4MOE_KNOB_BK32 = 4, GLM4MOE_KNOB_DOWN2 = 5, GLM4MOE_KNOB_FORCE_TILE_ROWS = 6 };
 int glm4moe_debug_set(int knob, int value);
 const char* glm4moe_error_string(int code);
 
