@@ -1,0 +1,238 @@
+"""Host-side shim that lets the UNMODIFIED reference engine run a full GLM4-MoE decoder stack with this
+package's sparse block swapped in (BASELINE configs[3]).
+
+The reference's GLM path is work in progress and cannot run a model as shipped.  Nothing
+under `nanovllm/` is edited: `install()` imports the installed copy (`baseline/_ref/`, put there by
+`oracle/make_ref.py`) and rebinds, at construction time only,
+
+  decode_layer.py:6,29     `Glm4MoeMoE`        -> `glm4_moe_b200.Glm4MoeMoE` (the one-line swap of INTEGRATION.md)
+  model.py:20-22           2 hard-coded layers  -> `config.num_hidden_layers` (the reference's own
+                                                   commented-out line, model.py:19)
+  model.py:75-76           final norm without the residual -> `self.norm(hidden_states, residual)`
+                                                   (its commented-out line, model.py:75; cf. qwen3.py:176)
+  moe.py:153-157, attention_new.py:288-292   per-forward debug `load_file` of a path that exists only on
+                                                   the author's machine -> placeholder (oracle.reference_live
+                                                   does the same for the checker)
+  config.py:24 / attention_new.py:90-95       `hf_config.rope_theta`, `.rope_scaling`, `.head_dim`,
+                                                   `.torch_dtype`: renamed / dropped by transformers 5.x
+                                                   -> an attribute view that restores them
+  model.py:107-132         `load_weights` from a checkpoint -> deterministic random init when the model
+                                                   directory carries `dummy_weights.json` (no checkpoint and
+                                                   no network in this environment)
+
+Attention (`nanovllm/layers/attention.py`, flash-attn), the KV cache, the scheduler, the sampler and the
+CUDA-graph runner (`engine/model_runner.py:216-258`) run as shipped.  `make_model_dir()` writes the synthetic
+model directory (`config.json`, a word-level tokenizer, `dummy_weights.json`) that `Config` / `LLMEngine`
+insist on (`config.py:21-24`, `llm_engine.py:31`).
+"""
+from __future__ import annotations
+
+import json
+import os
+import sys
+import types
+
+import torch
+from torch import nn
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF_CANDIDATES = (os.path.join(ROOT, "baseline", "_ref"), "/root/reference")
+DUMMY_MARKER = "dummy_weights.json"
+
+
+def reference_root() -> str | None:
+    for c in REF_CANDIDATES:
+        if os.path.exists(os.path.join(c, "nanovllm", "engine", "model_runner.py")):
+            return c
+    return None
+
+
+class HfConfigView:
+    """Attribute view over a transformers config restoring the names the reference reads
+    (`config.py:24`, `model_runner.py:29,108-112`, `attention_new.py:29,84-95`)."""
+
+    def __init__(self, hf, dtype=None):
+        object.__setattr__(self, "_hf", hf)
+        rp = getattr(hf, "rope_parameters", None) or {}
+        over = {}
+        if "rope_theta" not in hf.__dict__:
+            over["rope_theta"] = float(rp.get("rope_theta", 10000.0))
+        # the reference asserts `rope_scaling is None` (rotary_embedding.py:66); transformers 5.x aliases the
+        # attribute to the `rope_parameters` dict even for the default rope type
+        over["rope_scaling"] = None if rp.get("rope_type", "default") == "default" else rp
+        if "head_dim" not in hf.__dict__:
+            over["head_dim"] = hf.hidden_size // hf.num_attention_heads
+        td = dtype or hf.__dict__.get("dtype") or hf.__dict__.get("torch_dtype") or torch.bfloat16
+        if isinstance(td, str):
+            td = getattr(torch, td.replace("torch.", ""))
+        over["torch_dtype"] = td
+        object.__setattr__(self, "_over", over)
+
+    def __getattr__(self, name):
+        over = object.__getattribute__(self, "_over")
+        if name in over:
+            return over[name]
+        return getattr(object.__getattribute__(self, "_hf"), name)
+
+    def __setattr__(self, name, value):
+        object.__getattribute__(self, "_over")[name] = value
+
+
+_installed = {}
+
+
+def install(sparse_block: str = "ours", weight_format: str = "native", share_workspace: bool = True):
+    """Import the reference package and apply the construction-time rebinding described above.
+    `sparse_block`: "ours" (this package's `Glm4MoeMoE`) or "reference" (the reference's own block, for
+    A/B runs of the same stack).  Returns the `nanovllm` package."""
+    root = reference_root()
+    if root is None:
+        raise RuntimeError("the reference engine is not installed: run `python oracle/make_ref.py` where "
+                           "/root/reference is mounted (baseline/_ref/ then travels with the repo)")
+    if root not in sys.path:
+        sys.path.insert(0, root)
+    # debug file reads (moe.py:153-157, attention_new.py:288-292)
+    import safetensors.torch as st
+    if not getattr(st.load_file, "_glm4moe_patched", False):
+        real = st.load_file
+
+        def load_file(filename, *a, **k):
+            if str(filename).startswith("/data/ai_infra/debug"):
+                z = torch.zeros(1)
+                return {"experts_output": z, "shared_output": z, "final_hidden_states": z}
+            return real(filename, *a, **k)
+
+        load_file._glm4moe_patched = True
+        st.load_file = load_file
+
+    import nanovllm
+    from nanovllm import config as ref_config
+    from nanovllm.models.glm4_moe import decode_layer as DL
+    from nanovllm.models.glm4_moe import model as M
+    from nanovllm.models.glm4_moe import moe as ref_moe
+    from nanovllm.layers.embed_head import VocabParallelEmbedding
+    from nanovllm.layers.layernorm import RMSNorm
+
+    if "ref_block" not in _installed:
+        _installed["ref_block"] = ref_moe.Glm4MoeMoE
+        _installed["post_init"] = ref_config.Config.__post_init__
+
+    from . import moe as ours
+    if sparse_block == "ours":
+        ours.Glm4MoeMoE.default_weight_format = weight_format
+        ours.Glm4MoeMoE.share_workspace = bool(share_workspace)
+        DL.Glm4MoeMoE = ours.Glm4MoeMoE                      # decode_layer.py:6 — the swap
+    elif sparse_block == "reference":
+        DL.Glm4MoeMoE = _installed["ref_block"]
+    else:
+        raise ValueError(sparse_block)
+
+    def model_init(self, config):                            # model.py:14-24 with the line of model.py:19
+        nn.Module.__init__(self)
+        self.embed_tokens = VocabParallelEmbedding(config.vocab_size, config.hidden_size)
+        self.layers = nn.ModuleList([DL.Glm4MoeDecoderLayer(config, prefix=f"model.layers.{i}")
+                                     for i in range(config.num_hidden_layers)])
+        self.norm = RMSNorm(config.hidden_size, eps=config.rms_norm_eps)
+
+    def model_forward(self, input_ids, positions):           # model.py:63-78 with the line of model.py:75
+        hidden_states = self.embed_tokens(input_ids)
+        residual = None
+        for layer in self.layers:
+            hidden_states, residual = layer(positions, hidden_states, residual)
+        hidden_states, _ = self.norm(hidden_states, residual)
+        return hidden_states
+
+    M.Glm4MoeModel.__init__ = model_init
+    M.Glm4MoeModel.forward = model_forward
+
+    real_load = _installed.setdefault("load_weights", M.Glm4MoeForCausalLM.load_weights)
+
+    def load_weights(self, model_path):                      # model.py:107-132
+        marker = os.path.join(model_path, DUMMY_MARKER)
+        if os.path.exists(marker):
+            init_dummy_weights(self, **json.load(open(marker)))
+        else:
+            real_load(self, model_path)
+
+    M.Glm4MoeForCausalLM.load_weights = load_weights
+
+    post_init = _installed["post_init"]
+
+    def config_post_init(self):                              # config.py:20-26
+        post_init(self)
+        if not isinstance(self.hf_config, HfConfigView):
+            self.hf_config = HfConfigView(self.hf_config)
+
+    ref_config.Config.__post_init__ = config_post_init
+    return nanovllm
+
+
+def init_dummy_weights(model, seed: int = 1234, std: float = 0.02, **_):
+    """Deterministic random init of a `Glm4MoeForCausalLM`: N(0, std^2) for every matrix, ones for the norm
+    weights, U(0, 0.1) for the fp32 router bias; this package's blocks fill themselves
+    (`Glm4MoeMoE.init_random_`, which also quantises into the e4m3 stacks of an FP8 block)."""
+    from . import moe as ours
+    own = set()
+    with torch.no_grad():
+        for li, layer in enumerate(model.model.layers):
+            if isinstance(layer.mlp, ours.Glm4MoeMoE):
+                layer.mlp.init_random_(seed * 1000 + li, std)
+                own.update(id(t) for t in layer.mlp.parameters())
+                own.update(id(t) for t in layer.mlp.buffers())
+        gens = {}
+
+        def gen(dev):
+            if dev not in gens:
+                gens[dev] = torch.Generator(device=dev).manual_seed(seed)
+            return gens[dev]
+
+        for name, p in model.named_parameters():
+            if id(p) in own or p.numel() == 0:
+                continue
+            if p.dim() == 1:
+                p.fill_(1.0 if "norm" in name else 0.0)
+            else:
+                p.copy_((torch.randn(p.shape, generator=gen(p.device), device=p.device, dtype=torch.float32) * std).to(p.dtype))
+        for name, b in model.named_buffers():
+            if id(b) not in own and name.endswith("e_score_correction_bias"):
+                b.copy_(torch.rand(b.shape, generator=gen(b.device), device=b.device, dtype=torch.float32) * 0.1)
+
+
+def make_model_dir(path: str, *, hidden_size: int, n_routed_experts: int, num_experts_per_tok: int,
+                   moe_intermediate_size: int, intermediate_size: int, num_hidden_layers: int,
+                   num_attention_heads: int, num_key_value_heads: int, head_dim: int, vocab_size: int,
+                   routed_scaling_factor: float = 1.0, first_k_dense_replace: int = 1,
+                   max_position_embeddings: int = 4096, dtype: str = "bfloat16", seed: int = 1234) -> str:
+    """Synthetic GLM4-MoE model directory: what `Config` (config.py:21-24: a directory with a
+    `config.json` AutoConfig can read) and `LLMEngine` (llm_engine.py:31: a fast tokenizer) need."""
+    os.makedirs(path, exist_ok=True)
+    cfg = {
+        "architectures": ["Glm4MoeForCausalLM"], "model_type": "glm4_moe", "hidden_size": hidden_size,
+        "n_routed_experts": n_routed_experts, "num_experts_per_tok": num_experts_per_tok,
+        "moe_intermediate_size": moe_intermediate_size, "intermediate_size": intermediate_size,
+        "n_shared_experts": 1, "n_group": 1, "topk_group": 1, "norm_topk_prob": True,
+        "routed_scaling_factor": routed_scaling_factor, "first_k_dense_replace": first_k_dense_replace,
+        "num_hidden_layers": num_hidden_layers, "num_attention_heads": num_attention_heads,
+        "num_key_value_heads": num_key_value_heads, "head_dim": head_dim, "vocab_size": vocab_size,
+        "max_position_embeddings": max_position_embeddings, "rms_norm_eps": 1e-5, "hidden_act": "silu",
+        "attention_bias": False, "use_qk_norm": False, "partial_rotary_factor": 0.5, "rope_theta": 10000.0,
+        "tie_word_embeddings": False, "dtype": dtype, "torch_dtype": dtype, "eos_token_id": 1, "pad_token_id": 0,
+    }
+    json.dump(cfg, open(os.path.join(path, "config.json"), "w"), indent=1)
+    json.dump({"seed": seed, "std": 0.02}, open(os.path.join(path, DUMMY_MARKER), "w"))
+    from tokenizers import Tokenizer, models, pre_tokenizers
+    vocab = {"<pad>": 0, "</s>": 1, "<unk>": 2}
+    for i in range(3, vocab_size):
+        vocab[f"t{i}"] = i
+    tok = Tokenizer(models.WordLevel(vocab=vocab, unk_token="<unk>"))
+    tok.pre_tokenizer = pre_tokenizers.WhitespaceSplit()
+    tok.save(os.path.join(path, "tokenizer.json"))
+    json.dump({"tokenizer_class": "PreTrainedTokenizerFast", "eos_token": "</s>", "pad_token": "<pad>",
+               "unk_token": "<unk>", "model_max_length": max_position_embeddings},
+              open(os.path.join(path, "tokenizer_config.json"), "w"))
+    return path
+
+
+AIR_MODEL = dict(hidden_size=4096, n_routed_experts=128, num_experts_per_tok=8, moe_intermediate_size=1408,
+                 intermediate_size=10944, num_attention_heads=96, num_key_value_heads=8, head_dim=128,
+                 vocab_size=151552, routed_scaling_factor=1.0, first_k_dense_replace=1)

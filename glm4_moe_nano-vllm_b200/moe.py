@@ -155,7 +155,20 @@ class Glm4MoeMoE(nn.Module):
                    local experts (+ the shared expert on this rank's 1/size slice of the tokens,
                    `with_shared = 2`); see distributed.py
       impl         "auto" | "simt" | "umma": expert-GEMM implementation
+
+    Class-level construction defaults, for hosts that call `Glm4MoeMoE(config)` with no room for keyword
+    arguments (the reference decoder layer, decode_layer.py:29):
+      default_weight_format  "native" | "fp8": "fp8" allocates the e4m3 stacks + block scales directly
+                   and no model-dtype stacks (a 46-layer GLM-4.5-Air holds 45 of these blocks: 199 GB in
+                   bf16, 101 GB in e4m3)
+      share_workspace  True: blocks of one device with the same shape share ONE workspace allocation
+                   (layers of a model run one after the other on one stream; every in-kernel counter
+                   re-arms itself).  A private workspace per layer costs 2.8 GB at 16 k prefill tokens.
     """
+
+    default_weight_format = "native"
+    share_workspace = False
+    _workspace_pool: dict = {}
 
     def __init__(self, config, *, max_tokens: int = 256, ep_rank: int = 0, ep_size: int = 1,
                  impl: str = "auto", peer_workspace: bool = False):
@@ -178,14 +191,30 @@ class Glm4MoeMoE(nn.Module):
         n_local = self.expert_end - self.expert_begin
         # stacked storage, created under the process-wide default dtype/device like the
         # reference's parameters (model_runner.py:29-31)
-        self._w_gate_up = torch.empty((n_local + 1, 2 * I, H))
-        self._w_down = torch.empty((n_local + 1, H, I))
-        self.experts = nn.ModuleList(
-            [Glm4MoeMLP(self._w_gate_up[i], self._w_down[i], config.hidden_act) for i in range(n_local)])
+        fp8_only = type(self).default_weight_format == "fp8"
+        if fp8_only:
+            if I % 128 or H % 128:
+                raise ValueError(f"block-128 FP8 needs dimensions divisible by 128, got I={I}, H={H}")
+            self._w_gate_up = torch.empty((0,))
+            self._w_down = torch.empty((0,))
+            gu = [self._w_gate_up] * (n_local + 1)
+            dn = [self._w_down] * (n_local + 1)
+        else:
+            self._w_gate_up = torch.empty((n_local + 1, 2 * I, H))
+            self._w_down = torch.empty((n_local + 1, H, I))
+            gu, dn = self._w_gate_up, self._w_down
+        self.experts = nn.ModuleList([Glm4MoeMLP(gu[i], dn[i], config.hidden_act) for i in range(n_local)])
         self.gate = GlmMoeSelectTopk(config)
-        self.shared_experts = Glm4MoeMLP(self._w_gate_up[n_local], self._w_down[n_local], config.hidden_act)
+        self.shared_experts = Glm4MoeMLP(gu[n_local], dn[n_local], config.hidden_act)
         self.weight_format = "native"
         self._wq_gate_up = self._wq_down = self._s_gate_up = self._s_down = None
+        if fp8_only:
+            f8 = torch.float8_e4m3fn
+            self._wq_gate_up = torch.empty((n_local + 1, 2 * I, H), dtype=f8)
+            self._wq_down = torch.empty((n_local + 1, H, I), dtype=f8)
+            self._s_gate_up = torch.empty((n_local + 1, 2 * I // 128, H // 128), dtype=torch.float32)
+            self._s_down = torch.empty((n_local + 1, H // 128, I // 128), dtype=torch.float32)
+            self.weight_format = "fp8"
         self._max_tokens = int(max_tokens)
         self._handle = None
         self._workspace = None
@@ -227,6 +256,8 @@ class Glm4MoeMoE(nn.Module):
         if getattr(self, "_handle", None) is not None:
             _lib.load().glm4moe_layer_destroy(self._handle)
         self._handle = None
+        for _, users in type(self)._workspace_pool.values():
+            users.discard(self)
         self._workspace = None
         self._host = None
         if getattr(self, "_ipc_ptr", None):
@@ -276,6 +307,18 @@ class Glm4MoeMoE(nn.Module):
                 _lib.check(lib.glm4moe_p2p_alloc(nbytes + 1024, C.byref(ptr), hbuf), "p2p_alloc")
             self._ipc_ptr, self._ipc_handle = ptr.value, hbuf.raw
             self._workspace = torch.as_tensor(_ForeignCudaBuffer(ptr.value, nbytes + 1024), device=dev)
+        elif type(self).share_workspace:
+            # one allocation per (device, layout): the layout is a function of the config alone, so every
+            # block with this key sees the same counters at the same offsets
+            key = (str(dev), nbytes, tuple(getattr(cfg, f[0]) for f in cfg._fields_ if f[0] not in ("impl",)))
+            pool = type(self)._workspace_pool
+            for k_ in [k_ for k_, (_, users) in pool.items() if k_[0] == str(dev) and not len(users)]:
+                del pool[k_]                       # grown out of: nobody holds it any more
+            if key not in pool:
+                import weakref
+                pool[key] = (torch.empty(nbytes + 1024, dtype=torch.uint8, device=dev), weakref.WeakSet())
+            self._workspace = pool[key][0]
+            pool[key][1].add(self)
         else:
             self._workspace = torch.empty(nbytes + 1024, dtype=torch.uint8, device=dev)
         base = (self._workspace.data_ptr() + 1023) // 1024 * 1024
@@ -465,6 +508,40 @@ class Glm4MoeMoE(nn.Module):
             self.weight_format = "fp8"
 
     # ---- helpers used by tests / bench -------------------------------------------------------
+    def init_random_(self, seed: int, std: float = 0.02, bias_high: float = 0.1, chunk: int = 16):
+        """Random-init in place (no checkpoint, no network): weights ~ N(0, std^2), bias ~ U(0, bias_high)
+        as in synth.py, drawn on the block's own device.  FP8 blocks draw the model-dtype values `chunk`
+        experts at a time and quantise them (fp8.quantize_block128), so no full model-dtype stack exists."""
+        from . import fp8
+        dev, md = self.gate.weight.device, self.gate.weight.dtype
+        gen = torch.Generator(device=dev).manual_seed(seed)
+        c = self.config
+        H, I = c.hidden_size, c.moe_intermediate_size
+        n = self.expert_end - self.expert_begin + 1
+
+        def draw(shape):
+            return (torch.randn(shape, generator=gen, device=dev, dtype=torch.float32) * std).to(md)
+
+        with torch.no_grad():
+            self._destroy_handle()
+            for s0 in range(0, n, chunk):
+                m = min(chunk, n - s0)
+                gu, dn = draw((m, 2 * I, H)), draw((m, H, I))
+                if self.weight_format == "fp8":
+                    q, sc = fp8.quantize_block128(gu)
+                    self._wq_gate_up[s0:s0 + m].view(torch.uint8).copy_(q.view(torch.uint8))
+                    self._s_gate_up[s0:s0 + m].copy_(sc)
+                    q, sc = fp8.quantize_block128(dn)
+                    self._wq_down[s0:s0 + m].view(torch.uint8).copy_(q.view(torch.uint8))
+                    self._s_down[s0:s0 + m].copy_(sc)
+                else:
+                    self._w_gate_up[s0:s0 + m].copy_(gu)
+                    self._w_down[s0:s0 + m].copy_(dn)
+            self.gate.weight.data.copy_(draw((c.n_routed_experts, H)))
+            self.gate.e_score_correction_bias.copy_(
+                torch.rand(c.n_routed_experts, generator=gen, device=dev, dtype=torch.float32) * bias_high)
+        return self
+
     def load_stacked(self, weights: dict):
         """Fill from the stacked synthetic dict of `synth.make_weights` (full E+1 stacks)."""
         with torch.no_grad():

@@ -1,0 +1,142 @@
+"""GPU: the REAL reference decoder layer / engine hosting this package's sparse block (SURVEY 8f-1,
+BASELINE configs[3]).  The host stack is the unmodified reference from baseline/_ref (oracle/make_ref.py),
+rebound at construction time by glm4_moe_b200.engine_shim; attention is the reference's flash-attn path.
+
+1. `Glm4MoeDecoderLayer.forward` (decode_layer.py:79-100) with our block against the same layer with the
+   reference's own block on identical weights, eager, and our layer under CUDA-graph capture (the way
+   `ModelRunner.capture_cudagraph` replays decode, model_runner.py:216-258);
+2. `nanovllm.LLM` end to end on a 4-layer random-init model: greedy tokens of the CUDA-graph decode runner
+   equal the eager run's, through `scripts/engine_run.py` in a subprocess (the engine owns a NCCL group and
+   the process-wide default device)."""
+import json
+import os
+import subprocess
+import sys
+import types
+
+import pytest
+import torch
+
+import glm4_moe_b200
+from glm4_moe_b200 import engine_shim as S
+from conftest import ROOT
+
+pytestmark = [pytest.mark.gpu,
+              pytest.mark.skipif(S.reference_root() is None, reason="baseline/_ref missing: run python oracle/make_ref.py")]
+
+
+def _config(H=512, E=32, k=8, I=256):
+    return types.SimpleNamespace(
+        hidden_size=H, n_routed_experts=E, num_experts_per_tok=k, moe_intermediate_size=I,
+        intermediate_size=2 * H, n_shared_experts=1, n_group=1, topk_group=1, routed_scaling_factor=2.5,
+        norm_topk_prob=True, num_attention_heads=8, num_key_value_heads=2, head_dim=64, first_k_dense_replace=1,
+        num_hidden_layers=2, max_position_embeddings=512, rope_theta=10000.0, rope_scaling=None,
+        partial_rotary_factor=0.5, rms_norm_eps=1e-5, attention_bias=False, hidden_act="silu", use_qk_norm=False)
+
+
+def _layer(block, dt):
+    S.install(sparse_block=block, share_workspace=False)
+    from nanovllm.models.glm4_moe import decode_layer as DL
+    prev = torch.get_default_dtype()
+    torch.set_default_dtype(dt)
+    try:
+        with torch.device("cuda"):
+            return DL.Glm4MoeDecoderLayer(_config(), "model.layers.1")
+    finally:
+        torch.set_default_dtype(prev)
+        S.install(sparse_block="ours", share_workspace=False)
+
+
+@pytest.mark.parametrize("T", [24, 300])
+def test_real_decoder_layer_forward_with_the_swapped_block(T):
+    dt = torch.bfloat16
+    ref, ours = _layer("reference", dt), _layer("ours", dt)
+    assert isinstance(ours.mlp, glm4_moe_b200.Glm4MoeMoE) and type(ref.mlp).__module__.startswith("nanovllm.")
+    g = torch.Generator(device="cuda").manual_seed(5)
+    with torch.no_grad():
+        for name, p in ref.named_parameters():
+            if p.dim() == 1:
+                p.fill_(1.0)
+            else:
+                p.copy_((torch.randn(p.shape, generator=g, device="cuda", dtype=torch.float32) * 0.02).to(dt))
+        ref.mlp.gate.e_score_correction_bias.copy_(torch.rand(32, generator=g, device="cuda") * 0.1)
+        missing = ours.load_state_dict(ref.state_dict(), strict=True)      # same keys, shapes, dtypes
+    assert not missing.missing_keys and not missing.unexpected_keys
+    from nanovllm.utils.context import set_context, reset_context
+    x = torch.randn((T, 512), generator=g, device="cuda", dtype=torch.float32).to(dt)
+    res = torch.randn((T, 512), generator=g, device="cuda", dtype=torch.float32).to(dt)
+    pos = torch.arange(T, device="cuda")
+    cu = torch.tensor([0, T], dtype=torch.int32, device="cuda")
+
+    def run(layer, hidden, residual):
+        set_context(True, cu, cu, T, T, None, None, None)      # one prefill sequence of T tokens, no KV cache
+        try:
+            with torch.inference_mode():
+                return layer(pos, hidden.clone(), None if residual is None else residual.clone())
+        finally:
+            reset_context()
+
+    for residual in (None, res):
+        h_ref, r_ref = run(ref, x, residual)
+        h_our, r_our = run(ours, x, residual)
+        torch.cuda.synchronize()
+        assert h_our.shape == h_ref.shape == (T, 512) and h_our.dtype == dt
+        assert torch.equal(r_our, r_ref)                        # attention + norms are the reference's own code
+        # rows whose top-8 set differs (a bf16 boundary logit rounded differently) may be off: at most 3 %
+        d = (h_our.float() - h_ref.float()).abs()
+        rms = h_ref.float().pow(2).mean().sqrt()
+        row_ok = (d <= 2e-2 * h_ref.float().abs() + 2e-2 * rms).all(-1)
+        assert float(row_ok.float().mean()) >= 0.97, float(row_ok.float().mean())
+        assert float(d[row_ok].max()) <= 1e-2 + 1e-2 * float(h_ref.float().abs().max())
+    # CUDA-graph capture of the real layer forward with our block, decode-shaped (T tokens, static buffers)
+    if T <= 32:
+        set_context(True, cu, cu, T, T, None, None, None)
+        try:
+            with torch.inference_mode():
+                static_x, static_r = x.clone(), res.clone()
+                eager_h, eager_r = ours(pos, static_x.clone(), static_r.clone())
+                s = torch.cuda.Stream()
+                s.wait_stream(torch.cuda.current_stream())
+                with torch.cuda.stream(s):
+                    ours(pos, static_x.clone(), static_r.clone())
+                torch.cuda.current_stream().wait_stream(s)
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph):
+                    gh, gr = ours(pos, static_x.clone(), static_r.clone())
+                graph.replay()
+                torch.cuda.synchronize()
+                assert torch.equal(gh, eager_h) and torch.equal(gr, eager_r)
+                static_x.copy_(torch.randn_like(static_x))
+                graph.replay()
+                torch.cuda.synchronize()
+                h2, _ = ours(pos, static_x.clone(), static_r.clone())
+                assert torch.equal(gh, h2)
+        finally:
+            reset_context()
+
+
+def _engine(*extra):
+    cmd = [sys.executable, os.path.join(ROOT, "scripts", "engine_run.py"), "--preset", "small", "--layers", "4",
+           "--seqs", "6", "--max-tokens", "10", "--max-num-seqs", "8", "--mem", "0.3", *extra]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=ROOT)
+    assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-3000:])
+    lines = [json.loads(l) for l in r.stdout.splitlines() if l.startswith("{")]
+    assert len(lines) == 1, r.stdout[-2000:]
+    return lines[0]
+
+
+def test_reference_engine_decodes_with_the_swapped_block_eager_and_graph():
+    eager = _engine("--eager")
+    graph = _engine()
+    for run in (eager, graph):
+        assert run["sparse_blocks_ours"] == 3 and run["last_impl"] == "umma" and run["last_fused"] is True
+        assert len(run["token_ids"]) == 6 and all(len(t) == 10 for t in run["token_ids"])
+        assert all(0 <= t < 2048 for seq in run["token_ids"] for t in seq)
+    assert graph["cuda_graph_decode"] and not eager["cuda_graph_decode"]
+    assert graph["token_ids"] == eager["token_ids"], "CUDA-graph decode differs from eager decode"
+    fp8 = _engine("--weights", "fp8")
+    assert fp8["sparse_blocks_ours"] == 3 and len(fp8["token_ids"]) == 6
+    os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+    with open(os.path.join(ROOT, "gpurun_out", "engine_small.jsonl"), "w") as f:
+        for run in (eager, graph, fp8):
+            f.write(json.dumps({k: v for k, v in run.items() if k != "token_ids"}) + "\n")
