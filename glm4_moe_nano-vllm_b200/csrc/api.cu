@@ -51,12 +51,13 @@ int g_router_rows = 0;   // 0: pick by T; 16/32/64/128: token rows per router ti
 int g_bk32 = -1;         // see bk32_enabled()
 int g_down2 = -1;        // see down2_enabled()
 int g_force_bn = -2;     // see forced_bn_index()
+int g_ep_fast = 1;       // decode fast path of the peer-memory combine (one rendezvous per step), KNOB_EP_FAST
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct WsLayout {
   size_t logits, idx, w, offsets, row_token, row_weight, slot_row, num_tiles, sched, ready, fdone, tiles, scratch, x_rows,
-      act, y, xq, sx, actq, sact, ctl, stage, total;
+      act, y, xq, sx, actq, sact, ctl, stage, y_alt[2], slot_row_alt[2], total;
   int tile_capacity;
 };
 
@@ -101,6 +102,12 @@ WsLayout make_layout(const glm4moe_config_t& c) {
   // that can run expert-parallel (with_shared == 2 or a strict subset of the experts) pay for it.
   const bool ep_capable = c.with_shared == 2 || c.expert_end - c.expert_begin < c.n_routed_experts;
   L.stage = take(ep_capable && c.dtype != GLM4MOE_F32 ? T * H * es : 0);
+  // decode fast path of the peer-memory combine: weighted rows and slot_row of a call live in the buffer
+  // of the call's parity (<= 32 tokens; ep_combine.cu)
+  for (int i = 0; i < 2; ++i) {
+    L.y_alt[i] = take(ep_capable ? static_cast<size_t>(kDirectMaxTokens) * (k + 1) * H * es : 0);
+    L.slot_row_alt[i] = take(ep_capable ? static_cast<size_t>(kDirectMaxTokens) * k * 4 : 0);
+  }
   L.total = off;
   return L;
 }
@@ -159,6 +166,7 @@ extern "C" int glm4moe_debug_set(int knob, int value) {
       if (value != 0 && value != 16 && value != 32 && value != 64 && value != 128) return GLM4MOE_ERR_ARG;
       g_router_rows = value;
       return GLM4MOE_OK;
+    case GLM4MOE_KNOB_EP_FAST: g_ep_fast = value ? 1 : 0; return GLM4MOE_OK;
     case GLM4MOE_KNOB_BK32: g_bk32 = value ? 1 : 0; return GLM4MOE_OK;
     case GLM4MOE_KNOB_DOWN2: g_down2 = value ? 1 : 0; return GLM4MOE_OK;
     case GLM4MOE_KNOB_FORCE_TILE_ROWS:
@@ -358,7 +366,10 @@ extern "C" int glm4moe_layer_tile_rows(const glm4moe_layer_t* l, int T) {
 }
 
 static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, void* stream, cudaEvent_t* ev,
-                        int sh_lo_arg = -1, int sh_hi_arg = -1, bool rows_only = false) {
+                        int sh_lo_arg = -1, int sh_hi_arg = -1, bool rows_only = false,
+                        const EpFastSignal* epf = nullptr, bool* ep_fast_used = nullptr) {
+  // epf (rows_only): when this call runs the fused decode kernel, use the expert-parallel fast path (rows and
+  // slot_row in the parity buffers, ready flags published by the expert kernel) and report it in *ep_fast_used
   // rows_only: stop after the weighted expert rows y (no combine, `out` unused): the peer-memory
   // expert-parallel combine (ep_combine.cu) reads the rows of every rank
   if (!l || !x || (!out && !rows_only)) return GLM4MOE_ERR_ARG;
@@ -421,16 +432,23 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
   int rc;
   alignas(64) CUtensorMap tm_xdirect;
   bool combine_done = false;
+  const bool ep_fast = epf != nullptr && rows_only && direct && fused_enabled();
+  if (ep_fast_used) *ep_fast_used = ep_fast;
   STAGE_MARK(0);
   if (direct) {
     if (!fp8 && (rc = umma_make_tensor_map(&tm_xdirect, x, c.dtype, static_cast<uint64_t>(T), H, tile_rows)))
       return rc;
-    if ((rc = glm4moe_route_small(x, l->gate_w, l->bias, logits, T, H, E, k, c.routed_scaling_factor, c.dtype,
-                                  c.expert_begin, c.expert_end, tile_rows, sh_lo, sh_hi, idx, w, offsets, row_token,
-                                  row_weight, slot_row, tiles, L.tile_capacity, num_tiles,
-                                  reinterpret_cast<int32_t*>(ws + L.sched) + 24, fp8 ? ws + L.xq : nullptr,
-                                  fp8 ? reinterpret_cast<float*>(ws + L.sx) : nullptr,
-                                  c.max_tokens * (k + 1), stream)))
+    RouteSmallEp rep{};
+    if (ep_fast) {
+      rep.epoch = reinterpret_cast<const int32_t*>(ws + L.ctl);
+      for (int i = 0; i < 2; ++i) rep.slot_row_alt[i] = reinterpret_cast<int32_t*>(ws + L.slot_row_alt[i]);
+    }
+    if ((rc = route_small_ep(x, l->gate_w, l->bias, logits, T, H, E, k, c.routed_scaling_factor, c.dtype,
+                             c.expert_begin, c.expert_end, tile_rows, sh_lo, sh_hi, idx, w, offsets, row_token,
+                             row_weight, slot_row, tiles, L.tile_capacity, num_tiles,
+                             reinterpret_cast<int32_t*>(ws + L.sched) + 24, fp8 ? ws + L.xq : nullptr,
+                             fp8 ? reinterpret_cast<float*>(ws + L.sx) : nullptr,
+                             c.max_tokens * (k + 1), rep, stream)))
       return rc;
     STAGE_MARK(1);
     STAGE_MARK(2);
@@ -533,6 +551,7 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
       f.q.actq = ws + L.actq;
       f.q.scale_ld = R_cap;
     }
+    if (ep_fast) f.ep = *epf;
     if ((rc = decode_fused_launch(f, stream))) return rc;
     STAGE_MARK(5);
     combine_done = true;
@@ -818,6 +837,7 @@ extern "C" int glm4moe_p2p_free(void* ptr) {
 
 // sliced peer-memory combine: -1 = by size (default), 0 = never, 1 = whenever the layer has a staging region
 static int g_ep_sliced_mode = -1;
+
 extern "C" int glm4moe_set_ep_sliced(int mode) {
   if (mode < -1 || mode > 1) return GLM4MOE_ERR_ARG;
   g_ep_sliced_mode = mode;
@@ -838,13 +858,27 @@ extern "C" int glm4moe_layer_forward_ep_p2p(glm4moe_layer_t* l, const void* x, v
   if (T < 0 || T > c.max_tokens) return GLM4MOE_ERR_ARG;
   if (T == 0) return GLM4MOE_OK;
   const int launches0 = g_launches;
-  int rc = forward_impl(l, x, nullptr, T, stream, nullptr, -1, -1, /*rows_only=*/true);
-  if (rc) return rc;
   EpCombineArgs a{};
+  EpFastSignal sig{};
+  sig.enabled = 1;
+  sig.world = world;
+  sig.rank = rank;
+  sig.ctl = reinterpret_cast<int32_t*>(l->ws + l->L.ctl);
   for (int r = 0; r < world; ++r) {
     if (!peer_workspaces[r]) return GLM4MOE_ERR_ARG;
     a.ws[r] = static_cast<unsigned char*>(peer_workspaces[r]);
+    sig.peer_ready[r] = reinterpret_cast<int32_t*>(a.ws[r] + l->L.ctl) + 16 + rank;
   }
+  for (int i = 0; i < 2; ++i) {
+    sig.y_alt[i] = l->ws + l->L.y_alt[i];
+    a.off_y_alt[i] = l->L.y_alt[i];
+    a.off_slot_row_alt[i] = l->L.slot_row_alt[i];
+  }
+  bool fast = false;
+  int rc = forward_impl(l, x, nullptr, T, stream, nullptr, -1, -1, /*rows_only=*/true,
+                        g_ep_fast ? &sig : nullptr, &fast);
+  if (rc) return rc;
+  a.fast = fast ? 1 : 0;
   a.off_y = l->L.y;
   a.off_slot_row = l->L.slot_row;
   a.off_idx = l->L.idx;
@@ -865,6 +899,7 @@ extern "C" int glm4moe_layer_forward_ep_p2p(glm4moe_layer_t* l, const void* x, v
   const size_t row_bytes = static_cast<size_t>(T) * (a.k + 1) * a.H * dtype_size(c.dtype);
   a.sliced = g_ep_sliced_mode == 1 ? (has_stage || world == 1)      // world == 1: no peer, no staging needed
                                    : g_ep_sliced_mode == -1 && has_stage && row_bytes >= (16u << 20);
+  if (fast) a.sliced = 0;      // the decode fast path is a pull (<= 32 tokens)
   rc = ep_combine_p2p_launch(a, out, c.dtype, stream);
   l->last_launches = g_launches - launches0;
   return rc;

@@ -70,6 +70,13 @@ struct FusedItem {
 
 constexpr int kFusedQueue = 4;
 
+// expert-parallel fast path: tell every rank (incl. this one) that this rank's rows of call e are complete
+__device__ __forceinline__ void ep_publish_ready(const EpFastSignal& ep, int e) {
+  __threadfence_system();
+  for (int r = 0; r < ep.world; ++r)
+    asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(ep.peer_ready[r]), "r"(e * 4 + kEpModeFast) : "memory");
+}
+
 template <typename T, int BN, bool FP8>
 __global__ void __launch_bounds__(FusedCfg<BN, FP8>::kThreads, 1) decode_fused_kernel(
     const __grid_constant__ CUtensorMap tm_wgu,   // gate_up stack [n_stack * 2I, H], box {64, 128}
@@ -85,7 +92,8 @@ __global__ void __launch_bounds__(FusedCfg<BN, FP8>::kThreads, 1) decode_fused_k
     int32_t* __restrict__ fdone,                  // [H/128] down items finished per feature tile
     const unsigned char* __restrict__ pf0, size_t pf0_bytes,    // shared expert's gate_up / down weights:
     const unsigned char* __restrict__ pf1, size_t pf1_bytes,    // pulled into L2 while the router runs
-    const Fp8Args q) {                            // e4m3 tier: scales and the quantised activation buffer
+    const Fp8Args q,                              // e4m3 tier: scales and the quantised activation buffer
+    const EpFastSignal ep) {                      // expert-parallel fast path: parity row buffers + ready flags
   using Cfg = FusedCfg<BN, FP8>;
   constexpr int AK = Cfg::kAtomK;
   constexpr int NS = Cfg::kAccSlots;
@@ -303,8 +311,12 @@ __global__ void __launch_bounds__(FusedCfg<BN, FP8>::kThreads, 1) decode_fused_k
         }
       const int n_routed = *num_tiles_ptr - has_shared;
       const int total = n_routed * FG + (n_routed + has_shared) * FD;
-      if (n_routed + has_shared == 0)   // expert-parallel rank without a hit expert: the partial output is zero
+      if (n_routed + has_shared == 0) {   // expert-parallel rank without a hit expert: the partial output is zero
         for (int f = blockIdx.x; f < FD; f += gridDim.x) push(kZeroBase + f, 0);
+        // ... and it has no row to write: "complete" right away (the epoch is final after the wait above)
+        if (ep.enabled && blockIdx.x == 0)
+          ep_publish_ready(ep, *reinterpret_cast<const volatile int32_t*>(ep.ctl) + 1);
+      }
       for (;;) {
         const int w = atomicAdd(&sched[0], 1);
         if (w >= total) {
@@ -448,12 +460,26 @@ __global__ void __launch_bounds__(FusedCfg<BN, FP8>::kThreads, 1) decode_fused_k
     };
     int pend_f = -1, pend_done = 0, pend_target = 0;   // down item whose feature-tile count is in flight
     int pend_slot = 0;                                  // broadcast slot (alternates, so one barrier suffices)
+    T* y_rows = y;      // expert-parallel fast path: the buffer of this call's parity (resolved at the first down item)
+    int ep_e = 0;
     // publish(): thread 0 turns the count that came back for the PREVIOUS down item into a flag in
     // s_last[slot]; after the caller's next epi_sync every epilogue thread reads it (resolve()).
     auto publish = [&]() {
       if (pend_f >= 0 && ewi == 0 && lane == 0) {
         const int last = pend_done == pend_target;
-        if (last) fdone[pend_f] = 0;                    // re-armed for the next launch
+        if (last) {
+          fdone[pend_f] = 0;                            // re-armed for the next launch
+          if (ep.enabled) {
+            // feature tile complete on this rank; the thread that completes the last one publishes the
+            // ready flags (its acq_rel chain has seen every other CTA's row stores)
+            int c;
+            asm volatile("atom.add.acq_rel.gpu.global.s32 %0, [%1], 1;" : "=r"(c) : "l"(fdone + FD + 1) : "memory");
+            if (c == FD - 1) {
+              fdone[FD + 1] = 0;
+              ep_publish_ready(ep, ep_e);
+            }
+          }
+        }
         s_last[pend_slot] = last;
       }
     };
@@ -604,7 +630,11 @@ __global__ void __launch_bounds__(FusedCfg<BN, FP8>::kThreads, 1) decode_fused_k
         }
         }
       } else {
-        T* out_col = y + static_cast<size_t>(it.row_start) * H + feat;
+        if (ep.enabled && ep_e == 0) {   // after the dependency wait above: the previous combine has retired
+          ep_e = *reinterpret_cast<const volatile int32_t*>(ep.ctl) + 1;
+          y_rows = static_cast<T*>(ep.y_alt[ep_e & 1]);
+        }
+        T* out_col = y_rows + static_cast<size_t>(it.row_start) * H + feat;
         if constexpr (FP8) {
           // The activation scales were written by other CTAs' gate_up epilogues.  This CTA's producer
           // acquired ready[flag] before it loaded the activation atoms whose MMAs these warps wait on,
@@ -738,7 +768,7 @@ static int launch_fused_one(const DecodeFusedLaunch& a, cudaStream_t st) {
       a.row_weight, static_cast<T*>(a.act), static_cast<T*>(a.y), a.H, a.I, a.tokens, a.n_routed_rows,
       a.shared_expert, a.sh_lo, a.sh_hi, a.sched, a.ready, a.slot_row, static_cast<T*>(a.out), a.k, a.fdone,
       static_cast<const unsigned char*>(a.pf0), a.pf0_bytes, static_cast<const unsigned char*>(a.pf1), a.pf1_bytes,
-      a.q));
+      a.q, a.ep));
   return GLM4MOE_OK;
 }
 

@@ -18,6 +18,18 @@
 //   done:  the last block of the grid (ticket) stores e into every peer's done[me] and spins on its
 //          own done[0..R) >= e before the grid retires -> nobody overwrites y / slot_row (next
 //          forward) while a peer still reads them.
+//
+// Decode fast path (T <= 32, `a.fast`): ONE rendezvous per step.  The rows and slot_row of call e live
+// in buffers selected by the parity of e, the fused expert kernel itself stores the ready flags the moment
+// its last down item has landed (decode_fused.cu), and the done round is gone: rank r overwrites the
+// parity-p buffers again in call e + 2, after its combine of call e + 1 has seen every peer's
+// ready(e + 1) — which a peer only sends after its own combine of call e (the last reader of my
+// parity-p buffers) has completed.  Calls of the other modes use the plain buffers and keep their done
+// round, so the modes can be mixed freely.
+//
+// Every cross-GPU wait is bounded (~18 s of SM clocks): a rank that never arrives, or arrives in
+// another mode (`glm4moe_set_ep_sliced` set differently), stores an error code in ctl[2] and traps
+// instead of hanging the GPU.
 #include "common.cuh"
 #include "ep_combine.cuh"
 
@@ -32,6 +44,25 @@ __device__ __forceinline__ int32_t ld_acquire_sys(const int32_t* p) {
   int32_t v;
   asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
+}
+constexpr long long kSpinTimeoutCycles = 1ll << 35;
+// wait until the flag reaches call `e` (flag = epoch * 4 + mode); wrap-safe compare
+__device__ __forceinline__ void wait_flag(const int32_t* flag, int e, int mode, int32_t* ctl) {
+  const int target = e * 4;
+  const long long t0 = clock64();
+  int v;
+  while ((v = ld_acquire_sys(flag)) - target < 0) {
+    if (clock64() - t0 > kSpinTimeoutCycles) {
+      ctl[2] = kEpErrTimeout;
+      __threadfence_system();
+      __trap();
+    }
+  }
+  if ((v >> 2) == e && (v & 3) != mode) {
+    ctl[2] = kEpErrModeMismatch;
+    __threadfence_system();
+    __trap();
+  }
 }
 __device__ __forceinline__ uint4 ld_peer16(const void* p) {   // L1-bypassing 128-bit load (peer or local)
   uint4 r;
@@ -57,21 +88,21 @@ __global__ void __launch_bounds__(kEpThreads) ep_combine_p2p_kernel(const EpComb
   unsigned char* my_ws = a.ws[a.rank];
   int32_t* ctl = reinterpret_cast<int32_t*>(my_ws + a.off_ctl);   // [0] epoch, [1] blocks done, [16..] ready, [32..] done
   const int e = *reinterpret_cast<volatile int32_t*>(ctl) + 1;
-  // ---- ready: tell every peer our rows exist, wait until theirs do ----
-  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x < a.world) {
+  const int mode = a.fast ? kEpModeFast : kEpModePull;
+  // ---- ready: tell every peer our rows exist (fast path: the expert kernel already did), wait until theirs do ----
+  if (!a.fast && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x < a.world) {
     __threadfence_system();
     int32_t* peer_ctl = reinterpret_cast<int32_t*>(a.ws[threadIdx.x] + a.off_ctl);
-    st_release_sys(peer_ctl + 16 + a.rank, e);
+    st_release_sys(peer_ctl + 16 + a.rank, e * 4 + mode);
   }
-  if (threadIdx.x < a.world) {
-    while (ld_acquire_sys(ctl + 16 + threadIdx.x) < e) {
-    }
-  }
+  if (threadIdx.x < a.world) wait_flag(ctl + 16 + threadIdx.x, e, mode, ctl);
   __syncthreads();
 
   // ---- reduce: block (x = column chunk, y strides over tokens) ----
   const int col = (blockIdx.x * kEpThreads + threadIdx.x) * V;
   const int32_t* my_idx = reinterpret_cast<const int32_t*>(my_ws + a.off_idx);
+  const size_t off_y = a.fast ? a.off_y_alt[e & 1] : a.off_y;
+  const size_t off_slot_row = a.fast ? a.off_slot_row_alt[e & 1] : a.off_slot_row;
   for (int t = blockIdx.y; t < a.tokens; t += gridDim.y) {
     // slot j -> (owner rank, row on the owner); the shared expert's row lives on the rank owning t's slice
     if (threadIdx.x <= a.k) {
@@ -79,7 +110,7 @@ __global__ void __launch_bounds__(kEpThreads) ep_combine_p2p_kernel(const EpComb
       if (threadIdx.x < a.k) {
         const int ex = my_idx[static_cast<size_t>(t) * a.k + threadIdx.x];
         owner = ex / a.experts_per_rank;
-        row = ld_peer_s32(reinterpret_cast<const int32_t*>(a.ws[owner] + a.off_slot_row) +
+        row = ld_peer_s32(reinterpret_cast<const int32_t*>(a.ws[owner] + off_slot_row) +
                           static_cast<size_t>(t) * a.k + threadIdx.x);
       } else {
         owner = a.with_shared ? min(t / a.shared_per_rank, a.world - 1) : 0;
@@ -98,7 +129,7 @@ __global__ void __launch_bounds__(kEpThreads) ep_combine_p2p_kernel(const EpComb
 #pragma unroll
       for (int j = 0; j <= kEpMaxTopK; ++j) {
         if (j <= a.k && s_row[j] >= 0)
-          raw[j] = ld_peer16(a.ws[s_owner[j]] + a.off_y +
+          raw[j] = ld_peer16(a.ws[s_owner[j]] + off_y +
                              (static_cast<size_t>(s_row[j]) * a.H + col) * sizeof(T));
       }
 #pragma unroll
@@ -126,11 +157,10 @@ __global__ void __launch_bounds__(kEpThreads) ep_combine_p2p_kernel(const EpComb
   }
   __syncthreads();
   if (!s_last) return;
-  if (threadIdx.x < a.world) {
+  if (!a.fast && threadIdx.x < a.world) {
     int32_t* peer_ctl = reinterpret_cast<int32_t*>(a.ws[threadIdx.x] + a.off_ctl);
-    st_release_sys(peer_ctl + 32 + a.rank, e);
-    while (ld_acquire_sys(ctl + 32 + threadIdx.x) < e) {
-    }
+    st_release_sys(peer_ctl + 32 + a.rank, e * 4 + mode);
+    wait_flag(ctl + 32 + threadIdx.x, e, mode, ctl);
   }
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -167,12 +197,9 @@ __global__ void __launch_bounds__(kEpThreads) ep_combine_sliced_kernel(const EpC
   if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x < a.world) {
     __threadfence_system();
     int32_t* peer_ctl = reinterpret_cast<int32_t*>(a.ws[threadIdx.x] + a.off_ctl);
-    st_release_sys(peer_ctl + 16 + a.rank, e);
+    st_release_sys(peer_ctl + 16 + a.rank, e * 4 + kEpModeSliced);
   }
-  if (threadIdx.x < a.world) {
-    while (ld_acquire_sys(ctl + 16 + threadIdx.x) < e) {
-    }
-  }
+  if (threadIdx.x < a.world) wait_flag(ctl + 16 + threadIdx.x, e, kEpModeSliced, ctl);
   __syncthreads();
 
   const int col = (blockIdx.x * kEpThreads + threadIdx.x) * V;
@@ -237,12 +264,9 @@ __global__ void __launch_bounds__(kEpThreads) ep_combine_sliced_kernel(const EpC
   if (s_last && threadIdx.x < a.world) {
     __threadfence_system();
     int32_t* peer_ctl = reinterpret_cast<int32_t*>(a.ws[threadIdx.x] + a.off_ctl);
-    st_release_sys(peer_ctl + 32 + a.rank, e);
+    st_release_sys(peer_ctl + 32 + a.rank, e * 4 + kEpModeSliced);
   }
-  if (threadIdx.x < a.world) {
-    while (ld_acquire_sys(ctl + 32 + threadIdx.x) < e) {
-    }
-  }
+  if (threadIdx.x < a.world) wait_flag(ctl + 32 + threadIdx.x, e, kEpModeSliced, ctl);
   __syncthreads();
   // ---- the other ranks' slices: local staging region -> out ----
   if (col < a.H) {
@@ -271,6 +295,7 @@ int ep_combine_p2p_launch(const EpCombineArgs& a, void* out, int dtype, void* st
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int gx = (a.H / 8 + kEpThreads - 1) / kEpThreads;
   int gy = a.tokens < 128 ? a.tokens : 128;
+  if (a.fast && a.sliced) return GLM4MOE_ERR_ARG;
   if (a.sliced) {
     // every block waits for the peers inside the kernel: keep the whole grid co-resident
     // (128-thread blocks without shared-memory demand: >= 4 per SM on every register budget)

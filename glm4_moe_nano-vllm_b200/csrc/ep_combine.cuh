@@ -19,11 +19,39 @@ struct EpCombineArgs {
   int experts_per_rank;             // E / world (contiguous expert blocks)
   int with_shared;                  // 1: shared-expert rows T*k + t exist on the rank owning token t's slice
   int shared_per_rank;              // ceil(T / world): token slice size of the shared expert
+  // decode fast path (T <= 32, fused expert kernel): the rows and slot_row of call e live in the
+  // epoch-parity buffers below, the producer kernel itself has sent the ready flags, and there is no
+  // done round (see ep_combine.cu)
+  int fast;
+  size_t off_y_alt[2], off_slot_row_alt[2];
 };
 
-// control block inside the workspace (int32): [0] epoch, [1] blocks finished, [16 + r] ready flag
-// written by rank r, [32 + r] done flag written by rank r
+// control block inside the workspace (int32): [0] epoch (calls completed), [1] blocks finished,
+// [2] error code of a timed-out / mismatched wait, [16 + r] ready flag written by rank r,
+// [32 + r] done flag written by rank r.  Flag value = epoch * 4 + mode (kEpMode*).
 constexpr size_t kEpCtlBytes = 256;
+constexpr int kEpModePull = 0, kEpModeSliced = 1, kEpModeFast = 2;
+constexpr int kEpErrTimeout = 1, kEpErrModeMismatch = 2;
+
+// What the fused decode kernel needs to publish "my rows of call e are complete" to every rank itself.
+struct EpFastSignal {
+  int enabled;
+  int world, rank;
+  int32_t* ctl;                      // own control block (epoch)
+  int32_t* peer_ready[kEpMaxRanks];  // rank r's ctl + 16 + my rank, as mapped in this process
+  void* y_alt[2];                    // epoch-parity row buffers, [32 * (k + 1), H] each
+};
+
+// route_small.cu, expert-parallel decode fast path: slot_row goes to the buffer of the call's parity
+struct RouteSmallEp {
+  const int32_t* epoch;             // own ctl[0]; nullptr = off
+  int32_t* slot_row_alt[2];
+};
+int route_small_ep(const void* h, const void* gate_w, const float* bias, void* logits, int T, int H, int E, int k,
+                   float scale, int dtype, int e_lo, int e_hi, int tile_rows, int shared_lo, int shared_hi,
+                   int32_t* idx, float* w, int32_t* expert_offsets, int32_t* row_token, float* row_weight,
+                   int32_t* slot_row, int32_t* tiles, int32_t tile_capacity, int32_t* num_tiles, int32_t* ticket,
+                   void* xq, float* x_scale_t, int x_scale_ld, const RouteSmallEp& ep, void* stream);
 
 int ep_combine_p2p_launch(const EpCombineArgs& args, void* out, int dtype, void* stream);
 

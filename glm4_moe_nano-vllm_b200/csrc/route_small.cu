@@ -12,6 +12,7 @@
 
 #include "common.cuh"
 #include "route_device.cuh"
+#include "ep_combine.cuh"
 
 namespace glm4moe {
 
@@ -22,7 +23,7 @@ __global__ void __launch_bounds__(256) route_small_kernel(
     float* w, int32_t* __restrict__ expert_offsets, int32_t* __restrict__ row_token,
     float* __restrict__ row_weight, int32_t* __restrict__ slot_row, int4* __restrict__ tiles, int tile_capacity,
     int32_t* __restrict__ num_tiles, int32_t* __restrict__ ticket, unsigned char* __restrict__ xq,
-    float* __restrict__ sx_t, int sx_ld) {
+    float* __restrict__ sx_t, int sx_ld, const RouteSmallEp ep) {
   constexpr int V = Dt<T>::kVec;
   __shared__ float part[8][TT * EB];
   __shared__ PermuteSmallSmem psm;
@@ -139,6 +140,9 @@ __global__ void __launch_bounds__(256) route_small_kernel(
   if (!s_last) return;
   __threadfence();
   __syncthreads();   // idx / w of this block's own global writes are visible to the block
+  // expert-parallel decode fast path: the peers read slot_row of call e from the buffer of e's parity
+  // (ep_combine.cu); the epoch is final here (this kernel started after the previous combine retired)
+  if (ep.epoch != nullptr) slot_row = ((*reinterpret_cast<const volatile int32_t*>(ep.epoch) + 1) & 1) ? ep.slot_row_alt[1] : ep.slot_row_alt[0];
   permute_small_body(psm, idx, w, Tn, k, E, e_lo, e_hi, tile_rows, sh_lo, sh_hi, expert_offsets, row_token,
                      row_weight, slot_row, tiles, tile_capacity, num_tiles);
 }
@@ -148,7 +152,8 @@ static int launch_route_small(const void* h, const void* gw, const float* bias, 
                               int k, float scale, int e_lo, int e_hi, int tile_rows, int sh_lo, int sh_hi,
                               int32_t* idx, float* w, int32_t* offsets, int32_t* row_token, float* row_weight,
                               int32_t* slot_row, int32_t* tiles, int tile_capacity, int32_t* num_tiles,
-                              int32_t* ticket, void* xq, float* sx_t, int sx_ld, cudaStream_t st) {
+                              int32_t* ticket, void* xq, float* sx_t, int sx_ld, const RouteSmallEp& ep,
+                              cudaStream_t st) {
   constexpr int V = Dt<T>::kVec;
   if (H % V != 0) return GLM4MOE_ERR_UNSUPPORTED;
   if (T_ <= 2) {
@@ -157,28 +162,27 @@ static int launch_route_small(const void* h, const void* gw, const float* bias, 
                                   static_cast<const T*>(gw), bias, static_cast<T*>(logits), T_, H, E, k, scale, e_lo,
                                   e_hi, tile_rows, sh_lo, sh_hi, idx, w, offsets, row_token, row_weight, slot_row,
                                   reinterpret_cast<int4*>(tiles), tile_capacity, num_tiles, ticket,
-                                  static_cast<unsigned char*>(xq), sx_t, sx_ld));
+                                  static_cast<unsigned char*>(xq), sx_t, sx_ld, ep));
   } else {
     dim3 grid((E + 3) / 4, (T_ + 3) / 4);
     GLM4MOE_CUDA_CHECK(launch_pdl(route_small_kernel<T, 4, 4>, grid, dim3(256), 0, st, static_cast<const T*>(h),
                                   static_cast<const T*>(gw), bias, static_cast<T*>(logits), T_, H, E, k, scale, e_lo,
                                   e_hi, tile_rows, sh_lo, sh_hi, idx, w, offsets, row_token, row_weight, slot_row,
                                   reinterpret_cast<int4*>(tiles), tile_capacity, num_tiles, ticket,
-                                  static_cast<unsigned char*>(xq), sx_t, sx_ld));
+                                  static_cast<unsigned char*>(xq), sx_t, sx_ld, ep));
   }
   return GLM4MOE_OK;
 }
 
 }  // namespace glm4moe
 
-using namespace glm4moe;
-
-extern "C" int glm4moe_route_small(const void* h, const void* gate_w, const float* bias, void* logits, int T, int H,
-                                   int E, int k, float scale, int dtype, int e_lo, int e_hi, int tile_rows,
-                                   int shared_lo, int shared_hi, int32_t* idx, float* w, int32_t* expert_offsets,
-                                   int32_t* row_token, float* row_weight, int32_t* slot_row, int32_t* tiles,
-                                   int32_t tile_capacity, int32_t* num_tiles, int32_t* ticket, void* xq,
-                                   float* x_scale_t, int x_scale_ld, void* stream) {
+namespace glm4moe {
+int route_small_ep(const void* h, const void* gate_w, const float* bias, void* logits, int T, int H,
+                   int E, int k, float scale, int dtype, int e_lo, int e_hi, int tile_rows,
+                   int shared_lo, int shared_hi, int32_t* idx, float* w, int32_t* expert_offsets,
+                   int32_t* row_token, float* row_weight, int32_t* slot_row, int32_t* tiles,
+                   int32_t tile_capacity, int32_t* num_tiles, int32_t* ticket, void* xq,
+                   float* x_scale_t, int x_scale_ld, const RouteSmallEp& ep, void* stream) {
   if (!h || !gate_w || !bias || !logits || !idx || !w || !expert_offsets || !row_token || !row_weight ||
       !slot_row || !tiles || !num_tiles || !ticket)
     return GLM4MOE_ERR_ARG;
@@ -195,6 +199,20 @@ extern "C" int glm4moe_route_small(const void* h, const void* gate_w, const floa
                          return launch_route_small<T_>(h, gate_w, bias, logits, T, H, E, k, scale, e_lo, e_hi,
                                                        tile_rows, shared_lo, shared_hi, idx, w, expert_offsets,
                                                        row_token, row_weight, slot_row, tiles, tile_capacity,
-                                                       num_tiles, ticket, xq, x_scale_t, x_scale_ld, st));
+                                                       num_tiles, ticket, xq, x_scale_t, x_scale_ld, ep, st));
   return GLM4MOE_OK;
+}
+}  // namespace glm4moe
+
+using namespace glm4moe;
+
+extern "C" int glm4moe_route_small(const void* h, const void* gate_w, const float* bias, void* logits, int T, int H,
+                                   int E, int k, float scale, int dtype, int e_lo, int e_hi, int tile_rows,
+                                   int shared_lo, int shared_hi, int32_t* idx, float* w, int32_t* expert_offsets,
+                                   int32_t* row_token, float* row_weight, int32_t* slot_row, int32_t* tiles,
+                                   int32_t tile_capacity, int32_t* num_tiles, int32_t* ticket, void* xq,
+                                   float* x_scale_t, int x_scale_ld, void* stream) {
+  return route_small_ep(h, gate_w, bias, logits, T, H, E, k, scale, dtype, e_lo, e_hi, tile_rows, shared_lo, shared_hi,
+                        idx, w, expert_offsets, row_token, row_weight, slot_row, tiles, tile_capacity, num_tiles, ticket,
+                        xq, x_scale_t, x_scale_ld, RouteSmallEp{}, stream);
 }

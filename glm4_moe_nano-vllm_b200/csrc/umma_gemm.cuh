@@ -2,6 +2,8 @@
 #pragma once
 #include <stdint.h>
 
+#include "ep_combine.cuh"
+
 namespace glm4moe {
 
 // Decode "direct" mode of the gate_up GEMM (T <= tile_rows <= 32): the MMA token tile is the layer
@@ -93,6 +95,9 @@ struct DecodeFusedLaunch {
   size_t pf1_bytes;
   int fp8;                   // 1: e4m3 weights / activations (tm_* are byte maps), q is set
   Fp8Args q;
+  // expert-parallel decode fast path (out == nullptr): rows go to the epoch-parity buffer and the kernel
+  // itself publishes "rows of this call complete" to every rank when its last down item has landed
+  EpFastSignal ep;
 };
 int decode_fused_launch(const DecodeFusedLaunch& args, void* stream);
 

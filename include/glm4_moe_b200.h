@@ -68,7 +68,10 @@ int glm4moe_abi_version(void);
  * expert; 16/32/64/128/256 force one tile size (parity tests walk every tile geometry with it). */
 enum { GLM4MOE_KNOB_DIRECT = 0, GLM4MOE_KNOB_FUSED = 1, GLM4MOE_KNOB_FP8_PREFILL = 2,
        GLM4MOE_KNOB_ROUTER_ROWS = 3 /* token rows per tensor-core router tile: 0 = by T, 16/32/64/128 */,
-       GLM4MOE_KNOB_BK32 = 4, GLM4MOE_KNOB_DOWN2 = 5, GLM4MOE_KNOB_FORCE_TILE_ROWS = 6 };
+       GLM4MOE_KNOB_BK32 = 4, GLM4MOE_KNOB_DOWN2 = 5, GLM4MOE_KNOB_FORCE_TILE_ROWS = 6,
+       GLM4MOE_KNOB_EP_FAST = 7 /* 1 (default): decode-size expert-parallel calls use ONE cross-rank rendezvous (rows in
+                                   epoch-parity buffers, ready flags from the expert kernel, no done round); must be
+                                   the same on every rank (a mismatch traps with an error code instead of hanging) */ };
 int glm4moe_debug_set(int knob, int value);
 const char* glm4moe_error_string(int code);
 

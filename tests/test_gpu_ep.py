@@ -52,6 +52,13 @@ def _worker(rank, world, port, q):
                             dist.barrier()
                             ys = ep(x.cuda())
                             assert torch.equal(ys, y1), f"T={T}: sliced mode {mode} differs"
+                        # decode fast path (one rendezvous per step) on / off, several steps back to back
+                        for fast in (0, 1, 1, 0, 1):
+                            _lib.check(_lib.load().glm4moe_debug_set(7, fast))
+                            dist.barrier()
+                            for rep in range(3):
+                                assert torch.equal(ep(x.cuda()), y1), f"T={T}: fast={fast} rep={rep} differs"
+                        _lib.check(_lib.load().glm4moe_debug_set(7, 1))
                 torch.cuda.synchronize()
                 if layout == "p2p":
                     ep.close_p2p()

@@ -863,6 +863,7 @@ def test_peer_memory_combine_world1_bit_identical(shape_name, Ts):
     handle, off = ep.ipc_handle()
     assert len(handle) == 64
     bases = (C.c_void_p * 1)(ep.workspace_base())
+    lib = _lib.load()
     for T in Ts:
         x = synth.make_tokens(shape, T, dt, 50 + T).cuda()
         with torch.inference_mode():
@@ -871,13 +872,16 @@ def test_peer_memory_combine_world1_bit_identical(shape_name, Ts):
                 got = ep.forward_ep_p2p(x, bases)
                 assert torch.equal(got, want), f"T={T} rep={rep}"
             assert torch.equal(ep(x), want)       # the ordinary entry still works on the same workspace
-            # sliced form of the combine (own token slice = all tokens in a world of one)
-            _lib.check(_lib.load().glm4moe_set_ep_sliced(1))
+            # decode fast path (T <= 32: rows in epoch-parity buffers, ready flags from the expert kernel, no
+            # done round) interleaved with the plain pull form and the sliced form on the same epoch counter
             try:
-                for rep in range(2):
-                    assert torch.equal(ep.forward_ep_p2p(x, bases), want), f"sliced T={T} rep={rep}"
+                for fast, sliced in ((1, -1), (0, -1), (1, -1), (1, -1), (0, 1), (1, 1), (0, 0), (1, -1)):
+                    _lib.check(lib.glm4moe_debug_set(7, fast))
+                    _lib.check(lib.glm4moe_set_ep_sliced(sliced))
+                    assert torch.equal(ep.forward_ep_p2p(x, bases), want), f"T={T} fast={fast} sliced={sliced}"
             finally:
-                _lib.check(_lib.load().glm4moe_set_ep_sliced(-1))
+                _lib.check(lib.glm4moe_debug_set(7, 1))
+                _lib.check(lib.glm4moe_set_ep_sliced(-1))
 
 
 # ------------------------------------------------------------------------------------------
