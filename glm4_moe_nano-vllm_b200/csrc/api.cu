@@ -103,10 +103,12 @@ WsLayout make_layout(const glm4moe_config_t& c) {
   const bool ep_capable = c.with_shared == 2 || c.expert_end - c.expert_begin < c.n_routed_experts;
   L.stage = take(ep_capable && c.dtype != GLM4MOE_F32 ? T * H * es : 0);
   // decode fast path of the peer-memory combine: weighted rows and slot_row of a call live in the buffer
-  // of the call's parity (<= 32 tokens; ep_combine.cu)
+  // of the call's parity (<= 32 tokens; ep_combine.cu).  Small (2 x 32 * (k + 1) rows), so every layer the
+  // peer-memory entry accepts has them (a world of one rank included).
+  const bool ep_alt = c.dtype != GLM4MOE_F32;
   for (int i = 0; i < 2; ++i) {
-    L.y_alt[i] = take(ep_capable ? static_cast<size_t>(kDirectMaxTokens) * (k + 1) * H * es : 0);
-    L.slot_row_alt[i] = take(ep_capable ? static_cast<size_t>(kDirectMaxTokens) * k * 4 : 0);
+    L.y_alt[i] = take(ep_alt ? static_cast<size_t>(kDirectMaxTokens) * (k + 1) * H * es : 0);
+    L.slot_row_alt[i] = take(ep_alt ? static_cast<size_t>(kDirectMaxTokens) * k * 4 : 0);
   }
   L.total = off;
   return L;
