@@ -61,7 +61,10 @@ def _explain_routing(idx, logits, x, gate_w, bias, shape, dt, max_frac=2e-2):
     `scores_for_choice`, and (c) the two logit computations actually rounded one of the pair's logits
     differently (fp32 accumulation order).  Returns the number of such tokens."""
     ref_logits = O.router_logits(x, gate_w)
-    oi, ow = O.canonical_routing(*O.select_from_logits(ref_logits, bias, shape.k, shape.routed_scaling_factor))
+    # ties in scores_for_choice: torch.topk's pick is implementation-defined, the kernel's rule is pinned
+    # (lower expert id), so the oracle is asked for that rule
+    oi, ow = O.canonical_routing(*O.select_from_logits(ref_logits, bias, shape.k, shape.routed_scaling_factor,
+                                                       tie_rule="lowest_index"))
     mism = (idx != oi).any(-1)
     d = (logits.float() - ref_logits.float()).abs()
     sc = logits.float().sigmoid().to(dt).float() + bias
@@ -82,7 +85,9 @@ def _explain_routing(idx, logits, x, gate_w, bias, shape, dt, max_frac=2e-2):
                 ulp_v = u * 2.0 ** (torch.tensor(v).log2().floor().item() + 1)      # spacing of dt at v
                 frac = (v / ulp_v) % 1.0
                 on_boundary |= abs(frac - 0.5) < 2e-3
-            assert on_boundary, f"token {t}: mismatch without a logit flip or a sigmoid rounding boundary"
+            assert on_boundary, (f"token {t}: mismatch without a logit flip or a sigmoid rounding boundary: experts "
+                                 f"{only}, logits {logits[t, only].tolist()}, scores_for_choice "
+                                 f"{sc[t, only].tolist()}, bias {bias[only].tolist()}")
     assert float(mism.float().mean()) <= max_frac, float(mism.float().mean())
     return int(mism.sum())
 
