@@ -128,7 +128,7 @@ def _hf_config(shape):
 def _workload(shape, T, fp8):
     regime = "decode batch" if T <= 256 else "prefill"
     return (f"{shape.name} MoE layer (H={shape.H}, E={shape.E}, top-{shape.k}, I={shape.I}, 1 shared) "
-            f"{'FP8 e4m3 block-128 expert weights, bf16 activations in/out,' if fp8 else 'bf16'} "
+            f"{'FP8 e4m3 block-128 expert weights (power-of-two scales), bf16 activations in/out,' if fp8 == 'fp8_pow2' else 'FP8 e4m3 block-128 expert weights, bf16 activations in/out,' if fp8 else 'bf16'} "
             f"random-init, {regime} T={T}")
 
 
@@ -195,7 +195,7 @@ def main():
     ap.add_argument("--ep-layout", default="p2p", choices=["p2p", "allreduce", "alltoall"],
                     help="expert-parallel layout for --gpus > 1 (distributed.py): p2p = combine + reduction in "
                          "one kernel over NVLink peer memory, allreduce / alltoall = NCCL")
-    ap.add_argument("--weights", default="bf16", choices=["bf16", "fp8"],
+    ap.add_argument("--weights", default="bf16", choices=["bf16", "fp8", "fp8_pow2"],
                     help="fp8 = e4m3 expert weights with 128x128 fp32 block scales, per-token 1x128 activations "
                          "(BASELINE configs[2]); single GPU")
     ap.add_argument("--ep-sliced", type=int, default=-1, choices=[-1, 0, 1],
@@ -212,11 +212,12 @@ def main():
     shape = synth.SHAPES[args.shape]
     dt = torch.bfloat16
     T = args.tokens
-    fp8 = args.weights == "fp8"
+    fp8 = args.weights in ("fp8", "fp8_pow2")
+    pow2 = args.weights == "fp8_pow2"      # UE8M0 scales: prefill GEMMs with hardware block scaling (umma_fp8_mx.cu)
     if fp8 and world > 1:
         raise SystemExit("--weights fp8 is a single-GPU bench")
     n_batches = N_BATCHES if T <= 1024 else 4
-    config = _config(shape, T, fp8, n_batches)
+    config = _config(shape, T, args.weights if fp8 else False, n_batches)
 
     # ------------------------------------------------------------------ reference arm (CPU)
     if args.impl == "reference":
@@ -259,7 +260,7 @@ def main():
     weights = synth.make_weights_device(shape, dt, dev, experts=range(moe.expert_begin, moe.expert_end))
     moe.load_local_stacks(weights)
     if fp8:
-        moe.quantize_fp8(drop_native=True)      # offline conversion (fp8.quantize_block128), outside the timed region
+        moe.quantize_fp8(drop_native=True, pow2_scales=pow2)      # offline conversion (fp8.quantize_block128), outside the timed region
     if world > 1:
         from glm4_moe_b200.distributed import ExpertParallelMoE
         layer = ExpertParallelMoE(moe, shape.E, layout=args.ep_layout)
@@ -451,7 +452,8 @@ def main():
         kern = "decode_fused_kernel<gate_up+silu_mul+down+combine>"
         gu_bytes = (U + n_sh) * 3 * I * H * wb + (T / world) * H * 2 + T * H * 2
     else:
-        kern = ("umma_fp8_prefill_kernel<gate_up+silu_mul+requant>" if fp8 and T * k / shape.E >= 48 else
+        kern = ("umma_fp8_mx_kernel<gate_up+silu_mul+requant> (tcgen05 block-scaled MMA)" if pow2 and T * k / shape.E >= 48 else
+                "umma_fp8_prefill_kernel<gate_up+silu_mul+requant>" if fp8 and T * k / shape.E >= 48 else
                 "umma_fp8_kernel<gate_up+silu_mul>" if fp8 else "umma_grouped_kernel<gate_up+silu_mul>")
         gu_bytes = (U + n_sh) * 2 * I * H * wb + rows * H * wb + rows * I * wb
     achieved = gu_bytes / gu_ms / 1e6
@@ -503,7 +505,9 @@ def main():
     line = {"metric": METRIC, "value": T * 1e3 / ms_step, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "ms_per_step_median": ms_median,
             "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "bf16" if not fp8 else "fp8_e4m3 (fp32 block scales, fp32 accumulate)",
+            "scaling": "strong", "vs_baseline": None, "dtype": "bf16" if not fp8 else
+            "fp8_e4m3 (power-of-two block scales applied by the MMA, fp32 accumulate)" if pow2 else
+            "fp8_e4m3 (fp32 block scales, fp32 accumulate)",
             "data": "synthetic", "config": config,
             "details": {"experts_hit_mean": U, "expert_gemm_impl": impl_name, "fused_decode_kernel": bool(fused),
                         "parallelism": (f"ep{world}-{args.ep_layout}" + (f"-sliced{args.ep_sliced}" if args.ep_sliced >= 0 else ""))

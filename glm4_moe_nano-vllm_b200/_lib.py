@@ -13,7 +13,7 @@ from .build import LIB_PATH
 
 F32, F16, BF16 = 0, 1, 2
 IMPL_AUTO, IMPL_SIMT, IMPL_UMMA = 0, 1, 2
-W_NATIVE, W_FP8_BLOCK128 = 0, 1
+W_NATIVE, W_FP8_BLOCK128, W_FP8_BLOCK128_POW2 = 0, 1, 2
 
 DTYPE_CODE = {torch.float32: F32, torch.float16: F16, torch.bfloat16: BF16}
 

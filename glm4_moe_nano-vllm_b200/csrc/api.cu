@@ -51,15 +51,20 @@ int g_router_rows = 0;   // 0: pick by T; 16/32/64/128: token rows per router ti
 int g_bk32 = -1;         // see bk32_enabled()
 int g_down2 = -1;        // see down2_enabled()
 int g_force_bn = -2;     // see forced_bn_index()
+int g_fp8_mx = 1;        // hardware block scaling for FP8_BLOCK128_POW2 prefill (umma_fp8_mx.cu), KNOB_FP8_MX
 int g_ep_fast = 1;       // decode fast path of the peer-memory combine (one rendezvous per step), KNOB_EP_FAST
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct WsLayout {
   size_t logits, idx, w, offsets, row_token, row_weight, slot_row, num_tiles, sched, ready, fdone, tiles, scratch, x_rows,
-      act, y, xq, sx, actq, sact, ctl, stage, y_alt[2], slot_row_alt[2], total;
+      act, y, xq, sx, actq, sact, sx_sf, sact_sf, ctl, stage, y_alt[2], slot_row_alt[2], total;
   int tile_capacity;
 };
+
+bool is_fp8(int weight_format) {
+  return weight_format == GLM4MOE_W_FP8_BLOCK128 || weight_format == GLM4MOE_W_FP8_BLOCK128_POW2;
+}
 
 WsLayout make_layout(const glm4moe_config_t& c) {
   WsLayout L{};
@@ -90,12 +95,17 @@ WsLayout make_layout(const glm4moe_config_t& c) {
   L.x_rows = take(R * H * es);
   L.act = take(R * I * es);
   L.y = take(R * H * es);
-  L.xq = L.sx = L.actq = L.sact = 0;
-  if (c.weight_format == GLM4MOE_W_FP8_BLOCK128) {
+  L.xq = L.sx = L.actq = L.sact = L.sx_sf = L.sact_sf = 0;
+  if (is_fp8(c.weight_format)) {
     L.xq = take(R * H);                 // e4m3 activation rows
     L.sx = take((H / 128) * R * 4);     // their per-128 scales, k-block major [H/128, R]
     L.actq = take(R * I);
     L.sact = take(((I + 127) / 128) * R * 4);
+  }
+  if (c.weight_format == GLM4MOE_W_FP8_BLOCK128_POW2) {
+    // the same scales as packed UE8M0 exponent bytes, 4 k-blocks per word: [ceil(K/512), R] (umma_fp8_mx.cu)
+    L.sx_sf = take(((H / 128 + 3) / 4) * R * 4);
+    L.sact_sf = take(((I / 128 + 3) / 4) * R * 4);
   }
   L.ctl = take(kEpCtlBytes);   // peer-memory combine: epoch, ticket, ready / done flags (ep_combine.cu)
   // sliced peer-memory combine: the rows peers store their reduced token slices into.  Only layers
@@ -126,6 +136,8 @@ struct glm4moe_layer {
   const void* w_down;
   const float* s_gate_up;
   const float* s_down;
+  uint32_t* sf_gate_up;   // FP8_BLOCK128_POW2: packed UE8M0 copies of the block scales (owned, cudaMalloc)
+  uint32_t* sf_down;
   int sm_count;
   bool umma_ok;
   int last_launches;
@@ -169,6 +181,7 @@ extern "C" int glm4moe_debug_set(int knob, int value) {
       g_router_rows = value;
       return GLM4MOE_OK;
     case GLM4MOE_KNOB_EP_FAST: g_ep_fast = value ? 1 : 0; return GLM4MOE_OK;
+    case GLM4MOE_KNOB_FP8_MX: g_fp8_mx = value ? 1 : 0; return GLM4MOE_OK;
     case GLM4MOE_KNOB_BK32: g_bk32 = value ? 1 : 0; return GLM4MOE_OK;
     case GLM4MOE_KNOB_DOWN2: g_down2 = value ? 1 : 0; return GLM4MOE_OK;
     case GLM4MOE_KNOB_FORCE_TILE_ROWS:
@@ -202,7 +215,7 @@ static int check_cfg(const glm4moe_config_t* c) {
   if (c->dtype != GLM4MOE_F32 && c->dtype != GLM4MOE_F16 && c->dtype != GLM4MOE_BF16) return GLM4MOE_ERR_ARG;
   if (c->expert_begin < 0 || c->expert_end > c->n_routed_experts || c->expert_begin > c->expert_end)
     return GLM4MOE_ERR_ARG;
-  if (c->weight_format == GLM4MOE_W_FP8_BLOCK128) {
+  if (is_fp8(c->weight_format)) {
     // e4m3 weights with 128x128 fp32 block scales run only on the tensor-core path
     if (c->dtype == GLM4MOE_F32 || c->hidden_size % 128 != 0 || c->moe_intermediate_size % 128 != 0)
       return GLM4MOE_ERR_UNSUPPORTED;
@@ -238,6 +251,7 @@ extern "C" int glm4moe_layer_create(const glm4moe_config_t* cfg, const void* gat
   l->w_down = w_down;
   l->s_gate_up = s_gate_up;
   l->s_down = s_down;
+  l->sf_gate_up = l->sf_down = nullptr;
   l->last_launches = 0;
   l->last_impl = GLM4MOE_IMPL_AUTO;
   l->last_fused = 0;
@@ -260,13 +274,34 @@ extern "C" int glm4moe_layer_create(const glm4moe_config_t* cfg, const void* gat
     cudaDeviceGetAttribute(&l->sm_count, cudaDevAttrMultiProcessorCount, dev);
   const int H = cfg->hidden_size, I = cfg->moe_intermediate_size;
   l->umma_ok = false;
-  const bool fp8 = cfg->weight_format == GLM4MOE_W_FP8_BLOCK128;
+  const bool fp8 = is_fp8(cfg->weight_format);
   if (fp8) {
     if (!s_gate_up || !s_down || cfg->impl == GLM4MOE_IMPL_SIMT) {
       delete l;
       return GLM4MOE_ERR_ARG;
     }
     const uint64_t n_stack = static_cast<uint64_t>(cfg->expert_end - cfg->expert_begin) + 1;
+    if (cfg->weight_format == GLM4MOE_W_FP8_BLOCK128_POW2) {
+      // packed exponent bytes of the block scales for the block-scaled MMA; refuses scales that are
+      // not powers of two (this format is a promise about the checkpoint, not a conversion)
+      const size_t nb_gu = n_stack * (2 * I / 128), nb_d = n_stack * (H / 128);
+      const int kb_gu = H / 128, kb_d = I / 128;
+      int* bad = nullptr;
+      int bad_h = 0;
+      bool ok = cudaMalloc(&l->sf_gate_up, nb_gu * ((kb_gu + 3) / 4) * 4) == cudaSuccess &&
+                cudaMalloc(&l->sf_down, nb_d * ((kb_d + 3) / 4) * 4) == cudaSuccess &&
+                cudaMalloc(&bad, 4) == cudaSuccess && cudaMemset(bad, 0, 4) == cudaSuccess &&
+                pack_weight_sf(s_gate_up, l->sf_gate_up, nb_gu, kb_gu, bad, nullptr) == GLM4MOE_OK &&
+                pack_weight_sf(s_down, l->sf_down, nb_d, kb_d, bad, nullptr) == GLM4MOE_OK &&
+                cudaMemcpy(&bad_h, bad, 4, cudaMemcpyDeviceToHost) == cudaSuccess;
+      cudaFree(bad);
+      if (!ok || bad_h) {
+        cudaFree(l->sf_gate_up);
+        cudaFree(l->sf_down);
+        delete l;
+        return ok ? GLM4MOE_ERR_ARG : GLM4MOE_ERR_DEVICE;
+      }
+    }
     const uint64_t R = static_cast<uint64_t>(cfg->max_tokens) * (cfg->num_experts_per_tok + 1);
     rc = umma_make_tensor_map_u8(&l->tm_w_gu, w_gate_up, n_stack * 2 * I, H, 128);
     if (rc == GLM4MOE_OK) rc = umma_make_tensor_map_u8(&l->tm_w_d, w_down, n_stack * H, I, 128);
@@ -314,6 +349,10 @@ extern "C" int glm4moe_layer_create(const glm4moe_config_t* cfg, const void* gat
 extern "C" int glm4moe_layer_destroy(glm4moe_layer_t* layer) {
   if (layer && layer->events_ready)
     for (int i = 0; i < 8; ++i) cudaEventDestroy(layer->ev[i]);
+  if (layer) {
+    cudaFree(layer->sf_gate_up);
+    cudaFree(layer->sf_down);
+  }
   delete layer;
   return GLM4MOE_OK;
 }
@@ -418,7 +457,8 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
     sh_hi = sh_hi_arg;
   }
   const bool use_umma = l->umma_ok;
-  const bool fp8 = c.weight_format == GLM4MOE_W_FP8_BLOCK128;
+  const bool fp8 = is_fp8(c.weight_format);
+  const int pow2 = c.weight_format == GLM4MOE_W_FP8_BLOCK128_POW2 ? 1 : 0;
   // decode "direct" mode: fused front-end + gate_up reading the input tokens in place
   // (the e4m3 tier has no un-fused direct variant)
   const bool direct = use_umma && T <= kDirectMaxTokens && H % 64 == 0 && direct_enabled() &&
@@ -441,6 +481,7 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
     if (!fp8 && (rc = umma_make_tensor_map(&tm_xdirect, x, c.dtype, static_cast<uint64_t>(T), H, tile_rows)))
       return rc;
     RouteSmallEp rep{};
+    rep.act_pow2 = pow2;
     if (ep_fast) {
       rep.epoch = reinterpret_cast<const int32_t*>(ws + L.ctl);
       for (int i = 0; i < 2; ++i) rep.slot_row_alt[i] = reinterpret_cast<int32_t*>(ws + L.slot_row_alt[i]);
@@ -503,7 +544,8 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
   } else if (fp8) {
     // gather fused with the per-token 1x128 activation quantiser
     if ((rc = quant_scatter_fp8(x, H, slot_row, T, k, sh_lo, sh_hi, ws + L.xq,
-                                reinterpret_cast<float*>(ws + L.sx), R_cap, c.dtype, stream)))
+                                reinterpret_cast<float*>(ws + L.sx), R_cap, c.dtype, pow2,
+                                pow2 ? ws + L.sx_sf : nullptr, stream)))
       return rc;
   } else if ((rc = glm4moe_gather_rows(x, row_token, offsets, x_rows, T, k, E, H, sh_lo, sh_hi, c.dtype, stream))) {
     return rc;
@@ -552,13 +594,58 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
       f.q.sact_t = reinterpret_cast<float*>(ws + L.sact);
       f.q.actq = ws + L.actq;
       f.q.scale_ld = R_cap;
+      f.q.pow2 = pow2;
     }
     if (ep_fast) f.ep = *epf;
     if ((rc = decode_fused_launch(f, stream))) return rc;
     STAGE_MARK(5);
     combine_done = true;
+  } else if (fp8_prefill && pow2 && g_fp8_mx) {
+    // scales applied by the tensor pipe (tcgen05 block-scaled MMA), one accumulator read per tile
+    UmmaFp8MxLaunch a{};
+    a.tiles = tiles;
+    a.num_tiles = num_tiles;
+    a.dtype = c.dtype;
+    a.grid = l->sm_count;
+    a.row_weight = row_weight;
+    a.n_routed_rows = T * k;
+    a.scale_ld = R_cap;
+    a.tm_w = &l->tm_w_gu;
+    a.tm_x = &l->tm_x[bi];
+    a.w_sf = l->sf_gate_up;
+    a.x_sf = reinterpret_cast<const uint32_t*>(ws + L.sx_sf);
+    a.out = nullptr;
+    a.ld_out = I;
+    a.out_q = ws + L.actq;
+    a.out_scale_t = reinterpret_cast<float*>(ws + L.sact);
+    a.out_sf = ws + L.sact_sf;
+    a.n_feat_tiles = I / 128;
+    a.n_kblocks = H / 128;
+    a.w_rows_per_expert = 2 * I;
+    a.up_row_offset = I;
+    a.gated = 1;
+    a.sched = reinterpret_cast<int32_t*>(ws + L.sched);
+    if ((rc = umma_fp8_mx_launch(a, stream))) return rc;
+    STAGE_MARK(5);
+    a.tm_w = &l->tm_w_d;
+    a.tm_x = &l->tm_act[bi];
+    a.w_sf = l->sf_down;
+    a.x_sf = reinterpret_cast<const uint32_t*>(ws + L.sact_sf);
+    a.out = y;
+    a.ld_out = H;
+    a.out_q = nullptr;
+    a.out_scale_t = nullptr;
+    a.out_sf = nullptr;
+    a.n_feat_tiles = H / 256;
+    a.n_kblocks = I / 128;
+    a.w_rows_per_expert = H;
+    a.up_row_offset = 0;
+    a.gated = 0;
+    a.sched = reinterpret_cast<int32_t*>(ws + L.sched) + 2;
+    if ((rc = umma_fp8_mx_launch(a, stream))) return rc;
   } else if (fp8_prefill) {
     UmmaFp8PrefillLaunch a{};
+    a.pow2 = pow2;
     a.tiles = tiles;
     a.num_tiles = num_tiles;
     a.dtype = c.dtype;
@@ -575,6 +662,7 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
     a.ld_out = I;
     a.out_q = ws + L.actq;
     a.out_scale_t = reinterpret_cast<float*>(ws + L.sact);
+    a.out_sf = nullptr;
     a.n_feat_tiles = I / 128;
     a.n_kblocks = H / 128;
     a.w_rows_per_expert = 2 * I;
@@ -626,7 +714,7 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
     STAGE_MARK(5);
     // re-quantise the activation rows for the down projection
     if ((rc = quant_rows_fp8(act, I, nullptr, offsets, E, T, k, I, sh_lo, sh_hi, ws + L.actq,
-                             reinterpret_cast<float*>(ws + L.sact), R_cap, c.dtype, stream)))
+                             reinterpret_cast<float*>(ws + L.sact), R_cap, c.dtype, pow2, nullptr, stream)))
       return rc;
     a.tm_w = &l->tm_w_d;
     a.tm_x = &l->tm_act[bi];

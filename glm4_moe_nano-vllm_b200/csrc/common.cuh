@@ -99,6 +99,21 @@ __device__ __forceinline__ float silu_f(float x) { return x / (1.0f + expf(-x));
 // tensor-core epilogues: fast exp + fast divide (rel. error ~1e-6, far below the 2-byte output ulp)
 __device__ __forceinline__ float silu_fast(float x) { return __fdividef(x, 1.0f + __expf(-x)); }
 
+// FP8 activation scales of one 1x128 group.  Default tier: scale = amax / 448 (fp32).  Power-of-two tier
+// (GLM4MOE_W_FP8_BLOCK128_POW2): the smallest power of two >= amax / 448, i.e. a UE8M0 exponent byte, the
+// only scale type the tcgen05 block-scaled MMA reads (umma_fp8_mx.cu); v / scale is then exact.
+__device__ __forceinline__ float pow2_scale(float amax, uint32_t* ebyte) {
+  const uint32_t b = __float_as_uint(__fdiv_rn(fmaxf(amax, 1e-10f), 448.0f));
+  const uint32_t e = (b >> 23) + ((b & 0x7fffffu) != 0u ? 1u : 0u);   // biased exponent of the ceiling
+  *ebyte = e;
+  return __uint_as_float(e << 23);
+}
+__device__ __forceinline__ float pow2_inverse(uint32_t ebyte) { return __uint_as_float((254u - ebyte) << 23); }
+__device__ __forceinline__ float act_scale(float amax, int pow2) {
+  uint32_t e;
+  return pow2 ? pow2_scale(amax, &e) : __fdiv_rn(fmaxf(amax, 1e-10f), 448.0f);
+}
+
 // Programmatic dependent launch.  Every kernel on the forward path runs
 //   [prologue that touches nothing a predecessor writes] -> pdl_wait() -> pdl_launch() -> body
 // so a kernel only starts once its predecessor passed its own wait: everything two or more

@@ -586,7 +586,7 @@ __global__ void __launch_bounds__(FusedCfg<BN, FP8>::kThreads, 1) decode_fused_k
               if (m) {
                 const int row = it.row_start + __ffs(m) - 1;
                 const float amax = fmaxf(fmaxf(s_amax[col], s_amax[32 + col]), fmaxf(s_amax[64 + col], s_amax[96 + col]));
-                const float scale = __fdiv_rn(fmaxf(amax, 1e-10f), 448.0f);
+                const float scale = act_scale(amax, q.pow2);
                 act[static_cast<size_t>(row) * I + feat] = Dt<T>::from_f(acc_g[c]);
                 q.actq[static_cast<size_t>(row) * I + feat] = static_cast<unsigned char>(
                     __nv_cvt_float_to_fp8(__fdiv_rn(acc_g[c], scale), __NV_SATFINITE, __NV_E4M3));

@@ -46,6 +46,7 @@ struct EpFastSignal {
 struct RouteSmallEp {
   const int32_t* epoch;             // own ctl[0]; nullptr = off
   int32_t* slot_row_alt[2];
+  int act_pow2;                     // e4m3 tier: token scales rounded up to a power of two (not an EP matter; rides here)
 };
 int route_small_ep(const void* h, const void* gate_w, const float* bias, void* logits, int T, int H, int E, int k,
                    float scale, int dtype, int e_lo, int e_hi, int tile_rows, int shared_lo, int shared_hi,

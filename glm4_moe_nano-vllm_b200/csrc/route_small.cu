@@ -58,7 +58,7 @@ __global__ void __launch_bounds__(256) route_small_kernel(
         for (int i = 0; i < 8; ++i) amax = fmaxf(amax, fabsf(v[i]));
 #pragma unroll
         for (int o = 8; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
-        const float sc = __fdiv_rn(fmaxf(amax, 1e-10f), 448.0f);
+        const float sc = act_scale(amax, ep.act_pow2);
         uint32_t lo = 0, hi = 0;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {

@@ -281,7 +281,7 @@ template <typename T>
 __global__ void __launch_bounds__(256) quant_rows_fp8_kernel(
     const T* __restrict__ src, int src_ld, const int32_t* __restrict__ row_token /*nullable*/,
     const int32_t* __restrict__ expert_offsets, int E, int T_tokens, int k, int K, int sh_lo, int sh_hi,
-    uint8_t* __restrict__ dst, float* __restrict__ scale_t, int scale_ld) {
+    uint8_t* __restrict__ dst, float* __restrict__ scale_t, int scale_ld, int pow2, uint8_t* __restrict__ sf) {
   pdl_wait();
   pdl_launch();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -315,7 +315,9 @@ __global__ void __launch_bounds__(256) quant_rows_fp8_kernel(
     // IEEE divisions, exactly the published formula (scale = amax / 448, q = rn_e4m3(v / scale)):
     // with 8-bit-mantissa inputs v / scale lands on e4m3 rounding ties often enough that a
     // reciprocal-multiply variant re-rounds ~0.3 % of the elements differently
-    const float scale = __fdiv_rn(fmaxf(amax, 1e-10f), 448.0f);
+    // (power-of-two tier: the next power of two at or above it, and the division is exact)
+    uint32_t ebyte = 0;
+    const float scale = pow2 ? pow2_scale(amax, &ebyte) : __fdiv_rn(fmaxf(amax, 1e-10f), 448.0f);
     uint32_t lo = 0, hi = 0;
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
@@ -324,7 +326,12 @@ __global__ void __launch_bounds__(256) quant_rows_fp8_kernel(
     }
     if (ok) {
       *reinterpret_cast<uint2*>(d + c) = make_uint2(lo, hi);
-      if ((lane & 15) == 0) scale_t[static_cast<size_t>(c / 128) * scale_ld + row] = scale;
+      if ((lane & 15) == 0) {
+        const int g = c / 128;
+        scale_t[static_cast<size_t>(g) * scale_ld + row] = scale;
+        // packed UE8M0 copy for the block-scaled MMA: [g / 4, scale_ld] words, byte g % 4
+        if (sf) sf[(static_cast<size_t>(g >> 2) * scale_ld + row) * 4 + (g & 3)] = static_cast<uint8_t>(ebyte);
+      }
     }
   }
 }
@@ -336,7 +343,8 @@ __global__ void __launch_bounds__(256) quant_rows_fp8_kernel(
 template <typename T>
 __global__ void __launch_bounds__(256) quant_scatter_fp8_kernel(
     const T* __restrict__ x, int K, const int32_t* __restrict__ slot_row, int T_tokens, int k, int sh_lo,
-    int sh_hi, uint8_t* __restrict__ dst, float* __restrict__ scale_t, int scale_ld) {
+    int sh_hi, uint8_t* __restrict__ dst, float* __restrict__ scale_t, int scale_ld, int pow2,
+    uint8_t* __restrict__ sf) {
   pdl_wait();
   pdl_launch();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -359,18 +367,23 @@ __global__ void __launch_bounds__(256) quant_scatter_fp8_kernel(
     for (int q = 0; q < 8; ++q) amax = fmaxf(amax, fabsf(v[q]));
 #pragma unroll
     for (int o = 8; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
-    const float scale = __fdiv_rn(fmaxf(amax, 1e-10f), 448.0f);
+    uint32_t ebyte = 0;
+    const float scale = pow2 ? pow2_scale(amax, &ebyte) : __fdiv_rn(fmaxf(amax, 1e-10f), 448.0f);
     uint32_t lo = 0, hi = 0;
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       lo |= static_cast<uint32_t>(__nv_cvt_float_to_fp8(__fdiv_rn(v[q], scale), __NV_SATFINITE, __NV_E4M3)) << (8 * q);
       hi |= static_cast<uint32_t>(__nv_cvt_float_to_fp8(__fdiv_rn(v[4 + q], scale), __NV_SATFINITE, __NV_E4M3)) << (8 * q);
     }
+    const int g = c / 128;
     for (int j = 0; j <= k; ++j) {
       const int row = __shfl_sync(0xffffffffu, my_row, j);
       if (row >= 0 && ok) {
         *reinterpret_cast<uint2*>(dst + static_cast<size_t>(row) * K + c) = make_uint2(lo, hi);
-        if ((lane & 15) == 0) scale_t[static_cast<size_t>(c / 128) * scale_ld + row] = scale;
+        if ((lane & 15) == 0) {
+          scale_t[static_cast<size_t>(g) * scale_ld + row] = scale;
+          if (sf) sf[(static_cast<size_t>(g >> 2) * scale_ld + row) * 4 + (g & 3)] = static_cast<uint8_t>(ebyte);
+        }
       }
     }
   }
@@ -440,7 +453,7 @@ int umma_fp8_launch(const UmmaFp8Launch& a, void* stream) {
 
 int quant_rows_fp8(const void* src, int src_ld, const int32_t* row_token, const int32_t* expert_offsets, int E,
                    int T, int k, int K, int sh_lo, int sh_hi, void* dst, float* scale_t, int scale_ld, int dtype,
-                   void* stream) {
+                   int pow2, void* sf, void* stream) {
   if (K % 256 != 0 && K % 128 != 0) return GLM4MOE_ERR_UNSUPPORTED;
   if (K % 128 != 0) return GLM4MOE_ERR_UNSUPPORTED;
   const int rows = T * k + sh_hi;
@@ -449,11 +462,13 @@ int quant_rows_fp8(const void* src, int src_ld, const int32_t* row_token, const 
   if (dtype == GLM4MOE_BF16) {
     GLM4MOE_CUDA_CHECK(launch_pdl(quant_rows_fp8_kernel<__nv_bfloat16>, dim3((rows + 7) / 8), dim3(256), 0, st,
                                   static_cast<const __nv_bfloat16*>(src), src_ld, row_token, expert_offsets, E, T, k,
-                                  K, sh_lo, sh_hi, static_cast<uint8_t*>(dst), scale_t, scale_ld));
+                                  K, sh_lo, sh_hi, static_cast<uint8_t*>(dst), scale_t, scale_ld, pow2,
+                                  static_cast<uint8_t*>(sf)));
   } else if (dtype == GLM4MOE_F16) {
     GLM4MOE_CUDA_CHECK(launch_pdl(quant_rows_fp8_kernel<__half>, dim3((rows + 7) / 8), dim3(256), 0, st,
                                   static_cast<const __half*>(src), src_ld, row_token, expert_offsets, E, T, k, K,
-                                  sh_lo, sh_hi, static_cast<uint8_t*>(dst), scale_t, scale_ld));
+                                  sh_lo, sh_hi, static_cast<uint8_t*>(dst), scale_t, scale_ld, pow2,
+                                  static_cast<uint8_t*>(sf)));
   } else {
     return GLM4MOE_ERR_UNSUPPORTED;
   }
@@ -461,18 +476,18 @@ int quant_rows_fp8(const void* src, int src_ld, const int32_t* row_token, const 
 }
 
 int quant_scatter_fp8(const void* x, int K, const int32_t* slot_row, int T, int k, int sh_lo, int sh_hi, void* dst,
-                      float* scale_t, int scale_ld, int dtype, void* stream) {
+                      float* scale_t, int scale_ld, int dtype, int pow2, void* sf, void* stream) {
   if (K % 128 != 0 || k >= 32) return GLM4MOE_ERR_UNSUPPORTED;
   if (T <= 0) return GLM4MOE_OK;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (dtype == GLM4MOE_BF16) {
     GLM4MOE_CUDA_CHECK(launch_pdl(quant_scatter_fp8_kernel<__nv_bfloat16>, dim3((T + 7) / 8), dim3(256), 0, st,
                                   static_cast<const __nv_bfloat16*>(x), K, slot_row, T, k, sh_lo, sh_hi,
-                                  static_cast<uint8_t*>(dst), scale_t, scale_ld));
+                                  static_cast<uint8_t*>(dst), scale_t, scale_ld, pow2, static_cast<uint8_t*>(sf)));
   } else if (dtype == GLM4MOE_F16) {
     GLM4MOE_CUDA_CHECK(launch_pdl(quant_scatter_fp8_kernel<__half>, dim3((T + 7) / 8), dim3(256), 0, st,
                                   static_cast<const __half*>(x), K, slot_row, T, k, sh_lo, sh_hi,
-                                  static_cast<uint8_t*>(dst), scale_t, scale_ld));
+                                  static_cast<uint8_t*>(dst), scale_t, scale_ld, pow2, static_cast<uint8_t*>(sf)));
   } else {
     return GLM4MOE_ERR_UNSUPPORTED;
   }

@@ -80,7 +80,8 @@ __global__ void __launch_bounds__(kPThreads, 1) umma_fp8_prefill_kernel(
     float* __restrict__ out_scale_t,            // gate_up: their scales [I/128, scale_ld]
     const float* __restrict__ row_weight, int n_routed_rows,
     int n_feat_tiles,                           // gate_up: I/128, down: H/256
-    int n_kblocks, int w_rows_per_expert, int up_row_offset, int32_t* __restrict__ sched) {
+    int n_kblocks, int w_rows_per_expert, int up_row_offset, int32_t* __restrict__ sched,
+    int pow2, uint8_t* __restrict__ out_sf) {   // gate_up: power-of-two scales (+ packed UE8M0 copy, nullable)
   extern __shared__ unsigned char smem_dyn[];
   unsigned char* smem = reinterpret_cast<unsigned char*>(
       (reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~static_cast<uintptr_t>(1023));
@@ -306,7 +307,8 @@ __global__ void __launch_bounds__(kPThreads, 1) umma_fp8_prefill_kernel(
         ax[cg * kPM + r] = amax;
         epi_bar_sync();
         amax = fmaxf(fmaxf(ax[r], ax[kPM + r]), fmaxf(ax[2 * kPM + r], ax[3 * kPM + r]));
-        const float sc = __fdiv_rn(fmaxf(amax, 1e-10f), 448.0f);
+        uint32_t ebyte = 0;
+        const float sc = pow2 ? pow2_scale(amax, &ebyte) : __fdiv_rn(fmaxf(amax, 1e-10f), 448.0f);
         if (row_ok) {
           uint32_t p[8];
 #pragma unroll
@@ -316,7 +318,10 @@ __global__ void __launch_bounds__(kPThreads, 1) umma_fp8_prefill_kernel(
           uint4* dst = reinterpret_cast<uint4*>(out_q + static_cast<size_t>(row) * ld_out + tile.f * 128 + 32 * cg);
           dst[0] = make_uint4(p[0], p[1], p[2], p[3]);
           dst[1] = make_uint4(p[4], p[5], p[6], p[7]);
-          if (cg == 0) out_scale_t[static_cast<size_t>(tile.f) * scale_ld + row] = sc;
+          if (cg == 0) {
+            out_scale_t[static_cast<size_t>(tile.f) * scale_ld + row] = sc;
+            if (out_sf) out_sf[(static_cast<size_t>(tile.f >> 2) * scale_ld + row) * 4 + (tile.f & 3)] = static_cast<uint8_t>(ebyte);
+          }
         }
       } else {
         // y = acc * routing weight (mlp.py:52, moe.py:149); shared-expert rows carry weight 1
@@ -352,7 +357,8 @@ static int launch_prefill_one(const UmmaFp8PrefillLaunch& a, cudaStream_t st) {
                                 a.w_scale, a.x_scale_t, a.scale_ld, reinterpret_cast<const int4*>(a.tiles),
                                 a.num_tiles, static_cast<T*>(a.out), a.ld_out, static_cast<uint8_t*>(a.out_q),
                                 a.out_scale_t, a.row_weight, a.n_routed_rows, a.n_feat_tiles, a.n_kblocks,
-                                a.w_rows_per_expert, a.up_row_offset, a.sched));
+                                a.w_rows_per_expert, a.up_row_offset, a.sched, a.pow2,
+                                static_cast<uint8_t*>(a.out_sf)));
   return GLM4MOE_OK;
 }
 

@@ -62,6 +62,7 @@ struct Fp8Args {
   float* sact_t;             // [I/128, scale_ld]: scales of the quantised activation rows
   unsigned char* actq;       // [R, I] e4m3 activation rows
   int scale_ld;
+  int pow2;                  // activation scales rounded up to a power of two (GLM4MOE_W_FP8_BLOCK128_POW2)
 };
 
 struct DecodeFusedLaunch {
@@ -129,10 +130,11 @@ int umma_fp8_launch(const UmmaFp8Launch& args, void* stream);
 // rows -> e4m3 + per-128 fp32 scales (scale_t is k-block major); row_token != nullptr gathers tokens
 int quant_rows_fp8(const void* src, int src_ld, const int32_t* row_token, const int32_t* expert_offsets, int E,
                    int T, int k, int K, int sh_lo, int sh_hi, void* dst, float* scale_t, int scale_ld, int dtype,
-                   void* stream);
+                   int pow2, void* sf, void* stream);
 // layer input -> e4m3 rows, each token quantised once and written to its k expert rows + shared row
 int quant_scatter_fp8(const void* x, int K, const int32_t* slot_row, int T, int k, int sh_lo, int sh_hi, void* dst,
-                      float* scale_t, int scale_ld, int dtype, void* stream);
+                      float* scale_t, int scale_ld, int dtype, int pow2, void* sf, void* stream);
+// pow2 = 1: scales rounded up to a power of two; sf (nullable): packed UE8M0 copy [ceil(K/512), scale_ld] x 4 bytes
 
 // ---- FP8 tier, prefill geometry (umma_fp8_prefill.cu): token rows = MMA M (128), weight rows = N (256) ----
 struct UmmaFp8PrefillLaunch {
@@ -157,8 +159,40 @@ struct UmmaFp8PrefillLaunch {
   int dtype;
   int grid;
   int32_t* sched;
+  int pow2;                  // gate_up: power-of-two activation scales
+  void* out_sf;              // gate_up, nullable: packed UE8M0 copy of out_scale_t
 };
 bool umma_fp8_prefill_shape_ok(int H, int I);
 int umma_fp8_prefill_launch(const UmmaFp8PrefillLaunch& args, void* stream);
+
+// ---- FP8 tier, prefill geometry with hardware block scaling (umma_fp8_mx.cu) ----
+struct UmmaFp8MxLaunch {
+  const void* tm_w;          // e4m3 weight stack (uint8), box {128 bytes, 128 rows}
+  const void* tm_x;          // e4m3 activation rows, box {128 bytes, 128 rows}
+  const uint32_t* w_sf;      // [n_stack, w_rows_per_expert/128, ceil(K/512)] packed UE8M0 block scales
+  const uint32_t* x_sf;      // [ceil(K/512), scale_ld] packed UE8M0 activation scales
+  int scale_ld;
+  const int32_t* tiles;      // 128-row tiles
+  const int32_t* num_tiles;
+  void* out;                 // down: y rows [R, H] model dtype
+  int ld_out;
+  void* out_q;               // gate_up: e4m3 activation rows [R, I]
+  float* out_scale_t;        // gate_up: [I/128, scale_ld] fp32 copy of the scales (decode-size kernels read these)
+  void* out_sf;              // gate_up: [ceil(I/512), scale_ld] packed UE8M0
+  const float* row_weight;
+  int n_routed_rows;
+  int n_feat_tiles;          // gate_up: I/128; down: H/256
+  int n_kblocks;             // K / 128
+  int w_rows_per_expert;
+  int up_row_offset;
+  int gated;
+  int dtype;
+  int grid;
+  int32_t* sched;
+};
+int umma_fp8_mx_launch(const UmmaFp8MxLaunch& args, void* stream);
+// fp32 128x128 block scales [n_blocks, nkb] -> packed UE8M0 words [n_blocks, ceil(nkb/4)]; *bad (device int)
+// is set when a scale is not a power of two in UE8M0 range
+int pack_weight_sf(const float* scales, uint32_t* out, size_t n_blocks, int nkb, int* bad, void* stream);
 
 }  // namespace glm4moe

@@ -12,14 +12,29 @@ E4M3_MAX = 448.0
 BLOCK = 128
 
 
-def quantize_block128(w: torch.Tensor):
-    """w [..., R, C] (R, C multiples of 128) -> (q float8_e4m3fn [..., R, C], scale fp32 [..., R/128, C/128])."""
+def pow2_ceil(s: torch.Tensor) -> torch.Tensor:
+    """Smallest power of two >= s (fp32, s > 0): the UE8M0 rounding of a scale."""
+    m, e = torch.frexp(s.float())                       # s = m * 2^e, m in [0.5, 1)
+    return torch.ldexp(torch.ones_like(m), torch.where(m == 0.5, e - 1, e))
+
+
+def is_pow2(s: torch.Tensor) -> bool:
+    """Every scale a normal power of two (what GLM4MOE_W_FP8_BLOCK128_POW2 requires)."""
+    s = s.float()
+    return bool(((torch.frexp(s)[0] == 0.5) & (s >= 2.0 ** -126) & (s <= 2.0 ** 127)).all())
+
+
+def quantize_block128(w: torch.Tensor, pow2_scales: bool = False):
+    """w [..., R, C] (R, C multiples of 128) -> (q float8_e4m3fn [..., R, C], scale fp32 [..., R/128, C/128]).
+    `pow2_scales`: scales rounded up to a power of two (UE8M0 checkpoints; the hardware block-scaled MMA)."""
     *lead, R, C = w.shape
     if R % BLOCK or C % BLOCK:
         raise ValueError(f"block-128 FP8 needs dimensions divisible by 128, got {R}x{C}")
     blocks = w.float().reshape(*lead, R // BLOCK, BLOCK, C // BLOCK, BLOCK)
     amax = blocks.abs().amax(dim=(-3, -1), keepdim=True).clamp_min(1e-10)
     scale = amax / E4M3_MAX
+    if pow2_scales:
+        scale = pow2_ceil(scale)
     q = (blocks / scale).clamp(-E4M3_MAX, E4M3_MAX).to(torch.float8_e4m3fn)
     return q.reshape(*lead, R, C), scale.reshape(*lead, R // BLOCK, C // BLOCK).contiguous()
 
@@ -30,16 +45,18 @@ def dequantize_block128(q: torch.Tensor, scale: torch.Tensor, dtype=torch.float3
     return (blocks * scale.reshape(*lead, R // BLOCK, 1, C // BLOCK, 1)).reshape(*lead, R, C).to(dtype)
 
 
-def quantize_rows_1x128(x: torch.Tensor):
+def quantize_rows_1x128(x: torch.Tensor, pow2_scales: bool = False):
     """Reference for the device activation quantiser: per-token groups of 128 along the last dim."""
     *lead, K = x.shape
     g = x.float().reshape(*lead, K // BLOCK, BLOCK)
     scale = g.abs().amax(-1, keepdim=True).clamp_min(1e-10) / E4M3_MAX
+    if pow2_scales:
+        scale = pow2_ceil(scale)
     q = (g / scale).clamp(-E4M3_MAX, E4M3_MAX).to(torch.float8_e4m3fn)
     return q.reshape(*lead, K), scale.squeeze(-1)
 
 
-def convert_checkpoint(src: str, dst: str, prefixes=None) -> dict:
+def convert_checkpoint(src: str, dst: str, prefixes=None, pow2_scales: bool = False) -> dict:
     """Offline conversion of the sparse-block expert weights of an HF-layout checkpoint to the block
     FP8 format `Glm4MoeMoE.load_weights` reads.
 
@@ -68,7 +85,7 @@ def convert_checkpoint(src: str, dst: str, prefixes=None) -> dict:
                 t = f.get_tensor(key)
                 wanted = prefixes is None or any(key.startswith(p + ".") for p in prefixes)
                 if wanted and pat.search(key) and t.dtype != torch.float8_e4m3fn:
-                    q, s = quantize_block128(t.contiguous())
+                    q, s = quantize_block128(t.contiguous(), pow2_scales)
                     out[key] = q
                     out[key[:-len("weight")] + "weight_scale_inv"] = s
                     stats["converted"] += 1
@@ -85,5 +102,6 @@ if __name__ == "__main__":
     ap.add_argument("src")
     ap.add_argument("dst")
     ap.add_argument("--prefix", action="append", help="only convert keys under this prefix (repeatable)")
+    ap.add_argument("--pow2-scales", action="store_true", help="power-of-two (UE8M0) block scales")
     a = ap.parse_args()
-    print(convert_checkpoint(a.src, a.dst, a.prefix))
+    print(convert_checkpoint(a.src, a.dst, a.prefix, a.pow2_scales))

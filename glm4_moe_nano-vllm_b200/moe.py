@@ -191,7 +191,7 @@ class Glm4MoeMoE(nn.Module):
         n_local = self.expert_end - self.expert_begin
         # stacked storage, created under the process-wide default dtype/device like the
         # reference's parameters (model_runner.py:29-31)
-        fp8_only = type(self).default_weight_format == "fp8"
+        fp8_only = type(self).default_weight_format in ("fp8", "fp8_pow2")
         if fp8_only:
             if I % 128 or H % 128:
                 raise ValueError(f"block-128 FP8 needs dimensions divisible by 128, got I={I}, H={H}")
@@ -207,6 +207,9 @@ class Glm4MoeMoE(nn.Module):
         self.gate = GlmMoeSelectTopk(config)
         self.shared_experts = Glm4MoeMLP(gu[n_local], dn[n_local], config.hidden_act)
         self.weight_format = "native"
+        # FP8 tier with power-of-two (UE8M0) block scales: activations get power-of-two scales too and the
+        # prefill GEMMs use the hardware block-scaled MMA (csrc/umma_fp8_mx.cu)
+        self.fp8_pow2_scales = type(self).default_weight_format == "fp8_pow2"
         self._wq_gate_up = self._wq_down = self._s_gate_up = self._s_down = None
         if fp8_only:
             f8 = torch.float8_e4m3fn
@@ -273,7 +276,9 @@ class Glm4MoeMoE(nn.Module):
 
     def _lib_config(self, max_tokens: int) -> _lib.Config:
         c = self.config
-        fmt = _lib.W_FP8_BLOCK128 if self.weight_format == "fp8" else _lib.W_NATIVE
+        fmt = _lib.W_NATIVE
+        if self.weight_format == "fp8":
+            fmt = _lib.W_FP8_BLOCK128_POW2 if self.fp8_pow2_scales else _lib.W_FP8_BLOCK128
         return _lib.Config(c.hidden_size, c.n_routed_experts, c.num_experts_per_tok, c.moe_intermediate_size,
                            float(c.routed_scaling_factor), _lib.DTYPE_CODE[self.gate.weight.dtype], fmt,
                            max_tokens, self.expert_begin, self.expert_end, int(self.with_shared),
@@ -335,14 +340,17 @@ class Glm4MoeMoE(nn.Module):
         self._handle = handle
         self._cfg = cfg
 
-    def quantize_fp8(self, drop_native: bool = False):
+    def quantize_fp8(self, drop_native: bool = False, pow2_scales: bool = False):
         """Convert the expert stacks to e4m3 + 128x128 fp32 block scales (fp8.py) and switch the
-        block to the FP8 tensor-core path.  Router weights and activations keep the model dtype."""
+        block to the FP8 tensor-core path.  Router weights and activations keep the model dtype.
+        `pow2_scales`: power-of-two (UE8M0) scales for weights and activations, which the prefill kernel
+        applies in hardware (tcgen05 block-scaled MMA)."""
         from . import fp8
         self._destroy_handle()
-        self._wq_gate_up, self._s_gate_up = fp8.quantize_block128(self._w_gate_up)
-        self._wq_down, self._s_down = fp8.quantize_block128(self._w_down)
+        self._wq_gate_up, self._s_gate_up = fp8.quantize_block128(self._w_gate_up, pow2_scales)
+        self._wq_down, self._s_down = fp8.quantize_block128(self._w_down, pow2_scales)
         self.weight_format = "fp8"
+        self.fp8_pow2_scales = bool(pow2_scales)
         if drop_native:
             dev, dt = self._w_gate_up.device, self._w_gate_up.dtype
             self._w_gate_up = torch.empty((0,), device=dev, dtype=dt)
@@ -504,8 +512,11 @@ class Glm4MoeMoE(nn.Module):
                 assert (slot, proj, is_fp8) in seen, f"{proj}.weight missing for expert slot {slot}"   # mlp.py:113-115
                 assert not is_fp8 or (slot, proj) in seen_scale, f"{proj}.weight_scale_inv missing for expert slot {slot}"
         if is_fp8:
+            from . import fp8
             self._destroy_handle()
             self.weight_format = "fp8"
+            # a checkpoint whose block scales are all powers of two (UE8M0) takes the hardware-scaled path
+            self.fp8_pow2_scales = fp8.is_pow2(self._s_gate_up) and fp8.is_pow2(self._s_down)
 
     # ---- helpers used by tests / bench -------------------------------------------------------
     def init_random_(self, seed: int, std: float = 0.02, bias_high: float = 0.1, chunk: int = 16):
@@ -528,10 +539,10 @@ class Glm4MoeMoE(nn.Module):
                 m = min(chunk, n - s0)
                 gu, dn = draw((m, 2 * I, H)), draw((m, H, I))
                 if self.weight_format == "fp8":
-                    q, sc = fp8.quantize_block128(gu)
+                    q, sc = fp8.quantize_block128(gu, self.fp8_pow2_scales)
                     self._wq_gate_up[s0:s0 + m].view(torch.uint8).copy_(q.view(torch.uint8))
                     self._s_gate_up[s0:s0 + m].copy_(sc)
-                    q, sc = fp8.quantize_block128(dn)
+                    q, sc = fp8.quantize_block128(dn, self.fp8_pow2_scales)
                     self._wq_down[s0:s0 + m].view(torch.uint8).copy_(q.view(torch.uint8))
                     self._s_down[s0:s0 + m].copy_(sc)
                 else:

@@ -27,7 +27,11 @@ extern "C" {
 #define GLM4MOE_ABI_VERSION 1
 
 enum { GLM4MOE_F32 = 0, GLM4MOE_F16 = 1, GLM4MOE_BF16 = 2 };          /* model dtype */
-enum { GLM4MOE_W_NATIVE = 0, GLM4MOE_W_FP8_BLOCK128 = 1 };            /* expert weight format */
+/* expert weight format.  FP8_BLOCK128: e4m3 bytes + one fp32 scale per 128 x 128 block, activations e4m3 with
+ * scale = amax / 448 per token per 128 columns.  FP8_BLOCK128_POW2: the same layout, but every weight block scale
+ * must be a power of two (checked at layer_create) and activation scales are rounded UP to a power of two (UE8M0):
+ * the scale format the tcgen05 block-scaled MMA applies in hardware, used by the prefill kernel (umma_fp8_mx.cu). */
+enum { GLM4MOE_W_NATIVE = 0, GLM4MOE_W_FP8_BLOCK128 = 1, GLM4MOE_W_FP8_BLOCK128_POW2 = 2 };
 enum { GLM4MOE_IMPL_AUTO = 0, GLM4MOE_IMPL_SIMT = 1, GLM4MOE_IMPL_UMMA = 2 };
 
 #define GLM4MOE_OK 0
@@ -71,7 +75,9 @@ enum { GLM4MOE_KNOB_DIRECT = 0, GLM4MOE_KNOB_FUSED = 1, GLM4MOE_KNOB_FP8_PREFILL
        GLM4MOE_KNOB_BK32 = 4, GLM4MOE_KNOB_DOWN2 = 5, GLM4MOE_KNOB_FORCE_TILE_ROWS = 6,
        GLM4MOE_KNOB_EP_FAST = 7 /* 1 (default): decode-size expert-parallel calls use ONE cross-rank rendezvous (rows in
                                    epoch-parity buffers, ready flags from the expert kernel, no done round); must be
-                                   the same on every rank (a mismatch traps with an error code instead of hanging) */ };
+                                   the same on every rank (a mismatch traps with an error code instead of hanging) */,
+       GLM4MOE_KNOB_FP8_MX = 8 /* 1 (default): FP8_BLOCK128_POW2 layers run the prefill GEMMs with hardware block
+                                  scaling (umma_fp8_mx.cu); 0 = the software-scaled kernel on the same operands */ };
 int glm4moe_debug_set(int knob, int value);
 const char* glm4moe_error_string(int code);
 

@@ -134,25 +134,32 @@ def moe_forward_fp32(h: torch.Tensor, weights: dict, k: int, scale: float, routi
 # the caller), activations e4m3 with one fp32 scale per token per 128 columns, scale = amax/448,
 # products exact, fp32 accumulation; the SiLU*mul intermediate is rounded to the model dtype
 # (it is stored in it) before it is re-quantised for the down projection.
+# `pow2_scales` (UE8M0 variant of the same published format, the scale type the Blackwell
+# block-scaled MMA reads): every activation scale is rounded UP to a power of two; weight block
+# scales are powers of two already when they reach the oracle (dequantised by the caller).
 # --------------------------------------------------------------------------------------
-def fp8_act_roundtrip(a: torch.Tensor) -> torch.Tensor:
+def fp8_act_roundtrip(a: torch.Tensor, pow2_scales: bool = False) -> torch.Tensor:
     """a [n, K] -> fp32 values of its per-token 1x128 e4m3 quantisation."""
     n, K = a.shape
     g = a.float().reshape(n, K // 128, 128)
     scale = g.abs().amax(-1, keepdim=True).clamp_min(1e-10) / 448.0
+    if pow2_scales:
+        m, e = torch.frexp(scale)                       # scale = m * 2^e, m in [0.5, 1)
+        scale = torch.ldexp(torch.ones_like(m), torch.where(m == 0.5, e - 1, e))
     q = (g / scale).clamp(-448.0, 448.0).to(torch.float8_e4m3fn).float()
     return (q * scale).reshape(n, K)
 
 
 def expert_mlp_fp8(x: torch.Tensor, w_gate_up_deq: torch.Tensor, w_down_deq: torch.Tensor,
-                   model_dtype: torch.dtype) -> torch.Tensor:
-    gate_up = F.linear(fp8_act_roundtrip(x), w_gate_up_deq.float())
+                   model_dtype: torch.dtype, pow2_scales: bool = False) -> torch.Tensor:
+    gate_up = F.linear(fp8_act_roundtrip(x, pow2_scales), w_gate_up_deq.float())
     g, u = gate_up.chunk(2, -1)
     act = (F.silu(g) * u).to(model_dtype)
-    return F.linear(fp8_act_roundtrip(act), w_down_deq.float())
+    return F.linear(fp8_act_roundtrip(act, pow2_scales), w_down_deq.float())
 
 
-def moe_forward_fp8(h: torch.Tensor, deq_weights: dict, routing, model_dtype: torch.dtype) -> torch.Tensor:
+def moe_forward_fp8(h: torch.Tensor, deq_weights: dict, routing, model_dtype: torch.dtype,
+                    pow2_scales: bool = False) -> torch.Tensor:
     """fp32 evaluation of the quant-tier algorithm with forced routing (idx, w)."""
     w_gu, w_d = deq_weights["w_gate_up"], deq_weights["w_down"]
     E = w_gu.shape[0] - 1
@@ -164,9 +171,9 @@ def moe_forward_fp8(h: torch.Tensor, deq_weights: dict, routing, model_dtype: to
         if not mask.any():
             continue
         tok, pos = torch.where(mask)
-        y = expert_mlp_fp8(h2[tok], w_gu[e], w_d[e], model_dtype)
+        y = expert_mlp_fp8(h2[tok], w_gu[e], w_d[e], model_dtype, pow2_scales)
         acc.index_add_(0, tok, y * w[tok, pos].float().unsqueeze(-1))
-    return acc + expert_mlp_fp8(h2, w_gu[E], w_d[E], model_dtype)
+    return acc + expert_mlp_fp8(h2, w_gu[E], w_d[E], model_dtype, pow2_scales)
 
 
 def count_experts_hit(idx: torch.Tensor) -> int:

@@ -37,7 +37,7 @@ def main():
     ap.add_argument("--preset", default="small", choices=["small", "air"])
     ap.add_argument("--layers", type=int, default=4)
     ap.add_argument("--block", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--weights", default="bf16", choices=["bf16", "fp8"])
+    ap.add_argument("--weights", default="bf16", choices=["bf16", "fp8", "fp8_pow2"])
     ap.add_argument("--eager", action="store_true", help="enforce_eager=True (no CUDA-graph decode)")
     ap.add_argument("--seqs", type=int, default=8)
     ap.add_argument("--prompt-len", type=int, default=24)
@@ -49,7 +49,7 @@ def main():
     ap.add_argument("--model-dir", default="")
     args = ap.parse_args()
 
-    nanovllm = S.install(sparse_block=args.block, weight_format="fp8" if args.weights == "fp8" else "native")
+    nanovllm = S.install(sparse_block=args.block, weight_format=args.weights if args.weights != "bf16" else "native")
     geom = dict(S.AIR_MODEL if args.preset == "air" else SMALL)
     d = args.model_dir or tempfile.mkdtemp(prefix="glm4moe_model_")
     S.make_model_dir(d, num_hidden_layers=args.layers, max_position_embeddings=max(args.max_model_len, 512), **geom)

@@ -182,6 +182,43 @@ def test_offline_fp8_conversion_round_trip(tmp_path):
     assert torch.equal(moe._s_gate_up, s_gu)
     assert torch.equal(moe._wq_down.view(torch.uint8), q_d.view(torch.uint8))
     assert torch.equal(moe._s_down, s_d)
+    assert not moe.fp8_pow2_scales
+    # power-of-two (UE8M0) block scales: detected at load, selects GLM4MOE_W_FP8_BLOCK128_POW2
+    fp8.convert_checkpoint(str(tmp_path / "src"), str(tmp_path / "dst2"), pow2_scales=True)
+    moe2 = glm4_moe_b200.Glm4MoeMoE(_cfg(shape))
+    moe2.load_weights(str(tmp_path / "dst2"), p)
+    assert moe2.weight_format == "fp8" and moe2.fp8_pow2_scales
+    assert moe2._lib_config(64).weight_format == _lib.W_FP8_BLOCK128_POW2
+    q2, s2 = fp8.quantize_block128(w["w_down"], pow2_scales=True)
+    assert torch.equal(moe2._s_down, s2) and fp8.is_pow2(s2)
+    assert bool(((s2 >= s_d) & (s2 < 2 * s_d)).all())            # the smallest power of two >= amax/448
+    assert torch.equal(moe2._wq_down.view(torch.uint8), q2.view(torch.uint8))
+
+
+def test_pow2_scale_rounding_and_workspace():
+    """UE8M0 rounding used by the quant tier's power-of-two variant (fp8.py, oracle, common.cuh pow2_scale):
+    exact powers stay, everything else goes up; the oracle's activation round trip is exact on values that
+    are e4m3-representable under such a scale; the POW2 layout carries the packed scale words on top."""
+    from glm4_moe_b200 import fp8
+    from oracle import moe_oracle as O
+    s = torch.tensor([1.0, 0.75, 0.5, 0.500001, 3e-5, 2.0 ** -20, 1.9999], dtype=torch.float32)
+    want = torch.tensor([1.0, 1.0, 0.5, 1.0, 2.0 ** -15, 2.0 ** -20, 2.0], dtype=torch.float32)
+    assert torch.equal(fp8.pow2_ceil(s), want)
+    assert fp8.is_pow2(want) and not fp8.is_pow2(s)
+    g = torch.Generator().manual_seed(3)
+    a = torch.randn(5, 256, generator=g)
+    r = O.fp8_act_roundtrip(a, pow2_scales=True)
+    assert torch.equal(O.fp8_act_roundtrip(r, pow2_scales=True), r)          # idempotent
+    q, sc = fp8.quantize_rows_1x128(a, pow2_scales=True)
+    assert fp8.is_pow2(sc) and torch.equal((q.float().reshape(5, 2, 128) * sc.unsqueeze(-1)).reshape(5, 256), r)
+    assert float((r - a).abs().max()) <= float(a.abs().max()) * 2.0 ** -3      # e4m3: 3 mantissa bits, <= 2x headroom lost
+    lib = _lib.load()
+    import ctypes as C
+    sh = synth.AIR
+    sizes = [lib.glm4moe_workspace_bytes(C.byref(_lib.Config(sh.H, sh.E, sh.k, sh.I, 1.0, _lib.BF16, f, 256, 0,
+                                                             sh.E, 1, 0))) for f in (1, 2, 3)]
+    rows = 256 * (sh.k + 1)
+    assert sizes[1] >= sizes[0] + rows * 4 * (8 + 3) and sizes[2] == 0
 
 
 def test_casts_keep_bias_fp32_and_move_only_the_stacks():

@@ -686,7 +686,7 @@ def test_second_device_after_first():
 RTOL_FP8 = 5e-2      # north_star: FP8 outputs within 5e-2 of the fp32 reference (on the dequantised weights)
 
 
-def _fp8_check(out, x, deq, idx, w, shape, dt):
+def _fp8_check(out, x, deq, idx, w, shape, dt, pow2=False):
     """Two gates.  (1) kernel == the quant-tier algorithm (oracle.moe_forward_fp8: identical e4m3
     operands, fp32 math) under the elementwise bf16 criterion, rtol 2e-2.  (2) north_star's FP8
     tolerance against the fp32 reference with *unquantised* activations: e4m3 activations carry
@@ -695,7 +695,7 @@ def _fp8_check(out, x, deq, idx, w, shape, dt):
     that noise, which a Gaussian leaves with probability 6e-5: at most 1e-4 of the elements may;
     the reference torch W8A8 emulation fails the tighter form the same way)."""
     ref_w = {"w_gate_up": deq["w_gate_up"].cpu(), "w_down": deq["w_down"].cpu()}
-    algo = O.moe_forward_fp8(x, ref_w, (idx, w), dt)
+    algo = O.moe_forward_fp8(x, ref_w, (idx, w), dt, pow2_scales=pow2)
     nbad, rel = _close(out, algo, 2e-2)
     assert nbad == 0 and rel < 6e-3, ("vs quant-tier oracle", nbad, rel)
     truth = O.moe_forward(x.float(), ref_w, shape.k, shape.routed_scaling_factor, routing=(idx, w.float()))["out"]
@@ -706,10 +706,10 @@ def _fp8_check(out, x, deq, idx, w, shape, dt):
     assert rel < RTOL_FP8 and nbad <= 1e-4 * got.numel(), ("vs fp32 reference", rel, nbad)
 
 
-def _fp8_case(shape, dt, T, batch, max_tokens=256):
+def _fp8_case(shape, dt, T, batch, max_tokens=256, pow2=False):
     wts = synth.make_weights(shape, dt)
     moe = _module(shape, dt, wts, max_tokens=max_tokens)
-    moe.quantize_fp8()
+    moe.quantize_fp8(pow2_scales=pow2)
     x = synth.make_tokens(shape, T, dt, batch)
     with torch.inference_mode():
         out = moe(x.cuda())
@@ -720,12 +720,66 @@ def _fp8_case(shape, dt, T, batch, max_tokens=256):
         oi, _ = O.canonical_routing(*O.router(x, wts["gate_weight"], wts["bias"], shape.k,
                                               shape.routed_scaling_factor))
         assert torch.equal(idx, oi)
-        _fp8_check(out, x, moe.dequantized_weights(), idx, w, shape, dt)
+        _fp8_check(out, x, moe.dequantized_weights(), idx, w, shape, dt, pow2)
+    return moe
 
 
 @pytest.mark.parametrize("T", [1, 40, 200, 700])
 def test_fp8_block_scaled_mini(T):
     _fp8_case(synth.MINI, torch.bfloat16, T, T, max_tokens=max(T, 256))
+
+
+@pytest.mark.parametrize("T", [1, 17, 40, 200, 700, 1000])
+def test_fp8_pow2_scales_mini(T):
+    """Power-of-two (UE8M0) tier: weight block scales and every activation scale are powers of two in all
+    regimes (fused decode kernel, swap-AB tiles, prefill); from ~48 rows per expert the GEMMs run with
+    hardware block scaling (umma_fp8_mx.cu: tcgen05.mma.kind::mxf8f6f4.block_scale, scales in TMEM)."""
+    moe = _fp8_case(synth.MINI, torch.bfloat16, T, T, max_tokens=max(T, 256), pow2=True)
+    assert moe._cfg.weight_format == _lib.W_FP8_BLOCK128_POW2
+
+
+def test_fp8_pow2_tiny_fp16_ragged():
+    _fp8_case(synth.TINY, torch.float16, 333, 9, max_tokens=512, pow2=True)
+
+
+def test_fp8_pow2_format_refuses_other_scales():
+    """GLM4MOE_W_FP8_BLOCK128_POW2 is a promise about the checkpoint: amax/448 scales are refused at creation."""
+    shape, dt = synth.MINI, torch.bfloat16
+    moe = _module(shape, dt, synth.make_weights(shape, dt), max_tokens=64)
+    moe.quantize_fp8()
+    moe.fp8_pow2_scales = True
+    with pytest.raises(_lib.Glm4MoeLibraryError):
+        moe(synth.make_tokens(shape, 8, dt, 1).cuda())
+
+
+@pytest.mark.parametrize("shape_name,T", [("mini", 200), ("mini", 700), ("tiny", 333)])
+def test_fp8_hardware_block_scaling_matches_software_scaling(shape_name, T):
+    """Same e4m3 operands and the same power-of-two scales through the two prefill kernels: scales applied by
+    the tensor pipe (one TMEM accumulator over all of K) vs per-k-block fp32 promotion in the epilogue warps.
+    Power-of-two scaling is exact, so the two differ by fp32 summation order only; each is run-to-run
+    bit-deterministic; the layer's launch count is the same."""
+    lib = _lib.load()
+    shape, dt = synth.SHAPES[shape_name], torch.bfloat16
+    moe = _module(shape, dt, synth.make_weights(shape, dt), max_tokens=1024)
+    moe.quantize_fp8(drop_native=True, pow2_scales=True)
+    x = synth.make_tokens(shape, T, dt, 78).cuda()
+    try:
+        outs, n_launch = {}, {}
+        for name, knob in (("mx", 1), ("software", 0)):
+            _lib.check(lib.glm4moe_debug_set(8, knob))
+            for rep in range(3):
+                out = moe(x).clone()
+                n_launch[name] = moe.last_launches
+                if rep:
+                    assert torch.equal(out, outs[name]), f"{name}: run-to-run difference"
+                outs[name] = out
+        assert n_launch["mx"] == n_launch["software"], n_launch
+        a, b = outs["mx"].float(), outs["software"].float()
+        rel = float((a - b).norm() / b.norm())
+        nbad, _ = _close(outs["mx"], b.cpu(), 2e-2)
+        assert rel < 2e-3 and nbad == 0, (rel, nbad)
+    finally:
+        lib.glm4moe_debug_set(8, 1)
 
 
 def test_fp8_block_scaled_tiny_fp16():
@@ -808,7 +862,7 @@ class _LazyDequant:
         return fp8.dequantize_block128(self.q[e:e + 1], self.s[e:e + 1])[0].cpu()
 
 
-def _fp8_sampled_check(moe, out, x, shape, dt, idx, w, tile_rows, seed):
+def _fp8_sampled_check(moe, out, x, shape, dt, idx, w, tile_rows, seed, pow2=False):
     """The two gates of `_fp8_check` on sampled token rows of a full-size batch."""
     sel = _sample_tokens(idx, shape.E, tile_rows, 48, seed)
     deq = {"w_gate_up": _LazyDequant(moe._wq_gate_up, moe._s_gate_up),
@@ -816,7 +870,7 @@ def _fp8_sampled_check(moe, out, x, shape, dt, idx, w, tile_rows, seed):
     xs, ri, rw = x[sel], idx[sel], w[sel]
     got = out[sel.to(out.device)]
     with torch.inference_mode():
-        algo = O.moe_forward_fp8(xs, deq, (ri, rw), dt)
+        algo = O.moe_forward_fp8(xs, deq, (ri, rw), dt, pow2_scales=pow2)
         truth = O.moe_forward(xs.float(), deq, shape.k, shape.routed_scaling_factor, routing=(ri, rw.float()))["out"]
     nbad, rel = _close(got, algo, 2e-2)
     assert nbad == 0 and rel < 6e-3, ("vs quant-tier oracle", nbad, rel)
@@ -828,16 +882,17 @@ def _fp8_sampled_check(moe, out, x, shape, dt, idx, w, tile_rows, seed):
     return int(sel.numel())
 
 
-@pytest.mark.parametrize("T", [4096, 1000])
-def test_fp8_air_prefill_vs_quant_oracle(air, T):
+@pytest.mark.parametrize("T,pow2", [(4096, False), (1000, False), (4096, True), (1000, True)])
+def test_fp8_air_prefill_vs_quant_oracle(air, T, pow2):
     """Air shape, FP8 tier at prefill (token-major 128 x 256 tiles, fused re-quantiser): sampled token rows
     against the quant-tier oracle (`moe_forward_fp8`, identical e4m3 operands, fp32 math) at rtol 2e-2 and
     against the fp32 reference on the dequantised weights at north_star's 5e-2 (form: DESIGN.md section 4);
     plus batch-split consistency: rows [0, 1024) of the batch equal a 1024-token forward of those rows to
-    fp32 rounding (tile boundaries move, values may not)."""
+    fp32 rounding (tile boundaries move, values may not).  `pow2`: the UE8M0 tier, whose prefill GEMMs run with
+    hardware block scaling (umma_fp8_mx.cu)."""
     shape, dt, wts, _ = air
     moe = _module(shape, dt, wts, max_tokens=T)
-    moe.quantize_fp8(drop_native=True)
+    moe.quantize_fp8(drop_native=True, pow2_scales=pow2)
     x = synth.make_tokens(shape, T, dt, 4242 + T)
     with torch.inference_mode():
         out = moe(x.cuda())
@@ -849,7 +904,7 @@ def test_fp8_air_prefill_vs_quant_oracle(air, T):
         half = moe(x[:n_half].cuda())
     _explain_routing(idx, logits, x, wts["gate_weight"], wts["bias"], shape, dt)
     assert torch.isfinite(out.float()).all()
-    assert _fp8_sampled_check(moe, out, x, shape, dt, idx, w, 128, T) >= 320
+    assert _fp8_sampled_check(moe, out, x, shape, dt, idx, w, 128, T, pow2) >= 320
     d = float((out[:n_half].float() - half.float()).norm() / half.float().norm())
     assert d < 1e-3, d
 
