@@ -348,6 +348,16 @@ def main():
             local = idx[(idx >= moe.expert_begin) & (idx < moe.expert_end)]
             hits.append(int(torch.unique(local).numel()))
         U = sum(hits) / len(hits)
+        # expert-parallel load: local experts hit per rank per batch (the step waits for the slowest rank;
+        # SURVEY 8e "per-rank load imbalance (max / mean)")
+        ep_load = None
+        if world > 1:
+            mine = torch.tensor(hits, dtype=torch.float32, device=dev)
+            allh = [torch.empty_like(mine) for _ in range(world)]
+            dist.all_gather(allh, mine)
+            allh = torch.stack(allh)                                   # [rank, batch]
+            ep_load = {"experts_hit_per_rank_mean": [round(v, 2) for v in allh.mean(1).tolist()],
+                       "max_over_mean_per_step": round(float((allh.max(0)[0] / allh.mean(0)).mean()), 3)}
 
         # N > 1: one batch of the expert-parallel layer against a single-GPU forward, bit for bit
         ep_bit_identical = None
@@ -513,7 +523,7 @@ def main():
                         "parallelism": (f"ep{world}-{args.ep_layout}" + (f"-sliced{args.ep_sliced}" if args.ep_sliced >= 0 else ""))
                         if world > 1 else "single",
                         "weights_touched_per_step_gb": (U + 1) * 3 * H * I * wb / 1e9,
-                        "ep_bit_identical": ep_bit_identical},
+                        "ep_bit_identical": ep_bit_identical, "ep_load": ep_load},
             "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roofline,
             "cpu_baseline": cpu_baseline}
     if ep_bit_identical is not None:

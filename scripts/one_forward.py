@@ -5,7 +5,8 @@ import torch
 import glm4_moe_b200
 from glm4_moe_b200 import synth
 from bench import _hf_config
-FP8 = "--fp8" in sys.argv
+FP8 = "--fp8" in sys.argv or "--fp8-pow2" in sys.argv
+POW2 = "--fp8-pow2" in sys.argv
 args = [int(a) for a in sys.argv[1:] if not a.startswith("--")]
 T = args[0] if args else 32
 iters = args[1] if len(args) > 1 else 6
@@ -20,7 +21,7 @@ with torch.no_grad():
     moe._w_gate_up.normal_(0, 0.02); moe._w_down.normal_(0, 0.02); moe.gate.weight.normal_(0, 0.02)
     moe.gate.e_score_correction_bias.uniform_(0, 0.1)
 if FP8:
-    moe.quantize_fp8(drop_native=True)
+    moe.quantize_fp8(drop_native=True, pow2_scales=POW2)
 xs = [torch.randn(T, shape.H, device="cuda", dtype=dt) for _ in range(iters)]
 torch.cuda.synchronize()
 for x in xs:

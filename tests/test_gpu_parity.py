@@ -132,13 +132,21 @@ def _check_sampled_rows(out, x, wts, shape, dt, idx, w, tile_rows, seed=0, n_ext
     nbad, rel = _close(got, truth, RTOL_BF16)
     assert nbad == 0 and rel < 6e-3, (nbad, rel, int(sel.numel()))
     # The reference's own tolerance (rtol = atol = 1e-2, tests/moe.py:40) against its native-dtype result.  At
-    # these shapes outputs reach |y| ~ 2..8, where one bf16 ulp is 0.016..0.031, so that tolerance is 1-2 ulps:
-    # the reference's k model-dtype accumulations (moe.py:151) alone put 1.8e-4 of ITS elements outside the
-    # same tolerance of its own fp32 evaluation (Air, measured on the CPU).  Bar: at most 1e-3 of the elements
-    # outside rtol = atol = 1e-2 (measured 5.7e-4), none further than 4 model-dtype ulps of the value range.
-    g, n_ = got.float().cpu(), native.float()
-    outside = ((g - n_).abs() > 1e-2 + 1e-2 * n_.abs()).float().mean().item()
-    assert outside <= 1e-3, outside
+    # these shapes outputs reach |y| ~ 2..8 (routed_scaling_factor 2.5: ~7), where one bf16 ulp is 0.016..0.031,
+    # so that tolerance is 1-2 ulps and the reference's k model-dtype accumulations (moe.py:151) alone put a
+    # fraction o_nt of ITS elements outside the same tolerance of its own fp32 evaluation (measured on the
+    # CPU: Air 1.8e-4, GLM-4.5 1.4e-2; an ideal kernel = the fp32 truth rounded once = lands 1.6e-2 of the
+    # GLM-4.5 elements outside the native result).  Bar, relative to that measured noise of the reference
+    # itself: vs the native result at most 2 * o_nt + 1e-3 of the elements outside (measured Air 5.7e-4,
+    # GLM-4.5 2.4e-2), and vs the fp32 truth no more elements outside than the native result has (+1e-3);
+    # none further than 4 model-dtype ulps of the value range.
+    g, n_, t_ = got.float().cpu(), native.float(), truth.float()
+
+    def outside(a, b):
+        return ((a - b).abs() > 1e-2 + 1e-2 * b.abs()).float().mean().item()
+    o_nt, o_gn, o_gt = outside(n_, t_), outside(g, n_), outside(g, t_)
+    assert o_gn <= 2 * o_nt + 1e-3, (o_gn, o_nt)
+    assert o_gt <= o_nt + 1e-3, (o_gt, o_nt)
     assert float((g - n_).abs().max()) <= 4 * _ulp(dt) * float(n_.abs().max()), float((g - n_).abs().max())
     return int(sel.numel()), rel
 
