@@ -132,6 +132,25 @@ def _workload(shape, T, fp8):
             f"random-init, {regime} T={T}")
 
 
+def _dominant_kernel(shape, T, U, world, fused, fp8, pow2):
+    """(name, algorithmic bytes of one launch, its flops).  Dominant kernel = the gate_up grouped GEMM (decode:
+    the fused gate_up + down + combine launch).  Bytes = weights of the (U local + 1 shared) experts it touches
+    + the activation rows it reads + the rows it writes."""
+    H, I, k = shape.H, shape.I, shape.k
+    wb = 1 if fp8 else 2          # bytes per expert-weight element (and per gathered / activation row element)
+    rows = T * k / world + T / world
+    if fused:
+        # decode regime: gate_up + SiLU*mul + down + combine are ONE persistent launch (decode_fused.cu)
+        kern = "decode_fused_kernel<gate_up+silu_mul+down+combine>"
+        by = (U + 1) * 3 * I * H * wb + (T / world) * H * 2 + T * H * 2
+    else:
+        kern = ("umma_fp8_mx_kernel<gate_up+silu_mul+requant> (tcgen05 block-scaled MMA)" if pow2 and T * k / shape.E >= 48 else
+                "umma_fp8_prefill_kernel<gate_up+silu_mul+requant>" if fp8 and T * k / shape.E >= 48 else
+                "umma_fp8_kernel<gate_up+silu_mul>" if fp8 else "umma_grouped_kernel<gate_up+silu_mul>")
+        by = (U + 1) * 2 * I * H * wb + rows * H * wb + rows * I * wb
+    return kern, by, rows * 2 * H * 2 * I
+
+
 def _config(shape, T, fp8, n_batches):
     """The `config` object: identical in both arms (the driver compares them)."""
     return {"workload": _workload(shape, T, fp8), "tokens_per_step": T,
@@ -282,8 +301,15 @@ def main():
             step(batches[i % n_batches])
         torch.cuda.synchronize()
         if args.one_forward:
+            # ncu target (scripts/ncu_traffic.sh): the forward after the warm-up is the captured one
             step(batches[0])
             torch.cuda.synchronize()
+            idx0 = moe.workspace_view("idx", T)
+            U0 = int(torch.unique(idx0[(idx0 >= moe.expert_begin) & (idx0 < moe.expert_end)]).numel())
+            kern, by, fl = _dominant_kernel(shape, T, U0, world, moe.last_fused, fp8, pow2)
+            print(json.dumps({"one_forward": f"{shape.name}:T={T}:{args.weights}:n={world}", "kernel": kern,
+                              "experts_hit": U0, "algorithmic_bytes": by, "flops": fl,
+                              "warmup_forwards": max(args.warmup, 3)}))
             return
         # ---- timed region: exactly K steps, CUDA events, max over ranks.  Everything host-side that
         # differs per rank (NVML init, thread start) happens BEFORE the barrier; a tiny NCCL all-reduce
@@ -450,24 +476,10 @@ def main():
     if fp8:
         tc_peak, tc_src = _fp8_peak(tc_peak)
     H, I, k = shape.H, shape.I, shape.k
-    # dominant kernel: gate_up grouped GEMM. Algorithmic bytes of one launch = gate_up weights of
-    # the (U local + shared) experts it touches + the activation rows it reads + act rows it writes.
-    n_sh = 1
-    wb = 1 if fp8 else 2          # bytes per expert-weight element (and per gathered / activation row element)
-    rows = T * k / world + T / world
-    gu_ms = stage_acc["gate_up"]
-    if fused:
-        # decode regime: gate_up + SiLU*mul + down + combine are ONE persistent launch
-        # (decode_fused.cu); the "gate_up" stage interval brackets exactly that launch.
-        kern = "decode_fused_kernel<gate_up+silu_mul+down+combine>"
-        gu_bytes = (U + n_sh) * 3 * I * H * wb + (T / world) * H * 2 + T * H * 2
-    else:
-        kern = ("umma_fp8_mx_kernel<gate_up+silu_mul+requant> (tcgen05 block-scaled MMA)" if pow2 and T * k / shape.E >= 48 else
-                "umma_fp8_prefill_kernel<gate_up+silu_mul+requant>" if fp8 and T * k / shape.E >= 48 else
-                "umma_fp8_kernel<gate_up+silu_mul>" if fp8 else "umma_grouped_kernel<gate_up+silu_mul>")
-        gu_bytes = (U + n_sh) * 2 * I * H * wb + rows * H * wb + rows * I * wb
+    wb = 1 if fp8 else 2
+    gu_ms = stage_acc["gate_up"]     # decode: this stage interval brackets exactly the fused launch
+    kern, gu_bytes, gu_flops = _dominant_kernel(shape, T, U, world, fused, fp8, pow2)
     achieved = gu_bytes / gu_ms / 1e6
-    gu_flops = rows * 2 * H * 2 * I
     # DRAM traffic of this launch as ncu saw it on THIS bench's batch 0 (`bench.py --one-forward` under
     # `ncu --set full`, summarised by scripts/ncu_traffic.py into profiles/ncu_traffic_r2.json together
     # with the experts that launch hit); null when no capture of this exact workload is committed.
