@@ -19,6 +19,17 @@ under `nanovllm/` is edited: `install()` imports the installed copy (`baseline/_
   model.py:107-132         `load_weights` from a checkpoint -> deterministic random init when the model
                                                    directory carries `dummy_weights.json` (no checkpoint and
                                                    no network in this environment)
+  parallel_state.py:1-9    dummy TP group (world 1)  -> the real rank / world of the NCCL group the engine
+                                                   creates (model_runner.py:27), so that with
+                                                   `tensor_parallel_size = N` attention and the dense MLP are
+                                                   tensor-parallel as the reference's own layers implement it
+                                                   (linear.py, the KV cache already divides the heads,
+                                                   model_runner.py:111) while the sparse blocks are
+                                                   EXPERT-parallel (`expert_parallel="p2p" | "allreduce"`,
+                                                   distributed.py): BASELINE configs[3] at 2/4/8 GPUs
+  llm_engine.py:26         `ModelRunner` as the spawn target -> `shim_model_runner` (same arguments), which
+                                                   re-applies this shim in the spawned rank before constructing
+                                                   the reference's `ModelRunner`
 
 Attention (`nanovllm/layers/attention.py`, flash-attn), the KV cache, the scheduler, the sampler and the
 CUDA-graph runner (`engine/model_runner.py:216-258`) run as shipped.  `make_model_dir()` writes the synthetic
@@ -79,12 +90,68 @@ class HfConfigView:
 
 
 _installed = {}
+ENV_ARGS = "GLM4MOE_SHIM_ARGS"
 
 
-def install(sparse_block: str = "ours", weight_format: str = "native", share_workspace: bool = True):
+class _TPGroup:
+    """What `get_tp_group()` callers read (`linear.py:25-26`, `attention_new.py:16,117-119`): rank and
+    world size of the default process group the engine initialises (`model_runner.py:27`)."""
+
+    @property
+    def world_size(self):
+        import torch.distributed as dist
+        return dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+
+    @property
+    def rank(self):
+        import torch.distributed as dist
+        return dist.get_rank() if dist.is_available() and dist.is_initialized() else 0
+
+
+def shim_model_runner(config, rank, event):
+    """Spawn target standing in for `ModelRunner` (llm_engine.py:26): a spawned rank starts from a fresh
+    interpreter, so the rebinding is re-applied from the arguments the parent recorded, then the
+    reference's own `ModelRunner` runs as shipped."""
+    kw = json.loads(os.environ.get(ENV_ARGS, "{}"))
+    if "runner" not in _installed:
+        install(**kw)
+    _installed["max_tokens"] = int(config.max_num_batched_tokens)
+    if rank > 0:
+        # a spawned rank blocks in ModelRunner.loop() for its whole life: leave when the parent is gone
+        import threading
+        import time
+        parent = os.getppid()
+
+        def watchdog():
+            while os.getppid() == parent:
+                time.sleep(1.0)
+            os._exit(1)
+
+        threading.Thread(target=watchdog, daemon=True).start()
+    import torch.distributed as dist
+    if not getattr(dist.init_process_group, "_glm4moe_patched", False):
+        real_init = dist.init_process_group
+
+        def init_process_group(backend=None, init_method=None, *a, **k):     # model_runner.py:27
+            if isinstance(init_method, str):      # the container's "localhost" may not resolve
+                init_method = init_method.replace("tcp://localhost:", "tcp://127.0.0.1:")
+            return real_init(backend, init_method, *a, **k)
+
+        init_process_group._glm4moe_patched = True
+        dist.init_process_group = init_process_group
+    return _installed["runner"](config, rank, event)
+
+
+def install(sparse_block: str = "ours", weight_format: str = "native", share_workspace: bool = True,
+            expert_parallel: str | None = None):
     """Import the reference package and apply the construction-time rebinding described above.
     `sparse_block`: "ours" (this package's `Glm4MoeMoE`) or "reference" (the reference's own block, for
-    A/B runs of the same stack).  Returns the `nanovllm` package."""
+    A/B runs of the same stack).  `expert_parallel`: layout of the sparse blocks when the engine runs
+    `tensor_parallel_size > 1` ranks ("p2p": peer-memory combine, "allreduce": NCCL; None: every rank holds
+    all experts).  Returns the `nanovllm` package."""
+    os.environ[ENV_ARGS] = json.dumps(dict(sparse_block=sparse_block, weight_format=weight_format,
+                                           share_workspace=share_workspace, expert_parallel=expert_parallel))
+    _installed["ep_layout"] = expert_parallel if sparse_block == "ours" else None
     root = reference_root()
     if root is None:
         raise RuntimeError("the reference engine is not installed: run `python oracle/make_ref.py` where "
@@ -113,9 +180,18 @@ def install(sparse_block: str = "ours", weight_format: str = "native", share_wor
     from nanovllm.layers.embed_head import VocabParallelEmbedding
     from nanovllm.layers.layernorm import RMSNorm
 
+    from nanovllm.engine import llm_engine as LE
+    from nanovllm.engine import model_runner as MR
     if "ref_block" not in _installed:
         _installed["ref_block"] = ref_moe.Glm4MoeMoE
         _installed["post_init"] = ref_config.Config.__post_init__
+        _installed["runner"] = MR.ModelRunner
+    LE.ModelRunner = shim_model_runner                       # llm_engine.py:26,30
+    # parallel_state.py:1-9: every module that imported the dummy group by name
+    tp = _TPGroup()
+    for name, mod in list(sys.modules.items()):
+        if name.startswith("nanovllm") and mod is not None and hasattr(mod, "get_tp_group"):
+            mod.get_tp_group = lambda: tp
 
     from . import moe as ours
     if sparse_block == "ours":
@@ -129,6 +205,15 @@ def install(sparse_block: str = "ours", weight_format: str = "native", share_wor
 
     def model_init(self, config):                            # model.py:14-24 with the line of model.py:19
         nn.Module.__init__(self)
+        import torch.distributed as dist
+        world = dist.get_world_size() if dist.is_initialized() else 1
+        ours.Glm4MoeMoE.default_ep = None
+        ours.Glm4MoeMoE.default_max_tokens = _installed.get("max_tokens")
+        if world > 1 and _installed.get("ep_layout"):
+            layout = _installed["ep_layout"]
+            ours.Glm4MoeMoE.default_ep = (dist.get_rank(), world, layout == "p2p")
+            if layout == "p2p":
+                ours.Glm4MoeMoE.share_workspace = False      # peer-mapped workspaces are per layer
         self.embed_tokens = VocabParallelEmbedding(config.vocab_size, config.hidden_size)
         self.layers = nn.ModuleList([DL.Glm4MoeDecoderLayer(config, prefix=f"model.layers.{i}")
                                      for i in range(config.num_hidden_layers)])
@@ -153,6 +238,7 @@ def install(sparse_block: str = "ours", weight_format: str = "native", share_wor
             init_dummy_weights(self, **json.load(open(marker)))
         else:
             real_load(self, model_path)
+        setup_expert_parallel(self)
 
     M.Glm4MoeForCausalLM.load_weights = load_weights
 
@@ -165,6 +251,29 @@ def install(sparse_block: str = "ours", weight_format: str = "native", share_wor
 
     ref_config.Config.__post_init__ = config_post_init
     return nanovllm
+
+
+def setup_expert_parallel(model) -> int:
+    """Wrap every sparse block of an expert-parallel rank in `distributed.ExpertParallelMoE` (collective:
+    every rank calls it at the same point, right after its weights exist).  Layout "p2p" allocates and
+    exchanges the peer-mapped workspaces here, sized for the engine's largest batch, so nothing is
+    allocated during warm-up or CUDA-graph capture.  Returns the number of blocks wrapped."""
+    import torch.distributed as dist
+    from . import moe as ours
+    from .distributed import ExpertParallelMoE
+    layout = _installed.get("ep_layout")
+    if not layout or not dist.is_initialized() or dist.get_world_size() == 1:
+        return 0
+    n = 0
+    for layer in model.model.layers:
+        blk = layer.mlp
+        if isinstance(blk, ours.Glm4MoeMoE) and blk.ep_size > 1:
+            ep = ExpertParallelMoE(blk, blk.config.n_routed_experts, layout=layout)
+            if layout == "p2p":
+                ep.setup_p2p(_installed.get("max_tokens"))
+            layer.mlp = ep
+            n += 1
+    return n
 
 
 def init_dummy_weights(model, seed: int = 1234, std: float = 0.02, **_):

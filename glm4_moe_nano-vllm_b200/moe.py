@@ -164,16 +164,29 @@ class Glm4MoeMoE(nn.Module):
       share_workspace  True: blocks of one device with the same shape share ONE workspace allocation
                    (layers of a model run one after the other on one stream; every in-kernel counter
                    re-arms itself).  A private workspace per layer costs 2.8 GB at 16 k prefill tokens.
+      default_ep   None | (ep_rank, ep_size, peer_workspace): expert-parallel shard of a block constructed
+                   without keyword arguments (engine_shim.py sets it per process once torch.distributed is up)
+      default_max_tokens  initial workspace capacity of such a block
     """
 
     default_weight_format = "native"
     share_workspace = False
+    default_ep = None
+    default_max_tokens = None
     _workspace_pool: dict = {}
 
-    def __init__(self, config, *, max_tokens: int = 256, ep_rank: int = 0, ep_size: int = 1,
-                 impl: str = "auto", peer_workspace: bool = False):
+    def __init__(self, config, *, max_tokens: int | None = None, ep_rank: int | None = None,
+                 ep_size: int | None = None, impl: str = "auto", peer_workspace: bool | None = None):
         super().__init__()
         self.config = config
+        cls = type(self)
+        if ep_rank is None and ep_size is None and cls.default_ep is not None:
+            ep_rank, ep_size = cls.default_ep[0], cls.default_ep[1]
+            if peer_workspace is None:
+                peer_workspace = cls.default_ep[2]
+        ep_rank, ep_size = ep_rank or 0, ep_size or 1
+        if max_tokens is None:
+            max_tokens = cls.default_max_tokens or 256
         E, H, I = config.n_routed_experts, config.hidden_size, config.moe_intermediate_size
         if E % ep_size != 0:
             raise ValueError(f"n_routed_experts={E} not divisible by ep_size={ep_size}")
@@ -521,23 +534,28 @@ class Glm4MoeMoE(nn.Module):
     # ---- helpers used by tests / bench -------------------------------------------------------
     def init_random_(self, seed: int, std: float = 0.02, bias_high: float = 0.1, chunk: int = 16):
         """Random-init in place (no checkpoint, no network): weights ~ N(0, std^2), bias ~ U(0, bias_high)
-        as in synth.py, drawn on the block's own device.  FP8 blocks draw the model-dtype values `chunk`
-        experts at a time and quantise them (fp8.quantize_block128), so no full model-dtype stack exists."""
+        as in synth.py, drawn on the block's own device.  Every expert is drawn from its own generator seed
+        (its GLOBAL expert id; the shared expert, the gate and the bias follow), so an expert-parallel shard
+        holds exactly the experts of the single-GPU block.  FP8 blocks quantise `chunk` experts at a time
+        (fp8.quantize_block128), so no full model-dtype stack exists."""
         from . import fp8
         dev, md = self.gate.weight.device, self.gate.weight.dtype
-        gen = torch.Generator(device=dev).manual_seed(seed)
+        gen = torch.Generator(device=dev)
         c = self.config
-        H, I = c.hidden_size, c.moe_intermediate_size
+        H, I, E = c.hidden_size, c.moe_intermediate_size, c.n_routed_experts
         n = self.expert_end - self.expert_begin + 1
+        ids = list(range(self.expert_begin, self.expert_end)) + [E]
 
-        def draw(shape):
+        def draw(shape, ident):
+            gen.manual_seed(seed * 100003 + ident)
             return (torch.randn(shape, generator=gen, device=dev, dtype=torch.float32) * std).to(md)
 
         with torch.no_grad():
             self._destroy_handle()
             for s0 in range(0, n, chunk):
                 m = min(chunk, n - s0)
-                gu, dn = draw((m, 2 * I, H)), draw((m, H, I))
+                gu = torch.stack([draw((2 * I, H), 2 * ids[s0 + j]) for j in range(m)])
+                dn = torch.stack([draw((H, I), 2 * ids[s0 + j] + 1) for j in range(m)])
                 if self.weight_format == "fp8":
                     q, sc = fp8.quantize_block128(gu, self.fp8_pow2_scales)
                     self._wq_gate_up[s0:s0 + m].view(torch.uint8).copy_(q.view(torch.uint8))
@@ -548,9 +566,10 @@ class Glm4MoeMoE(nn.Module):
                 else:
                     self._w_gate_up[s0:s0 + m].copy_(gu)
                     self._w_down[s0:s0 + m].copy_(dn)
-            self.gate.weight.data.copy_(draw((c.n_routed_experts, H)))
+            self.gate.weight.data.copy_(draw((E, H), 2 * E + 2))
+            gen.manual_seed(seed * 100003 + 2 * E + 3)
             self.gate.e_score_correction_bias.copy_(
-                torch.rand(c.n_routed_experts, generator=gen, device=dev, dtype=torch.float32) * bias_high)
+                torch.rand(E, generator=gen, device=dev, dtype=torch.float32) * bias_high)
         return self
 
     def load_stacked(self, weights: dict):

@@ -47,15 +47,20 @@ def main():
     ap.add_argument("--max-batched-tokens", type=int, default=2048)
     ap.add_argument("--mem", type=float, default=0.85, help="gpu_memory_utilization (KV cache sizing)")
     ap.add_argument("--model-dir", default="")
+    ap.add_argument("--tp", type=int, default=1, help="ranks (tensor_parallel_size): attention / dense MLP "
+                    "tensor-parallel as the reference's layers do it, sparse blocks expert-parallel (--ep)")
+    ap.add_argument("--ep", default="p2p", choices=["p2p", "allreduce", "none"],
+                    help="layout of the sparse blocks when --tp > 1 (none: every rank holds all experts)")
     args = ap.parse_args()
 
-    nanovllm = S.install(sparse_block=args.block, weight_format=args.weights if args.weights != "bf16" else "native")
+    nanovllm = S.install(sparse_block=args.block, weight_format=args.weights if args.weights != "bf16" else "native",
+                         expert_parallel=None if args.ep == "none" or args.tp == 1 else args.ep)
     geom = dict(S.AIR_MODEL if args.preset == "air" else SMALL)
     d = args.model_dir or tempfile.mkdtemp(prefix="glm4moe_model_")
     S.make_model_dir(d, num_hidden_layers=args.layers, max_position_embeddings=max(args.max_model_len, 512), **geom)
 
     t0 = time.perf_counter()
-    llm = nanovllm.LLM(d, enforce_eager=args.eager, tensor_parallel_size=1, max_num_seqs=args.max_num_seqs,
+    llm = nanovllm.LLM(d, enforce_eager=args.eager, tensor_parallel_size=args.tp, max_num_seqs=args.max_num_seqs,
                        max_model_len=args.max_model_len, max_num_batched_tokens=args.max_batched_tokens,
                        gpu_memory_utilization=args.mem)
     build_s = time.perf_counter() - t0
@@ -86,11 +91,15 @@ def main():
     toks = [outputs[k] for k in sorted(outputs)]
     steady = decode_steps[2:] or decode_steps         # the first replays of a graph pay one-time costs
     ms = sorted(s[0] for s in steady)[len(steady) // 2] * 1e3 if steady else None
-    mlps = [l.mlp for l in llm.model_runner.model.model.layers]
+    mlps = [getattr(l.mlp, "local", l.mlp) for l in llm.model_runner.model.model.layers]
     ours = [m for m in mlps if isinstance(m, glm4_moe_b200.Glm4MoeMoE)]
     line = {"what": "decoder stack through the reference engine (nanovllm.LLM) with the sparse block swapped in",
             "preset": args.preset, "layers": args.layers, "moe_layers": len(mlps) - 1, "block": args.block,
             "weights": args.weights, "cuda_graph_decode": not args.eager, "seqs": args.seqs,
+            "ranks": args.tp, "parallelism": "single" if args.tp == 1 else
+            f"tp{args.tp} attention + dense MLP (reference layers, NCCL all-reduce), sparse blocks " +
+            ("replicated" if args.ep == "none" else f"ep{args.tp}-{args.ep}"),
+            "experts_per_rank": (ours[0].expert_end - ours[0].expert_begin) if ours else None,
             "prompt_len": args.prompt_len, "max_tokens": args.max_tokens,
             "prefill_tokens_per_s": prefill_tok / prefill_s if prefill_s else None,
             "decode_tokens_per_s": decode_tok / decode_s if decode_s else None,
@@ -101,6 +110,11 @@ def main():
             "digest": hashlib.sha256(json.dumps(toks).encode()).hexdigest()[:16], "token_ids": toks}
     print(json.dumps(line))
     sys.stdout.flush()
+    if args.tp > 1:
+        try:
+            llm.exit()         # tells the spawned ranks to leave their loop (llm_engine.py:37-41)
+        except Exception as e:  # noqa: BLE001
+            print(f"engine exit: {e}", file=sys.stderr)
     os._exit(0)        # the engine's atexit handler tears NCCL down; nothing left to flush
 
 

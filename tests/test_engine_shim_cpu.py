@@ -104,3 +104,58 @@ def test_fp8_construction_keeps_no_model_dtype_stack(tmp_path, group):
         assert 0.015 < float(deq.std()) < 0.025
     finally:
         S.install(sparse_block="ours", weight_format="native")
+
+
+def test_multi_rank_plumbing(tmp_path):
+    """What the shim adds for `tensor_parallel_size > 1` (BASELINE configs[3] at 2/4/8 GPUs): the dummy TP
+    group becomes the real one in every module that imported it, the spawn target is picklable by name and
+    carries the install arguments through the environment, the config view survives the spawn pickling."""
+    import json
+    import pickle
+    S.install(sparse_block="ours", weight_format="fp8", expert_parallel="p2p")
+    import nanovllm.layers.linear as lin
+    from nanovllm.models.glm4_moe import attention_new
+    from nanovllm.engine import llm_engine
+    assert isinstance(lin.get_tp_group(), S._TPGroup) and isinstance(attention_new.get_tp_group(), S._TPGroup)
+    g = lin.get_tp_group()
+    assert (g.rank, g.world_size) == ((dist.get_rank(), dist.get_world_size()) if dist.is_initialized() else (0, 1))
+    assert llm_engine.ModelRunner is S.shim_model_runner
+    assert pickle.loads(pickle.dumps(S.shim_model_runner)) is S.shim_model_runner
+    assert json.loads(os.environ[S.ENV_ARGS]) == dict(sparse_block="ours", weight_format="fp8", share_workspace=True,
+                                                      expert_parallel="p2p")
+    d = S.make_model_dir(str(tmp_path / "m"), **SMALL)
+    from nanovllm.config import Config
+    cfg = pickle.loads(pickle.dumps(Config(d, max_num_batched_tokens=512, max_model_len=256)))
+    assert cfg.hf_config.head_dim == 64 and cfg.hf_config.rope_scaling is None
+    assert cfg.hf_config.torch_dtype == torch.bfloat16
+    S.install()            # back to the defaults for the other tests
+    assert json.loads(os.environ[S.ENV_ARGS])["expert_parallel"] is None
+
+
+def test_random_init_of_an_expert_parallel_shard_equals_the_single_gpu_block(tmp_path):
+    """`init_random_` seeds every expert by its global id: rank r's shard holds experts [r*E/R, (r+1)*E/R) of
+    the single-GPU block, with the same shared expert, gate and bias (identical routing on every rank)."""
+    S.install()
+    d = S.make_model_dir(str(tmp_path / "m"), **SMALL)
+    from nanovllm.config import Config
+    hf = Config(d, max_num_batched_tokens=512, max_model_len=256).hf_config
+    prev = torch.get_default_dtype()
+    torch.set_default_dtype(torch.bfloat16)
+    try:
+        one = glm4_moe_b200.Glm4MoeMoE(hf).init_random_(7)
+        glm4_moe_b200.Glm4MoeMoE.default_ep = (1, 2, False)
+        try:
+            shard = glm4_moe_b200.Glm4MoeMoE(hf)          # as decode_layer.py:29 constructs it
+        finally:
+            glm4_moe_b200.Glm4MoeMoE.default_ep = None
+        shard.init_random_(7)
+    finally:
+        torch.set_default_dtype(prev)
+    E = hf.n_routed_experts
+    assert (shard.ep_rank, shard.ep_size, shard.expert_begin, shard.expert_end) == (1, 2, E // 2, E)
+    assert torch.equal(shard._w_gate_up[:-1], one._w_gate_up[E // 2:E])
+    assert torch.equal(shard._w_down[:-1], one._w_down[E // 2:E])
+    assert torch.equal(shard._w_gate_up[-1], one._w_gate_up[-1]) and torch.equal(shard._w_down[-1], one._w_down[-1])
+    assert torch.equal(shard.gate.weight, one.gate.weight)
+    assert torch.equal(shard.gate.e_score_correction_bias, one.gate.e_score_correction_bias)
+    assert not torch.equal(one._w_gate_up[0], one._w_gate_up[1])
