@@ -1,28 +1,33 @@
 // FP8 (e4m3) grouped expert GEMMs for the prefill regime with HARDWARE block scaling, sm_100a.
 //
-// Same tile geometry as umma_fp8_prefill.cu (tokens = MMA M = 128, weight rows = MMA N = 256, one
-// 128-byte k-block per pipeline stage), but the 128x128 weight block scales and the per-token 1x128
-// activation scales are applied by the tensor pipe itself: `tcgen05.mma.kind::mxf8f6f4.block_scale`
-// multiplies every K = 32 slice by one UE8M0 (power-of-two) factor per A row and one per B row, read
-// from tensor memory.  The whole K loop therefore accumulates into ONE TMEM accumulator and the
-// epilogue reads it once per tile, instead of pulling every k-block's 128 x 256 fp32 partial through
-// `tcgen05.ld` to scale it in registers (the TMEM-read bound the software-scaled kernel sits on:
-// 128 KB per 8.4 MFLOP = 1/4 of the e4m3 tensor peak).
+// The 128x128 weight block scales and the per-token 1x128 activation scales are applied by the tensor
+// pipe itself: `tcgen05.mma.kind::mxf8f6f4.block_scale` multiplies every K = 32 slice by one UE8M0
+// (power-of-two) factor per A row and one per B row, read from tensor memory.  The whole K loop therefore
+// accumulates into ONE TMEM accumulator and the epilogue reads it once per tile, instead of pulling every
+// k-block's fp32 partial through `tcgen05.ld` to scale it in registers (the TMEM-read bound the
+// software-scaled kernel umma_fp8_prefill.cu sits on).
+//
+// Tile: TWO 128-row weight slabs (MMA M = 128 each: gate rows + up rows of 128 features, or 256 consecutive
+// down features) x one token tile of <= 128 rows (MMA N), one 128-byte k-block per pipeline stage (48 KB).
+// Tokens are the N dimension so that a ragged last tile of an expert costs tensor time in proportion to its
+// rows (N = rows rounded up to 16): with tokens as M a 14-row tail cost a full 128-row tile, 20 % of all MMA
+// work at T = 4096 where an expert holds 256 +- 16 rows (profiles/r2f: pipe 69 % active, 55 % useful).
+// Accumulators: slab 0 -> TMEM columns [0, 128), slab 1 -> [128, 256); lane = output feature, column = token.
 //
 // Requires power-of-two scales: activation scales always are (common.cuh `pow2_scale`); weight block
 // scales when the checkpoint / `quantize_fp8(pow2_scales=True)` made them so
 // (GLM4MOE_W_FP8_BLOCK128_POW2).  Scale operands, per 4 consecutive k-blocks (K = 512), one uint32 per
 // row holding their 4 exponent bytes (byte j = k-block 4g + j; the MMA's a_sf_id / b_sf_id pick the byte):
-//   SFA  x_sf [ceil(nkb/4), scale_ld]   written by the activation quantisers (token row minor)
-//   SFB  w_sf [n_stack, rows/128, ceil(nkb/4)]   packed once per layer from the fp32 block scales;
-//        one value per 128-row weight block, replicated over its rows here
+//   SFB  x_sf [ceil(nkb/4), scale_ld]   written by the activation quantisers (token row minor)
+//   SFA  w_sf [n_stack, rows/128, ceil(nkb/4)]   packed once per layer from the fp32 block scales;
+//        one value per 128-row weight slab, replicated over its rows here
 // staged per k-group by warp 3 into shared memory in the layout `tcgen05.cp.32x128b.warpx4` expects
 // (row r of a 128-row block at word (r % 32) * 4 + r / 32), copied to TMEM by the MMA warp right in
 // front of the group's MMAs (tcgen05.cp and tcgen05.mma execute in issue order).
 //
-// TMEM: 256 accumulator columns + 2 x (4 SFA + 8 SFB) columns.  Two 256-column accumulators would
-// fill all 512 columns, so there is ONE accumulator stage; the ring keeps filling while the epilogue
-// drains it.  Replaces mlp.py:50-52 for the quant tier at prefill (BASELINE.json configs[2]).
+// TMEM: 256 accumulator columns + 2 x (4 SFB + 2 x 4 SFA) columns.  Two accumulator pairs would fill all
+// 512 columns, so there is ONE accumulator stage; the ring keeps filling while the epilogue drains it.
+// Replaces mlp.py:50-52 for the quant tier at prefill (BASELINE.json configs[2]).
 #include <cuda_fp8.h>
 
 #include "umma_common.cuh"
@@ -33,45 +38,25 @@ namespace glm4moe {
 namespace {
 
 constexpr int kXK = 128;                         // e4m3 elements (= bytes) per k-block = one scale block
-constexpr int kXM = 128;                         // token rows per tile (MMA M)
-constexpr int kXN = 256;                         // weight rows per tile (MMA N)
+constexpr int kXM = 128;                         // token rows per tile (MMA N, <= 128)
+constexpr int kXN = 256;                         // weight rows per tile: two slabs of MMA M = 128
 constexpr int kXStages = 4;
-constexpr int kXABytes = kXM * kXK;              // 16 KB
-constexpr int kXBBytes = kXN * kXK;              // 32 KB
+constexpr int kXABytes = kXM * kXK;              // token tile, 16 KB
+constexpr int kXBBytes = kXN * kXK;              // two weight slabs, 32 KB
 constexpr int kXStageBytes = kXABytes + kXBBytes;
 constexpr int kXEpiWarps = 16;
 constexpr int kXEpiThreads = 32 * kXEpiWarps;
 constexpr int kXThreads = 128 + kXEpiThreads;    // 640
-constexpr int kXSfSlotBytes = (kXM + kXN) * 4;   // 128 SFA words + 256 SFB words
+constexpr int kXSfSlotBytes = (kXM + kXN) * 4;   // 128 token words + 2 x 128 weight-slab words
 constexpr int kXAmaxBytes = 2 * 4 * kXM * 4;     // [tile parity][column group][row] fp32
 constexpr int kXBarBytes = 512;
 constexpr int kXSmemBytes = kXStages * kXStageBytes + 1024 /*align*/ + kXBarBytes + 2 * kXSfSlotBytes + kXAmaxBytes;
 constexpr int kXSchedDepth = 4;
 constexpr uint32_t kXSfCol0 = 256;               // first scale-factor column in TMEM
-constexpr uint32_t kXSfColStride = 16;           // per slot: SFA at +0 (4 columns), SFB at +4 (8 columns)
+constexpr uint32_t kXSfColStride = 16;           // per slot: tokens (SFB) at +0, slab 0 (SFA) at +4, slab 1 at +8
 
 __device__ __forceinline__ void xepi_bar_sync() {   // the 16 epilogue warps only
   asm volatile("bar.sync 1, %0;" ::"n"(kXEpiThreads) : "memory");
-}
-
-__device__ __forceinline__ uint32_t xpack_e4m3x4(float a, float b, float c, float d) {
-  return static_cast<uint32_t>(__nv_cvt_float_to_fp8(a, __NV_SATFINITE, __NV_E4M3)) |
-         static_cast<uint32_t>(__nv_cvt_float_to_fp8(b, __NV_SATFINITE, __NV_E4M3)) << 8 |
-         static_cast<uint32_t>(__nv_cvt_float_to_fp8(c, __NV_SATFINITE, __NV_E4M3)) << 16 |
-         static_cast<uint32_t>(__nv_cvt_float_to_fp8(d, __NV_SATFINITE, __NV_E4M3)) << 24;
-}
-
-template <typename T>
-__device__ __forceinline__ uint32_t xpack2(float a, float b);
-template <>
-__device__ __forceinline__ uint32_t xpack2<__nv_bfloat16>(float a, float b) {
-  __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
-  return *reinterpret_cast<uint32_t*>(&v);
-}
-template <>
-__device__ __forceinline__ uint32_t xpack2<__half>(float a, float b) {
-  __half2 v = __floats2half2_rn(a, b);
-  return *reinterpret_cast<uint32_t*>(&v);
 }
 
 // D[tmem] (+)= (A * SFA) x (B * SFB): e4m3 operands, UE8M0 scale per row per K = 32, fp32 accumulate
@@ -87,7 +72,7 @@ __device__ __forceinline__ void umma_f8_block_scaled(uint32_t d_tmem, uint64_t a
       : "memory");
 }
 // instruction descriptor, kind::mxf8f6f4.block_scale: A/B e4m3 (format 0) K-major, UE8M0 scales,
-// M = 128, N = n, scale-factor byte ids of this K = 32 slice's k-block
+// M = 128, N = n (multiple of 16), scale-factor byte ids of this K = 32 slice's k-block
 __device__ __forceinline__ uint32_t make_idesc_mx(int n, uint32_t a_sf_id, uint32_t b_sf_id) {
   return (b_sf_id << 4) | (static_cast<uint32_t>(n >> 3) << 17) | (1u << 23) | (static_cast<uint32_t>(128 >> 4) << 24) |
          (a_sf_id << 29);
@@ -241,27 +226,29 @@ __global__ void __launch_bounds__(kXThreads, 1) umma_fp8_mx_kernel(
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer: scale factors to TMEM, then 4 block-scaled MMAs per k-block =====================
+    // ===================== MMA issuer: scale factors to TMEM, then 2 x 4 block-scaled MMAs per k-block =====================
     int stage = 0;
     uint32_t phase = 0;
     uint32_t gcount = 0;      // k-groups consumed so far (scale-factor slot ring)
     for (int it = 0;; ++it) {
       const int w = next_work(it);
       if (w < 0) break;
+      const WorkRef tile = get_work<kXM>(tiles, w, n_feat_tiles, n_tiles, 0);
+      const int n_eff = min(kXM, (tile.nrows + 15) & ~15);     // MMA N: the tile's rows, rounded up to 16
       mbar_wait(&tmem_empty[0], (it & 1u) ^ 1u);
       tc_fence_after();
       for (int kb = 0; kb < n_kblocks; ++kb) {
         const int slot = gcount & 1u;
-        const uint32_t sfa_t = tmem_base + kXSfCol0 + slot * kXSfColStride;
-        const uint32_t sfb_t = sfa_t + 4;
+        const uint32_t sfb_t = tmem_base + kXSfCol0 + slot * kXSfColStride;   // tokens
+        const uint32_t sfa_t = sfb_t + 4;                                     // slab 0; slab 1 at +4
         if ((kb & 3) == 0) {
           mbar_wait(&sf_full[slot], (gcount >> 1) & 1u);
           tc_fence_after();
           if (elect_one()) {
             const uint32_t ss = smem_u32(sf_smem + slot * (kXM + kXN));
-            utccp_32x128b_x4(sfa_t, make_sf_desc(ss));                 // 128 token rows   -> 4 columns
-            utccp_32x128b_x4(sfb_t, make_sf_desc(ss + 512));           // weight rows 0..127   -> 4 columns
-            utccp_32x128b_x4(sfb_t + 4, make_sf_desc(ss + 1024));      // weight rows 128..255 -> 4 columns
+            utccp_32x128b_x4(sfb_t, make_sf_desc(ss));                 // 128 token rows      -> 4 columns
+            utccp_32x128b_x4(sfa_t, make_sf_desc(ss + 512));           // weight slab 0 rows  -> 4 columns
+            utccp_32x128b_x4(sfa_t + 4, make_sf_desc(ss + 1024));      // weight slab 1 rows  -> 4 columns
           }
           __syncwarp();
         }
@@ -269,13 +256,16 @@ __global__ void __launch_bounds__(kXThreads, 1) umma_fp8_mx_kernel(
         tc_fence_after();
         if (elect_one()) {
           const uint32_t sa = smem_u32(smem + stage * kXStageBytes);
-          const uint64_t a_desc = make_kmajor_desc(sa);              // tokens  [128 x 128 B]
-          const uint64_t b_desc = make_kmajor_desc(sa + kXABytes);   // weights [256 x 128 B]
-          const uint32_t idesc = make_idesc_mx(kXN, kb & 3, kb & 3);
+          const uint64_t b_desc = make_kmajor_desc(sa);                           // tokens  [128 x 128 B]
+          const uint64_t a0_desc = make_kmajor_desc(sa + kXABytes);               // slab 0  [128 x 128 B]
+          const uint64_t a1_desc = make_kmajor_desc(sa + kXABytes + kXBBytes / 2);
+          const uint32_t idesc = make_idesc_mx(n_eff, kb & 3, kb & 3);
 #pragma unroll
-          for (int ks = 0; ks < kXK / 32; ++ks)
-            umma_f8_block_scaled(tmem_base, a_desc + 2 * ks, b_desc + 2 * ks, idesc, sfa_t, sfb_t,
-                                 (kb > 0 || ks > 0) ? 1u : 0u);
+          for (int ks = 0; ks < kXK / 32; ++ks) {
+            const uint32_t acc = (kb > 0 || ks > 0) ? 1u : 0u;
+            umma_f8_block_scaled(tmem_base, a0_desc + 2 * ks, b_desc + 2 * ks, idesc, sfa_t, sfb_t, acc);
+            umma_f8_block_scaled(tmem_base + kXM, a1_desc + 2 * ks, b_desc + 2 * ks, idesc, sfa_t + 4, sfb_t, acc);
+          }
           umma_commit(&empty_bar[stage]);
           if ((kb & 3) == 3 || kb == n_kblocks - 1) umma_commit(&sf_empty[slot]);   // group's scale factors consumed
           if (kb == n_kblocks - 1) umma_commit(&tmem_full[0]);
@@ -288,7 +278,7 @@ __global__ void __launch_bounds__(kXThreads, 1) umma_fp8_mx_kernel(
   } else if (warp == 3) {
     // ===================== scale-factor loader =====================
     // per k-group: 128 token words (one coalesced 512-byte read per 32-row block) and the two weight
-    // block words of this tile, written in the order tcgen05.cp.32x128b.warpx4 reads them
+    // slab words of this tile, written in the order tcgen05.cp.32x128b.warpx4 reads them
     pdl_wait();      // x_sf is the direct predecessor's output
     const int wblocks = w_rows_per_expert / 128;
     uint32_t gcount = 0;
@@ -319,91 +309,104 @@ __global__ void __launch_bounds__(kXThreads, 1) umma_fp8_mx_kernel(
       }
     }
   } else if (warp >= 4) {
-    // ===================== epilogue: one read of the accumulator per tile, fused output math =====================
-    // warp -> TMEM lane quadrant q (hardware: warp id % 4) and column group cg:
-    //   gate_up: gate columns [32cg, 32cg+32) and up columns [128+32cg, +32)  (32 outputs, 64 accumulators)
-    //   down:    columns [64cg, 64cg+64)                                      (64 outputs)
+    // ===================== epilogue: one read of the accumulators per tile, fused output math =====================
+    // warp -> TMEM lane quadrant q (hardware: warp id % 4) = output features [32q, 32q + 32) of both slabs, and
+    // token group cg = token columns [32cg, 32cg + 32); a thread holds, for its feature, 32 tokens x 2 slabs.
     const int q = warp & 3;
     const int cg = (warp - 4) >> 2;
     const uint32_t lane_base = static_cast<uint32_t>(q * 32) << 16;
-    const int r = q * 32 + lane;                    // token row inside the tile held by this thread
+    const int feat = q * 32 + lane;                 // feature inside a slab
     pdl_wait();
     for (int it = 0;; ++it) {
       const int w = next_work(it);
       if (w < 0) break;
       const WorkRef tile = get_work<kXM>(tiles, w, n_feat_tiles, n_tiles, 0);
-      const bool row_ok = r < tile.nrows;
-      const int row = tile.row_start + r;
-      const int col0 = GATED ? 32 * cg : 64 * cg;
-      const int col1 = GATED ? 128 + 32 * cg : 64 * cg + 32;
-      float rw = 1.0f;
-      if (!GATED && row_ok && row < n_routed_rows) rw = __ldg(row_weight + row);
+      const int n_eff = min(kXM, (tile.nrows + 15) & ~15);
+      const bool have = 32 * cg < n_eff;            // this warp's token columns were computed (warp-uniform)
+      const int n_here = min(32, tile.nrows - 32 * cg);   // valid tokens among them (may be <= 0)
       mbar_wait(&tmem_full[0], it & 1u);
       tc_fence_after();
-      const uint32_t t_acc = tmem_base + lane_base;
-      uint32_t a0[16], a1[16], b0[16], b1[16];
-      tmem_ld16(t_acc + col0, a0);
-      tmem_ld16(t_acc + col0 + 16, a1);
-      tmem_ld16(t_acc + col1, b0);
-      tmem_ld16(t_acc + col1 + 16, b1);
-      tmem_ld_wait();
-      // everything is in registers: hand the accumulator back before the output math
+      const uint32_t t_acc = tmem_base + lane_base + 32 * cg;
+      uint32_t a0[16], a1[16], b0[16], b1[16];      // slab 0 (gate) / slab 1 (up), tokens 0-15 / 16-31 of the group
+      if (have) {
+        tmem_ld16(t_acc, a0);
+        tmem_ld16(t_acc + kXM, b0);
+        if (32 * cg + 16 < n_eff) {
+          tmem_ld16(t_acc + 16, a1);
+          tmem_ld16(t_acc + kXM + 16, b1);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) a1[j] = b1[j] = 0u;
+        }
+        tmem_ld_wait();
+      } else {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) a0[j] = a1[j] = b0[j] = b1[j] = 0u;
+      }
+      // everything is in registers: hand the accumulators back before the output math
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty[0]);
       if (GATED) {
-        // a = gate, b = up of output features f*128 + 32cg + j.  SiLU*mul (activation.py:13-14), one
-        // rounding to the model dtype (the reference stores the intermediate in it), then the 1x128 e4m3
-        // quantiser of the down projection's input with a power-of-two scale: the group = this tile's 128
-        // features of the token = the 4 column groups of the quadrant.
-        float v[32];
-        float amax = 0.f;
-#pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          v[j] = Dt<T>::round(silu_fast(__uint_as_float(a0[j])) * __uint_as_float(b0[j]));
-          v[16 + j] = Dt<T>::round(silu_fast(__uint_as_float(a1[j])) * __uint_as_float(b1[j]));
-          amax = fmaxf(amax, fmaxf(fabsf(v[j]), fabsf(v[16 + j])));
-        }
+        // a = gate, b = up of feature f*128 + feat for 32 tokens.  SiLU*mul (activation.py:13-14), one rounding
+        // to the model dtype (the reference stores the intermediate in it), then the 1x128 e4m3 quantiser of the
+        // down projection's input with a power-of-two scale: the group = this tile's 128 features of a token =
+        // the 32 lanes of the 4 quadrant warps.
         float* ax = amax_x + (it & 1) * 4 * kXM;
-        ax[cg * kXM + r] = amax;
-        xepi_bar_sync();
-        amax = fmaxf(fmaxf(ax[r], ax[kXM + r]), fmaxf(ax[2 * kXM + r], ax[3 * kXM + r]));
-        uint32_t ebyte;
-        const float sc = pow2_scale(amax, &ebyte);
-        const float inv = pow2_inverse(ebyte);
-        if (row_ok) {
-          uint32_t p[8];
 #pragma unroll
-          for (int j = 0; j < 8; ++j)
-            p[j] = xpack_e4m3x4(v[4 * j] * inv, v[4 * j + 1] * inv, v[4 * j + 2] * inv, v[4 * j + 3] * inv);
-          uint4* dst = reinterpret_cast<uint4*>(out_q + static_cast<size_t>(row) * ld_out + tile.f * 128 + 32 * cg);
-          dst[0] = make_uint4(p[0], p[1], p[2], p[3]);
-          dst[1] = make_uint4(p[4], p[5], p[6], p[7]);
-          if (cg == 0) {
-            out_scale_t[static_cast<size_t>(tile.f) * scale_ld + row] = sc;
-            out_sf[(static_cast<size_t>(tile.f >> 2) * scale_ld + row) * 4 + (tile.f & 3)] = static_cast<uint8_t>(ebyte);
+        for (int h = 0; h < 2; ++h) {
+          uint32_t* g_ = h ? a1 : a0;
+          const uint32_t* u_ = h ? b1 : b0;
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const float v = Dt<T>::round(silu_fast(__uint_as_float(g_[j])) * __uint_as_float(u_[j]));
+            g_[j] = __float_as_uint(v);
+            // |v| as an unsigned integer orders like the float: one redux instead of 5 shuffles
+            const uint32_t m = __reduce_max_sync(0xffffffffu, __float_as_uint(fabsf(v)));
+            if (lane == 16 * h + j) ax[q * kXM + 32 * cg + lane] = __uint_as_float(m);
+          }
+        }
+        xepi_bar_sync();
+        const int tok = 32 * cg + lane;             // the token this lane publishes the scale of
+        const float am = fmaxf(fmaxf(ax[tok], ax[kXM + tok]), fmaxf(ax[2 * kXM + tok], ax[3 * kXM + tok]));
+        uint32_t ebyte;
+        const float sc = pow2_scale(am, &ebyte);
+        if (q == 0 && lane < n_here) {
+          const int row = tile.row_start + tok;
+          out_scale_t[static_cast<size_t>(tile.f) * scale_ld + row] = sc;
+          out_sf[(static_cast<size_t>(tile.f >> 2) * scale_ld + row) * 4 + (tile.f & 3)] = static_cast<uint8_t>(ebyte);
+        }
+        uint8_t* dst = out_q + static_cast<size_t>(tile.row_start + 32 * cg) * ld_out + tile.f * 128 + feat;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const uint32_t* g_ = h ? a1 : a0;
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const int t = 16 * h + j;
+            const float inv = pow2_inverse(__shfl_sync(0xffffffffu, ebyte, t));
+            if (t < n_here)
+              dst[static_cast<size_t>(t) * ld_out] = static_cast<uint8_t>(
+                  __nv_cvt_float_to_fp8(__uint_as_float(g_[j]) * inv, __NV_SATFINITE, __NV_E4M3));
           }
         }
       } else {
         // y = acc * routing weight (mlp.py:52, moe.py:149); shared-expert rows carry weight 1
-        if (row_ok) {
-          uint4* dst = reinterpret_cast<uint4*>(out + static_cast<size_t>(row) * ld_out + tile.f * 256 + 64 * cg);
-          auto f = [&](const uint32_t* s, int j) { return __uint_as_float(s[j]) * rw; };
+        const int row_l = tile.row_start + 32 * cg + lane;
+        float rw_l = 1.0f;
+        if (lane < n_here && row_l < n_routed_rows) rw_l = __ldg(row_weight + row_l);
+        T* dst = out + static_cast<size_t>(tile.row_start + 32 * cg) * ld_out + tile.f * 256 + feat;
 #pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            const uint32_t* s = h ? a1 : a0;
-            dst[2 * h] = make_uint4(xpack2<T>(f(s, 0), f(s, 1)), xpack2<T>(f(s, 2), f(s, 3)), xpack2<T>(f(s, 4), f(s, 5)),
-                                    xpack2<T>(f(s, 6), f(s, 7)));
-            dst[2 * h + 1] = make_uint4(xpack2<T>(f(s, 8), f(s, 9)), xpack2<T>(f(s, 10), f(s, 11)),
-                                        xpack2<T>(f(s, 12), f(s, 13)), xpack2<T>(f(s, 14), f(s, 15)));
-          }
+        for (int h = 0; h < 2; ++h) {
+          const uint32_t* s0 = h ? a1 : a0;
+          const uint32_t* s1 = h ? b1 : b0;
 #pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            const uint32_t* s = h ? b1 : b0;
-            dst[4 + 2 * h] = make_uint4(xpack2<T>(f(s, 0), f(s, 1)), xpack2<T>(f(s, 2), f(s, 3)),
-                                        xpack2<T>(f(s, 4), f(s, 5)), xpack2<T>(f(s, 6), f(s, 7)));
-            dst[4 + 2 * h + 1] = make_uint4(xpack2<T>(f(s, 8), f(s, 9)), xpack2<T>(f(s, 10), f(s, 11)),
-                                            xpack2<T>(f(s, 12), f(s, 13)), xpack2<T>(f(s, 14), f(s, 15)));
+          for (int j = 0; j < 16; ++j) {
+            const int t = 16 * h + j;
+            const float rw = __shfl_sync(0xffffffffu, rw_l, t);
+            if (t < n_here) {
+              dst[static_cast<size_t>(t) * ld_out] = Dt<T>::from_f(__uint_as_float(s0[j]) * rw);
+              dst[static_cast<size_t>(t) * ld_out + 128] = Dt<T>::from_f(__uint_as_float(s1[j]) * rw);
+            }
           }
         }
       }
