@@ -51,7 +51,15 @@ int g_router_rows = 0;   // 0: pick by T; 16/32/64/128: token rows per router ti
 int g_bk32 = -1;         // see bk32_enabled()
 int g_down2 = -1;        // see down2_enabled()
 int g_force_bn = -2;     // see forced_bn_index()
-int g_fp8_mx = 1;        // hardware block scaling for FP8_BLOCK128_POW2 prefill (umma_fp8_mx.cu), KNOB_FP8_MX
+int g_fp8_mx = -1;       // hardware block scaling for FP8_BLOCK128_POW2 prefill: 0 off, 1 one CTA per tile
+                         // (umma_fp8_mx.cu), 2 CTA pairs (umma_fp8_mx2.cu); KNOB_FP8_MX / GLM4MOE_FP8_MX
+int fp8_mx_mode() {
+  if (g_fp8_mx < 0) {
+    const char* e = getenv("GLM4MOE_FP8_MX");
+    g_fp8_mx = (e && e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 1;
+  }
+  return g_fp8_mx;
+}
 int g_ep_fast = 1;       // decode fast path of the peer-memory combine (one rendezvous per step), KNOB_EP_FAST
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
@@ -181,7 +189,7 @@ extern "C" int glm4moe_debug_set(int knob, int value) {
       g_router_rows = value;
       return GLM4MOE_OK;
     case GLM4MOE_KNOB_EP_FAST: g_ep_fast = value ? 1 : 0; return GLM4MOE_OK;
-    case GLM4MOE_KNOB_FP8_MX: g_fp8_mx = value ? 1 : 0; return GLM4MOE_OK;
+    case GLM4MOE_KNOB_FP8_MX: g_fp8_mx = value < 0 || value > 2 ? 1 : value; return GLM4MOE_OK;
     case GLM4MOE_KNOB_BK32: g_bk32 = value ? 1 : 0; return GLM4MOE_OK;
     case GLM4MOE_KNOB_DOWN2: g_down2 = value ? 1 : 0; return GLM4MOE_OK;
     case GLM4MOE_KNOB_FORCE_TILE_ROWS:
@@ -466,7 +474,10 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
   // e4m3 tier at prefill (>= ~48 rows per expert): token-major 128 x 256 tiles (umma_fp8_prefill.cu)
   const bool fp8_prefill = fp8 && !direct && pick_bn_index(c, T) >= 3 && fp8_prefill_enabled() &&
                            umma_fp8_prefill_shape_ok(H, I);
+  // block-scaled pair kernel (cta_group::2): 256-row tiles, each CTA of a pair loads 128-row boxes
+  const bool fp8_mx2 = fp8_prefill && pow2 && fp8_mx_mode() == 2;
   const int bi = direct ? (T <= 16 ? 0 : 1)
+                 : fp8_mx2 ? 4
                  : fp8_prefill ? 3
                  : fp8 ? (pick_bn_index(c, T) < 2 ? pick_bn_index(c, T) : 2) : pick_bn_index(c, T);
   const int tile_rows = use_umma ? kBnChoices[bi] : kSimtRows;
@@ -600,7 +611,7 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
     if ((rc = decode_fused_launch(f, stream))) return rc;
     STAGE_MARK(5);
     combine_done = true;
-  } else if (fp8_prefill && pow2 && g_fp8_mx) {
+  } else if (fp8_prefill && pow2 && fp8_mx_mode() != 0) {
     // scales applied by the tensor pipe (tcgen05 block-scaled MMA), one accumulator read per tile
     UmmaFp8MxLaunch a{};
     a.tiles = tiles;
@@ -611,7 +622,7 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
     a.n_routed_rows = T * k;
     a.scale_ld = R_cap;
     a.tm_w = &l->tm_w_gu;
-    a.tm_x = &l->tm_x[bi];
+    a.tm_x = &l->tm_x[3];
     a.w_sf = l->sf_gate_up;
     a.x_sf = reinterpret_cast<const uint32_t*>(ws + L.sx_sf);
     a.out = nullptr;
@@ -625,10 +636,10 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
     a.up_row_offset = I;
     a.gated = 1;
     a.sched = reinterpret_cast<int32_t*>(ws + L.sched);
-    if ((rc = umma_fp8_mx_launch(a, stream))) return rc;
+    if ((rc = fp8_mx2 ? umma_fp8_mx2_launch(a, stream) : umma_fp8_mx_launch(a, stream))) return rc;
     STAGE_MARK(5);
     a.tm_w = &l->tm_w_d;
-    a.tm_x = &l->tm_act[bi];
+    a.tm_x = &l->tm_act[3];
     a.w_sf = l->sf_down;
     a.x_sf = reinterpret_cast<const uint32_t*>(ws + L.sact_sf);
     a.out = y;
@@ -642,7 +653,7 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
     a.up_row_offset = 0;
     a.gated = 0;
     a.sched = reinterpret_cast<int32_t*>(ws + L.sched) + 2;
-    if ((rc = umma_fp8_mx_launch(a, stream))) return rc;
+    if ((rc = fp8_mx2 ? umma_fp8_mx2_launch(a, stream) : umma_fp8_mx_launch(a, stream))) return rc;
   } else if (fp8_prefill) {
     UmmaFp8PrefillLaunch a{};
     a.pow2 = pow2;

@@ -773,7 +773,7 @@ def test_fp8_hardware_block_scaling_matches_software_scaling(shape_name, T):
     x = synth.make_tokens(shape, T, dt, 78).cuda()
     try:
         outs, n_launch = {}, {}
-        for name, knob in (("mx", 1), ("software", 0)):
+        for name, knob in (("pair", 2), ("mx", 1), ("software", 0)):
             _lib.check(lib.glm4moe_debug_set(8, knob))
             for rep in range(3):
                 out = moe(x).clone()
@@ -781,11 +781,13 @@ def test_fp8_hardware_block_scaling_matches_software_scaling(shape_name, T):
                 if rep:
                     assert torch.equal(out, outs[name]), f"{name}: run-to-run difference"
                 outs[name] = out
-        assert n_launch["mx"] == n_launch["software"], n_launch
-        a, b = outs["mx"].float(), outs["software"].float()
-        rel = float((a - b).norm() / b.norm())
-        nbad, _ = _close(outs["mx"], b.cpu(), 2e-2)
-        assert rel < 2e-3 and nbad == 0, (rel, nbad)
+        assert n_launch["mx"] == n_launch["software"] == n_launch["pair"], n_launch
+        b = outs["software"].float()
+        for name in ("mx", "pair"):           # pair: tcgen05 cta_group::2, 256-token x 256-row tiles (umma_fp8_mx2.cu)
+            a = outs[name].float()
+            rel = float((a - b).norm() / b.norm())
+            nbad, _ = _close(outs[name], b.cpu(), 2e-2)
+            assert rel < 2e-3 and nbad == 0, (name, rel, nbad)
     finally:
         lib.glm4moe_debug_set(8, 1)
 
@@ -890,7 +892,7 @@ def _fp8_sampled_check(moe, out, x, shape, dt, idx, w, tile_rows, seed, pow2=Fal
     return int(sel.numel())
 
 
-@pytest.mark.parametrize("T,pow2", [(4096, False), (1000, False), (4096, True), (1000, True)])
+@pytest.mark.parametrize("T,pow2", [(4096, False), (1000, False), (4096, True), (1000, True), (4096, 2), (1000, 2)])
 def test_fp8_air_prefill_vs_quant_oracle(air, T, pow2):
     """Air shape, FP8 tier at prefill (token-major 128 x 256 tiles, fused re-quantiser): sampled token rows
     against the quant-tier oracle (`moe_forward_fp8`, identical e4m3 operands, fp32 math) at rtol 2e-2 and
@@ -900,16 +902,21 @@ def test_fp8_air_prefill_vs_quant_oracle(air, T, pow2):
     hardware block scaling (umma_fp8_mx.cu)."""
     shape, dt, wts, _ = air
     moe = _module(shape, dt, wts, max_tokens=T)
-    moe.quantize_fp8(drop_native=True, pow2_scales=pow2)
+    moe.quantize_fp8(drop_native=True, pow2_scales=bool(pow2))
     x = synth.make_tokens(shape, T, dt, 4242 + T)
-    with torch.inference_mode():
-        out = moe(x.cuda())
-        torch.cuda.synchronize()
-        idx = moe.workspace_view("idx", T).cpu().long()
-        w = moe.workspace_view("w", T).cpu().to(dt)
-        logits = moe.workspace_view("logits", T).cpu()
-        n_half = min(1024, T // 2)
-        half = moe(x[:n_half].cuda())
+    lib = _lib.load()
+    try:
+        _lib.check(lib.glm4moe_debug_set(8, 2 if pow2 == 2 else 1))      # pow2 == 2: the CTA-pair kernel
+        with torch.inference_mode():
+            out = moe(x.cuda())
+            torch.cuda.synchronize()
+            idx = moe.workspace_view("idx", T).cpu().long()
+            w = moe.workspace_view("w", T).cpu().to(dt)
+            logits = moe.workspace_view("logits", T).cpu()
+            n_half = min(1024, T // 2)
+            half = moe(x[:n_half].cuda())
+    finally:
+        lib.glm4moe_debug_set(8, 1)
     _explain_routing(idx, logits, x, wts["gate_weight"], wts["bias"], shape, dt)
     assert torch.isfinite(out.float()).all()
     assert _fp8_sampled_check(moe, out, x, shape, dt, idx, w, 128, T, pow2) >= 320
