@@ -52,11 +52,12 @@ int g_bk32 = -1;         // see bk32_enabled()
 int g_down2 = -1;        // see down2_enabled()
 int g_force_bn = -2;     // see forced_bn_index()
 int g_fp8_mx = -1;       // hardware block scaling for FP8_BLOCK128_POW2 prefill: 0 off, 1 one CTA per tile
-                         // (umma_fp8_mx.cu), 2 CTA pairs (umma_fp8_mx2.cu); KNOB_FP8_MX / GLM4MOE_FP8_MX
+                         // (gate_up umma_fp8_mx_tm.cu, down umma_fp8_mx.cu), 2 CTA pairs (umma_fp8_mx2.cu),
+                         // 3 feature-major for both GEMMs; KNOB_FP8_MX / GLM4MOE_FP8_MX
 int fp8_mx_mode() {
   if (g_fp8_mx < 0) {
     const char* e = getenv("GLM4MOE_FP8_MX");
-    g_fp8_mx = (e && e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 1;
+    g_fp8_mx = (e && e[0] >= '0' && e[0] <= '3') ? e[0] - '0' : 1;
   }
   return g_fp8_mx;
 }
@@ -189,7 +190,7 @@ extern "C" int glm4moe_debug_set(int knob, int value) {
       g_router_rows = value;
       return GLM4MOE_OK;
     case GLM4MOE_KNOB_EP_FAST: g_ep_fast = value ? 1 : 0; return GLM4MOE_OK;
-    case GLM4MOE_KNOB_FP8_MX: g_fp8_mx = value < 0 || value > 2 ? 1 : value; return GLM4MOE_OK;
+    case GLM4MOE_KNOB_FP8_MX: g_fp8_mx = value < 0 || value > 3 ? 1 : value; return GLM4MOE_OK;
     case GLM4MOE_KNOB_BK32: g_bk32 = value ? 1 : 0; return GLM4MOE_OK;
     case GLM4MOE_KNOB_DOWN2: g_down2 = value ? 1 : 0; return GLM4MOE_OK;
     case GLM4MOE_KNOB_FORCE_TILE_ROWS:
@@ -636,7 +637,10 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
     a.up_row_offset = I;
     a.gated = 1;
     a.sched = reinterpret_cast<int32_t*>(ws + L.sched);
-    if ((rc = fp8_mx2 ? umma_fp8_mx2_launch(a, stream) : umma_fp8_mx_launch(a, stream))) return rc;
+    // gate_up: token-major (thread-local re-quantiser); down: feature-major (ragged tails cost their rows)
+    if ((rc = fp8_mx2 ? umma_fp8_mx2_launch(a, stream)
+              : fp8_mx_mode() == 3 ? umma_fp8_mx_launch(a, stream) : umma_fp8_mx_tm_launch(a, stream)))
+      return rc;
     STAGE_MARK(5);
     a.tm_w = &l->tm_w_d;
     a.tm_x = &l->tm_act[3];

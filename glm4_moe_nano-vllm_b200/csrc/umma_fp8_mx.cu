@@ -280,32 +280,58 @@ __global__ void __launch_bounds__(kXThreads, 1) umma_fp8_mx_kernel(
     // per k-group: 128 token words (one coalesced 512-byte read per 32-row block) and the two weight
     // slab words of this tile, written in the order tcgen05.cp.32x128b.warpx4 reads them
     pdl_wait();      // x_sf is the direct predecessor's output
+    // The words of group g + 1 are fetched into registers BEFORE group g is published, so the global-load
+    // latency of a group hides behind the previous group's slot wait (with the loads issued only after the
+    // publish, the MMA warp waited on sf_full 4-26 % of its time, profiles/r2k).
     const int wblocks = w_rows_per_expert / 128;
-    uint32_t gcount = 0;
-    for (int it = 0;; ++it) {
-      const int w = next_work(it);
-      if (w < 0) break;
-      const WorkRef tile = get_work<kXM>(tiles, w, n_feat_tiles, n_tiles, 0);
+    struct SfWords { uint32_t a[4], b0, b1; };
+    auto fetch = [&](const WorkRef& tile, int g) {
       const uint32_t* wb0 = w_sf + (static_cast<size_t>(tile.expert) * wblocks + (GATED ? tile.f : 2 * tile.f)) * n_kgroups;
       const uint32_t* wb1 = GATED ? wb0 + static_cast<size_t>(up_row_offset / 128) * n_kgroups : wb0 + n_kgroups;
-      for (int g = 0; g < n_kgroups; ++g, ++gcount) {
-        const int slot = gcount & 1u;
-        const uint32_t* xs = x_sf + static_cast<size_t>(g) * scale_ld;
-        uint32_t a[4];
+      const uint32_t* xs = x_sf + static_cast<size_t>(g) * scale_ld;
+      SfWords r;
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const int row = min(tile.row_start + i * 32 + lane, scale_ld - 1);   // rows past the tile: any in-bounds word
-          a[i] = __ldcg(xs + row);
+      for (int i = 0; i < 4; ++i) {
+        const int row = min(tile.row_start + i * 32 + lane, scale_ld - 1);   // rows past the tile: any in-bounds word
+        r.a[i] = __ldcg(xs + row);
+      }
+      r.b0 = __ldg(wb0 + g);
+      r.b1 = __ldg(wb1 + g);
+      return r;
+    };
+    uint32_t gcount = 0;
+    int it = 0;
+    int w = next_work(it);
+    if (w >= 0) {
+      WorkRef tile = get_work<kXM>(tiles, w, n_feat_tiles, n_tiles, 0);
+      int g = 0;
+      SfWords cur = fetch(tile, g);
+      for (;;) {
+        bool more = true;
+        WorkRef ntile = tile;
+        int ng = g + 1;
+        if (ng == n_kgroups) {
+          w = next_work(++it);
+          more = w >= 0;
+          ng = 0;
+          if (more) ntile = get_work<kXM>(tiles, w, n_feat_tiles, n_tiles, 0);
         }
-        const uint32_t b0 = __ldg(wb0 + g), b1 = __ldg(wb1 + g);
+        SfWords nxt = cur;
+        if (more) nxt = fetch(ntile, ng);
+        const int slot = gcount & 1u;
         mbar_wait(&sf_empty[slot], ((gcount >> 1) & 1u) ^ 1u);
         uint32_t* dst = sf_smem + slot * (kXM + kXN);
-        *reinterpret_cast<uint4*>(dst + lane * 4) = make_uint4(a[0], a[1], a[2], a[3]);
-        *reinterpret_cast<uint4*>(dst + 128 + lane * 4) = make_uint4(b0, b0, b0, b0);
-        *reinterpret_cast<uint4*>(dst + 256 + lane * 4) = make_uint4(b1, b1, b1, b1);
+        *reinterpret_cast<uint4*>(dst + lane * 4) = make_uint4(cur.a[0], cur.a[1], cur.a[2], cur.a[3]);
+        *reinterpret_cast<uint4*>(dst + 128 + lane * 4) = make_uint4(cur.b0, cur.b0, cur.b0, cur.b0);
+        *reinterpret_cast<uint4*>(dst + 256 + lane * 4) = make_uint4(cur.b1, cur.b1, cur.b1, cur.b1);
         fence_proxy_async();      // generic-proxy stores -> async-proxy (tcgen05.cp) reads
         __syncwarp();
         if (lane == 0) mbar_arrive(&sf_full[slot]);
+        ++gcount;
+        if (!more) break;
+        cur = nxt;
+        tile = ntile;
+        g = ng;
       }
     }
   } else if (warp >= 4) {

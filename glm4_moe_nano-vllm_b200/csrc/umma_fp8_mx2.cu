@@ -303,32 +303,57 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kYThreads, 1) umma_f
   } else if (warp == 3) {
     // ===================== scale-factor loader (both CTAs; signals the leader) =====================
     pdl_wait();      // x_sf is the direct predecessor's output
+    // group g + 1 is fetched into registers before group g is published (see umma_fp8_mx.cu)
     const int wblocks = w_rows_per_expert / 128;
-    uint32_t gcount = 0;
     const uint32_t sf_full_leader0 = mapa_u32(smem_u32(&sf_full[0]), 0);
-    for (int w = cluster_id; w < total_work; w += n_clusters) {
-      const WorkRef tile = get_work<256>(tiles, w, n_feat_tiles, n_tiles, 0);
+    struct SfWords { uint32_t a[4], b0, b1; };
+    auto fetch = [&](const WorkRef& tile, int g) {
       const uint32_t* wb0 = w_sf + (static_cast<size_t>(tile.expert) * wblocks + (GATED ? tile.f : 2 * tile.f)) * n_kgroups;
       const uint32_t* wb1 = GATED ? wb0 + static_cast<size_t>(up_row_offset / 128) * n_kgroups : wb0 + n_kgroups;
+      const uint32_t* xs = x_sf + static_cast<size_t>(g) * scale_ld;
       const int row0 = tile.row_start + static_cast<int>(rank) * kYM;
-      for (int g = 0; g < n_kgroups; ++g, ++gcount) {
-        const int slot = gcount & 1u;
-        const uint32_t* xs = x_sf + static_cast<size_t>(g) * scale_ld;
-        uint32_t a[4];
+      SfWords r;
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const int row = min(row0 + i * 32 + lane, scale_ld - 1);   // rows past the tile: any in-bounds word
-          a[i] = __ldcg(xs + row);
+      for (int i = 0; i < 4; ++i) {
+        const int row = min(row0 + i * 32 + lane, scale_ld - 1);   // rows past the tile: any in-bounds word
+        r.a[i] = __ldcg(xs + row);
+      }
+      r.b0 = __ldg(wb0 + g);
+      r.b1 = __ldg(wb1 + g);
+      return r;
+    };
+    uint32_t gcount = 0;
+    int w = cluster_id;
+    if (w < total_work) {
+      WorkRef tile = get_work<256>(tiles, w, n_feat_tiles, n_tiles, 0);
+      int g = 0;
+      SfWords cur = fetch(tile, g);
+      for (;;) {
+        bool more = true;
+        WorkRef ntile = tile;
+        int ng = g + 1;
+        if (ng == n_kgroups) {
+          w += n_clusters;
+          more = w < total_work;
+          ng = 0;
+          if (more) ntile = get_work<256>(tiles, w, n_feat_tiles, n_tiles, 0);
         }
-        const uint32_t b0 = __ldg(wb0 + g), b1 = __ldg(wb1 + g);
+        SfWords nxt = cur;
+        if (more) nxt = fetch(ntile, ng);
+        const int slot = gcount & 1u;
         mbar_wait_b(&sf_empty[slot], ((gcount >> 1) & 1u) ^ 1u, 5);
         uint32_t* dst = sf_smem + slot * (kYM + kYN);
-        *reinterpret_cast<uint4*>(dst + lane * 4) = make_uint4(a[0], a[1], a[2], a[3]);
-        *reinterpret_cast<uint4*>(dst + 128 + lane * 4) = make_uint4(b0, b0, b0, b0);
-        *reinterpret_cast<uint4*>(dst + 256 + lane * 4) = make_uint4(b1, b1, b1, b1);
+        *reinterpret_cast<uint4*>(dst + lane * 4) = make_uint4(cur.a[0], cur.a[1], cur.a[2], cur.a[3]);
+        *reinterpret_cast<uint4*>(dst + 128 + lane * 4) = make_uint4(cur.b0, cur.b0, cur.b0, cur.b0);
+        *reinterpret_cast<uint4*>(dst + 256 + lane * 4) = make_uint4(cur.b1, cur.b1, cur.b1, cur.b1);
         fence_proxy_async();      // generic-proxy stores -> async-proxy (tcgen05.cp) reads
         __syncwarp();
         if (lane == 0) mbar_arrive_cluster(sf_full_leader0 + 8u * slot);
+        ++gcount;
+        if (!more) break;
+        cur = nxt;
+        tile = ntile;
+        g = ng;
       }
     }
   } else if (warp >= 4) {

@@ -191,6 +191,8 @@ struct UmmaFp8MxLaunch {
   int32_t* sched;
 };
 int umma_fp8_mx_launch(const UmmaFp8MxLaunch& args, void* stream);
+// token-major form (umma_fp8_mx_tm.cu): tokens = MMA M, one N = 256 instruction per K slice; used for gate_up
+int umma_fp8_mx_tm_launch(const UmmaFp8MxLaunch& args, void* stream);
 // CTA-pair form (umma_fp8_mx2.cu, tcgen05 cta_group::2): 256-token x 256-weight-row tiles, `tiles` = 256-row tiles
 int umma_fp8_mx2_launch(const UmmaFp8MxLaunch& args, void* stream);
 // fp32 128x128 block scales [n_blocks, nkb] -> packed UE8M0 words [n_blocks, ceil(nkb/4)]; *bad (device int)

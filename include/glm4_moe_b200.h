@@ -77,9 +77,10 @@ enum { GLM4MOE_KNOB_DIRECT = 0, GLM4MOE_KNOB_FUSED = 1, GLM4MOE_KNOB_FP8_PREFILL
                                    epoch-parity buffers, ready flags from the expert kernel, no done round); must be
                                    the same on every rank (a mismatch traps with an error code instead of hanging) */,
        GLM4MOE_KNOB_FP8_MX = 8 /* FP8_BLOCK128_POW2 layers at prefill: 1 (default) = hardware block scaling, one CTA
-                                  per tile (umma_fp8_mx.cu); 2 = hardware block scaling on CTA pairs, 256-token x
-                                  256-row tiles (umma_fp8_mx2.cu, tcgen05 cta_group::2); 0 = the software-scaled
-                                  kernel on the same operands */ };
+                                  per tile (gate_up token-major umma_fp8_mx_tm.cu, down feature-major
+                                  umma_fp8_mx.cu); 2 = hardware block scaling on CTA pairs, 256-token x 256-row tiles
+                                  (umma_fp8_mx2.cu, tcgen05 cta_group::2); 3 = feature-major for both GEMMs;
+                                  0 = the software-scaled kernel on the same operands */ };
 int glm4moe_debug_set(int knob, int value);
 const char* glm4moe_error_string(int code);
 

@@ -773,7 +773,7 @@ def test_fp8_hardware_block_scaling_matches_software_scaling(shape_name, T):
     x = synth.make_tokens(shape, T, dt, 78).cuda()
     try:
         outs, n_launch = {}, {}
-        for name, knob in (("pair", 2), ("mx", 1), ("software", 0)):
+        for name, knob in (("pair", 2), ("mx", 1), ("feature_major", 3), ("software", 0)):
             _lib.check(lib.glm4moe_debug_set(8, knob))
             for rep in range(3):
                 out = moe(x).clone()
@@ -781,9 +781,11 @@ def test_fp8_hardware_block_scaling_matches_software_scaling(shape_name, T):
                 if rep:
                     assert torch.equal(out, outs[name]), f"{name}: run-to-run difference"
                 outs[name] = out
-        assert n_launch["mx"] == n_launch["software"] == n_launch["pair"], n_launch
+        assert n_launch["mx"] == n_launch["software"] == n_launch["pair"] == n_launch["feature_major"], n_launch
         b = outs["software"].float()
-        for name in ("mx", "pair"):           # pair: tcgen05 cta_group::2, 256-token x 256-row tiles (umma_fp8_mx2.cu)
+        # mx: gate_up token-major (umma_fp8_mx_tm.cu) + down feature-major (umma_fp8_mx.cu); feature_major: both
+        # GEMMs feature-major; pair: tcgen05 cta_group::2, 256-token x 256-row tiles (umma_fp8_mx2.cu)
+        for name in ("mx", "feature_major", "pair"):
             a = outs[name].float()
             rel = float((a - b).norm() / b.norm())
             nbad, _ = _close(outs[name], b.cpu(), 2e-2)
