@@ -3,11 +3,11 @@
 library for sm_100a (`csrc/`, header `include/glm4_moe_b200.h`).  No CPU fallback."""
 from . import synth  # noqa: F401
 
-__all__ = ["synth", "Glm4MoeMoE", "GlmMoeSelectTopk", "Glm4MoeMLP", "RMSNorm", "lib"]
+__all__ = ["synth", "Glm4MoeMoE", "GlmMoeSelectTopk", "Glm4MoeMLP", "Glm4MoeDenseMLP", "RMSNorm", "lib"]
 
 
 def __getattr__(name):
-    if name in ("Glm4MoeMoE", "GlmMoeSelectTopk", "Glm4MoeMLP"):
+    if name in ("Glm4MoeMoE", "GlmMoeSelectTopk", "Glm4MoeMLP", "Glm4MoeDenseMLP"):
         from . import moe
         return getattr(moe, name)
     if name == "RMSNorm":

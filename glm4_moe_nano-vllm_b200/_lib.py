@@ -21,7 +21,7 @@ DTYPE_CODE = {torch.float32: F32, torch.float16: F16, torch.bfloat16: BF16}
 SYMBOLS = [
     "glm4moe_abi_version", "glm4moe_debug_set", "glm4moe_error_string", "glm4moe_router_logits", "glm4moe_router_select",
     "glm4moe_route_small", "glm4moe_permute", "glm4moe_permute_scratch_elems", "glm4moe_tile_capacity", "glm4moe_gather_rows",
-    "glm4moe_expert_gate_up_simt", "glm4moe_expert_down_simt", "glm4moe_combine",
+    "glm4moe_expert_gate_up_simt", "glm4moe_expert_down_simt", "glm4moe_mlp_forward", "glm4moe_combine",
     "glm4moe_workspace_bytes", "glm4moe_layer_create", "glm4moe_layer_destroy",
     "glm4moe_layer_forward", "glm4moe_layer_forward_ex", "glm4moe_layer_forward_timed", "glm4moe_layer_forward_host", "glm4moe_layer_view",
     "glm4moe_layer_last_launches", "glm4moe_layer_last_impl", "glm4moe_layer_last_fused", "glm4moe_layer_tile_rows",
@@ -74,6 +74,7 @@ def load() -> C.CDLL:
     lib.glm4moe_gather_rows.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp]
     lib.glm4moe_expert_gate_up_simt.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, vp]
     lib.glm4moe_expert_down_simt.argtypes = [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp]
+    lib.glm4moe_mlp_forward.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, vp, vp]
     lib.glm4moe_combine.argtypes = [vp, vp, vp, i32, i32, i32, i32, i32, i32, vp]
     lib.glm4moe_workspace_bytes.restype = sz
     lib.glm4moe_workspace_bytes.argtypes = [C.POINTER(Config)]

@@ -856,6 +856,68 @@ extern "C" int glm4moe_layer_forward_timed(glm4moe_layer_t* l, const void* x, vo
   return GLM4MOE_OK;
 }
 
+// Dense SiLU-gated MLP on the tensor-core grouped GEMM: one weight pair, all T rows ("tiles == nullptr"
+// path of umma_grouped_kernel, the form the router GEMM already uses).  Stateless: tensor maps are
+// encoded per call on the host, the only device state is `sched` (4 self re-arming ints).
+extern "C" int glm4moe_mlp_forward(const void* x, const void* w_gate_up, const void* w_down, void* act_ws,
+                                   void* out, int T, int H, int I, int dtype, int32_t* sched, void* stream) {
+  if (!x || !w_gate_up || !w_down || !act_ws || !out || !sched || T < 0 || H <= 0 || I <= 0) return GLM4MOE_ERR_ARG;
+  if (T == 0) return GLM4MOE_OK;
+  // 2-byte dtypes; K of the first GEMM in whole 64-element blocks; row pitches 16-byte aligned for TMA.
+  // I need not be a multiple of 128 (Air's dense layer: 10944): the ragged last feature tile is bounded
+  // in the epilogue and the ragged last K block of the down GEMM is zero-filled by TMA on both operands.
+  if ((dtype != GLM4MOE_BF16 && dtype != GLM4MOE_F16) || H % 128 != 0 || I % 8 != 0) return GLM4MOE_ERR_UNSUPPORTED;
+  int dev = 0, sms = 148;
+  if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int bn = T <= 16 ? 16 : T <= 32 ? 32 : T <= 64 ? 64 : T <= 128 ? 128 : 256;
+  alignas(64) CUtensorMap tm_wgu, tm_wd, tm_xin, tm_act;
+  int rc;
+  if ((rc = umma_make_tensor_map(&tm_wgu, w_gate_up, dtype, static_cast<uint64_t>(2) * I, H, 128))) return rc;
+  if ((rc = umma_make_tensor_map(&tm_wd, w_down, dtype, static_cast<uint64_t>(H), I, 128))) return rc;
+  if ((rc = umma_make_tensor_map(&tm_xin, x, dtype, static_cast<uint64_t>(T), H, bn))) return rc;
+  if ((rc = umma_make_tensor_map(&tm_act, act_ws, dtype, static_cast<uint64_t>(T), I, bn))) return rc;
+  UmmaLaunch a{};
+  a.tiles = nullptr;
+  a.num_tiles = nullptr;
+  a.dense_rows = T;
+  a.tile_rows = bn;
+  a.dtype = dtype;
+  a.grid = sms;
+  a.row_weight = nullptr;
+  a.n_routed_rows = 0;          // every row takes weight 1
+  // gate_up + SiLU*mul (mlp.py:50-51)
+  a.tm_w = &tm_wgu;
+  a.tm_x = &tm_xin;
+  a.out = act_ws;
+  a.ld_out = I;
+  a.n_feat_tiles = (I + 127) / 128;
+  a.n_feat_valid = I;
+  a.n_kblocks = H / 64;
+  a.w_rows_per_expert = 2 * I;
+  a.up_row_offset = I;
+  a.mode = 1;
+  a.sched = sched;
+  if ((rc = umma_launch(a, stream))) return rc;
+  // down (mlp.py:52)
+  a.tm_w = &tm_wd;
+  a.tm_x = &tm_act;
+  a.out = out;
+  a.ld_out = H;
+  a.n_feat_tiles = H / 128;
+  a.n_feat_valid = H;
+  a.n_kblocks = (I + 63) / 64;
+  a.w_rows_per_expert = H;
+  a.up_row_offset = 0;
+  a.mode = 0;
+  if (bn == 256 && H % 256 == 0 && down2_enabled()) {
+    a.mode = 3;
+    a.n_feat_tiles = H / 256;
+    a.up_row_offset = 128;
+  }
+  a.sched = sched + 2;
+  return umma_launch(a, stream);
+}
+
 extern "C" int glm4moe_layer_forward_host(glm4moe_layer_t* l, const void* x_host, void* out_host, int T,
                                           void* x_dev_staging, void* out_dev_staging, void* stream) {
   if (!l || !x_host || !out_host || !x_dev_staging || !out_dev_staging) return GLM4MOE_ERR_ARG;

@@ -341,7 +341,9 @@ __global__ void __launch_bounds__(UmmaCfg<BN, MODE, BK>::kThreads, 1) umma_group
       tc_fence_after();
       const uint32_t t_acc = tmem_base + lane_base + as * Cfg::kAccCols;
       const int feat = wr.f * Cfg::kFeatPerTile + ew * 32 + lane;
-      const bool feat_ok = MODE != kModePlain || feat < n_feat_valid;
+      // output features past n_feat_valid (the ragged last feature tile of a dense MLP whose width is not a
+      // multiple of 128, or the router's E) are computed on whatever rows the box covers and not stored
+      const bool feat_ok = feat < n_feat_valid;
       T* out_col = out + static_cast<size_t>(wr.row_start) * ld_out + feat;
 #pragma unroll 1
       const int n_cols = (MODE == kModeGated && direct.tokens > 0) ? direct.tokens : wr.nrows;
@@ -358,7 +360,7 @@ __global__ void __launch_bounds__(UmmaCfg<BN, MODE, BK>::kThreads, 1) umma_group
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
               const uint32_t m = __ballot_sync(0xffffffffu, tok_lane == c0 + j);
-              if (m) {
+              if (m && feat_ok) {
                 const float v = silu_fast(__uint_as_float(g[j])) * __uint_as_float(u[j]);
                 out_col[static_cast<size_t>(__ffs(m) - 1) * ld_out] = Dt<T>::from_f(v);
               }
@@ -366,7 +368,7 @@ __global__ void __launch_bounds__(UmmaCfg<BN, MODE, BK>::kThreads, 1) umma_group
           } else {
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
-              if (c0 + j < wr.nrows) {
+              if (c0 + j < wr.nrows && feat_ok) {
                 const float v = silu_fast(__uint_as_float(g[j])) * __uint_as_float(u[j]);
                 out_col[static_cast<size_t>(c0 + j) * ld_out] = Dt<T>::from_f(v);
               }
@@ -386,8 +388,8 @@ __global__ void __launch_bounds__(UmmaCfg<BN, MODE, BK>::kThreads, 1) umma_group
           for (int j = 0; j < 16; ++j) {
             const float rw = __shfl_sync(0xffffffffu, rw_lane, j);
             if (c0 + j < wr.nrows) {
-              out_col[static_cast<size_t>(c0 + j) * ld_out] = Dt<T>::from_f(__uint_as_float(g[j]) * rw);
-              if (MODE == kModeDown2)
+              if (feat_ok) out_col[static_cast<size_t>(c0 + j) * ld_out] = Dt<T>::from_f(__uint_as_float(g[j]) * rw);
+              if (MODE == kModeDown2 && feat + kBM < n_feat_valid)
                 out_col[static_cast<size_t>(c0 + j) * ld_out + kBM] = Dt<T>::from_f(__uint_as_float(g2[j]) * rw);
             }
           }

@@ -143,14 +143,16 @@ def shim_model_runner(config, rank, event):
 
 
 def install(sparse_block: str = "ours", weight_format: str = "native", share_workspace: bool = True,
-            expert_parallel: str | None = None):
+            expert_parallel: str | None = None, dense_mlp: str = "reference"):
     """Import the reference package and apply the construction-time rebinding described above.
     `sparse_block`: "ours" (this package's `Glm4MoeMoE`) or "reference" (the reference's own block, for
     A/B runs of the same stack).  `expert_parallel`: layout of the sparse blocks when the engine runs
     `tensor_parallel_size > 1` ranks ("p2p": peer-memory combine, "allreduce": NCCL; None: every rank holds
-    all experts).  Returns the `nanovllm` package."""
+    all experts).  `dense_mlp`: "ours" also swaps the dense MLP of the first layers (decode_layer.py:31-36) for
+    `Glm4MoeDenseMLP` (the same tensor-core grouped GEMM).  Returns the `nanovllm` package."""
     os.environ[ENV_ARGS] = json.dumps(dict(sparse_block=sparse_block, weight_format=weight_format,
-                                           share_workspace=share_workspace, expert_parallel=expert_parallel))
+                                           share_workspace=share_workspace, expert_parallel=expert_parallel,
+                                           dense_mlp=dense_mlp))
     _installed["ep_layout"] = expert_parallel if sparse_block == "ours" else None
     root = reference_root()
     if root is None:
@@ -183,6 +185,7 @@ def install(sparse_block: str = "ours", weight_format: str = "native", share_wor
     from nanovllm.engine import llm_engine as LE
     from nanovllm.engine import model_runner as MR
     if "ref_block" not in _installed:
+        _installed["ref_dense"] = DL.Glm4MoeMLP
         _installed["ref_block"] = ref_moe.Glm4MoeMoE
         _installed["post_init"] = ref_config.Config.__post_init__
         _installed["runner"] = MR.ModelRunner
@@ -202,6 +205,9 @@ def install(sparse_block: str = "ours", weight_format: str = "native", share_wor
         DL.Glm4MoeMoE = _installed["ref_block"]
     else:
         raise ValueError(sparse_block)
+    if dense_mlp not in ("ours", "reference"):
+        raise ValueError(dense_mlp)
+    DL.Glm4MoeMLP = ours.Glm4MoeDenseMLP if dense_mlp == "ours" else _installed["ref_dense"]   # decode_layer.py:7,31
 
     def model_init(self, config):                            # model.py:14-24 with the line of model.py:19
         nn.Module.__init__(self)

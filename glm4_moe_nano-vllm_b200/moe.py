@@ -49,31 +49,125 @@ class Glm4MoeMLP(nn.Module):
         self.down_proj = _Weight(down_view)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        """mlp.py:49-54 for one expert, through the CUDA-core expert kernels (exact path)."""
-        lib = _lib.load()
+        """mlp.py:49-54 for one expert: the tensor-core dense path (`glm4moe_mlp_forward`) for bf16 / fp16
+        weights whose shape it covers, else the CUDA-core expert kernels (exact fp32-FMA path)."""
         wgu, wd = self.gate_up_proj.weight, self.down_proj.weight
         x2 = x.reshape(-1, x.shape[-1]).contiguous()
         _lib.require_cuda(x2, "x")
-        n, H = x2.shape
-        I = wd.shape[1]
-        dt = _lib.DTYPE_CODE[x2.dtype]
-        dev = x2.device
-        ntile = (n + 7) // 8
-        tiles = torch.tensor([[0, 8 * i, min(8, n - 8 * i), 0] for i in range(ntile)], dtype=torch.int32,
-                             device=dev).reshape(-1, 4)
-        num = torch.tensor([ntile], dtype=torch.int32, device=dev)
-        act = torch.empty((n, I), dtype=x2.dtype, device=dev)
-        y = torch.empty((n, H), dtype=x2.dtype, device=dev)
-        ones = torch.ones(max(n, 1), dtype=torch.float32, device=dev)
-        st = _lib.stream_ptr(dev)
-        if n:
-            _lib.check(lib.glm4moe_expert_gate_up_simt(x2.data_ptr(), wgu.data_ptr(), tiles.data_ptr(),
-                                                       num.data_ptr(), act.data_ptr(), H, I, 8, dt, st), "gate_up")
-            # T*k = n with k = 1 so every row takes its weight (1.0) from `ones`
-            _lib.check(lib.glm4moe_expert_down_simt(act.data_ptr(), wd.data_ptr(), tiles.data_ptr(),
-                                                    num.data_ptr(), ones.data_ptr(), y.data_ptr(), H, I, n, 1,
-                                                    8, dt, st), "down")
+        return dense_mlp_forward(x2, wgu, wd, self)
+
+
+def dense_mlp_forward(x2: torch.Tensor, wgu: torch.Tensor, wd: torch.Tensor, owner=None, impl: str = "auto"):
+    """`down(silu(gate(x)) * up(x))` of ONE weight pair (mlp.py:49-54) on `x2 [n, H]`.  `impl`: "auto" picks
+    the tcgen05 dense path where `glm4moe_mlp_forward` supports the shape (2-byte dtype, H % 128 == 0,
+    I % 8 == 0), "simt" forces the CUDA-core kernels, "umma" insists on the tensor cores."""
+    lib = _lib.load()
+    n, H = x2.shape
+    I = wd.shape[1]
+    dt = _lib.DTYPE_CODE[x2.dtype]
+    dev = x2.device
+    act = torch.empty((n, I), dtype=x2.dtype, device=dev)
+    y = torch.empty((n, H), dtype=x2.dtype, device=dev)
+    if n == 0:
         return y
+    tc_ok = x2.dtype in (torch.bfloat16, torch.float16) and H % 128 == 0 and I % 8 == 0 and wgu.dtype == x2.dtype
+    if impl == "umma" and not tc_ok:
+        raise _lib.Glm4MoeLibraryError(f"dense tensor-core MLP does not cover H={H}, I={I}, {x2.dtype}")
+    st = _lib.stream_ptr(dev)
+    if tc_ok and impl != "simt":
+        # 4 self re-arming counters, zeroed once per (owner, device)
+        sched = getattr(owner, "_dense_sched", None) if owner is not None else None
+        if sched is None or sched.device != dev:
+            sched = torch.zeros(4, dtype=torch.int32, device=dev)
+            if owner is not None:
+                object.__setattr__(owner, "_dense_sched", sched)
+        with torch.cuda.device(dev):
+            _lib.check(lib.glm4moe_mlp_forward(x2.data_ptr(), wgu.data_ptr(), wd.data_ptr(), act.data_ptr(),
+                                               y.data_ptr(), n, H, I, dt, sched.data_ptr(), st), "mlp_forward")
+        return y
+    ntile = (n + 7) // 8
+    tiles = torch.tensor([[0, 8 * i, min(8, n - 8 * i), 0] for i in range(ntile)], dtype=torch.int32,
+                         device=dev).reshape(-1, 4)
+    num = torch.tensor([ntile], dtype=torch.int32, device=dev)
+    ones = torch.ones(n, dtype=torch.float32, device=dev)
+    _lib.check(lib.glm4moe_expert_gate_up_simt(x2.data_ptr(), wgu.data_ptr(), tiles.data_ptr(),
+                                               num.data_ptr(), act.data_ptr(), H, I, 8, dt, st), "gate_up")
+    # T*k = n with k = 1 so every row takes its weight (1.0) from `ones`
+    _lib.check(lib.glm4moe_expert_down_simt(act.data_ptr(), wd.data_ptr(), tiles.data_ptr(),
+                                            num.data_ptr(), ones.data_ptr(), y.data_ptr(), H, I, n, 1,
+                                            8, dt, st), "down")
+    return y
+
+
+class Glm4MoeDenseMLP(nn.Module):
+    """The DENSE MLP of the decoder stack's first layers (`decode_layer.py:31-36` constructs the reference's
+    `Glm4MoeMLP(hidden_size, intermediate_size, hidden_act, prefix=...)`, `mlp.py:12-54`) through the same
+    tensor-core grouped GEMM as the experts ("the E = 1 case").  Same constructor, parameter
+    names (`gate_up_proj.weight [2I/tp, H]`, `down_proj.weight [H, I/tp]`) and `load_weights(path, prefix)`
+    as the reference class; tensor parallel like its `MergedColumnParallelLinear` / `RowParallelLinear`
+    (`linear.py:79-155`): rank r holds rows [r*I/tp, (r+1)*I/tp) of gate and of up and the matching columns of
+    down, and the partial outputs are summed with `dist.all_reduce` (`linear.py:153-154`)."""
+
+    def __init__(self, hidden_size: int, intermediate_size: int, hidden_act: str = "silu", quant_config=None,
+                 reduce_results: bool = True, prefix: str = "", tp_rank: int | None = None, tp_size: int | None = None):
+        super().__init__()
+        if hidden_act.lower() != "silu":      # mlp.py:41-44
+            raise ValueError(f"Unsupported activation: {hidden_act}. Only silu is supported for now.")
+        import torch.distributed as dist
+        live = dist.is_available() and dist.is_initialized()
+        self.tp_size = tp_size if tp_size is not None else (dist.get_world_size() if live else 1)
+        self.tp_rank = tp_rank if tp_rank is not None else (dist.get_rank() if live else 0)
+        if intermediate_size % self.tp_size:
+            raise ValueError(f"intermediate_size={intermediate_size} not divisible by tp_size={self.tp_size}")
+        self.hidden_size, self.intermediate_size = hidden_size, intermediate_size
+        self.local_intermediate = intermediate_size // self.tp_size
+        self.reduce_results = reduce_results
+        self.prefix = prefix
+        self.impl = "auto"
+        self.gate_up_proj = _Weight(torch.empty((2 * self.local_intermediate, hidden_size)))
+        self.down_proj = _Weight(torch.empty((hidden_size, self.local_intermediate)))
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        x2 = x.reshape(-1, x.shape[-1])
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        _lib.require_cuda(x2, "x")
+        y = dense_mlp_forward(x2, self.gate_up_proj.weight, self.down_proj.weight, self, self.impl)
+        if self.tp_size > 1 and self.reduce_results:
+            import torch.distributed as dist
+            dist.all_reduce(y)
+        return y.reshape(*x.shape[:-1], self.hidden_size)
+
+    def load_weights(self, model_path: str, prefix: str | None = None):
+        """`{prefix}.gate_proj|up_proj|down_proj.weight` of an HF-layout checkpoint (a `.safetensors` file or a
+        directory of them), the keys the reference loader reads (`mlp.py:83-131`); one pass, exact-key match,
+        this rank's shard only."""
+        import os
+        from safetensors import safe_open
+        prefix = self.prefix if prefix is None else prefix
+        files = [model_path] if os.path.isfile(model_path) else \
+            [os.path.join(model_path, f) for f in sorted(os.listdir(model_path)) if f.endswith(".safetensors")]
+        Il, r = self.local_intermediate, self.tp_rank
+        seen = set()
+        with torch.no_grad():
+            for fn in files:
+                with safe_open(fn, framework="pt", device="cpu") as f:
+                    keys = set(f.keys())
+                    for proj in ("gate_proj", "up_proj", "down_proj"):
+                        key = f"{prefix}.{proj}.weight"
+                        if key not in keys:
+                            continue
+                        if proj == "down_proj":
+                            t = f.get_slice(key)[:, r * Il:(r + 1) * Il]
+                            self.down_proj.weight.copy_(t)
+                        else:
+                            t = f.get_slice(key)[r * Il:(r + 1) * Il, :]
+                            dst = self.gate_up_proj.weight[:Il] if proj == "gate_proj" else self.gate_up_proj.weight[Il:]
+                            dst.copy_(t)
+                        seen.add(proj)
+        missing = {"gate_proj", "up_proj", "down_proj"} - seen
+        if missing:
+            raise ValueError(f"No tensors {sorted(missing)} with prefix '{prefix}' found in '{model_path}'")
 
 
 class GlmMoeSelectTopk(nn.Module):

@@ -141,6 +141,15 @@ int glm4moe_expert_down_simt(const void* act, const void* w_down, const int32_t*
                              const int32_t* num_tiles, const float* row_weight, void* y, int H,
                              int I, int T, int k, int tile_rows, int dtype, void* stream);
 
+/* Dense SiLU-gated MLP on the tensor cores: replaces Glm4MoeMLP.forward (mlp.py:49-54) for ONE weight pair, e.g.
+ * the dense layer-0 MLP of the decoder stack (decode_layer.py:31-36; Air: I = 10944) or a single expert.
+ * x [T, H], w_gate_up [2I, H] (rows [0,I) gate, [I,2I) up), w_down [H, I], out [T, H], all in `dtype` (bf16 / fp16);
+ * act_ws: [T, I] scratch; sched: 4 int32 zero-initialised once by the caller (the kernels re-arm them).
+ * H % 128 == 0, I % 8 == 0 (I need not be a multiple of 128 or 64).  GLM4MOE_ERR_UNSUPPORTED otherwise: the
+ * caller keeps the exact CUDA-core entries above for fp32 / odd shapes. */
+int glm4moe_mlp_forward(const void* x, const void* w_gate_up, const void* w_down, void* act_ws, void* out, int T,
+                        int H, int I, int dtype, int32_t* sched, void* stream);
+
 /* ---- combine: replaces index_add_ + shared add (moe.py:151,171) ----------------------------- */
 /* out[t] = sum_{slot, ascending expert} y[slot_row[t,slot]] (+ y[T*k+t] for t in
  * [shared_lo, shared_hi)); fp32 accumulate.                                                     */

@@ -51,10 +51,12 @@ def main():
                     "tensor-parallel as the reference's layers do it, sparse blocks expert-parallel (--ep)")
     ap.add_argument("--ep", default="p2p", choices=["p2p", "allreduce", "none"],
                     help="layout of the sparse blocks when --tp > 1 (none: every rank holds all experts)")
+    ap.add_argument("--dense", default="reference", choices=["ours", "reference"],
+                    help="dense MLP of layer 0 (decode_layer.py:31-36): ours = Glm4MoeDenseMLP (tensor-core grouped GEMM)")
     args = ap.parse_args()
 
     nanovllm = S.install(sparse_block=args.block, weight_format=args.weights if args.weights != "bf16" else "native",
-                         expert_parallel=None if args.ep == "none" or args.tp == 1 else args.ep)
+                         expert_parallel=None if args.ep == "none" or args.tp == 1 else args.ep, dense_mlp=args.dense)
     geom = dict(S.AIR_MODEL if args.preset == "air" else SMALL)
     d = args.model_dir or tempfile.mkdtemp(prefix="glm4moe_model_")
     S.make_model_dir(d, num_hidden_layers=args.layers, max_position_embeddings=max(args.max_model_len, 512), **geom)
@@ -96,6 +98,8 @@ def main():
     line = {"what": "decoder stack through the reference engine (nanovllm.LLM) with the sparse block swapped in",
             "preset": args.preset, "layers": args.layers, "moe_layers": len(mlps) - 1, "block": args.block,
             "weights": args.weights, "cuda_graph_decode": not args.eager, "seqs": args.seqs,
+            "dense_mlp": type(llm.model_runner.model.model.layers[0].mlp).__module__.split(".")[0] + "." +
+            type(llm.model_runner.model.model.layers[0].mlp).__name__,
             "ranks": args.tp, "parallelism": "single" if args.tp == 1 else
             f"tp{args.tp} attention + dense MLP (reference layers, NCCL all-reduce), sparse blocks " +
             ("replicated" if args.ep == "none" else f"ep{args.tp}-{args.ep}"),

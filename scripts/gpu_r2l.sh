@@ -19,4 +19,3 @@ except Exception as e:
 PY
 done; done
 timeout -k 10 600 python -m pytest tests/test_gpu_parity.py -m gpu -q --timeout=300 -p no:cacheprovider -k "fp8_air_prefill or glm45" > gpurun_out/r2l_pytest_fp8.log 2>&1; echo "rc=$?"; tail -4 gpurun_out/r2l_pytest_fp8.log
-bash scripts/gpu_sanitizer.sh memcheck

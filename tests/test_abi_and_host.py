@@ -260,3 +260,43 @@ def test_apply_after_dropping_the_native_stacks():
     assert moe._w_gate_up.numel() == 0 and moe.experts[0].gate_up_proj.weight.numel() == 0
     assert moe._wq_gate_up.shape == (shape.E + 1, 2 * shape.I, shape.H)
     assert moe.gate.e_score_correction_bias.dtype == torch.float32
+
+
+def test_dense_mlp_mirrors_the_reference_class_and_shards_like_its_linear_layers(tmp_path):
+    """`Glm4MoeDenseMLP`: the reference dense class's constructor and parameter names
+    (mlp.py:12-47), `load_weights(path, prefix)` from the HF keys, tensor-parallel shards = the rows of gate / up
+    and the columns of down that `MergedColumnParallelLinear` / `RowParallelLinear` give rank r
+    (linear.py:79-155); CPU tensors are refused loudly."""
+    from safetensors.torch import save_file
+    H, I = 256, 200
+    g = torch.Generator().manual_seed(5)
+    w = {k_: (torch.randn(s, generator=g) * 0.05).to(torch.bfloat16)
+         for k_, s in (("gate_proj", (I, H)), ("up_proj", (I, H)), ("down_proj", (H, I)))}
+    p = "model.layers.0.mlp"
+    save_file({f"{p}.{k_}.weight": v for k_, v in w.items()} | {f"{p}x.gate_proj.weight": w["gate_proj"] * 0},
+              str(tmp_path / "m.safetensors"))
+    prev = torch.get_default_dtype()
+    torch.set_default_dtype(torch.bfloat16)
+    try:
+        one = glm4_moe_b200.Glm4MoeDenseMLP(hidden_size=H, intermediate_size=I, hidden_act="silu", prefix=p)
+        shards = [glm4_moe_b200.Glm4MoeDenseMLP(H, I, "silu", prefix=p, tp_rank=r, tp_size=2) for r in range(2)]
+        with pytest.raises(ValueError):
+            glm4_moe_b200.Glm4MoeDenseMLP(H, I, "gelu")
+    finally:
+        torch.set_default_dtype(prev)
+    assert [n for n, _ in one.named_parameters()] == ["gate_up_proj.weight", "down_proj.weight"]
+    assert one.gate_up_proj.weight.shape == (2 * I, H) and one.down_proj.weight.dtype == torch.bfloat16
+    one.load_weights(str(tmp_path), p)
+    assert torch.equal(one.gate_up_proj.weight, torch.cat([w["gate_proj"], w["up_proj"]]))
+    assert torch.equal(one.down_proj.weight, w["down_proj"])
+    for r, m in enumerate(shards):
+        m.load_weights(str(tmp_path / "m.safetensors"))
+        sl = slice(r * I // 2, (r + 1) * I // 2)
+        assert torch.equal(m.gate_up_proj.weight, torch.cat([w["gate_proj"][sl], w["up_proj"][sl]]))
+        assert torch.equal(m.down_proj.weight, w["down_proj"][:, sl])
+    with pytest.raises(ValueError):
+        one.load_weights(str(tmp_path), "model.layers.9.mlp")
+    with pytest.raises(_lib.Glm4MoeLibraryError):
+        one(torch.zeros(3, H, dtype=torch.bfloat16))
+    lib = _lib.load()
+    assert lib.glm4moe_mlp_forward(None, None, None, None, None, 4, 256, 200, _lib.BF16, None, None) == -1

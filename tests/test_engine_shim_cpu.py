@@ -122,7 +122,7 @@ def test_multi_rank_plumbing(tmp_path):
     assert llm_engine.ModelRunner is S.shim_model_runner
     assert pickle.loads(pickle.dumps(S.shim_model_runner)) is S.shim_model_runner
     assert json.loads(os.environ[S.ENV_ARGS]) == dict(sparse_block="ours", weight_format="fp8", share_workspace=True,
-                                                      expert_parallel="p2p")
+                                                      expert_parallel="p2p", dense_mlp="reference")
     d = S.make_model_dir(str(tmp_path / "m"), **SMALL)
     from nanovllm.config import Config
     cfg = pickle.loads(pickle.dumps(Config(d, max_num_batched_tokens=512, max_model_len=256)))

@@ -1049,3 +1049,44 @@ def test_rmsnorm_vs_reference_golden(name):
     with torch.inference_mode():
         again, _ = norm(x, res)
     assert torch.equal(again, y1[0])
+
+
+# ------------------------------------------------------------------------------------------
+# dense MLP through the tensor-core grouped GEMM (SURVEY 8f-2 part ii; decode_layer.py:31-36)
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("H,I,dt,Ts", [
+    (4096, 10944, torch.bfloat16, (1, 33, 200, 1024)),     # GLM-4.5-Air dense layer 0: I = 85.5 x 128
+    (4096, 1368, torch.bfloat16, (7, 300)),                # its tensor-parallel shard at 8 ranks: K tail of 24
+    (256, 200, torch.float16, (5, 129)),                   # everything ragged
+])
+def test_dense_mlp_tensor_cores_vs_oracle(H, I, dt, Ts):
+    """`glm4moe_mlp_forward` (one weight pair, all rows, `tiles == nullptr` path of umma_grouped_kernel) against
+    the fp32 evaluation of mlp.py:49-54 (oracle.expert_mlp) and against the CUDA-core exact path."""
+    from glm4_moe_b200.moe import Glm4MoeDenseMLP, dense_mlp_forward
+    g = torch.Generator().manual_seed(H + I)
+    prev = torch.get_default_dtype()
+    torch.set_default_dtype(dt)
+    try:
+        m = Glm4MoeDenseMLP(H, I, "silu", tp_rank=0, tp_size=1)
+    finally:
+        torch.set_default_dtype(prev)
+    with torch.no_grad():
+        m.gate_up_proj.weight.copy_((torch.randn((2 * I, H), generator=g) * 0.02).to(dt))
+        m.down_proj.weight.copy_((torch.randn((H, I), generator=g) * 0.02).to(dt))
+    m = m.cuda()
+    m.impl = "umma"
+    for T in Ts:
+        x = torch.randn((T, H), generator=g).to(dt)
+        with torch.inference_mode():
+            y = m(x.cuda())
+            y2 = m(x.cuda())
+            assert torch.equal(y, y2)                      # deterministic, counters re-armed
+            truth = O.expert_mlp(x.float(), m.gate_up_proj.weight.float().cpu(), m.down_proj.weight.float().cpu())
+            nbad, rel = _close(y, truth, RTOL_BF16)
+            assert nbad == 0 and rel < 6e-3, (T, nbad, rel)
+            if T <= 64:
+                ys = dense_mlp_forward(x.cuda(), m.gate_up_proj.weight, m.down_proj.weight, impl="simt")
+                nbad, rel = _close(y, ys.float().cpu(), RTOL_BF16)
+                assert nbad == 0 and rel < 6e-3, ("vs simt", T, nbad, rel)
+    # a 3-D input keeps its leading shape (decode_layer.py:100 passes [T, H]; the reference linear layers accept any)
+    assert m(torch.zeros((2, 3, H), dtype=dt, device="cuda")).shape == (2, 3, H)
