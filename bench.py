@@ -79,19 +79,28 @@ class ClockSampler:
         except Exception:
             self._nv = None
 
-    def _run(self):
+    NAMES = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "hw_thermal_slowdown": 0x40,
+             "sw_thermal_slowdown": 0x20, "hw_power_brake": 0x80}
+
+    def sample_now(self):
+        """One synchronous sample.  The main thread calls it right after the timed steps are ENQUEUED (the GPU is
+        then still inside the timed region): a 3 ms region (20 steps at 8 GPUs) otherwise races the sampler thread,
+        which has to win the GIL from the launching thread."""
         nv = self._nv
-        names = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "hw_thermal_slowdown": 0x40,
-                 "sw_thermal_slowdown": 0x20, "hw_power_brake": 0x80}
+        if nv is None:
+            return
+        try:
+            self.samples.append(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM))
+            r = nv.nvmlDeviceGetCurrentClocksEventReasons(self._h)
+            for n, bit in self.NAMES.items():
+                if r & bit:
+                    self.reasons.add(n)
+        except Exception:
+            pass
+
+    def _run(self):
         while not self._stop.is_set():
-            try:
-                self.samples.append(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM))
-                r = nv.nvmlDeviceGetCurrentClocksEventReasons(self._h)
-                for n, bit in names.items():
-                    if r & bit:
-                        self.reasons.add(n)
-            except Exception:
-                pass
+            self.sample_now()
             time.sleep(0.001)
 
     def start(self):
@@ -327,6 +336,7 @@ def main():
         for i in range(args.steps):
             step(batches[i % n_batches])
         end.record()
+        clk.sample_now()              # the queue is still draining: inside the timed region
         torch.cuda.synchronize()
         clocks = clk.summary()
         if world > 1:

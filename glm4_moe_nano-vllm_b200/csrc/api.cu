@@ -61,6 +61,7 @@ int fp8_mx_mode() {
   }
   return g_fp8_mx;
 }
+int g_merge_front = 1;   // T <= 2: router front-end inside the persistent decode kernel (one launch per layer), KNOB_MERGE_FRONT
 int g_ep_fast = 1;       // decode fast path of the peer-memory combine (one rendezvous per step), KNOB_EP_FAST
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
@@ -190,6 +191,7 @@ extern "C" int glm4moe_debug_set(int knob, int value) {
       g_router_rows = value;
       return GLM4MOE_OK;
     case GLM4MOE_KNOB_EP_FAST: g_ep_fast = value ? 1 : 0; return GLM4MOE_OK;
+    case GLM4MOE_KNOB_MERGE_FRONT: g_merge_front = value ? 1 : 0; return GLM4MOE_OK;
     case GLM4MOE_KNOB_FP8_MX: g_fp8_mx = value < 0 || value > 3 ? 1 : value; return GLM4MOE_OK;
     case GLM4MOE_KNOB_BK32: g_bk32 = value ? 1 : 0; return GLM4MOE_OK;
     case GLM4MOE_KNOB_DOWN2: g_down2 = value ? 1 : 0; return GLM4MOE_OK;
@@ -487,6 +489,9 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
   alignas(64) CUtensorMap tm_xdirect;
   bool combine_done = false;
   const bool ep_fast = epf != nullptr && rows_only && direct && fused_enabled();
+  // T <= 2: the front-end runs inside the persistent kernel (decode_fused.cu, RouteMerged): one launch per layer
+  const bool merged = direct && fused_enabled() && !fp8 && !rows_only && T <= 2 && T * k <= 32 && E <= 256 &&
+                      g_merge_front != 0 && ev == nullptr;
   if (ep_fast_used) *ep_fast_used = ep_fast;
   STAGE_MARK(0);
   if (direct) {
@@ -494,6 +499,7 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
       return rc;
     RouteSmallEp rep{};
     rep.act_pow2 = pow2;
+    if (!merged) {
     if (ep_fast) {
       rep.epoch = reinterpret_cast<const int32_t*>(ws + L.ctl);
       for (int i = 0; i < 2; ++i) rep.slot_row_alt[i] = reinterpret_cast<int32_t*>(ws + L.slot_row_alt[i]);
@@ -505,6 +511,7 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
                              fp8 ? reinterpret_cast<float*>(ws + L.sx) : nullptr,
                              c.max_tokens * (k + 1), rep, stream)))
       return rc;
+    }
     STAGE_MARK(1);
     STAGE_MARK(2);
     STAGE_MARK(3);
@@ -609,6 +616,28 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
       f.q.pow2 = pow2;
     }
     if (ep_fast) f.ep = *epf;
+    if (merged) {
+      f.rt.enabled = 1;
+      f.rt.x = x;
+      f.rt.gate_w = l->gate_w;
+      f.rt.bias = l->bias;
+      f.rt.logits = logits;
+      f.rt.idx = idx;
+      f.rt.w = w;
+      f.rt.expert_offsets = offsets;
+      f.rt.row_token = row_token;
+      f.rt.row_weight = row_weight;
+      f.rt.slot_row = slot_row;
+      f.rt.tiles = tiles;
+      f.rt.tile_capacity = L.tile_capacity;
+      f.rt.num_tiles = num_tiles;
+      f.rt.E = E;
+      f.rt.k = k;
+      f.rt.e_lo = c.expert_begin;
+      f.rt.e_hi = c.expert_end;
+      f.rt.scale = c.routed_scaling_factor;
+      f.rt.sync = reinterpret_cast<int32_t*>(ws + L.sched) + 40;
+    }
     if ((rc = decode_fused_launch(f, stream))) return rc;
     STAGE_MARK(5);
     combine_done = true;
@@ -869,13 +898,31 @@ extern "C" int glm4moe_mlp_forward(const void* x, const void* w_gate_up, const v
   if ((dtype != GLM4MOE_BF16 && dtype != GLM4MOE_F16) || H % 128 != 0 || I % 8 != 0) return GLM4MOE_ERR_UNSUPPORTED;
   int dev = 0, sms = 148;
   if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  const int bn = T <= 16 ? 16 : T <= 32 ? 32 : T <= 64 ? 64 : T <= 128 ? 128 : 256;
+  // token rows per tile, per GEMM: an item streams its weight rows (256 gate+up / 128 down) plus BN token rows per
+  // k-block, items = token tiles x feature tiles run in waves over the SMs: take the BN with the fewest
+  // wave x (weight rows + BN) units (T = 256: one 256-row tile would leave the down GEMM with H/128 = 32 items)
+  auto pick = [&](int n_feat, int w_rows) {
+    int best = 16;
+    long best_cost = -1;
+    for (int i = 0; i < kNumBn; ++i) {
+      const int bn_i = kBnChoices[i];
+      const long items = static_cast<long>((T + bn_i - 1) / bn_i) * n_feat;
+      const long cost = ((items + sms - 1) / sms) * (w_rows + bn_i);
+      if (best_cost < 0 || cost < best_cost) {
+        best_cost = cost;
+        best = bn_i;
+      }
+      if (bn_i >= T) break;
+    }
+    return best;
+  };
+  const int bn = pick((I + 127) / 128, 256), bn_d = pick(H / 128, 128);
   alignas(64) CUtensorMap tm_wgu, tm_wd, tm_xin, tm_act;
   int rc;
   if ((rc = umma_make_tensor_map(&tm_wgu, w_gate_up, dtype, static_cast<uint64_t>(2) * I, H, 128))) return rc;
   if ((rc = umma_make_tensor_map(&tm_wd, w_down, dtype, static_cast<uint64_t>(H), I, 128))) return rc;
   if ((rc = umma_make_tensor_map(&tm_xin, x, dtype, static_cast<uint64_t>(T), H, bn))) return rc;
-  if ((rc = umma_make_tensor_map(&tm_act, act_ws, dtype, static_cast<uint64_t>(T), I, bn))) return rc;
+  if ((rc = umma_make_tensor_map(&tm_act, act_ws, dtype, static_cast<uint64_t>(T), I, bn_d))) return rc;
   UmmaLaunch a{};
   a.tiles = nullptr;
   a.num_tiles = nullptr;
@@ -909,7 +956,8 @@ extern "C" int glm4moe_mlp_forward(const void* x, const void* w_gate_up, const v
   a.w_rows_per_expert = H;
   a.up_row_offset = 0;
   a.mode = 0;
-  if (bn == 256 && H % 256 == 0 && down2_enabled()) {
+  a.tile_rows = bn_d;
+  if (bn_d == 256 && H % 256 == 0 && down2_enabled()) {
     a.mode = 3;
     a.n_feat_tiles = H / 256;
     a.up_row_offset = 128;

@@ -29,6 +29,8 @@
 // allocator, warps 4-7 epilogue (tcgen05.ld, fused math, stores with lane = output feature).
 #include <cuda_fp8.h>
 
+#include "route_device.cuh"
+
 #include "umma_common.cuh"
 #include "umma_gemm.cuh"
 
@@ -83,7 +85,7 @@ __global__ void __launch_bounds__(FusedCfg<BN, FP8>::kThreads, 1) decode_fused_k
     const __grid_constant__ CUtensorMap tm_wd,    // down stack    [n_stack * H, I],  box {64, 128}
     const __grid_constant__ CUtensorMap tm_x,     // the layer input [T, H],          box {64, BN}
     const __grid_constant__ CUtensorMap tm_act,   // activation rows [R, I],          box {64, BN}
-    const int4* __restrict__ tiles, const int32_t* __restrict__ num_tiles_ptr,
+    const int4* tiles, const int32_t* num_tiles_ptr,       // (may be written by this kernel: RouteMerged)
     const int32_t* row_token, const float* row_weight, T* __restrict__ act, T* __restrict__ y, int H, int I,
     int tokens, int n_routed_rows, int shared_expert, int sh_lo, int sh_hi,
     int32_t* __restrict__ sched,                  // [0] queue head, [1] CTAs finished
@@ -93,7 +95,8 @@ __global__ void __launch_bounds__(FusedCfg<BN, FP8>::kThreads, 1) decode_fused_k
     const unsigned char* __restrict__ pf0, size_t pf0_bytes,    // shared expert's gate_up / down weights:
     const unsigned char* __restrict__ pf1, size_t pf1_bytes,    // pulled into L2 while the router runs
     const Fp8Args q,                              // e4m3 tier: scales and the quantised activation buffer
-    const EpFastSignal ep) {                      // expert-parallel fast path: parity row buffers + ready flags
+    const EpFastSignal ep,                        // expert-parallel fast path: parity row buffers + ready flags
+    const RouteMerged rt) {                       // T <= 2: router front-end inside this kernel
   using Cfg = FusedCfg<BN, FP8>;
   constexpr int AK = Cfg::kAtomK;
   constexpr int NS = Cfg::kAccSlots;
@@ -164,7 +167,7 @@ __global__ void __launch_bounds__(FusedCfg<BN, FP8>::kThreads, 1) decode_fused_k
     const int G = n_routed * FG;
     if (w < G) {
       const int t = w / FG;
-      const int4 tl = tiles[t];
+      const int4 tl = __ldcg(tiles + t);
       it = FusedItem{0, tl.x, tl.y, tl.z, w - t * FG, 1 + t, 0};
       return it;
     }
@@ -175,7 +178,7 @@ __global__ void __launch_bounds__(FusedCfg<BN, FP8>::kThreads, 1) decode_fused_k
       it = FusedItem{1, shared_expert, shared_row0, n_sh, f, 0, 1};
     } else {
       const int t = td - has_shared;
-      const int4 tl = tiles[t];
+      const int4 tl = __ldcg(tiles + t);
       it = FusedItem{1, tl.x, tl.y, tl.z, f, 1 + t, 0};
     }
     return it;
@@ -296,20 +299,35 @@ __global__ void __launch_bounds__(FusedCfg<BN, FP8>::kThreads, 1) decode_fused_k
         prefetch_slice(pf0, pf0_bytes);
         prefetch_slice(pf1, pf1_bytes);
       }
+      // merged front-end: this kernel is the first of the layer, so x itself is the predecessor's output
+      if (rt.enabled) {
+        pdl_wait();
+        pdl_launch();
+      }
       // (e4m3: the token tile is the router kernel's quantised copy of x, so phase S follows the wait)
       if (has_shared && !FP8)
         for (int f = blockIdx.x; f < FG; f += gridDim.x) {
           push(kSharedBase + f, 0);
           stream_gate_up(FusedItem{0, shared_expert, shared_row0, n_sh, f, 0, 1});
         }
-      pdl_wait();
-      pdl_launch();
+      if (rt.enabled) {
+        // the routing of this call: released by the router CTA's epilogue warps (below)
+        int v;
+        const long long t0 = clock64();
+        do {
+          asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(rt.sync + 1) : "memory");
+          if (v == 0 && clock64() - t0 > (1ll << 32)) __trap();     // never in a correct run
+        } while (v == 0);
+      } else {
+        pdl_wait();
+        pdl_launch();
+      }
       if (has_shared && FP8)
         for (int f = blockIdx.x; f < FG; f += gridDim.x) {
           push(kSharedBase + f, 0);
           stream_gate_up(FusedItem{0, shared_expert, shared_row0, n_sh, f, 0, 1});
         }
-      const int n_routed = *num_tiles_ptr - has_shared;
+      const int n_routed = *reinterpret_cast<const volatile int32_t*>(num_tiles_ptr) - has_shared;
       const int total = n_routed * FG + (n_routed + has_shared) * FD;
       if (n_routed + has_shared == 0) {   // expert-parallel rank without a hit expert: the partial output is zero
         for (int f = blockIdx.x; f < FD; f += gridDim.x) push(kZeroBase + f, 0);
@@ -334,6 +352,7 @@ __global__ void __launch_bounds__(FusedCfg<BN, FP8>::kThreads, 1) decode_fused_k
         sched[0] = 0;
         sched[1] = 0;
         for (int i = 0; i <= n_routed; ++i) ready[i] = 0;
+        if (rt.enabled) rt.sync[1] = 0;      // every producer is past its acquire of the routing flag
         __threadfence();
       }
     }
@@ -458,6 +477,82 @@ __global__ void __launch_bounds__(FusedCfg<BN, FP8>::kThreads, 1) decode_fused_k
         *reinterpret_cast<uint2*>(out + static_cast<size_t>(t) * H + col) = *reinterpret_cast<uint2*>(o);
       }
     };
+    // ---- merged router front-end (T <= 2): logits of expert blockIdx.x (+ gridDim.x, ...) by this CTA's 4
+    // epilogue warps in route_small_kernel's summation order (its 256 threads = 2 "virtual" threads per
+    // thread here: vectors v, v + 256, ... accumulated in order, warp sums over the same lanes, the 8 warp
+    // partials added in order), then ticket -> selection -> permutation -> flag. ----
+    if constexpr (!FP8) {
+      if (rt.enabled) {
+        pdl_wait();
+        constexpr int V = Dt<T>::kVec;
+        const int E = rt.E, nvec = H / V;
+        const T* xin = static_cast<const T*>(rt.x);
+        const T* gw = static_cast<const T*>(rt.gate_w);
+        T* lg = static_cast<T*>(rt.logits);
+        const int tid = ewi * 32 + lane;                       // 0..127 (4 epilogue warps in this tier)
+        const int n_rt = min(static_cast<int>(gridDim.x), E);  // CTAs that own at least one expert
+        for (int e = blockIdx.x; e < E; e += gridDim.x) {
+          float acc[2][2] = {{0.f, 0.f}, {0.f, 0.f}};         // [virtual thread][token]
+#pragma unroll
+          for (int vt = 0; vt < 2; ++vt) {
+            for (int c = tid + 128 * vt; c < nvec; c += 256) {
+              float wv[V], xv[2][V];
+              unpack16<T>(ld_cached16(reinterpret_cast<const uint4*>(gw + static_cast<size_t>(e) * H) + c), wv);
+#pragma unroll
+              for (int i = 0; i < 2; ++i)
+                unpack16<T>(ld_cached16(reinterpret_cast<const uint4*>(xin + static_cast<size_t>(min(i, tokens - 1)) * H) + c), xv[i]);
+#pragma unroll
+              for (int i = 0; i < 2; ++i)
+#pragma unroll
+                for (int qv = 0; qv < V; ++qv) acc[vt][i] = fmaf(xv[i][qv], wv[qv], acc[vt][i]);
+            }
+          }
+#pragma unroll
+          for (int vt = 0; vt < 2; ++vt)
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+              const float s = warp_sum(acc[vt][i]);
+              if (lane == 0) s_amax[(ewi + 4 * vt) * 2 + i] = s;       // virtual warp ewi + 4 vt
+            }
+          epi_sync();
+          if (tid < tokens) {
+            float s = 0.f;
+#pragma unroll
+            for (int wdx = 0; wdx < 8; ++wdx) s += s_amax[wdx * 2 + tid];
+            lg[static_cast<size_t>(tid) * E + e] = Dt<T>::from_f(s);
+            __threadfence();
+          }
+          epi_sync();
+        }
+        if (tid == 0) {
+          int last = 0;
+          if (static_cast<int>(blockIdx.x) < n_rt) {
+            __threadfence();
+            last = atomicAdd(rt.sync, 1) == n_rt - 1;
+            if (last) rt.sync[0] = 0;                         // re-armed for the next launch
+          }
+          s_last[0] = last;
+        }
+        epi_sync();
+        if (s_last[0]) {
+          __threadfence();
+          if (ewi < tokens)
+            select_token<T>(lg + static_cast<size_t>(ewi) * E, rt.bias, E, rt.k, rt.scale, lane,
+                            rt.idx + static_cast<size_t>(ewi) * rt.k, rt.w + static_cast<size_t>(ewi) * rt.k);
+          __threadfence();
+          epi_sync();
+          if (ewi == 0) {
+            permute_tiny_warp(rt.idx, rt.w, tokens, rt.k, E, rt.e_lo, rt.e_hi, BN, sh_lo, sh_hi, rt.expert_offsets,
+                              rt.row_token, rt.row_weight, rt.slot_row, reinterpret_cast<int4*>(rt.tiles),
+                              rt.tile_capacity, rt.num_tiles, lane);
+            __threadfence();
+            __syncwarp();
+            if (lane == 0) asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(rt.sync + 1), "r"(1) : "memory");
+          }
+        }
+        epi_sync();     // s_last / s_amax are reused by the main loop
+      }
+    }
     int pend_f = -1, pend_done = 0, pend_target = 0;   // down item whose feature-tile count is in flight
     int pend_slot = 0;                                  // broadcast slot (alternates, so one barrier suffices)
     T* y_rows = y;      // expert-parallel fast path: the buffer of this call's parity (resolved at the first down item)
@@ -768,7 +863,7 @@ static int launch_fused_one(const DecodeFusedLaunch& a, cudaStream_t st) {
       a.row_weight, static_cast<T*>(a.act), static_cast<T*>(a.y), a.H, a.I, a.tokens, a.n_routed_rows,
       a.shared_expert, a.sh_lo, a.sh_hi, a.sched, a.ready, a.slot_row, static_cast<T*>(a.out), a.k, a.fdone,
       static_cast<const unsigned char*>(a.pf0), a.pf0_bytes, static_cast<const unsigned char*>(a.pf1), a.pf1_bytes,
-      a.q, a.ep));
+      a.q, a.ep, a.rt));
   return GLM4MOE_OK;
 }
 
@@ -783,6 +878,7 @@ int decode_fused_launch(const DecodeFusedLaunch& a, void* stream) {
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (a.tokens <= 0 || a.tokens > a.tile_rows || (a.tile_rows != 16 && a.tile_rows != 32)) return GLM4MOE_ERR_ARG;
   if (a.fp8 && (!a.q.s_gate_up || !a.q.s_down || !a.q.sx_t || !a.q.sact_t || !a.q.actq)) return GLM4MOE_ERR_ARG;
+  if (a.rt.enabled && (a.fp8 || a.ep.enabled || a.tokens > 2 || a.rt.k * a.tokens > 32 || !a.rt.sync)) return GLM4MOE_ERR_ARG;
   if (a.dtype == GLM4MOE_BF16) return launch_fused_t<__nv_bfloat16>(a, st);
   if (a.dtype == GLM4MOE_F16) return launch_fused_t<__half>(a, st);
   return GLM4MOE_ERR_UNSUPPORTED;

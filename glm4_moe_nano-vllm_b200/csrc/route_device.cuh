@@ -178,4 +178,73 @@ __device__ __forceinline__ void permute_small_body(
   }
 }
 
+// The same bookkeeping for T * k <= 32 (token, slot) pairs by ONE warp (lane = pair), no shared memory: used
+// by the router front-end merged into the persistent decode kernel (decode_fused.cu, T <= 2).  Output
+// identical to permute_small_body.
+__device__ __forceinline__ void permute_tiny_warp(
+    const int32_t* idx, const float* w, int T, int k, int E, int e_lo, int e_hi, int tile_rows, int sh_lo, int sh_hi,
+    int32_t* __restrict__ expert_offsets, int32_t* __restrict__ row_token, float* __restrict__ row_weight,
+    int32_t* __restrict__ slot_row, int4* __restrict__ tiles, int tile_capacity, int32_t* __restrict__ num_tiles,
+    int lane) {
+  const int n = T * k;
+  int e = -1;
+  float wt = 0.f;
+  const int t = lane / k;
+  if (lane < n) {
+    e = __ldcg(idx + lane);
+    wt = __ldcg(w + lane);
+  }
+  const bool valid = lane < n && e >= e_lo && e < e_hi;
+  int row = 0, cnt = 0, earlier_same = 0;
+  for (int j = 0; j < n; ++j) {
+    const int ej = __shfl_sync(0xffffffffu, e, j);
+    const int vj = __shfl_sync(0xffffffffu, valid ? 1 : 0, j);
+    const int tj = j / k;
+    if (vj) {
+      if (ej < e || (ej == e && tj < t)) ++row;
+      if (ej == e) {
+        ++cnt;
+        if (tj < t) ++earlier_same;
+      }
+    }
+  }
+  const bool first = valid && earlier_same == 0;      // one lane per hit expert
+  // tile index of a hit expert = hit experts below it
+  int tile_i = 0, n_hit = 0;
+  for (int j = 0; j < n; ++j) {
+    const int ej = __shfl_sync(0xffffffffu, e, j);
+    const int fj = __shfl_sync(0xffffffffu, first ? 1 : 0, j);
+    if (fj) {
+      ++n_hit;
+      if (ej < e) ++tile_i;
+    }
+  }
+  // rows of an expert never exceed T <= tile_rows: one tile per hit expert
+  const int shared_tiles = (sh_hi - sh_lo + tile_rows - 1) / tile_rows;
+  const bool fits = n_hit + shared_tiles <= tile_capacity;
+  if (lane == 0) *num_tiles = fits ? n_hit + shared_tiles : 0;
+  // expert_offsets[el] = valid pairs with a smaller expert id
+  for (int base = 0; base <= E; base += 32) {           // warp-uniform trip count (shuffles inside)
+    const int el = base + lane;
+    int off = 0;
+    for (int j = 0; j < n; ++j) {
+      const int ej = __shfl_sync(0xffffffffu, e, j);
+      const int vj = __shfl_sync(0xffffffffu, valid ? 1 : 0, j);
+      if (vj && ej < el) ++off;
+    }
+    if (el <= E) expert_offsets[el] = off;
+  }
+  if (fits) {
+    if (first) emit_tiles(tiles, tile_i, e - e_lo, row, cnt, tile_rows);
+    if (lane == 31) emit_tiles(tiles, n_hit, e_hi - e_lo, T * k + sh_lo, sh_hi - sh_lo, tile_rows);
+  }
+  if (lane < n) {
+    if (valid) {
+      row_token[row] = t;
+      row_weight[row] = wt;
+    }
+    slot_row[lane] = valid ? row : -1;
+  }
+}
+
 }  // namespace glm4moe

@@ -65,6 +65,32 @@ struct Fp8Args {
   int pow2;                  // activation scales rounded up to a power of two (GLM4MOE_W_FP8_BLOCK128_POW2)
 };
 
+// T <= 2 (bf16 / fp16, single rank): the router front-end runs INSIDE the persistent kernel instead of as its
+// own launch.  The epilogue warps of CTA c compute the logits of expert c (the summation order of
+// route_small_kernel, bit for bit), the last CTA to finish selects the experts of the <= 2 tokens (the same
+// `select_token`) and builds the permutation / work list with one warp, then releases a flag the producers
+// acquire before they fetch routed work.  Saves the grid dependency between two launches (~5 us of a 70 us
+// layer at T = 1).
+struct RouteMerged {
+  int enabled;
+  const void* x;              // [T, H] layer input
+  const void* gate_w;         // [E, H]
+  const float* bias;          // [E] fp32
+  void* logits;               // [T, E] model dtype (kept: tests and callers read it)
+  int32_t* idx;               // [T, k]
+  float* w;                   // [T, k]
+  int32_t* expert_offsets;    // [E + 1]
+  int32_t* row_token;         // the same buffers the kernel reads through its const parameters
+  float* row_weight;
+  int32_t* slot_row;
+  int32_t* tiles;
+  int tile_capacity;
+  int32_t* num_tiles;
+  int E, k, e_lo, e_hi;
+  float scale;
+  int32_t* sync;              // [0] ticket, [1] flag: zero-initialised, re-armed by the kernel
+};
+
 struct DecodeFusedLaunch {
   const void* tm_wgu;        // gate_up weight stack, box {64, 128}
   const void* tm_wd;         // down weight stack, box {64, 128}
@@ -99,6 +125,7 @@ struct DecodeFusedLaunch {
   // expert-parallel decode fast path (out == nullptr): rows go to the epoch-parity buffer and the kernel
   // itself publishes "rows of this call complete" to every rank when its last down item has landed
   EpFastSignal ep;
+  RouteMerged rt;            // T <= 2: router front-end inside this kernel (no route_small launch)
 };
 int decode_fused_launch(const DecodeFusedLaunch& args, void* stream);
 

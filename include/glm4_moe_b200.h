@@ -76,6 +76,9 @@ enum { GLM4MOE_KNOB_DIRECT = 0, GLM4MOE_KNOB_FUSED = 1, GLM4MOE_KNOB_FP8_PREFILL
        GLM4MOE_KNOB_EP_FAST = 7 /* 1 (default): decode-size expert-parallel calls use ONE cross-rank rendezvous (rows in
                                    epoch-parity buffers, ready flags from the expert kernel, no done round); must be
                                    the same on every rank (a mismatch traps with an error code instead of hanging) */,
+       GLM4MOE_KNOB_MERGE_FRONT = 9 /* 1 (default): at T <= 2 (bf16 / fp16, single rank) the router front-end runs
+                                       inside the persistent decode kernel: ONE launch per layer; 0 = route_small +
+                                       decode_fused as for larger decode batches */,
        GLM4MOE_KNOB_FP8_MX = 8 /* FP8_BLOCK128_POW2 layers at prefill: 1 (default) = hardware block scaling, one CTA
                                   per tile (gate_up token-major umma_fp8_mx_tm.cu, down feature-major
                                   umma_fp8_mx.cu); 2 = hardware block scaling on CTA pairs, 256-token x 256-row tiles
