@@ -68,7 +68,7 @@ class ClockSampler:
     """Samples SM clocks / throttle reasons during the timed region (NVML, ~1 ms period)."""
 
     def __init__(self, index: int):
-        self.index, self.samples, self.reasons = index, [], set()
+        self.index, self.samples, self.reasons, self.watts, self.limit_w = index, [], set(), [], None
         self.max_mhz, self._stop, self._thr = None, threading.Event(), None
         try:
             import pynvml
@@ -76,6 +76,7 @@ class ClockSampler:
             self._nv = pynvml
             self._h = pynvml.nvmlDeviceGetHandleByIndex(index)
             self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM)
+            self.limit_w = pynvml.nvmlDeviceGetEnforcedPowerLimit(self._h) / 1000.0
         except Exception:
             self._nv = None
 
@@ -91,6 +92,7 @@ class ClockSampler:
             return
         try:
             self.samples.append(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM))
+            self.watts.append(nv.nvmlDeviceGetPowerUsage(self._h) / 1000.0)   # NVML averages this over ~0.1 s
             r = nv.nvmlDeviceGetCurrentClocksEventReasons(self._h)
             for n, bit in self.NAMES.items():
                 if r & bit:
@@ -114,6 +116,7 @@ class ClockSampler:
         """Samples taken so far are outside the timed region: forget them."""
         self.samples.clear()
         self.reasons.clear()
+        self.watts.clear()
 
     def stop(self):
         self._stop.set()
@@ -124,7 +127,8 @@ class ClockSampler:
         if not self.samples:
             return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": 0}
         return {"sm_mhz": statistics.median(self.samples), "sm_max_mhz": self.max_mhz,
-                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+                "reasons": sorted(self.reasons), "samples": len(self.samples),
+                "power_w_max": round(max(self.watts), 1) if self.watts else None, "power_limit_w": self.limit_w}
 
 
 def _hf_config(shape):
@@ -232,6 +236,8 @@ def main():
     ap.add_argument("--no-ep-check", action="store_true", help="skip the single-GPU bit-identity check at N > 1")
     ap.add_argument("--one-forward", action="store_true",
                     help="after warm-up run ONE forward of batch 0 and exit (the launch an ncu capture profiles)")
+    ap.add_argument("--knob", action="append", default=[], metavar="K=V",
+                    help="glm4moe_debug_set(K, V) before the run (A/B measurements; include/glm4_moe_b200.h)")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -246,6 +252,8 @@ def main():
         raise SystemExit("--weights fp8 is a single-GPU bench")
     n_batches = N_BATCHES if T <= 1024 else 4
     config = _config(shape, T, args.weights if fp8 else False, n_batches)
+    if args.knob:
+        config["knobs"] = list(args.knob)
 
     # ------------------------------------------------------------------ reference arm (CPU)
     if args.impl == "reference":
@@ -278,6 +286,11 @@ def main():
         build()
     if world > 1:
         dist.barrier()
+
+    for kv in args.knob:
+        from glm4_moe_b200 import _lib
+        k_, v_ = kv.split("=")
+        _lib.check(_lib.load().glm4moe_debug_set(int(k_), int(v_)))
 
     torch.set_default_dtype(dt)
     torch.set_default_device(dev)

@@ -50,6 +50,7 @@ bool direct_enabled() {
 int g_router_rows = 0;   // 0: pick by T; 16/32/64/128: token rows per router tile (glm4moe_debug_set(3, v))
 int g_bk32 = -1;         // see bk32_enabled()
 int g_down2 = -1;        // see down2_enabled()
+int g_tail_box = 1;      // ragged token tiles fetched through smaller TMA boxes (umma_gemm.cu TailMaps)
 int g_force_bn = -2;     // see forced_bn_index()
 int g_fp8_mx = -1;       // hardware block scaling for FP8_BLOCK128_POW2 prefill: 0 off, 1 one CTA per tile
                          // (gate_up umma_fp8_mx_tm.cu, down umma_fp8_mx.cu), 2 CTA pairs (umma_fp8_mx2.cu),
@@ -195,6 +196,7 @@ extern "C" int glm4moe_debug_set(int knob, int value) {
     case GLM4MOE_KNOB_FP8_MX: g_fp8_mx = value < 0 || value > 3 ? 1 : value; return GLM4MOE_OK;
     case GLM4MOE_KNOB_BK32: g_bk32 = value ? 1 : 0; return GLM4MOE_OK;
     case GLM4MOE_KNOB_DOWN2: g_down2 = value ? 1 : 0; return GLM4MOE_OK;
+    case GLM4MOE_KNOB_TAIL_BOX: g_tail_box = value ? 1 : 0; return GLM4MOE_OK;
     case GLM4MOE_KNOB_FORCE_TILE_ROWS:
       g_force_bn = -1;
       if (value == 0) return GLM4MOE_OK;
@@ -381,6 +383,8 @@ static bool bk32_enabled() {
   return g_bk32 == 1;
 }
 // GLM4MOE_NO_DOWN2=1: plain 128-feature down tiles at prefill instead of 256 features x 256 tokens
+static bool tail_box_enabled() { return g_tail_box != 0; }
+
 static bool down2_enabled() {
   if (g_down2 < 0) {
     const char* e = getenv("GLM4MOE_NO_DOWN2");
@@ -785,6 +789,14 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
     // gate_up + SiLU*mul
     a.tm_w = &l->tm_w_gu;
     a.tm_x = &l->tm_x[bi];
+    // ragged tiles come through the smaller boxes over the same rows (the three tile sizes below this one)
+    const int tail_lo = bi >= 3 ? bi - 3 : 0;
+    const bool tails = !direct && tail_box_enabled();
+    for (int i = 0; i < 3; ++i) {
+      const bool on = tails && tail_lo + i < bi;
+      a.tm_x_tail[i] = on ? &l->tm_x[tail_lo + i] : nullptr;
+      a.tail_rows[i] = on ? kBnChoices[tail_lo + i] : 0;
+    }
     a.out = act;
     a.ld_out = I;
     a.n_feat_tiles = I / 128;
@@ -817,6 +829,7 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
     // down * routing weight
     a.tm_w = &l->tm_w_d;
     a.tm_x = &l->tm_act[bi];
+    for (int i = 0; i < 3; ++i) a.tm_x_tail[i] = a.tm_x_tail[i] ? &l->tm_act[tail_lo + i] : nullptr;
     a.out = y;
     a.ld_out = H;
     a.n_feat_tiles = H / 128;

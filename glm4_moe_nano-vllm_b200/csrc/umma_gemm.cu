@@ -70,6 +70,16 @@ struct UmmaCfg {
 // ------------------------------------------------------------------------------------------
 // the kernel
 // ------------------------------------------------------------------------------------------
+// Activation tensor maps with fewer box rows than BN over the same buffer (ascending `rows`, 0 = unused).
+// The producer picks the smallest box that covers a tile's rows: the ragged last token tile of an
+// expert (256 +- 16 rows per expert at Air T = 4096: half of the experts own a 1..48-row second tile)
+// then brings its rows across L2 -> SM, not a whole BN-row box.
+struct TailMaps {
+  CUtensorMap m[3];
+  int rows[3];
+  int pad;
+};
+
 constexpr int kSharedWorkBase = 1 << 30;   // direct mode: work id of the shared expert's feature tile f
 constexpr int kSchedDepth = 4;   // work-index queue between the producer and the consumer warps
 
@@ -77,6 +87,7 @@ template <typename T, int BN, int MODE, int BK = kBK>
 __global__ void __launch_bounds__(UmmaCfg<BN, MODE, BK>::kThreads, 1) umma_grouped_kernel(
     const __grid_constant__ CUtensorMap tm_w,   // weights  [rows_w_total, K], box {64, 128}
     const __grid_constant__ CUtensorMap tm_x,   // activation rows [rows_x_total, K], box {64, BN}
+    const __grid_constant__ TailMaps tail,      // same rows, smaller boxes
     const int4* __restrict__ tiles, const int32_t* __restrict__ num_tiles_ptr, int dense_rows,
     T* __restrict__ out, int ld_out,            // out[row, feature]
     const float* __restrict__ row_weight,       // kModeDown: per-row scale for rows < n_routed_rows
@@ -166,17 +177,27 @@ __global__ void __launch_bounds__(UmmaCfg<BN, MODE, BK>::kThreads, 1) umma_group
       };
       WorkRef wr{0, 0, 0, 0};
       const bool is_direct = direct.tokens > 0;
+      const CUtensorMap* mx = &tm_x;
+      uint32_t x_bytes = Cfg::kBBytes;
+      auto pick_x = [&]() {   // after every change of `wr` (not in direct mode: the box is the token count)
+        const int need = max(16, (wr.nrows + 15) & ~15);
+        mx = &tm_x;
+        x_bytes = Cfg::kBBytes;
+        if (tail.rows[2] >= need) { mx = &tail.m[2]; x_bytes = tail.rows[2] * BK * 2; }
+        if (tail.rows[1] >= need) { mx = &tail.m[1]; x_bytes = tail.rows[1] * BK * 2; }
+        if (tail.rows[0] >= need) { mx = &tail.m[0]; x_bytes = tail.rows[0] * BK * 2; }
+      };
       auto issue = [&](int kb, int stage, bool do_w, bool do_x) {
         unsigned char* sa = smem + stage * Cfg::kStageBytes;
         if (do_w) {
           const int w_row = wr.expert * w_rows_per_expert + wr.f * Cfg::kFeatPerTile;
-          mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+          mbar_expect_tx(&full_bar[stage], (GATED ? 2 : 1) * Cfg::kABytes + x_bytes);
           tma_load_2d(&tm_w, &full_bar[stage], sa, kb * BK, w_row, kEvictFirst);
           if (GATED)
             tma_load_2d(&tm_w, &full_bar[stage], sa + Cfg::kABytes, kb * BK, w_row + up_row_offset, kEvictFirst);
         }
         if (do_x)
-          tma_load_2d(&tm_x, &full_bar[stage], sa + (GATED ? 2 : 1) * Cfg::kABytes, kb * BK,
+          tma_load_2d(mx, &full_bar[stage], sa + (GATED ? 2 : 1) * Cfg::kABytes, kb * BK,
                       is_direct ? 0 : wr.row_start, kEvictLast);
       };
       if (is_direct) {
@@ -223,7 +244,10 @@ __global__ void __launch_bounds__(UmmaCfg<BN, MODE, BK>::kThreads, 1) umma_group
         }
       } else {
       int w = fetch_push();
-      if (w >= 0) wr = get_work<BN>(tiles, w, n_feat_tiles, n_tiles, dense_rows);
+      if (w >= 0) {
+        wr = get_work<BN>(tiles, w, n_feat_tiles, n_tiles, dense_rows);
+        pick_x();
+      }
       // (1) Before the dependency wait: weight tiles of the first item for the first pass over
       //     the ring.  Weights and the work list are at least two launches old (see common.cuh),
       //     so this overlaps the predecessor's tail with our pipeline fill.
@@ -241,7 +265,10 @@ __global__ void __launch_bounds__(UmmaCfg<BN, MODE, BK>::kThreads, 1) umma_group
       while (w >= 0) {
         if (kb == n_kblocks) {
           w = fetch_push();
-          if (w >= 0) wr = get_work<BN>(tiles, w, n_feat_tiles, n_tiles, dense_rows);
+          if (w >= 0) {
+            wr = get_work<BN>(tiles, w, n_feat_tiles, n_tiles, dense_rows);
+            pick_x();
+          }
           kb = 0;
           continue;
         }
@@ -462,9 +489,20 @@ static int launch_one(const UmmaLaunch& a, cudaStream_t st) {
   auto kern = umma_grouped_kernel<T, BN, MODE, BK>;
   static unsigned long long attr_done = 0;   // per instantiation, one bit per device
   GLM4MOE_CUDA_CHECK(ensure_dynamic_smem(kern, Cfg::kSmemBytes, &attr_done));
+  TailMaps tail{};
+  if (BK == kBK && a.direct.tokens == 0) {
+    int n = 0;
+    for (int i = 0; i < 3; ++i)
+      if (a.tm_x_tail[i] && a.tail_rows[i] > 0 && a.tail_rows[i] < BN && a.tail_rows[i] % 16 == 0 &&
+          (n == 0 || a.tail_rows[i] > tail.rows[n - 1])) {
+        tail.m[n] = *static_cast<const CUtensorMap*>(a.tm_x_tail[i]);
+        tail.rows[n++] = a.tail_rows[i];
+      }
+  }
   GLM4MOE_CUDA_CHECK(launch_pdl(
       kern, dim3(a.grid), dim3(Cfg::kThreads), Cfg::kSmemBytes, st, *static_cast<const CUtensorMap*>(a.tm_w),
-      *static_cast<const CUtensorMap*>(a.tm_x), reinterpret_cast<const int4*>(a.tiles), a.num_tiles, a.dense_rows,
+      *static_cast<const CUtensorMap*>(a.tm_x), tail, reinterpret_cast<const int4*>(a.tiles), a.num_tiles,
+      a.dense_rows,
       static_cast<T*>(a.out), a.ld_out, a.row_weight, a.n_routed_rows, a.n_feat_tiles, a.n_feat_valid, a.n_kblocks,
       a.w_rows_per_expert, a.up_row_offset, a.sched, a.direct));
   return GLM4MOE_OK;

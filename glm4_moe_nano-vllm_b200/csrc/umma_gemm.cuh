@@ -22,6 +22,8 @@ struct DirectArgs {
 struct UmmaLaunch {
   const void* tm_w;        // CUtensorMap (128 bytes) over the stacked weights
   const void* tm_x;        // CUtensorMap over the activation rows, box rows == tile_rows
+  const void* tm_x_tail[3];   // optional: the same rows with smaller boxes (ascending tail_rows, multiples of 16):
+  int tail_rows[3];           // a tile whose rows fit a smaller box is fetched through it (ragged expert tails)
   const int32_t* tiles;    // int4 {expert, row_start, nrows, index in expert | tiles of expert << 16}
   const int32_t* num_tiles;
   int dense_rows;          // tiles == nullptr: rows [0, dense_rows) in tile_rows chunks, expert 0

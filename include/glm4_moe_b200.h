@@ -79,6 +79,8 @@ enum { GLM4MOE_KNOB_DIRECT = 0, GLM4MOE_KNOB_FUSED = 1, GLM4MOE_KNOB_FP8_PREFILL
        GLM4MOE_KNOB_MERGE_FRONT = 9 /* 1 (default): at T <= 2 (bf16 / fp16, single rank) the router front-end runs
                                        inside the persistent decode kernel: ONE launch per layer; 0 = route_small +
                                        decode_fused as for larger decode batches */,
+       GLM4MOE_KNOB_TAIL_BOX = 10 /* 1 (default): a ragged token tile of the tensor-core grouped GEMM is fetched
+                                     through a TMA box just large enough for its rows; 0 = always a whole tile box */,
        GLM4MOE_KNOB_FP8_MX = 8 /* FP8_BLOCK128_POW2 layers at prefill: 1 (default) = hardware block scaling, one CTA
                                   per tile (gate_up token-major umma_fp8_mx_tm.cu, down feature-major
                                   umma_fp8_mx.cu); 2 = hardware block scaling on CTA pairs, 256-token x 256-row tiles

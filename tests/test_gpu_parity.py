@@ -153,10 +153,10 @@ def _check_sampled_rows(out, x, wts, shape, dt, idx, w, tile_rows, seed=0, n_ext
 
 class _knobs:
     """glm4moe_debug_set for the duration of a block; restores the defaults."""
-    DEFAULTS = {4: 0, 5: 1, 6: 0}          # BK32 off, DOWN2 on, tile rows by mean rows per expert
+    DEFAULTS = {4: 0, 5: 1, 6: 0, 10: 1}   # BK32 off, DOWN2 on, tile rows by mean rows per expert, tail boxes on
 
     def __init__(self, **kw):
-        names = {"bk32": 4, "down2": 5, "tile_rows": 6}
+        names = {"bk32": 4, "down2": 5, "tile_rows": 6, "tail_box": 10}
         self.values = {names[k_]: v for k_, v in kw.items()}
 
     def __enter__(self):
@@ -703,6 +703,22 @@ def test_air_prefill_tiles_vs_oracle(air, T, knobs, want_rows):
     assert torch.equal(moe.workspace_view("row_token").cpu()[:T * shape.k], rt)
     n, rel = _check_sampled_rows(out, x, wts, shape, dt, idx, w, want_rows, seed=T)
     assert n >= 320
+
+
+@pytest.mark.parametrize("T,knobs", [(4096, {}), (4000, {"down2": 0}), (1024, {}), (700, {"tile_rows": 128}),
+                                     (333, {"tile_rows": 256})])
+def test_air_prefill_tail_boxes_bit_identical(air, T, knobs):
+    """A ragged token tile fetched through a TMA box just large enough for its rows (`TailMaps`,
+    umma_gemm.cu) feeds the MMA the same operands as the whole-tile box: outputs bit for bit."""
+    shape, dt, wts, moe = air
+    x = synth.make_tokens(shape, T, dt, 4400 + T).cuda()
+    outs = []
+    for tail in (1, 0, 1):
+        with _knobs(tail_box=tail, **knobs), torch.inference_mode():
+            outs.append(moe(x).clone())
+            assert moe.last_impl == "umma" and not moe.last_fused
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+    assert bool(torch.isfinite(outs[0].float()).all())
 
 
 def test_bias_survives_a_dtype_cast_on_the_gpu():
