@@ -822,6 +822,45 @@ def test_fp8_pow2_scales_mini(T):
     assert moe._cfg.weight_format == _lib.W_FP8_BLOCK128_POW2
 
 
+def test_fp8_scale_rounding_error_budget():
+    """DESIGN.md section 4 "scale rounding budget": relative Frobenius error of the FP8 layer output against the
+    fp32 reference, for the amax/448 tier and the power-of-two tier, (a) on the dequantised weights (north_star's
+    5e-2 bar: activation quantisation only) and (b) on the ORIGINAL weights (weight + activation quantisation).
+    Rounding the scales up to powers of two may cost at most a quarter on top of the fp32-scale tier.  The
+    numbers go to gpurun_out/r2_fp8_error_budget.json when that directory exists."""
+    import json
+    import os
+    shape, dt = synth.MINI, torch.bfloat16
+    wts = synth.make_weights(shape, dt)
+    ref_w = {"w_gate_up": wts["w_gate_up"].float(), "w_down": wts["w_down"].float()}
+    report = {}
+    for T in (40, 700):
+        x = synth.make_tokens(shape, T, dt, 77 + T)
+        for pow2 in (False, True):
+            moe = _module(shape, dt, wts, max_tokens=1024)
+            moe.quantize_fp8(pow2_scales=pow2)
+            with torch.inference_mode():
+                out = moe(x.cuda()).float().cpu()
+                idx = moe.workspace_view("idx", T).cpu().long()
+                w = moe.workspace_view("w", T).cpu().to(dt)
+                deq = {k_: v.cpu() for k_, v in moe.dequantized_weights().items()}
+                t_deq = O.moe_forward(x.float(), deq, shape.k, shape.routed_scaling_factor,
+                                      routing=(idx, w.float()))["out"]
+                t_orig = O.moe_forward(x.float(), ref_w, shape.k, shape.routed_scaling_factor,
+                                       routing=(idx, w.float()))["out"]
+            report[f"T={T} {'pow2' if pow2 else 'amax/448'}"] = {
+                "vs_fp32_on_dequantised_weights": float((out - t_deq).norm() / t_deq.norm()),
+                "vs_fp32_on_original_weights": float((out - t_orig).norm() / t_orig.norm())}
+        a, b = report[f"T={T} amax/448"], report[f"T={T} pow2"]
+        for key in a:
+            assert b[key] < RTOL_FP8, (T, key, b[key])
+            assert b[key] <= 1.25 * a[key] + 1e-3, (T, key, a[key], b[key])
+    print(json.dumps(report))
+    if os.path.isdir("gpurun_out"):
+        with open("gpurun_out/r2_fp8_error_budget.json", "w") as f:
+            json.dump(report, f, indent=1)
+
+
 def test_fp8_pow2_tiny_fp16_ragged():
     _fp8_case(synth.TINY, torch.float16, 333, 9, max_tokens=512, pow2=True)
 
