@@ -26,6 +26,8 @@ SYMBOLS = [
     "glm4moe_layer_forward", "glm4moe_layer_forward_ex", "glm4moe_layer_forward_timed", "glm4moe_layer_forward_host", "glm4moe_layer_view",
     "glm4moe_layer_last_launches", "glm4moe_layer_last_impl", "glm4moe_layer_last_fused", "glm4moe_layer_tile_rows",
     "glm4moe_p2p_alloc", "glm4moe_p2p_open", "glm4moe_p2p_close", "glm4moe_p2p_free", "glm4moe_layer_forward_ep_p2p", "glm4moe_set_ep_sliced", "glm4moe_add_rmsnorm",
+    "glm4moe_layer_forward_prenorm", "glm4moe_ep_comm_bytes", "glm4moe_ep_allreduce_add_rmsnorm",
+    "glm4moe_layer_forward_ep_p2p_prenorm",
 ]
 
 
@@ -96,6 +98,13 @@ def load() -> C.CDLL:
     lib.glm4moe_p2p_free.argtypes = [vp]
     lib.glm4moe_layer_forward_ep_p2p.argtypes = [vp, vp, vp, i32, C.POINTER(vp), i32, i32, vp]
     lib.glm4moe_set_ep_sliced.argtypes = [i32]
+    lib.glm4moe_layer_forward_prenorm.argtypes = [vp, vp, vp, vp, f32, vp, vp, i32, vp]
+    lib.glm4moe_ep_comm_bytes.restype = sz
+    lib.glm4moe_ep_comm_bytes.argtypes = [i32, i32, i32, i32]
+    lib.glm4moe_ep_allreduce_add_rmsnorm.argtypes = [C.POINTER(vp), i32, i32, i32, vp, vp, vp, f32, i32, i32, i32,
+                                                     vp, vp, vp]
+    lib.glm4moe_layer_forward_ep_p2p_prenorm.argtypes = [vp, vp, vp, vp, f32, vp, vp, i32, C.POINTER(vp),
+                                                         C.POINTER(vp), i32, i32, i32, vp]
     for name in SYMBOLS:
         if lib.glm4moe_abi_version is None or not hasattr(lib, name):
             raise Glm4MoeLibraryError(f"{LIB_PATH} does not export {name}")

@@ -7,7 +7,7 @@ import subprocess
 
 CSRC = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc")
 LIB_PATH = os.path.join(CSRC, "libglm4moe_b200.so")
-SOURCES = ["api.cu", "router.cu", "route_small.cu", "permute.cu", "simt_mlp.cu", "umma_gemm.cu", "umma_fp8.cu", "umma_fp8_prefill.cu", "umma_fp8_mx.cu", "umma_fp8_mx_tm.cu", "umma_fp8_mx2.cu", "decode_fused.cu", "ep_combine.cu", "rmsnorm.cu"]
+SOURCES = ["api.cu", "router.cu", "route_small.cu", "permute.cu", "simt_mlp.cu", "umma_gemm.cu", "umma_fp8.cu", "umma_fp8_prefill.cu", "umma_fp8_mx.cu", "umma_fp8_mx_tm.cu", "umma_fp8_mx2.cu", "decode_fused.cu", "ep_combine.cu", "ep_allreduce.cu", "rmsnorm.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "--use_fast_math=false"]
 

@@ -11,6 +11,7 @@
 #include "common.cuh"
 #include "umma_gemm.cuh"
 #include "ep_combine.cuh"
+#include "ep_allreduce.cuh"
 
 using namespace glm4moe;
 
@@ -63,13 +64,14 @@ int fp8_mx_mode() {
   return g_fp8_mx;
 }
 int g_merge_front = 1;   // T <= 2: router front-end inside the persistent decode kernel (one launch per layer), KNOB_MERGE_FRONT
+int g_ep_ar_mode = -1;    // fused all-reduce + norm (ep_allreduce.cu): -1 by size, 0 one-shot, 1 two-shot, KNOB_EP_AR_MODE
 int g_ep_fast = 1;       // decode fast path of the peer-memory combine (one rendezvous per step), KNOB_EP_FAST
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct WsLayout {
   size_t logits, idx, w, offsets, row_token, row_weight, slot_row, num_tiles, sched, ready, fdone, tiles, scratch, x_rows,
-      act, y, xq, sx, actq, sact, sx_sf, sact_sf, ctl, stage, y_alt[2], slot_row_alt[2], total;
+      act, y, xq, sx, actq, sact, sx_sf, sact_sf, ctl, stage, y_alt[2], slot_row_alt[2], xn, total;
   int tile_capacity;
 };
 
@@ -131,6 +133,8 @@ WsLayout make_layout(const glm4moe_config_t& c) {
     L.y_alt[i] = take(ep_alt ? static_cast<size_t>(kDirectMaxTokens) * (k + 1) * H * es : 0);
     L.slot_row_alt[i] = take(ep_alt ? static_cast<size_t>(kDirectMaxTokens) * k * 4 : 0);
   }
+  // glm4moe_layer_forward_prenorm: the normalised tokens (the block's actual input), [T, H]
+  L.xn = take(T * H * es);
   L.total = off;
   return L;
 }
@@ -192,6 +196,7 @@ extern "C" int glm4moe_debug_set(int knob, int value) {
       g_router_rows = value;
       return GLM4MOE_OK;
     case GLM4MOE_KNOB_EP_FAST: g_ep_fast = value ? 1 : 0; return GLM4MOE_OK;
+    case GLM4MOE_KNOB_EP_AR_MODE: g_ep_ar_mode = value < 0 ? -1 : value ? 1 : 0; return GLM4MOE_OK;
     case GLM4MOE_KNOB_MERGE_FRONT: g_merge_front = value ? 1 : 0; return GLM4MOE_OK;
     case GLM4MOE_KNOB_FP8_MX: g_fp8_mx = value < 0 || value > 3 ? 1 : value; return GLM4MOE_OK;
     case GLM4MOE_KNOB_BK32: g_bk32 = value ? 1 : 0; return GLM4MOE_OK;
@@ -1129,6 +1134,90 @@ extern "C" int glm4moe_layer_forward_ep_p2p(glm4moe_layer_t* l, const void* x, v
                                    : g_ep_sliced_mode == -1 && has_stage && row_bytes >= (16u << 20);
   if (fast) a.sliced = 0;      // the decode fast path is a pull (<= 32 tokens)
   rc = ep_combine_p2p_launch(a, out, c.dtype, stream);
+  l->last_launches = g_launches - launches0;
+  return rc;
+}
+
+// ---- the step in front of the block fused to it (SURVEY 8f-2 part i, 8f-4) ----------------------------------
+// decode_layer.py:98-99: `hidden, residual = post_attention_layernorm(hidden, residual); hidden = mlp(hidden)` as ONE
+// library call: add_rmsnorm_kernel writes the normalised tokens into the layer workspace (`xn`) and the block's
+// launches follow in the same programmatic-dependent-launch chain (the norm is two launches old when the
+// persistent decode kernel streams the shared expert against it before its own dependency wait).
+extern "C" int glm4moe_layer_forward_prenorm(glm4moe_layer_t* l, const void* x, const void* residual,
+                                             const void* norm_weight, float eps, void* residual_out, void* out,
+                                             int T, void* stream) {
+  if (!l || !x || !norm_weight || !out || (residual && !residual_out)) return GLM4MOE_ERR_ARG;
+  const glm4moe_config_t& c = l->cfg;
+  if (T < 0 || T > c.max_tokens) return GLM4MOE_ERR_ARG;
+  if (T == 0) return GLM4MOE_OK;
+  const int launches0 = g_launches;
+  void* xn = l->ws + l->L.xn;
+  int rc = glm4moe_add_rmsnorm(x, residual, norm_weight, eps, T, c.hidden_size, c.dtype, xn, residual_out, stream);
+  if (rc) return rc;
+  rc = forward_impl(l, xn, out, T, stream, nullptr);
+  l->last_launches = g_launches - launches0;
+  return rc;
+}
+
+extern "C" size_t glm4moe_ep_comm_bytes(int max_tokens, int H, int dtype, int world) {
+  if (max_tokens <= 0 || H <= 0 || H % 8 != 0 || world < 1 || world > kEpMaxRanks ||
+      (dtype != GLM4MOE_BF16 && dtype != GLM4MOE_F16))
+    return 0;
+  return ep_comm_layout(max_tokens, H, dtype, world).total;
+}
+
+extern "C" int glm4moe_ep_allreduce_add_rmsnorm(void* const* peer_comm, int rank, int world, int max_tokens,
+                                                const void* partial, const void* residual, const void* weight,
+                                                float eps, int T, int H, int dtype, void* out, void* residual_out,
+                                                void* stream) {
+  if (!peer_comm || !partial || !out) return GLM4MOE_ERR_ARG;
+  if (residual && (!weight || !residual_out)) return GLM4MOE_ERR_ARG;
+  if (world < 1 || world > kEpMaxRanks || rank < 0 || rank >= world) return GLM4MOE_ERR_ARG;
+  if (T < 0 || T > max_tokens || H <= 0 || H % 8 != 0) return GLM4MOE_ERR_ARG;
+  if (dtype != GLM4MOE_BF16 && dtype != GLM4MOE_F16) return GLM4MOE_ERR_UNSUPPORTED;
+  if (T == 0) return GLM4MOE_OK;
+  EpArArgs a{};
+  for (int r = 0; r < world; ++r) {
+    if (!peer_comm[r]) return GLM4MOE_ERR_ARG;
+    a.comm[r] = static_cast<unsigned char*>(peer_comm[r]);
+  }
+  a.L = ep_comm_layout(max_tokens, H, dtype, world);
+  a.rank = rank;
+  a.world = world;
+  a.tokens = T;
+  a.H = H;
+  a.per = (T + world - 1) / world;
+  a.eps = eps;
+  a.partial = partial;
+  a.residual = residual;
+  a.weight = weight;
+  a.out = out;
+  a.residual_out = residual_out;
+  // Same decision on every rank (T, H, world only).  One-shot while the pushed copies stay small: (R-1) x the
+  // partial leaves every rank, against 3(R-1)/R x in the two-shot form, which pays a second flag round.
+  const size_t bytes = static_cast<size_t>(T) * H * dtype_size(dtype);
+  const bool fits = bytes <= a.L.os_slot;
+  bool two = !fits || bytes * static_cast<size_t>(world - 1) > (2u << 20);
+  if (g_ep_ar_mode == 0 && fits) two = false;
+  if (g_ep_ar_mode == 1) two = true;
+  return ep_allreduce_launch(a, dtype, two ? 1 : 0, stream);
+}
+
+extern "C" int glm4moe_layer_forward_ep_p2p_prenorm(glm4moe_layer_t* l, const void* partial, const void* residual,
+                                                    const void* norm_weight, float eps, void* residual_out,
+                                                    void* out, int T, void* const* peer_workspaces,
+                                                    void* const* peer_comm, int comm_max_tokens, int rank,
+                                                    int world, void* stream) {
+  if (!l || !partial || !norm_weight || !out || !peer_workspaces || !peer_comm) return GLM4MOE_ERR_ARG;
+  const glm4moe_config_t& c = l->cfg;
+  if (T < 0 || T > c.max_tokens) return GLM4MOE_ERR_ARG;
+  if (T == 0) return GLM4MOE_OK;
+  const int launches0 = g_launches;
+  void* xn = l->ws + l->L.xn;
+  int rc = glm4moe_ep_allreduce_add_rmsnorm(peer_comm, rank, world, comm_max_tokens, partial, residual, norm_weight,
+                                            eps, T, c.hidden_size, c.dtype, xn, residual_out, stream);
+  if (rc) return rc;
+  rc = glm4moe_layer_forward_ep_p2p(l, xn, out, T, peer_workspaces, rank, world, stream);
   l->last_launches = g_launches - launches0;
   return rc;
 }

@@ -1,0 +1,353 @@
+// Tensor-parallel boundary in front of the sparse block, fused over NVLink peer memory:
+//
+//   reference, per decoder layer (decode_layer.py:96-99):
+//     hidden = o_proj(attn)            RowParallelLinear.forward: F.linear + dist.all_reduce (linear.py:151-155)
+//     hidden, residual = post_attention_layernorm(hidden, residual)      (layernorm.py:29-40, ~8 torch launches)
+//     hidden = mlp(hidden)
+//
+//   here: every rank hands its o_proj PARTIAL sums [T, H] to ONE kernel that is the all-reduce, the residual add
+//   and the RMSNorm at once; no NCCL call, CUDA-graph capturable.
+//
+//   y            = round_dtype( sum_r partial_r )        fp32, ranks in ascending order (identical bits on every rank:
+//                                                        the routing that follows must agree everywhere)
+//   x32          = float(y) + float(residual)            residual_out = round(x32)
+//   out          = round(round(x32 * rsqrt(mean(x32^2) + eps)) * weight)
+//   i.e. exactly `add_rmsnorm_kernel` (rmsnorm.cu, same thread mapping and summation order: bit-identical) applied
+//   to an all-reduce whose sum is taken in fp32 with one rounding.  weight == nullptr: out = y (a plain all-reduce).
+//
+// Two forms, chosen by size (same choice on every rank: it depends on T, H only):
+//   one-shot  (T*H*es <= 1 MiB): every rank PUSHES its partial rows into an inbox on every peer (posted NVLink
+//             writes, no read round trip), one flag round, then every rank reduces all T rows from its local
+//             inboxes.  One cross-rank rendezvous per call; (R-1)*T*H*es bytes out per rank.
+//   two-shot  (prefill): reduce-scatter -> norm on the token shard -> all-gather, in one launch.  Rank r pushes,
+//             for every peer s, its partial rows of s's token slice into s's inbox; after the first flag round
+//             rank s reduces ITS ceil(T/R) tokens, normalises them, and pushes the finished out / residual_out
+//             rows to every peer; after the second flag round every rank copies the other slices from its local
+//             inbox.  3*(R-1)/R*T*H*es bytes out per rank instead of (R-1)*T*H*es, the norm is computed once per
+//             token instead of R times.
+//
+// Ordering (epoch e = calls completed + 1, kept in the comm buffer: graph-replay safe).  Inboxes are selected by the
+// parity of e and there is NO "done" round: a rank overwrites the parity-p inboxes of its peers again in call
+// e + 2, after it has seen every peer's flag of call e + 1 — which a peer sends only after its own call e has
+// retired (stream order), i.e. after its last read of the parity-p inbox.  Flags carry epoch*4 + mode; every
+// spin is bounded and traps with an error code (ranks that disagree on the form or on call counts fail loudly).
+// All blocks of a launch wait for the peers inside the kernel: the grid is capped so that it is co-resident.
+#include "common.cuh"
+#include "ep_allreduce.cuh"
+
+namespace glm4moe {
+
+namespace {
+
+constexpr int kArMaxVec = 4;     // 16-byte vectors per thread: H <= 256 * 4 * 8 = 8192 two-byte elements
+
+__device__ __forceinline__ void st_release_sys(int32_t* p, int32_t v) {
+  asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ int32_t ld_acquire_sys(const int32_t* p) {
+  int32_t v;
+  asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+constexpr long long kSpinTimeoutCycles = 1ll << 35;
+__device__ __forceinline__ void wait_flag(const int32_t* flag, int e, int mode, int32_t* ctl) {
+  const int target = e * 4;
+  const long long t0 = clock64();
+  int v;
+  while ((v = ld_acquire_sys(flag)) - target < 0) {
+    if (clock64() - t0 > kSpinTimeoutCycles) {
+      ctl[2] = kEpErrTimeout;
+      __threadfence_system();
+      __trap();
+    }
+  }
+  if ((v >> 2) == e && (v & 3) != mode) {
+    ctl[2] = kEpErrModeMismatch;
+    __threadfence_system();
+    __trap();
+  }
+}
+// L1-bypassing 128-bit load: inbox rows are written by peers over NVLink (L1 may hold the rows of call e - 2)
+__device__ __forceinline__ uint4 ld_cg16(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+
+// every thread's stores are globally visible, then one ticket per block; true in the LAST block to arrive
+__device__ __forceinline__ bool block_ticket(int32_t* counter, int* s_flag) {
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) *s_flag = atomicAdd(counter, 1) == static_cast<int>(gridDim.x) - 1;
+  __syncthreads();
+  return *s_flag != 0;
+}
+
+// One token row: fp32 sum of the R partials in rank order (own partial read in place, the others from the local
+// inbox), one rounding, residual add, RMSNorm.  Thread mapping and reduction order of add_rmsnorm_kernel.
+// PUSH: finished rows also go to every peer's all-gather inbox (two-shot).
+template <typename T, bool PUSH>
+__device__ __forceinline__ void reduce_norm_row(const EpArArgs& a, int t, const unsigned char* inbox, size_t slot_bytes,
+                                                int inbox_row, int p, float* s_part) {
+  constexpr int V = Dt<T>::kVec;
+  const int nvec = a.H / V;
+  const size_t row_off = static_cast<size_t>(t) * a.H;
+  const T* residual = static_cast<const T*>(a.residual);
+  const T* weight = static_cast<const T*>(a.weight);
+  T* out = static_cast<T*>(a.out);
+  T* residual_out = static_cast<T*>(a.residual_out);
+  float v[kArMaxVec][V];
+  float ss = 0.f;
+#pragma unroll
+  for (int i = 0; i < kArMaxVec; ++i) {
+    const int c = threadIdx.x + i * kEpArThreads;
+    if (c < nvec) {
+      uint4 raw[kEpMaxRanks];
+#pragma unroll
+      for (int r = 0; r < kEpMaxRanks; ++r) {
+        if (r < a.world)
+          raw[r] = r == a.rank
+                       ? ld_cg16(reinterpret_cast<const uint4*>(static_cast<const T*>(a.partial) + row_off) + c)
+                       : ld_cg16(reinterpret_cast<const uint4*>(inbox + static_cast<size_t>(r) * slot_bytes +
+                                                                static_cast<size_t>(inbox_row) * a.H * sizeof(T)) + c);
+      }
+      float acc[V];
+#pragma unroll
+      for (int q = 0; q < V; ++q) acc[q] = 0.f;
+#pragma unroll
+      for (int r = 0; r < kEpMaxRanks; ++r) {
+        if (r < a.world) {
+          float f[V];
+          unpack16<T>(raw[r], f);
+#pragma unroll
+          for (int q = 0; q < V; ++q) acc[q] += f[q];
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < V; ++q) v[i][q] = Dt<T>::round(acc[q]);      // the all-reduce result in the model dtype
+      if (weight == nullptr) {
+        __align__(16) T o[V];
+#pragma unroll
+        for (int q = 0; q < V; ++q) o[q] = Dt<T>::from_f(v[i][q]);
+        const uint4 ov = *reinterpret_cast<uint4*>(o);
+        reinterpret_cast<uint4*>(out + row_off)[c] = ov;
+        if (PUSH) {
+          for (int r = 0; r < a.world; ++r)
+            if (r != a.rank)
+              reinterpret_cast<uint4*>(a.comm[r] + a.L.ag[p] + row_off * sizeof(T))[c] = ov;
+        }
+        continue;
+      }
+      if (residual != nullptr) {
+        float rr[V];
+        unpack16<T>(ld_cached16(reinterpret_cast<const uint4*>(residual + row_off) + c), rr);
+#pragma unroll
+        for (int q = 0; q < V; ++q) v[i][q] += rr[q];
+        __align__(16) T o[V];
+#pragma unroll
+        for (int q = 0; q < V; ++q) o[q] = Dt<T>::from_f(v[i][q]);
+        const uint4 ov = *reinterpret_cast<uint4*>(o);
+        reinterpret_cast<uint4*>(residual_out + row_off)[c] = ov;
+        if (PUSH) {
+          for (int r = 0; r < a.world; ++r)
+            if (r != a.rank)
+              reinterpret_cast<uint4*>(a.comm[r] + a.L.ag[p] + a.L.ag_plane + row_off * sizeof(T))[c] = ov;
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < V; ++q) ss = fmaf(v[i][q], v[i][q], ss);
+    }
+  }
+  if (weight == nullptr) return;
+  ss = warp_sum(ss);
+  __syncthreads();                    // s_part of the previous row has been read by everyone
+  if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = ss;
+  __syncthreads();
+  float tot = 0.f;
+#pragma unroll
+  for (int w = 0; w < kEpArThreads / 32; ++w) tot += s_part[w];
+  const float rs = rsqrtf(tot / static_cast<float>(a.H) + a.eps);
+#pragma unroll
+  for (int i = 0; i < kArMaxVec; ++i) {
+    const int c = threadIdx.x + i * kEpArThreads;
+    if (c < nvec) {
+      float g[V];
+      unpack16<T>(ld_cached16(reinterpret_cast<const uint4*>(weight) + c), g);
+      __align__(16) T o[V];
+#pragma unroll
+      for (int q = 0; q < V; ++q) o[q] = Dt<T>::from_f(Dt<T>::round(v[i][q] * rs) * g[q]);
+      const uint4 ov = *reinterpret_cast<uint4*>(o);
+      reinterpret_cast<uint4*>(out + row_off)[c] = ov;
+      if (PUSH) {
+        for (int r = 0; r < a.world; ++r)
+          if (r != a.rank) reinterpret_cast<uint4*>(a.comm[r] + a.L.ag[p] + row_off * sizeof(T))[c] = ov;
+      }
+    }
+  }
+}
+
+}  // namespace
+
+template <typename T>
+__global__ void __launch_bounds__(kEpArThreads, 2) ep_ar_oneshot_kernel(const EpArArgs a) {
+  constexpr int V = Dt<T>::kVec;
+  __shared__ float s_part[kEpArThreads / 32];
+  __shared__ int s_flag;
+  pdl_wait();        // the partial sums are the direct predecessor's output
+  pdl_launch();
+  int32_t* ctl = reinterpret_cast<int32_t*>(a.comm[a.rank] + a.L.ctl);
+  const int e = *reinterpret_cast<volatile int32_t*>(ctl) + 1;
+  const int p = e & 1;
+  const int nvec = a.H / V;
+  // ---- push: my partial rows into inbox[p][me] of every peer ----
+  if (a.world > 1) {
+    for (int t = blockIdx.x; t < a.tokens; t += gridDim.x) {
+      const size_t row_off = static_cast<size_t>(t) * a.H;
+      const uint4* src = reinterpret_cast<const uint4*>(static_cast<const T*>(a.partial) + row_off);
+      for (int c = threadIdx.x; c < nvec; c += kEpArThreads) {
+        const uint4 val = ld_cg16(src + c);
+        for (int r = 0; r < a.world; ++r)
+          if (r != a.rank)
+            reinterpret_cast<uint4*>(a.comm[r] + a.L.os[p] + static_cast<size_t>(a.rank) * a.L.os_slot +
+                                     row_off * sizeof(T))[c] = val;
+      }
+    }
+    if (block_ticket(ctl + 1, &s_flag) && threadIdx.x < a.world) {
+      int32_t* peer_ctl = reinterpret_cast<int32_t*>(a.comm[threadIdx.x] + a.L.ctl);
+      st_release_sys(peer_ctl + 16 + a.rank, e * 4 + kEpArModeOne);
+    }
+    if (threadIdx.x < a.world) wait_flag(ctl + 16 + threadIdx.x, e, kEpArModeOne, ctl);
+    __syncthreads();
+  }
+  // ---- reduce + residual add + norm: every rank, every row (identical bits everywhere) ----
+  const unsigned char* inbox = a.comm[a.rank] + a.L.os[p];
+  for (int t = blockIdx.x; t < a.tokens; t += gridDim.x)
+    reduce_norm_row<T, false>(a, t, inbox, a.L.os_slot, t, p, s_part);
+  // ---- retire: last block bumps the epoch and re-arms the tickets ----
+  if (block_ticket(ctl + 3, &s_flag) && threadIdx.x == 0) {
+    ctl[1] = 0;
+    ctl[3] = 0;
+    *reinterpret_cast<volatile int32_t*>(ctl) = e;
+    __threadfence();
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kEpArThreads, 2) ep_ar_twoshot_kernel(const EpArArgs a) {
+  constexpr int V = Dt<T>::kVec;
+  __shared__ float s_part[kEpArThreads / 32];
+  __shared__ int s_flag;
+  pdl_wait();
+  pdl_launch();
+  int32_t* ctl = reinterpret_cast<int32_t*>(a.comm[a.rank] + a.L.ctl);
+  const int e = *reinterpret_cast<volatile int32_t*>(ctl) + 1;
+  const int p = e & 1;
+  const int nvec = a.H / V;
+  const int lo = min(a.rank * a.per, a.tokens);
+  const int hi = min(lo + a.per, a.tokens);
+  // ---- reduce-scatter, push side: my partial rows of slice s -> rank s ----
+  for (int t = blockIdx.x; t < a.tokens; t += gridDim.x) {
+    const int s = t / a.per;
+    if (s == a.rank) continue;
+    const size_t row_off = static_cast<size_t>(t) * a.H;
+    const uint4* src = reinterpret_cast<const uint4*>(static_cast<const T*>(a.partial) + row_off);
+    uint4* dst = reinterpret_cast<uint4*>(a.comm[s] + a.L.rs[p] + static_cast<size_t>(a.rank) * a.L.rs_slot +
+                                          static_cast<size_t>(t - s * a.per) * a.H * sizeof(T));
+    for (int c = threadIdx.x; c < nvec; c += kEpArThreads) dst[c] = ld_cg16(src + c);
+  }
+  if (block_ticket(ctl + 1, &s_flag) && threadIdx.x < a.world) {
+    int32_t* peer_ctl = reinterpret_cast<int32_t*>(a.comm[threadIdx.x] + a.L.ctl);
+    st_release_sys(peer_ctl + 16 + a.rank, e * 4 + kEpArModeTwo);
+  }
+  if (threadIdx.x < a.world) wait_flag(ctl + 16 + threadIdx.x, e, kEpArModeTwo, ctl);
+  __syncthreads();
+  // ---- my token slice: reduce, residual add, norm; finished rows to `out` and to every peer ----
+  const unsigned char* inbox = a.comm[a.rank] + a.L.rs[p];
+  for (int t = lo + blockIdx.x; t < hi; t += gridDim.x)
+    reduce_norm_row<T, true>(a, t, inbox, a.L.rs_slot, t - lo, p, s_part);
+  if (block_ticket(ctl + 3, &s_flag) && threadIdx.x < a.world) {
+    int32_t* peer_ctl = reinterpret_cast<int32_t*>(a.comm[threadIdx.x] + a.L.ctl);
+    st_release_sys(peer_ctl + 32 + a.rank, e * 4 + kEpArModeTwo);
+  }
+  if (threadIdx.x < a.world) wait_flag(ctl + 32 + threadIdx.x, e, kEpArModeTwo, ctl);
+  __syncthreads();
+  // ---- all-gather, local side: the other ranks' slices from my inbox ----
+  const unsigned char* ag = a.comm[a.rank] + a.L.ag[p];
+  const bool two_planes = a.weight != nullptr && a.residual != nullptr;
+  for (int t = blockIdx.x; t < a.tokens; t += gridDim.x) {
+    if (t >= lo && t < hi) continue;
+    const size_t row_off = static_cast<size_t>(t) * a.H;
+    for (int c = threadIdx.x; c < nvec; c += kEpArThreads) {
+      reinterpret_cast<uint4*>(static_cast<T*>(a.out) + row_off)[c] =
+          ld_cg16(reinterpret_cast<const uint4*>(ag + row_off * sizeof(T)) + c);
+      if (two_planes)
+        reinterpret_cast<uint4*>(static_cast<T*>(a.residual_out) + row_off)[c] =
+            ld_cg16(reinterpret_cast<const uint4*>(ag + a.L.ag_plane + row_off * sizeof(T)) + c);
+    }
+  }
+  if (block_ticket(ctl + 4, &s_flag) && threadIdx.x == 0) {
+    ctl[1] = 0;
+    ctl[3] = 0;
+    ctl[4] = 0;
+    *reinterpret_cast<volatile int32_t*>(ctl) = e;
+    __threadfence();
+  }
+}
+
+EpCommLayout ep_comm_layout(int max_tokens, int H, int dtype, int world) {
+  EpCommLayout L{};
+  const size_t es = dtype_size(dtype);
+  const size_t row = static_cast<size_t>(H) * es;
+  auto up = [](size_t v) { return (v + 1023) / 1024 * 1024; };
+  size_t off = 0;
+  L.ctl = off;
+  off += 1024;
+  const size_t full = up(static_cast<size_t>(max_tokens) * row);
+  L.os_slot = full < kEpArOneShotSlot ? full : kEpArOneShotSlot;
+  for (int p = 0; p < 2; ++p) {
+    L.os[p] = off;
+    off += L.os_slot * world;
+  }
+  const size_t per_cap = (static_cast<size_t>(max_tokens) + world - 1) / world;
+  L.rs_slot = up(per_cap * row);
+  for (int p = 0; p < 2; ++p) {
+    L.rs[p] = off;
+    off += L.rs_slot * world;
+  }
+  L.ag_plane = full;
+  for (int p = 0; p < 2; ++p) {
+    L.ag[p] = off;
+    off += 2 * L.ag_plane;
+  }
+  L.total = off;
+  return L;
+}
+
+int ep_allreduce_launch(const EpArArgs& a, int dtype, int two_shot, void* stream) {
+  if (a.world < 1 || a.world > kEpMaxRanks || a.rank < 0 || a.rank >= a.world) return GLM4MOE_ERR_ARG;
+  if (dtype != GLM4MOE_BF16 && dtype != GLM4MOE_F16) return GLM4MOE_ERR_UNSUPPORTED;
+  if (a.H % 8 != 0 || a.H / 8 > kEpArThreads * kArMaxVec || a.tokens <= 0) return GLM4MOE_ERR_UNSUPPORTED;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int dev = 0, sms = 0;
+  GLM4MOE_CUDA_CHECK(cudaGetDevice(&dev));
+  GLM4MOE_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  // every block waits for the peers inside the kernel: the whole grid must be co-resident (2 blocks / SM by
+  // __launch_bounds__)
+  const int cap = sms * 2;
+  int grid = a.tokens < cap ? a.tokens : cap;
+  if (grid < 1) grid = 1;
+  if (two_shot) {
+    if (dtype == GLM4MOE_BF16)
+      GLM4MOE_CUDA_CHECK(launch_pdl(ep_ar_twoshot_kernel<__nv_bfloat16>, dim3(grid), dim3(kEpArThreads), 0, st, a));
+    else
+      GLM4MOE_CUDA_CHECK(launch_pdl(ep_ar_twoshot_kernel<__half>, dim3(grid), dim3(kEpArThreads), 0, st, a));
+  } else {
+    if (dtype == GLM4MOE_BF16)
+      GLM4MOE_CUDA_CHECK(launch_pdl(ep_ar_oneshot_kernel<__nv_bfloat16>, dim3(grid), dim3(kEpArThreads), 0, st, a));
+    else
+      GLM4MOE_CUDA_CHECK(launch_pdl(ep_ar_oneshot_kernel<__half>, dim3(grid), dim3(kEpArThreads), 0, st, a));
+  }
+  return GLM4MOE_OK;
+}
+
+}  // namespace glm4moe

@@ -81,6 +81,10 @@ enum { GLM4MOE_KNOB_DIRECT = 0, GLM4MOE_KNOB_FUSED = 1, GLM4MOE_KNOB_FP8_PREFILL
                                        decode_fused as for larger decode batches */,
        GLM4MOE_KNOB_TAIL_BOX = 10 /* 1 (default): a ragged token tile of the tensor-core grouped GEMM is fetched
                                      through a TMA box just large enough for its rows; 0 = always a whole tile box */,
+       GLM4MOE_KNOB_EP_AR_MODE = 11 /* fused all-reduce + residual add + RMSNorm over peer memory
+                                       (glm4moe_ep_allreduce_add_rmsnorm): -1 (default) one-shot or two-shot by size,
+                                       0 one-shot whenever the batch fits its inbox, 1 always two-shot (reduce-scatter ->
+                                       norm on the token shard -> all-gather); must be the same on every rank */,
        GLM4MOE_KNOB_FP8_MX = 8 /* FP8_BLOCK128_POW2 layers at prefill: 1 (default) = hardware block scaling, one CTA
                                   per tile (gate_up token-major umma_fp8_mx_tm.cu, down feature-major
                                   umma_fp8_mx.cu); 2 = hardware block scaling on CTA pairs, 256-token x 256-row tiles
@@ -226,6 +230,38 @@ int glm4moe_p2p_free(void* ptr);
 int glm4moe_layer_forward_ep_p2p(glm4moe_layer_t* layer, const void* x, void* out, int T,
                                  void* const* peer_workspaces, int rank, int world, void* stream);
 int glm4moe_set_ep_sliced(int mode);
+
+
+/* ---- the norm in front of the block fused to the block (decode_layer.py:98-99 as one call) --------------------
+ * out = Glm4MoeMoE.forward(post_attention_layernorm(x, residual)[0]), residual_out = round(x + residual): the
+ * arithmetic of glm4moe_add_rmsnorm followed by glm4moe_layer_forward, one launch chain, the normalised tokens
+ * never leave the layer workspace.  residual == NULL: plain RMSNorm (layernorm.py:17-26). */
+int glm4moe_layer_forward_prenorm(glm4moe_layer_t* layer, const void* x, const void* residual,
+                                  const void* norm_weight, float eps, void* residual_out, void* out, int T,
+                                  void* stream);
+
+/* ---- the tensor-parallel boundary in front of the block, fused over NVLink peer memory -----------
+ * Replaces `dist.all_reduce(y)` of RowParallelLinear.forward (linear.py:153-154; the attention o_proj) TOGETHER
+ * with the residual add + RMSNorm that follows it (layernorm.py:29-40, decode_layer.py:98): every rank passes its
+ * PARTIAL sums [T, H]; ONE kernel per rank produces, identically on every rank,
+ *   y = round(sum_r partial_r)  (fp32, ascending rank)      residual_out = round(y + residual)
+ *   out = round(round((y + residual) * rsqrt(mean((y + residual)^2) + eps)) * weight)
+ * weight == NULL (then residual must be NULL too): out = y, a plain all-reduce.  No NCCL call, graph capturable.
+ * Small batches are one-shot (partials pushed to every peer, one flag round); large ones run reduce-scatter ->
+ * norm on the rank's token shard -> all-gather inside the same launch (csrc/ep_allreduce.cu).
+ * peer_comm[r]: rank r's communication buffer as mapped in this process (glm4moe_p2p_alloc / _open, zero-filled,
+ * glm4moe_ep_comm_bytes(max_tokens, H, dtype, world) bytes, one per process, shared by all layers); every rank
+ * passes the same max_tokens and calls the entry the same number of times with the same T. */
+size_t glm4moe_ep_comm_bytes(int max_tokens, int H, int dtype, int world);
+int glm4moe_ep_allreduce_add_rmsnorm(void* const* peer_comm, int rank, int world, int max_tokens,
+                                     const void* partial, const void* residual, const void* weight, float eps,
+                                     int T, int H, int dtype, void* out, void* residual_out, void* stream);
+/* o_proj partial sums -> fused all-reduce + add + norm -> expert-parallel block (glm4moe_layer_forward_ep_p2p):
+ * the reference's decode_layer.py:96-99 from the output of the o_proj GEMM to the block's output. */
+int glm4moe_layer_forward_ep_p2p_prenorm(glm4moe_layer_t* layer, const void* partial, const void* residual,
+                                         const void* norm_weight, float eps, void* residual_out, void* out, int T,
+                                         void* const* peer_workspaces, void* const* peer_comm,
+                                         int comm_max_tokens, int rank, int world, void* stream);
 
 #ifdef __cplusplus
 }
