@@ -62,6 +62,99 @@ def dispatch_plan(idx: torch.Tensor, n_experts: int, world: int):
     return mask, mask.sum(0)
 
 
+class PeerComm:
+    """One peer-mapped communication buffer per process for the fused all-reduce + residual add + RMSNorm
+    (`csrc/ep_allreduce.cu`): replaces `dist.all_reduce(y)` of the reference's
+    `RowParallelLinear.forward` (`nanovllm/layers/linear.py:153-154`) TOGETHER with the add + RMSNorm that follows
+    the attention block (`layers/layernorm.py:29-40`, `decode_layer.py:98`).  Collective constructor: every rank
+    allocates `glm4moe_ep_comm_bytes(max_tokens, H, dtype, world)` with `glm4moe_p2p_alloc`, the cudaIpc handles
+    are exchanged on the host once (`all_gather_object`), every peer's buffer is mapped.  Shared by all layers;
+    every rank must make the same sequence of calls with the same token counts."""
+
+    def __init__(self, max_tokens: int, hidden_size: int, dtype: torch.dtype, group=None, device=None):
+        import ctypes as C
+        from . import _lib
+        lib = _lib.load()
+        self.group = group
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        self.max_tokens, self.hidden_size, self.dtype = int(max_tokens), int(hidden_size), dtype
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        nbytes = lib.glm4moe_ep_comm_bytes(self.max_tokens, self.hidden_size, _lib.DTYPE_CODE[dtype], self.world)
+        if nbytes == 0:
+            raise _lib.Glm4MoeLibraryError(f"no peer-memory all-reduce for H={hidden_size}, {dtype}, world={self.world}")
+        self.nbytes = nbytes
+        ptr, hbuf = C.c_void_p(), C.create_string_buffer(64)
+        with torch.cuda.device(self.device):
+            _lib.check(lib.glm4moe_p2p_alloc(nbytes + 1024, C.byref(ptr), hbuf), "p2p_alloc")
+        self._ptr = ptr.value
+        base = (self._ptr + 1023) // 1024 * 1024
+        gathered = [None] * self.world
+        dist.all_gather_object(gathered, (hbuf.raw, base - self._ptr), group=group)
+        self.bases = (C.c_void_p * self.world)()
+        self._opened = []
+        for r, (h, off) in enumerate(gathered):
+            if r == self.rank:
+                self.bases[r] = base
+                continue
+            p = C.c_void_p()
+            with torch.cuda.device(self.device):
+                _lib.check(lib.glm4moe_p2p_open(h, C.byref(p)), "p2p_open")
+            self._opened.append(p.value)
+            self.bases[r] = p.value + off
+        dist.barrier(group=group)      # nobody launches before every mapping exists
+
+    def allreduce_add_rmsnorm(self, partial: torch.Tensor, residual: torch.Tensor | None = None,
+                              weight: torch.Tensor | None = None, eps: float = 1e-6):
+        """`y = all_reduce(partial)` (fp32 sum in rank order, one rounding), then the reference's
+        `add_rms_forward(y, residual)` / `rms_forward(y)` in the same kernel.  Returns `(out, residual_out)`
+        with a residual, `out` without; `weight=None` is a plain all-reduce."""
+        from . import _lib
+        H = partial.shape[-1]
+        x = partial.reshape(-1, H)
+        if not x.is_contiguous():
+            x = x.contiguous()
+        _lib.require_cuda(x, "partial")
+        if x.dtype != self.dtype or H != self.hidden_size:
+            raise _lib.Glm4MoeLibraryError(f"partial {x.dtype} [.., {H}] != comm {self.dtype} [.., {self.hidden_size}]")
+        T = x.shape[0]
+        if T > self.max_tokens:
+            raise _lib.Glm4MoeLibraryError(f"{T} tokens exceed the comm buffer's {self.max_tokens}")
+        r = None
+        if residual is not None:
+            if weight is None:
+                raise _lib.Glm4MoeLibraryError("a residual needs the norm weight")
+            r = residual.reshape(-1, H)
+            if not r.is_contiguous():
+                r = r.contiguous()
+            if r.shape != x.shape or r.dtype != x.dtype:
+                raise _lib.Glm4MoeLibraryError("residual must match partial in shape and dtype")
+        out = torch.empty_like(x)
+        res_out = torch.empty_like(x) if r is not None else None
+        if T:
+            with torch.cuda.device(x.device):
+                _lib.check(_lib.load().glm4moe_ep_allreduce_add_rmsnorm(
+                    self.bases, self.rank, self.world, self.max_tokens, x.data_ptr(), _lib.ptr(r), _lib.ptr(weight),
+                    float(eps), T, H, _lib.DTYPE_CODE[x.dtype], out.data_ptr(), _lib.ptr(res_out),
+                    _lib.stream_ptr(x.device)), "ep_allreduce_add_rmsnorm")
+        out = out.reshape(partial.shape)
+        return out if r is None else (out, res_out.reshape(partial.shape))
+
+    def all_reduce(self, partial: torch.Tensor) -> torch.Tensor:
+        return self.allreduce_add_rmsnorm(partial)
+
+    def close(self) -> None:
+        from . import _lib
+        if self._ptr is None:
+            return
+        torch.cuda.synchronize()
+        dist.barrier(group=self.group)
+        for p in self._opened:
+            _lib.load().glm4moe_p2p_close(p)
+        dist.barrier(group=self.group)
+        _lib.load().glm4moe_p2p_free(self._ptr)
+        self._opened, self._ptr = [], None
+
+
 class ExpertParallelMoE(nn.Module):
     def __init__(self, local_moe: nn.Module, n_experts: int, group=None, layout: str = "allreduce"):
         super().__init__()
@@ -170,6 +263,25 @@ class ExpertParallelMoE(nn.Module):
         gathered = torch.empty((R * per, H), dtype=h.dtype, device=h.device)
         dist.all_gather_into_tensor(gathered, padded, group=self.group)
         return gathered[:T].contiguous()
+
+    def forward_prenorm(self, partial: torch.Tensor, residual: torch.Tensor | None, norm_weight: torch.Tensor,
+                        eps: float, comm: "PeerComm | None" = None):
+        """`decode_layer.py:96-99` from the o_proj output to the block's output: `partial` is this rank's o_proj
+        result BEFORE the all-reduce (`linear.py:153-154`).  Layout "p2p" with a `PeerComm`: one library call
+        (fused all-reduce + add + norm kernel, then the expert-parallel block).  Otherwise the same steps with
+        NCCL: all-reduce, `glm4moe_add_rmsnorm`, this module's `forward`.  Returns `(out, residual_out)`."""
+        comm = comm if comm is not None else getattr(self, "comm", None)
+        if self.layout == "p2p" and comm is not None:
+            if self._peer_bases is None:
+                self.setup_p2p()
+            return self.local.forward_ep_p2p_prenorm(partial, residual, norm_weight, eps, self._peer_bases, comm)
+        from .layernorm import rmsnorm
+        y = partial.clone()
+        dist.all_reduce(y, group=self.group)
+        normed = rmsnorm(y, norm_weight, eps, residual)
+        if residual is None:
+            return self.forward(normed), None
+        return self.forward(normed[0]), normed[1]
 
     def forward(self, hidden_states: torch.Tensor) -> torch.Tensor:
         h = hidden_states.reshape(-1, hidden_states.shape[-1])

@@ -27,6 +27,14 @@ under `nanovllm/` is edited: `install()` imports the installed copy (`baseline/_
                                                    model_runner.py:111) while the sparse blocks are
                                                    EXPERT-parallel (`expert_parallel="p2p" | "allreduce"`,
                                                    distributed.py): BASELINE configs[3] at 2/4/8 GPUs
+  decode_layer.py:96-99    (opt-in, `fused_norm=True`) `self_attn` -> `post_attention_layernorm` -> `mlp` ->
+                                                   the o_proj GEMM keeps its PARTIAL sums (its `tp_size` is set to 1
+                                                   after construction, so `linear.py:153-154` skips the NCCL
+                                                   all-reduce) and ONE library call does all-reduce + residual add
+                                                   + RMSNorm + sparse block (`distributed.PeerComm`,
+                                                   `csrc/ep_allreduce.cu`); `RMSNorm`
+                                                   (decode_layer.py:8) becomes the one-launch kernel of
+                                                   `layernorm.py` (the reference's is ~8 torch launches)
   llm_engine.py:26         `ModelRunner` as the spawn target -> `shim_model_runner` (same arguments), which
                                                    re-applies this shim in the spawned rank before constructing
                                                    the reference's `ModelRunner`
@@ -143,16 +151,19 @@ def shim_model_runner(config, rank, event):
 
 
 def install(sparse_block: str = "ours", weight_format: str = "native", share_workspace: bool = True,
-            expert_parallel: str | None = None, dense_mlp: str = "reference"):
+            expert_parallel: str | None = None, dense_mlp: str = "reference", fused_norm: bool = False):
     """Import the reference package and apply the construction-time rebinding described above.
     `sparse_block`: "ours" (this package's `Glm4MoeMoE`) or "reference" (the reference's own block, for
     A/B runs of the same stack).  `expert_parallel`: layout of the sparse blocks when the engine runs
     `tensor_parallel_size > 1` ranks ("p2p": peer-memory combine, "allreduce": NCCL; None: every rank holds
     all experts).  `dense_mlp`: "ours" also swaps the dense MLP of the first layers (decode_layer.py:31-36) for
-    `Glm4MoeDenseMLP` (the same tensor-core grouped GEMM).  Returns the `nanovllm` package."""
+    `Glm4MoeDenseMLP` (the same tensor-core grouped GEMM).  `fused_norm`: the norms of the decoder
+    layer run as this package's kernel and the post-attention norm (with the o_proj all-reduce when
+    `tensor_parallel_size > 1`) is fused to the block that follows it.  Returns the `nanovllm` package."""
     os.environ[ENV_ARGS] = json.dumps(dict(sparse_block=sparse_block, weight_format=weight_format,
                                            share_workspace=share_workspace, expert_parallel=expert_parallel,
-                                           dense_mlp=dense_mlp))
+                                           dense_mlp=dense_mlp, fused_norm=bool(fused_norm)))
+    _installed["fused_norm"] = bool(fused_norm) and sparse_block == "ours"
     _installed["ep_layout"] = expert_parallel if sparse_block == "ours" else None
     root = reference_root()
     if root is None:
@@ -189,6 +200,8 @@ def install(sparse_block: str = "ours", weight_format: str = "native", share_wor
         _installed["ref_block"] = ref_moe.Glm4MoeMoE
         _installed["post_init"] = ref_config.Config.__post_init__
         _installed["runner"] = MR.ModelRunner
+        _installed["ref_norm"] = DL.RMSNorm
+        _installed["ref_layer_forward"] = DL.Glm4MoeDecoderLayer.forward
     LE.ModelRunner = shim_model_runner                       # llm_engine.py:26,30
     # parallel_state.py:1-9: every module that imported the dummy group by name
     tp = _TPGroup()
@@ -209,6 +222,24 @@ def install(sparse_block: str = "ours", weight_format: str = "native", share_wor
         raise ValueError(dense_mlp)
     DL.Glm4MoeMLP = ours.Glm4MoeDenseMLP if dense_mlp == "ours" else _installed["ref_dense"]   # decode_layer.py:7,31
 
+    from . import layernorm as our_norm
+    Norm = our_norm.RMSNorm if _installed["fused_norm"] else _installed["ref_norm"]
+    DL.RMSNorm = Norm                                        # decode_layer.py:8,37-38
+
+    def layer_forward(self, positions, hidden_states, residual):     # decode_layer.py:80-100
+        if residual is None:
+            hidden_states, residual = self.input_layernorm(hidden_states), hidden_states
+        else:
+            hidden_states, residual = self.input_layernorm(hidden_states, residual)
+        hidden_states = self.self_attn(hidden_states, positions)      # partial sums when the o_proj all-reduce is off
+        fused = self.__dict__.get("_fused_post")
+        if fused is not None:                                # all-reduce + add + norm + block: one library call
+            return fused(hidden_states, residual)
+        hidden_states, residual = self.post_attention_layernorm(hidden_states, residual)
+        return self.mlp(hidden_states), residual
+
+    DL.Glm4MoeDecoderLayer.forward = layer_forward if _installed["fused_norm"] else _installed["ref_layer_forward"]
+
     def model_init(self, config):                            # model.py:14-24 with the line of model.py:19
         nn.Module.__init__(self)
         import torch.distributed as dist
@@ -223,7 +254,7 @@ def install(sparse_block: str = "ours", weight_format: str = "native", share_wor
         self.embed_tokens = VocabParallelEmbedding(config.vocab_size, config.hidden_size)
         self.layers = nn.ModuleList([DL.Glm4MoeDecoderLayer(config, prefix=f"model.layers.{i}")
                                      for i in range(config.num_hidden_layers)])
-        self.norm = RMSNorm(config.hidden_size, eps=config.rms_norm_eps)
+        self.norm = Norm(config.hidden_size, eps=config.rms_norm_eps)
 
     def model_forward(self, input_ids, positions):           # model.py:63-78 with the line of model.py:75
         hidden_states = self.embed_tokens(input_ids)
@@ -245,6 +276,7 @@ def install(sparse_block: str = "ours", weight_format: str = "native", share_wor
         else:
             real_load(self, model_path)
         setup_expert_parallel(self)
+        setup_fused_norm(self)
 
     M.Glm4MoeForCausalLM.load_weights = load_weights
 
@@ -279,6 +311,45 @@ def setup_expert_parallel(model) -> int:
                 ep.setup_p2p(_installed.get("max_tokens"))
             layer.mlp = ep
             n += 1
+    return n
+
+
+def setup_fused_norm(model) -> int:
+    """`fused_norm=True`: give every decoder layer the one-call form of decode_layer.py:96-99 (collective when the
+    engine runs several ranks: the peer-mapped communication buffer is allocated and exchanged here, sized for
+    the engine's largest batch).  Returns the number of layers whose post-attention step is fused."""
+    import torch.distributed as dist
+    from . import moe as ours
+    from .distributed import ExpertParallelMoE, PeerComm
+    if not _installed.get("fused_norm"):
+        return 0
+    world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+    layers = list(model.model.layers)
+    comm = None
+    if world > 1:
+        w = layers[0].post_attention_layernorm.weight
+        comm = PeerComm(_installed.get("max_tokens") or 4096, w.numel(), w.dtype, device=w.device)
+        _installed["comm"] = comm
+    n = 0
+    for layer in layers:
+        norm, mlp = layer.post_attention_layernorm, layer.mlp
+        if world > 1:
+            # RowParallelLinear.forward reads `tp_size` only to decide on the all-reduce (linear.py:153): the
+            # weight shard was cut at construction, so the GEMM now returns this rank's partial sums
+            layer.self_attn.o_proj.tp_size = 1
+        if isinstance(mlp, ExpertParallelMoE):
+            mlp.comm = comm
+            fused = lambda h, r, m=mlp, nm=norm: m.forward_prenorm(h, r, nm.weight, nm.eps)
+        elif isinstance(mlp, ours.Glm4MoeMoE) and world == 1:
+            fused = lambda h, r, m=mlp, nm=norm: m.forward_prenorm(h, r, nm.weight, nm.eps)
+        elif world > 1:
+            def fused(h, r, m=mlp, nm=norm, c=comm):         # dense layer: fused all-reduce + add + norm, then the MLP
+                x, r2 = c.allreduce_add_rmsnorm(h, r, nm.weight, nm.eps)
+                return m(x), r2
+        else:
+            continue
+        layer.__dict__["_fused_post"] = fused
+        n += 1
     return n
 
 

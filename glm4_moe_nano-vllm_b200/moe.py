@@ -496,6 +496,44 @@ class Glm4MoeMoE(nn.Module):
                                                                _lib.stream_ptr(h.device)), "layer_forward_ex")
         return out
 
+    def forward_prenorm(self, hidden_states: torch.Tensor, residual: torch.Tensor | None, norm_weight: torch.Tensor,
+                        eps: float):
+        """`decode_layer.py:98-99` as one library call (`glm4moe_layer_forward_prenorm`):
+        `hidden, residual = post_attention_layernorm(hidden, residual); hidden = mlp(hidden)`.
+        Returns `(out [T, H], residual_out)`; `residual=None` is the plain RMSNorm form (`layernorm.py:17-26`)
+        and returns `(out, None)`.  The normalised tokens stay in the layer workspace; results are bit-identical
+        to `RMSNorm` + `forward`."""
+        h, r, T = self._prenorm_args(hidden_states, residual, norm_weight)
+        out = torch.empty_like(h)
+        res_out = torch.empty_like(h) if r is not None else None
+        if T == 0:
+            return out, res_out
+        self._ensure_layer(T)
+        with torch.cuda.device(h.device):
+            _lib.check(_lib.load().glm4moe_layer_forward_prenorm(
+                self._handle, h.data_ptr(), _lib.ptr(r), norm_weight.data_ptr(), float(eps),
+                _lib.ptr(res_out), out.data_ptr(), T, _lib.stream_ptr(h.device)), "layer_forward_prenorm")
+        return out, res_out
+
+    def _prenorm_args(self, hidden_states, residual, norm_weight):
+        h = hidden_states.reshape(-1, hidden_states.shape[-1])
+        if not h.is_contiguous():
+            h = h.contiguous()
+        _lib.require_cuda(h, "hidden_states")
+        md = self.gate.weight.dtype
+        if h.dtype != md or norm_weight.dtype != md:
+            raise _lib.Glm4MoeLibraryError(f"hidden_states {h.dtype} / norm weight {norm_weight.dtype} != model dtype {md}")
+        if norm_weight.numel() != h.shape[-1] or not norm_weight.is_contiguous():
+            raise _lib.Glm4MoeLibraryError("norm weight must be a contiguous [H] tensor")
+        r = None
+        if residual is not None:
+            r = residual.reshape(-1, residual.shape[-1])
+            if not r.is_contiguous():
+                r = r.contiguous()
+            if r.shape != h.shape or r.dtype != h.dtype:
+                raise _lib.Glm4MoeLibraryError("residual must match hidden_states in shape and dtype")
+        return h, r, h.shape[0]
+
     STAGES = ("router_logits", "router_select", "permute", "gather", "gate_up", "down", "combine", "total")
 
     def forward_timed(self, hidden_states: torch.Tensor):
@@ -760,3 +798,22 @@ class Glm4MoeMoE(nn.Module):
                                                                peer_bases, self.ep_rank, self.ep_size,
                                                                _lib.stream_ptr(h.device)), "layer_forward_ep_p2p")
         return out
+
+    def forward_ep_p2p_prenorm(self, partial: torch.Tensor, residual: torch.Tensor | None, norm_weight: torch.Tensor,
+                               eps: float, peer_bases, comm):
+        """The tensor-parallel boundary + norm + expert-parallel block in one library call
+        (`glm4moe_layer_forward_ep_p2p_prenorm`): `partial` is this rank's o_proj output BEFORE the
+        all-reduce of `linear.py:153-154`; `comm` is the process's `distributed.PeerComm`.  Returns the
+        replicated `(out, residual_out)`."""
+        h, r, T = self._prenorm_args(partial, residual, norm_weight)
+        out = torch.empty_like(h)
+        res_out = torch.empty_like(h) if r is not None else None
+        if T == 0:
+            return out, res_out
+        self._ensure_layer(T)
+        with torch.cuda.device(h.device):
+            _lib.check(_lib.load().glm4moe_layer_forward_ep_p2p_prenorm(
+                self._handle, h.data_ptr(), _lib.ptr(r), norm_weight.data_ptr(), float(eps), _lib.ptr(res_out),
+                out.data_ptr(), T, peer_bases, comm.bases, comm.max_tokens, self.ep_rank, self.ep_size,
+                _lib.stream_ptr(h.device)), "layer_forward_ep_p2p_prenorm")
+        return out, res_out

@@ -53,10 +53,14 @@ def main():
                     help="layout of the sparse blocks when --tp > 1 (none: every rank holds all experts)")
     ap.add_argument("--dense", default="reference", choices=["ours", "reference"],
                     help="dense MLP of layer 0 (decode_layer.py:31-36): ours = Glm4MoeDenseMLP (tensor-core grouped GEMM)")
+    ap.add_argument("--fused-norm", action="store_true",
+                    help="decoder-layer norms through our kernel; post-attention norm (+ the o_proj all-reduce at "
+                         "tp > 1) fused to the block that follows (engine_shim.install(fused_norm=True))")
     args = ap.parse_args()
 
     nanovllm = S.install(sparse_block=args.block, weight_format=args.weights if args.weights != "bf16" else "native",
-                         expert_parallel=None if args.ep == "none" or args.tp == 1 else args.ep, dense_mlp=args.dense)
+                         expert_parallel=None if args.ep == "none" or args.tp == 1 else args.ep, dense_mlp=args.dense,
+                         fused_norm=args.fused_norm)
     geom = dict(S.AIR_MODEL if args.preset == "air" else SMALL)
     d = args.model_dir or tempfile.mkdtemp(prefix="glm4moe_model_")
     S.make_model_dir(d, num_hidden_layers=args.layers, max_position_embeddings=max(args.max_model_len, 512), **geom)
@@ -108,7 +112,8 @@ def main():
             "prefill_tokens_per_s": prefill_tok / prefill_s if prefill_s else None,
             "decode_tokens_per_s": decode_tok / decode_s if decode_s else None,
             "decode_ms_per_step_median": ms, "decode_batch": args.seqs, "build_s": build_s,
-            "sparse_blocks_ours": len(ours),
+            "sparse_blocks_ours": len(ours), "fused_norm": bool(args.fused_norm),
+            "fused_post_layers": sum(1 for l in llm.model_runner.model.model.layers if "_fused_post" in l.__dict__),
             "last_impl": ours[0].last_impl if ours else None, "last_fused": ours[0].last_fused if ours else None,
             "gpu_mem_gb": torch.cuda.max_memory_allocated() / 1e9,
             "digest": hashlib.sha256(json.dumps(toks).encode()).hexdigest()[:16], "token_ids": toks}
