@@ -114,6 +114,29 @@ def load() -> C.CDLL:
     return lib
 
 
+NVTX = os.environ.get("GLM4MOE_NVTX", "0") == "1"
+
+
+class nvtx_range:
+    """`with nvtx_range("glm4moe.forward", T):` — an NVTX range around a host entry point when GLM4MOE_NVTX=1
+    (the reference has no tracing of its own; nsys / ncu --nvtx pick these up), else free."""
+
+    __slots__ = ("on",)
+
+    def __init__(self, name: str, T: int | None = None):
+        self.on = NVTX
+        if self.on:
+            torch.cuda.nvtx.range_push(name if T is None else f"{name} T={T}")
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        if self.on:
+            torch.cuda.nvtx.range_pop()
+        return False
+
+
 def check(code: int, what: str = "") -> None:
     if code != 0:
         msg = load().glm4moe_error_string(code).decode()

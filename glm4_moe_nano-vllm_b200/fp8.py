@@ -65,7 +65,7 @@ def convert_checkpoint(src: str, dst: str, prefixes=None, pow2_scales: bool = Fa
     (optionally restricted to keys starting with one of `prefixes`) is replaced by an e4m3 `weight`
     and an fp32 `weight_scale_inv [rows/128, cols/128]`; router weights, the fp32
     `e_score_correction_bias` and everything outside the sparse block are copied through untouched.
-    One pass, one tensor in memory at a time.  Returns {"converted": n, "copied": m}."""
+    One pass over the keys; one output FILE is held in memory at a time (safetensors writes a file whole).  Returns {"converted": n, "copied": m}."""
     import os
     import re
     from safetensors import safe_open

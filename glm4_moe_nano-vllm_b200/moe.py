@@ -486,7 +486,7 @@ class Glm4MoeMoE(nn.Module):
         if T == 0:
             return out
         self._ensure_layer(T)
-        with torch.cuda.device(h.device):
+        with torch.cuda.device(h.device), _lib.nvtx_range("glm4moe.forward", T):
             if shared_range is None:
                 _lib.check(_lib.load().glm4moe_layer_forward(self._handle, h.data_ptr(), out.data_ptr(), T,
                                                             _lib.stream_ptr(h.device)), "layer_forward")
@@ -509,7 +509,7 @@ class Glm4MoeMoE(nn.Module):
         if T == 0:
             return out, res_out
         self._ensure_layer(T)
-        with torch.cuda.device(h.device):
+        with torch.cuda.device(h.device), _lib.nvtx_range("glm4moe.forward_prenorm", T):
             _lib.check(_lib.load().glm4moe_layer_forward_prenorm(
                 self._handle, h.data_ptr(), _lib.ptr(r), norm_weight.data_ptr(), float(eps),
                 _lib.ptr(res_out), out.data_ptr(), T, _lib.stream_ptr(h.device)), "layer_forward_prenorm")
@@ -793,7 +793,7 @@ class Glm4MoeMoE(nn.Module):
         if T == 0:
             return out
         self._ensure_layer(T)
-        with torch.cuda.device(h.device):
+        with torch.cuda.device(h.device), _lib.nvtx_range("glm4moe.forward_ep_p2p", T):
             _lib.check(_lib.load().glm4moe_layer_forward_ep_p2p(self._handle, h.data_ptr(), out.data_ptr(), T,
                                                                peer_bases, self.ep_rank, self.ep_size,
                                                                _lib.stream_ptr(h.device)), "layer_forward_ep_p2p")
@@ -811,7 +811,7 @@ class Glm4MoeMoE(nn.Module):
         if T == 0:
             return out, res_out
         self._ensure_layer(T)
-        with torch.cuda.device(h.device):
+        with torch.cuda.device(h.device), _lib.nvtx_range("glm4moe.forward_ep_p2p_prenorm", T):
             _lib.check(_lib.load().glm4moe_layer_forward_ep_p2p_prenorm(
                 self._handle, h.data_ptr(), _lib.ptr(r), norm_weight.data_ptr(), float(eps), _lib.ptr(res_out),
                 out.data_ptr(), T, peer_bases, comm.bases, comm.max_tokens, self.ep_rank, self.ep_size,

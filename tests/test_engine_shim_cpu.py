@@ -122,7 +122,8 @@ def test_multi_rank_plumbing(tmp_path):
     assert llm_engine.ModelRunner is S.shim_model_runner
     assert pickle.loads(pickle.dumps(S.shim_model_runner)) is S.shim_model_runner
     assert json.loads(os.environ[S.ENV_ARGS]) == dict(sparse_block="ours", weight_format="fp8", share_workspace=True,
-                                                      expert_parallel="p2p", dense_mlp="reference")
+                                                      expert_parallel="p2p", dense_mlp="reference",
+                                                      fused_norm=False)
     d = S.make_model_dir(str(tmp_path / "m"), **SMALL)
     from nanovllm.config import Config
     cfg = pickle.loads(pickle.dumps(Config(d, max_num_batched_tokens=512, max_model_len=256)))
@@ -130,6 +131,55 @@ def test_multi_rank_plumbing(tmp_path):
     assert cfg.hf_config.torch_dtype == torch.bfloat16
     S.install()            # back to the defaults for the other tests
     assert json.loads(os.environ[S.ENV_ARGS])["expert_parallel"] is None
+
+
+def test_fused_norm_plumbing(tmp_path, group):
+    """`install(fused_norm=True)` (SURVEY 8f-2 part i / 8f-4): decode_layer.py:8 resolves to this package's RMSNorm,
+    every sparse layer carries the one-call form of decode_layer.py:98-99 and the patched layer forward routes
+    through it (stub callable: the real one needs the GPU library), the dense layer keeps the two-step form on
+    one rank; `install()` puts the reference's own forward and norm back."""
+    S.install()
+    from nanovllm.models.glm4_moe import decode_layer as DL
+    ref_forward = S._installed.get("ref_layer_forward", DL.Glm4MoeDecoderLayer.forward)
+    S.install(sparse_block="ours", fused_norm=True)
+    try:
+        from glm4_moe_b200 import layernorm as LN
+        assert DL.RMSNorm is LN.RMSNorm and DL.Glm4MoeDecoderLayer.forward is not ref_forward
+        d = S.make_model_dir(str(tmp_path / "m"), **SMALL)
+        from nanovllm.config import Config
+        from nanovllm.models.glm4_moe import Glm4MoeForCausalLM
+        hf = Config(d, max_num_batched_tokens=512, max_model_len=256).hf_config
+        prev = torch.get_default_dtype()
+        torch.set_default_dtype(hf.torch_dtype)
+        try:
+            model = Glm4MoeForCausalLM(hf)
+        finally:
+            torch.set_default_dtype(prev)
+        model.load_weights(d)
+        layers = model.model.layers
+        assert isinstance(layers[1].input_layernorm, LN.RMSNorm) and isinstance(model.model.norm, LN.RMSNorm)
+        assert "_fused_post" not in layers[0].__dict__                   # dense layer, one rank: nothing to fuse
+        assert all("_fused_post" in l.__dict__ for l in layers[1:])
+        # the patched forward hands (attention output, residual) to the fused callable and returns its pair
+        lay = layers[1]
+        calls = []
+        class Norm(torch.nn.Module):
+            def forward(self, h, r=None):
+                return (h + 1, h) if r is not None else h + 1
+
+        class Attn(torch.nn.Module):
+            def forward(self, h, pos):
+                return h * 2
+
+        lay.input_layernorm, lay.self_attn = Norm(), Attn()
+        lay.__dict__["_fused_post"] = lambda h, r: (calls.append((h.clone(), r.clone())) or (h - r, r + 7))
+        x = torch.ones(3, 4)
+        out, res = lay(torch.arange(3), x, None)
+        assert torch.equal(calls[0][0], (x + 1) * 2) and torch.equal(calls[0][1], x)
+        assert torch.equal(out, (x + 1) * 2 - x) and torch.equal(res, x + 7)
+    finally:
+        S.install()
+    assert DL.Glm4MoeDecoderLayer.forward is ref_forward and DL.RMSNorm is S._installed["ref_norm"]
 
 
 def test_random_init_of_an_expert_parallel_shard_equals_the_single_gpu_block(tmp_path):

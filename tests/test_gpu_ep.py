@@ -73,6 +73,125 @@ def _worker(rank, world, port, q):
         dist.destroy_process_group()
 
 
+def _worker_front(rank, world, port, q):
+    """Fused all-reduce + residual add + RMSNorm over peer memory (csrc/ep_allreduce.cu) and the
+    one-call form o_proj partial sums -> norm -> expert-parallel block."""
+    import glm4_moe_b200
+    from glm4_moe_b200 import synth, _lib
+    from glm4_moe_b200 import layernorm as LN
+    from glm4_moe_b200.distributed import ExpertParallelMoE, PeerComm
+    from test_gpu_parity import _module
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    lib = _lib.load()
+    try:
+        shape, dt, eps = synth.MINI, torch.bfloat16, 1e-5
+        H = shape.H
+        comm = PeerComm(3000, H, dt)
+        g = torch.Generator().manual_seed(5)
+        nw = (1.0 + 0.1 * torch.randn(H, generator=g)).to(dt).cuda()
+        checked = 0
+
+        def parts_of(T, seed):
+            gg = torch.Generator().manual_seed(seed)
+            parts = [(0.5 * torch.randn(T, H, generator=gg)).to(dt) for _ in range(world)]
+            res = torch.randn(T, H, generator=gg).to(dt).cuda()
+            acc = torch.zeros(T, H)
+            for p_ in parts:                     # fp32, ascending rank: the kernel's order
+                acc += p_.float()
+            return parts, res, acc.to(dt).cuda()
+
+        # T < world, ragged slices, the one-shot capacity edge (1 MiB = 1024 rows of 512 bf16) and beyond it
+        for T in (1, 3, 32, 130, 1024, 1025, 3000):
+            parts, res, y = parts_of(T, 1000 + T)
+            mine = parts[rank].cuda()
+            want_n, want_r = LN.rmsnorm(y, nw, eps, res)
+            want_p = LN.rmsnorm(y, nw, eps)
+            for mode in (-1, 0, 1, 1, 0, -1):
+                _lib.check(lib.glm4moe_debug_set(11, mode))
+                dist.barrier()
+                for rep in range(2):
+                    out, r_out = comm.allreduce_add_rmsnorm(mine, res, nw, eps)
+                    assert torch.equal(out, want_n) and torch.equal(r_out, want_r), f"T={T} mode={mode} rep={rep}"
+                assert torch.equal(comm.allreduce_add_rmsnorm(mine, None, nw, eps), want_p), f"T={T} mode={mode}"
+                assert torch.equal(comm.all_reduce(mine), y), f"T={T} mode={mode}: plain all-reduce"
+                checked += 4
+            if world == 2:        # a + b in fp32, one rounding: what NCCL computes for two ranks
+                z = mine.clone()
+                dist.all_reduce(z)
+                assert torch.equal(z, y)
+        _lib.check(lib.glm4moe_debug_set(11, -1))
+        # CUDA-graph capture + replay (epoch and tickets live in the comm buffer)
+        parts, res, y = parts_of(32, 77)
+        mine = parts[rank].cuda()
+        want_n, want_r = LN.rmsnorm(y, nw, eps, res)
+        dist.barrier()
+        side = torch.cuda.Stream()
+        with torch.cuda.stream(side):
+            comm.allreduce_add_rmsnorm(mine, res, nw, eps)
+        side.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            g_out, g_res = comm.allreduce_add_rmsnorm(mine, res, nw, eps)
+        for rep in range(3):
+            g_out.zero_()
+            graph.replay()
+            torch.cuda.synchronize()
+            assert torch.equal(g_out, want_n) and torch.equal(g_res, want_r), f"graph replay {rep}"
+        # o_proj partial sums -> fused all-reduce + add + norm -> expert-parallel block, one library call
+        wts = synth.make_weights(shape, dt)
+        single = _module(shape, dt, wts, max_tokens=512)
+        local = _module(shape, dt, wts, ep_rank=rank, ep_size=world, max_tokens=512, peer_workspace=True)
+        ep = ExpertParallelMoE(local, shape.E, layout="p2p")
+        ep.comm = comm
+        local_nccl = _module(shape, dt, wts, ep_rank=rank, ep_size=world, max_tokens=512)
+        ep_nccl = ExpertParallelMoE(local_nccl, shape.E, layout="allreduce")
+        for T in (1, 5, 32, 300):
+            parts, res, y = parts_of(T, 2000 + T)
+            mine = parts[rank].cuda()
+            with torch.inference_mode():
+                want, want_r = single.forward_prenorm(y, res, nw, eps)
+                for rep in range(3):
+                    got, got_r = ep.forward_prenorm(mine, res, nw, eps)
+                    assert torch.equal(got_r, want_r), f"T={T} rep={rep}: residual stream"
+                    assert torch.equal(got, want), f"T={T} rep={rep}: block output differs from one GPU"
+                got2, got2_r = ep_nccl.forward_prenorm(mine, res, nw, eps)     # the same steps over NCCL
+                if world == 2:
+                    assert torch.equal(got2_r, want_r)
+                d = float((got2.float() - want.float()).abs().max() / want.float().abs().max())
+                assert d < 3e-2, d
+            checked += 4
+        torch.cuda.synchronize()
+        ep.close_p2p()
+        comm.close()
+        q.put((rank, checked))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_fused_allreduce_norm_and_prenorm_block_two_gpus():
+    """world = 2 by default; GLM4MOE_TEST_WORLD=4/8 for more ranks of one box."""
+    world = int(os.environ.get("GLM4MOE_TEST_WORLD", "2"))
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker_front, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    out = [q.get(timeout=600) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    assert all(n > 0 for _, n in out)
+
+
 def test_expert_parallel_two_gpus():
     """world = 2 by default; GLM4MOE_TEST_WORLD=4/8 runs the same checks over more ranks of one box."""
     world = int(os.environ.get("GLM4MOE_TEST_WORLD", "2"))

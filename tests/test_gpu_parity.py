@@ -10,6 +10,7 @@ import torch
 
 import glm4_moe_b200
 from glm4_moe_b200 import synth, _lib
+from glm4_moe_b200 import layernorm as LN
 from oracle import moe_oracle as O
 from conftest import load_golden, dtype_of
 
@@ -1164,6 +1165,130 @@ def test_rmsnorm_vs_reference_golden(name):
     with torch.inference_mode():
         again, _ = norm(x, res)
     assert torch.equal(again, y1[0])
+
+
+@pytest.mark.parametrize("shape_name,dt,Ts", [("mini", torch.bfloat16, (1, 2, 7, 32, 33, 300)),
+                                              ("mini", torch.float16, (1, 16, 200)),
+                                              ("glm-4.5-air", torch.bfloat16, (1, 2, 32, 256))])
+def test_forward_prenorm_matches_norm_then_block(shape_name, dt, Ts):
+    """`glm4moe_layer_forward_prenorm` (decode_layer.py:98-99 as one call) against the two steps it fuses:
+    the norm against the ORACLE (`oracle.rmsnorm`: residual stream bit-exact, normalised tokens within one
+    ulp), the block's output BIT-IDENTICAL to `RMSNorm` mirror + `forward` (same kernels, the normalised
+    tokens only live in the workspace), in every regime (merged one-launch front end at T <= 2, fused decode
+    kernel, general path) and repeatedly."""
+    shape = synth.SHAPES[shape_name]
+    wts = synth.make_weights(shape, dt)
+    moe = _module(shape, dt, wts, max_tokens=512)
+    g = torch.Generator().manual_seed(99)
+    nw = (1.0 + 0.1 * torch.randn(shape.H, generator=g)).to(dt)
+    eps = 1e-5
+    for T in Ts:
+        x = synth.make_tokens(shape, T, dt, 300 + T)
+        res = synth.make_tokens(shape, T, dt, 900 + T)
+        want_n, want_r = O.rmsnorm(x, nw, eps, res)
+        with torch.inference_mode():
+            n_gpu, r_gpu = LN.rmsnorm(x.cuda(), nw.cuda(), eps, res.cuda())
+            want_out = moe(n_gpu)
+            for rep in range(2):
+                out, r_out = moe.forward_prenorm(x.cuda(), res.cuda(), nw.cuda(), eps)
+                assert torch.equal(r_out, r_gpu) and torch.equal(out, want_out), f"T={T} rep={rep}"
+            # plain RMSNorm form (no residual), 3-D input like the runner's
+            out0, r0 = moe.forward_prenorm(x.cuda().view(1, T, -1), None, nw.cuda(), eps)
+            assert r0 is None
+            assert torch.equal(out0, moe(LN.rmsnorm(x.cuda(), nw.cuda(), eps)))
+        assert torch.equal(r_gpu.cpu(), want_r)
+        d = (n_gpu.float().cpu() - want_n.float()).abs()
+        assert bool((d <= 2 * _ulp(dt) * want_n.float().abs() + 1e-30).all())
+        assert float((d > 0).float().mean()) < 5e-3
+
+
+def _peer_buffer(nbytes):
+    """(ptr, 1 KB-aligned base) of a zeroed cudaIpc-exportable allocation"""
+    import ctypes as C
+    ptr, hbuf = C.c_void_p(), C.create_string_buffer(64)
+    _lib.check(_lib.load().glm4moe_p2p_alloc(nbytes + 1024, C.byref(ptr), hbuf), "p2p_alloc")
+    return ptr.value, (ptr.value + 1023) // 1024 * 1024
+
+
+@pytest.mark.parametrize("H,dt", [(4096, torch.bfloat16), (1024, torch.float16), (5120, torch.bfloat16)])
+def test_fused_allreduce_norm_world1(H, dt):
+    """`glm4moe_ep_allreduce_add_rmsnorm` with a world of one rank (no peer: the all-reduce is the identity),
+    one-shot and two-shot form interleaved on the same epoch counter: bit-identical to `glm4moe_add_rmsnorm`
+    (same thread mapping and summation order); weight == NULL returns the input (plain all-reduce).  The
+    2/8-rank runs are in test_gpu_ep.py."""
+    import ctypes as C
+    lib = _lib.load()
+    max_tokens = 600
+    nbytes = lib.glm4moe_ep_comm_bytes(max_tokens, H, _lib.DTYPE_CODE[dt], 1)
+    assert nbytes > 0
+    raw, base = _peer_buffer(nbytes)
+    bases = (C.c_void_p * 1)(base)
+    g = torch.Generator().manual_seed(7)
+    nw = (1.0 + 0.1 * torch.randn(H, generator=g)).to(dt).cuda()
+    st = _lib.stream_ptr(torch.device("cuda"))
+    try:
+        for T in (1, 3, 32, 128, 129, 600):
+            x = torch.randn(T, H, generator=g).to(dt).cuda()
+            res = torch.randn(T, H, generator=g).to(dt).cuda()
+            want_n, want_r = LN.rmsnorm(x, nw, 1e-5, res)
+            want_p = LN.rmsnorm(x, nw, 1e-5)
+            for mode in (-1, 0, 1, 1, 0, -1):
+                _lib.check(lib.glm4moe_debug_set(11, mode))
+                out, r_out, plain, copy = (torch.empty_like(x) for _ in range(4))
+                args = (bases, 0, 1, max_tokens)
+                _lib.check(lib.glm4moe_ep_allreduce_add_rmsnorm(*args, x.data_ptr(), res.data_ptr(), nw.data_ptr(), 1e-5,
+                                                                T, H, _lib.DTYPE_CODE[dt], out.data_ptr(),
+                                                                r_out.data_ptr(), st))
+                _lib.check(lib.glm4moe_ep_allreduce_add_rmsnorm(*args, x.data_ptr(), None, nw.data_ptr(), 1e-5,
+                                                                T, H, _lib.DTYPE_CODE[dt], plain.data_ptr(), None, st))
+                _lib.check(lib.glm4moe_ep_allreduce_add_rmsnorm(*args, x.data_ptr(), None, None, 0.0,
+                                                                T, H, _lib.DTYPE_CODE[dt], copy.data_ptr(), None, st))
+                torch.cuda.synchronize()
+                assert torch.equal(out, want_n) and torch.equal(r_out, want_r), f"T={T} mode={mode}"
+                assert torch.equal(plain, want_p) and torch.equal(copy, x), f"T={T} mode={mode}"
+        # argument errors, not crashes
+        x = torch.zeros(4, H, dtype=dt, device="cuda")
+        assert lib.glm4moe_ep_allreduce_add_rmsnorm(bases, 0, 1, max_tokens, x.data_ptr(), x.data_ptr(), None, 1e-5, 4, H,
+                                                    _lib.DTYPE_CODE[dt], x.data_ptr(), x.data_ptr(), st) == -1
+        assert lib.glm4moe_ep_allreduce_add_rmsnorm(bases, 0, 1, max_tokens, x.data_ptr(), None, None, 1e-5,
+                                                    max_tokens + 1, H, _lib.DTYPE_CODE[dt], x.data_ptr(), None, st) == -1
+        assert lib.glm4moe_ep_comm_bytes(16, H, _lib.F32, 1) == 0
+    finally:
+        _lib.check(lib.glm4moe_debug_set(11, -1))
+        torch.cuda.synchronize()
+        lib.glm4moe_p2p_free(raw)
+
+
+def test_forward_ep_p2p_prenorm_world1():
+    """`glm4moe_layer_forward_ep_p2p_prenorm` with one rank: fused all-reduce + add + norm kernel, then the
+    rows-only block + peer-memory combine; bit-identical to `forward_prenorm` of the ordinary block."""
+    import ctypes as C
+    shape, dt = synth.SHAPES["mini"], torch.bfloat16
+    wts = synth.make_weights(shape, dt)
+    ref = _module(shape, dt, wts, max_tokens=256)
+    ep = _module(shape, dt, wts, max_tokens=256, peer_workspace=True)
+    ep.ipc_handle()
+    lib = _lib.load()
+    raw, base = _peer_buffer(lib.glm4moe_ep_comm_bytes(256, shape.H, _lib.DTYPE_CODE[dt], 1))
+
+    class Comm:
+        bases = (C.c_void_p * 1)(base)
+        max_tokens = 256
+
+    bases = (C.c_void_p * 1)(ep.workspace_base())
+    nw = (1.0 + 0.05 * torch.randn(shape.H)).to(dt).cuda()
+    try:
+        for T in (1, 9, 32, 200):
+            x = synth.make_tokens(shape, T, dt, 70 + T).cuda()
+            res = synth.make_tokens(shape, T, dt, 170 + T).cuda()
+            with torch.inference_mode():
+                want, want_r = ref.forward_prenorm(x, res, nw, 1e-5)
+                for rep in range(3):
+                    got, got_r = ep.forward_ep_p2p_prenorm(x, res, nw, 1e-5, bases, Comm)
+                    assert torch.equal(got, want) and torch.equal(got_r, want_r), f"T={T} rep={rep}"
+    finally:
+        torch.cuda.synchronize()
+        lib.glm4moe_p2p_free(raw)
 
 
 # ------------------------------------------------------------------------------------------
