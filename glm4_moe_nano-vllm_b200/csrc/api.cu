@@ -64,6 +64,7 @@ int fp8_mx_mode() {
   return g_fp8_mx;
 }
 int g_merge_front = 1;   // T <= 2: router front-end inside the persistent decode kernel (one launch per layer), KNOB_MERGE_FRONT
+int g_spec_prefetch = -1; // decode: local experts whose weights are L2-prefetched before the routing is known; -1 auto, KNOB_SPEC_PREFETCH
 int g_ep_ar_mode = -1;    // fused all-reduce + norm (ep_allreduce.cu): -1 by size, 0 one-shot, 1 two-shot, KNOB_EP_AR_MODE
 int g_ep_fast = 1;       // decode fast path of the peer-memory combine (one rendezvous per step), KNOB_EP_FAST
 
@@ -196,6 +197,7 @@ extern "C" int glm4moe_debug_set(int knob, int value) {
       g_router_rows = value;
       return GLM4MOE_OK;
     case GLM4MOE_KNOB_EP_FAST: g_ep_fast = value ? 1 : 0; return GLM4MOE_OK;
+    case GLM4MOE_KNOB_SPEC_PREFETCH: g_spec_prefetch = value < 0 ? -1 : value; return GLM4MOE_OK;
     case GLM4MOE_KNOB_EP_AR_MODE: g_ep_ar_mode = value < 0 ? -1 : value ? 1 : 0; return GLM4MOE_OK;
     case GLM4MOE_KNOB_MERGE_FRONT: g_merge_front = value ? 1 : 0; return GLM4MOE_OK;
     case GLM4MOE_KNOB_FP8_MX: g_fp8_mx = value < 0 || value > 3 ? 1 : value; return GLM4MOE_OK;
@@ -613,6 +615,21 @@ static int forward_impl(glm4moe_layer_t* l, const void* x, void* out, int T, voi
       f.pf0_bytes = static_cast<size_t>(2) * I * H * es;
       f.pf1 = static_cast<const unsigned char*>(l->w_down) + n_local * H * I * es;
       f.pf1_bytes = static_cast<size_t>(H) * I * es;
+      // speculative prefetch of the first local experts (decode_fused.cu): on when an expert is hit with
+      // probability >= 0.8 (1 - (1 - k/E)^T), as many experts as fit ~70 MB of L2 next to the shared expert
+      int n_spec = g_spec_prefetch;
+      if (n_spec < 0) {
+        float miss = 1.f;
+        for (int t = 0; t < T; ++t) miss *= 1.f - static_cast<float>(k) / static_cast<float>(E);
+        const size_t per_expert = static_cast<size_t>(3) * I * H * es;
+        n_spec = miss <= 0.2f ? static_cast<int>((70u << 20) / per_expert) : 0;
+      }
+      if (n_spec > static_cast<int>(n_local)) n_spec = static_cast<int>(n_local);
+      if (merged) n_spec = 0;
+      f.pf2 = l->w_gate_up;
+      f.pf2_bytes = static_cast<size_t>(n_spec) * 2 * I * H * es;
+      f.pf3 = l->w_down;
+      f.pf3_bytes = static_cast<size_t>(n_spec) * H * I * es;
     }
     if (fp8) {
       f.fp8 = 1;

@@ -94,6 +94,8 @@ __global__ void __launch_bounds__(FusedCfg<BN, FP8>::kThreads, 1) decode_fused_k
     int32_t* __restrict__ fdone,                  // [H/128] down items finished per feature tile
     const unsigned char* __restrict__ pf0, size_t pf0_bytes,    // shared expert's gate_up / down weights:
     const unsigned char* __restrict__ pf1, size_t pf1_bytes,    // pulled into L2 while the router runs
+    const unsigned char* __restrict__ pf2, size_t pf2_bytes,    // speculative: the first local experts' weights
+    const unsigned char* __restrict__ pf3, size_t pf3_bytes,    // (probably hit at T >= 24), same L2 prefetch
     const Fp8Args q,                              // e4m3 tier: scales and the quantised activation buffer
     const EpFastSignal ep,                        // expert-parallel fast path: parity row buffers + ready flags
     const RouteMerged rt) {                       // T <= 2: router front-end inside this kernel
@@ -286,7 +288,7 @@ __global__ void __launch_bounds__(FusedCfg<BN, FP8>::kThreads, 1) decode_fused_k
       // ---- before the dependency wait: the shared expert is always on.  Every CTA pulls its slice of
       // the shared expert's 3*H*I weights into L2 (HBM would otherwise idle while the router runs;
       // they fit the 126 MB L2 many times over), then phase S streams gate_up from there. ----
-      if (has_shared) {
+      {
         constexpr size_t kChunk = 32768;
         auto prefetch_slice = [&](const unsigned char* base, size_t bytes) {
           const size_t n_chunks = (bytes + kChunk - 1) / kChunk;
@@ -296,8 +298,16 @@ __global__ void __launch_bounds__(FusedCfg<BN, FP8>::kThreads, 1) decode_fused_k
             asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(base + off), "r"(sz) : "memory");
           }
         };
-        prefetch_slice(pf0, pf0_bytes);
-        prefetch_slice(pf1, pf1_bytes);
+        if (has_shared) {
+          prefetch_slice(pf0, pf0_bytes);
+          prefetch_slice(pf1, pf1_bytes);
+        }
+        // Speculation: with >= ~24 tokens each expert is hit with probability >= 0.8 and the work list visits
+        // the local experts in ascending order, so the first ones are the first routed items after the wait.
+        // Their weights are pulled towards L2 in the router's shadow too (HBM is idle there); a miss costs
+        // bandwidth nobody was using.
+        if (pf2_bytes) prefetch_slice(pf2, pf2_bytes);
+        if (pf3_bytes) prefetch_slice(pf3, pf3_bytes);
       }
       // merged front-end: this kernel is the first of the layer, so x itself is the predecessor's output
       if (rt.enabled) {
@@ -863,6 +873,7 @@ static int launch_fused_one(const DecodeFusedLaunch& a, cudaStream_t st) {
       a.row_weight, static_cast<T*>(a.act), static_cast<T*>(a.y), a.H, a.I, a.tokens, a.n_routed_rows,
       a.shared_expert, a.sh_lo, a.sh_hi, a.sched, a.ready, a.slot_row, static_cast<T*>(a.out), a.k, a.fdone,
       static_cast<const unsigned char*>(a.pf0), a.pf0_bytes, static_cast<const unsigned char*>(a.pf1), a.pf1_bytes,
+      static_cast<const unsigned char*>(a.pf2), a.pf2_bytes, static_cast<const unsigned char*>(a.pf3), a.pf3_bytes,
       a.q, a.ep, a.rt));
   return GLM4MOE_OK;
 }

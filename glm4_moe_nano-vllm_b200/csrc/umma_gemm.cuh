@@ -122,6 +122,10 @@ struct DecodeFusedLaunch {
   size_t pf0_bytes;
   const void* pf1;           // shared expert's down weights
   size_t pf1_bytes;
+  const void* pf2;           // speculative: gate_up weights of the first local experts (see api.cu, spec_prefetch_experts)
+  size_t pf2_bytes;
+  const void* pf3;           // speculative: their down weights
+  size_t pf3_bytes;
   int fp8;                   // 1: e4m3 weights / activations (tm_* are byte maps), q is set
   Fp8Args q;
   // expert-parallel decode fast path (out == nullptr): rows go to the epoch-parity buffer and the kernel
