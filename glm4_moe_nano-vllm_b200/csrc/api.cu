@@ -1213,7 +1213,7 @@ extern "C" int glm4moe_ep_allreduce_add_rmsnorm(void* const* peer_comm, int rank
   // Same decision on every rank (T, H, world only).  One-shot while the pushed copies stay small: (R-1) x the
   // partial leaves every rank, against 3(R-1)/R x in the two-shot form, which pays a second flag round.
   const size_t bytes = static_cast<size_t>(T) * H * dtype_size(dtype);
-  const bool fits = bytes <= a.L.os_slot;
+  const bool fits = bytes <= a.L.os_slot && T <= kEpArOneShotRows;
   bool two = !fits || bytes * static_cast<size_t>(world - 1) > (2u << 20);
   if (g_ep_ar_mode == 0 && fits) two = false;
   if (g_ep_ar_mode == 1) two = true;

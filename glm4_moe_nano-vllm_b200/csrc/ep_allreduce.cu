@@ -16,22 +16,22 @@
 //   to an all-reduce whose sum is taken in fp32 with one rounding.  weight == nullptr: out = y (a plain all-reduce).
 //
 // Two forms, chosen by size (same choice on every rank: it depends on T, H only):
-//   one-shot  (T*H*es <= 1 MiB): every rank PUSHES its partial rows into an inbox on every peer (posted NVLink
-//             writes, no read round trip), one flag round, then every rank reduces all T rows from its local
-//             inboxes.  One cross-rank rendezvous per call; (R-1)*T*H*es bytes out per rank.
-//   two-shot  (prefill): reduce-scatter -> norm on the token shard -> all-gather, in one launch.  Rank r pushes,
-//             for every peer s, its partial rows of s's token slice into s's inbox; after the first flag round
-//             rank s reduces ITS ceil(T/R) tokens, normalises them, and pushes the finished out / residual_out
-//             rows to every peer; after the second flag round every rank copies the other slices from its local
-//             inbox.  3*(R-1)/R*T*H*es bytes out per rank instead of (R-1)*T*H*es, the norm is computed once per
-//             token instead of R times.
+//   one-shot  (T*H*es <= 1 MiB, T <= 1024): every rank PUSHES its partial rows into an inbox on every peer (posted
+//             NVLink writes, no read round trip) and releases a flag PER ROW; the block that owns row t waits for
+//             the peers' flags of row t only, then reduces and normalises it.  (R-1)*T*H*es bytes out per rank.
+//   two-shot  (prefill): reduce-scatter -> token shard -> all-gather, in one launch.  Rank r pushes, for every
+//             peer s, its partial rows of s's token slice into s's inbox; after the first flag round rank s sums
+//             ITS ceil(T/R) tokens and pushes y to every peer; after the second flag round every rank holds y of
+//             every token and applies the residual add + norm locally (HBM traffic, which is plentiful, instead
+//             of a second NVLink plane).  2*(R-1)/R*T*H*es bytes out per rank, the traffic of a ring all-reduce.
 //
 // Ordering (epoch e = calls completed + 1, kept in the comm buffer: graph-replay safe).  Inboxes are selected by the
 // parity of e and there is NO "done" round: a rank overwrites the parity-p inboxes of its peers again in call
 // e + 2, after it has seen every peer's flag of call e + 1 — which a peer sends only after its own call e has
 // retired (stream order), i.e. after its last read of the parity-p inbox.  Flags carry epoch*4 + mode; every
 // spin is bounded and traps with an error code (ranks that disagree on the form or on call counts fail loudly).
-// All blocks of a launch wait for the peers inside the kernel: the grid is capped so that it is co-resident.
+// The blocks of a two-shot launch wait for the peers' grid-wide flags inside the kernel: its grid is capped so
+// that it is co-resident.
 #include "common.cuh"
 #include "ep_allreduce.cuh"
 
@@ -83,21 +83,21 @@ __device__ __forceinline__ bool block_ticket(int32_t* counter, int* s_flag) {
   return *s_flag != 0;
 }
 
-// One token row: fp32 sum of the R partials in rank order (own partial read in place, the others from the local
-// inbox), one rounding, residual add, RMSNorm.  Thread mapping and reduction order of add_rmsnorm_kernel.
-// PUSH: finished rows also go to every peer's all-gather inbox (two-shot).
+// ---- one token row, in two steps -------------------------------------------------------------------------
+// Thread mapping of add_rmsnorm_kernel (rmsnorm.cu): thread `tid` owns the 16-byte vectors tid + i * 256.
+template <typename T>
+struct RowRegs {
+  float v[kArMaxVec][Dt<T>::kVec];
+};
+
+// (1) y = round(sum_r partial_r): fp32, rank order; own partial read in place, the others from the local inbox.
+//     PUSH: y also goes to every peer's all-gather inbox (two-shot).
 template <typename T, bool PUSH>
-__device__ __forceinline__ void reduce_norm_row(const EpArArgs& a, int t, const unsigned char* inbox, size_t slot_bytes,
-                                                int inbox_row, int p, float* s_part) {
+__device__ __forceinline__ void sum_row(const EpArArgs& a, int t, const unsigned char* inbox, size_t slot_bytes,
+                                        int inbox_row, int p, RowRegs<T>& R) {
   constexpr int V = Dt<T>::kVec;
   const int nvec = a.H / V;
   const size_t row_off = static_cast<size_t>(t) * a.H;
-  const T* residual = static_cast<const T*>(a.residual);
-  const T* weight = static_cast<const T*>(a.weight);
-  T* out = static_cast<T*>(a.out);
-  T* residual_out = static_cast<T*>(a.residual_out);
-  float v[kArMaxVec][V];
-  float ss = 0.f;
 #pragma unroll
   for (int i = 0; i < kArMaxVec; ++i) {
     const int c = threadIdx.x + i * kEpArThreads;
@@ -123,42 +123,77 @@ __device__ __forceinline__ void reduce_norm_row(const EpArArgs& a, int t, const 
           for (int q = 0; q < V; ++q) acc[q] += f[q];
         }
       }
+      __align__(16) T o[V];
 #pragma unroll
-      for (int q = 0; q < V; ++q) v[i][q] = Dt<T>::round(acc[q]);      // the all-reduce result in the model dtype
-      if (weight == nullptr) {
+      for (int q = 0; q < V; ++q) {
+        o[q] = Dt<T>::from_f(acc[q]);           // the all-reduce result in the model dtype
+        R.v[i][q] = Dt<T>::to_f(o[q]);
+      }
+      if (PUSH) {
+        const uint4 ov = *reinterpret_cast<uint4*>(o);
+        for (int r = 0; r < a.world; ++r)
+          if (r != a.rank) reinterpret_cast<uint4*>(a.comm[r] + a.L.ag[p] + row_off * sizeof(T))[c] = ov;
+      }
+    }
+  }
+}
+
+// (1') y of a row another rank reduced: from the local all-gather inbox
+template <typename T>
+__device__ __forceinline__ void load_row(const EpArArgs& a, int t, const unsigned char* ag, RowRegs<T>& R) {
+  constexpr int V = Dt<T>::kVec;
+  const int nvec = a.H / V;
+#pragma unroll
+  for (int i = 0; i < kArMaxVec; ++i) {
+    const int c = threadIdx.x + i * kEpArThreads;
+    if (c < nvec)
+      unpack16<T>(ld_cg16(reinterpret_cast<const uint4*>(ag + static_cast<size_t>(t) * a.H * sizeof(T)) + c), R.v[i]);
+  }
+}
+
+// (2) residual add + RMSNorm of y, the arithmetic and summation order of add_rmsnorm_kernel; weight == nullptr:
+//     out = y.  Contains block barriers: call it from uniform control flow.
+template <typename T>
+__device__ __forceinline__ void finish_row(const EpArArgs& a, int t, RowRegs<T>& R, float* s_part) {
+  constexpr int V = Dt<T>::kVec;
+  const int nvec = a.H / V;
+  const size_t row_off = static_cast<size_t>(t) * a.H;
+  const T* residual = static_cast<const T*>(a.residual);
+  const T* weight = static_cast<const T*>(a.weight);
+  T* out = static_cast<T*>(a.out);
+  T* residual_out = static_cast<T*>(a.residual_out);
+  if (weight == nullptr) {
+#pragma unroll
+    for (int i = 0; i < kArMaxVec; ++i) {
+      const int c = threadIdx.x + i * kEpArThreads;
+      if (c < nvec) {
         __align__(16) T o[V];
 #pragma unroll
-        for (int q = 0; q < V; ++q) o[q] = Dt<T>::from_f(v[i][q]);
-        const uint4 ov = *reinterpret_cast<uint4*>(o);
-        reinterpret_cast<uint4*>(out + row_off)[c] = ov;
-        if (PUSH) {
-          for (int r = 0; r < a.world; ++r)
-            if (r != a.rank)
-              reinterpret_cast<uint4*>(a.comm[r] + a.L.ag[p] + row_off * sizeof(T))[c] = ov;
-        }
-        continue;
+        for (int q = 0; q < V; ++q) o[q] = Dt<T>::from_f(R.v[i][q]);
+        reinterpret_cast<uint4*>(out + row_off)[c] = *reinterpret_cast<uint4*>(o);
       }
+    }
+    return;
+  }
+  float ss = 0.f;
+#pragma unroll
+  for (int i = 0; i < kArMaxVec; ++i) {
+    const int c = threadIdx.x + i * kEpArThreads;
+    if (c < nvec) {
       if (residual != nullptr) {
         float rr[V];
         unpack16<T>(ld_cached16(reinterpret_cast<const uint4*>(residual + row_off) + c), rr);
 #pragma unroll
-        for (int q = 0; q < V; ++q) v[i][q] += rr[q];
+        for (int q = 0; q < V; ++q) R.v[i][q] += rr[q];
         __align__(16) T o[V];
 #pragma unroll
-        for (int q = 0; q < V; ++q) o[q] = Dt<T>::from_f(v[i][q]);
-        const uint4 ov = *reinterpret_cast<uint4*>(o);
-        reinterpret_cast<uint4*>(residual_out + row_off)[c] = ov;
-        if (PUSH) {
-          for (int r = 0; r < a.world; ++r)
-            if (r != a.rank)
-              reinterpret_cast<uint4*>(a.comm[r] + a.L.ag[p] + a.L.ag_plane + row_off * sizeof(T))[c] = ov;
-        }
+        for (int q = 0; q < V; ++q) o[q] = Dt<T>::from_f(R.v[i][q]);
+        reinterpret_cast<uint4*>(residual_out + row_off)[c] = *reinterpret_cast<uint4*>(o);
       }
 #pragma unroll
-      for (int q = 0; q < V; ++q) ss = fmaf(v[i][q], v[i][q], ss);
+      for (int q = 0; q < V; ++q) ss = fmaf(R.v[i][q], R.v[i][q], ss);
     }
   }
-  if (weight == nullptr) return;
   ss = warp_sum(ss);
   __syncthreads();                    // s_part of the previous row has been read by everyone
   if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = ss;
@@ -175,19 +210,35 @@ __device__ __forceinline__ void reduce_norm_row(const EpArArgs& a, int t, const 
       unpack16<T>(ld_cached16(reinterpret_cast<const uint4*>(weight) + c), g);
       __align__(16) T o[V];
 #pragma unroll
-      for (int q = 0; q < V; ++q) o[q] = Dt<T>::from_f(Dt<T>::round(v[i][q] * rs) * g[q]);
-      const uint4 ov = *reinterpret_cast<uint4*>(o);
-      reinterpret_cast<uint4*>(out + row_off)[c] = ov;
-      if (PUSH) {
-        for (int r = 0; r < a.world; ++r)
-          if (r != a.rank) reinterpret_cast<uint4*>(a.comm[r] + a.L.ag[p] + row_off * sizeof(T))[c] = ov;
-      }
+      for (int q = 0; q < V; ++q) o[q] = Dt<T>::from_f(Dt<T>::round(R.v[i][q] * rs) * g[q]);
+      reinterpret_cast<uint4*>(out + row_off)[c] = *reinterpret_cast<uint4*>(o);
+    }
+  }
+}
+
+// retire a launch: the last block bumps the epoch and re-arms the tickets (no system-scope fence: nothing
+// cross-GPU depends on it)
+__device__ __forceinline__ void retire(int32_t* ctl, int e, int* s_flag) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    if (atomicAdd(ctl + 4, 1) == static_cast<int>(gridDim.x) - 1) {
+      ctl[1] = 0;
+      ctl[3] = 0;
+      ctl[4] = 0;
+      *reinterpret_cast<volatile int32_t*>(ctl) = e;
+      __threadfence();
     }
   }
 }
 
 }  // namespace
 
+// One-shot: ROW-granular hand-off.  The block that owns row t pushes its partial row to every peer and releases
+// that row's flag there; it then waits only for the peers' flags of the same row.  No grid-wide ticket, no block
+// depends on another block of its own grid (so the grid needs no co-residency), and the latency of a decode-size
+// call is one push + one system-scope fence + one flag.  A flag word holds epoch*4 + mode of the last call that
+// wrote the row; data live in the inbox of the call's parity, so a peer that is one call ahead passes the wait
+// without having touched this call's rows (see the header comment for why it cannot be two ahead).
 template <typename T>
 __global__ void __launch_bounds__(kEpArThreads, 2) ep_ar_oneshot_kernel(const EpArArgs a) {
   constexpr int V = Dt<T>::kVec;
@@ -199,7 +250,6 @@ __global__ void __launch_bounds__(kEpArThreads, 2) ep_ar_oneshot_kernel(const Ep
   const int e = *reinterpret_cast<volatile int32_t*>(ctl) + 1;
   const int p = e & 1;
   const int nvec = a.H / V;
-  // ---- push: my partial rows into inbox[p][me] of every peer ----
   if (a.world > 1) {
     for (int t = blockIdx.x; t < a.tokens; t += gridDim.x) {
       const size_t row_off = static_cast<size_t>(t) * a.H;
@@ -211,27 +261,29 @@ __global__ void __launch_bounds__(kEpArThreads, 2) ep_ar_oneshot_kernel(const Ep
             reinterpret_cast<uint4*>(a.comm[r] + a.L.os[p] + static_cast<size_t>(a.rank) * a.L.os_slot +
                                      row_off * sizeof(T))[c] = val;
       }
+      __threadfence_system();
+      __syncthreads();
+      if (threadIdx.x < a.world && threadIdx.x != a.rank) {
+        int32_t* peer_flags = reinterpret_cast<int32_t*>(a.comm[threadIdx.x] + a.L.rowflag);
+        st_release_sys(peer_flags + a.rank * kEpArOneShotRows + t, e * 4 + kEpArModeOne);
+      }
     }
-    if (block_ticket(ctl + 1, &s_flag) && threadIdx.x < a.world) {
-      int32_t* peer_ctl = reinterpret_cast<int32_t*>(a.comm[threadIdx.x] + a.L.ctl);
-      st_release_sys(peer_ctl + 16 + a.rank, e * 4 + kEpArModeOne);
-    }
-    if (threadIdx.x < a.world) wait_flag(ctl + 16 + threadIdx.x, e, kEpArModeOne, ctl);
-    __syncthreads();
   }
-  // ---- reduce + residual add + norm: every rank, every row (identical bits everywhere) ----
   const unsigned char* inbox = a.comm[a.rank] + a.L.os[p];
-  for (int t = blockIdx.x; t < a.tokens; t += gridDim.x)
-    reduce_norm_row<T, false>(a, t, inbox, a.L.os_slot, t, p, s_part);
-  // ---- retire: last block bumps the epoch and re-arms the tickets ----
-  if (block_ticket(ctl + 3, &s_flag) && threadIdx.x == 0) {
-    ctl[1] = 0;
-    ctl[3] = 0;
-    *reinterpret_cast<volatile int32_t*>(ctl) = e;
-    __threadfence();
+  const int32_t* my_flags = reinterpret_cast<const int32_t*>(a.comm[a.rank] + a.L.rowflag);
+  for (int t = blockIdx.x; t < a.tokens; t += gridDim.x) {
+    if (threadIdx.x < a.world && threadIdx.x != a.rank)
+      wait_flag(my_flags + threadIdx.x * kEpArOneShotRows + t, e, kEpArModeOne, ctl);
+    __syncthreads();
+    RowRegs<T> R;
+    sum_row<T, false>(a, t, inbox, a.L.os_slot, t, p, R);
+    finish_row<T>(a, t, R, s_part);
   }
+  retire(ctl, e, &s_flag);
 }
 
+// Two-shot: reduce-scatter -> my token shard -> all-gather of y, then the residual add + norm of every row
+// locally (one NVLink plane instead of two: NVLink, not HBM, is the scarce resource at prefill sizes).
 template <typename T>
 __global__ void __launch_bounds__(kEpArThreads, 2) ep_ar_twoshot_kernel(const EpArArgs a) {
   constexpr int V = Dt<T>::kVec;
@@ -261,37 +313,28 @@ __global__ void __launch_bounds__(kEpArThreads, 2) ep_ar_twoshot_kernel(const Ep
   }
   if (threadIdx.x < a.world) wait_flag(ctl + 16 + threadIdx.x, e, kEpArModeTwo, ctl);
   __syncthreads();
-  // ---- my token slice: reduce, residual add, norm; finished rows to `out` and to every peer ----
+  // ---- my token slice: y to every peer's inbox; residual add + norm locally ----
   const unsigned char* inbox = a.comm[a.rank] + a.L.rs[p];
-  for (int t = lo + blockIdx.x; t < hi; t += gridDim.x)
-    reduce_norm_row<T, true>(a, t, inbox, a.L.rs_slot, t - lo, p, s_part);
+  for (int t = lo + blockIdx.x; t < hi; t += gridDim.x) {
+    RowRegs<T> R;
+    sum_row<T, true>(a, t, inbox, a.L.rs_slot, t - lo, p, R);
+    finish_row<T>(a, t, R, s_part);
+  }
   if (block_ticket(ctl + 3, &s_flag) && threadIdx.x < a.world) {
     int32_t* peer_ctl = reinterpret_cast<int32_t*>(a.comm[threadIdx.x] + a.L.ctl);
     st_release_sys(peer_ctl + 32 + a.rank, e * 4 + kEpArModeTwo);
   }
   if (threadIdx.x < a.world) wait_flag(ctl + 32 + threadIdx.x, e, kEpArModeTwo, ctl);
   __syncthreads();
-  // ---- all-gather, local side: the other ranks' slices from my inbox ----
+  // ---- the other ranks' slices: y from my inbox, same residual add + norm ----
   const unsigned char* ag = a.comm[a.rank] + a.L.ag[p];
-  const bool two_planes = a.weight != nullptr && a.residual != nullptr;
   for (int t = blockIdx.x; t < a.tokens; t += gridDim.x) {
     if (t >= lo && t < hi) continue;
-    const size_t row_off = static_cast<size_t>(t) * a.H;
-    for (int c = threadIdx.x; c < nvec; c += kEpArThreads) {
-      reinterpret_cast<uint4*>(static_cast<T*>(a.out) + row_off)[c] =
-          ld_cg16(reinterpret_cast<const uint4*>(ag + row_off * sizeof(T)) + c);
-      if (two_planes)
-        reinterpret_cast<uint4*>(static_cast<T*>(a.residual_out) + row_off)[c] =
-            ld_cg16(reinterpret_cast<const uint4*>(ag + a.L.ag_plane + row_off * sizeof(T)) + c);
-    }
+    RowRegs<T> R;
+    load_row<T>(a, t, ag, R);
+    finish_row<T>(a, t, R, s_part);
   }
-  if (block_ticket(ctl + 4, &s_flag) && threadIdx.x == 0) {
-    ctl[1] = 0;
-    ctl[3] = 0;
-    ctl[4] = 0;
-    *reinterpret_cast<volatile int32_t*>(ctl) = e;
-    __threadfence();
-  }
+  retire(ctl, e, &s_flag);
 }
 
 EpCommLayout ep_comm_layout(int max_tokens, int H, int dtype, int world) {
@@ -314,11 +357,12 @@ EpCommLayout ep_comm_layout(int max_tokens, int H, int dtype, int world) {
     L.rs[p] = off;
     off += L.rs_slot * world;
   }
-  L.ag_plane = full;
   for (int p = 0; p < 2; ++p) {
     L.ag[p] = off;
-    off += 2 * L.ag_plane;
+    off += full;
   }
+  L.rowflag = off;
+  off += up(static_cast<size_t>(world) * kEpArOneShotRows * 4);
   L.total = off;
   return L;
 }
@@ -331,8 +375,8 @@ int ep_allreduce_launch(const EpArArgs& a, int dtype, int two_shot, void* stream
   int dev = 0, sms = 0;
   GLM4MOE_CUDA_CHECK(cudaGetDevice(&dev));
   GLM4MOE_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  // every block waits for the peers inside the kernel: the whole grid must be co-resident (2 blocks / SM by
-  // __launch_bounds__)
+  // two-shot: every block waits for the peers' grid-wide flags inside the kernel, so the whole grid must be
+  // co-resident (2 blocks / SM by __launch_bounds__); the one-shot form has no such need but gains nothing from more
   const int cap = sms * 2;
   int grid = a.tokens < cap ? a.tokens : cap;
   if (grid < 1) grid = 1;
