@@ -64,7 +64,8 @@ int fp8_mx_mode() {
   return g_fp8_mx;
 }
 int g_merge_front = 1;   // T <= 2: router front-end inside the persistent decode kernel (one launch per layer), KNOB_MERGE_FRONT
-int g_spec_prefetch = -1; // decode: local experts whose weights are L2-prefetched before the routing is known; -1 auto, KNOB_SPEC_PREFETCH
+int g_spec_prefetch = 0;  // decode: local experts whose weights are L2-prefetched before the routing is known (KNOB_SPEC_PREFETCH;
+                          // -1 = as many as fit 70 MB once P(hit) >= 0.8).  Measured neutral to -2 % (profiles/r2.md section 11): off
 int g_ep_ar_mode = -1;    // fused all-reduce + norm (ep_allreduce.cu): -1 by size, 0 one-shot, 1 two-shot, KNOB_EP_AR_MODE
 int g_ep_fast = 1;       // decode fast path of the peer-memory combine (one rendezvous per step), KNOB_EP_FAST
 
