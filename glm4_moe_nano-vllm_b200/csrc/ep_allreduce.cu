@@ -74,11 +74,17 @@ __device__ __forceinline__ uint4 ld_cg16(const void* p) {
   return r;
 }
 
-// every thread's stores are globally visible, then one ticket per block; true in the LAST block to arrive
+// One ticket per block; true in the LAST block to arrive.  Release pattern of ep_combine.cu (and of NCCL's
+// primitives): block barrier, then ONE thread fences at system scope before it publishes; the barrier puts every
+// thread's stores before that fence in causality order, so 2-8 threads fence per block instead of 256 (the
+// all-threads form cost ~4 us of a 19 us one-shot call at T = 32).  The caller's flag writers fence again after
+// the second barrier, which orders the other blocks' stores (observed through the ticket) before the flag.
 __device__ __forceinline__ bool block_ticket(int32_t* counter, int* s_flag) {
-  __threadfence_system();
   __syncthreads();
-  if (threadIdx.x == 0) *s_flag = atomicAdd(counter, 1) == static_cast<int>(gridDim.x) - 1;
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    *s_flag = atomicAdd(counter, 1) == static_cast<int>(gridDim.x) - 1;
+  }
   __syncthreads();
   return *s_flag != 0;
 }
@@ -261,10 +267,10 @@ __global__ void __launch_bounds__(kEpArThreads, 2) ep_ar_oneshot_kernel(const Ep
             reinterpret_cast<uint4*>(a.comm[r] + a.L.os[p] + static_cast<size_t>(a.rank) * a.L.os_slot +
                                      row_off * sizeof(T))[c] = val;
       }
-      __threadfence_system();
       __syncthreads();
       if (threadIdx.x < a.world && threadIdx.x != a.rank) {
         int32_t* peer_flags = reinterpret_cast<int32_t*>(a.comm[threadIdx.x] + a.L.rowflag);
+        __threadfence_system();      // the block's row (ordered before by the barrier) is visible before the flag
         st_release_sys(peer_flags + a.rank * kEpArOneShotRows + t, e * 4 + kEpArModeOne);
       }
     }
@@ -309,6 +315,7 @@ __global__ void __launch_bounds__(kEpArThreads, 2) ep_ar_twoshot_kernel(const Ep
   }
   if (block_ticket(ctl + 1, &s_flag) && threadIdx.x < a.world) {
     int32_t* peer_ctl = reinterpret_cast<int32_t*>(a.comm[threadIdx.x] + a.L.ctl);
+    __threadfence_system();
     st_release_sys(peer_ctl + 16 + a.rank, e * 4 + kEpArModeTwo);
   }
   if (threadIdx.x < a.world) wait_flag(ctl + 16 + threadIdx.x, e, kEpArModeTwo, ctl);
@@ -322,6 +329,7 @@ __global__ void __launch_bounds__(kEpArThreads, 2) ep_ar_twoshot_kernel(const Ep
   }
   if (block_ticket(ctl + 3, &s_flag) && threadIdx.x < a.world) {
     int32_t* peer_ctl = reinterpret_cast<int32_t*>(a.comm[threadIdx.x] + a.L.ctl);
+    __threadfence_system();
     st_release_sys(peer_ctl + 32 + a.rank, e * 4 + kEpArModeTwo);
   }
   if (threadIdx.x < a.world) wait_flag(ctl + 32 + threadIdx.x, e, kEpArModeTwo, ctl);
