@@ -303,15 +303,28 @@ __global__ void __launch_bounds__(kEpArThreads, 2) ep_ar_twoshot_kernel(const Ep
   const int nvec = a.H / V;
   const int lo = min(a.rank * a.per, a.tokens);
   const int hi = min(lo + a.per, a.tokens);
-  // ---- reduce-scatter, push side: my partial rows of slice s -> rank s ----
-  for (int t = blockIdx.x; t < a.tokens; t += gridDim.x) {
-    const int s = t / a.per;
-    if (s == a.rank) continue;
-    const size_t row_off = static_cast<size_t>(t) * a.H;
-    const uint4* src = reinterpret_cast<const uint4*>(static_cast<const T*>(a.partial) + row_off);
-    uint4* dst = reinterpret_cast<uint4*>(a.comm[s] + a.L.rs[p] + static_cast<size_t>(a.rank) * a.L.rs_slot +
-                                          static_cast<size_t>(t - s * a.per) * a.H * sizeof(T));
-    for (int c = threadIdx.x; c < nvec; c += kEpArThreads) dst[c] = ld_cg16(src + c);
+  // ---- reduce-scatter, push side: my partial rows of slice s -> rank s.  The rows of a slice are contiguous on
+  // both sides: R - 1 flat copies, four independent 16-byte loads in flight per thread (one load + one store per
+  // iteration left the NVLink pipe latency-bound: 312 GB/s per rank at 8 ranks, profiles/r2.md section 10) ----
+  {
+    const size_t stride = static_cast<size_t>(gridDim.x) * kEpArThreads;
+    const size_t tid = static_cast<size_t>(blockIdx.x) * kEpArThreads + threadIdx.x;
+    for (int ds = 1; ds < a.world; ++ds) {
+      const int s = (a.rank + ds) % a.world;            // start with the next rank: spread the first bytes over the links
+      const int s_lo = min(s * a.per, a.tokens), s_hi = min(s_lo + a.per, a.tokens);
+      const size_t n = static_cast<size_t>(s_hi - s_lo) * nvec;
+      const uint4* src = reinterpret_cast<const uint4*>(static_cast<const T*>(a.partial) + static_cast<size_t>(s_lo) * a.H);
+      uint4* dst = reinterpret_cast<uint4*>(a.comm[s] + a.L.rs[p] + static_cast<size_t>(a.rank) * a.L.rs_slot);
+      for (size_t i = tid; i < n; i += 4 * stride) {
+        uint4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          if (i + u * stride < n) v[u] = ld_cg16(src + i + u * stride);
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          if (i + u * stride < n) dst[i + u * stride] = v[u];
+      }
+    }
   }
   if (block_ticket(ctl + 1, &s_flag) && threadIdx.x < a.world) {
     int32_t* peer_ctl = reinterpret_cast<int32_t*>(a.comm[threadIdx.x] + a.L.ctl);
