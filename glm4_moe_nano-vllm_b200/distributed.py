@@ -275,7 +275,9 @@ class ExpertParallelMoE(nn.Module):
             if self._peer_bases is None:
                 self.setup_p2p()
             return self.local.forward_ep_p2p_prenorm(partial, residual, norm_weight, eps, self._peer_bases, comm)
-        from .layernorm import rmsnorm
+        rmsnorm = getattr(self, "norm_fn", None)        # tests on CPU inject the oracle's norm
+        if rmsnorm is None:
+            from .layernorm import rmsnorm
         y = partial.clone()
         dist.all_reduce(y, group=self.group)
         normed = rmsnorm(y, norm_weight, eps, residual)

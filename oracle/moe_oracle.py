@@ -194,3 +194,22 @@ def rmsnorm(x: torch.Tensor, weight: torch.Tensor, eps: float, residual: torch.T
     var = x32.pow(2).mean(dim=-1, keepdim=True)             # :22 / :37
     y = (x32 * torch.rsqrt(var + eps)).to(orig) * weight    # :23-24 / :38-39
     return y if residual is None else (y, res_out)
+
+
+# --------------------------------------------------------------------------------------
+# the tensor-parallel boundary in front of the block
+# --------------------------------------------------------------------------------------
+def allreduce_add_rmsnorm(partials, weight, eps: float, residual: torch.Tensor | None = None):
+    """What decode_layer.py:96-98 computes from the per-rank o_proj outputs: `dist.all_reduce(y)` of
+    `RowParallelLinear.forward` (layers/linear.py:153-154: the sum lands in the model dtype), then
+    `post_attention_layernorm(y, residual)` (layers/layernorm.py:29-40).  The sum order of an all-reduce is the
+    library's business; pinned here: fp32, ascending rank, one rounding (for two ranks that IS what NCCL computes:
+    a + b is commutative and is rounded once).  `weight=None`: the all-reduce alone."""
+    acc = torch.zeros_like(partials[0], dtype=torch.float32)
+    for p in partials:
+        acc = acc + p.float()
+    y = acc.to(partials[0].dtype)
+    if weight is None:
+        return y
+    return rmsnorm(y, weight, eps, residual)
+

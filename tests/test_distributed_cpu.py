@@ -87,6 +87,52 @@ def test_expert_parallel_layouts_match_single_rank(layout, T):
         assert err < 1e-5, (layout, rank, err)
 
 
+def _worker_prenorm(rank, world, port, layout, T, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        torch.set_num_threads(2)
+        wts = synth.make_weights(SHAPE, torch.float32)
+        g = torch.Generator().manual_seed(17)
+        parts = [torch.randn(T, SHAPE.H, generator=g) for _ in range(world)]     # per-rank o_proj partial sums
+        res = torch.randn(T, SHAPE.H, generator=g)
+        nw = 1.0 + 0.1 * torch.randn(SHAPE.H, generator=g)
+        ep = ExpertParallelMoE(OracleLocal(wts, SHAPE, rank, world), SHAPE.E, layout=layout)
+        ep.norm_fn = O.rmsnorm
+        out, res_out = ep.forward_prenorm(parts[rank], res, nw, 1e-5)
+        want_n, want_r = O.allreduce_add_rmsnorm(parts, nw, 1e-5, res)
+        want = O.moe_forward(want_n, wts, SHAPE.k, SHAPE.routed_scaling_factor, tie_rule="lowest_index")["out"]
+        out0, r0 = ep.forward_prenorm(parts[rank], None, nw, 1e-5)
+        want0 = O.moe_forward(O.allreduce_add_rmsnorm(parts, nw, 1e-5), wts, SHAPE.k, SHAPE.routed_scaling_factor,
+                              tie_rule="lowest_index")["out"]
+        q.put((rank, float((out - want).abs().max()), float((res_out - want_r).abs().max()),
+               float((out0 - want0).abs().max()), r0 is None, tuple(out.shape)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("layout,T", [("allreduce", 21), ("alltoall", 5)])
+def test_forward_prenorm_over_the_process_group(layout, T):
+    """`ExpertParallelMoE.forward_prenorm` without a peer-memory communicator: all-reduce of the o_proj partial
+    sums, residual add + RMSNorm, the expert-parallel block (decode_layer.py:96-99) against the oracle's
+    restatement of the same steps (`oracle.allreduce_add_rmsnorm` + `moe_forward`), two gloo ranks."""
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker_prenorm, args=(r, world, port, layout, T, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, err, err_r, err0, r0_none, shape in res:
+        assert shape == (T, SHAPE.H) and r0_none
+        assert err_r < 1e-6 and err < 1e-5 and err0 < 1e-5, (layout, rank, err, err_r, err0)
+
+
 def test_partition_helpers():
     assert expert_range(128, 3, 8) == (48, 64)
     with pytest.raises(ValueError):

@@ -80,6 +80,7 @@ def _worker_front(rank, world, port, q):
     from glm4_moe_b200 import synth, _lib
     from glm4_moe_b200 import layernorm as LN
     from glm4_moe_b200.distributed import ExpertParallelMoE, PeerComm
+    from oracle import moe_oracle as O
     from test_gpu_parity import _module
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
@@ -109,6 +110,12 @@ def _worker_front(rank, world, port, q):
             mine = parts[rank].cuda()
             want_n, want_r = LN.rmsnorm(y, nw, eps, res)
             want_p = LN.rmsnorm(y, nw, eps)
+            # the oracle's restatement of linear.py:153-154 + layernorm.py:29-40 on the CPU: the all-reduced sum and
+            # the residual stream bit for bit, the normalised tokens within the two nested roundings
+            o_n, o_r = O.allreduce_add_rmsnorm(parts, nw.cpu(), eps, res.cpu())
+            assert torch.equal(O.allreduce_add_rmsnorm(parts, None, eps), y.cpu()) and torch.equal(o_r, want_r.cpu())
+            dn = (want_n.float().cpu() - o_n.float()).abs()
+            assert bool((dn <= 2.0 ** -6 * o_n.float().abs() + 1e-30).all()) and float((dn > 0).float().mean()) < 5e-3
             for mode in (-1, 0, 1, 1, 0, -1):
                 _lib.check(lib.glm4moe_debug_set(11, mode))
                 dist.barrier()

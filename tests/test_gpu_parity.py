@@ -1236,6 +1236,10 @@ def test_fused_allreduce_norm_world1(H, dt):
             res = torch.randn(T, H, generator=g).to(dt).cuda()
             want_n, want_r = LN.rmsnorm(x, nw, 1e-5, res)
             want_p = LN.rmsnorm(x, nw, 1e-5)
+            o_n, o_r = O.allreduce_add_rmsnorm([x.cpu()], nw.cpu(), 1e-5, res.cpu())      # the oracle, one rank
+            assert torch.equal(o_r, want_r.cpu())
+            dn = (want_n.float().cpu() - o_n.float()).abs()
+            assert bool((dn <= 4 * _ulp(dt) * o_n.float().abs() + 1e-30).all())
             for mode in (-1, 0, 1, 1, 0, -1):
                 _lib.check(lib.glm4moe_debug_set(11, mode))
                 out, r_out, plain, copy = (torch.empty_like(x) for _ in range(4))
