@@ -50,18 +50,21 @@ __device__ __forceinline__ int32_t ld_acquire_sys(const int32_t* p) {
   return v;
 }
 constexpr long long kSpinTimeoutCycles = 1ll << 35;
+// Wait until `flag` carries call e (or e + 1: a peer can be at most one call ahead, see the header).  Accepting only
+// that window keeps a word that was last written ~2^29 calls ago (a row index not used since) from looking "ahead"
+// once the 32-bit epoch arithmetic wraps.
 __device__ __forceinline__ void wait_flag(const int32_t* flag, int e, int mode, int32_t* ctl) {
   const int target = e * 4;
   const long long t0 = clock64();
-  int v;
-  while ((v = ld_acquire_sys(flag)) - target < 0) {
+  int d;
+  while ((d = ld_acquire_sys(flag) - target) < 0 || d >= 8) {
     if (clock64() - t0 > kSpinTimeoutCycles) {
       ctl[2] = kEpErrTimeout;
       __threadfence_system();
       __trap();
     }
   }
-  if ((v >> 2) == e && (v & 3) != mode) {
+  if (d < 4 && d != mode) {
     ctl[2] = kEpErrModeMismatch;
     __threadfence_system();
     __trap();
