@@ -56,6 +56,39 @@ def test_workspace_and_arg_errors_without_gpu():
     assert lib.glm4moe_tile_capacity(32, 8, 128, 16) == 128 + 16 + 2 + 1
 
 
+def test_front_end_entries_without_gpu():
+    """Host arithmetic and argument checks of the fused front end (no compute call without a GPU): the
+    communication buffer of the peer-memory all-reduce (csrc/ep_allreduce.cuh: 1 KB of flags, 2 x R one-shot
+    inboxes, 2 x R reduce-scatter inboxes, 2 all-gather inboxes, R x 1024 row flags), refusals, NULL checks."""
+    import ctypes as C
+    lib = _lib.load()
+    H, es = 4096, 2
+    for T, R in ((32, 2), (8192, 8), (100, 3)):
+        n = lib.glm4moe_ep_comm_bytes(T, H, _lib.BF16, R)
+        full = (T * H * es + 1023) // 1024 * 1024
+        slot = min(full, 1 << 20)
+        per = (-(-T // R) * H * es + 1023) // 1024 * 1024
+        assert n == 1024 + 2 * R * slot + 2 * R * per + 2 * full + (R * 1024 * 4 + 1023) // 1024 * 1024, (T, R, n)
+    assert lib.glm4moe_ep_comm_bytes(32, H, _lib.F32, 2) == 0          # 2-byte dtypes only
+    assert lib.glm4moe_ep_comm_bytes(32, H, _lib.BF16, 9) == 0         # one NVSwitch box
+    assert lib.glm4moe_ep_comm_bytes(32, 4090, _lib.BF16, 2) == 0      # 16-byte rows
+    assert lib.glm4moe_ep_comm_bytes(0, H, _lib.BF16, 2) == 0
+    bases = (C.c_void_p * 2)(None, None)
+    assert lib.glm4moe_ep_allreduce_add_rmsnorm(None, 0, 2, 32, None, None, None, 1e-5, 4, H, _lib.BF16, None, None,
+                                                None) == -1
+    assert lib.glm4moe_ep_allreduce_add_rmsnorm(bases, 2, 2, 32, 8, None, None, 1e-5, 4, H, _lib.BF16, 8, None,
+                                                None) == -1            # rank outside the world
+    assert lib.glm4moe_ep_allreduce_add_rmsnorm(bases, 0, 2, 32, 8, None, None, 1e-5, 4, H, _lib.F32, 8, None,
+                                                None) == -2            # fp32 activations: unsupported
+    assert lib.glm4moe_ep_allreduce_add_rmsnorm(bases, 0, 2, 32, 8, None, None, 1e-5, 4, H, _lib.BF16, 8, None,
+                                                None) == -1            # unmapped peer buffer
+    assert lib.glm4moe_layer_forward_prenorm(None, None, None, None, 1e-5, None, None, 1, None) == -1
+    assert lib.glm4moe_layer_forward_ep_p2p_prenorm(None, None, None, None, 1e-5, None, None, 1, None, None, 32, 0, 1,
+                                                    None) == -1
+    assert lib.glm4moe_debug_set(11, 1) == 0 and lib.glm4moe_debug_set(11, -1) == 0     # KNOB_EP_AR_MODE
+    assert lib.glm4moe_debug_set(12, 2) == 0 and lib.glm4moe_debug_set(12, 0) == 0      # KNOB_SPEC_PREFETCH
+
+
 def test_module_names_match_reference_and_alias_stacks():
     shape = synth.TINY
     moe = glm4_moe_b200.Glm4MoeMoE(_cfg(shape))
