@@ -133,6 +133,74 @@ def test_forward_prenorm_over_the_process_group(layout, T):
         assert err_r < 1e-6 and err < 1e-5 and err0 < 1e-5, (layout, rank, err, err_r, err0)
 
 
+def _worker_ref_boundary(rank, world, port, dt_name, q):
+    """The REAL reference layers on two gloo ranks: `RowParallelLinear.forward` (linear.py:151-155: F.linear on the
+    rank's weight shard + dist.all_reduce) followed by `RMSNorm.forward(y, residual)` (layernorm.py:29-40)."""
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        torch.set_num_threads(2)
+        from glm4_moe_b200 import engine_shim as S
+        S.install()                                    # puts the reference on sys.path, real group behind get_tp_group()
+        from nanovllm.layers.linear import RowParallelLinear
+        from nanovllm.layers.layernorm import RMSNorm
+        dt = getattr(torch, dt_name)
+        T, K, H = 7, 96, 64
+        g = torch.Generator().manual_seed(23)
+        W = (0.05 * torch.randn(H, K, generator=g)).to(dt)
+        x = torch.randn(T, K, generator=g).to(dt)
+        res = torch.randn(T, H, generator=g).to(dt)
+        nw = (1.0 + 0.1 * torch.randn(H, generator=g)).to(dt)
+        prev = torch.get_default_dtype()
+        torch.set_default_dtype(dt)
+        try:
+            lin = RowParallelLinear(K, H)
+            norm = RMSNorm(H, eps=1e-5)
+        finally:
+            torch.set_default_dtype(prev)
+        assert lin.tp_size == world and tuple(lin.weight.shape) == (H, K // world)
+        with torch.no_grad():
+            lin.weight_loader(lin.weight, W)           # the reference's own shard arithmetic (linear.py:142-147)
+            norm.weight.copy_(nw)
+            shard = K // world
+            y = lin(x[:, rank * shard:(rank + 1) * shard])
+            ref_n, ref_r = norm(y.clone(), res.clone())
+            # what every rank's o_proj GEMM alone produces (the partial sums the fused kernel is handed)
+            parts = [torch.nn.functional.linear(x[:, r * shard:(r + 1) * shard], W[:, r * shard:(r + 1) * shard])
+                     for r in range(world)]
+        o_y = O.allreduce_add_rmsnorm(parts, None, 1e-5)
+        o_n, o_r = O.allreduce_add_rmsnorm(parts, nw, 1e-5, res)
+        q.put((rank, bool(torch.equal(o_y, y)), bool(torch.equal(o_n, ref_n)),
+               bool(torch.equal(o_r, ref_r if dt != torch.float32 else y + res))))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("dt_name", ["bfloat16", "float32"])
+def test_oracle_tp_boundary_bit_exact_vs_live_reference_layers(dt_name):
+    """Pins `oracle.allreduce_add_rmsnorm` (the checker of `glm4moe_ep_allreduce_add_rmsnorm`) to the reference
+    itself: its `RowParallelLinear` + `RMSNorm` run live on two gloo ranks; all-reduced sum, normalised tokens and
+    residual stream bit for bit (fp32: the reference's aliasing quirk of layernorm.py:36-39, see
+    test_rmsnorm_oracle_matches_reference_outputs, is not reproduced)."""
+    from glm4_moe_b200 import engine_shim as S
+    if S.reference_root() is None:
+        pytest.skip("reference package not installed (oracle/make_ref.py)")
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker_ref_boundary, args=(r, world, port, dt_name, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=180) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, same_y, same_n, same_r in res:
+        assert same_y and same_n and same_r, (dt_name, rank, same_y, same_n, same_r)
+
+
 def test_partition_helpers():
     assert expert_range(128, 3, 8) == (48, 64)
     with pytest.raises(ValueError):
