@@ -330,27 +330,32 @@ def setup_fused_norm(model) -> int:
         w = layers[0].post_attention_layernorm.weight
         comm = PeerComm(_installed.get("max_tokens") or 4096, w.numel(), w.dtype, device=w.device)
         _installed["comm"] = comm
-    n = 0
-    for layer in layers:
-        norm, mlp = layer.post_attention_layernorm, layer.mlp
-        if world > 1:
-            # RowParallelLinear.forward reads `tp_size` only to decide on the all-reduce (linear.py:153): the
-            # weight shard was cut at construction, so the GEMM now returns this rank's partial sums
-            layer.self_attn.o_proj.tp_size = 1
-        if isinstance(mlp, ExpertParallelMoE):
-            mlp.comm = comm
-            fused = lambda h, r, m=mlp, nm=norm: m.forward_prenorm(h, r, nm.weight, nm.eps)
-        elif isinstance(mlp, ours.Glm4MoeMoE) and world == 1:
-            fused = lambda h, r, m=mlp, nm=norm: m.forward_prenorm(h, r, nm.weight, nm.eps)
-        elif world > 1:
-            def fused(h, r, m=mlp, nm=norm, c=comm):         # dense layer: fused all-reduce + add + norm, then the MLP
-                x, r2 = c.allreduce_add_rmsnorm(h, r, nm.weight, nm.eps)
-                return m(x), r2
-        else:
-            continue
-        layer.__dict__["_fused_post"] = fused
-        n += 1
-    return n
+    return sum(fuse_layer(layer, world, comm) for layer in layers)
+
+
+def fuse_layer(layer, world: int = 1, comm=None) -> bool:
+    """Give ONE `Glm4MoeDecoderLayer` the one-call form of decode_layer.py:96-99 (the patched layer forward of
+    `install(fused_norm=True)` routes through `_fused_post` when a layer has it).  Returns whether it was fused."""
+    from . import moe as ours
+    from .distributed import ExpertParallelMoE
+    norm, mlp = layer.post_attention_layernorm, layer.mlp
+    if world > 1:
+        # RowParallelLinear.forward reads `tp_size` only to decide on the all-reduce (linear.py:153): the
+        # weight shard was cut at construction, so the GEMM now returns this rank's partial sums
+        layer.self_attn.o_proj.tp_size = 1
+    if isinstance(mlp, ExpertParallelMoE):
+        mlp.comm = comm
+        fused = lambda h, r, m=mlp, nm=norm: m.forward_prenorm(h, r, nm.weight, nm.eps)
+    elif isinstance(mlp, ours.Glm4MoeMoE) and world == 1:
+        fused = lambda h, r, m=mlp, nm=norm: m.forward_prenorm(h, r, nm.weight, nm.eps)
+    elif world > 1:
+        def fused(h, r, m=mlp, nm=norm, c=comm):         # dense layer: fused all-reduce + add + norm, then the MLP
+            x, r2 = c.allreduce_add_rmsnorm(h, r, nm.weight, nm.eps)
+            return m(x), r2
+    else:
+        return False
+    layer.__dict__["_fused_post"] = fused
+    return True
 
 
 def init_dummy_weights(model, seed: int = 1234, std: float = 0.02, **_):

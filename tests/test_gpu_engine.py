@@ -115,6 +115,86 @@ def test_real_decoder_layer_forward_with_the_swapped_block(T):
             reset_context()
 
 
+@pytest.mark.parametrize("T", [1, 24, 300])
+def test_fused_layer_forward_against_the_real_decoder_layer_forward(T):
+    """`install(fused_norm=True)`: the patched layer forward (norms through `glm4moe_add_rmsnorm`,
+    `post_attention_layernorm` + block as `glm4moe_layer_forward_prenorm`) against the REAL
+    `Glm4MoeDecoderLayer.forward` (decode_layer.py:79-100, reference norms) hosting the same block on the same
+    weights: residual stream bit for bit, hidden states equal up to the one-ulp moves of the normalised tokens
+    (a boundary token may then pick another expert), eager and under CUDA-graph capture."""
+    dt = torch.bfloat16
+    plain = _layer("ours", dt)                       # reference forward + reference norms + our block
+    g = torch.Generator(device="cuda").manual_seed(9)
+    with torch.no_grad():
+        for name, p in plain.named_parameters():
+            if p.dim() == 1:
+                p.copy_((1.0 + 0.1 * torch.randn(p.shape, generator=g, device="cuda", dtype=torch.float32)).to(dt))
+            else:
+                p.copy_((torch.randn(p.shape, generator=g, device="cuda", dtype=torch.float32) * 0.02).to(dt))
+        plain.mlp.gate.e_score_correction_bias.copy_(torch.rand(32, generator=g, device="cuda") * 0.1)
+    from nanovllm.utils.context import set_context, reset_context
+    x = torch.randn((T, 512), generator=g, device="cuda", dtype=torch.float32).to(dt)
+    res = torch.randn((T, 512), generator=g, device="cuda", dtype=torch.float32).to(dt)
+    pos = torch.arange(T, device="cuda")
+    cu = torch.tensor([0, T], dtype=torch.int32, device="cuda")
+
+    def run(layer, hidden, residual):
+        set_context(True, cu, cu, T, T, None, None, None)
+        try:
+            with torch.inference_mode():
+                return layer(pos, hidden.clone(), None if residual is None else residual.clone())
+        finally:
+            reset_context()
+
+    want = [run(plain, x, r) for r in (None, res)]
+    S.install(sparse_block="ours", share_workspace=False, fused_norm=True)
+    try:
+        from nanovllm.models.glm4_moe import decode_layer as DL
+        from glm4_moe_b200 import layernorm as LN
+        prev = torch.get_default_dtype()
+        torch.set_default_dtype(dt)
+        try:
+            with torch.device("cuda"):
+                fused = DL.Glm4MoeDecoderLayer(_config(), "model.layers.1")
+        finally:
+            torch.set_default_dtype(prev)
+        assert isinstance(fused.post_attention_layernorm, LN.RMSNorm) and isinstance(fused.input_layernorm, LN.RMSNorm)
+        missing = fused.load_state_dict(plain.state_dict(), strict=True)
+        assert not missing.missing_keys and not missing.unexpected_keys
+        assert S.fuse_layer(fused) and "_fused_post" in fused.__dict__
+        for (h_ref, r_ref), residual in zip(want, (None, res)):
+            h, r = run(fused, x, residual)
+            torch.cuda.synchronize()
+            assert h.shape == (T, 512) and h.dtype == dt
+            assert torch.equal(r, r_ref)
+            d = (h.float() - h_ref.float()).abs()
+            rms = h_ref.float().pow(2).mean().sqrt()
+            row_ok = (d <= 2e-2 * h_ref.float().abs() + 2e-2 * rms).all(-1)
+            assert bool(torch.isfinite(h.float()).all())
+            if T > 1:       # a single token sitting on a routing boundary would decide the whole comparison
+                assert float(row_ok.float().mean()) >= 0.97, float(row_ok.float().mean())
+        if T <= 32:
+            set_context(True, cu, cu, T, T, None, None, None)
+            try:
+                with torch.inference_mode():
+                    eager_h, eager_r = fused(pos, x.clone(), res.clone())
+                    s_ = torch.cuda.Stream()
+                    s_.wait_stream(torch.cuda.current_stream())
+                    with torch.cuda.stream(s_):
+                        fused(pos, x.clone(), res.clone())
+                    torch.cuda.current_stream().wait_stream(s_)
+                    graph = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(graph):
+                        gh, gr = fused(pos, x.clone(), res.clone())
+                    graph.replay()
+                    torch.cuda.synchronize()
+                    assert torch.equal(gh, eager_h) and torch.equal(gr, eager_r)
+            finally:
+                reset_context()
+    finally:
+        S.install(sparse_block="ours", share_workspace=False)
+
+
 def _engine(*extra):
     cmd = [sys.executable, os.path.join(ROOT, "scripts", "engine_run.py"), "--preset", "small", "--layers", "4",
            "--seqs", "6", "--max-tokens", "10", "--max-num-seqs", "8", "--mem", "0.3", *extra]
