@@ -120,8 +120,8 @@ def test_fused_layer_forward_against_the_real_decoder_layer_forward(T):
     """`install(fused_norm=True)`: the patched layer forward (norms through `glm4moe_add_rmsnorm`,
     `post_attention_layernorm` + block as `glm4moe_layer_forward_prenorm`) against the REAL
     `Glm4MoeDecoderLayer.forward` (decode_layer.py:79-100, reference norms) hosting the same block on the same
-    weights: residual stream bit for bit, hidden states equal up to the one-ulp moves of the normalised tokens
-    (a boundary token may then pick another expert), eager and under CUDA-graph capture."""
+    weights: residual stream and hidden states equal up to the one-ulp moves of the normalised tokens (a boundary
+    token may then pick another expert), eager and under CUDA-graph capture."""
     dt = torch.bfloat16
     plain = _layer("ours", dt)                       # reference forward + reference norms + our block
     g = torch.Generator(device="cuda").manual_seed(9)
@@ -166,7 +166,12 @@ def test_fused_layer_forward_against_the_real_decoder_layer_forward(T):
             h, r = run(fused, x, residual)
             torch.cuda.synchronize()
             assert h.shape == (T, 512) and h.dtype == dt
-            assert torch.equal(r, r_ref)
+            # the input norm is this package's kernel here: its output may sit one ulp off the reference's torch
+            # ops (two nested roundings, tests/test_gpu_parity.py::test_rmsnorm_vs_reference_golden), attention
+            # carries that into the residual stream: equal to rounding, on nearly every element bit for bit
+            dr = (r.float() - r_ref.float()).abs()
+            assert bool((dr <= 2.0 ** -6 * r_ref.float().abs() + 2.0 ** -7).all()), float(dr.max())
+            assert float((dr > 0).float().mean()) < 2e-2, float((dr > 0).float().mean())
             d = (h.float() - h_ref.float()).abs()
             rms = h_ref.float().pow(2).mean().sqrt()
             row_ok = (d <= 2e-2 * h_ref.float().abs() + 2e-2 * rms).all(-1)
