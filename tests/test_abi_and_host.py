@@ -42,6 +42,32 @@ def test_no_torch_types_in_abi():
     assert "torch" not in hdr and "at::" not in hdr and "Tensor" not in hdr
 
 
+def test_header_is_plain_c99(tmp_path):
+    """The boundary is a C ABI: the header must compile as C99 on its own (no C++, no torch, no CUDA headers) and a C
+    host must link against the shared library with nothing but the header."""
+    import shutil
+    import subprocess
+    gcc = shutil.which("gcc")
+    if gcc is None:
+        pytest.skip("no gcc")
+    src = tmp_path / "host.c"
+    src.write_text('#include "glm4_moe_b200.h"\n#include <stdio.h>\n'
+                   'int main(void) {\n'
+                   '  glm4moe_config_t c = {4096, 128, 8, 1408, 1.0f, GLM4MOE_BF16, GLM4MOE_W_NATIVE, 256, 0, 128, 1, 0};\n'
+                   '  printf("%d %zu %zu\\n", glm4moe_abi_version(), glm4moe_workspace_bytes(&c),\n'
+                   '         glm4moe_ep_comm_bytes(256, 4096, GLM4MOE_BF16, 8));\n'
+                   '  return 0;\n}\n')
+    inc = os.path.join(ROOT, "include")
+    subprocess.run([gcc, "-std=c99", "-Wall", "-Werror", "-pedantic", "-fsyntax-only", "-I", inc, str(src)], check=True)
+    from glm4_moe_b200.build import LIB_PATH
+    exe = tmp_path / "host"
+    subprocess.run([gcc, "-std=c99", "-I", inc, str(src), "-o", str(exe), LIB_PATH,
+                    "-Wl,-rpath," + os.path.dirname(LIB_PATH)], check=True)
+    out = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()
+    lib = _lib.load()
+    assert int(out[0]) == 1 and int(out[2]) == lib.glm4moe_ep_comm_bytes(256, 4096, _lib.BF16, 8) and int(out[1]) > 0
+
+
 def test_workspace_and_arg_errors_without_gpu():
     lib = _lib.load()
     import ctypes as C
