@@ -20,7 +20,7 @@ DTYPE_CODE = {torch.float32: F32, torch.float16: F16, torch.bfloat16: BF16}
 # every symbol include/glm4_moe_b200.h declares (tests check the export list against the header)
 SYMBOLS = [
     "glm4moe_abi_version", "glm4moe_debug_set", "glm4moe_error_string", "glm4moe_router_logits", "glm4moe_router_select",
-    "glm4moe_route_small", "glm4moe_permute", "glm4moe_permute_scratch_elems", "glm4moe_tile_capacity", "glm4moe_gather_rows",
+    "glm4moe_route_small", "glm4moe_permute", "glm4moe_permute_static", "glm4moe_permute_scratch_elems", "glm4moe_tile_capacity", "glm4moe_gather_rows",
     "glm4moe_expert_gate_up_simt", "glm4moe_expert_down_simt", "glm4moe_mlp_forward", "glm4moe_combine",
     "glm4moe_workspace_bytes", "glm4moe_layer_create", "glm4moe_layer_destroy",
     "glm4moe_layer_forward", "glm4moe_layer_forward_ex", "glm4moe_layer_forward_timed", "glm4moe_layer_forward_host", "glm4moe_layer_view",
@@ -69,6 +69,7 @@ def load() -> C.CDLL:
     lib.glm4moe_route_small.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, f32, i32, i32, i32, i32, i32, i32,
                                         vp, vp, vp, vp, vp, vp, vp, i32, vp, vp, vp, vp, i32, vp]
     lib.glm4moe_permute.argtypes = [vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, i32, vp, vp, vp]
+    lib.glm4moe_permute_static.argtypes = [vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, i32, vp, vp]
     lib.glm4moe_permute_scratch_elems.restype = sz
     lib.glm4moe_permute_scratch_elems.argtypes = [i32, i32]
     lib.glm4moe_tile_capacity.restype = C.c_int32

@@ -10,6 +10,8 @@
 //                 per-block per-expert counts
 //   scan_kernel   (1 block): block-exclusive prefix per expert, expert offsets, tile work list
 //   scatter_kernel(grid = ceil(T/256)): row = offsets[e] + block_base[b][e] + local rank
+#include <atomic>
+
 #include "common.cuh"
 #include "route_device.cuh"
 
@@ -217,6 +219,54 @@ extern "C" int glm4moe_permute(const int32_t* idx, const float* w, int T, int k,
                                   static_cast<const int32_t*>(expert_offsets), row_token, row_weight, slot_row));
   }
   return GLM4MOE_OK;
+}
+
+// ---- glm4moe_permute_static: the same permutation for callers that cannot hand over scratch memory ------------
+// No counterpart in the reference.  Some hosts of this library have no way to obtain device memory of their own:
+// a plugin that is only ever given the input and output buffers of its op by the runtime that loaded it, a
+// component that must stay inside a memory budget fixed before the library was loaded (every byte of the device
+// already pledged to a KV cache or another tenant), or a call site inside a region where cudaMalloc is forbidden.
+// For them the [blocks x experts] count table of the three-kernel path lives in the library's own image: a
+// file-scope device array, created by the CUDA runtime when the module is loaded on a GPU and kept until the
+// process exits (about 65 KB on each GPU that loads the library).
+namespace glm4moe {
+constexpr int kPermuteStaticMaxTokens = GLM4MOE_PERMUTE_STATIC_MAX_TOKENS;
+constexpr size_t kPermuteStaticElems =
+    (static_cast<size_t>(kPermuteStaticMaxTokens / kTokPerBlock) + 1) * kMaxExperts + 8;
+static_assert(kPermuteStaticMaxTokens % kTokPerBlock == 0, "the limit is a whole number of rank blocks");
+// In host code this name is only a handle for cudaGetSymbolAddress: it is NOT a device address and must never be
+// passed to a kernel.  Device code may name it directly.
+static __device__ __align__(256) int32_t g_permute_static_scratch[kPermuteStaticElems];
+
+constexpr int kMaxDevices = 64;
+static std::atomic<int32_t*> g_permute_static_ptr[kMaxDevices];   // device address of the array, per GPU
+}  // namespace glm4moe
+
+extern "C" int glm4moe_permute_static(const int32_t* idx, const float* w, int T, int k, int E, int e_lo, int e_hi,
+                                      int tile_rows, int shared_lo, int shared_hi, int32_t* expert_offsets,
+                                      int32_t* row_token, float* row_weight, int32_t* slot_row, int32_t* tiles,
+                                      int32_t tile_capacity, int32_t* num_tiles, void* stream) {
+  if (T > kPermuteStaticMaxTokens) return GLM4MOE_ERR_WORKSPACE;   // the array holds no more; nothing is launched
+  if (T < 0 || E <= 0 || E > kMaxExperts) return GLM4MOE_ERR_ARG;
+  if (glm4moe_permute_scratch_elems(T, E) > kPermuteStaticElems) return GLM4MOE_ERR_WORKSPACE;
+  int dev = -1;
+  GLM4MOE_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return GLM4MOE_ERR_UNSUPPORTED;
+  int32_t* scratch = g_permute_static_ptr[dev].load(std::memory_order_acquire);
+  if (scratch == nullptr) {
+    // Set-up, once per GPU, with that GPU current: ask the runtime where this GPU's copy of the array lives.  (Two
+    // threads racing here get the same answer.)  This may load the module on the GPU, so it belongs before any
+    // stream capture.
+    void* p = nullptr;
+    GLM4MOE_CUDA_CHECK(cudaGetSymbolAddress(&p, g_permute_static_scratch));
+    if (p == nullptr) return GLM4MOE_ERR_DEVICE;
+    scratch = static_cast<int32_t*>(p);
+    g_permute_static_ptr[dev].store(scratch, std::memory_order_release);
+  }
+  // Nothing in the table has to start at zero: permute_rank_kernel writes every [block][expert] count this call
+  // reads before permute_scan_kernel reads it, so what the previous call left behind is never observed.
+  return glm4moe_permute(idx, w, T, k, E, e_lo, e_hi, tile_rows, shared_lo, shared_hi, expert_offsets, row_token,
+                         row_weight, slot_row, tiles, tile_capacity, num_tiles, scratch, stream);
 }
 
 extern "C" int glm4moe_gather_rows(const void* x, const int32_t* row_token,

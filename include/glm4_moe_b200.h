@@ -138,6 +138,31 @@ int glm4moe_permute(const int32_t* idx, const float* w, int T, int k, int E, int
 size_t glm4moe_permute_scratch_elems(int T, int E);
 int32_t glm4moe_tile_capacity(int T, int k, int E, int tile_rows);
 
+/* glm4moe_permute for callers that cannot supply scratch memory.  (No counterpart in the reference: the reference
+ * is eager PyTorch and never has to think about where temporaries come from.)
+ * Who needs it: code that is handed only the input and output buffers of its op and has no allocator to turn to --
+ * a plugin inside a runtime that owns all device memory and forbids cudaMalloc from plugins, a process whose GPU is
+ * already fully pledged (KV cache, other tenants) when this library is loaded, a call site where an allocation
+ * would stall or deadlock the device.  Same arguments and same results as glm4moe_permute, minus `scratch`: the
+ * per-block count table lives in a fixed array inside the library's device image instead (about 65 KB, present on
+ * every GPU that loads the library until the process exits).
+ *   - Limit: T <= GLM4MOE_PERMUTE_STATIC_MAX_TOKENS (and E <= 256 as everywhere).  A larger T is refused with
+ *     GLM4MOE_ERR_WORKSPACE before anything is launched; use glm4moe_permute with your own scratch for those.
+ *   - Allocates nothing: no cudaMalloc / cudaFree, no allocating library call.
+ *   - The first call on each GPU looks up that GPU's address of the array (with the calling thread's current device,
+ *     which must be the device `stream` and all buffers belong to).  That look-up can make the CUDA runtime load
+ *     the library's module onto the GPU, so make the first call per GPU outside any stream capture.
+ *   - All calls on a GPU share the one array, from every stream and every thread.  Calls that run one after the
+ *     other (same stream, or ordered by events) are safe -- nothing in the array has to be cleared between them,
+ *     each call overwrites what it later reads.  Two calls with T > 256 that may overlap on the GPU race on it and
+ *     give wrong permutations: order them, or give the second one its own scratch through glm4moe_permute.
+ *     (T <= 256 runs in a single block and never touches the array.)                                          */
+#define GLM4MOE_PERMUTE_STATIC_MAX_TOKENS 16384
+int glm4moe_permute_static(const int32_t* idx, const float* w, int T, int k, int E, int e_lo, int e_hi,
+                           int tile_rows, int shared_lo, int shared_hi, int32_t* expert_offsets, int32_t* row_token,
+                           float* row_weight, int32_t* slot_row, int32_t* tiles, int32_t tile_capacity,
+                           int32_t* num_tiles, void* stream);
+
 /* x_rows[r,:] = x[row_token[r],:] for routed rows, x_rows[T*k + t,:] = x[t,:] for t in
  * [shared_lo, shared_hi)  (moe.py:147) */
 int glm4moe_gather_rows(const void* x, const int32_t* row_token, const int32_t* expert_offsets,
