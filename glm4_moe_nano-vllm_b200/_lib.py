@@ -11,6 +11,7 @@ import torch
 
 from .build import LIB_PATH
 
+ABI_VERSION = 2          # GLM4MOE_ABI_VERSION of include/glm4_moe_b200.h
 F32, F16, BF16 = 0, 1, 2
 IMPL_AUTO, IMPL_SIMT, IMPL_UMMA = 0, 1, 2
 W_NATIVE, W_FP8_BLOCK128, W_FP8_BLOCK128_POW2 = 0, 1, 2
@@ -109,7 +110,7 @@ def load() -> C.CDLL:
     for name in SYMBOLS:
         if lib.glm4moe_abi_version is None or not hasattr(lib, name):
             raise Glm4MoeLibraryError(f"{LIB_PATH} does not export {name}")
-    if lib.glm4moe_abi_version() != 1:
+    if lib.glm4moe_abi_version() != ABI_VERSION:
         raise Glm4MoeLibraryError("ABI version mismatch between _lib.py and the built library")
     _lib = lib
     return lib

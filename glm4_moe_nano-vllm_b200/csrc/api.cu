@@ -1178,7 +1178,8 @@ extern "C" int glm4moe_layer_forward_prenorm(glm4moe_layer_t* l, const void* x, 
 }
 
 extern "C" size_t glm4moe_ep_comm_bytes(int max_tokens, int H, int dtype, int world) {
-  if (max_tokens <= 0 || H <= 0 || H % 8 != 0 || world < 1 || world > kEpMaxRanks ||
+  // the same limits ep_allreduce_launch applies, so that a buffer that can be sized can also be used
+  if (max_tokens <= 0 || H <= 0 || H % 8 != 0 || H > GLM4MOE_EP_COMM_MAX_HIDDEN || world < 1 || world > kEpMaxRanks ||
       (dtype != GLM4MOE_BF16 && dtype != GLM4MOE_F16))
     return 0;
   return ep_comm_layout(max_tokens, H, dtype, world).total;

@@ -40,6 +40,7 @@ namespace glm4moe {
 namespace {
 
 constexpr int kArMaxVec = 4;     // 16-byte vectors per thread: H <= 256 * 4 * 8 = 8192 two-byte elements
+static_assert(kEpArThreads * kArMaxVec * 8 == GLM4MOE_EP_COMM_MAX_HIDDEN, "glm4moe_ep_comm_bytes refuses what the kernels cannot hold");
 
 __device__ __forceinline__ void st_release_sys(int32_t* p, int32_t v) {
   asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");

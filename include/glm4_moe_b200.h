@@ -4,10 +4,17 @@
  * Drop-in boundary for the reference's MoE layer (a Python nn.Module; the reference has no FFI
  * of its own).  Each entry point names the reference code it replaces.
  * All pointers are raw device pointers unless the name says `_host`; sizes are element counts;
- * `stream` is a `cudaStream_t` passed as `void*`.  No entry point allocates device memory,
- * none synchronises except `glm4moe_layer_forward_host` (its stream) and `glm4moe_layer_create`
- * (the device, once: it zeroes the workspace counters).  Return value: 0 = ok, <0 = argument /
- * support error (GLM4MOE_ERR_*), >0 = `cudaError_t`.
+ * `stream` is a `cudaStream_t` passed as `void*`.  Device memory: the forward / kernel entry points allocate
+ * nothing (the caller passes workspace, staging and scratch).  Two set-up entries do allocate:
+ * `glm4moe_p2p_alloc` (that is its job; `glm4moe_p2p_free` releases it) and `glm4moe_layer_create` with
+ * weight_format = GLM4MOE_W_FP8_BLOCK128_POW2 (two packed UE8M0 copies of the block scales, 1 byte per
+ * 128 x 128 weight block, owned by the layer and released by `glm4moe_layer_destroy`, plus a 4-byte flag freed
+ * before it returns).
+ * Synchronisation: `glm4moe_layer_forward_host` waits for its stream; `glm4moe_layer_create` synchronises the
+ * device twice (around zeroing the workspace counters and the power-of-two scale check); nothing else does.
+ * Return value: 0 = ok, <0 = argument / support error (GLM4MOE_ERR_*), >0 = `cudaError_t`.
+ * ABI history: 1 = round 1; 2 = weight-format enum + FP8 tiers, debug knobs, p2p / prenorm / all-reduce entries,
+ * `glm4moe_permute_static`, H <= GLM4MOE_EP_COMM_MAX_HIDDEN enforced by `glm4moe_ep_comm_bytes`.
  *
  * Row space used by permute / expert GEMMs / combine:
  *   rows [0, T*k)        routed rows, expert-major, token-ascending inside an expert
@@ -24,7 +31,7 @@
 extern "C" {
 #endif
 
-#define GLM4MOE_ABI_VERSION 1
+#define GLM4MOE_ABI_VERSION 2
 
 enum { GLM4MOE_F32 = 0, GLM4MOE_F16 = 1, GLM4MOE_BF16 = 2 };          /* model dtype */
 /* expert weight format.  FP8_BLOCK128: e4m3 bytes + one fp32 scale per 128 x 128 block, activations e4m3 with
@@ -282,6 +289,7 @@ int glm4moe_layer_forward_prenorm(glm4moe_layer_t* layer, const void* x, const v
  * peer_comm[r]: rank r's communication buffer as mapped in this process (glm4moe_p2p_alloc / _open, zero-filled,
  * glm4moe_ep_comm_bytes(max_tokens, H, dtype, world) bytes, one per process, shared by all layers); every rank
  * passes the same max_tokens and calls the entry the same number of times with the same T. */
+#define GLM4MOE_EP_COMM_MAX_HIDDEN 8192   /* one row = at most 4 16-byte vectors per thread of a 256-thread block */
 size_t glm4moe_ep_comm_bytes(int max_tokens, int H, int dtype, int world);
 int glm4moe_ep_allreduce_add_rmsnorm(void* const* peer_comm, int rank, int world, int max_tokens,
                                      const void* partial, const void* residual, const void* weight, float eps,

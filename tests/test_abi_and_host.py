@@ -33,7 +33,7 @@ def test_header_symbols_are_exported():
     lib = _lib.load()
     for name in declared:
         assert hasattr(lib, name), name
-    assert lib.glm4moe_abi_version() == 1
+    assert lib.glm4moe_abi_version() == 2 == _lib.ABI_VERSION
     assert lib.glm4moe_error_string(-2).decode().startswith("unsupported")
 
 
@@ -65,7 +65,7 @@ def test_header_is_plain_c99(tmp_path):
                     "-Wl,-rpath," + os.path.dirname(LIB_PATH)], check=True)
     out = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()
     lib = _lib.load()
-    assert int(out[0]) == 1 and int(out[2]) == lib.glm4moe_ep_comm_bytes(256, 4096, _lib.BF16, 8) and int(out[1]) > 0
+    assert int(out[0]) == 2 and int(out[2]) == lib.glm4moe_ep_comm_bytes(256, 4096, _lib.BF16, 8) and int(out[1]) > 0
 
 
 def test_workspace_and_arg_errors_without_gpu():
@@ -99,6 +99,8 @@ def test_front_end_entries_without_gpu():
     assert lib.glm4moe_ep_comm_bytes(32, H, _lib.BF16, 9) == 0         # one NVSwitch box
     assert lib.glm4moe_ep_comm_bytes(32, 4090, _lib.BF16, 2) == 0      # 16-byte rows
     assert lib.glm4moe_ep_comm_bytes(0, H, _lib.BF16, 2) == 0
+    assert lib.glm4moe_ep_comm_bytes(32, 8192, _lib.BF16, 2) > 0
+    assert lib.glm4moe_ep_comm_bytes(32, 8200, _lib.BF16, 2) == 0      # a row the all-reduce kernels cannot hold: refused at set-up
     bases = (C.c_void_p * 2)(None, None)
     assert lib.glm4moe_ep_allreduce_add_rmsnorm(None, 0, 2, 32, None, None, None, 1e-5, 4, H, _lib.BF16, None, None,
                                                 None) == -1
