@@ -370,23 +370,57 @@ def init_dummy_weights(model, seed: int = 1234, std: float = 0.02, **_):
                 layer.mlp.init_random_(seed * 1000 + li, std)
                 own.update(id(t) for t in layer.mlp.parameters())
                 own.update(id(t) for t in layer.mlp.buffers())
-        gens = {}
-
-        def gen(dev):
-            if dev not in gens:
-                gens[dev] = torch.Generator(device=dev).manual_seed(seed)
-            return gens[dev]
-
+        sharded = {}
+        for mname, mod in model.named_modules():
+            wt = mod._parameters.get("weight")
+            if wt is not None and hasattr(wt, "weight_loader") and hasattr(mod, "tp_size"):
+                sharded[id(wt)] = mod
         for name, p in model.named_parameters():
             if id(p) in own or p.numel() == 0:
                 continue
             if p.dim() == 1:
                 p.fill_(1.0 if "norm" in name else 0.0)
+            elif id(p) in sharded:
+                _init_sharded_matrix(sharded[id(p)], p, name, seed, std)
             else:
-                p.copy_((torch.randn(p.shape, generator=gen(p.device), device=p.device, dtype=torch.float32) * std).to(p.dtype))
+                p.copy_(_draw(p.shape, name, seed, std, p.device).to(p.dtype))
         for name, b in model.named_buffers():
             if id(b) not in own and name.endswith("e_score_correction_bias"):
-                b.copy_(torch.rand(b.shape, generator=gen(b.device), device=b.device, dtype=torch.float32) * 0.1)
+                g = torch.Generator(device=b.device).manual_seed(_name_seed(name, seed))
+                b.copy_(torch.rand(b.shape, generator=g, device=b.device, dtype=torch.float32) * 0.1)
+
+
+def _name_seed(name: str, seed: int) -> int:
+    import zlib
+    return (zlib.crc32(name.encode()) ^ (int(seed) * 0x9E3779B1)) & 0x7FFFFFFFFFFFFFFF
+
+
+def _draw(shape, name: str, seed: int, std: float, device) -> torch.Tensor:
+    """N(0, std^2) fp32 tensor that depends only on (parameter name, seed, shape): the same on every rank."""
+    g = torch.Generator(device=device).manual_seed(_name_seed(name, seed))
+    return torch.randn(tuple(shape), generator=g, device=device, dtype=torch.float32) * std
+
+
+def _init_sharded_matrix(mod, p, name: str, seed: int, std: float) -> None:
+    """Fill the tensor-parallel shard `p` of `mod.weight` the way a checkpoint would: draw the FULL matrix (every
+    rank draws the same one, keyed by the parameter name) and hand it to the reference's own `weight_loader`,
+    which narrows it to this rank (linear.py:67-72,89-95,116-130,144-149, embed_head.py:27-32).  The tpN model is
+    then the tp1 model cut into shards, so token ids and digests compare across tensor-parallel sizes."""
+    tp = int(mod.tp_size)
+    loader = p.weight_loader
+    cols = p.shape[1]
+    if hasattr(mod, "output_sizes"):                               # MergedColumnParallelLinear: [gate; up]
+        for i, rows in enumerate(mod.output_sizes):
+            loader(p, _draw((rows, cols), f"{name}#{i}", seed, std, p.device).to(p.dtype), i)
+    elif hasattr(mod, "num_kv_heads") and hasattr(mod, "head_size"):   # QKVParallelLinear: [q; k; v]
+        for sid, heads in (("q", mod.num_heads), ("k", mod.num_kv_heads), ("v", mod.num_kv_heads)):
+            loader(p, _draw((heads * tp * mod.head_size, cols), f"{name}#{sid}", seed, std, p.device).to(p.dtype), sid)
+    else:                                                          # column / row / replicated linear, embeddings
+        tp_dim = getattr(mod, "tp_dim", 0)                         # embeddings: vocabulary rows (embed_head.py:27-32)
+        full = list(p.shape)
+        if tp_dim is not None:
+            full[tp_dim] *= tp
+        loader(p, _draw(full, name, seed, std, p.device).to(p.dtype))
 
 
 def make_model_dir(path: str, *, hidden_size: int, n_routed_experts: int, num_experts_per_tok: int,

@@ -209,3 +209,60 @@ def test_random_init_of_an_expert_parallel_shard_equals_the_single_gpu_block(tmp
     assert torch.equal(shard.gate.weight, one.gate.weight)
     assert torch.equal(shard.gate.e_score_correction_bias, one.gate.e_score_correction_bias)
     assert not torch.equal(one._w_gate_up[0], one._w_gate_up[1])
+
+
+def test_dummy_weights_of_a_tensor_parallel_rank_are_shards_of_the_tp1_model(monkeypatch):
+    """`init_dummy_weights` draws every matrix in full, keyed by its parameter name, and lets the reference's own
+    `weight_loader` cut this rank's shard: concatenating what ranks 0 and 1 of a tp2 run hold gives the tp1 tensor,
+    for every linear flavour the decoder uses (qkv, merged gate/up, row-parallel, column-parallel, embedding)."""
+    from torch import nn
+    import nanovllm.layers.linear as lin
+    import nanovllm.layers.embed_head as eh
+
+    class FakeGroup:
+        def __init__(self, rank, world):
+            self.rank, self.world_size = rank, world
+
+    def build(rank, world):
+        monkeypatch.setattr(lin, "get_tp_group", lambda: FakeGroup(rank, world))
+        monkeypatch.setattr(eh.dist, "get_rank", lambda *a, **k: rank)
+        monkeypatch.setattr(eh.dist, "get_world_size", lambda *a, **k: world)
+
+        class Net(nn.Module):
+            def __init__(self):
+                super().__init__()
+                self.qkv = lin.QKVParallelLinear(64, 16, 4, 2)
+                self.gate_up = lin.MergedColumnParallelLinear(64, [96, 96])
+                self.down = lin.RowParallelLinear(96, 64)
+                self.col = lin.ColumnParallelLinear(64, 32)
+                self.rep = lin.ReplicatedLinear(64, 8)
+                self.emb = eh.VocabParallelEmbedding(128, 64)
+                self.norm = nn.LayerNorm(64)
+
+        class Model(nn.Module):
+            def __init__(self):
+                super().__init__()
+                self.model = nn.Module()
+                self.model.layers = nn.ModuleList()
+                self.net = Net()
+
+        m = Model()
+        S.init_dummy_weights(m, seed=7, std=0.02)
+        return m.net
+
+    one, r0, r1 = build(0, 1), build(0, 2), build(1, 2)
+    q, kv = 4 * 16, 2 * 16
+    full = one.qkv.weight
+    for lo, n in ((0, q), (q, kv), (q + kv, kv)):               # q, k, v blocks: each cut in half by heads
+        h = n // 2
+        off = {0: 0, q: q // 2, q + kv: q // 2 + kv // 2}[lo]
+        assert torch.equal(torch.cat([r0.qkv.weight[off:off + h], r1.qkv.weight[off:off + h]]), full[lo:lo + n])
+    for i in range(2):                                          # gate rows, up rows
+        got = torch.cat([r0.gate_up.weight[i * 48:(i + 1) * 48], r1.gate_up.weight[i * 48:(i + 1) * 48]])
+        assert torch.equal(got, one.gate_up.weight[i * 96:(i + 1) * 96])
+    assert torch.equal(torch.cat([r0.down.weight, r1.down.weight], dim=1), one.down.weight)
+    assert torch.equal(torch.cat([r0.col.weight, r1.col.weight], dim=0), one.col.weight)
+    assert torch.equal(torch.cat([r0.emb.weight, r1.emb.weight], dim=0), one.emb.weight)
+    assert torch.equal(r0.rep.weight, one.rep.weight) and torch.equal(r1.rep.weight, one.rep.weight)
+    assert not torch.equal(r0.col.weight, r1.col.weight)        # the shards are different slices, not one tensor twice
+    assert 0.015 < float(one.qkv.weight.std()) < 0.025 and bool((one.norm.weight == 1).all())
