@@ -156,6 +156,8 @@ class PeerComm:
 
 
 class ExpertParallelMoE(nn.Module):
+    _p2p_maps: dict = {}             # (group, local allocation) -> mappings of a shared peer workspace
+
     def __init__(self, local_moe: nn.Module, n_experts: int, group=None, layout: str = "allreduce"):
         super().__init__()
         if layout not in ("allreduce", "alltoall", "p2p"):
@@ -168,6 +170,7 @@ class ExpertParallelMoE(nn.Module):
         self.world = dist.get_world_size(group)
         self._peer_bases = None      # ctypes array of every rank's workspace base (layout "p2p")
         self._peer_opened = []
+        self._p2p_shared = None      # entry of _p2p_maps when the workspace (and its mappings) are shared
 
     # ---- layout "p2p": one-time handle exchange ---------------------------------------------------
     def setup_p2p(self, max_tokens: int | None = None) -> None:
@@ -176,6 +179,17 @@ class ExpertParallelMoE(nn.Module):
         import ctypes as C
         from . import _lib
         handle, off = self.local.ipc_handle(max_tokens)
+        # blocks that share ONE peer-mapped workspace (Glm4MoeMoE.share_workspace) share its mappings too: the
+        # first of them exchanges the handles, the others reuse what it opened.  Every rank builds the same model,
+        # so every rank takes this branch for the same blocks and the collective below stays matched.
+        shared = type(self)._p2p_maps.get((id(self.group), self.local._ipc_ptr))
+        if shared is not None:
+            self._peer_bases, self._p2p_shared = shared["bases"], shared
+            shared["users"] += 1
+            # this block's layer_create has just zeroed the counters of the shared workspace: no rank may start a
+            # forward (and push flags into a peer) before every rank is past that point
+            dist.barrier(group=self.group)
+            return
         gathered = [None] * self.world
         dist.all_gather_object(gathered, (handle, off), group=self.group)
         lib = _lib.load()
@@ -190,10 +204,23 @@ class ExpertParallelMoE(nn.Module):
             self._peer_opened.append(ptr.value)
             bases[r] = ptr.value + o
         self._peer_bases = bases
+        if getattr(self.local, "_peer_pool_entry", None) is not None:
+            self._p2p_shared = {"bases": bases, "opened": self._peer_opened, "users": 1,
+                                "key": (id(self.group), self.local._ipc_ptr)}
+            type(self)._p2p_maps[self._p2p_shared["key"]] = self._p2p_shared
+            self._peer_opened = []
         dist.barrier(group=self.group)     # nobody launches before every mapping exists
 
     def close_p2p(self) -> None:
         from . import _lib
+        shared, self._p2p_shared = self._p2p_shared, None
+        if shared is not None:
+            shared["users"] -= 1
+            if shared["users"] > 0:                 # another block still runs on these mappings
+                self._peer_bases = None
+                return
+            type(self)._p2p_maps.pop(shared["key"], None)
+            self._peer_opened = shared["opened"]
         if self._peer_opened:
             torch.cuda.synchronize()
             dist.barrier(group=self.group)

@@ -249,8 +249,9 @@ def install(sparse_block: str = "ours", weight_format: str = "native", share_wor
         if world > 1 and _installed.get("ep_layout"):
             layout = _installed["ep_layout"]
             ours.Glm4MoeMoE.default_ep = (dist.get_rank(), world, layout == "p2p")
-            if layout == "p2p":
-                ours.Glm4MoeMoE.share_workspace = False      # peer-mapped workspaces are per layer
+            # layout "p2p": with share_workspace the blocks share ONE peer-mapped workspace and its mappings
+            # (moe.py `_peer_workspace_pool`); a private one per layer is 3 GB x 45 at the reference's default
+            # max_num_batched_tokens = 16384
         self.embed_tokens = VocabParallelEmbedding(config.vocab_size, config.hidden_size)
         self.layers = nn.ModuleList([DL.Glm4MoeDecoderLayer(config, prefix=f"model.layers.{i}")
                                      for i in range(config.num_hidden_layers)])

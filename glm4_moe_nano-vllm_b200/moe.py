@@ -268,6 +268,9 @@ class Glm4MoeMoE(nn.Module):
     default_ep = None
     default_max_tokens = None
     _workspace_pool: dict = {}
+    # share_workspace + peer_workspace: ONE cudaMalloc'd, IPC-exported workspace per (device, layout), used by every
+    # expert-parallel block of the process.  key -> {"ptr", "handle", "tensor", "users" (WeakSet), "used" (a forward ran)}
+    _peer_workspace_pool: dict = {}
 
     def __init__(self, config, *, max_tokens: int | None = None, ep_rank: int | None = None,
                  ep_size: int | None = None, impl: str = "auto", peer_workspace: bool | None = None):
@@ -295,6 +298,7 @@ class Glm4MoeMoE(nn.Module):
         self.peer_workspace = bool(peer_workspace)
         self._ipc_ptr = None
         self._ipc_handle = None
+        self._peer_pool_entry = None
         n_local = self.expert_end - self.expert_begin
         # stacked storage, created under the process-wide default dtype/device like the
         # reference's parameters (model_runner.py:29-31)
@@ -370,7 +374,18 @@ class Glm4MoeMoE(nn.Module):
             users.discard(self)
         self._workspace = None
         self._host = None
-        if getattr(self, "_ipc_ptr", None):
+        ent = getattr(self, "_peer_pool_entry", None)
+        if ent is not None:
+            # shared peer workspace: freed with its last user (peers unmap first: ExpertParallelMoE.close_p2p)
+            ent["users"].discard(self)
+            self._peer_pool_entry = None
+            if not len(ent["users"]):
+                pool = type(self)._peer_workspace_pool
+                for k_ in [k_ for k_, v in pool.items() if v is ent]:
+                    del pool[k_]
+                ent["tensor"] = None
+                _lib.load().glm4moe_p2p_free(ent["ptr"])
+        elif getattr(self, "_ipc_ptr", None):
             _lib.load().glm4moe_p2p_free(self._ipc_ptr)
         self._ipc_ptr = None
         self._ipc_handle = None
@@ -413,7 +428,30 @@ class Glm4MoeMoE(nn.Module):
         if nbytes == 0:
             raise _lib.Glm4MoeLibraryError("unsupported GLM4-MoE configuration for the CUDA library")
         dev = self.gate.weight.device
-        if self.peer_workspace:
+        if self.peer_workspace and type(self).share_workspace:
+            # One peer-mapped workspace for all the expert-parallel blocks of this process (a 46-layer model would
+            # otherwise hold 45 of them: 3 GB each at 16 k tokens).  The layers of a model run one after the other
+            # on one stream and every cross-GPU counter (epoch, parity, ready / done flags) lives IN the workspace,
+            # so to the protocol of ep_combine.cu the next layer is simply the next call.  `glm4moe_layer_create`
+            # zeroes those counters: every sharer must be created before the first forward on the workspace.
+            key = (str(dev), nbytes, tuple(getattr(cfg, f[0]) for f in cfg._fields_ if f[0] not in ("impl",)))
+            pool = type(self)._peer_workspace_pool
+            ent = pool.get(key)
+            if ent is None:
+                import weakref
+                ptr, hbuf = C.c_void_p(), C.create_string_buffer(64)
+                with torch.cuda.device(dev):
+                    _lib.check(lib.glm4moe_p2p_alloc(nbytes + 1024, C.byref(ptr), hbuf), "p2p_alloc")
+                ent = pool[key] = {"ptr": ptr.value, "handle": hbuf.raw, "users": weakref.WeakSet(), "used": False,
+                                   "tensor": torch.as_tensor(_ForeignCudaBuffer(ptr.value, nbytes + 1024), device=dev)}
+            elif ent["used"]:
+                raise _lib.Glm4MoeLibraryError(
+                    "a shared peer-mapped workspace already ran a forward: creating another block on it would reset "
+                    "its cross-GPU counters. Call setup_p2p() on every expert-parallel block before the first forward")
+            ent["users"].add(self)
+            self._peer_pool_entry = ent
+            self._ipc_ptr, self._ipc_handle, self._workspace = ent["ptr"], ent["handle"], ent["tensor"]
+        elif self.peer_workspace:
             ptr, hbuf = C.c_void_p(), C.create_string_buffer(64)
             with torch.cuda.device(dev):
                 _lib.check(lib.glm4moe_p2p_alloc(nbytes + 1024, C.byref(ptr), hbuf), "p2p_alloc")
@@ -793,6 +831,8 @@ class Glm4MoeMoE(nn.Module):
         if T == 0:
             return out
         self._ensure_layer(T)
+        if self._peer_pool_entry is not None:
+            self._peer_pool_entry["used"] = True
         with torch.cuda.device(h.device), _lib.nvtx_range("glm4moe.forward_ep_p2p", T):
             _lib.check(_lib.load().glm4moe_layer_forward_ep_p2p(self._handle, h.data_ptr(), out.data_ptr(), T,
                                                                peer_bases, self.ep_rank, self.ep_size,
@@ -811,6 +851,8 @@ class Glm4MoeMoE(nn.Module):
         if T == 0:
             return out, res_out
         self._ensure_layer(T)
+        if self._peer_pool_entry is not None:
+            self._peer_pool_entry["used"] = True
         with torch.cuda.device(h.device), _lib.nvtx_range("glm4moe.forward_ep_p2p_prenorm", T):
             _lib.check(_lib.load().glm4moe_layer_forward_ep_p2p_prenorm(
                 self._handle, h.data_ptr(), _lib.ptr(r), norm_weight.data_ptr(), float(eps), _lib.ptr(res_out),

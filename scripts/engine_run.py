@@ -116,6 +116,7 @@ def main():
             "fused_post_layers": sum(1 for l in llm.model_runner.model.model.layers if "_fused_post" in l.__dict__),
             "last_impl": ours[0].last_impl if ours else None, "last_fused": ours[0].last_fused if ours else None,
             "gpu_mem_gb": torch.cuda.max_memory_allocated() / 1e9,
+            "workspace_allocations": len({m.workspace_base() for m in ours if m._workspace is not None}),
             "digest": hashlib.sha256(json.dumps(toks).encode()).hexdigest()[:16], "token_ids": toks}
     print(json.dumps(line))
     sys.stdout.flush()

@@ -228,3 +228,20 @@ def test_reference_engine_decodes_with_the_swapped_block_eager_and_graph():
     with open(os.path.join(ROOT, "gpurun_out", "engine_small.jsonl"), "w") as f:
         for run in (eager, graph, fp8):
             f.write(json.dumps({k: v for k, v in run.items() if k != "token_ids"}) + "\n")
+
+
+def test_engine_two_ranks_share_one_peer_workspace_at_the_reference_default_batch():
+    """tp2 with the expert-parallel peer-memory layout at the reference's default `max_num_batched_tokens` = 16384
+    (config.py:9): the sparse blocks of a rank run on ONE peer-mapped workspace (a private one per layer is what ran
+    out of memory at that size on a 46-layer model), and because that layout is bit-identical to the single-GPU
+    block the engine must emit exactly the tokens it emits with every block replicated on both ranks."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    p2p = _engine("--tp", "2", "--ep", "p2p", "--max-batched-tokens", "16384", "--eager")
+    rep = _engine("--tp", "2", "--ep", "none", "--max-batched-tokens", "16384", "--eager")
+    assert p2p["sparse_blocks_ours"] == 3 and p2p["experts_per_rank"] * 2 == rep["experts_per_rank"], (p2p, rep)
+    assert p2p["workspace_allocations"] == 1, p2p
+    assert p2p["token_ids"] == rep["token_ids"], "expert-parallel p2p run differs from the replicated-block run"
+    graph = _engine("--tp", "2", "--ep", "p2p", "--max-batched-tokens", "16384")
+    assert graph["cuda_graph_decode"] and graph["token_ids"] == p2p["token_ids"]

@@ -168,13 +168,28 @@ def _worker_front(rank, world, port, q):
                 if world == 2:
                     assert torch.equal(got2_r, want_r)
                 # Beyond two ranks NCCL sums the bf16 partials in another order with other roundings: the residual
-                # stream agrees to an ulp, and a token whose k-th / (k+1)-th router scores sit within that ulp may
-                # route differently (its whole output row then differs): most rows must agree, not all
+                # stream agrees to an ulp with the peer-memory kernel's.  The block's OUTPUT is therefore compared on
+                # the input this path itself normalised (NCCL's sum, the same norm kernel), where no token can route
+                # differently: the single-GPU block on that input, rows within the expert-parallel all-reduce's
+                # own rounding (its partial outputs are rounded per rank, then summed), every row, no exemptions.
                 dr = (got2_r.float() - want_r.float()).abs()
                 assert bool((dr <= 2.0 ** -6 * want_r.float().abs() + 2.0 ** -6).all()), float(dr.max())
-                row_d = (got2.float() - want.float()).abs().amax(1) / want.float().abs().max()
-                if world == 2 or T >= 32:
-                    assert float((row_d > 3e-2).float().mean()) <= (0.0 if world == 2 else 0.34), row_d.tolist()[:8]
+                y2 = mine.clone()
+                dist.all_reduce(y2)
+                x2, r2 = LN.rmsnorm(y2, nw, eps, res)
+                assert torch.equal(r2, got2_r)
+                want2 = single(x2)
+                idx2 = single.workspace_view("idx", T).clone()
+                assert torch.equal(local_nccl.workspace_view("idx", T), idx2), f"T={T}: routing on identical input"
+                row_d = (got2.float() - want2.float()).abs().amax(1) / want2.float().abs().max()
+                assert float(row_d.max()) < 3e-2, (T, row_d.tolist()[:8])
+                # and that output against the fp32 truth under the routing the kernel chose (north_star rtol 2e-2)
+                truth = O.moe_forward_fp32(x2.cpu(), wts, shape.k, shape.routed_scaling_factor,
+                                           routing=(idx2.cpu().long(),
+                                                    single.workspace_view("w", T).cpu().to(dt)))["out"]
+                rms = truth.pow(2).mean().sqrt()
+                g2 = got2.float().cpu()
+                assert int(((g2 - truth).abs() > 2e-2 * truth.abs() + 2e-2 * rms).sum()) == 0
             checked += 4
         torch.cuda.synchronize()
         ep.close_p2p()
@@ -227,3 +242,88 @@ def test_expert_parallel_two_gpus():
         for key, (bad, rel, d1) in res.items():
             assert bad == 0 and rel < 8e-3, (rank, key, bad, rel)
             assert d1 < 3e-2, (rank, key, d1)
+
+
+def _worker_shared(rank, world, port, q):
+    """Several expert-parallel blocks on ONE peer-mapped workspace (`Glm4MoeMoE.share_workspace`, what the engine
+    shim uses for the 45 sparse layers of a model): called one after the other like the layers of a decoder stack,
+    each must stay bit-identical to its single-GPU block, step after step, in every combine mode."""
+    import glm4_moe_b200
+    from glm4_moe_b200 import synth, _lib
+    from glm4_moe_b200.distributed import ExpertParallelMoE
+    from test_gpu_parity import _module
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    lib = _lib.load()
+    try:
+        shape, dt = synth.MINI, torch.bfloat16
+        n_layers = 3
+        wts = [synth.make_weights(shape, dt, seed=4000 + i) for i in range(n_layers)]
+        singles = [_module(shape, dt, w, max_tokens=512) for w in wts]
+        glm4_moe_b200.Glm4MoeMoE.share_workspace = True
+        try:
+            eps_ = []
+            for w in wts:
+                local = _module(shape, dt, w, ep_rank=rank, ep_size=world, max_tokens=512, peer_workspace=True)
+                ep = ExpertParallelMoE(local, shape.E, layout="p2p")
+                ep.setup_p2p(512)
+                eps_.append(ep)
+            assert len({e.local._ipc_ptr for e in eps_}) == 1 and len(ExpertParallelMoE._p2p_maps) == 1
+            assert len({e.local.workspace_base() for e in eps_}) == 1
+            checked = 0
+            for T in (1, 7, 32, 40, 300, 512):
+                x = synth.make_tokens(shape, T, dt, T).cuda()
+                with torch.inference_mode():
+                    want = []
+                    h = x
+                    for sgl in singles:                      # a small "decoder stack": each block feeds the next
+                        h = sgl(h)
+                        want.append(h.clone())
+                    for mode, fast in ((-1, 1), (1, 1), (0, 0), (-1, 1)):
+                        _lib.check(lib.glm4moe_set_ep_sliced(mode))
+                        _lib.check(lib.glm4moe_debug_set(7, fast))
+                        dist.barrier()
+                        for step in range(3):
+                            h = x
+                            for li, ep in enumerate(eps_):
+                                h = ep(h)
+                                assert torch.equal(h, want[li]), f"T={T} mode={mode} fast={fast} step={step} layer={li}"
+                                checked += 1
+                _lib.check(lib.glm4moe_set_ep_sliced(-1))
+                _lib.check(lib.glm4moe_debug_set(7, 1))
+            # a block that joins after forwards ran would reset the cross-GPU counters: refused, on every rank alike
+            late = _module(shape, dt, wts[0], ep_rank=rank, ep_size=world, max_tokens=512, peer_workspace=True)
+            with pytest.raises(_lib.Glm4MoeLibraryError):
+                late.ipc_handle(512)
+            torch.cuda.synchronize()
+            for ep in eps_:
+                ep.close_p2p()
+            assert not ExpertParallelMoE._p2p_maps
+        finally:
+            glm4_moe_b200.Glm4MoeMoE.share_workspace = False
+        q.put((rank, checked))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_expert_parallel_blocks_share_one_peer_workspace():
+    """world = 2 by default; GLM4MOE_TEST_WORLD=4/8 for more ranks of one box."""
+    world = int(os.environ.get("GLM4MOE_TEST_WORLD", "2"))
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker_shared, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    out = [q.get(timeout=600) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    assert all(n > 0 for _, n in out)
