@@ -11,6 +11,32 @@ import torch.multiprocessing as mp
 pytestmark = pytest.mark.gpu
 
 
+def _collect(procs, q, world, limit_s=600):
+    """One result per rank; a rank that dies ends the test at once (the survivors would sit in a collective until
+    the limit: on an 8-GPU box that is ten minutes of eight GPUs)."""
+    import queue
+    import time
+    out, t0 = [], time.time()
+    while len(out) < world:
+        try:
+            out.append(q.get(timeout=2))
+            continue
+        except queue.Empty:
+            pass
+        dead = [p for p in procs if p.exitcode not in (None, 0)]
+        if dead or time.time() - t0 > limit_s:
+            for p in procs:
+                if p.is_alive():
+                    p.kill()
+            pytest.fail(f"{len(dead)} of {world} ranks failed (exit codes {[p.exitcode for p in procs]}); "
+                        f"{len(out)} finished" if dead else f"no result after {limit_s} s")
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    return out
+
+
+
 def _worker(rank, world, port, q):
     import glm4_moe_b200
     from glm4_moe_b200 import synth
@@ -172,15 +198,23 @@ def _worker_front(rank, world, port, q):
                 # the input this path itself normalised (NCCL's sum, the same norm kernel), where no token can route
                 # differently: the single-GPU block on that input, rows within the expert-parallel all-reduce's
                 # own rounding (its partial outputs are rounded per rank, then summed), every row, no exemptions.
+                # (NCCL rounds its running sums to bf16: up to world - 1 roundings, each at most half an ulp, 2^-9, of
+                # a running sum no larger than sum_r |partial_r|; then the residual add rounds once more.  Measured on
+                # 8 ranks: 2^-5 on elements whose partials cancel.)
+                mag = sum(p_.float().abs() for p_ in parts).cuda()
                 dr = (got2_r.float() - want_r.float()).abs()
-                assert bool((dr <= 2.0 ** -6 * want_r.float().abs() + 2.0 ** -6).all()), float(dr.max())
+                bound = world * 2.0 ** -9 * mag + 2.0 ** -7 * want_r.float().abs() + 2.0 ** -10
+                assert bool((dr <= bound).all()), (float(dr.max()), float((dr - bound).max()))
                 y2 = mine.clone()
                 dist.all_reduce(y2)
                 x2, r2 = LN.rmsnorm(y2, nw, eps, res)
-                assert torch.equal(r2, got2_r)
+                got3 = ep_nccl(x2)
+                if torch.equal(r2, got2_r):          # NCCL chose the same sum order twice: the one-call form agrees
+                    assert torch.equal(got3, got2)
                 want2 = single(x2)
                 idx2 = single.workspace_view("idx", T).clone()
                 assert torch.equal(local_nccl.workspace_view("idx", T), idx2), f"T={T}: routing on identical input"
+                got2 = got3
                 row_d = (got2.float() - want2.float()).abs().amax(1) / want2.float().abs().max()
                 assert float(row_d.max()) < 3e-2, (T, row_d.tolist()[:8])
                 # and that output against the fp32 truth under the routing the kernel chose (north_star rtol 2e-2)
@@ -213,10 +247,7 @@ def test_fused_allreduce_norm_and_prenorm_block_two_gpus():
     procs = [ctx.Process(target=_worker_front, args=(r, world, port, q)) for r in range(world)]
     for p in procs:
         p.start()
-    out = [q.get(timeout=600) for _ in range(world)]
-    for p in procs:
-        p.join(timeout=120)
-        assert p.exitcode == 0
+    out = _collect(procs, q, world)
     assert all(n > 0 for _, n in out)
 
 
@@ -234,10 +265,7 @@ def test_expert_parallel_two_gpus():
     procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
     for p in procs:
         p.start()
-    out = [q.get(timeout=600) for _ in range(world)]
-    for p in procs:
-        p.join(timeout=120)
-        assert p.exitcode == 0
+    out = _collect(procs, q, world)
     for rank, res in out:
         for key, (bad, rel, d1) in res.items():
             assert bad == 0 and rel < 8e-3, (rank, key, bad, rel)
@@ -322,8 +350,5 @@ def test_expert_parallel_blocks_share_one_peer_workspace():
     procs = [ctx.Process(target=_worker_shared, args=(r, world, port, q)) for r in range(world)]
     for p in procs:
         p.start()
-    out = [q.get(timeout=600) for _ in range(world)]
-    for p in procs:
-        p.join(timeout=120)
-        assert p.exitcode == 0
+    out = _collect(procs, q, world)
     assert all(n > 0 for _, n in out)
