@@ -28,7 +28,7 @@ SYMBOLS = [
     "glm4moe_layer_last_launches", "glm4moe_layer_last_impl", "glm4moe_layer_last_fused", "glm4moe_layer_tile_rows",
     "glm4moe_p2p_alloc", "glm4moe_p2p_open", "glm4moe_p2p_close", "glm4moe_p2p_free", "glm4moe_layer_forward_ep_p2p", "glm4moe_set_ep_sliced", "glm4moe_add_rmsnorm",
     "glm4moe_layer_forward_prenorm", "glm4moe_ep_comm_bytes", "glm4moe_ep_allreduce_add_rmsnorm",
-    "glm4moe_layer_forward_ep_p2p_prenorm",
+    "glm4moe_layer_forward_ep_p2p_prenorm", "glm4moe_ep_last_error", "glm4moe_ep_set_timeout_ms",
 ]
 
 
@@ -107,6 +107,8 @@ def load() -> C.CDLL:
                                                      vp, vp, vp]
     lib.glm4moe_layer_forward_ep_p2p_prenorm.argtypes = [vp, vp, vp, vp, f32, vp, vp, i32, C.POINTER(vp),
                                                          C.POINTER(vp), i32, i32, i32, vp]
+    lib.glm4moe_ep_last_error.argtypes = [C.POINTER(C.c_int32), i32]
+    lib.glm4moe_ep_set_timeout_ms.argtypes = [i32]
     for name in SYMBOLS:
         if lib.glm4moe_abi_version is None or not hasattr(lib, name):
             raise Glm4MoeLibraryError(f"{LIB_PATH} does not export {name}")
@@ -139,9 +141,27 @@ class nvtx_range:
         return False
 
 
+def ep_last_error(clear: bool = False) -> dict | None:
+    """What a cross-GPU wait that gave up recorded (glm4moe_ep_last_error), or None.  Makes no CUDA call: usable
+    after the trap that follows such a failure has poisoned the context."""
+    lib = load()
+    info = (C.c_int32 * 6)()
+    code = lib.glm4moe_ep_last_error(info, int(clear))
+    if code == 0:
+        return None
+    return {"code": code, "error": lib.glm4moe_error_string(code).decode(), "rank": info[1], "waited_for_call": info[2],
+            "last_flag": info[3], "site": {1: "expert combine", 2: "all-reduce + norm"}.get(info[4], str(info[4])),
+            "peer": info[5]}
+
+
 def check(code: int, what: str = "") -> None:
     if code != 0:
         msg = load().glm4moe_error_string(code).decode()
+        if code > 0:                      # a cudaError_t: say so when an expert-parallel wait is behind it
+            ep = ep_last_error()
+            if ep is not None:
+                msg += f" [{ep['error']}: rank {ep['rank']} waited for call {ep['waited_for_call']} of rank " \
+                       f"{ep['peer']} in the {ep['site']}, last flag {ep['last_flag']}]"
         raise Glm4MoeLibraryError(f"{what or 'glm4moe call'} failed: {msg} (code {code})")
 
 

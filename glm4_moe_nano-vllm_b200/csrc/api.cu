@@ -6,6 +6,7 @@
 
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <new>
 
 #include "common.cuh"
@@ -223,6 +224,8 @@ extern "C" const char* glm4moe_error_string(int code) {
     case GLM4MOE_ERR_UNSUPPORTED: return "unsupported shape or dtype";
     case GLM4MOE_ERR_WORKSPACE: return "workspace too small";
     case GLM4MOE_ERR_DEVICE: return "device/driver does not provide the required sm_100 features";
+    case GLM4MOE_ERR_EP_TIMEOUT: return "expert-parallel wait timed out: a peer rank never signalled (see glm4moe_ep_last_error)";
+    case GLM4MOE_ERR_EP_MODE: return "expert-parallel ranks disagree on the call form (sliced / fast / all-reduce mode set differently)";
     default: return code > 0 ? cudaGetErrorString(static_cast<cudaError_t>(code)) : "unknown error";
   }
 }
@@ -1048,10 +1051,85 @@ extern "C" int glm4moe_layer_last_launches(const glm4moe_layer_t* l) { return l 
 extern "C" int glm4moe_layer_last_impl(const glm4moe_layer_t* l) { return l ? l->last_impl : 0; }
 extern "C" int glm4moe_layer_last_fused(const glm4moe_layer_t* l) { return l ? l->last_fused : 0; }
 
+// ---- what a cross-GPU wait that gives up leaves behind (ep_combine.cuh: EpErrorRecord) ------------------------
+namespace {
+std::mutex g_ep_watch_mu;
+glm4moe::EpErrorRecord* g_ep_rec_host = nullptr;   // pinned + mapped + portable: readable after the context is lost
+glm4moe::EpErrorRecord* g_ep_rec_dev = nullptr;    // the same record as the GPUs address it
+long long g_ep_spin_limit = 0;                     // 0 = not decided yet (GLM4MOE_EP_TIMEOUT_MS, else the default)
+constexpr long long kEpDefaultSpinLimit = 1ll << 35;   // ~18 s of SM clocks
+
+long long cycles_of_ms(long long ms) {
+  int dev = 0, khz = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, dev) != cudaSuccess ||
+      khz <= 0)
+    khz = 1965000;                                 // B200 boost clock
+  return ms * static_cast<long long>(khz);
+}
+
+// host memory only: called from the set-up entry every expert-parallel user goes through (never inside a capture)
+int ep_record_ensure() {
+  std::lock_guard<std::mutex> lock(g_ep_watch_mu);
+  if (g_ep_rec_host) return GLM4MOE_OK;
+  void* h = nullptr;
+  GLM4MOE_CUDA_CHECK(cudaHostAlloc(&h, sizeof(glm4moe::EpErrorRecord), cudaHostAllocMapped | cudaHostAllocPortable));
+  memset(h, 0, sizeof(glm4moe::EpErrorRecord));
+  void* d = nullptr;
+  cudaError_t e = cudaHostGetDevicePointer(&d, h, 0);
+  if (e != cudaSuccess) {
+    cudaFreeHost(h);
+    return static_cast<int>(e);
+  }
+  g_ep_rec_host = static_cast<glm4moe::EpErrorRecord*>(h);
+  g_ep_rec_dev = static_cast<glm4moe::EpErrorRecord*>(d);
+  return GLM4MOE_OK;
+}
+}  // namespace
+
+namespace glm4moe {
+EpWatch ep_watch(int rank, int site) {
+  std::lock_guard<std::mutex> lock(g_ep_watch_mu);
+  if (g_ep_spin_limit == 0) {
+    const char* e = getenv("GLM4MOE_EP_TIMEOUT_MS");
+    const long long ms = e ? atoll(e) : 0;
+    g_ep_spin_limit = ms > 0 ? cycles_of_ms(ms) : kEpDefaultSpinLimit;
+  }
+  EpWatch w{};
+  w.rec = g_ep_rec_dev;
+  w.spin_limit = g_ep_spin_limit;
+  w.rank = rank;
+  w.site = site;
+  return w;
+}
+}  // namespace glm4moe
+
+extern "C" int glm4moe_ep_set_timeout_ms(int ms) {
+  std::lock_guard<std::mutex> lock(g_ep_watch_mu);
+  g_ep_spin_limit = ms > 0 ? cycles_of_ms(ms) : kEpDefaultSpinLimit;
+  return GLM4MOE_OK;
+}
+
+extern "C" int glm4moe_ep_last_error(int32_t* info6, int clear) {
+  std::lock_guard<std::mutex> lock(g_ep_watch_mu);
+  if (!g_ep_rec_host) return GLM4MOE_OK;
+  volatile int32_t* r = &g_ep_rec_host->code;       // plain host reads: no CUDA call, works on a poisoned context
+  const int code = r[0];
+  if (info6) {
+    for (int i = 0; i < 6; ++i) info6[i] = r[i];
+  }
+  if (clear) {
+    for (int i = 0; i < 6; ++i) r[i] = 0;
+  }
+  if (code == kEpErrTimeout) return GLM4MOE_ERR_EP_TIMEOUT;
+  if (code == kEpErrModeMismatch) return GLM4MOE_ERR_EP_MODE;
+  return GLM4MOE_OK;
+}
+
 // ---- expert parallelism over peer memory (distributed.py layout "p2p") -------------------------
 extern "C" int glm4moe_p2p_alloc(size_t bytes, void** ptr, unsigned char* handle64) {
   if (!ptr || !handle64 || bytes == 0) return GLM4MOE_ERR_ARG;
   static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  if (int rc = ep_record_ensure()) return rc;
   void* p = nullptr;
   GLM4MOE_CUDA_CHECK(cudaMalloc(&p, bytes));
   cudaError_t e = cudaMemset(p, 0, bytes);

@@ -50,26 +50,35 @@ __device__ __forceinline__ int32_t ld_acquire_sys(const int32_t* p) {
   asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
-constexpr long long kSpinTimeoutCycles = 1ll << 35;
+__device__ __noinline__ void ep_give_up(const EpWatch& w, int32_t* ctl, int code, int e, int observed, int peer) {
+  ctl[2] = code;
+  if (w.rec != nullptr) {
+    // plain stores over PCIe (no reliance on host atomics): several threads may give up at once and each describes
+    // a real failure, so whichever lands last is a valid report.  `code` goes last.
+    volatile int32_t* r = &w.rec->code;
+    r[1] = w.rank;
+    r[2] = e;
+    r[3] = observed;
+    r[4] = w.site;
+    r[5] = peer;
+    __threadfence_system();
+    r[0] = code;
+  }
+  __threadfence_system();
+  __trap();
+}
 // Wait until `flag` carries call e (or e + 1: a peer can be at most one call ahead, see the header).  Accepting only
 // that window keeps a word that was last written ~2^29 calls ago (a row index not used since) from looking "ahead"
 // once the 32-bit epoch arithmetic wraps.
-__device__ __forceinline__ void wait_flag(const int32_t* flag, int e, int mode, int32_t* ctl) {
+__device__ __forceinline__ void wait_flag(const int32_t* flag, int e, int mode, int32_t* ctl, const EpWatch& w,
+                                          int peer) {
   const int target = e * 4;
   const long long t0 = clock64();
   int d;
   while ((d = ld_acquire_sys(flag) - target) < 0 || d >= 8) {
-    if (clock64() - t0 > kSpinTimeoutCycles) {
-      ctl[2] = kEpErrTimeout;
-      __threadfence_system();
-      __trap();
-    }
+    if (clock64() - t0 > w.spin_limit) ep_give_up(w, ctl, kEpErrTimeout, e, d + target, peer);
   }
-  if (d < 4 && d != mode) {
-    ctl[2] = kEpErrModeMismatch;
-    __threadfence_system();
-    __trap();
-  }
+  if (d < 4 && d != mode) ep_give_up(w, ctl, kEpErrModeMismatch, e, d + target, peer);
 }
 // L1-bypassing 128-bit load: inbox rows are written by peers over NVLink (L1 may hold the rows of call e - 2)
 __device__ __forceinline__ uint4 ld_cg16(const void* p) {
@@ -283,7 +292,7 @@ __global__ void __launch_bounds__(kEpArThreads, 2) ep_ar_oneshot_kernel(const Ep
   const int32_t* my_flags = reinterpret_cast<const int32_t*>(a.comm[a.rank] + a.L.rowflag);
   for (int t = blockIdx.x; t < a.tokens; t += gridDim.x) {
     if (threadIdx.x < a.world && threadIdx.x != a.rank)
-      wait_flag(my_flags + threadIdx.x * kEpArOneShotRows + t, e, kEpArModeOne, ctl);
+      wait_flag(my_flags + threadIdx.x * kEpArOneShotRows + t, e, kEpArModeOne, ctl, a.watch, threadIdx.x);
     __syncthreads();
     RowRegs<T> R;
     sum_row<T, false>(a, t, inbox, a.L.os_slot, t, p, R);
@@ -335,7 +344,7 @@ __global__ void __launch_bounds__(kEpArThreads, 2) ep_ar_twoshot_kernel(const Ep
     __threadfence_system();
     st_release_sys(peer_ctl + 16 + a.rank, e * 4 + kEpArModeTwo);
   }
-  if (threadIdx.x < a.world) wait_flag(ctl + 16 + threadIdx.x, e, kEpArModeTwo, ctl);
+  if (threadIdx.x < a.world) wait_flag(ctl + 16 + threadIdx.x, e, kEpArModeTwo, ctl, a.watch, threadIdx.x);
   __syncthreads();
   // ---- my token slice: y to every peer's inbox; residual add + norm locally ----
   const unsigned char* inbox = a.comm[a.rank] + a.L.rs[p];
@@ -349,7 +358,7 @@ __global__ void __launch_bounds__(kEpArThreads, 2) ep_ar_twoshot_kernel(const Ep
     __threadfence_system();
     st_release_sys(peer_ctl + 32 + a.rank, e * 4 + kEpArModeTwo);
   }
-  if (threadIdx.x < a.world) wait_flag(ctl + 32 + threadIdx.x, e, kEpArModeTwo, ctl);
+  if (threadIdx.x < a.world) wait_flag(ctl + 32 + threadIdx.x, e, kEpArModeTwo, ctl, a.watch, threadIdx.x);
   __syncthreads();
   // ---- the other ranks' slices: y from my inbox, same residual add + norm ----
   const unsigned char* ag = a.comm[a.rank] + a.L.ag[p];
@@ -392,7 +401,9 @@ EpCommLayout ep_comm_layout(int max_tokens, int H, int dtype, int world) {
   return L;
 }
 
-int ep_allreduce_launch(const EpArArgs& a, int dtype, int two_shot, void* stream) {
+int ep_allreduce_launch(const EpArArgs& args, int dtype, int two_shot, void* stream) {
+  EpArArgs a = args;
+  a.watch = ep_watch(a.rank, kEpSiteAllReduce);
   if (a.world < 1 || a.world > kEpMaxRanks || a.rank < 0 || a.rank >= a.world) return GLM4MOE_ERR_ARG;
   if (dtype != GLM4MOE_BF16 && dtype != GLM4MOE_F16) return GLM4MOE_ERR_UNSUPPORTED;
   if (a.H % 8 != 0 || a.H / 8 > kEpArThreads * kArMaxVec || a.tokens <= 0) return GLM4MOE_ERR_UNSUPPORTED;

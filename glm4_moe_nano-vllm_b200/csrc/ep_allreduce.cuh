@@ -26,6 +26,7 @@ constexpr int kEpArThreads = 256;
 EpCommLayout ep_comm_layout(int max_tokens, int H, int dtype, int world);
 
 struct EpArArgs {
+  EpWatch watch;
   unsigned char* comm[kEpMaxRanks];   // comm buffer of every rank as mapped in THIS process (own = local)
   EpCommLayout L;
   int rank, world, tokens, H;

@@ -28,8 +28,9 @@
 // round, so the modes can be mixed freely.
 //
 // Every cross-GPU wait is bounded (~18 s of SM clocks): a rank that never arrives, or arrives in
-// another mode (`glm4moe_set_ep_sliced` set differently), stores an error code in ctl[2] and traps
-// instead of hanging the GPU.
+// another mode (`glm4moe_set_ep_sliced` set differently), records what it waited for in the process's pinned host
+// error record (read it with glm4moe_ep_last_error: it survives the trap) and traps instead of hanging the GPU.
+// The limit is glm4moe_ep_set_timeout_ms / GLM4MOE_EP_TIMEOUT_MS.
 #include "common.cuh"
 #include "ep_combine.cuh"
 
@@ -45,24 +46,33 @@ __device__ __forceinline__ int32_t ld_acquire_sys(const int32_t* p) {
   asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
-constexpr long long kSpinTimeoutCycles = 1ll << 35;
+__device__ __noinline__ void ep_give_up(const EpWatch& w, int32_t* ctl, int code, int e, int observed, int peer) {
+  ctl[2] = code;
+  if (w.rec != nullptr) {
+    // plain stores over PCIe (no reliance on host atomics): several threads may give up at once and each describes
+    // a real failure, so whichever lands last is a valid report.  `code` goes last.
+    volatile int32_t* r = &w.rec->code;
+    r[1] = w.rank;
+    r[2] = e;
+    r[3] = observed;
+    r[4] = w.site;
+    r[5] = peer;
+    __threadfence_system();
+    r[0] = code;
+  }
+  __threadfence_system();
+  __trap();
+}
 // wait until the flag reaches call `e` (flag = epoch * 4 + mode); wrap-safe compare
-__device__ __forceinline__ void wait_flag(const int32_t* flag, int e, int mode, int32_t* ctl) {
+__device__ __forceinline__ void wait_flag(const int32_t* flag, int e, int mode, int32_t* ctl, const EpWatch& w,
+                                          int peer) {
   const int target = e * 4;
   const long long t0 = clock64();
   int v;
   while ((v = ld_acquire_sys(flag)) - target < 0) {
-    if (clock64() - t0 > kSpinTimeoutCycles) {
-      ctl[2] = kEpErrTimeout;
-      __threadfence_system();
-      __trap();
-    }
+    if (clock64() - t0 > w.spin_limit) ep_give_up(w, ctl, kEpErrTimeout, e, v, peer);
   }
-  if ((v >> 2) == e && (v & 3) != mode) {
-    ctl[2] = kEpErrModeMismatch;
-    __threadfence_system();
-    __trap();
-  }
+  if ((v >> 2) == e && (v & 3) != mode) ep_give_up(w, ctl, kEpErrModeMismatch, e, v, peer);
 }
 __device__ __forceinline__ uint4 ld_peer16(const void* p) {   // L1-bypassing 128-bit load (peer or local)
   uint4 r;
@@ -95,7 +105,7 @@ __global__ void __launch_bounds__(kEpThreads) ep_combine_p2p_kernel(const EpComb
     int32_t* peer_ctl = reinterpret_cast<int32_t*>(a.ws[threadIdx.x] + a.off_ctl);
     st_release_sys(peer_ctl + 16 + a.rank, e * 4 + mode);
   }
-  if (threadIdx.x < a.world) wait_flag(ctl + 16 + threadIdx.x, e, mode, ctl);
+  if (threadIdx.x < a.world) wait_flag(ctl + 16 + threadIdx.x, e, mode, ctl, a.watch, threadIdx.x);
   __syncthreads();
 
   // ---- reduce: block (x = column chunk, y strides over tokens) ----
@@ -160,7 +170,7 @@ __global__ void __launch_bounds__(kEpThreads) ep_combine_p2p_kernel(const EpComb
   if (!a.fast && threadIdx.x < a.world) {
     int32_t* peer_ctl = reinterpret_cast<int32_t*>(a.ws[threadIdx.x] + a.off_ctl);
     st_release_sys(peer_ctl + 32 + a.rank, e * 4 + mode);
-    wait_flag(ctl + 32 + threadIdx.x, e, mode, ctl);
+    wait_flag(ctl + 32 + threadIdx.x, e, mode, ctl, a.watch, threadIdx.x);
   }
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -199,7 +209,7 @@ __global__ void __launch_bounds__(kEpThreads) ep_combine_sliced_kernel(const EpC
     int32_t* peer_ctl = reinterpret_cast<int32_t*>(a.ws[threadIdx.x] + a.off_ctl);
     st_release_sys(peer_ctl + 16 + a.rank, e * 4 + kEpModeSliced);
   }
-  if (threadIdx.x < a.world) wait_flag(ctl + 16 + threadIdx.x, e, kEpModeSliced, ctl);
+  if (threadIdx.x < a.world) wait_flag(ctl + 16 + threadIdx.x, e, kEpModeSliced, ctl, a.watch, threadIdx.x);
   __syncthreads();
 
   const int col = (blockIdx.x * kEpThreads + threadIdx.x) * V;
@@ -266,7 +276,7 @@ __global__ void __launch_bounds__(kEpThreads) ep_combine_sliced_kernel(const EpC
     int32_t* peer_ctl = reinterpret_cast<int32_t*>(a.ws[threadIdx.x] + a.off_ctl);
     st_release_sys(peer_ctl + 32 + a.rank, e * 4 + kEpModeSliced);
   }
-  if (threadIdx.x < a.world) wait_flag(ctl + 32 + threadIdx.x, e, kEpModeSliced, ctl);
+  if (threadIdx.x < a.world) wait_flag(ctl + 32 + threadIdx.x, e, kEpModeSliced, ctl, a.watch, threadIdx.x);
   __syncthreads();
   // ---- the other ranks' slices: local staging region -> out ----
   if (col < a.H) {
@@ -287,7 +297,9 @@ __global__ void __launch_bounds__(kEpThreads) ep_combine_sliced_kernel(const EpC
   }
 }
 
-int ep_combine_p2p_launch(const EpCombineArgs& a, void* out, int dtype, void* stream) {
+int ep_combine_p2p_launch(const EpCombineArgs& args, void* out, int dtype, void* stream) {
+  EpCombineArgs a = args;
+  a.watch = ep_watch(a.rank, kEpSiteCombine);
   if (a.world < 1 || a.world > kEpMaxRanks || a.k > kEpMaxTopK || a.rank < 0 || a.rank >= a.world)
     return GLM4MOE_ERR_ARG;
   if (dtype != GLM4MOE_BF16 && dtype != GLM4MOE_F16) return GLM4MOE_ERR_UNSUPPORTED;

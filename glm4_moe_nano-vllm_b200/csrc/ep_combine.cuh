@@ -9,7 +9,30 @@ constexpr int kEpMaxRanks = 8;     // one NVSwitch box
 constexpr int kEpMaxTopK = 8;
 constexpr int kEpThreads = 128;
 
+// What a cross-GPU wait that gives up leaves behind.  The record sits in pinned, device-mapped HOST memory (allocated
+// once per process by glm4moe_p2p_alloc): the wait still ends in a trap -- the other blocks of the grid cannot be
+// unwound -- and a trap poisons the CUDA context, but host memory stays readable, so glm4moe_ep_last_error can tell
+// the operator which rank waited for what.  `spin_limit`: SM clocks a wait may spin (glm4moe_ep_set_timeout_ms).
+struct EpErrorRecord {
+  int32_t code;        // 0 none, kEpErrTimeout, kEpErrModeMismatch (first failure wins)
+  int32_t rank;        // the rank that gave up
+  int32_t expected;    // call number it was waiting for
+  int32_t observed;    // flag word it last read (call * 4 + mode)
+  int32_t site;        // kEpSite*
+  int32_t peer;        // index of the flag within its group (the rank being waited for), -1 unknown
+  int32_t pad[10];
+};
+struct EpWatch {
+  EpErrorRecord* rec;  // device-visible address of the host record, nullptr = none
+  long long spin_limit;
+  int rank;
+  int site;
+};
+constexpr int kEpSiteCombine = 1, kEpSiteAllReduce = 2;
+EpWatch ep_watch(int rank, int site);     // api.cu: current record and limit
+
 struct EpCombineArgs {
+  EpWatch watch;
   unsigned char* ws[kEpMaxRanks];   // workspace base of every rank as mapped in THIS process (own = local)
   size_t off_y, off_slot_row, off_idx, off_ctl;   // identical workspace layout on every rank
   size_t off_stage;                 // [T_max, H] staging rows peers store their token slices into (sliced mode)

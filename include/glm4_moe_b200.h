@@ -6,7 +6,8 @@
  * All pointers are raw device pointers unless the name says `_host`; sizes are element counts;
  * `stream` is a `cudaStream_t` passed as `void*`.  Device memory: the forward / kernel entry points allocate
  * nothing (the caller passes workspace, staging and scratch).  Two set-up entries do allocate:
- * `glm4moe_p2p_alloc` (that is its job; `glm4moe_p2p_free` releases it) and `glm4moe_layer_create` with
+ * `glm4moe_p2p_alloc` (that is its job; `glm4moe_p2p_free` releases it; the first call of a process also pins a
+ * 64-byte host record for glm4moe_ep_last_error) and `glm4moe_layer_create` with
  * weight_format = GLM4MOE_W_FP8_BLOCK128_POW2 (two packed UE8M0 copies of the block scales, 1 byte per
  * 128 x 128 weight block, owned by the layer and released by `glm4moe_layer_destroy`, plus a 4-byte flag freed
  * before it returns).
@@ -14,7 +15,8 @@
  * device twice (around zeroing the workspace counters and the power-of-two scale check); nothing else does.
  * Return value: 0 = ok, <0 = argument / support error (GLM4MOE_ERR_*), >0 = `cudaError_t`.
  * ABI history: 1 = round 1; 2 = weight-format enum + FP8 tiers, debug knobs, p2p / prenorm / all-reduce entries,
- * `glm4moe_permute_static`, H <= GLM4MOE_EP_COMM_MAX_HIDDEN enforced by `glm4moe_ep_comm_bytes`.
+ * `glm4moe_permute_static`, H <= GLM4MOE_EP_COMM_MAX_HIDDEN enforced by `glm4moe_ep_comm_bytes`,
+ * `glm4moe_ep_last_error` / `glm4moe_ep_set_timeout_ms`.
  *
  * Row space used by permute / expert GEMMs / combine:
  *   rows [0, T*k)        routed rows, expert-major, token-ascending inside an expert
@@ -46,6 +48,8 @@ enum { GLM4MOE_IMPL_AUTO = 0, GLM4MOE_IMPL_SIMT = 1, GLM4MOE_IMPL_UMMA = 2 };
 #define GLM4MOE_ERR_UNSUPPORTED (-2)  /* shape or dtype outside what the kernels cover */
 #define GLM4MOE_ERR_WORKSPACE (-3)    /* workspace too small */
 #define GLM4MOE_ERR_DEVICE (-4)       /* not an sm_100 device / driver entry point missing */
+#define GLM4MOE_ERR_EP_TIMEOUT (-5)   /* glm4moe_ep_last_error: a cross-GPU wait gave up, a peer never signalled */
+#define GLM4MOE_ERR_EP_MODE (-6)      /* glm4moe_ep_last_error: the ranks disagree on the form of the call */
 
 typedef struct glm4moe_config {
   int32_t hidden_size;            /* H   (Glm4MoeConfig.hidden_size) */
@@ -267,6 +271,21 @@ int glm4moe_p2p_free(void* ptr);
 int glm4moe_layer_forward_ep_p2p(glm4moe_layer_t* layer, const void* x, void* out, int T,
                                  void* const* peer_workspaces, int rank, int world, void* stream);
 int glm4moe_set_ep_sliced(int mode);
+
+/* When a cross-GPU wait gives up.  Every wait inside the peer-memory kernels (glm4moe_layer_forward_ep_p2p*,
+ * glm4moe_ep_allreduce_add_rmsnorm) is bounded: a rank that never arrives, or arrives in another form of the call,
+ * must not hang the GPU.  The kernel cannot unwind the rest of its grid, so it still ends in a trap, and a trap
+ * makes every later CUDA call of the process fail (cudaErrorLaunchFailed).  Before trapping it writes what it was
+ * waiting for into a record in pinned HOST memory (allocated by the first glm4moe_p2p_alloc of the process), and
+ * these two entries make no CUDA call, so they still work afterwards:
+ * glm4moe_ep_last_error: 0 = no failure recorded, else GLM4MOE_ERR_EP_TIMEOUT / GLM4MOE_ERR_EP_MODE; info6 (may be
+ *   NULL) = {raw code, rank that gave up, call number it waited for, flag word it last saw (call * 4 + mode),
+ *   site (1 = expert combine, 2 = all-reduce + norm), peer rank it was waiting for}; clear != 0 resets the record.
+ * glm4moe_ep_set_timeout_ms: how long a wait may spin; ms <= 0 restores the default (2^35 SM clocks, about 18 s).
+ *   Process-wide, read at every launch; env GLM4MOE_EP_TIMEOUT_MS sets the initial value.  Raise it when a peer may
+ *   legitimately be late (first-call module load, a debugger); lower it in tests. */
+int glm4moe_ep_last_error(int32_t* info6, int clear);
+int glm4moe_ep_set_timeout_ms(int ms);
 
 
 /* ---- the norm in front of the block fused to the block (decode_layer.py:98-99 as one call) --------------------

@@ -361,3 +361,15 @@ def test_dense_mlp_mirrors_the_reference_class_and_shards_like_its_linear_layers
         one(torch.zeros(3, H, dtype=torch.bfloat16))
     lib = _lib.load()
     assert lib.glm4moe_mlp_forward(None, None, None, None, None, 4, 256, 200, _lib.BF16, None, None) == -1
+
+
+def test_ep_error_record_entries_without_gpu():
+    """No failure recorded -> 0 and an untouched info array; the timeout setter accepts any value (<= 0 = default)
+    and neither entry needs a device."""
+    import ctypes as C
+    lib = _lib.load()
+    info = (C.c_int32 * 6)(*([7] * 6))
+    assert lib.glm4moe_ep_last_error(info, 1) == 0 and lib.glm4moe_ep_last_error(None, 0) == 0
+    assert _lib.ep_last_error() is None
+    assert lib.glm4moe_ep_set_timeout_ms(250) == 0 and lib.glm4moe_ep_set_timeout_ms(0) == 0
+    assert b"timed out" in lib.glm4moe_error_string(-5) and b"disagree" in lib.glm4moe_error_string(-6)

@@ -352,3 +352,62 @@ def test_expert_parallel_blocks_share_one_peer_workspace():
         p.start()
     out = _collect(procs, q, world)
     assert all(n > 0 for _, n in out)
+
+
+_TIMEOUT_SCRIPT = r'''
+import ctypes as C, json, sys
+import torch
+sys.path.insert(0, %(root)r)
+import glm4_moe_b200
+from glm4_moe_b200 import _lib
+lib = _lib.load()
+T, H, world = 4, 512, 2
+n = lib.glm4moe_ep_comm_bytes(64, H, _lib.BF16, world)
+bufs = []
+for _ in range(world):                    # "rank 1" is a second local buffer nobody ever writes flags into
+    p, h = C.c_void_p(), C.create_string_buffer(64)
+    _lib.check(lib.glm4moe_p2p_alloc(n + 1024, C.byref(p), h))
+    bufs.append((p.value + 1023) // 1024 * 1024)
+assert _lib.ep_last_error() is None
+_lib.check(lib.glm4moe_ep_set_timeout_ms(%(ms)d))
+x = torch.randn(T, H, device="cuda").to(torch.bfloat16)
+out = torch.empty_like(x)
+bases = (C.c_void_p * world)(*bufs)
+rc = lib.glm4moe_ep_allreduce_add_rmsnorm(bases, 0, world, 64, x.data_ptr(), None, None, 1e-5, T, H, _lib.BF16,
+                                          out.data_ptr(), None, _lib.stream_ptr())
+res = {"launch_rc": rc}
+try:
+    torch.cuda.synchronize()
+    res["sync"] = "ok"
+except RuntimeError as e:
+    res["sync"] = str(e)[:200]
+res["ep"] = _lib.ep_last_error()          # no CUDA call: works on the poisoned context
+try:
+    _lib.check(719, "after the trap")
+except _lib.Glm4MoeLibraryError as e:
+    res["message"] = str(e)
+print(json.dumps(res))
+sys.stdout.flush()
+import os
+os._exit(0)
+'''
+
+
+def test_a_wait_that_gives_up_is_reported_through_the_host_record():
+    """One GPU: an all-reduce over two 'ranks' of which the second never shows up.  With the limit lowered to 50 ms
+    the kernel gives up instead of spinning for 18 s; the trap that follows kills the CUDA context of that process
+    (hence the subprocess), and `glm4moe_ep_last_error` still says which rank waited for whom."""
+    import json
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", _TIMEOUT_SCRIPT % {"root": root, "ms": 50}], capture_output=True,
+                       text=True, timeout=300)
+    lines = [l for l in r.stdout.splitlines() if l.startswith("{")]
+    assert lines, (r.stdout[-1000:], r.stderr[-2000:])
+    res = json.loads(lines[-1])
+    assert res["launch_rc"] == 0 and res["sync"] != "ok", res
+    ep = res["ep"]
+    assert ep is not None and ep["code"] == -5 and ep["rank"] == 0 and ep["peer"] == 1, res
+    assert ep["site"] == "all-reduce + norm" and ep["waited_for_call"] == 1 and ep["last_flag"] == 0, res
+    assert "timed out" in res["message"] and "rank 0 waited for call 1 of rank 1" in res["message"], res
