@@ -213,6 +213,95 @@ def _cpu_reference_run(shape, dt, weights, T, steps, warmup, budget_s=150.0):
     return T * done / dt_s, dt_s / done * 1e3, cores, done, ref.kind, ref.what
 
 
+def _timed(fn, xs, warm, n):
+    """ms per call of fn over the rotating device batches xs (CUDA events on the current stream)."""
+    for i in range(warm):
+        fn(xs[i % len(xs)])
+    torch.cuda.synchronize()
+    s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s0.record()
+    for i in range(n):
+        fn(xs[i % len(xs)])
+    s1.record()
+    torch.cuda.synchronize()
+    return s0.elapsed_time(s1) / n
+
+
+def _context_legs(moe, shape, dt, dev, weights, T, ms_step, hbm_peak, tc_peak):
+    """Short extra measurements printed beside the headline (N = 1, bf16 arm only); none of them is `value`.
+      gpu_reference  the reference's own Glm4MoeMoE.forward (moe.py:128-176: per-expert cuBLAS F.linear loop, imported
+                     unmodified from oracle/_ref) on THIS GPU with the same weights and batches: SURVEY 2.1's
+                     "kernel to beat" on Blackwell, where the headline ratio is against the 16-core CPU run
+      other_configs  the other BASELINE.json configurations on the same layer: T = 1 decode, T = 4096 prefill (bf16,
+                     same module) and the e4m3 tier at T = 32 (configs[2]; a second module quantised from the same
+                     weights).  Same timing rules: device batches rotated, CUDA events, warm-up first
+    Every leg is fenced: a failure becomes {"error": ...} and never costs the headline line."""
+    out = {"gpu_reference": None, "other_configs": []}
+    with torch.inference_mode():
+        try:
+            from oracle import reference_live as R
+            if R.available():
+                ref = R.build_reference_module(shape, dt, device=str(dev))
+                R.fill_reference_module(ref, weights)
+                xs = [synth.make_tokens(shape, T, dt, b).to(dev) for b in range(8)]
+                ms = _timed(ref, xs, 3, 20)
+                got, want = moe(xs[0]).float(), ref(xs[0]).float()
+                rel = float((got - want).norm() / want.norm())
+                out["gpu_reference"] = {
+                    "what": "reference Glm4MoeMoE.forward (oracle/_ref, unmodified) on the same GPU, same weights, "
+                            f"T={T}, 20 steps after 3 warm-up, CUDA events",
+                    "ms_per_step": ms, "tokens_per_s": T / ms * 1e3, "speedup_device_timed": ms / ms_step,
+                    "rel_l2_ours_vs_reference": rel}
+                del ref
+                torch.cuda.empty_cache()
+            else:
+                out["gpu_reference"] = {"unavailable": "oracle/_ref not installed (python oracle/make_ref.py)"}
+        except Exception as e:  # noqa: BLE001
+            out["gpu_reference"] = {"error": f"{type(e).__name__}: {e}"[:300]}
+
+        def leg(module, Ts, wfmt, peak_tc):
+            xs = [synth.make_tokens(shape, Ts, dt, 100 + b).to(dev) for b in range(8 if Ts <= 256 else 4)]
+            ms = _timed(module, xs, 5, 100 if Ts <= 256 else 20)
+            us = []
+            for x in xs:
+                module(x)
+                us.append(int(torch.unique(module.workspace_view("idx", Ts)).numel()))
+            U = sum(us) / len(us)
+            fp8_ = wfmt != "bf16"
+            by = shape.algorithmic_bytes(Ts, U, weight_bytes=1 if fp8_ else 2, fp8_scales=fp8_)
+            fl = shape.flops_per_token() * Ts
+            tensor_bound = Ts * shape.k / shape.E >= 96
+            return {"workload": f"{shape.name} MoE layer, {wfmt}, T={Ts}", "tokens": Ts, "weights": wfmt,
+                    "ms_per_step": ms, "tokens_per_s": Ts / ms * 1e3, "experts_hit_mean": U,
+                    "layer_GBps": by / ms / 1e6, "layer_TFLOPs": fl / ms / 1e9,
+                    "bound": "tensor" if tensor_bound else "hbm",
+                    "layer_frac": (fl / ms / 1e9 / peak_tc) if tensor_bound else (by / ms / 1e6 / hbm_peak),
+                    "peak": peak_tc if tensor_bound else hbm_peak, "impl": module.last_impl,
+                    "fused_decode_kernel": module.last_fused}
+
+        for Ts in (1, 4096):
+            try:
+                out["other_configs"].append(leg(moe, Ts, "bf16", tc_peak))
+            except Exception as e:  # noqa: BLE001
+                out["other_configs"].append({"workload": f"bf16 T={Ts}", "error": f"{type(e).__name__}: {e}"[:300]})
+        try:
+            torch.set_default_dtype(dt)
+            torch.set_default_device(dev)
+            try:
+                q = glm4_moe_b200.Glm4MoeMoE(_hf_config(shape), max_tokens=256)
+            finally:
+                torch.set_default_device("cpu")
+                torch.set_default_dtype(torch.float32)
+            q.load_local_stacks(weights)
+            q.quantize_fp8(drop_native=True, pow2_scales=False)
+            out["other_configs"].append(leg(q, 32, "fp8_e4m3 (fp32 block scales)", _fp8_peak(tc_peak)[0]))
+            del q
+            torch.cuda.empty_cache()
+        except Exception as e:  # noqa: BLE001
+            out["other_configs"].append({"workload": "fp8 T=32", "error": f"{type(e).__name__}: {e}"[:300]})
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -224,6 +313,8 @@ def main():
     ap.add_argument("--sweep", action="store_true", help="also report T in {1..256, 4096} in `sweep`")
     ap.add_argument("--cpu-steps", type=int, default=0, help="cpu_baseline steps (0 = about 15 s of CPU work)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-context", action="store_true",
+                    help="skip the context legs (reference module on the GPU, the other BASELINE configurations)")
     ap.add_argument("--ep-layout", default="p2p", choices=["p2p", "allreduce", "alltoall"],
                     help="expert-parallel layout for --gpus > 1 (distributed.py): p2p = combine + reduction in "
                          "one kernel over NVLink peer memory, allreduce / alltoall = NCCL")
@@ -547,6 +638,9 @@ def main():
         cpu_baseline = {"value": tps, "unit": UNIT, "cores": cores, "kind": kind, "ms_per_step": ms,
                         "sample": f"{done} steps of the same workload (T={T}) after 2 warm-up: {what}; "
                                   f"torch threads = all {cores} host cores"}
+    context = None
+    if world == 1 and not fp8 and not args.no_context and T <= 256:
+        context = _context_legs(moe, shape, dt, dev, weights, T, ms_step, hbm_peak, tc_peak)
     line = {"metric": METRIC, "value": T * 1e3 / ms_step, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "ms_per_step_median": ms_median,
             "higher_is_better": True,
@@ -565,6 +659,8 @@ def main():
         line["ep_bit_identical"] = ep_bit_identical
     if sweep:
         line["sweep"] = sweep
+    if context:
+        line.update(context)
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
