@@ -55,6 +55,23 @@ def _impls(shape, dt):
     return ["simt", "umma"] if ok else ["simt"]
 
 
+def _log_routing(kind, shape, dt, tokens, flips, against):
+    """The observed count, not only the cap: one JSON line per routing comparison into gpurun_out/routing_flips.jsonl
+    (summarised in profiles/).  `flips` = tokens whose expert SET differs from `against`, each one already explained
+    as a k-th / (k+1)-th boundary pair by the caller."""
+    import json
+    rec = {"test": os.environ.get("PYTEST_CURRENT_TEST", "").split(" ")[0], "kind": kind, "shape": shape.name,
+           "dtype": str(dt), "tokens": int(tokens), "boundary_flips": int(flips), "against": against}
+    out_dir = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+    try:
+        os.makedirs(out_dir, exist_ok=True)
+        with open(os.path.join(out_dir, "routing_flips.jsonl"), "a") as f:
+            f.write(json.dumps(rec) + "\n")
+    except OSError:
+        pass
+    print("routing:", json.dumps(rec))
+
+
 def _explain_routing(idx, logits, x, gate_w, bias, shape, dt, max_frac=2e-2):
     """Kernel routing (`idx` canonical [T,k], `logits` the kernel's own) against the oracle router run on
     this machine's CPU.  Index sets must be equal except on tokens where (a) the two sets differ in exactly
@@ -89,6 +106,7 @@ def _explain_routing(idx, logits, x, gate_w, bias, shape, dt, max_frac=2e-2):
             assert on_boundary, (f"token {t}: mismatch without a logit flip or a sigmoid rounding boundary: experts "
                                  f"{only}, logits {logits[t, only].tolist()}, scores_for_choice "
                                  f"{sc[t, only].tolist()}, bias {bias[only].tolist()}")
+    _log_routing("layer", shape, dt, idx.shape[0], mism.sum(), "oracle router on this host's CPU")
     assert float(mism.float().mean()) <= max_frac, float(mism.float().mean())
     return int(mism.sum())
 
@@ -217,6 +235,7 @@ def _check_router(x, gate_w, bias, shape, dt, ref_idx, ref_w):
             gap = abs(float(sc[t, only[0]] - sc[t, only[1]]))
             assert gap <= 2 * _ulp(dt), f"token {t}: real routing mismatch (gap {gap})"
             assert float(d[t, only].max()) > 0, f"token {t}: mismatch without a logit flip"
+    _log_routing("router", shape, dt, idx.shape[0], mism.sum(), "golden outputs of the real reference")
     assert float(mism.float().mean()) <= 2e-3
     return int(mism.sum())
 

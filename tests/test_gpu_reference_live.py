@@ -53,6 +53,8 @@ def test_cuda_path_vs_real_reference_module_on_the_same_gpu(shape_name, dt, T):
         assert len(only) == 2, f"token {t}: sets differ in more than one expert"
         assert float(dl[t, only].max()) > 0, f"token {t}: routing differs without a logit rounding difference"
         assert abs(float(sc[t, only[0]] - sc[t, only[1]])) <= 2 * _ulp(dt), f"token {t}: not a boundary pair"
+    from test_gpu_parity import _log_routing
+    _log_routing("layer", shape, dt, T, mism.sum(), "the real reference module on the same GPU")
     assert float(mism.float().mean()) <= 0.02
     same = ~mism
     got, want = out.cpu().float()[same], rout.cpu().float()[same]
