@@ -76,18 +76,35 @@ def test_real_decoder_layer_forward_with_the_swapped_block(T):
         finally:
             reset_context()
 
+    seen = {}
+    hook = ref.mlp.gate.register_forward_hook(lambda m, i, o: seen.__setitem__("idx", o[0]))
     for residual in (None, res):
         h_ref, r_ref = run(ref, x, residual)
         h_our, r_our = run(ours, x, residual)
         torch.cuda.synchronize()
         assert h_our.shape == h_ref.shape == (T, 512) and h_our.dtype == dt
         assert torch.equal(r_our, r_ref)                        # attention + norms are the reference's own code
-        # rows whose top-8 set differs (a bf16 boundary logit rounded differently) may be off: at most 3 %
+        # A row may be off ONLY if its token's top-8 set differs between the reference's gate and ours (a bf16
+        # boundary logit rounded differently), the two sets then differ in exactly one expert pair, and that
+        # happens to at most 3 % of the tokens; every other row is held to the tolerance
         d = (h_our.float() - h_ref.float()).abs()
         rms = h_ref.float().pow(2).mean().sqrt()
-        row_ok = (d <= 2e-2 * h_ref.float().abs() + 2e-2 * rms).all(-1)
-        assert float(row_ok.float().mean()) >= 0.97, float(row_ok.float().mean())
-        assert float(d[row_ok].max()) <= 1e-2 + 1e-2 * float(h_ref.float().abs().max())
+        row_ok = (d <= 2e-2 * h_ref.float().abs() + 2e-2 * rms).all(-1).cpu()
+        ri = seen["idx"].long().sort(-1).values.cpu()
+        oi = ours.mlp.workspace_view("idx", T).cpu().long()
+        flipped = (ri != oi).any(-1)
+        for t in torch.nonzero(flipped).flatten().tolist():
+            assert len(set(ri[t].tolist()) ^ set(oi[t].tolist())) == 2, f"token {t}: sets differ in more than one expert"
+        assert float(flipped.float().mean()) <= 0.03, int(flipped.sum())
+        # every token with the same experts: within the reference's own tolerance for this block (rtol = atol = 1e-2,
+        # nanovllm/tests/moe.py:40), no row exempt.  The tighter elementwise bound (2e-2 of |ref| + 2e-2 of the
+        # rms, ~1e-3 absolute here) is below what the reference's bf16 index_add_ accumulation itself scatters on
+        # single elements, so it is held as a rate: 97 % of all rows, as before
+        same = (~flipped).cuda()
+        torch.testing.assert_close(h_our.float()[same], h_ref.float()[same], rtol=1e-2, atol=1e-2)
+        assert float((row_ok | flipped).float().mean()) >= 0.97, float(row_ok.float().mean())
+        assert float(row_ok.float().mean()) >= 0.97 - float(flipped.float().mean())
+    hook.remove()
     # CUDA-graph capture of the real layer forward with our block, decode-shaped (T tokens, static buffers)
     if T <= 32:
         set_context(True, cu, cu, T, T, None, None, None)
@@ -146,7 +163,10 @@ def test_fused_layer_forward_against_the_real_decoder_layer_forward(T):
         finally:
             reset_context()
 
-    want = [run(plain, x, r) for r in (None, res)]
+    want, want_idx = [], []
+    for r_ in (None, res):
+        want.append(run(plain, x, r_))
+        want_idx.append(plain.mlp.workspace_view("idx", T).cpu())
     S.install(sparse_block="ours", share_workspace=False, fused_norm=True)
     try:
         from nanovllm.models.glm4_moe import decode_layer as DL
@@ -162,7 +182,7 @@ def test_fused_layer_forward_against_the_real_decoder_layer_forward(T):
         missing = fused.load_state_dict(plain.state_dict(), strict=True)
         assert not missing.missing_keys and not missing.unexpected_keys
         assert S.fuse_layer(fused) and "_fused_post" in fused.__dict__
-        for (h_ref, r_ref), residual in zip(want, (None, res)):
+        for (h_ref, r_ref), ref_idx, residual in zip(want, want_idx, (None, res)):
             h, r = run(fused, x, residual)
             torch.cuda.synchronize()
             assert h.shape == (T, 512) and h.dtype == dt
@@ -174,10 +194,19 @@ def test_fused_layer_forward_against_the_real_decoder_layer_forward(T):
             assert float((dr > 0).float().mean()) < 5e-2, float((dr > 0).float().mean())
             d = (h.float() - h_ref.float()).abs()
             rms = h_ref.float().pow(2).mean().sqrt()
-            row_ok = (d <= 2e-2 * h_ref.float().abs() + 2e-2 * rms).all(-1)
+            row_ok = (d <= 2e-2 * h_ref.float().abs() + 2e-2 * rms).all(-1).cpu()
             assert bool(torch.isfinite(h.float()).all())
+            # a row may miss ONLY where the one-ulp move of the normalised token made the router pick another
+            # boundary expert (the two top-8 sets then differ in exactly one pair)
+            idx = fused.mlp.workspace_view("idx", T).cpu()
+            flipped = (idx != ref_idx).any(-1)
+            for t in torch.nonzero(flipped).flatten().tolist():
+                assert len(set(idx[t].tolist()) ^ set(ref_idx[t].tolist())) == 2, f"token {t}"
+            same = (~flipped).cuda()
+            torch.testing.assert_close(h.float()[same], h_ref.float()[same], rtol=1e-2, atol=1e-2)   # no row exempt
             if T > 1:       # a single token sitting on a routing boundary would decide the whole comparison
-                assert float(row_ok.float().mean()) >= 0.95, float(row_ok.float().mean())
+                assert float(flipped.float().mean()) <= 0.05, int(flipped.sum())
+                assert float((row_ok | flipped).float().mean()) >= 0.95, float(row_ok.float().mean())
         if T <= 32:
             set_context(True, cu, cu, T, T, None, None, None)
             try:
