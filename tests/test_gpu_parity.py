@@ -72,7 +72,7 @@ def _log_routing(kind, shape, dt, tokens, flips, against):
     print("routing:", json.dumps(rec))
 
 
-def _explain_routing(idx, logits, x, gate_w, bias, shape, dt, max_frac=2e-2):
+def _explain_routing(idx, logits, x, gate_w, bias, shape, dt, max_frac=2e-3):
     """Kernel routing (`idx` canonical [T,k], `logits` the kernel's own) against the oracle router run on
     this machine's CPU.  Index sets must be equal except on tokens where (a) the two sets differ in exactly
     one expert pair, (b) that pair sits on the k-th / (k+1)-th boundary within two model-dtype ulps of
@@ -107,7 +107,9 @@ def _explain_routing(idx, logits, x, gate_w, bias, shape, dt, max_frac=2e-2):
                                  f"{only}, logits {logits[t, only].tolist()}, scores_for_choice "
                                  f"{sc[t, only].tolist()}, bias {bias[only].tolist()}")
     _log_routing("layer", shape, dt, idx.shape[0], mism.sum(), "oracle router on this host's CPU")
-    assert float(mism.float().mean()) <= max_frac, float(mism.float().mean())
+    # observed on B200: at most 1 token in 4096 (profiles/r3_routing_flips.md); the cap leaves room for one token in
+    # a small batch and 8x the observed rate in a large one
+    assert int(mism.sum()) <= max(1, int(max_frac * idx.shape[0])), (int(mism.sum()), idx.shape[0])
     return int(mism.sum())
 
 
@@ -653,8 +655,7 @@ def test_air_decode_vs_oracle(air, T):
         # routing vs the oracle router on the box's CPU: every differing token must be a boundary pair with a
         # logit rounding flip (_explain_routing), none is excused wholesale
         logits = moe.workspace_view("logits", T).cpu()
-        _explain_routing(idx, logits, x, wts["gate_weight"], wts["bias"], shape, dt,
-                         max_frac=1.0 if T == 1 else 2e-2)
+        _explain_routing(idx, logits, x, wts["gate_weight"], wts["bias"], shape, dt)
         rt, _, offs = O.permutation(idx, shape.E)
         assert torch.equal(moe.workspace_view("expert_offsets").cpu(), offs)
         assert torch.equal(moe.workspace_view("row_token").cpu()[:T * shape.k], rt)
@@ -1119,7 +1120,7 @@ def test_glm45_shape_decode_and_prefill():
         idx = moe.workspace_view("idx", T).cpu().long()
         w = moe.workspace_view("w", T).cpu().to(dt)
         logits = moe.workspace_view("logits", T).cpu()
-        _explain_routing(idx, logits, x, wts["gate_weight"], wts["bias"], shape, dt, max_frac=0.13)
+        _explain_routing(idx, logits, x, wts["gate_weight"], wts["bias"], shape, dt)
         truth = O.moe_forward_fp32(x, wts, shape.k, shape.routed_scaling_factor, routing=(idx, w))["out"]
         nbad, rel = _close(out, truth, RTOL_BF16)
         assert nbad == 0 and rel < 6e-3, (nbad, rel)
